@@ -1,0 +1,104 @@
+/* fe_oracle.h — C interface of the CPU ORACLE.
+ *
+ * TEST INFRASTRUCTURE ONLY.  This library is a plain-C++ restatement of libMesh's finite-element
+ * assembly path (FEMap::compute_map + FE::reinit -> Ke/Fe -> DofMap::dof_indices ->
+ * SparseMatrix::add_matrix / NumericVector::add_vector).  It is the checker for the CUDA product in
+ * libmesh_b200/ and the timed CPU baseline of bench.py.  Nothing in the product may include, link or
+ * call it; only tests/, __graft_entry__.smoke() and bench.py's cpu_baseline / --impl reference legs do.
+ *
+ * Parity status: the reference cannot be compiled in the build container (TIMPI / MetaPhysicL
+ * submodules are empty), so element-level arithmetic is pinned by the reference's own unit-test known
+ * answers (tests/fe/fe_test.h, tests/quadrature/quadrature_test.C, tests/numerics/sparse_matrix_test.h,
+ * tests/systems/systems_test.C, tests/base/dof_map_test.C, tests/mesh/mesh_generation_test.C) restated
+ * in tests/test_oracle_*.py; GLOBAL matrix/RHS numbers against a real libMesh build are "parity unpinned".
+ *
+ * Every function cites the reference file:line it follows (paths relative to /root/reference).
+ */
+#ifndef FE_ORACLE_H
+#define FE_ORACLE_H
+
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+/* element types (values = nodes per element) */
+#define ORC_HEX8 8
+#define ORC_HEX27 27
+#define ORC_TET10 10
+
+/* problems */
+#define ORC_POISSON_EX4 1    /* examples/introduction/introduction_ex4/introduction_ex4.C:313-563 */
+#define ORC_ELASTICITY_EX6 2 /* examples/systems_of_equations/systems_of_equations_ex6/systems_of_equations_ex6.C:156-264 (no traction) */
+#define ORC_LAPLACE 3        /* Poisson with f = 0 (config 4) */
+
+/* forcing selection for ORC_POISSON_EX4 */
+#define ORC_FORCING_FD 0        /* the finite-difference Laplacian of introduction_ex4.C:500-537 */
+#define ORC_FORCING_TABULATED 1 /* f at quadrature points supplied by the caller, [n_elem][nq] */
+
+typedef struct orc_mesh orc_mesh;
+typedef struct orc_system orc_system;
+
+/* ---- quadrature / shape tables (src/quadrature, src/fe) ---- */
+/* qorder: libMesh Order of the Gauss rule (3 = THIRD, 5 = FIFTH).  Returns nq; fills up to cap entries. */
+int orc_quadrature(int elem_type, int qorder, int cap, double* points /*nq*3*/, double* weights /*nq*/);
+/* reference shape functions at arbitrary reference points: phi[n][np], dphidxi/eta/zeta[n][np] */
+int orc_shapes(int elem_type, int np, const double* ref_points, double* phi, double* dxi, double* deta, double* dzeta);
+/* FE::reinit on one element with explicit reference points + weights (FE::reinit(elem, pts, wts)):
+ * outputs xyz[np][3], JxW[np], phi[n][np], dphi[n][np][3]; returns 1 if the affine branch was taken, 0 if
+ * general, <0 on a degenerate map. */
+int orc_fe_reinit(int elem_type, const double* node_xyz /*n*3*/, int np, const double* ref_points,
+                  const double* weights, double* xyz, double* JxW, double* phi, double* dphi);
+int orc_has_affine_map(int elem_type, const double* node_xyz);
+
+/* ---- mesh (src/mesh/mesh_generation.C build_cube) ---- */
+orc_mesh* orc_mesh_build_cube(int elem_type, int nx, int ny, int nz, double xmin, double xmax, double ymin,
+                              double ymax, double zmin, double zmax, int renumber_nodes);
+void orc_mesh_free(orc_mesh*);
+int64_t orc_mesh_n_elem(const orc_mesh*);
+int64_t orc_mesh_n_nodes(const orc_mesh*);
+int orc_mesh_nodes_per_elem(const orc_mesh*);
+void orc_mesh_get(const orc_mesh*, double* xyz /*n_nodes*3*/, uint32_t* conn /*n_elem*npe*/,
+                  uint8_t* node_boundary_mask /*n_nodes, bit b = on boundary id b*/);
+/* tests/fe/fe_test.h:40-64 SkewFunc: x += 0.1*y ... ; kind 1 = seeded interior perturbation */
+void orc_mesh_skew(orc_mesh*, int kind, double amplitude, uint64_t seed);
+/* LinearPartitioner (src/partitioning/linear_partitioner.C:36-80) */
+void orc_mesh_partition_linear(orc_mesh*, int n_parts);
+void orc_mesh_set_partition(orc_mesh*, int n_parts, const int32_t* elem_pid);
+void orc_mesh_get_partition(const orc_mesh*, int32_t* elem_pid, int32_t* node_pid);
+
+/* ---- system: dofs, constraints, sparsity, assembly ---- */
+orc_system* orc_system_create(const orc_mesh*, int n_vars);
+void orc_system_free(orc_system*);
+int64_t orc_system_n_dofs(const orc_system*);
+int orc_system_dofs_per_elem(const orc_system*);
+void orc_system_get_dofs(const orc_system*, uint32_t* elem_dofs /*n_elem*nd*/, uint32_t* node_dof_base /*n_nodes*/,
+                         uint32_t* first_dof /*n_parts+1*/);
+/* Dirichlet on the boundary ids in id_mask; kind 0: g = exact_solution (ex4), kind 1: g = 0 (ex6).  Returns count. */
+int64_t orc_system_add_dirichlet(orc_system*, uint32_t id_mask, int kind);
+void orc_system_get_constraints(const orc_system*, uint32_t* dofs, double* values);
+/* SparsityPattern::Build (src/base/sparsity_pattern.C:96-363): returns nnz */
+int64_t orc_system_build_sparsity(orc_system*);
+void orc_system_get_sparsity(const orc_system*, uint64_t* row_ptr /*n_dofs+1*/, uint32_t* col_idx /*nnz*/);
+/* element matrices for elements [e0,e1): Ke [ne][nd*nd] row-major, Fe [ne][nd]; constrained!=0 applies the
+ * (heterogeneous for ex4, homogeneous for ex6) element constraint.  qorder 0 = default of the problem. */
+int orc_element_matrices(const orc_system*, int problem, int qorder, int forcing, const double* f_tab,
+                         int64_t e0, int64_t e1, int constrained, double* Ke, double* Fe);
+/* forcing f(x_q) of ex4 at every quadrature point: f[n_elem][nq], xyz_q[n_elem][nq][3] (either may be NULL) */
+int orc_forcing_at_qps(const orc_system*, int qorder, double* f, double* xyz_q);
+/* full assembly into CSR values (nnz) and rhs (n_dofs), zeroed first.  n_threads 1 = the reference's serial
+ * loop; >1 = OpenMP over elements with atomic adds.  phase_seconds[4] = elem init, Ke, Fe, matrix insertion
+ * (filled for n_threads==1 only).  Returns 0, or <0 on error (degenerate map, missing sparsity entry). */
+int orc_assemble(const orc_system*, int problem, int qorder, int forcing, const double* f_tab, int n_threads,
+                 double* values, double* rhs, double* phase_seconds);
+/* the same loop restricted to elements [e0,e1), all work done and discarded into the same arrays (baseline timing) */
+int orc_assemble_range(const orc_system*, int problem, int qorder, int forcing, const double* f_tab, int n_threads,
+                       int64_t e0, int64_t e1, double* values, double* rhs);
+double orc_exact_solution(double x, double y, double z);
+const char* orc_last_error(void);
+
+#ifdef __cplusplus
+}
+#endif
+#endif

@@ -1,0 +1,394 @@
+// orc_fe.cpp — quadrature rules, Lagrange shape tables and the reference->physical map of the CPU oracle.
+// TEST INFRASTRUCTURE (see fe_oracle.h).  Restates, in libMesh's own operation order:
+//   src/quadrature/quadrature_gauss_1D.C:28-70, src/quadrature/quadrature.C:283-305,
+//   src/quadrature/quadrature_gauss_3D.C:233-290, include/fe/fe_lagrange_shape_1D.h:31-167,
+//   src/fe/fe_lagrange_shape_3D.C:72-413 (hex), :961-1009 and :2179-2330 (TET10),
+//   src/fe/fe_map.C:958-1077, :1167-1244, :1323-1372, src/fe/h1_fe_transformation.C:150-187,
+//   src/geom/cell_hex8.C:121-135, cell_hex27.C:125-166, cell_tet10.C:143-170.
+#include <cmath>
+#include <cstring>
+
+#include "orc_internal.h"
+
+namespace orc {
+
+static thread_local std::string g_err;
+void set_error(const std::string& msg) { g_err = msg; }
+const std::string& get_error() { return g_err; }
+
+// ---- 1D Gauss rules (quadrature_gauss_1D.C:28-70) --------------------------------------------
+static int gauss_1d(int qorder, double* x, double* w) {
+  switch (qorder) {
+    case 0:
+    case 1:
+      x[0] = 0.;
+      w[0] = 2.;
+      return 1;
+    case 2:
+    case 3:
+      x[0] = -std::sqrt(3.0) / 3;
+      x[1] = -x[0];
+      w[0] = 1.;
+      w[1] = w[0];
+      return 2;
+    case 4:
+    case 5:
+      x[0] = -7.7459666924148337703585307995648e-01;
+      x[1] = 0.;
+      x[2] = -x[0];
+      w[0] = 5.0 / 9;
+      w[1] = 8.0 / 9;
+      w[2] = w[0];
+      return 3;
+    default:
+      return 0;
+  }
+}
+
+bool gauss_rule(int elem_type, int qorder, QRule& q) {
+  if (elem_type == ORC_HEX8 || elem_type == ORC_HEX27) {
+    double x[3], w[3];
+    const int np = gauss_1d(qorder, x, w);
+    if (!np) { set_error("unsupported hex quadrature order"); return false; }
+    q.nq = np * np * np;
+    q.pts.resize(3 * q.nq);
+    q.w.resize(q.nq);
+    int p = 0;  // QBase::tensor_product_hex, quadrature.C:283-305
+    for (int k = 0; k < np; k++)
+      for (int j = 0; j < np; j++)
+        for (int i = 0; i < np; i++) {
+          q.pts[3 * p + 0] = x[i];
+          q.pts[3 * p + 1] = x[j];
+          q.pts[3 * p + 2] = x[k];
+          q.w[p] = w[i] * w[j] * w[k];
+          p++;
+        }
+    return true;
+  }
+  if (elem_type == ORC_TET10) {
+    if (qorder != 5) { set_error("tet quadrature: only FIFTH restated"); return false; }
+    // Walkington 14-point rule, quadrature_gauss_3D.C:233-290
+    q.nq = 14;
+    q.pts.assign(42, 0.);
+    q.w.assign(14, 0.);
+    const double a[3] = {0.31088591926330060980, 0.092735250310891226402, 0.045503704125649649492};
+    const double wt[3] = {0.018781320953002641800, 0.012248840519393658257, 0.0070910034628469110730};
+    auto set = [&](int p, double x, double y, double z) {
+      q.pts[3 * p] = x; q.pts[3 * p + 1] = y; q.pts[3 * p + 2] = z;
+    };
+    for (int i = 0; i < 2; ++i) {
+      const int off = 4 * i;
+      const double b = 1. - 3. * a[i];
+      set(off + 0, a[i], a[i], a[i]);
+      set(off + 1, a[i], b, a[i]);
+      set(off + 2, b, a[i], a[i]);
+      set(off + 3, a[i], a[i], b);
+      for (int j = 0; j < 4; ++j) q.w[off + j] = wt[i];
+    }
+    {
+      const int off = 8;
+      const double b = 0.5 * (1. - 2. * a[2]);
+      set(off + 0, b, b, a[2]);
+      set(off + 1, b, a[2], a[2]);
+      set(off + 2, a[2], a[2], b);
+      set(off + 3, a[2], b, a[2]);
+      set(off + 4, b, a[2], b);
+      set(off + 5, a[2], b, b);
+      for (int j = 0; j < 6; ++j) q.w[off + j] = wt[2];
+    }
+    return true;
+  }
+  set_error("unknown element type");
+  return false;
+}
+
+// ---- 1D Lagrange (fe_lagrange_shape_1D.h) ----------------------------------------------------
+static inline double lin(int i, double xi) { return i == 0 ? .5 * (1. - xi) : .5 * (1. + xi); }
+static inline double dlin(int i) { return i == 0 ? -.5 : .5; }
+static inline double quad(int i, double xi) {
+  switch (i) {
+    case 0: return .5 * xi * (xi - 1.);
+    case 1: return .5 * xi * (xi + 1);
+    default: return (1. - xi * xi);
+  }
+}
+static inline double dquad(int i, double xi) {
+  switch (i) {
+    case 0: return xi - .5;
+    case 1: return xi + .5;
+    default: return -2. * xi;
+  }
+}
+
+// fe_lagrange_shape_3D.C:109-111 and :163-165
+static const int H8_I0[8] = {0, 1, 1, 0, 0, 1, 1, 0};
+static const int H8_I1[8] = {0, 0, 1, 1, 0, 0, 1, 1};
+static const int H8_I2[8] = {0, 0, 0, 0, 1, 1, 1, 1};
+static const int H27_I0[27] = {0, 1, 1, 0, 0, 1, 1, 0, 2, 1, 2, 0, 0, 1, 1, 0, 2, 1, 2, 0, 2, 2, 1, 2, 0, 2, 2};
+static const int H27_I1[27] = {0, 0, 1, 1, 0, 0, 1, 1, 0, 2, 1, 2, 0, 0, 1, 1, 0, 2, 1, 2, 2, 0, 2, 1, 2, 2, 2};
+static const int H27_I2[27] = {0, 0, 0, 0, 1, 1, 1, 1, 0, 0, 0, 0, 2, 2, 2, 2, 1, 1, 1, 1, 0, 2, 2, 2, 2, 1, 2};
+
+void shape_table(int elem_type, int np, const double* pts, ShapeTable& t) {
+  const int n = elem_type;
+  t.n = n;
+  t.np = np;
+  t.phi.assign((size_t)n * np, 0.);
+  t.dxi.assign((size_t)n * np, 0.);
+  t.deta.assign((size_t)n * np, 0.);
+  t.dzeta.assign((size_t)n * np, 0.);
+  for (int p = 0; p < np; ++p) {
+    const double xi = pts[3 * p], eta = pts[3 * p + 1], zeta = pts[3 * p + 2];
+    if (elem_type == ORC_HEX8) {
+      const double s[3][2] = {{lin(0, xi), lin(1, xi)}, {lin(0, eta), lin(1, eta)}, {lin(0, zeta), lin(1, zeta)}};
+      const double d[3][2] = {{dlin(0), dlin(1)}, {dlin(0), dlin(1)}, {dlin(0), dlin(1)}};
+      for (int i = 0; i < 8; ++i) {
+        t.phi[i * np + p] = s[0][H8_I0[i]] * s[1][H8_I1[i]] * s[2][H8_I2[i]];
+        t.dxi[i * np + p] = d[0][H8_I0[i]] * s[1][H8_I1[i]] * s[2][H8_I2[i]];
+        t.deta[i * np + p] = s[0][H8_I0[i]] * d[1][H8_I1[i]] * s[2][H8_I2[i]];
+        t.dzeta[i * np + p] = s[0][H8_I0[i]] * s[1][H8_I1[i]] * d[2][H8_I2[i]];
+      }
+    } else if (elem_type == ORC_HEX27) {
+      const double s[3][3] = {{quad(0, xi), quad(1, xi), quad(2, xi)},
+                              {quad(0, eta), quad(1, eta), quad(2, eta)},
+                              {quad(0, zeta), quad(1, zeta), quad(2, zeta)}};
+      const double d[3][3] = {{dquad(0, xi), dquad(1, xi), dquad(2, xi)},
+                              {dquad(0, eta), dquad(1, eta), dquad(2, eta)},
+                              {dquad(0, zeta), dquad(1, zeta), dquad(2, zeta)}};
+      for (int i = 0; i < 27; ++i) {
+        t.phi[i * np + p] = s[0][H27_I0[i]] * s[1][H27_I1[i]] * s[2][H27_I2[i]];
+        t.dxi[i * np + p] = d[0][H27_I0[i]] * s[1][H27_I1[i]] * s[2][H27_I2[i]];
+        t.deta[i * np + p] = s[0][H27_I0[i]] * d[1][H27_I1[i]] * s[2][H27_I2[i]];
+        t.dzeta[i * np + p] = s[0][H27_I0[i]] * s[1][H27_I1[i]] * d[2][H27_I2[i]];
+      }
+    } else {  // TET10, fe_lagrange_shape_3D.C:961-1009, :2179-2330
+      const double z1 = xi, z2 = eta, z3 = zeta;
+      const double z0 = 1. - z1 - z2 - z3;
+      double* ph = &t.phi[p];
+      ph[0 * np] = z0 * (2. * z0 - 1.);
+      ph[1 * np] = z1 * (2. * z1 - 1.);
+      ph[2 * np] = z2 * (2. * z2 - 1.);
+      ph[3 * np] = z3 * (2. * z3 - 1.);
+      ph[4 * np] = 4. * z0 * z1;
+      ph[5 * np] = 4. * z1 * z2;
+      ph[6 * np] = 4. * z2 * z0;
+      ph[7 * np] = 4. * z0 * z3;
+      ph[8 * np] = 4. * z1 * z3;
+      ph[9 * np] = 4. * z2 * z3;
+      // d zeta_k / d(xi,eta,zeta)
+      const double dz[3][4] = {{-1., 1., 0., 0.}, {-1., 0., 1., 0.}, {-1., 0., 0., 1.}};
+      double* out[3] = {&t.dxi[p], &t.deta[p], &t.dzeta[p]};
+      const double z[4] = {z0, z1, z2, z3};
+      for (int j = 0; j < 3; ++j) {
+        const double* g = dz[j];
+        double* o = out[j];
+        o[0 * np] = (4. * z[0] - 1.) * g[0];
+        o[1 * np] = (4. * z[1] - 1.) * g[1];
+        o[2 * np] = (4. * z[2] - 1.) * g[2];
+        o[3 * np] = (4. * z[3] - 1.) * g[3];
+        o[4 * np] = 4. * (z[0] * g[1] + g[0] * z[1]);
+        o[5 * np] = 4. * (z[1] * g[2] + g[1] * z[2]);
+        o[6 * np] = 4. * (z[0] * g[2] + g[0] * z[2]);
+        o[7 * np] = 4. * (z[0] * g[3] + g[0] * z[3]);
+        o[8 * np] = 4. * (z[1] * g[3] + g[1] * z[3]);
+        o[9 * np] = 4. * (z[2] * g[3] + g[2] * z[3]);
+      }
+    }
+  }
+}
+
+void FEData::resize(int n_, int np_) {
+  n = n_;
+  np = np_;
+  xyz.assign((size_t)np * 3, 0.);
+  JxW.assign(np, 0.);
+  jinv.assign((size_t)np * 9, 0.);
+  dphi.assign((size_t)n * np * 3, 0.);
+}
+
+// ---- affine tests ------------------------------------------------------------------------------
+namespace {
+struct P3 { double x, y, z; };
+inline P3 pt(const double* X, int i) { return {X[3 * i], X[3 * i + 1], X[3 * i + 2]}; }
+inline P3 sub(P3 a, P3 b) { return {a.x - b.x, a.y - b.y, a.z - b.z}; }
+inline P3 scale(P3 a, double s) { return {a.x * s, a.y * s, a.z * s}; }
+inline P3 divide(P3 a, double s) { return {a.x / s, a.y / s, a.z / s}; }
+inline double l1(P3 a) { return std::fabs(a.x) + std::fabs(a.y) + std::fabs(a.z); }
+// include/utils/fuzzy_equals.h:96-112 with tol = affine_tol = TOLERANCE*TOLERANCE (include/geom/elem.h:2070)
+inline bool rfe(P3 a, P3 b) {
+  const double tol = 1e-6 * 1e-6;
+  return l1(sub(a, b)) <= tol * (l1(a) + l1(b));
+}
+}  // namespace
+
+bool has_affine_map(int type, const double* X) {
+  auto P = [&](int i) { return pt(X, i); };
+  if (type == ORC_HEX8) {  // cell_hex8.C:121-135
+    P3 v = sub(P(1), P(0));
+    if (!rfe(v, sub(P(2), P(3))) || !rfe(v, sub(P(5), P(4))) || !rfe(v, sub(P(6), P(7)))) return false;
+    v = sub(P(4), P(0));
+    if (!rfe(v, sub(P(7), P(3)))) return false;
+    return true;
+  }
+  if (type == ORC_HEX27) {  // cell_hex27.C:125-166
+    P3 v = sub(P(1), P(0));
+    if (!rfe(v, sub(P(2), P(3))) || !rfe(v, sub(P(5), P(4))) || !rfe(v, sub(P(6), P(7)))) return false;
+    v = divide(v, 2);
+    if (!rfe(v, sub(P(8), P(0))) || !rfe(v, sub(P(10), P(3))) || !rfe(v, sub(P(16), P(4))) ||
+        !rfe(v, sub(P(18), P(7))) || !rfe(v, sub(P(20), P(11))) || !rfe(v, sub(P(21), P(12))) ||
+        !rfe(v, sub(P(23), P(15))) || !rfe(v, sub(P(25), P(19))) || !rfe(v, sub(P(26), P(24))))
+      return false;
+    v = sub(P(4), P(0));
+    if (!rfe(v, sub(P(7), P(3)))) return false;
+    v = divide(v, 2);
+    if (!rfe(v, sub(P(12), P(0))) || !rfe(v, sub(P(13), P(1))) || !rfe(v, sub(P(14), P(2))) ||
+        !rfe(v, sub(P(15), P(3))) || !rfe(v, sub(P(22), P(9))) || !rfe(v, sub(P(24), P(11))))
+      return false;
+    v = divide(sub(P(3), P(0)), 2);
+    if (!rfe(v, sub(P(11), P(0))) || !rfe(v, sub(P(9), P(1))) || !rfe(v, sub(P(17), P(5))) ||
+        !rfe(v, sub(P(19), P(4))))
+      return false;
+    return true;
+  }
+  // TET10, cell_tet10.C:143-170
+  static const int e[6][3] = {{1, 0, 4}, {2, 1, 5}, {2, 0, 6}, {3, 0, 7}, {3, 1, 8}, {3, 2, 9}};
+  for (auto& t : e) {
+    P3 v = sub(P(t[0]), P(t[1]));
+    if (!rfe(v, scale(sub(P(t[2]), P(t[1])), 2))) return false;
+  }
+  return true;
+}
+
+// ---- compute_single_point_map, 3D case (fe_map.C:958-1077) --------------------------------------
+static bool single_point_map(int n, const double* X, const ShapeTable& t, const double* qw, int p, FEData& fe) {
+  const int np = t.np;
+  double x[3] = {0, 0, 0}, dxi[3] = {0, 0, 0}, deta[3] = {0, 0, 0}, dzeta[3] = {0, 0, 0};
+  for (int i = 0; i < n; ++i) {
+    const double* P = &X[3 * i];
+    const double ph = t.phi[i * np + p], a = t.dxi[i * np + p], b = t.deta[i * np + p], c = t.dzeta[i * np + p];
+    for (int d = 0; d < 3; ++d) {
+      x[d] += ph * P[d];
+      dxi[d] += a * P[d];
+      deta[d] += b * P[d];
+      dzeta[d] += c * P[d];
+    }
+  }
+  for (int d = 0; d < 3; ++d) fe.xyz[3 * p + d] = x[d];
+  const double dx_dxi = dxi[0], dy_dxi = dxi[1], dz_dxi = dxi[2];
+  const double dx_deta = deta[0], dy_deta = deta[1], dz_deta = deta[2];
+  const double dx_dzeta = dzeta[0], dy_dzeta = dzeta[1], dz_dzeta = dzeta[2];
+  const double jac = (dx_dxi * (dy_deta * dz_dzeta - dz_deta * dy_dzeta) +
+                      dy_dxi * (dz_deta * dx_dzeta - dx_deta * dz_dzeta) +
+                      dz_dxi * (dx_deta * dy_dzeta - dy_deta * dx_dzeta));
+  if (jac <= 0.) {  // jacobian_tolerance default 0 (fe_map.C:70, check :467)
+    set_error("Jacobian at or under tolerance (degenerate map)");
+    return false;
+  }
+  fe.JxW[p] = jac * qw[p];
+  const double inv_jac = 1. / jac;
+  double* J = &fe.jinv[9 * p];
+  J[0] = (dy_deta * dz_dzeta - dz_deta * dy_dzeta) * inv_jac;
+  J[1] = (dz_deta * dx_dzeta - dx_deta * dz_dzeta) * inv_jac;
+  J[2] = (dx_deta * dy_dzeta - dy_deta * dx_dzeta) * inv_jac;
+  J[3] = (dz_dxi * dy_dzeta - dy_dxi * dz_dzeta) * inv_jac;
+  J[4] = (dx_dxi * dz_dzeta - dz_dxi * dx_dzeta) * inv_jac;
+  J[5] = (dy_dxi * dx_dzeta - dx_dxi * dy_dzeta) * inv_jac;
+  J[6] = (dy_dxi * dz_deta - dz_dxi * dy_deta) * inv_jac;
+  J[7] = (dz_dxi * dx_deta - dx_dxi * dz_deta) * inv_jac;
+  J[8] = (dx_dxi * dy_deta - dy_dxi * dx_deta) * inv_jac;
+  return true;
+}
+
+int fe_reinit(int type, const double* X, const ShapeTable& t, const double* qw, FEData& fe) {
+  const int n = t.n, np = t.np;
+  if (fe.n != n || fe.np != np) fe.resize(n, np);
+  fe.tab = &t;
+  int affine = 0;
+  if (has_affine_map(type, X)) {  // FEMap::compute_affine_map, fe_map.C:1167-1244
+    affine = 1;
+    if (!single_point_map(n, X, t, qw, 0, fe)) return -1;
+    for (int p = 1; p < np; ++p) {
+      double x[3] = {0, 0, 0};
+      for (int i = 0; i < n; ++i)
+        for (int d = 0; d < 3; ++d) x[d] += t.phi[i * np + p] * X[3 * i + d];
+      for (int d = 0; d < 3; ++d) fe.xyz[3 * p + d] = x[d];
+      std::memcpy(&fe.jinv[9 * p], &fe.jinv[0], 9 * sizeof(double));
+      fe.JxW[p] = fe.JxW[0] / qw[0] * qw[p];
+    }
+  } else {  // FEMap::compute_map general branch, fe_map.C:1370-1371
+    for (int p = 0; p < np; ++p)
+      if (!single_point_map(n, X, t, qw, p, fe)) return -1;
+  }
+  // H1FETransformation::map_dphi, h1_fe_transformation.C:150-187
+  for (int i = 0; i < n; ++i)
+    for (int p = 0; p < np; ++p) {
+      const double a = t.dxi[i * np + p], b = t.deta[i * np + p], c = t.dzeta[i * np + p];
+      const double* J = &fe.jinv[9 * p];
+      double* g = &fe.dphi[((size_t)i * np + p) * 3];
+      g[0] = (a * J[0] + b * J[3] + c * J[6]);
+      g[1] = (a * J[1] + b * J[4] + c * J[7]);
+      g[2] = (a * J[2] + b * J[5] + c * J[8]);
+    }
+  return affine;
+}
+
+// examples/introduction/introduction_ex3/exact_solution.C:40-47
+double exact_solution(double x, double y, double z) {
+  static const double pi = std::acos(-1.);
+  return std::cos(.5 * pi * x) * std::sin(.5 * pi * y) * std::cos(.5 * pi * z);
+}
+
+// examples/introduction/introduction_ex4/introduction_ex4.C:500-537 (dim == 3)
+double ex4_forcing(double x, double y, double z) {
+  const double eps = 1.e-3;
+  const double uxx = (exact_solution(x - eps, y, z) + exact_solution(x + eps, y, z) + -2. * exact_solution(x, y, z)) / eps / eps;
+  const double uyy = (exact_solution(x, y - eps, z) + exact_solution(x, y + eps, z) + -2. * exact_solution(x, y, z)) / eps / eps;
+  const double uzz = (exact_solution(x, y, z - eps) + exact_solution(x, y, z + eps) + -2. * exact_solution(x, y, z)) / eps / eps;
+  return -(uxx + uyy + uzz);
+}
+
+}  // namespace orc
+
+namespace orc { const std::string& get_error(); }
+
+extern "C" {
+
+const char* orc_last_error(void) { return orc::get_error().c_str(); }
+double orc_exact_solution(double x, double y, double z) { return orc::exact_solution(x, y, z); }
+
+int orc_quadrature(int elem_type, int qorder, int cap, double* points, double* weights) {
+  orc::QRule q;
+  if (!orc::gauss_rule(elem_type, qorder, q)) return -1;
+  const int m = q.nq < cap ? q.nq : cap;
+  if (points) std::memcpy(points, q.pts.data(), sizeof(double) * 3 * m);
+  if (weights) std::memcpy(weights, q.w.data(), sizeof(double) * m);
+  return q.nq;
+}
+
+int orc_shapes(int elem_type, int np, const double* ref_points, double* phi, double* dxi, double* deta, double* dzeta) {
+  orc::ShapeTable t;
+  orc::shape_table(elem_type, np, ref_points, t);
+  const size_t b = sizeof(double) * t.n * np;
+  if (phi) std::memcpy(phi, t.phi.data(), b);
+  if (dxi) std::memcpy(dxi, t.dxi.data(), b);
+  if (deta) std::memcpy(deta, t.deta.data(), b);
+  if (dzeta) std::memcpy(dzeta, t.dzeta.data(), b);
+  return t.n;
+}
+
+int orc_has_affine_map(int elem_type, const double* node_xyz) { return orc::has_affine_map(elem_type, node_xyz) ? 1 : 0; }
+
+int orc_fe_reinit(int elem_type, const double* node_xyz, int np, const double* ref_points, const double* weights,
+                  double* xyz, double* JxW, double* phi, double* dphi) {
+  orc::ShapeTable t;
+  orc::shape_table(elem_type, np, ref_points, t);
+  orc::FEData fe;
+  const int rc = orc::fe_reinit(elem_type, node_xyz, t, weights, fe);
+  if (rc < 0) return rc;
+  if (xyz) std::memcpy(xyz, fe.xyz.data(), sizeof(double) * 3 * np);
+  if (JxW) std::memcpy(JxW, fe.JxW.data(), sizeof(double) * np);
+  if (phi) std::memcpy(phi, t.phi.data(), sizeof(double) * t.n * np);
+  if (dphi) std::memcpy(dphi, fe.dphi.data(), sizeof(double) * 3 * t.n * np);
+  return rc;
+}
+
+}  // extern "C"
