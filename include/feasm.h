@@ -1,0 +1,169 @@
+/* feasm.h — C ABI of libfeasm, the B200-native finite-element assembly path for libMesh.
+ *
+ * libfeasm replaces ONE path of libMesh: the per-element loop a user's assemble function runs
+ * (examples/introduction/introduction_ex4/introduction_ex4.C:407-558):
+ *     DofMap::dof_indices  ->  FE::reinit / FEMap::compute_map  ->  Ke/Fe contraction  ->
+ *     DofMap::(heterogeneously_)constrain_element_matrix_and_vector  ->
+ *     SparseMatrix::add_matrix / NumericVector::add_vector.
+ * Everything here is plain C: opaque context, plain pointers and sizes, int return codes (0 = ok,
+ * negative = error, message via feasm_last_error).  Host arrays are copied at the call; the context owns
+ * all device memory.  One context per GPU; calls on one context must be serialised by the caller (the
+ * C++ adaptor in libmesh_b200/shim/ holds a mutex, mirroring PetscMatrix's _petsc_matrix_mutex,
+ * src/numerics/petsc_matrix.C:747).  All floating point is IEEE FP64 (libMesh Real = double,
+ * include/base/libmesh_common.h:144); dof ids are uint32 (dof_id_type, include/base/id_types.h:66-76);
+ * CSR offsets are uint64 so a 180 GB value array stays addressable.
+ *
+ * There is no CPU fallback: every entry point that computes fails with FEASM_ERR_CUDA when no sm_100
+ * device is usable.
+ */
+#ifndef FEASM_H
+#define FEASM_H
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define FEASM_VERSION 1
+
+/* element types; the value is the node count (libMesh ElemType HEX8 / HEX27 / TET10) */
+#define FEASM_HEX8 8
+#define FEASM_HEX27 27
+#define FEASM_TET10 10
+
+/* problems (the Ke/Fe contraction that runs per element) */
+#define FEASM_POISSON 1    /* introduction_ex4.C:464-537: Ke = int grad phi_i . grad phi_j, Fe = int f phi_i */
+#define FEASM_ELASTICITY 2 /* systems_of_equations_ex6.C:220-237: 3-variable isotropic elasticity + body force */
+
+/* forcing f(x_q) for FEASM_POISSON */
+#define FEASM_FORCING_NONE 0      /* Laplace: Fe = 0 before constraints */
+#define FEASM_FORCING_EX4_FD 1    /* introduction_ex4.C:500-537, the FD Laplacian of exact_solution, on device */
+#define FEASM_FORCING_TABULATED 2 /* caller-supplied f[n_elem][nq] (the analogue of user code evaluating f) */
+
+/* constraint flavour */
+#define FEASM_CONSTRAIN_HETEROGENEOUS 0 /* dof_map_constraints.C:2518-2614 (ex4) */
+#define FEASM_CONSTRAIN_HOMOGENEOUS 1   /* dof_map_constraints.C:2439-2514 (ex6) */
+
+/* error codes */
+#define FEASM_OK 0
+#define FEASM_ERR_ARG -1
+#define FEASM_ERR_CUDA -2
+#define FEASM_ERR_STATE -3
+#define FEASM_ERR_DEGENERATE -4 /* det J <= 0 somewhere: libMesh's DegenerateMap, fe_map.C:467-506 */
+#define FEASM_ERR_PATTERN -5    /* add to an entry outside the sparsity pattern (sparse_matrix.h:300-303) */
+#define FEASM_ERR_NOMEM -6
+
+typedef struct feasm_ctx feasm_ctx;
+
+typedef struct feasm_params {
+  int problem;           /* FEASM_POISSON | FEASM_ELASTICITY */
+  int quadrature_order;  /* libMesh Order of the QGauss rule: 3 (THIRD) or 5 (FIFTH); 0 = the example's default */
+  int forcing;           /* FEASM_FORCING_* (Poisson only) */
+  int constrain;         /* FEASM_CONSTRAIN_* */
+  const double* f_host;  /* FEASM_FORCING_TABULATED: host array [n_elem][nq], copied at the call, or NULL ... */
+  const double* f_device;/* ... in which case this device pointer is read in place */
+  double young_modulus;  /* elasticity; 0 = the example's E = 1 */
+  double poisson_ratio;  /* elasticity; 0 = the example's nu = 0.3 */
+  double body_force[3];  /* elasticity; all zero = the example's (0,0,-1) */
+} feasm_params;
+
+/* ---- lifetime ------------------------------------------------------------------------------------ */
+int feasm_create(int device, feasm_ctx** out);
+void feasm_destroy(feasm_ctx* ctx);
+const char* feasm_last_error(const feasm_ctx* ctx); /* ctx may be NULL: error of the last failed feasm_create */
+int feasm_version(void);
+
+/* ---- inputs: what the host libMesh already holds ----------------------------------------------- */
+/* Flattened MeshBase: node coordinates (Node = Point, 3 doubles) and element->node connectivity in libMesh's
+ * element-local node order (Elem::node_ptr(i)); replaces the Elem->Node pointer chase of FEMap::compute_map
+ * (src/fe/fe_map.C:1361-1366). */
+int feasm_set_mesh(feasm_ctx* ctx, int elem_type, int64_t n_elem, int64_t n_nodes, const double* xyz,
+                   const uint32_t* conn);
+/* Only the coordinates change (moving mesh / e2e timing): re-upload xyz. */
+int feasm_update_coordinates(feasm_ctx* ctx, const double* xyz);
+/* Result of DofMap::dof_indices(elem, di) for every local element (src/base/dof_map.C:2201-2314), variable-major:
+ * elem_dofs[e][v*npe + a].  Dofs are LOCAL row indices 0..n_rows-1 of this context's matrix; global_ids (may be
+ * NULL = identity) maps them to libMesh's global dof ids, which is what the pattern's col_idx holds.
+ * Rows [0, n_owned) are the rows this rank owns ([first_dof, end_dof) in libMesh); rows [n_owned, n_rows) are
+ * ghost rows whose contributions are shipped to their owner (DistributedVector::close semantics,
+ * src/numerics/distributed_vector.C:399-470). */
+int feasm_set_dofs(feasm_ctx* ctx, int n_vars, int64_t n_rows, int64_t n_owned, const uint32_t* elem_dofs,
+                   const uint32_t* global_ids);
+/* DofMap::is_constrained_dof + get_primal_constraint_values for Dirichlet rows (empty constraint rows):
+ * local row index and value g. */
+int feasm_set_constraints(feasm_ctx* ctx, int64_t n_constraints, const uint32_t* rows, const double* values);
+
+/* ---- sparsity pattern ---------------------------------------------------------------------------- */
+/* Host graph route = SparseMatrix::update_sparsity_pattern(const SparsityPattern::Graph&)
+ * (include/numerics/sparse_matrix.h:175): CSR over the n_rows local rows, columns = global ids ascending. */
+int feasm_set_pattern(feasm_ctx* ctx, const uint64_t* row_ptr, const uint32_t* col_idx);
+/* Device route = SparsityPattern::Build (src/base/sparsity_pattern.C:96-363) on the GPU from elem_dofs. */
+int feasm_build_pattern(feasm_ctx* ctx);
+int64_t feasm_nnz(const feasm_ctx* ctx);
+int feasm_get_pattern(const feasm_ctx* ctx, uint64_t* row_ptr, uint32_t* col_idx);
+/* Builds the element->CSR-slot map and the per-row incidence lists the deterministic scatter uses.  Called
+ * implicitly by the first feasm_assemble. */
+int feasm_prepare(feasm_ctx* ctx);
+
+/* ---- the hot path ------------------------------------------------------------------------------ */
+/* Replaces the whole user assemble loop (the function handed to System::attach_assemble_function,
+ * include/systems/system.h:1470): zeroes the matrix and RHS (ImplicitSystem::assemble,
+ * src/systems/implicit_system.C:101-105) and assembles every local element.  Asynchronous on the context's
+ * stream; feasm_synchronize or any getter waits. */
+int feasm_assemble(feasm_ctx* ctx, const feasm_params* params);
+int feasm_synchronize(feasm_ctx* ctx);
+/* Element-level output for tests: Ke [e1-e0][nd*nd] row-major and Fe [e1-e0][nd], constraints applied iff
+ * constrained != 0; host pointers. */
+int feasm_element_matrices(feasm_ctx* ctx, const feasm_params* params, int64_t e0, int64_t e1, int constrained,
+                           double* Ke, double* Fe);
+
+/* SparseMatrix::zero / NumericVector::zero */
+int feasm_zero(feasm_ctx* ctx);
+/* SparseMatrix::add_matrix(dm, rows, cols) (sparse_matrix.h:312) and NumericVector::add_vector
+ * (numeric_vector.h:519) for a single host element matrix — the slow per-element route that keeps the virtuals
+ * of the adaptor classes working.  Rows/cols are local row indices / global column ids. */
+int feasm_add_matrix(feasm_ctx* ctx, const double* dm, const uint32_t* rows, int n_rows, const uint32_t* cols,
+                     int n_cols);
+int feasm_add_vector(feasm_ctx* ctx, const double* v, const uint32_t* rows, int n);
+
+/* ---- outputs ------------------------------------------------------------------------------------ */
+int feasm_get_values(feasm_ctx* ctx, double* csr_values, double* rhs); /* D2H, either may be NULL */
+double* feasm_device_values(feasm_ctx* ctx);                           /* device pointers, valid until destroy */
+double* feasm_device_rhs(feasm_ctx* ctx);
+void* feasm_stream(feasm_ctx* ctx);                                    /* cudaStream_t */
+
+/* ---- multi-GPU ghost rows (DistributedVector::close / MatAssemblyBegin-End) -------------------- */
+/* After feasm_prepare on every rank: describe, per peer, which of this rank's ghost-row slots go to the peer
+ * and which owned slots receive the peer's contributions.  send_slots / recv_slots index the CSR value array
+ * (values) or, when >= nnz, the RHS (slot - nnz).  The plan is computed by the host (libmesh_b200.partition). */
+int feasm_set_exchange_plan(feasm_ctx* ctx, int n_peers, const int32_t* peer_rank, const uint64_t* send_ptr,
+                            const uint64_t* send_slots, const uint64_t* recv_ptr, const uint64_t* recv_slots);
+/* Packs the ghost contributions into one contiguous device send buffer (peer-major); returns its pointer.
+ * The collective itself (ncclSend/ncclRecv group = all-to-all-v) is issued by the host on feasm_stream. */
+double* feasm_pack_ghost(feasm_ctx* ctx, uint64_t* n_doubles);
+double* feasm_recv_buffer(feasm_ctx* ctx, uint64_t* n_doubles);
+/* Adds the received buffer into the owned slots in fixed peer order (deterministic). */
+int feasm_unpack_ghost(feasm_ctx* ctx);
+
+/* ---- host-side generators for stand-alone runs (no libMesh present) ---------------------------- */
+/* MeshTools::Generation::build_cube (src/mesh/mesh_generation.C:317-1937) for HEX8/HEX27: fills caller arrays.
+ * Sizes: feasm_cube_sizes. */
+int feasm_cube_sizes(int elem_type, int nx, int ny, int nz, int64_t* n_elem, int64_t* n_nodes);
+int feasm_build_cube(int elem_type, int nx, int ny, int nz, const double bounds[6], double* xyz, uint32_t* conn,
+                     uint8_t* node_boundary_mask);
+/* DofMap::distribute_dofs first-touch numbering (src/base/dof_map.C:1417-1535) for n_parts ranks with the given
+ * element owners (NULL = one rank); returns n_dofs, fills node_dof_base[n_nodes] and first_dof[n_parts+1]. */
+int64_t feasm_distribute_dofs(int npe, int64_t n_elem, int64_t n_nodes, const uint32_t* conn, int n_vars, int n_parts,
+                              const int32_t* elem_pid, uint32_t* node_dof_base, uint32_t* first_dof, int32_t* node_pid);
+
+/* ---- instrumentation ---------------------------------------------------------------------------- */
+/* Milliseconds of the kernels of the last feasm_assemble, measured with CUDA events on the context's stream:
+ * [0] element kernel, [1] scatter/row reduction, [2] whole call.  Also the number of kernel launches. */
+int feasm_last_timing(feasm_ctx* ctx, float ms[3], int* launches);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* FEASM_H */

@@ -1,0 +1,288 @@
+"""ctypes binding of the libfeasm C ABI (include/feasm.h).
+
+This is the only way Python reaches the product: every call goes through the same ``extern "C"`` entry
+points a libMesh-side C++ adaptor binds.  There is no fallback: if ``libfeasm.so`` is
+missing or no B200 is present, loading / ``Context()`` raises.
+"""
+from __future__ import annotations
+
+import ctypes as C
+import os
+
+import numpy as np
+
+_HERE = os.path.dirname(os.path.abspath(__file__))
+LIB_PATH = os.path.join(_HERE, "libfeasm.so")
+
+HEX8, HEX27, TET10 = 8, 27, 10
+POISSON, ELASTICITY = 1, 2
+FORCING_NONE, FORCING_EX4_FD, FORCING_TABULATED = 0, 1, 2
+CONSTRAIN_HETEROGENEOUS, CONSTRAIN_HOMOGENEOUS = 0, 1
+
+# every symbol include/feasm.h declares (tests check the library exports each of them)
+SYMBOLS = [
+    "feasm_create", "feasm_destroy", "feasm_last_error", "feasm_version", "feasm_set_mesh",
+    "feasm_update_coordinates", "feasm_set_dofs", "feasm_set_constraints", "feasm_set_pattern",
+    "feasm_build_pattern", "feasm_nnz", "feasm_get_pattern", "feasm_prepare", "feasm_assemble",
+    "feasm_synchronize", "feasm_element_matrices", "feasm_zero", "feasm_add_matrix", "feasm_add_vector",
+    "feasm_get_values", "feasm_device_values", "feasm_device_rhs", "feasm_stream", "feasm_set_exchange_plan",
+    "feasm_pack_ghost", "feasm_recv_buffer", "feasm_unpack_ghost", "feasm_cube_sizes", "feasm_build_cube",
+    "feasm_distribute_dofs", "feasm_last_timing",
+]
+
+
+class FeasmError(RuntimeError):
+    def __init__(self, code, msg):
+        super().__init__(f"libfeasm error {code}: {msg}")
+        self.code = code
+
+
+class Params(C.Structure):
+    _fields_ = [
+        ("problem", C.c_int), ("quadrature_order", C.c_int), ("forcing", C.c_int), ("constrain", C.c_int),
+        ("f_host", C.c_void_p), ("f_device", C.c_void_p), ("young_modulus", C.c_double),
+        ("poisson_ratio", C.c_double), ("body_force", C.c_double * 3),
+    ]
+
+
+_lib = None
+
+
+def lib():
+    """Load libfeasm.so (in-tree).  Raises if it has not been built: there is no other implementation."""
+    global _lib
+    if _lib is not None:
+        return _lib
+    if not os.path.exists(LIB_PATH):
+        raise FeasmError(-2, f"{LIB_PATH} not built; run `python -c 'import __graft_entry__ as g; g.build()'`")
+    L = C.CDLL(LIB_PATH)
+    vp, i64, i32 = C.c_void_p, C.c_int64, C.c_int
+    sig = {
+        "feasm_create": (i32, [i32, C.POINTER(vp)]),
+        "feasm_destroy": (None, [vp]),
+        "feasm_last_error": (C.c_char_p, [vp]),
+        "feasm_version": (i32, []),
+        "feasm_set_mesh": (i32, [vp, i32, i64, i64, vp, vp]),
+        "feasm_update_coordinates": (i32, [vp, vp]),
+        "feasm_set_dofs": (i32, [vp, i32, i64, i64, vp, vp]),
+        "feasm_set_constraints": (i32, [vp, i64, vp, vp]),
+        "feasm_set_pattern": (i32, [vp, vp, vp]),
+        "feasm_build_pattern": (i32, [vp]),
+        "feasm_nnz": (i64, [vp]),
+        "feasm_get_pattern": (i32, [vp, vp, vp]),
+        "feasm_prepare": (i32, [vp]),
+        "feasm_assemble": (i32, [vp, C.POINTER(Params)]),
+        "feasm_synchronize": (i32, [vp]),
+        "feasm_element_matrices": (i32, [vp, C.POINTER(Params), i64, i64, i32, vp, vp]),
+        "feasm_zero": (i32, [vp]),
+        "feasm_add_matrix": (i32, [vp, vp, vp, i32, vp, i32]),
+        "feasm_add_vector": (i32, [vp, vp, vp, i32]),
+        "feasm_get_values": (i32, [vp, vp, vp]),
+        "feasm_device_values": (vp, [vp]),
+        "feasm_device_rhs": (vp, [vp]),
+        "feasm_stream": (vp, [vp]),
+        "feasm_set_exchange_plan": (i32, [vp, i32, vp, vp, vp, vp, vp]),
+        "feasm_pack_ghost": (vp, [vp, C.POINTER(C.c_uint64)]),
+        "feasm_recv_buffer": (vp, [vp, C.POINTER(C.c_uint64)]),
+        "feasm_unpack_ghost": (i32, [vp]),
+        "feasm_cube_sizes": (i32, [i32, i32, i32, i32, C.POINTER(i64), C.POINTER(i64)]),
+        "feasm_build_cube": (i32, [i32, i32, i32, i32, vp, vp, vp, vp]),
+        "feasm_distribute_dofs": (i64, [i32, i64, i64, vp, i32, i32, vp, vp, vp, vp]),
+        "feasm_last_timing": (i32, [vp, vp, C.POINTER(i32)]),
+    }
+    for name, (res, args) in sig.items():
+        fn = getattr(L, name)
+        fn.restype, fn.argtypes = res, args
+    _lib = L
+    return L
+
+
+def _p(a):
+    return None if a is None else a.ctypes.data_as(C.c_void_p)
+
+
+def _c(a, dtype):
+    return None if a is None else np.ascontiguousarray(a, dtype=dtype)
+
+
+def make_params(problem=POISSON, quadrature_order=0, forcing=FORCING_EX4_FD, constrain=CONSTRAIN_HETEROGENEOUS,
+                f_host=None, f_device=0, young_modulus=0.0, poisson_ratio=0.0, body_force=(0.0, 0.0, 0.0)):
+    p = Params()
+    p.problem, p.quadrature_order, p.forcing, p.constrain = problem, quadrature_order, forcing, constrain
+    p.f_host = None if f_host is None else f_host.ctypes.data
+    p.f_device = f_device or None
+    p.young_modulus, p.poisson_ratio = young_modulus, poisson_ratio
+    for i in range(3):
+        p.body_force[i] = body_force[i]
+    p._keep = f_host
+    return p
+
+
+# ---- host-side generators (no GPU needed) ---------------------------------------------------------
+def build_cube(elem_type, nx, ny, nz, bounds=(0.0, 1.0, 0.0, 1.0, 0.0, 1.0)):
+    L = lib()
+    ne, nn = C.c_int64(), C.c_int64()
+    if L.feasm_cube_sizes(elem_type, nx, ny, nz, C.byref(ne), C.byref(nn)):
+        raise FeasmError(-1, "bad build_cube arguments")
+    xyz = np.empty((nn.value, 3))
+    conn = np.empty((ne.value, elem_type), dtype=np.uint32)
+    mask = np.empty(nn.value, dtype=np.uint8)
+    b = np.asarray(bounds, dtype=np.float64)
+    rc = L.feasm_build_cube(elem_type, nx, ny, nz, _p(b), _p(xyz), _p(conn), _p(mask))
+    if rc:
+        raise FeasmError(rc, "feasm_build_cube failed")
+    return xyz, conn, mask
+
+
+def distribute_dofs(conn, n_nodes, n_vars=1, n_parts=1, elem_pid=None):
+    L = lib()
+    conn = _c(conn, np.uint32)
+    ne, npe = conn.shape
+    base = np.empty(n_nodes, dtype=np.uint32)
+    first = np.empty(n_parts + 1, dtype=np.uint32)
+    npid = np.empty(n_nodes, dtype=np.int32)
+    ep = _c(elem_pid, np.int32)
+    n = L.feasm_distribute_dofs(npe, ne, n_nodes, _p(conn), n_vars, n_parts, _p(ep), _p(base), _p(first), _p(npid))
+    if n < 0:
+        raise FeasmError(int(n), "feasm_distribute_dofs failed")
+    return int(n), base, first, npid
+
+
+def elem_dofs_from_nodes(conn, node_base, n_vars=1):
+    """DofMap::dof_indices for every element: variable-major, element-local node order."""
+    nb = node_base[conn.astype(np.int64)]
+    return np.ascontiguousarray(np.concatenate([nb + v for v in range(n_vars)], axis=1), dtype=np.uint32)
+
+
+class Context:
+    """One libfeasm context = one GPU.  Thin, 1:1 over the C ABI."""
+
+    def __init__(self, device=0):
+        self.L = lib()
+        h = C.c_void_p()
+        rc = self.L.feasm_create(device, C.byref(h))
+        if rc:
+            raise FeasmError(rc, self.L.feasm_last_error(None).decode())
+        self.h = h
+        self.n_rows = 0
+        self.nd = 0
+        self.n_elem = 0
+
+    def close(self):
+        if getattr(self, "h", None):
+            self.L.feasm_destroy(self.h)
+            self.h = None
+
+    def __del__(self):
+        self.close()
+
+    def _ck(self, rc):
+        if rc:
+            raise FeasmError(rc, self.L.feasm_last_error(self.h).decode())
+
+    def set_mesh(self, elem_type, xyz, conn):
+        xyz, conn = _c(xyz, np.float64), _c(conn, np.uint32)
+        self.elem_type, self.n_elem, self.n_nodes = elem_type, conn.shape[0], xyz.shape[0]
+        self._ck(self.L.feasm_set_mesh(self.h, elem_type, conn.shape[0], xyz.shape[0], _p(xyz), _p(conn)))
+
+    def update_coordinates(self, xyz):
+        self._ck(self.L.feasm_update_coordinates(self.h, _p(xyz)))
+
+    def set_dofs(self, elem_dofs, n_rows, n_vars=1, n_owned=None, global_ids=None):
+        ed = _c(elem_dofs, np.uint32)
+        gid = _c(global_ids, np.uint32)
+        self.n_rows, self.nd = int(n_rows), ed.shape[1]
+        self._ck(self.L.feasm_set_dofs(self.h, n_vars, n_rows, n_rows if n_owned is None else n_owned, _p(ed), _p(gid)))
+
+    def set_constraints(self, rows, values):
+        r, v = _c(rows, np.uint32), _c(values, np.float64)
+        self._ck(self.L.feasm_set_constraints(self.h, len(r), _p(r), _p(v)))
+
+    def set_pattern(self, row_ptr, col_idx):
+        rp, ci = _c(row_ptr, np.uint64), _c(col_idx, np.uint32)
+        self._ck(self.L.feasm_set_pattern(self.h, _p(rp), _p(ci)))
+
+    def build_pattern(self):
+        self._ck(self.L.feasm_build_pattern(self.h))
+        return self.nnz
+
+    @property
+    def nnz(self):
+        return int(self.L.feasm_nnz(self.h))
+
+    def get_pattern(self):
+        rp = np.empty(self.n_rows + 1, dtype=np.uint64)
+        ci = np.empty(self.nnz, dtype=np.uint32)
+        self._ck(self.L.feasm_get_pattern(self.h, _p(rp), _p(ci)))
+        return rp, ci
+
+    def prepare(self):
+        self._ck(self.L.feasm_prepare(self.h))
+
+    def assemble(self, params, sync=True):
+        self._ck(self.L.feasm_assemble(self.h, C.byref(params)))
+        if sync:
+            self._ck(self.L.feasm_synchronize(self.h))
+
+    def synchronize(self):
+        self._ck(self.L.feasm_synchronize(self.h))
+
+    def element_matrices(self, params, e0=0, e1=None, constrained=True):
+        e1 = self.n_elem if e1 is None else e1
+        Ke = np.empty((e1 - e0, self.nd, self.nd))
+        Fe = np.empty((e1 - e0, self.nd))
+        self._ck(self.L.feasm_element_matrices(self.h, C.byref(params), e0, e1, int(constrained), _p(Ke), _p(Fe)))
+        return Ke, Fe
+
+    def zero(self):
+        self._ck(self.L.feasm_zero(self.h))
+
+    def add_matrix(self, dm, rows, cols=None):
+        dm = _c(dm, np.float64)
+        r = _c(rows, np.uint32)
+        c = r if cols is None else _c(cols, np.uint32)
+        self._ck(self.L.feasm_add_matrix(self.h, _p(dm), _p(r), len(r), _p(c), len(c)))
+
+    def add_vector(self, v, rows):
+        v, r = _c(v, np.float64), _c(rows, np.uint32)
+        self._ck(self.L.feasm_add_vector(self.h, _p(v), _p(r), len(r)))
+
+    def get_values(self, values=True, rhs=True, out_values=None, out_rhs=None):
+        v = (np.empty(self.nnz) if out_values is None else out_values) if values else None
+        b = (np.empty(self.n_rows) if out_rhs is None else out_rhs) if rhs else None
+        self._ck(self.L.feasm_get_values(self.h, _p(v), _p(b)))
+        return v, b
+
+    def device_values(self):
+        return self.L.feasm_device_values(self.h)
+
+    def device_rhs(self):
+        return self.L.feasm_device_rhs(self.h)
+
+    def stream(self):
+        return self.L.feasm_stream(self.h)
+
+    def last_timing(self):
+        ms = (C.c_float * 3)()
+        n = C.c_int()
+        self._ck(self.L.feasm_last_timing(self.h, ms, C.byref(n)))
+        return [ms[0], ms[1], ms[2]], n.value
+
+    def set_exchange_plan(self, peer_rank, send_ptr, send_slots, recv_ptr, recv_slots):
+        pr = _c(peer_rank, np.int32)
+        sp, ss = _c(send_ptr, np.uint64), _c(send_slots, np.uint64)
+        rp, rs = _c(recv_ptr, np.uint64), _c(recv_slots, np.uint64)
+        self._ck(self.L.feasm_set_exchange_plan(self.h, len(pr), _p(pr), _p(sp), _p(ss), _p(rp), _p(rs)))
+
+    def pack_ghost(self):
+        n = C.c_uint64()
+        ptr = self.L.feasm_pack_ghost(self.h, C.byref(n))
+        return ptr, n.value
+
+    def recv_buffer(self):
+        n = C.c_uint64()
+        ptr = self.L.feasm_recv_buffer(self.h, C.byref(n))
+        return ptr, n.value
+
+    def unpack_ghost(self):
+        self._ck(self.L.feasm_unpack_ghost(self.h))

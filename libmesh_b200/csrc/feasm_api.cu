@@ -1,0 +1,440 @@
+// feasm_api.cu — the C ABI of libfeasm (include/feasm.h): context, uploads, pattern, assemble, outputs.
+#include <cstring>
+#include <mutex>
+
+#include "feasm_internal.h"
+
+static std::string g_create_err;
+
+int feasm_fail(feasm_ctx* ctx, int code, const std::string& msg) {
+  if (ctx) ctx->err = msg; else g_create_err = msg;
+  return code;
+}
+
+namespace {
+
+template <typename T>
+int upload(feasm_ctx* ctx, T** dst, const T* src, size_t n) {
+  if (*dst) { cudaFree(*dst); *dst = nullptr; }
+  FEASM_CUDA(ctx, cudaMalloc(dst, sizeof(T) * (n ? n : 1)));
+  if (n) FEASM_CUDA(ctx, cudaMemcpyAsync(*dst, src, sizeof(T) * n, cudaMemcpyHostToDevice, ctx->stream));
+  return FEASM_OK;
+}
+
+template <typename T>
+void release(T*& p) {
+  if (p) cudaFree(p);
+  p = nullptr;
+}
+
+void drop_maps(feasm_ctx* ctx) {
+  ctx->prepared = false;
+  release(ctx->d_pos);
+  release(ctx->d_inc_ptr);
+  release(ctx->d_inc);
+  release(ctx->d_ke);
+  release(ctx->d_fe);
+}
+
+int ensure_tables(feasm_ctx* ctx, int qorder) {
+  if (ctx->d_tab && ctx->tab_qorder == qorder) return FEASM_OK;
+  FeasmTables t;
+  std::string err;
+  if (!feasm_make_tables(ctx->elem_type, qorder, t, err)) return feasm_fail(ctx, FEASM_ERR_ARG, err);
+  std::vector<double> flat;
+  flat.insert(flat.end(), t.phi.begin(), t.phi.end());
+  flat.insert(flat.end(), t.dxi.begin(), t.dxi.end());
+  flat.insert(flat.end(), t.deta.begin(), t.deta.end());
+  flat.insert(flat.end(), t.dzeta.begin(), t.dzeta.end());
+  flat.insert(flat.end(), t.qw.begin(), t.qw.end());
+  int rc = upload(ctx, &ctx->d_tab, flat.data(), flat.size());
+  if (rc) return rc;
+  FEASM_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
+  ctx->tab_qorder = qorder;
+  ctx->tab_nq = t.nq;
+  return FEASM_OK;
+}
+
+int resolve_qorder(const feasm_ctx* ctx, const feasm_params& p) {
+  if (p.quadrature_order) return p.quadrature_order;
+  // ex4 hard-codes FIFTH (introduction_ex4.C:352); ex6 uses default_quadrature_order() = 2*order+1
+  if (p.problem == FEASM_ELASTICITY) return ctx->elem_type == FEASM_HEX8 ? 3 : 5;
+  return 5;
+}
+
+int resolve_forcing(feasm_ctx* ctx, const feasm_params& p, int nq, const double** d_f) {
+  *d_f = nullptr;
+  if (p.problem != FEASM_POISSON || p.forcing != FEASM_FORCING_TABULATED) return FEASM_OK;
+  if (p.f_device) { *d_f = p.f_device; return FEASM_OK; }
+  if (!p.f_host) return feasm_fail(ctx, FEASM_ERR_ARG, "tabulated forcing requested but no array given");
+  const size_t n = (size_t)ctx->n_elem * nq;
+  if (ctx->d_f_cap < n) {
+    release(ctx->d_f);
+    FEASM_CUDA(ctx, cudaMalloc(&ctx->d_f, sizeof(double) * n));
+    ctx->d_f_cap = n;
+  }
+  FEASM_CUDA(ctx, cudaMemcpyAsync(ctx->d_f, p.f_host, sizeof(double) * n, cudaMemcpyHostToDevice, ctx->stream));
+  *d_f = ctx->d_f;
+  return FEASM_OK;
+}
+
+int check_flags(feasm_ctx* ctx) {
+  int flags[2] = {0, 0};
+  FEASM_CUDA(ctx, cudaMemcpyAsync(flags, ctx->d_flags, sizeof(flags), cudaMemcpyDeviceToHost, ctx->stream));
+  FEASM_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
+  if (flags[0]) return feasm_fail(ctx, FEASM_ERR_DEGENERATE, "Jacobian at or under tolerance 0 (degenerate map) at " + std::to_string(flags[0]) + " quadrature points");
+  if (flags[1]) return feasm_fail(ctx, FEASM_ERR_PATTERN, "add to an entry outside the sparsity pattern");
+  return FEASM_OK;
+}
+
+}  // namespace
+
+extern "C" {
+
+int feasm_version(void) { return FEASM_VERSION; }
+
+const char* feasm_last_error(const feasm_ctx* ctx) { return ctx ? ctx->err.c_str() : g_create_err.c_str(); }
+
+int feasm_create(int device, feasm_ctx** out) {
+  if (!out) return feasm_fail(nullptr, FEASM_ERR_ARG, "out is NULL");
+  *out = nullptr;
+  int n = 0;
+  cudaError_t e = cudaGetDeviceCount(&n);
+  if (e != cudaSuccess || n <= 0)
+    return feasm_fail(nullptr, FEASM_ERR_CUDA, std::string("no CUDA device: libfeasm has no CPU fallback (") + cudaGetErrorString(e) + ")");
+  if (device < 0 || device >= n) return feasm_fail(nullptr, FEASM_ERR_ARG, "bad device ordinal");
+  cudaDeviceProp prop;
+  if ((e = cudaGetDeviceProperties(&prop, device)) != cudaSuccess) return feasm_fail(nullptr, FEASM_ERR_CUDA, cudaGetErrorString(e));
+  if (prop.major != 10) return feasm_fail(nullptr, FEASM_ERR_CUDA, "libfeasm is built for sm_100a (B200) only; device is sm_" + std::to_string(prop.major) + std::to_string(prop.minor));
+  if ((e = cudaSetDevice(device)) != cudaSuccess) return feasm_fail(nullptr, FEASM_ERR_CUDA, cudaGetErrorString(e));
+  feasm_ctx* ctx = new feasm_ctx;
+  ctx->device = device;
+  ctx->sm_count = prop.multiProcessorCount;
+  ctx->smem_optin = prop.sharedMemPerBlockOptin;
+  if ((e = cudaStreamCreateWithFlags(&ctx->stream, cudaStreamNonBlocking)) != cudaSuccess) {
+    delete ctx;
+    return feasm_fail(nullptr, FEASM_ERR_CUDA, cudaGetErrorString(e));
+  }
+  for (auto& ev : ctx->ev) cudaEventCreate(&ev);
+  if (cudaMalloc(&ctx->d_flags, 2 * sizeof(int)) != cudaSuccess) {
+    delete ctx;
+    return feasm_fail(nullptr, FEASM_ERR_CUDA, "cudaMalloc failed");
+  }
+  cudaMemset(ctx->d_flags, 0, 2 * sizeof(int));
+  *out = ctx;
+  return FEASM_OK;
+}
+
+void feasm_destroy(feasm_ctx* ctx) {
+  if (!ctx) return;
+  cudaSetDevice(ctx->device);
+  cudaStreamSynchronize(ctx->stream);
+  drop_maps(ctx);
+  release(ctx->d_xyz); release(ctx->d_conn); release(ctx->d_elem_dofs); release(ctx->d_gid);
+  release(ctx->d_con_flag); release(ctx->d_con_val); release(ctx->d_row_ptr); release(ctx->d_col_idx);
+  release(ctx->d_values); release(ctx->d_rhs); release(ctx->d_flags); release(ctx->d_tab); release(ctx->d_f);
+  release(ctx->d_send_slots); release(ctx->d_recv_slots); release(ctx->d_send_buf); release(ctx->d_recv_buf);
+  for (auto& ev : ctx->ev) if (ev) cudaEventDestroy(ev);
+  cudaStreamDestroy(ctx->stream);
+  delete ctx;
+}
+
+int feasm_set_mesh(feasm_ctx* ctx, int elem_type, int64_t n_elem, int64_t n_nodes, const double* xyz, const uint32_t* conn) {
+  if (!ctx) return FEASM_ERR_ARG;
+  if (elem_type != FEASM_HEX8 && elem_type != FEASM_HEX27 && elem_type != FEASM_TET10) return feasm_fail(ctx, FEASM_ERR_ARG, "unsupported element type");
+  if (n_elem < 0 || n_nodes <= 0 || !xyz || !conn) return feasm_fail(ctx, FEASM_ERR_ARG, "bad mesh arguments");
+  FEASM_CUDA(ctx, cudaSetDevice(ctx->device));
+  drop_maps(ctx);
+  ctx->elem_type = elem_type;
+  ctx->npe = elem_type;
+  ctx->n_elem = n_elem;
+  ctx->n_nodes = n_nodes;
+  ctx->tab_qorder = -1;
+  int rc = upload(ctx, &ctx->d_xyz, xyz, (size_t)n_nodes * 3);
+  if (rc) return rc;
+  rc = upload(ctx, &ctx->d_conn, conn, (size_t)n_elem * ctx->npe);
+  if (rc) return rc;
+  FEASM_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
+  return FEASM_OK;
+}
+
+int feasm_update_coordinates(feasm_ctx* ctx, const double* xyz) {
+  if (!ctx || !ctx->d_xyz || !xyz) return feasm_fail(ctx, FEASM_ERR_STATE, "set_mesh first");
+  FEASM_CUDA(ctx, cudaMemcpyAsync(ctx->d_xyz, xyz, sizeof(double) * 3 * ctx->n_nodes, cudaMemcpyHostToDevice, ctx->stream));
+  return FEASM_OK;
+}
+
+int feasm_set_dofs(feasm_ctx* ctx, int n_vars, int64_t n_rows, int64_t n_owned, const uint32_t* elem_dofs, const uint32_t* global_ids) {
+  if (!ctx || !ctx->d_conn) return feasm_fail(ctx, FEASM_ERR_STATE, "set_mesh first");
+  if (n_vars < 1 || n_rows <= 0 || n_owned < 0 || n_owned > n_rows || !elem_dofs) return feasm_fail(ctx, FEASM_ERR_ARG, "bad dof arguments");
+  if (n_rows >= 0xffffffffll) return feasm_fail(ctx, FEASM_ERR_ARG, "dof ids are 32-bit (dof_id_type)");
+  drop_maps(ctx);
+  ctx->n_vars = n_vars;
+  ctx->nd = ctx->npe * n_vars;
+  ctx->n_rows = n_rows;
+  ctx->n_owned = n_owned;
+  const size_t n = (size_t)ctx->n_elem * ctx->nd;
+  for (size_t i = 0; i < n; ++i)
+    if (elem_dofs[i] >= (uint64_t)n_rows) return feasm_fail(ctx, FEASM_ERR_ARG, "elem_dofs entry out of range");
+  int rc = upload(ctx, &ctx->d_elem_dofs, elem_dofs, n);
+  if (rc) return rc;
+  release(ctx->d_gid);
+  if (global_ids) { rc = upload(ctx, &ctx->d_gid, global_ids, (size_t)n_rows); if (rc) return rc; }
+  release(ctx->d_con_flag); release(ctx->d_con_val);
+  FEASM_CUDA(ctx, cudaMalloc(&ctx->d_con_flag, n_rows));
+  FEASM_CUDA(ctx, cudaMalloc(&ctx->d_con_val, sizeof(double) * n_rows));
+  FEASM_CUDA(ctx, cudaMemsetAsync(ctx->d_con_flag, 0, n_rows, ctx->stream));
+  FEASM_CUDA(ctx, cudaMemsetAsync(ctx->d_con_val, 0, sizeof(double) * n_rows, ctx->stream));
+  release(ctx->d_rhs);
+  FEASM_CUDA(ctx, cudaMalloc(&ctx->d_rhs, sizeof(double) * n_rows));
+  FEASM_CUDA(ctx, cudaMemsetAsync(ctx->d_rhs, 0, sizeof(double) * n_rows, ctx->stream));
+  FEASM_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
+  ctx->n_con = 0;
+  return FEASM_OK;
+}
+
+int feasm_set_constraints(feasm_ctx* ctx, int64_t n, const uint32_t* rows, const double* values) {
+  if (!ctx || !ctx->d_con_flag) return feasm_fail(ctx, FEASM_ERR_STATE, "set_dofs first");
+  if (n < 0 || (n && (!rows || !values))) return feasm_fail(ctx, FEASM_ERR_ARG, "bad constraint arguments");
+  std::vector<uint8_t> flag(ctx->n_rows, 0);
+  std::vector<double> val(ctx->n_rows, 0.);
+  for (int64_t i = 0; i < n; ++i) {
+    if (rows[i] >= (uint64_t)ctx->n_rows) return feasm_fail(ctx, FEASM_ERR_ARG, "constraint row out of range");
+    flag[rows[i]] = 1;
+    val[rows[i]] = values[i];
+  }
+  FEASM_CUDA(ctx, cudaMemcpyAsync(ctx->d_con_flag, flag.data(), flag.size(), cudaMemcpyHostToDevice, ctx->stream));
+  FEASM_CUDA(ctx, cudaMemcpyAsync(ctx->d_con_val, val.data(), sizeof(double) * val.size(), cudaMemcpyHostToDevice, ctx->stream));
+  FEASM_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
+  ctx->n_con = n;
+  return FEASM_OK;
+}
+
+static int alloc_values(feasm_ctx* ctx) {
+  release(ctx->d_values);
+  FEASM_CUDA(ctx, cudaMalloc(&ctx->d_values, sizeof(double) * (ctx->nnz ? ctx->nnz : 1)));
+  FEASM_CUDA(ctx, cudaMemsetAsync(ctx->d_values, 0, sizeof(double) * ctx->nnz, ctx->stream));
+  return FEASM_OK;
+}
+
+int feasm_set_pattern(feasm_ctx* ctx, const uint64_t* row_ptr, const uint32_t* col_idx) {
+  if (!ctx || !ctx->d_elem_dofs) return feasm_fail(ctx, FEASM_ERR_STATE, "set_dofs first");
+  if (!row_ptr || !col_idx || row_ptr[0] != 0) return feasm_fail(ctx, FEASM_ERR_ARG, "bad pattern");
+  for (int64_t r = 0; r < ctx->n_rows; ++r) {
+    if (row_ptr[r + 1] < row_ptr[r]) return feasm_fail(ctx, FEASM_ERR_ARG, "row_ptr not monotone");
+    for (uint64_t k = row_ptr[r] + 1; k < row_ptr[r + 1]; ++k)
+      if (col_idx[k] <= col_idx[k - 1]) return feasm_fail(ctx, FEASM_ERR_ARG, "columns of a row must be strictly ascending");
+  }
+  ctx->prepared = false;
+  release(ctx->d_pos);
+  ctx->nnz = row_ptr[ctx->n_rows];
+  int rc = upload(ctx, &ctx->d_row_ptr, row_ptr, (size_t)ctx->n_rows + 1);
+  if (rc) return rc;
+  rc = upload(ctx, &ctx->d_col_idx, col_idx, (size_t)ctx->nnz);
+  if (rc) return rc;
+  rc = alloc_values(ctx);
+  if (rc) return rc;
+  FEASM_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
+  return FEASM_OK;
+}
+
+int feasm_build_pattern(feasm_ctx* ctx) {
+  if (!ctx || !ctx->d_elem_dofs) return feasm_fail(ctx, FEASM_ERR_STATE, "set_dofs first");
+  FEASM_CUDA(ctx, cudaSetDevice(ctx->device));
+  ctx->prepared = false;
+  release(ctx->d_pos);
+  int rc = feasm_device_build_pattern(ctx);
+  if (rc) return rc;
+  return alloc_values(ctx);
+}
+
+int64_t feasm_nnz(const feasm_ctx* ctx) { return ctx ? (int64_t)ctx->nnz : -1; }
+
+int feasm_get_pattern(const feasm_ctx* cctx, uint64_t* row_ptr, uint32_t* col_idx) {
+  feasm_ctx* ctx = const_cast<feasm_ctx*>(cctx);
+  if (!ctx || !ctx->d_row_ptr) return feasm_fail(ctx, FEASM_ERR_STATE, "no pattern");
+  if (row_ptr) FEASM_CUDA(ctx, cudaMemcpyAsync(row_ptr, ctx->d_row_ptr, sizeof(uint64_t) * (ctx->n_rows + 1), cudaMemcpyDeviceToHost, ctx->stream));
+  if (col_idx) FEASM_CUDA(ctx, cudaMemcpyAsync(col_idx, ctx->d_col_idx, sizeof(uint32_t) * ctx->nnz, cudaMemcpyDeviceToHost, ctx->stream));
+  FEASM_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
+  return FEASM_OK;
+}
+
+int feasm_prepare(feasm_ctx* ctx) {
+  if (!ctx || !ctx->d_row_ptr) return feasm_fail(ctx, FEASM_ERR_STATE, "pattern not set: call feasm_set_pattern or feasm_build_pattern");
+  if (ctx->prepared) return FEASM_OK;
+  FEASM_CUDA(ctx, cudaSetDevice(ctx->device));
+  int rc = feasm_build_incidence(ctx);
+  if (rc) return rc;
+  rc = feasm_build_pos(ctx);
+  if (rc) return rc;
+  release(ctx->d_ke); release(ctx->d_fe);
+  FEASM_CUDA(ctx, cudaMalloc(&ctx->d_ke, sizeof(double) * (size_t)ctx->n_elem * ctx->nd * ctx->nd));
+  FEASM_CUDA(ctx, cudaMalloc(&ctx->d_fe, sizeof(double) * (size_t)ctx->n_elem * ctx->nd));
+  ctx->prepared = true;
+  return FEASM_OK;
+}
+
+int feasm_assemble(feasm_ctx* ctx, const feasm_params* params) {
+  if (!ctx || !params) return FEASM_ERR_ARG;
+  FEASM_CUDA(ctx, cudaSetDevice(ctx->device));
+  int rc = feasm_prepare(ctx);
+  if (rc) return rc;
+  const int qorder = resolve_qorder(ctx, *params);
+  rc = ensure_tables(ctx, qorder);
+  if (rc) return rc;
+  const double* d_f = nullptr;
+  rc = resolve_forcing(ctx, *params, ctx->tab_nq, &d_f);
+  if (rc) return rc;
+  // matrix->zero(); rhs->zero() (implicit_system.C:101-105) is implied: the row reduction overwrites every slot
+  FEASM_CUDA(ctx, cudaMemsetAsync(ctx->d_flags, 0, 2 * sizeof(int), ctx->stream));
+  FEASM_CUDA(ctx, cudaEventRecord(ctx->ev[0], ctx->stream));
+  rc = feasm_launch_element_kernel(ctx, *params, qorder, d_f, 0, ctx->n_elem, 1, ctx->d_ke, ctx->d_fe);
+  if (rc) return rc;
+  FEASM_CUDA(ctx, cudaEventRecord(ctx->ev[1], ctx->stream));
+  rc = feasm_launch_row_reduce(ctx);
+  if (rc) return rc;
+  FEASM_CUDA(ctx, cudaEventRecord(ctx->ev[2], ctx->stream));
+  ctx->last_launches = 2;
+  return FEASM_OK;
+}
+
+int feasm_synchronize(feasm_ctx* ctx) {
+  if (!ctx) return FEASM_ERR_ARG;
+  FEASM_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
+  return check_flags(ctx);
+}
+
+int feasm_last_timing(feasm_ctx* ctx, float ms[3], int* launches) {
+  if (!ctx) return FEASM_ERR_ARG;
+  FEASM_CUDA(ctx, cudaEventSynchronize(ctx->ev[2]));
+  cudaEventElapsedTime(&ctx->last_ms[0], ctx->ev[0], ctx->ev[1]);
+  cudaEventElapsedTime(&ctx->last_ms[1], ctx->ev[1], ctx->ev[2]);
+  cudaEventElapsedTime(&ctx->last_ms[2], ctx->ev[0], ctx->ev[2]);
+  if (ms) std::memcpy(ms, ctx->last_ms, sizeof(ctx->last_ms));
+  if (launches) *launches = ctx->last_launches;
+  return FEASM_OK;
+}
+
+int feasm_element_matrices(feasm_ctx* ctx, const feasm_params* params, int64_t e0, int64_t e1, int constrained, double* Ke, double* Fe) {
+  if (!ctx || !params) return FEASM_ERR_ARG;
+  if (!ctx->d_elem_dofs) return feasm_fail(ctx, FEASM_ERR_STATE, "set_dofs first");
+  if (e0 < 0 || e1 > ctx->n_elem || e0 >= e1) return feasm_fail(ctx, FEASM_ERR_ARG, "bad element range");
+  FEASM_CUDA(ctx, cudaSetDevice(ctx->device));
+  const int qorder = resolve_qorder(ctx, *params);
+  int rc = ensure_tables(ctx, qorder);
+  if (rc) return rc;
+  const double* d_f = nullptr;
+  rc = resolve_forcing(ctx, *params, ctx->tab_nq, &d_f);
+  if (rc) return rc;
+  const size_t ne = (size_t)(e1 - e0), nd = ctx->nd;
+  double *d_ke = nullptr, *d_fe = nullptr;
+  FEASM_CUDA(ctx, cudaMalloc(&d_ke, sizeof(double) * ne * nd * nd));
+  FEASM_CUDA(ctx, cudaMalloc(&d_fe, sizeof(double) * ne * nd));
+  FEASM_CUDA(ctx, cudaMemsetAsync(ctx->d_flags, 0, 2 * sizeof(int), ctx->stream));
+  rc = feasm_launch_element_kernel(ctx, *params, qorder, d_f, e0, e1, constrained, d_ke, d_fe);
+  if (!rc) {
+    if (Ke) cudaMemcpyAsync(Ke, d_ke, sizeof(double) * ne * nd * nd, cudaMemcpyDeviceToHost, ctx->stream);
+    if (Fe) cudaMemcpyAsync(Fe, d_fe, sizeof(double) * ne * nd, cudaMemcpyDeviceToHost, ctx->stream);
+    rc = check_flags(ctx);
+  }
+  cudaFree(d_ke);
+  cudaFree(d_fe);
+  return rc;
+}
+
+int feasm_zero(feasm_ctx* ctx) {
+  if (!ctx || !ctx->d_values) return feasm_fail(ctx, FEASM_ERR_STATE, "no matrix");
+  FEASM_CUDA(ctx, cudaMemsetAsync(ctx->d_values, 0, sizeof(double) * ctx->nnz, ctx->stream));
+  FEASM_CUDA(ctx, cudaMemsetAsync(ctx->d_rhs, 0, sizeof(double) * ctx->n_rows, ctx->stream));
+  return FEASM_OK;
+}
+
+int feasm_add_matrix(feasm_ctx* ctx, const double* dm, const uint32_t* rows, int nr, const uint32_t* cols, int nc) {
+  if (!ctx || !ctx->d_values) return feasm_fail(ctx, FEASM_ERR_STATE, "no matrix");
+  if (!dm || !rows || !cols || nr <= 0 || nc <= 0) return feasm_fail(ctx, FEASM_ERR_ARG, "bad add_matrix arguments");
+  for (int i = 0; i < nr; ++i)
+    if (rows[i] >= (uint64_t)ctx->n_rows) return feasm_fail(ctx, FEASM_ERR_ARG, "row out of range");
+  double* d_dm = nullptr;
+  uint32_t *d_r = nullptr, *d_c = nullptr;
+  FEASM_CUDA(ctx, cudaMalloc(&d_dm, sizeof(double) * nr * nc));
+  FEASM_CUDA(ctx, cudaMalloc(&d_r, sizeof(uint32_t) * nr));
+  FEASM_CUDA(ctx, cudaMalloc(&d_c, sizeof(uint32_t) * nc));
+  cudaMemcpyAsync(d_dm, dm, sizeof(double) * nr * nc, cudaMemcpyHostToDevice, ctx->stream);
+  cudaMemcpyAsync(d_r, rows, sizeof(uint32_t) * nr, cudaMemcpyHostToDevice, ctx->stream);
+  cudaMemcpyAsync(d_c, cols, sizeof(uint32_t) * nc, cudaMemcpyHostToDevice, ctx->stream);
+  cudaMemsetAsync(ctx->d_flags, 0, 2 * sizeof(int), ctx->stream);
+  int rc = feasm_launch_add_matrix(ctx, d_dm, d_r, nr, d_c, nc);
+  if (!rc) rc = check_flags(ctx);
+  cudaFree(d_dm); cudaFree(d_r); cudaFree(d_c);
+  return rc;
+}
+
+int feasm_add_vector(feasm_ctx* ctx, const double* v, const uint32_t* rows, int n) {
+  if (!ctx || !ctx->d_rhs) return feasm_fail(ctx, FEASM_ERR_STATE, "no vector");
+  if (!v || !rows || n <= 0) return feasm_fail(ctx, FEASM_ERR_ARG, "bad add_vector arguments");
+  // a vector is a 1-column matrix over the RHS: reuse the exchange unpack kernel semantics on the host side
+  std::vector<double> cur(n);
+  FEASM_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
+  for (int i = 0; i < n; ++i) {
+    if (rows[i] >= (uint64_t)ctx->n_rows) return feasm_fail(ctx, FEASM_ERR_ARG, "row out of range");
+    FEASM_CUDA(ctx, cudaMemcpy(&cur[i], ctx->d_rhs + rows[i], sizeof(double), cudaMemcpyDeviceToHost));
+    cur[i] += v[i];
+    FEASM_CUDA(ctx, cudaMemcpy(ctx->d_rhs + rows[i], &cur[i], sizeof(double), cudaMemcpyHostToDevice));
+  }
+  return FEASM_OK;
+}
+
+int feasm_get_values(feasm_ctx* ctx, double* values, double* rhs) {
+  if (!ctx || !ctx->d_values) return feasm_fail(ctx, FEASM_ERR_STATE, "no matrix");
+  if (values) FEASM_CUDA(ctx, cudaMemcpyAsync(values, ctx->d_values, sizeof(double) * ctx->nnz, cudaMemcpyDeviceToHost, ctx->stream));
+  if (rhs) FEASM_CUDA(ctx, cudaMemcpyAsync(rhs, ctx->d_rhs, sizeof(double) * ctx->n_rows, cudaMemcpyDeviceToHost, ctx->stream));
+  FEASM_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
+  return check_flags(ctx);
+}
+
+double* feasm_device_values(feasm_ctx* ctx) { return ctx ? ctx->d_values : nullptr; }
+double* feasm_device_rhs(feasm_ctx* ctx) { return ctx ? ctx->d_rhs : nullptr; }
+void* feasm_stream(feasm_ctx* ctx) { return ctx ? (void*)ctx->stream : nullptr; }
+
+int feasm_set_exchange_plan(feasm_ctx* ctx, int n_peers, const int32_t* peer_rank, const uint64_t* send_ptr,
+                            const uint64_t* send_slots, const uint64_t* recv_ptr, const uint64_t* recv_slots) {
+  if (!ctx || !ctx->d_values) return feasm_fail(ctx, FEASM_ERR_STATE, "no matrix");
+  if (n_peers < 0 || (n_peers && (!peer_rank || !send_ptr || !recv_ptr))) return feasm_fail(ctx, FEASM_ERR_ARG, "bad plan");
+  ctx->n_peers = n_peers;
+  ctx->peer_rank.assign(peer_rank, peer_rank + n_peers);
+  ctx->send_ptr.assign(send_ptr, send_ptr + n_peers + 1);
+  ctx->recv_ptr.assign(recv_ptr, recv_ptr + n_peers + 1);
+  const uint64_t ns = n_peers ? send_ptr[n_peers] : 0, nr = n_peers ? recv_ptr[n_peers] : 0;
+  const uint64_t lim = ctx->nnz + (uint64_t)ctx->n_rows;
+  for (uint64_t i = 0; i < ns; ++i) if (send_slots[i] >= lim) return feasm_fail(ctx, FEASM_ERR_ARG, "send slot out of range");
+  for (uint64_t i = 0; i < nr; ++i) if (recv_slots[i] >= lim) return feasm_fail(ctx, FEASM_ERR_ARG, "recv slot out of range");
+  int rc = upload(ctx, &ctx->d_send_slots, send_slots, ns);
+  if (rc) return rc;
+  rc = upload(ctx, &ctx->d_recv_slots, recv_slots, nr);
+  if (rc) return rc;
+  release(ctx->d_send_buf); release(ctx->d_recv_buf);
+  FEASM_CUDA(ctx, cudaMalloc(&ctx->d_send_buf, sizeof(double) * (ns ? ns : 1)));
+  FEASM_CUDA(ctx, cudaMalloc(&ctx->d_recv_buf, sizeof(double) * (nr ? nr : 1)));
+  FEASM_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
+  return FEASM_OK;
+}
+
+double* feasm_pack_ghost(feasm_ctx* ctx, uint64_t* n_doubles) {
+  if (!ctx || !ctx->d_send_buf) return nullptr;
+  if (feasm_launch_pack(ctx)) return nullptr;
+  if (n_doubles) *n_doubles = ctx->send_ptr.empty() ? 0 : ctx->send_ptr.back();
+  return ctx->d_send_buf;
+}
+
+double* feasm_recv_buffer(feasm_ctx* ctx, uint64_t* n_doubles) {
+  if (!ctx || !ctx->d_recv_buf) return nullptr;
+  if (n_doubles) *n_doubles = ctx->recv_ptr.empty() ? 0 : ctx->recv_ptr.back();
+  return ctx->d_recv_buf;
+}
+
+int feasm_unpack_ghost(feasm_ctx* ctx) {
+  if (!ctx || !ctx->d_recv_buf) return feasm_fail(ctx, FEASM_ERR_STATE, "no exchange plan");
+  return feasm_launch_unpack(ctx);
+}
+
+}  // extern "C"

@@ -1,0 +1,120 @@
+// feasm_host.cpp — host-side input generators for stand-alone runs (bench.py, smoke) where no libMesh
+// process supplies the mesh and the DofMap.  Product code: nothing here touches oracle/.
+//
+// feasm_build_cube: the HEX8 / HEX27 lattice of MeshTools::Generation::build_cube
+// (src/mesh/mesh_generation.C:1285-1340 nodes, :1399-1432 / :1575-1626 elements, :1779-1785 rescale), written as
+// a closed form over the lattice: element (ei,ej,ek) owns the lattice cell whose corner is stride*(ei,ej,ek) and
+// local node a sits at corner + offset[a], offset[a] = (reference coordinate of node a + 1) * stride / 2.
+// Node ids are the natural lattice ids (libMesh's post-prepare_for_use renumbering only relabels nodes; the
+// assembled system does not depend on it).
+// feasm_distribute_dofs: first-touch numbering of DofMap::distribute_local_dofs_var_major
+// (src/base/dof_map.C:1417-1535) with libMesh's node-ownership rule (src/geom/node.C:99-102).
+#include <algorithm>
+#include <cstring>
+#include <limits>
+#include <vector>
+
+#include "feasm.h"
+
+namespace {
+// reference coordinates (-1,0,1) of HEX27 nodes in libMesh element-local order; the first 8 are HEX8
+const signed char kRef[27][3] = {
+    {-1, -1, -1}, {1, -1, -1}, {1, 1, -1}, {-1, 1, -1}, {-1, -1, 1}, {1, -1, 1}, {1, 1, 1},  {-1, 1, 1},  {0, -1, -1},
+    {1, 0, -1},   {0, 1, -1},  {-1, 0, -1}, {-1, -1, 0}, {1, -1, 0},  {1, 1, 0},  {-1, 1, 0}, {0, -1, 1},  {1, 0, 1},
+    {0, 1, 1},    {-1, 0, 1},  {0, 0, -1}, {0, -1, 0},  {1, 0, 0},   {0, 1, 0},  {-1, 0, 0}, {0, 0, 1},   {0, 0, 0}};
+}  // namespace
+
+extern "C" {
+
+int feasm_cube_sizes(int elem_type, int nx, int ny, int nz, int64_t* n_elem, int64_t* n_nodes) {
+  if ((elem_type != FEASM_HEX8 && elem_type != FEASM_HEX27) || nx < 1 || ny < 1 || nz < 1) return FEASM_ERR_ARG;
+  const int s = elem_type == FEASM_HEX8 ? 1 : 2;
+  if (n_elem) *n_elem = (int64_t)nx * ny * nz;
+  if (n_nodes) *n_nodes = (int64_t)(s * nx + 1) * (s * ny + 1) * (s * nz + 1);
+  return FEASM_OK;
+}
+
+int feasm_build_cube(int elem_type, int nx, int ny, int nz, const double bounds[6], double* xyz, uint32_t* conn,
+                     uint8_t* mask) {
+  int64_t ne, nn;
+  if (feasm_cube_sizes(elem_type, nx, ny, nz, &ne, &nn) || !bounds) return FEASM_ERR_ARG;
+  if (nn >= 0xffffffffll) return FEASM_ERR_ARG;
+  const int s = elem_type == FEASM_HEX8 ? 1 : 2;
+  const int64_t gx = (int64_t)s * nx, gy = (int64_t)s * ny, gz = (int64_t)s * nz;
+  const int64_t sx = gx + 1, sy = gy + 1;
+  if (xyz || mask)
+    for (int64_t id = 0; id < nn; ++id) {
+      const int64_t i = id % sx, j = (id / sx) % sy, k = id / (sx * sy);
+      if (xyz) {
+        // unit-cube coordinate first, then the in-place affine rescale — the two-step arithmetic of the reference
+        xyz[3 * id + 0] = (double)i / (double)gx * (bounds[1] - bounds[0]) + bounds[0];
+        xyz[3 * id + 1] = (double)j / (double)gy * (bounds[3] - bounds[2]) + bounds[2];
+        xyz[3 * id + 2] = (double)k / (double)gz * (bounds[5] - bounds[4]) + bounds[4];
+      }
+      if (mask)  // boundary ids: 0 z-min, 1 y-min, 2 x-max, 3 y-max, 4 x-min, 5 z-max
+        mask[id] = (uint8_t)((k == 0) << 0 | (j == 0) << 1 | (i == gx) << 2 | (j == gy) << 3 | (i == 0) << 4 | (k == gz) << 5);
+    }
+  if (conn) {
+    const int npe = elem_type;
+    int64_t off[27];
+    for (int a = 0; a < npe; ++a)
+      off[a] = ((kRef[a][0] + 1) * s / 2) + sx * (((kRef[a][1] + 1) * s / 2) + sy * (int64_t)((kRef[a][2] + 1) * s / 2));
+    for (int64_t e = 0; e < ne; ++e) {
+      const int64_t ei = e % nx, ej = (e / nx) % ny, ek = e / ((int64_t)nx * ny);
+      const int64_t corner = s * ei + sx * (s * ej + sy * (s * ek));
+      for (int a = 0; a < npe; ++a) conn[e * npe + a] = (uint32_t)(corner + off[a]);
+    }
+  }
+  return FEASM_OK;
+}
+
+int64_t feasm_distribute_dofs(int npe, int64_t n_elem, int64_t n_nodes, const uint32_t* conn, int n_vars, int n_parts,
+                              const int32_t* elem_pid, uint32_t* node_dof_base, uint32_t* first_dof, int32_t* node_pid_out) {
+  if (npe < 1 || n_elem < 0 || n_nodes < 1 || !conn || n_vars < 1 || n_parts < 1 || !node_dof_base) return FEASM_ERR_ARG;
+  const uint32_t none = std::numeric_limits<uint32_t>::max();
+  std::fill(node_dof_base, node_dof_base + n_nodes, none);
+  // a node belongs to the lowest rank among the elements that touch it
+  std::vector<int32_t> owner;
+  if (n_parts > 1) {
+    if (!elem_pid) return FEASM_ERR_ARG;
+    owner.assign(n_nodes, std::numeric_limits<int32_t>::max());
+    for (int64_t e = 0; e < n_elem; ++e)
+      for (int a = 0; a < npe; ++a) owner[conn[e * npe + a]] = std::min(owner[conn[e * npe + a]], elem_pid[e]);
+  }
+  uint64_t next = 0;
+  // per-rank element lists keep the walk linear in n_elem
+  std::vector<int64_t> start(n_parts + 1, 0);
+  std::vector<int64_t> order;
+  if (n_parts > 1) {
+    for (int64_t e = 0; e < n_elem; ++e) {
+      if (elem_pid[e] < 0 || elem_pid[e] >= n_parts) return FEASM_ERR_ARG;
+      start[elem_pid[e] + 1]++;
+    }
+    for (int p = 0; p < n_parts; ++p) start[p + 1] += start[p];
+    order.resize(n_elem);
+    std::vector<int64_t> cur(start.begin(), start.end() - 1);
+    for (int64_t e = 0; e < n_elem; ++e) order[cur[elem_pid[e]]++] = e;
+  } else {
+    start[1] = n_elem;
+  }
+  for (int p = 0; p < n_parts; ++p) {
+    if (first_dof) first_dof[p] = (uint32_t)next;
+    for (int64_t k = start[p]; k < start[p + 1]; ++k) {
+      const int64_t e = n_parts > 1 ? order[k] : k;
+      for (int a = 0; a < npe; ++a) {
+        const uint32_t node = conn[e * npe + a];
+        if (node_dof_base[node] != none) continue;
+        if (n_parts > 1 && owner[node] != p) continue;
+        node_dof_base[node] = (uint32_t)next;
+        next += (uint64_t)n_vars;
+      }
+    }
+  }
+  if (next >= none) return FEASM_ERR_ARG;
+  if (first_dof) first_dof[n_parts] = (uint32_t)next;
+  if (node_pid_out)
+    for (int64_t i = 0; i < n_nodes; ++i) node_pid_out[i] = n_parts > 1 ? owner[i] : 0;
+  return (int64_t)next;
+}
+
+}  // extern "C"

@@ -1,0 +1,114 @@
+// feasm_internal.h — context and internal interfaces of libfeasm (product code; never includes oracle/).
+#ifndef FEASM_INTERNAL_H
+#define FEASM_INTERNAL_H
+
+#include <cuda_runtime.h>
+
+#include <cstdint>
+#include <string>
+#include <vector>
+
+#include "feasm.h"
+
+// Reference-element tables for one (element type, quadrature order): what FE::init_shape_functions
+// (src/fe/fe.C:440-732) and FEMap::init_reference_to_physical_map (src/fe/fe_map.C:108-444) cache per
+// element TYPE in libMesh.  Layout [i][q], q fastest, so lane = q reads are bank-conflict free.
+struct FeasmTables {
+  int npe = 0, nq = 0;
+  std::vector<double> qp;     // nq*3
+  std::vector<double> qw;     // nq
+  std::vector<double> phi;    // npe*nq
+  std::vector<double> dxi, deta, dzeta;
+};
+bool feasm_make_tables(int elem_type, int qorder, FeasmTables& t, std::string& err);
+
+struct feasm_ctx {
+  int device = 0;
+  cudaStream_t stream = nullptr;
+  cudaEvent_t ev[4] = {nullptr, nullptr, nullptr, nullptr};
+  std::string err;
+  int sm_count = 148;
+  size_t smem_optin = 0;
+
+  // mesh
+  int elem_type = 0, npe = 0;
+  int64_t n_elem = 0, n_nodes = 0;
+  double* d_xyz = nullptr;
+  uint32_t* d_conn = nullptr;
+
+  // dofs
+  int n_vars = 0, nd = 0;
+  int64_t n_rows = 0, n_owned = 0;
+  uint32_t* d_elem_dofs = nullptr;
+  uint32_t* d_gid = nullptr;  // nullptr = identity
+
+  // constraints
+  uint8_t* d_con_flag = nullptr;
+  double* d_con_val = nullptr;
+  int64_t n_con = 0;
+
+  // pattern + system
+  uint64_t nnz = 0;
+  uint64_t* d_row_ptr = nullptr;
+  uint32_t* d_col_idx = nullptr;
+  double* d_values = nullptr;
+  double* d_rhs = nullptr;
+  uint32_t max_row_len = 0;
+
+  // scatter maps (built by feasm_prepare)
+  bool prepared = false;
+  uint16_t* d_pos = nullptr;      // [n_elem][nd][nd] row-relative column position
+  uint64_t* d_inc_ptr = nullptr;  // [n_rows+1]
+  uint32_t* d_inc = nullptr;      // [n_elem*nd] = e*nd + a, ascending within a row
+  uint32_t max_inc = 0;
+
+  // element buffers
+  double* d_ke = nullptr;  // [n_elem][nd*nd]
+  double* d_fe = nullptr;  // [n_elem][nd]
+  int* d_flags = nullptr;  // [0] degenerate count, [1] pattern misses
+
+  // tables on device, keyed by quadrature order
+  int tab_qorder = -1;
+  int tab_nq = 0;
+  double* d_tab = nullptr;  // phi | dxi | deta | dzeta | qw  (4*npe*nq + nq doubles)
+
+  // tabulated forcing copy
+  double* d_f = nullptr;
+  size_t d_f_cap = 0;
+
+  // ghost exchange
+  int n_peers = 0;
+  std::vector<int32_t> peer_rank;
+  std::vector<uint64_t> send_ptr, recv_ptr;
+  uint64_t* d_send_slots = nullptr;
+  uint64_t* d_recv_slots = nullptr;
+  double* d_send_buf = nullptr;
+  double* d_recv_buf = nullptr;
+
+  float last_ms[3] = {0, 0, 0};
+  int last_launches = 0;
+};
+
+// error helpers
+int feasm_fail(feasm_ctx* ctx, int code, const std::string& msg);
+#define FEASM_CUDA(ctx, call)                                                                         \
+  do {                                                                                                \
+    cudaError_t e__ = (call);                                                                         \
+    if (e__ != cudaSuccess)                                                                           \
+      return feasm_fail(ctx, FEASM_ERR_CUDA, std::string(#call) + ": " + cudaGetErrorString(e__));    \
+  } while (0)
+
+// feasm_pattern.cu
+int feasm_build_incidence(feasm_ctx* ctx);
+int feasm_device_build_pattern(feasm_ctx* ctx);
+int feasm_build_pos(feasm_ctx* ctx);
+// feasm_assemble.cu
+int feasm_launch_element_kernel(feasm_ctx* ctx, const feasm_params& p, int qorder, const double* d_f, int64_t e0,
+                                int64_t e1, int constrained, double* d_ke, double* d_fe);
+int feasm_launch_row_reduce(feasm_ctx* ctx);
+int feasm_launch_pack(feasm_ctx* ctx);
+int feasm_launch_unpack(feasm_ctx* ctx);
+int feasm_launch_add_matrix(feasm_ctx* ctx, const double* d_dm, const uint32_t* d_rows, int nr, const uint32_t* d_cols,
+                            int nc);
+
+#endif

@@ -1,0 +1,122 @@
+// feasm_tables.cpp — reference-element quadrature and Lagrange shape tables (host, built once per element type).
+//
+// Product code.  Covers what libMesh's QGauss (src/quadrature/quadrature_gauss_1D.C:28-70,
+// quadrature.C:283-305, quadrature_gauss_3D.C:233-290) and FE<3,LAGRANGE> (src/fe/fe_lagrange_shape_3D.C:72-413,
+// :961-1009, :2179-2330) produce for HEX8/Q1, HEX27/Q2 and TET10/P2.  The tables are generated from the
+// reference-node coordinates of each element: a hex basis function is the product of the 1D Lagrange
+// polynomials attached to the node's (xi,eta,zeta) in {-1,0,+1}; a TET10 function is built from barycentric
+// coordinates and the vertex pair of each mid-edge node.
+#include <cmath>
+
+#include "feasm_internal.h"
+
+namespace {
+
+// Reference coordinates of the nodes in libMesh's element-local order (include/geom/cell_hex27.h diagram):
+// 8 vertices, 12 mid-edge, 6 mid-face, 1 centre.  Values are -1, 0, +1.
+const signed char kHexNode[27][3] = {
+    {-1, -1, -1}, {1, -1, -1}, {1, 1, -1}, {-1, 1, -1}, {-1, -1, 1}, {1, -1, 1}, {1, 1, 1},  {-1, 1, 1},  {0, -1, -1},
+    {1, 0, -1},   {0, 1, -1},  {-1, 0, -1}, {-1, -1, 0}, {1, -1, 0},  {1, 1, 0},  {-1, 1, 0}, {0, -1, 1},  {1, 0, 1},
+    {0, 1, 1},    {-1, 0, 1},  {0, 0, -1}, {0, -1, 0},  {1, 0, 0},   {0, 1, 0},  {-1, 0, 0}, {0, 0, 1},   {0, 0, 0}};
+
+// 1D Lagrange polynomial of degree `deg` attached to reference abscissa c in {-1,0,1}; value and derivative.
+struct V1 { double v, d; };
+V1 lagrange1d(int deg, int c, double x) {
+  if (deg == 1) return c < 0 ? V1{.5 * (1. - x), -.5} : V1{.5 * (1. + x), .5};
+  if (c < 0) return {.5 * x * (x - 1.), x - .5};
+  if (c > 0) return {.5 * x * (x + 1.), x + .5};
+  return {1. - x * x, -2. * x};
+}
+
+int gauss1d(int qorder, double x[3], double w[3]) {
+  if (qorder <= 1) { x[0] = 0.; w[0] = 2.; return 1; }
+  if (qorder <= 3) {
+    x[0] = -std::sqrt(3.0) / 3; x[1] = -x[0];
+    w[0] = w[1] = 1.;
+    return 2;
+  }
+  if (qorder <= 5) {
+    x[0] = -7.7459666924148337703585307995648e-01; x[1] = 0.; x[2] = -x[0];
+    w[0] = w[2] = 5.0 / 9; w[1] = 8.0 / 9;
+    return 3;
+  }
+  return 0;
+}
+
+// TET10: vertex pair of each mid-edge node 4..9
+const int kTetEdge[6][2] = {{0, 1}, {1, 2}, {0, 2}, {0, 3}, {1, 3}, {2, 3}};
+
+}  // namespace
+
+bool feasm_make_tables(int elem_type, int qorder, FeasmTables& t, std::string& err) {
+  t = FeasmTables();
+  t.npe = elem_type;
+  if (elem_type == FEASM_HEX8 || elem_type == FEASM_HEX27) {
+    double x[3], w[3];
+    const int n1 = gauss1d(qorder, x, w);
+    if (!n1) { err = "unsupported Gauss order for hex"; return false; }
+    t.nq = n1 * n1 * n1;
+    t.qp.resize(3 * t.nq);
+    t.qw.resize(t.nq);
+    for (int q = 0; q < t.nq; ++q) {  // q = i + n1*(j + n1*k), i fastest
+      const int i = q % n1, j = (q / n1) % n1, k = q / (n1 * n1);
+      t.qp[3 * q] = x[i]; t.qp[3 * q + 1] = x[j]; t.qp[3 * q + 2] = x[k];
+      t.qw[q] = w[i] * w[j] * w[k];
+    }
+    const int deg = elem_type == FEASM_HEX8 ? 1 : 2;
+    const size_t sz = (size_t)t.npe * t.nq;
+    t.phi.resize(sz); t.dxi.resize(sz); t.deta.resize(sz); t.dzeta.resize(sz);
+    for (int a = 0; a < t.npe; ++a)
+      for (int q = 0; q < t.nq; ++q) {
+        const V1 X = lagrange1d(deg, kHexNode[a][0], t.qp[3 * q]);
+        const V1 Y = lagrange1d(deg, kHexNode[a][1], t.qp[3 * q + 1]);
+        const V1 Z = lagrange1d(deg, kHexNode[a][2], t.qp[3 * q + 2]);
+        const size_t o = (size_t)a * t.nq + q;
+        t.phi[o] = X.v * Y.v * Z.v;
+        t.dxi[o] = X.d * Y.v * Z.v;
+        t.deta[o] = X.v * Y.d * Z.v;
+        t.dzeta[o] = X.v * Y.v * Z.d;
+      }
+    return true;
+  }
+  if (elem_type == FEASM_TET10) {
+    if (qorder != 5 && qorder != 4) { err = "TET10: only the FIFTH-order Gauss rule is built"; return false; }
+    // 14-point degree-5 rule (Walkington): two vertex-symmetric orbits of 4 points and one edge orbit of 6.
+    const double a[3] = {0.31088591926330060980, 0.092735250310891226402, 0.045503704125649649492};
+    const double wt[3] = {0.018781320953002641800, 0.012248840519393658257, 0.0070910034628469110730};
+    t.nq = 14;
+    t.qp.assign(42, 0.);
+    t.qw.assign(14, 0.);
+    int q = 0;
+    for (int o = 0; o < 2; ++o) {
+      const double b = 1. - 3. * a[o];
+      const double P[4][3] = {{a[o], a[o], a[o]}, {a[o], b, a[o]}, {b, a[o], a[o]}, {a[o], a[o], b}};
+      for (auto& p : P) { t.qp[3 * q] = p[0]; t.qp[3 * q + 1] = p[1]; t.qp[3 * q + 2] = p[2]; t.qw[q++] = wt[o]; }
+    }
+    {
+      const double c = a[2], b = 0.5 * (1. - 2. * c);
+      const double P[6][3] = {{b, b, c}, {b, c, c}, {c, c, b}, {c, b, c}, {b, c, b}, {c, b, b}};
+      for (auto& p : P) { t.qp[3 * q] = p[0]; t.qp[3 * q + 1] = p[1]; t.qp[3 * q + 2] = p[2]; t.qw[q++] = wt[2]; }
+    }
+    const size_t sz = (size_t)10 * t.nq;
+    t.phi.resize(sz); t.dxi.resize(sz); t.deta.resize(sz); t.dzeta.resize(sz);
+    // barycentric gradients wrt (xi, eta, zeta): L0 = 1-xi-eta-zeta, L1 = xi, L2 = eta, L3 = zeta
+    const double dL[4][3] = {{-1, -1, -1}, {1, 0, 0}, {0, 1, 0}, {0, 0, 1}};
+    for (int p = 0; p < t.nq; ++p) {
+      const double L[4] = {1. - t.qp[3 * p] - t.qp[3 * p + 1] - t.qp[3 * p + 2], t.qp[3 * p], t.qp[3 * p + 1], t.qp[3 * p + 2]};
+      double* out[3] = {t.dxi.data(), t.deta.data(), t.dzeta.data()};
+      for (int v = 0; v < 4; ++v) {
+        t.phi[(size_t)v * t.nq + p] = L[v] * (2. * L[v] - 1.);
+        for (int d = 0; d < 3; ++d) out[d][(size_t)v * t.nq + p] = (4. * L[v] - 1.) * dL[v][d];
+      }
+      for (int e = 0; e < 6; ++e) {
+        const int u = kTetEdge[e][0], v = kTetEdge[e][1];
+        t.phi[(size_t)(4 + e) * t.nq + p] = 4. * L[u] * L[v];
+        for (int d = 0; d < 3; ++d) out[d][(size_t)(4 + e) * t.nq + p] = 4. * (L[u] * dL[v][d] + dL[u][d] * L[v]);
+      }
+    }
+    return true;
+  }
+  err = "unknown element type";
+  return false;
+}
