@@ -148,7 +148,7 @@ double* feasm_recv_buffer(feasm_ctx* ctx, uint64_t* n_doubles);
 int feasm_unpack_ghost(feasm_ctx* ctx);
 
 /* ---- host-side generators for stand-alone runs (no libMesh present) ---------------------------- */
-/* MeshTools::Generation::build_cube (src/mesh/mesh_generation.C:317-1937) for HEX8/HEX27: fills caller arrays.
+/* MeshTools::Generation::build_cube (src/mesh/mesh_generation.C:317-1937) for HEX8/HEX27/TET10: fills caller arrays.
  * Sizes: feasm_cube_sizes. */
 int feasm_cube_sizes(int elem_type, int nx, int ny, int nz, int64_t* n_elem, int64_t* n_nodes);
 int feasm_build_cube(int elem_type, int nx, int ny, int nz, const double bounds[6], double* xyz, uint32_t* conn,

@@ -12,6 +12,7 @@
 #include <algorithm>
 #include <cstring>
 #include <limits>
+#include <unordered_map>
 #include <vector>
 
 #include "feasm.h"
@@ -22,11 +23,87 @@ const signed char kRef[27][3] = {
     {-1, -1, -1}, {1, -1, -1}, {1, 1, -1}, {-1, 1, -1}, {-1, -1, 1}, {1, -1, 1}, {1, 1, 1},  {-1, 1, 1},  {0, -1, -1},
     {1, 0, -1},   {0, 1, -1},  {-1, 0, -1}, {-1, -1, 0}, {1, -1, 0},  {1, 1, 0},  {-1, 1, 0}, {0, -1, 1},  {1, 0, 1},
     {0, 1, 1},    {-1, 0, 1},  {0, 0, -1}, {0, -1, 0},  {1, 0, 0},   {0, 1, 0},  {-1, 0, 0}, {0, 0, 1},   {0, 0, 0}};
+// HEX27 local nodes of each side: 4 corners in side order, then the side's centre node (src/geom/cell_hex27.C:37-45,
+// columns 0-3 and 8) — all the 24-tet split needs.
+const signed char kSide[6][5] = {{0, 3, 2, 1, 20}, {0, 1, 5, 4, 21}, {1, 2, 6, 5, 22}, {2, 3, 7, 6, 23}, {3, 0, 4, 7, 24}, {4, 5, 6, 7, 25}};
+// TET10 mid-edge node 4+e lies between these two vertices (src/geom/cell_tet10.C edge_nodes_map)
+const signed char kTetEdge[6][2] = {{0, 1}, {1, 2}, {0, 2}, {0, 3}, {1, 3}, {2, 3}};
+
+// build_cube(TET10) (src/mesh/mesh_generation.C:1795-1907): every HEX27 cell is cut into 24 tets
+// (side vertex t, side centre, side vertex t+1, cell centre), then all_second_order() adds one new node per tet
+// edge at first sight while walking the tets in order.  The HEX27 mid-edge lattice nodes end up unused and are
+// dropped (prepare_for_use); ids are compacted in ascending old-id order.
+int build_tet10_cube(int nx, int ny, int nz, const double b[6], double* xyz, uint32_t* conn, uint8_t* mask) {
+  const int64_t gx = 2 * (int64_t)nx, gy = 2 * (int64_t)ny, gz = 2 * (int64_t)nz, sx = gx + 1, sy = gy + 1;
+  const int64_t n_lat = sx * sy * (gz + 1), n_cell = (int64_t)nx * ny * nz;
+  if (n_lat + 40 * n_cell >= 0xffffffffll) return FEASM_ERR_ARG;
+  std::vector<uint32_t> lat_new(n_lat, 0xffffffffu);  // lattice id -> compact id (vertices only)
+  uint32_t next = 0;
+  for (int64_t id = 0; id < n_lat; ++id) {
+    const int odd = (int)((id % sx) & 1) + (int)(((id / sx) % sy) & 1) + (int)((id / (sx * sy)) & 1);
+    if (odd != 1) lat_new[id] = next++;  // corners (0 odd), side centres (2), cell centres (3); mid-edges (1) are orphans
+  }
+  const uint32_t n_vert = next;
+  auto put_vertex = [&](int64_t id) {
+    const int64_t i = id % sx, j = (id / sx) % sy, k = id / (sx * sy);
+    const uint32_t n = lat_new[id];
+    if (xyz) {
+      xyz[3 * (size_t)n + 0] = (double)i / (double)gx * (b[1] - b[0]) + b[0];
+      xyz[3 * (size_t)n + 1] = (double)j / (double)gy * (b[3] - b[2]) + b[2];
+      xyz[3 * (size_t)n + 2] = (double)k / (double)gz * (b[5] - b[4]) + b[4];
+    }
+    if (mask) mask[n] = (uint8_t)((k == 0) << 0 | (j == 0) << 1 | (i == gx) << 2 | (j == gy) << 3 | (i == 0) << 4 | (k == gz) << 5);
+  };
+  if (xyz || mask)
+    for (int64_t id = 0; id < n_lat; ++id)
+      if (lat_new[id] != 0xffffffffu) put_vertex(id);
+  if (!conn) return FEASM_OK;
+  if (!xyz || !mask) return FEASM_ERR_ARG;  // mid-edge nodes are averages of vertex data
+  int64_t off[27];
+  for (int a = 0; a < 27; ++a) off[a] = (kRef[a][0] + 1) + sx * ((kRef[a][1] + 1) + sy * (int64_t)(kRef[a][2] + 1));
+  std::unordered_map<uint64_t, uint32_t> mid;
+  mid.reserve((size_t)(n_cell * 40));
+  (void)n_vert;
+  int64_t t = 0;
+  for (int64_t c = 0; c < n_cell; ++c) {
+    const int64_t ci = c % nx, cj = (c / nx) % ny, ck = c / ((int64_t)nx * ny);
+    const int64_t corner = 2 * ci + sx * (2 * cj + sy * (2 * ck));
+    for (int s = 0; s < 6; ++s)
+      for (int sub = 0; sub < 4; ++sub, ++t) {
+        uint32_t* v = conn + t * 10;
+        v[0] = lat_new[corner + off[kSide[s][sub]]];
+        v[1] = lat_new[corner + off[kSide[s][4]]];
+        v[2] = lat_new[corner + off[kSide[s][(sub + 1) & 3]]];
+        v[3] = lat_new[corner + off[26]];
+        for (int e = 0; e < 6; ++e) {
+          uint32_t p = v[kTetEdge[e][0]], q = v[kTetEdge[e][1]];
+          if (p > q) std::swap(p, q);
+          auto ins = mid.emplace(((uint64_t)p << 32) | q, next);
+          if (ins.second) {
+            for (int d = 0; d < 3; ++d) xyz[3 * (size_t)next + d] = (xyz[3 * (size_t)p + d] + xyz[3 * (size_t)q + d]) / 2.0;
+            mask[next] = mask[p] & mask[q];
+            ++next;
+          }
+          v[4 + e] = ins.first->second;
+        }
+      }
+  }
+  return FEASM_OK;
+}
 }  // namespace
 
 extern "C" {
 
 int feasm_cube_sizes(int elem_type, int nx, int ny, int nz, int64_t* n_elem, int64_t* n_nodes) {
+  if (elem_type == FEASM_TET10 && nx >= 1 && ny >= 1 && nz >= 1) {
+    const int64_t X = nx, Y = ny, Z = nz, cells = X * Y * Z;
+    const int64_t corners = (X + 1) * (Y + 1) * (Z + 1), faces = X * Y * (Z + 1) + X * (Y + 1) * Z + (X + 1) * Y * Z;
+    const int64_t hex_edges = X * (Y + 1) * (Z + 1) + (X + 1) * Y * (Z + 1) + (X + 1) * (Y + 1) * Z;
+    if (n_elem) *n_elem = 24 * cells;
+    // vertices (corners, side centres, cell centres) + one node per tet edge (hex edges, 4 per side, 14 per cell)
+    if (n_nodes) *n_nodes = corners + faces + cells + hex_edges + 4 * faces + 14 * cells;
+    return FEASM_OK;
+  }
   if ((elem_type != FEASM_HEX8 && elem_type != FEASM_HEX27) || nx < 1 || ny < 1 || nz < 1) return FEASM_ERR_ARG;
   const int s = elem_type == FEASM_HEX8 ? 1 : 2;
   if (n_elem) *n_elem = (int64_t)nx * ny * nz;
@@ -39,6 +116,7 @@ int feasm_build_cube(int elem_type, int nx, int ny, int nz, const double bounds[
   int64_t ne, nn;
   if (feasm_cube_sizes(elem_type, nx, ny, nz, &ne, &nn) || !bounds) return FEASM_ERR_ARG;
   if (nn >= 0xffffffffll) return FEASM_ERR_ARG;
+  if (elem_type == FEASM_TET10) return build_tet10_cube(nx, ny, nz, bounds, xyz, conn, mask);
   const int s = elem_type == FEASM_HEX8 ? 1 : 2;
   const int64_t gx = (int64_t)s * nx, gy = (int64_t)s * ny, gz = (int64_t)s * nz;
   const int64_t sx = gx + 1, sy = gy + 1;

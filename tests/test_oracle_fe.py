@@ -1,0 +1,170 @@
+"""Pins the oracle's element-level arithmetic to the known answers of the reference's own unit tests.
+
+Restated from (paths relative to /root/reference):
+  tests/quadrature/quadrature_test.C:591-630 (test3DWeights: exact monomial integrals on hex and tet),
+  tests/fe/fe_test.h:67-110, :671-690, :812-813 (partition of unity, value / gradient reproduction of the linear
+  and quadratic test functions on build_cube meshes, incl. the SkewFunc-skewed mesh :40-64),
+  src/quadrature/quadrature_gauss_1D.C:28-70 and quadrature_gauss_3D.C:257-283 (the literal rule constants).
+"""
+import itertools
+import math
+
+import numpy as np
+import pytest
+
+from oracle import oracle as O
+
+TOL = 1e-12  # tests/quadrature/quadrature_test.C quadrature_tolerance = TOLERANCE*sqrt(TOLERANCE) ~ 1e-9; we are stricter
+
+
+def hex_integral(a, b, c):  # int_{[-1,1]^3} x^a y^b z^c
+    f = lambda p: 0.0 if p % 2 else 2.0 / (p + 1)
+    return f(a) * f(b) * f(c)
+
+
+def tet_integral(a, b, c):  # int over the reference tet = a! b! c! / (a+b+c+3)!
+    return math.factorial(a) * math.factorial(b) * math.factorial(c) / math.factorial(a + b + c + 3)
+
+
+@pytest.mark.parametrize("etype,qorder,nq,exact", [(O.HEX8, 3, 8, 3), (O.HEX8, 5, 27, 5), (O.HEX27, 5, 27, 5), (O.TET10, 5, 14, 5)])
+def test_quadrature_integrates_monomials_exactly(etype, qorder, nq, exact):
+    pts, w = O.quadrature(etype, qorder)
+    assert len(w) == nq
+    for a, b, c in itertools.product(range(exact + 1), repeat=3):
+        if etype == O.TET10 and a + b + c > exact:
+            continue
+        if etype != O.TET10 and max(a, b, c) > exact:
+            continue
+        got = float((w * pts[:, 0] ** a * pts[:, 1] ** b * pts[:, 2] ** c).sum())
+        want = tet_integral(a, b, c) if etype == O.TET10 else hex_integral(a, b, c)
+        assert abs(got - want) < TOL, (a, b, c, got, want)
+
+
+def test_gauss_constants_and_tensor_ordering():
+    # quadrature_gauss_1D.C: 2-pt -+sqrt(3)/3 w=1; 3-pt -+0.7745966692414834, 0, w=5/9, 8/9, 5/9
+    pts, w = O.quadrature(O.HEX8, 3)
+    g = math.sqrt(3.0) / 3.0
+    assert np.allclose(sorted(set(np.round(pts[:, 0], 15))), [-g, g], atol=1e-15)
+    assert np.allclose(w, 1.0)
+    pts, w = O.quadrature(O.HEX27, 5)
+    x1 = np.array([-7.7459666924148337703585307995648e-01, 0.0, 7.7459666924148337703585307995648e-01])
+    w1 = np.array([5 / 9, 8 / 9, 5 / 9])
+    # QBase::tensor_product_hex (quadrature.C:283-305): q = i + np*(j + np*k), x from i, y from j, z from k
+    for k in range(3):
+        for j in range(3):
+            for i in range(3):
+                q = i + 3 * (j + 3 * k)
+                assert np.allclose(pts[q], [x1[i], x1[j], x1[k]], atol=1e-16)
+                assert abs(w[q] - w1[i] * w1[j] * w1[k]) < 1e-16
+    # Walkington 14-point tet rule (quadrature_gauss_3D.C:257-283)
+    pts, w = O.quadrature(O.TET10, 5)
+    a = [0.31088591926330061, 0.092735250310891226, 0.045503704125649649]
+    wt = [0.018781320953002642, 0.012248840519393658, 0.0070910034628469111]
+    assert abs(w[:4] - wt[0]).max() < 1e-18 and abs(w[4:8] - wt[1]).max() < 1e-18 and abs(w[8:] - wt[2]).max() < 1e-18
+    assert abs(pts[0] - a[0]).max() < 1e-18 and abs(pts[4] - a[1]).max() < 1e-18
+    assert abs(w.sum() - 1.0 / 6.0) < 1e-15
+
+
+REF_NODES = {
+    O.HEX8: None,
+    O.HEX27: None,
+    O.TET10: np.array([[0, 0, 0], [1, 0, 0], [0, 1, 0], [0, 0, 1], [.5, 0, 0], [.5, .5, 0], [0, .5, 0], [0, 0, .5], [.5, 0, .5], [0, .5, .5]], dtype=float),
+}
+
+
+def _hex_ref_nodes(n):
+    ref = np.array([[-1, -1, -1], [1, -1, -1], [1, 1, -1], [-1, 1, -1], [-1, -1, 1], [1, -1, 1], [1, 1, 1], [-1, 1, 1], [0, -1, -1],
+                    [1, 0, -1], [0, 1, -1], [-1, 0, -1], [-1, -1, 0], [1, -1, 0], [1, 1, 0], [-1, 1, 0], [0, -1, 1], [1, 0, 1],
+                    [0, 1, 1], [-1, 0, 1], [0, 0, -1], [0, -1, 0], [1, 0, 0], [0, 1, 0], [-1, 0, 0], [0, 0, 1], [0, 0, 0]], dtype=float)
+    return ref[:n]
+
+
+@pytest.mark.parametrize("etype", [O.HEX8, O.HEX27, O.TET10])
+def test_shapes_are_nodal_and_partition_unity(etype):
+    nodes = REF_NODES[etype] if etype == O.TET10 else _hex_ref_nodes(etype)
+    phi, dxi, deta, dzeta = O.shapes(etype, nodes)
+    assert np.abs(phi - np.eye(etype)).max() < 1e-14  # Lagrange: phi_i(node_j) = delta_ij
+    rng = np.random.default_rng(7)
+    pts = rng.uniform(0.05, 0.3, size=(20, 3)) if etype == O.TET10 else rng.uniform(-1, 1, size=(20, 3))
+    phi, dxi, deta, dzeta = O.shapes(etype, pts)
+    assert np.abs(phi.sum(axis=0) - 1).max() < 1e-14  # fe_test.h:671-690
+    for d in (dxi, deta, dzeta):
+        assert np.abs(d.sum(axis=0)).max() < 1e-13
+    # derivatives agree with central differences of phi
+    h = 1e-6
+    for d, tab in enumerate((dxi, deta, dzeta)):
+        pp, pm = pts.copy(), pts.copy()
+        pp[:, d] += h
+        pm[:, d] -= h
+        fd = (O.shapes(etype, pp)[0] - O.shapes(etype, pm)[0]) / (2 * h)
+        assert np.abs(fd - tab).max() < 1e-8
+
+
+def linear_test(p):
+    return p[..., 0] + 0.25 * p[..., 1] + 0.0625 * p[..., 2]
+
+
+def quadratic_test(p):
+    x, y, z = p[..., 0], p[..., 1], p[..., 2]
+    return x * x + 0.5 * y * y + 0.25 * z * z + 0.125 * x * y + 0.0625 * x * z + 0.03125 * y * z
+
+
+def quadratic_grad(p):
+    x, y, z = p[..., 0], p[..., 1], p[..., 2]
+    return np.stack([2 * x + 0.125 * y + 0.0625 * z, y + 0.125 * x + 0.03125 * z, 0.5 * z + 0.0625 * x + 0.03125 * y], axis=-1)
+
+
+@pytest.mark.parametrize("etype,order", [(O.HEX8, 1), (O.HEX27, 2), (O.TET10, 2)])
+@pytest.mark.parametrize("skew", [False, True])
+def test_fe_reinit_reproduces_polynomials(etype, order, skew):
+    """fe_test.h testU/testGradU on the build_cube unit-cube mesh (fe_lagrange_test.C:23-30), plain and SkewFunc-skewed."""
+    m = O.Mesh(etype, 2, 2, 2)
+    if skew:
+        m.skew(0, 0.0)  # kind 0 = SkewFunc: x += 0.1 y, y += 0.2 z
+    xyz, conn, _ = m.arrays()
+    pts, w = O.quadrature(etype, 5)
+    vol = 0.0
+    for e in range(m.n_elem):
+        X = xyz[conn[e]]
+        r = O.fe_reinit(etype, X, pts, w)
+        vol += r["JxW"].sum()
+        f = quadratic_test if order == 2 else linear_test
+        u_nodes = f(X)
+        u_q = r["phi"].T @ u_nodes
+        assert np.abs(u_q - f(r["xyz"])).max() < 1e-13
+        g_q = np.einsum("iqd,i->qd", r["dphi"], u_nodes)
+        want = quadratic_grad(r["xyz"]) if order == 2 else np.broadcast_to([1, 0.25, 0.0625], g_q.shape)
+        assert np.abs(g_q - want).max() < 1e-12
+        # affine test: every build_cube hex/tet (also after the linear SkewFunc) has an affine map
+        assert r["affine"] == O.has_affine_map(etype, X) == True  # noqa: E712
+    assert abs(vol - 1.0) < 1e-13  # sum_q JxW = volume; SkewFunc is volume preserving
+
+
+def test_general_branch_matches_affine_branch_and_detects_nonaffine():
+    """compute_affine_map (fe_map.C:1167-1244) vs per-qp compute_single_point_map (:958-1077)."""
+    m = O.Mesh(O.HEX27, 2, 2, 2)
+    m.skew(1, 0.05, 12345)  # seeded interior perturbation: non-affine elements
+    xyz, conn, _ = m.arrays()
+    pts, w = O.quadrature(O.HEX27, 5)
+    n_general = 0
+    vol = 0.0
+    for e in range(m.n_elem):
+        X = xyz[conn[e]]
+        r = O.fe_reinit(O.HEX27, X, pts, w)
+        n_general += not r["affine"]
+        vol += r["JxW"].sum()
+        # an isoparametric map reproduces (only) linears exactly in physical space
+        u = linear_test(X)
+        assert np.abs(r["phi"].T @ u - linear_test(r["xyz"])).max() < 1e-13
+        g = np.einsum("iqd,i->qd", r["dphi"], u)
+        assert np.abs(g - [1, 0.25, 0.0625]).max() < 1e-12
+    assert n_general == m.n_elem
+    assert abs(vol - 1.0) < 1e-12  # interior perturbation keeps the cube's volume
+
+
+def test_degenerate_map_is_an_error():
+    X = _hex_ref_nodes(8).copy()
+    X[:, 2] = 0.0  # flat element: det J = 0 -> libMesh throws DegenerateMap (fe_map.C:467-506)
+    pts, w = O.quadrature(O.HEX8, 3)
+    with pytest.raises(O.OracleError):
+        O.fe_reinit(O.HEX8, X, pts, w)
