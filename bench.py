@@ -1,0 +1,321 @@
+#!/usr/bin/env python
+"""bench.py — Q2 HEX27 finite-element assembly throughput (elements/s) on B200, with roofline and CPU baseline.
+
+    python bench.py [--gpus N] [--steps K] [--warmup W] [--impl ours|reference] [--n 96] [--elem hex27|hex8|tet10]
+
+A "step" is one full assembly of the 3D Poisson system of introduction_ex4 (matrix + RHS zeroed -> final CSR
+values in HBM) on the synthetic build_cube mesh BASELINE.json's metric is quoted on: 96^3 HEX27, SECOND LAGRANGE,
+QGauss FIFTH, Dirichlet u = exact on all six sides, forcing = the example's FD Laplacian evaluated per quadrature
+point inside the kernel.  Setup (sparsity pattern, scatter maps, tables) is outside the timed region and reported.
+
+  value        elements/s with every input resident in HBM, CUDA-event timed on the library's stream
+  e2e          the same through the C ABI with HOST buffers: per step the node coordinates and Dirichlet values go
+               host->device from pinned memory, the assembled CSR values and RHS come back device->host
+  roofline     dominant kernel (element kernel, FP64 tensor pipe) + the slower-of FP64/HBM bound for the whole step
+  cpu_baseline the oracle (CPU restatement of the reference path) on this box's host cores, bounded sample
+
+--impl reference times that CPU path alone (the reference itself cannot be compiled here: TIMPI / MetaPhysicL
+submodules are empty), on all host threads.
+"""
+from __future__ import annotations
+
+import argparse
+import json
+import os
+import subprocess
+import sys
+import threading
+import time
+
+import numpy as np
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, ROOT)
+
+ELEM = {"hex27": 27, "hex8": 8, "tet10": 10}
+METRIC = "Q2 HEX27 assembly elements/s"
+
+
+def algorithmic_counts(etype: int, nq: int, nnz: int, n_dofs: int, n_elem: int, n_nodes: int):
+    """compulsory HBM bytes and FMA-contraction flops per element (general-Jacobian path)."""
+    n = etype
+    flops = 6 * nq * n * n + 15 * nq * n + 18 * n * nq + 2 * nq * n
+    byts = 4 * n + 24 * n_nodes / n_elem + 8 * nnz / n_elem + 8 * n_dofs / n_elem
+    return float(flops), float(byts)
+
+
+def peaks():
+    p = os.path.join(ROOT, "MEASURED_PEAKS.json")
+    if os.path.exists(p):
+        d = json.load(open(p))
+        return float(d["hbm_gbs"]), "measured (MEASURED_PEAKS.json)"
+    return 6650.0, "fallback (B200_PROFILING.md)"
+
+
+class ClockSampler:
+    """nvidia-smi clocks / throttle reasons sampled DURING the timed region."""
+
+    Q = ("clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown,"
+         "clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap")
+
+    def __init__(self, index: int):
+        self.index, self.rows, self.proc = index, [], None
+
+    def start(self):
+        try:
+            self.proc = subprocess.Popen(["nvidia-smi", f"--id={self.index}", f"--query-gpu={self.Q}", "--format=csv,noheader,nounits",
+                                          "-lms", "100"], stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
+            self.t = threading.Thread(target=self._pump, daemon=True)
+            self.t.start()
+        except OSError:
+            self.proc = None
+
+    def _pump(self):
+        for line in self.proc.stdout:
+            self.rows.append([c.strip() for c in line.split(",")])
+
+    def stop(self):
+        if not self.proc:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
+        time.sleep(0.15)
+        self.proc.terminate()
+        try:
+            self.proc.wait(timeout=5)
+        except subprocess.TimeoutExpired:
+            self.proc.kill()
+        sm, mx, reasons = [], [], set()
+        names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
+        for r in self.rows:
+            try:
+                sm.append(float(r[0]))
+                mx.append(float(r[1]))
+            except (ValueError, IndexError):
+                continue
+            for k, nm in enumerate(names):
+                if len(r) > 3 + k and r[3 + k].lower().startswith("active"):
+                    reasons.add(nm)
+        return {"sm_mhz": float(np.median(sm)) if sm else None, "sm_max_mhz": max(mx) if mx else None,
+                "reasons": sorted(reasons), "samples": len(sm)}
+
+
+def build_problem(F, etype: int, n: int, rank: int = 0, world: int = 1):
+    """Synthetic introduction_ex4 inputs from the product-side host generators (no oracle here)."""
+    t0 = time.time()
+    b = (-1.0, 1.0, -1.0, 1.0, -1.0, 1.0)
+    xyz, conn, mask = F.build_cube(etype, n, n, n, b)
+    n_dofs, base, _, _ = F.distribute_dofs(conn, xyz.shape[0])
+    elem_dofs = F.elem_dofs_from_nodes(conn, base)
+    bn = np.nonzero(mask)[0]
+    # Dirichlet data g = exact_solution at boundary nodes (introduction_ex3/exact_solution.C:40-47) — input data
+    g = np.cos(.5 * np.pi * xyz[bn, 0]) * np.sin(.5 * np.pi * xyz[bn, 1]) * np.cos(.5 * np.pi * xyz[bn, 2])
+    return dict(xyz=xyz, conn=conn, elem_dofs=elem_dofs, n_dofs=n_dofs, con_rows=base[bn].astype(np.uint32), con_vals=g,
+                host_gen_s=time.time() - t0)
+
+
+def run_ours(args):
+    import torch
+
+    from libmesh_b200 import capi as F
+
+    rank = int(os.environ.get("RANK", "0"))
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    local = int(os.environ.get("LOCAL_RANK", "0"))
+    if world != args.gpus:
+        raise SystemExit(f"--gpus {args.gpus} but WORLD_SIZE={world}: launch with torch.distributed.run --nproc-per-node {args.gpus}")
+    if world > 1:
+        from libmesh_b200 import multi
+
+        return multi.bench_multi(args, F, rank, world, local)
+    torch.cuda.set_device(local)
+    etype = ELEM[args.elem]
+    P = build_problem(F, etype, args.n)
+    n_elem = P["conn"].shape[0]
+    ctx = F.Context(local)
+    t0 = time.time()
+    ctx.set_mesh(etype, P["xyz"], P["conn"])
+    ctx.set_dofs(P["elem_dofs"], P["n_dofs"])
+    ctx.set_constraints(P["con_rows"], P["con_vals"])
+    t1 = time.time()
+    nnz = ctx.build_pattern()
+    ctx.prepare()
+    ctx.synchronize()
+    t2 = time.time()
+    params = F.make_params(F.POISSON, args.qorder, F.FORCING_EX4_FD)
+    stream = torch.cuda.ExternalStream(ctx.stream())
+    fp64 = ctx.measure_fp64_peaks()
+
+    # ---- value: inputs resident in HBM -------------------------------------------------------------------
+    for _ in range(args.warmup):
+        ctx.assemble(params, sync=False)
+    ctx.synchronize()
+    clocks = ClockSampler(local)
+    clocks.start()
+    ev0, ev1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    torch.cuda.synchronize()
+    k_ms = np.zeros((args.steps, 3))
+    launches = 0
+    ev0.record(stream)
+    for _ in range(args.steps):
+        ctx.assemble(params, sync=False)
+    ev1.record(stream)
+    ctx.synchronize()
+    torch.cuda.synchronize()
+    total_ms = ev0.elapsed_time(ev1)
+    # per-kernel durations (CUDA events inside the library, same stream): a second pass so the per-step event
+    # synchronisation does not sit inside the throughput measurement above
+    for i in range(args.steps):
+        ctx.assemble(params, sync=True)
+        ms, nl = ctx.last_timing()
+        k_ms[i] = ms
+        launches += nl
+    clk = clocks.stop()
+    ms_per_step = total_ms / args.steps
+    value = n_elem / (ms_per_step * 1e-3)
+
+    # ---- e2e: host buffers through the C ABI, H2D of inputs and D2H of the result every step -----------------
+    xyz_pin = torch.from_numpy(P["xyz"]).pin_memory()
+    val_pin = torch.empty(nnz, dtype=torch.float64).pin_memory()
+    rhs_pin = torch.empty(P["n_dofs"], dtype=torch.float64).pin_memory()
+    xyz_np, val_np, rhs_np = xyz_pin.numpy(), val_pin.numpy(), rhs_pin.numpy()
+    e2e_steps = max(2, min(args.steps, 5))
+
+    def e2e_step():
+        ctx.update_coordinates(xyz_np)
+        ctx.set_constraints(P["con_rows"], P["con_vals"])
+        ctx.assemble(params, sync=False)
+        ctx.get_values(out_values=val_np, out_rhs=rhs_np)  # synchronises
+
+    e2e_step()
+    torch.cuda.synchronize()
+    t_e = time.perf_counter()
+    for _ in range(e2e_steps):
+        e2e_step()
+    torch.cuda.synchronize()
+    e2e_s = (time.perf_counter() - t_e) / e2e_steps
+    h2d = xyz_np.nbytes + P["con_rows"].nbytes + P["con_vals"].nbytes + P["n_dofs"] * 9  # flags+values arrays uploaded by set_constraints
+    d2h = val_np.nbytes + rhs_np.nbytes
+    checksum = float(val_np.sum())
+
+    # ---- roofline ------------------------------------------------------------------------------------------
+    nq = {27: 27, 8: 27 if args.qorder in (0, 5) else 8, 10: 14}[etype]
+    flops_e, bytes_e = algorithmic_counts(etype, nq, nnz, P["n_dofs"], n_elem, P["xyz"].shape[0])
+    hbm_peak, peak_src = peaks()
+    elem_ms, red_ms = float(np.median(k_ms[:, 0])), float(np.median(k_ms[:, 1]))
+    fp64_peak = max(fp64["dmma_tflops"], fp64["dfma_tflops"])
+    ach_tf = flops_e * n_elem / (elem_ms * 1e-3) / 1e12
+    step_tf = flops_e * n_elem / (ms_per_step * 1e-3) / 1e12
+    step_gbs = bytes_e * n_elem / (ms_per_step * 1e-3) / 1e9
+    t_fp64, t_hbm = flops_e * n_elem / (fp64_peak * 1e12), bytes_e * n_elem / (hbm_peak * 1e9)
+    out = {
+        "metric": METRIC, "value": value, "unit": "elements/s", "n_gpus": 1, "steps": args.steps, "warmup": args.warmup,
+        "ms_per_step": ms_per_step, "higher_is_better": True, "scaling": "strong", "vs_baseline": None, "dtype": "f64",
+        "data": "synthetic",
+        "config": {"workload": f"introduction_ex4 3D Poisson, build_cube {args.n}^3 {args.elem.upper()} on [-1,1]^3, QGauss nq={nq}, "
+                               "Dirichlet on ids 0-5, FD forcing evaluated in-kernel", "n_elem": n_elem, "n_dofs": P["n_dofs"],
+                   "nnz": nnz, "l2": "inputs and outputs larger than L2 (CSR values %.2f GB)" % (nnz * 8 / 1e9),
+                   "setup_s": {"host_mesh_dofs": round(P["host_gen_s"], 3), "upload": round(t1 - t0, 3), "pattern_and_maps": round(t2 - t1, 3)}},
+        "clocks": clk, "gpu_launches": int(launches),  # kernels of libfeasm.so launched inside the timed K steps
+        "e2e": {"value": n_elem / e2e_s, "unit": "elements/s", "h2d_bytes_per_step": int(h2d), "d2h_bytes_per_step": int(d2h),
+                "ms_per_step": e2e_s * 1e3, "checksum_values": checksum},
+        "roofline": {"bound": "tensor", "kernel": "k_elem_poisson (FP64 DMMA contraction + geometry)", "achieved": ach_tf,
+                     "peak": fp64_peak, "unit": "TFLOP/s", "frac": ach_tf / fp64_peak, "traffic": None,
+                     "peak_source": "FP64 mma.sync/DFMA chain measured live by feasm_measure_fp64_peaks (MEASURED_PEAKS.json has no FP64 entry)",
+                     "kernel_ms": {"element": elem_ms, "row_reduce": red_ms},
+                     "flops_per_element": flops_e, "bytes_per_element": bytes_e},
+        "roofline_step": {"slower_of": "fp64" if t_fp64 >= t_hbm else "hbm", "fp64_tflops": step_tf, "fp64_frac": step_tf / fp64_peak,
+                          "hbm_gbs": step_gbs, "hbm_frac": step_gbs / hbm_peak, "hbm_peak": hbm_peak, "hbm_peak_source": peak_src,
+                          "frac_of_slower_of": max(t_fp64, t_hbm) / (ms_per_step * 1e-3)},
+        "fp64_peaks": fp64,
+    }
+    if not args.no_cpu:
+        out["cpu_baseline"] = cpu_baseline(etype, args.qorder, threads=os.cpu_count() or 1, budget_s=12.0)
+    ctx.close()
+    print(json.dumps(out))
+
+
+def cpu_sample(etype: int, qorder: int, threads: int, budget_s: float, sample_n: int | None = None):
+    """Times the oracle's assembly loop (the CPU restatement of the reference path; oracle/ is the checker and the
+    CPU baseline only) on a bounded sample of the same workload: the same build_cube/element type/quadrature/forcing,
+    a smaller cube, assembled repeatedly for about budget_s seconds.  Returns (elements/s, description, passes)."""
+    from oracle import oracle as O
+
+    n = sample_n or {27: 32, 8: 64, 10: 12}[etype]
+    m = O.Mesh(etype, n, n, n, bounds=(-1, 1, -1, 1, -1, 1), fast=True)
+    s = O.System(m)
+    s.add_dirichlet()
+    s.build_sparsity()
+    s.assemble(O.POISSON_EX4, n_threads=threads, qorder=qorder)  # warm-up pass (page faults, thread pool)
+    passes, t0 = 0, time.perf_counter()
+    while True:
+        s.assemble(O.POISSON_EX4, n_threads=threads, qorder=qorder)
+        passes += 1
+        dt = time.perf_counter() - t0
+        if dt >= budget_s or passes >= 200:
+            break
+    rate = passes * m.n_elem / dt
+    return rate, f"{passes} passes of build_cube {n}^3 ({m.n_elem} elements, same element/quadrature/forcing/constraints), {dt:.1f} s", passes
+
+
+def cpu_baseline(etype: int, qorder: int, threads: int, budget_s: float):
+    rate, sample, _ = cpu_sample(etype, qorder, threads, budget_s)
+    rate1, _, _ = cpu_sample(etype, qorder, 1, min(4.0, budget_s), sample_n={27: 16, 8: 32, 10: 6}[etype])
+    return {"value": rate, "unit": "elements/s", "cores": threads, "kind": "port", "sample": sample,
+            "single_thread_value": rate1,
+            "note": "oracle = CPU restatement of the reference loop (g++ -O3 -march=x86-64-v3, OpenMP over elements); the "
+                    "reference itself cannot be compiled here (empty TIMPI/MetaPhysicL submodules)"}
+
+
+def run_reference(args):
+    """The reference arm: the reference's CPU path (oracle port) on all host threads, bounded sample per step."""
+    rank = int(os.environ.get("RANK", "0"))
+    if rank != 0:
+        return
+    from oracle import oracle as O
+
+    etype = ELEM[args.elem]
+    threads = os.cpu_count() or 1
+    n = {27: 32, 8: 64, 10: 12}[etype]
+    m = O.Mesh(etype, n, n, n, bounds=(-1, 1, -1, 1, -1, 1), fast=True)
+    s = O.System(m)
+    s.add_dirichlet()
+    nnz = s.build_sparsity()
+    for _ in range(args.warmup):
+        s.assemble(O.POISSON_EX4, n_threads=threads, qorder=args.qorder)
+    t0 = time.perf_counter()
+    for _ in range(args.steps):
+        s.assemble(O.POISSON_EX4, n_threads=threads, qorder=args.qorder)
+    dt = (time.perf_counter() - t0) / args.steps
+    value = m.n_elem / dt
+    sample = f"each step = one assembly of build_cube {n}^3 {args.elem.upper()} ({m.n_elem} elements), {threads} OpenMP threads"
+    print(json.dumps({
+        "impl": "reference", "metric": METRIC, "value": value, "unit": "elements/s", "n_gpus": args.gpus, "steps": args.steps,
+        "warmup": args.warmup, "ms_per_step": dt * 1e3, "higher_is_better": True, "scaling": "strong", "vs_baseline": None,
+        "dtype": "f64", "data": "synthetic",
+        "config": {"workload": f"introduction_ex4 3D Poisson, build_cube {args.elem.upper()}, CPU assembly loop; bounded sample {n}^3 of the {args.n}^3 job",
+                   "n_elem": int(m.n_elem), "n_dofs": int(s.n_dofs), "nnz": int(nnz)},
+        "cpu_baseline": {"value": value, "unit": "elements/s", "cores": threads, "kind": "port", "sample": sample},
+        "e2e": {"value": value, "unit": "elements/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+        "gpu_launches": 0,
+    }))
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=20)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
+    ap.add_argument("--n", type=int, default=96, help="build_cube elements per side")
+    ap.add_argument("--elem", default="hex27", choices=sorted(ELEM))
+    ap.add_argument("--qorder", type=int, default=0, help="QGauss order (0 = the example's FIFTH)")
+    ap.add_argument("--no-cpu", action="store_true", help="skip the cpu_baseline leg")
+    args = ap.parse_args()
+    args.warmup = max(args.warmup, 3) if args.impl == "ours" else args.warmup
+    if args.impl == "reference":
+        run_reference(args)
+    else:
+        run_ours(args)
+
+
+if __name__ == "__main__":
+    main()

@@ -27,7 +27,7 @@ SYMBOLS = [
     "feasm_synchronize", "feasm_element_matrices", "feasm_zero", "feasm_add_matrix", "feasm_add_vector",
     "feasm_get_values", "feasm_device_values", "feasm_device_rhs", "feasm_stream", "feasm_set_exchange_plan",
     "feasm_pack_ghost", "feasm_recv_buffer", "feasm_unpack_ghost", "feasm_cube_sizes", "feasm_build_cube",
-    "feasm_distribute_dofs", "feasm_last_timing",
+    "feasm_distribute_dofs", "feasm_last_timing", "feasm_measure_fp64_peaks",
 ]
 
 
@@ -89,6 +89,7 @@ def lib():
         "feasm_build_cube": (i32, [i32, i32, i32, i32, vp, vp, vp, vp]),
         "feasm_distribute_dofs": (i64, [i32, i64, i64, vp, i32, i32, vp, vp, vp, vp]),
         "feasm_last_timing": (i32, [vp, vp, C.POINTER(i32)]),
+        "feasm_measure_fp64_peaks": (i32, [vp, C.POINTER(C.c_double), C.POINTER(C.c_double)]),
     }
     for name, (res, args) in sig.items():
         fn = getattr(L, name)
@@ -267,6 +268,11 @@ class Context:
         n = C.c_int()
         self._ck(self.L.feasm_last_timing(self.h, ms, C.byref(n)))
         return [ms[0], ms[1], ms[2]], n.value
+
+    def measure_fp64_peaks(self):
+        a, b = C.c_double(), C.c_double()
+        self._ck(self.L.feasm_measure_fp64_peaks(self.h, C.byref(a), C.byref(b)))
+        return {"dfma_tflops": a.value, "dmma_tflops": b.value}
 
     def set_exchange_plan(self, peer_rank, send_ptr, send_slots, recv_ptr, recv_slots):
         pr = _c(peer_rank, np.int32)
