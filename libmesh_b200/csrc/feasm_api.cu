@@ -32,8 +32,7 @@ void drop_maps(feasm_ctx* ctx) {
   release(ctx->d_pos);
   release(ctx->d_inc_ptr);
   release(ctx->d_inc);
-  release(ctx->d_ke);
-  release(ctx->d_fe);
+  release(ctx->d_kf);
 }
 
 int ensure_tables(feasm_ctx* ctx, int qorder) {
@@ -190,6 +189,7 @@ int feasm_set_dofs(feasm_ctx* ctx, int n_vars, int64_t n_rows, int64_t n_owned, 
   FEASM_CUDA(ctx, cudaMemsetAsync(ctx->d_rhs, 0, sizeof(double) * n_rows, ctx->stream));
   FEASM_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
   ctx->n_con = 0;
+  ctx->h_con_flag.assign((size_t)n_rows, 0);
   return FEASM_OK;
 }
 
@@ -203,9 +203,14 @@ int feasm_set_constraints(feasm_ctx* ctx, int64_t n, const uint32_t* rows, const
     flag[rows[i]] = 1;
     val[rows[i]] = values[i];
   }
-  FEASM_CUDA(ctx, cudaMemcpyAsync(ctx->d_con_flag, flag.data(), flag.size(), cudaMemcpyHostToDevice, ctx->stream));
+  // the constrained SET is baked into the position map's flag bits; new values alone leave it valid
+  if (flag != ctx->h_con_flag) {
+    ctx->pos_flags_valid = false;
+    FEASM_CUDA(ctx, cudaMemcpyAsync(ctx->d_con_flag, flag.data(), flag.size(), cudaMemcpyHostToDevice, ctx->stream));
+  }
   FEASM_CUDA(ctx, cudaMemcpyAsync(ctx->d_con_val, val.data(), sizeof(double) * val.size(), cudaMemcpyHostToDevice, ctx->stream));
   FEASM_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
+  ctx->h_con_flag.swap(flag);
   ctx->n_con = n;
   return FEASM_OK;
 }
@@ -267,9 +272,8 @@ int feasm_prepare(feasm_ctx* ctx) {
   if (rc) return rc;
   rc = feasm_build_pos(ctx);
   if (rc) return rc;
-  release(ctx->d_ke); release(ctx->d_fe);
-  FEASM_CUDA(ctx, cudaMalloc(&ctx->d_ke, sizeof(double) * (size_t)ctx->n_elem * ctx->nd * ctx->nd));
-  FEASM_CUDA(ctx, cudaMalloc(&ctx->d_fe, sizeof(double) * (size_t)ctx->n_elem * ctx->nd));
+  release(ctx->d_kf);
+  FEASM_CUDA(ctx, cudaMalloc(&ctx->d_kf, sizeof(double) * ((size_t)ctx->n_elem * ctx->nd * feasm_ldr(ctx->nd) + 1)));
   ctx->prepared = true;
   return FEASM_OK;
 }
@@ -288,13 +292,19 @@ int feasm_assemble(feasm_ctx* ctx, const feasm_params* params) {
   // matrix->zero(); rhs->zero() (implicit_system.C:101-105) is implied: the row reduction overwrites every slot
   FEASM_CUDA(ctx, cudaMemsetAsync(ctx->d_flags, 0, 2 * sizeof(int), ctx->stream));
   FEASM_CUDA(ctx, cudaEventRecord(ctx->ev[0], ctx->stream));
-  rc = feasm_launch_element_kernel(ctx, *params, qorder, d_f, 0, ctx->n_elem, 1, ctx->d_ke, ctx->d_fe);
+  int launches = 2;
+  if (!ctx->pos_flags_valid) {
+    rc = feasm_launch_pos_flags(ctx);
+    if (rc) return rc;
+    ++launches;
+  }
+  rc = feasm_launch_element_kernel(ctx, *params, d_f, 0, ctx->n_elem, ctx->d_kf);
   if (rc) return rc;
   FEASM_CUDA(ctx, cudaEventRecord(ctx->ev[1], ctx->stream));
-  rc = feasm_launch_row_reduce(ctx);
+  rc = feasm_launch_row_reduce(ctx, params->constrain, nullptr, ctx->n_rows, ctx->stream);
   if (rc) return rc;
   FEASM_CUDA(ctx, cudaEventRecord(ctx->ev[2], ctx->stream));
-  ctx->last_launches = 2;
+  ctx->last_launches = launches;
   return FEASM_OK;
 }
 
@@ -326,19 +336,19 @@ int feasm_element_matrices(feasm_ctx* ctx, const feasm_params* params, int64_t e
   const double* d_f = nullptr;
   rc = resolve_forcing(ctx, *params, ctx->tab_nq, &d_f);
   if (rc) return rc;
-  const size_t ne = (size_t)(e1 - e0), nd = ctx->nd;
-  double *d_ke = nullptr, *d_fe = nullptr;
-  FEASM_CUDA(ctx, cudaMalloc(&d_ke, sizeof(double) * ne * nd * nd));
-  FEASM_CUDA(ctx, cudaMalloc(&d_fe, sizeof(double) * ne * nd));
+  const size_t ne = (size_t)(e1 - e0), nd = ctx->nd, ldr = feasm_ldr(ctx->nd);
+  double* d_kf = nullptr;
+  FEASM_CUDA(ctx, cudaMalloc(&d_kf, sizeof(double) * ne * nd * ldr));
   FEASM_CUDA(ctx, cudaMemsetAsync(ctx->d_flags, 0, 2 * sizeof(int), ctx->stream));
-  rc = feasm_launch_element_kernel(ctx, *params, qorder, d_f, e0, e1, constrained, d_ke, d_fe);
+  rc = feasm_launch_element_kernel(ctx, *params, d_f, e0, e1, d_kf);
+  if (!rc && constrained) rc = feasm_launch_constrain_elements(ctx, params->constrain, e0, e1, d_kf);
   if (!rc) {
-    if (Ke) cudaMemcpyAsync(Ke, d_ke, sizeof(double) * ne * nd * nd, cudaMemcpyDeviceToHost, ctx->stream);
-    if (Fe) cudaMemcpyAsync(Fe, d_fe, sizeof(double) * ne * nd, cudaMemcpyDeviceToHost, ctx->stream);
+    // KF rows are (Ke row | Fe | pad): strip the padding on the way out
+    if (Ke) cudaMemcpy2DAsync(Ke, sizeof(double) * nd, d_kf, sizeof(double) * ldr, sizeof(double) * nd, ne * nd, cudaMemcpyDeviceToHost, ctx->stream);
+    if (Fe) cudaMemcpy2DAsync(Fe, sizeof(double), d_kf + nd, sizeof(double) * ldr, sizeof(double), ne * nd, cudaMemcpyDeviceToHost, ctx->stream);
     rc = check_flags(ctx);
   }
-  cudaFree(d_ke);
-  cudaFree(d_fe);
+  cudaFree(d_kf);
   return rc;
 }
 

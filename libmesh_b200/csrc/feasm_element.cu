@@ -1,0 +1,332 @@
+// feasm_element.cu — the element kernel: geometry + shape functions + Ke/Fe contraction.  sm_100a only.
+//
+// Element kernel = FEMap::compute_map (src/fe/fe_map.C:958-1077, :1167-1244, :1323-1372) +
+// H1FETransformation::map_dphi (src/fe/h1_fe_transformation.C:150-187) + the user contraction
+// (introduction_ex4.C:464-537).  One warp per element, persistent grid (one CTA per SM):
+//   0. gather: the next element's node coordinates are prefetched into registers one element ahead
+//   A. lane = quadrature point: affine test (Elem::has_affine_map), then either the affine branch (Jacobian at qp 0
+//      computed once by 9 lanes, JxW[p] = JxW[0]/qw[0]*qw[p]) or the general branch (J = sum_i X_i (x) dphi_i per qp);
+//      det, inverse-Jacobian rows scaled by sqrt(det), x_q, forcing
+//   B+C. Ke = G G^T with G[i][(d,q)] = sqrt(JxW_q) dphi_i/dx_d(q).  G never exists in memory: each lane builds the
+//      MMA fragments it owns straight from the reference-gradient table in shared memory (3 LDS + 9 DFMA per
+//      fragment triple) and feeds mma.sync.m8n8k4.f64 (SASS DMMA.8x8x4).  Ke is symmetric, so only the upper-
+//      triangular 8x8 blocks of the first 8*floor(n/8) rows go through DMMA (A and B fragments are the same
+//      register); the n mod 8 leftover rows (3 for HEX27, 2 for TET10) would waste 5/8 of a DMMA block each, so
+//      they are contracted with plain DFMA against fragments broadcast by shuffle.
+//   D. Fe, then fragments stored straight to the element buffer KF[e][i][LDR] (Ke row | Fe), mirrored for the
+//      lower triangle.  Constraints are NOT applied here: the row reduction applies them (feasm_scatter.cu).
+#include "feasm_internal.h"
+
+namespace {
+
+__device__ __forceinline__ void dmma884(double& c0, double& c1, double a, double b) {
+  asm volatile("mma.sync.aligned.m8n8k4.row.col.f64.f64.f64.f64 {%0,%1}, {%2}, {%3}, {%0,%1};\n"
+               : "+d"(c0), "+d"(c1)
+               : "d"(a), "d"(b));
+}
+
+constexpr int table_stride(int nqp) {
+  // lane (g = lane>>2, t = lane&3) reads T[row0+g][q0+t]: conflict-free 64-bit LDS needs stride = 4 or 12 (mod 16)
+  int s = nqp;
+  while (s % 16 != 4 && s % 16 != 12) ++s;
+  return s;
+}
+
+template <int NPE, int NQ>
+struct ElemCfg {
+  static constexpr int NBF = NPE / 8;               // full 8-row blocks of Ke: DMMA
+  static constexpr int REM = NPE - 8 * NBF;         // leftover rows: DFMA
+  static constexpr int NB = NBF + (REM ? 1 : 0);    // fragment row blocks a lane generates
+  static constexpr int NQP = (NQ + 3) & ~3;         // quadrature points padded to the MMA k step
+  static constexpr int QG = NQP / 4;
+  static constexpr int TS = table_stride(NQP);      // row stride of the scaled-gradient table
+  static constexpr int NBLK = NBF * (NBF + 1) / 2;
+  static constexpr int LDR = feasm_ldr(NPE);
+  static constexpr int TAB = 4 * NPE * NQ + NQ;     // phi | dxi | deta | dzeta | qw  (global layout, [i][q])
+  static constexpr int TAB_SZ = (TAB + 1) & ~1;
+  static constexpr int TW_SZ = 3 * NB * 8 * TS;     // sqrt(w_q) dref_c[i][q], zero padded
+  static constexpr int X_SZ = (NPE * 3 + 1) & ~1;
+  static constexpr int WARP_DBL = X_SZ + 32;        // X | fw
+  static constexpr int SMEM_DBL(int warps) { return TAB_SZ + TW_SZ + warps * WARP_DBL; }
+  static_assert(NQP <= 32, "lane = quadrature point needs nq <= 32");
+  static_assert(NPE <= 32, "lane = shape function needs npe <= 32");
+  static_assert(REM <= 4, "leftover rows beyond 4 should become a DMMA block");
+};
+
+// Elem::has_affine_map as a list of vector comparisons (a1-a0)*sa ~ (b1-b0)*sb with relative_fuzzy_equals at
+// affine_tol = TOLERANCE^2 (include/geom/elem.h:2070, include/utils/fuzzy_equals.h:96-112); one lane per check.
+struct AffineCheck { signed char a1, a0, b1, b0; float sa, sb; };
+__constant__ AffineCheck c_affine_hex8[4] = {{1, 0, 2, 3, 1, 1}, {1, 0, 5, 4, 1, 1}, {1, 0, 6, 7, 1, 1}, {4, 0, 7, 3, 1, 1}};  // cell_hex8.C:121-135
+__constant__ AffineCheck c_affine_hex27[23] = {  // cell_hex27.C:125-166
+    {1, 0, 2, 3, 1, 1},     {1, 0, 5, 4, 1, 1},     {1, 0, 6, 7, 1, 1},     {1, 0, 8, 0, .5f, 1},   {1, 0, 10, 3, .5f, 1},
+    {1, 0, 16, 4, .5f, 1},  {1, 0, 18, 7, .5f, 1},  {1, 0, 20, 11, .5f, 1}, {1, 0, 21, 12, .5f, 1}, {1, 0, 23, 15, .5f, 1},
+    {1, 0, 25, 19, .5f, 1}, {1, 0, 26, 24, .5f, 1}, {4, 0, 7, 3, 1, 1},     {4, 0, 12, 0, .5f, 1},  {4, 0, 13, 1, .5f, 1},
+    {4, 0, 14, 2, .5f, 1},  {4, 0, 15, 3, .5f, 1},  {4, 0, 22, 9, .5f, 1},  {4, 0, 24, 11, .5f, 1}, {3, 0, 11, 0, .5f, 1},
+    {3, 0, 9, 1, .5f, 1},   {3, 0, 17, 5, .5f, 1},  {3, 0, 19, 4, .5f, 1}};
+__constant__ AffineCheck c_affine_tet10[6] = {{1, 0, 4, 0, 1, 2}, {2, 1, 5, 1, 1, 2}, {2, 0, 6, 0, 1, 2},  // cell_tet10.C:143-170
+                                              {3, 0, 7, 0, 1, 2}, {3, 1, 8, 1, 1, 2}, {3, 2, 9, 2, 1, 2}};
+
+template <int NPE>
+__device__ __forceinline__ bool affine_check_lane(const double* X, int lane) {
+  constexpr int N = NPE == 27 ? 23 : (NPE == 8 ? 4 : 6);
+  if (lane >= N) return true;
+  const AffineCheck c = NPE == 27 ? c_affine_hex27[lane] : (NPE == 8 ? c_affine_hex8[lane] : c_affine_tet10[lane]);
+  double na = 0., nb = 0., nd = 0.;
+#pragma unroll
+  for (int d = 0; d < 3; ++d) {
+    const double a = (X[3 * c.a1 + d] - X[3 * c.a0 + d]) * (double)c.sa;
+    const double b = (X[3 * c.b1 + d] - X[3 * c.b0 + d]) * (double)c.sb;
+    na += fabs(a); nb += fabs(b); nd += fabs(a - b);
+  }
+  return nd <= 1e-12 * (na + nb);
+}
+
+// introduction_ex4.C:500-537 with exact_solution of introduction_ex3/exact_solution.C:40-47.  The seven
+// exact_solution() calls share nine distinct trig values; every product below is evaluated in the example's order
+// ((cos * sin) * cos), so the result equals the literal seven-call form bit for bit.
+__device__ __forceinline__ double ex4_forcing_dev(double x, double y, double z) {
+  // explicit _rn intrinsics: no FMA contraction, so only the libm sin/cos can differ from the host evaluation
+  const double hp = .5 * 3.141592653589793;  // .5 * acos(-1.)
+  const double eps = 1.e-3;
+  const double cx0 = cos(__dmul_rn(hp, x)), cxm = cos(__dmul_rn(hp, __dadd_rn(x, -eps))), cxp = cos(__dmul_rn(hp, __dadd_rn(x, eps)));
+  const double sy0 = sin(__dmul_rn(hp, y)), sym = sin(__dmul_rn(hp, __dadd_rn(y, -eps))), syp = sin(__dmul_rn(hp, __dadd_rn(y, eps)));
+  const double cz0 = cos(__dmul_rn(hp, z)), czm = cos(__dmul_rn(hp, __dadd_rn(z, -eps))), czp = cos(__dmul_rn(hp, __dadd_rn(z, eps)));
+  auto u = [](double a, double b, double c) { return __dmul_rn(__dmul_rn(a, b), c); };
+  auto fd = [eps](double m, double p, double u0) {
+    return __ddiv_rn(__ddiv_rn(__dadd_rn(__dadd_rn(m, p), __dmul_rn(-2., u0)), eps), eps);
+  };
+  const double u0 = u(cx0, sy0, cz0);
+  const double uxx = fd(u(cxm, sy0, cz0), u(cxp, sy0, cz0), u0);
+  const double uyy = fd(u(cx0, sym, cz0), u(cx0, syp, cz0), u0);
+  const double uzz = fd(u(cx0, sy0, czm), u(cx0, sy0, czp), u0);
+  return -__dadd_rn(__dadd_rn(uxx, uyy), uzz);
+}
+
+template <int NPE, int NQ, int WARPS>
+__global__ void __launch_bounds__(WARPS * 32, 1)
+k_elem_poisson(const double* __restrict__ xyz, const uint32_t* __restrict__ conn, const double* __restrict__ tab,
+               int forcing, const double* __restrict__ f_tab, int64_t e0, int64_t e1, double* __restrict__ kf, int* flags) {
+  using C = ElemCfg<NPE, NQ>;
+  extern __shared__ double smem[];
+  double* s_tab = smem;               // phi | dxi | deta | dzeta | qw, [i][q]: lane = q reads are conflict free
+  double* s_tw = smem + C::TAB_SZ;    // [c][row][TS]: sqrt(w_q) * d phi_row / d xi_c (q), zero padded
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  for (int t = threadIdx.x; t < C::TAB; t += WARPS * 32) s_tab[t] = tab[t];
+  for (int t = threadIdx.x; t < C::TW_SZ; t += WARPS * 32) {
+    const int c = t / (C::NB * 8 * C::TS), row = (t / C::TS) % (C::NB * 8), q = t % C::TS;
+    s_tw[t] = (row < NPE && q < NQ) ? sqrt(tab[4 * NPE * NQ + q]) * tab[(1 + c) * NPE * NQ + row * NQ + q] : 0.;
+  }
+  const double* s_phi = s_tab;
+  const double* s_dxi = s_tab + NPE * NQ;
+  const double* s_qw = s_tab + 4 * NPE * NQ;
+  double* X = s_tw + C::TW_SZ + (size_t)warp * C::WARP_DBL;  // node coordinates of the current element
+  double* fw = X + C::X_SZ;                                  // JxW_q * f(x_q)
+  const int g = lane >> 2, t4 = lane & 3;
+  const double* twp = s_tw + g * C::TS + t4;  // + c*NB*8*TS + ib*8*TS + 4*qg
+  __syncthreads();
+
+  const int64_t stride = (int64_t)gridDim.x * WARPS;
+  int64_t e = e0 + (int64_t)blockIdx.x * WARPS + warp;
+  // prefetch registers: node `lane` of the next element
+  double nx = 0., ny = 0., nz = 0.;
+  if (e < e1 && lane < NPE) {
+    const uint64_t node = conn[e * NPE + lane];
+    nx = xyz[node * 3]; ny = xyz[node * 3 + 1]; nz = xyz[node * 3 + 2];
+  }
+  for (; e < e1; e += stride) {
+    if (lane < NPE) { X[3 * lane] = nx; X[3 * lane + 1] = ny; X[3 * lane + 2] = nz; }
+    {
+      const int64_t en = e + stride;
+      if (en < e1 && lane < NPE) {
+        const uint64_t node = conn[en * NPE + lane];
+        nx = xyz[node * 3]; ny = xyz[node * 3 + 1]; nz = xyz[node * 3 + 2];
+      }
+    }
+    __syncwarp();
+
+    // ---- A: reference -> physical map at quadrature point q = lane ---------------------------------------
+    const bool affine = __all_sync(0xffffffffu, affine_check_lane<NPE>(X, lane));
+    double S[9];  // sqrt(det J) * (dxidx dxidy dxidz | detadx .. | dzetadx ..)
+    {
+      double x = 0, y = 0, z = 0;
+      double xa = 0, ya = 0, za = 0, xb = 0, yb = 0, zb = 0, xc = 0, yc = 0, zc = 0;
+      const int q = lane < NQ ? lane : 0;
+      if (affine) {
+        // compute_affine_map (fe_map.C:1167-1244): the Jacobian at qp 0 only — lane c < 9 sums component c —
+        // and xyz at every qp (:1190-1197)
+        double d = 0.;
+        if (lane < 9) {
+          const double* tabd = s_dxi + (lane / 3) * (NPE * NQ);
+          const int cd = lane % 3;
+#pragma unroll 9
+          for (int i = 0; i < NPE; ++i) d += tabd[i * NQ] * X[3 * i + cd];
+        }
+        if (forcing == FEASM_FORCING_EX4_FD) {
+#pragma unroll 9
+          for (int i = 0; i < NPE; ++i) {
+            const double p = s_phi[i * NQ + q];
+            x += p * X[3 * i]; y += p * X[3 * i + 1]; z += p * X[3 * i + 2];
+          }
+        }
+        xa = __shfl_sync(0xffffffffu, d, 0); ya = __shfl_sync(0xffffffffu, d, 1); za = __shfl_sync(0xffffffffu, d, 2);
+        xb = __shfl_sync(0xffffffffu, d, 3); yb = __shfl_sync(0xffffffffu, d, 4); zb = __shfl_sync(0xffffffffu, d, 5);
+        xc = __shfl_sync(0xffffffffu, d, 6); yc = __shfl_sync(0xffffffffu, d, 7); zc = __shfl_sync(0xffffffffu, d, 8);
+      } else {
+        // general branch: compute_single_point_map per qp (fe_map.C:994-1026)
+        const double* s_deta = s_dxi + NPE * NQ;
+        const double* s_dzeta = s_deta + NPE * NQ;
+#pragma unroll 3
+        for (int i = 0; i < NPE; ++i) {
+          const double px = X[3 * i], py = X[3 * i + 1], pz = X[3 * i + 2];
+          const double p = s_phi[i * NQ + q], a = s_dxi[i * NQ + q], b = s_deta[i * NQ + q], c = s_dzeta[i * NQ + q];
+          x += p * px; y += p * py; z += p * pz;
+          xa += a * px; ya += a * py; za += a * pz;
+          xb += b * px; yb += b * py; zb += b * pz;
+          xc += c * px; yc += c * py; zc += c * pz;
+        }
+      }
+      // det J in the order of fe_map.C:1046-1048, inverse rows :1056-1068
+      const double jac = (xa * (yb * zc - zb * yc) + ya * (zb * xc - xb * zc) + za * (xb * yc - yb * xc));
+      const bool bad = !(jac > 0.);
+      if (bad && lane < NQ) atomicAdd(&flags[0], 1);  // check_for_degenerate_map, fe_map.C:467-506
+      const double JxW = (affine && q != 0) ? jac * s_qw[0] / s_qw[0] * s_qw[q] : jac * s_qw[q];  // fe_map.C:1242 / :1052
+      const double s = bad ? 0. : sqrt(jac) / jac;
+      S[0] = (yb * zc - zb * yc) * s; S[1] = (zb * xc - xb * zc) * s; S[2] = (xb * yc - yb * xc) * s;
+      S[3] = (za * yc - ya * zc) * s; S[4] = (xa * zc - za * xc) * s; S[5] = (ya * xc - xa * yc) * s;
+      S[6] = (ya * zb - za * yb) * s; S[7] = (za * xb - xa * zb) * s; S[8] = (xa * yb - ya * xb) * s;
+      double f = 0.;
+      if (lane < NQ) {
+        if (forcing == FEASM_FORCING_EX4_FD) f = ex4_forcing_dev(x, y, z);
+        else if (forcing == FEASM_FORCING_TABULATED) f = f_tab[e * NQ + lane];
+      }
+      fw[lane] = lane < NQ ? JxW * f : 0.;
+    }
+
+    // ---- B+C: Ke = G G^T; fragments generated in registers -------------------------------------------------
+    double acc[C::NBLK > 0 ? C::NBLK : 1][2];
+    double pr[C::NB][C::REM > 0 ? C::REM : 1];  // leftover rows: partial (over k = t4 mod 4) K[ib*8+g][8*NBF+r]
+#pragma unroll
+    for (int b = 0; b < C::NBLK; ++b) { acc[b][0] = 0.; acc[b][1] = 0.; }
+#pragma unroll
+    for (int ib = 0; ib < C::NB; ++ib)
+#pragma unroll
+      for (int r = 0; r < (C::REM > 0 ? C::REM : 1); ++r) pr[ib][r] = 0.;
+#pragma unroll
+    for (int qg = 0; qg < C::QG; ++qg) {
+      double Sq[9];
+      if (affine) {
+#pragma unroll
+        for (int k = 0; k < 9; ++k) Sq[k] = S[k];
+      } else {
+#pragma unroll
+        for (int k = 0; k < 9; ++k) Sq[k] = __shfl_sync(0xffffffffu, S[k], 4 * qg + t4);
+      }
+      double G[C::NB][3];
+#pragma unroll
+      for (int ib = 0; ib < C::NB; ++ib) {
+        const double a = twp[ib * 8 * C::TS + 4 * qg];
+        const double b = twp[C::NB * 8 * C::TS + ib * 8 * C::TS + 4 * qg];
+        const double c = twp[2 * C::NB * 8 * C::TS + ib * 8 * C::TS + 4 * qg];
+        // h1_fe_transformation.C:150-187: dphi/dx_d = dphi/dxi dxi/dx_d + dphi/deta deta/dx_d + dphi/dzeta dzeta/dx_d
+        G[ib][0] = a * Sq[0] + b * Sq[3] + c * Sq[6];
+        G[ib][1] = a * Sq[1] + b * Sq[4] + c * Sq[7];
+        G[ib][2] = a * Sq[2] + b * Sq[5] + c * Sq[8];
+      }
+#pragma unroll
+      for (int d = 0; d < 3; ++d) {
+        int blk = 0;
+#pragma unroll
+        for (int jb = 0; jb < C::NBF; ++jb)
+#pragma unroll
+          for (int ib = 0; ib <= jb; ++ib) { dmma884(acc[blk][0], acc[blk][1], G[ib][d], G[jb][d]); ++blk; }
+        if (C::REM > 0) {
+#pragma unroll
+          for (int r = 0; r < C::REM; ++r) {
+            const double gr = __shfl_sync(0xffffffffu, G[C::NB - 1][d], 4 * r + t4);
+#pragma unroll
+            for (int ib = 0; ib < C::NB; ++ib) pr[ib][r] += G[ib][d] * gr;
+          }
+        }
+      }
+    }
+    if (C::REM > 0) {
+#pragma unroll
+      for (int ib = 0; ib < C::NB; ++ib)
+#pragma unroll
+        for (int r = 0; r < C::REM; ++r) {
+          pr[ib][r] += __shfl_xor_sync(0xffffffffu, pr[ib][r], 1);
+          pr[ib][r] += __shfl_xor_sync(0xffffffffu, pr[ib][r], 2);
+        }
+    }
+
+    // ---- D: Fe (introduction_ex4.C:536-537) and the stores ----------------------------------------------------
+    double* out = kf + (uint64_t)(e - e0) * (NPE * C::LDR);
+    if (lane < NPE) {
+      double Fe = 0.;
+      if (forcing != FEASM_FORCING_NONE) {
+#pragma unroll 3
+        for (int q = 0; q < NQ; ++q) Fe += fw[q] * s_phi[lane * NQ + q];
+      }
+      out[lane * C::LDR + NPE] = Fe;
+    }
+    {
+      int blk = 0;
+#pragma unroll
+      for (int jb = 0; jb < C::NBF; ++jb)
+#pragma unroll
+        for (int ib = 0; ib <= jb; ++ib, ++blk) {
+          const int i = ib * 8 + g, j = jb * 8 + 2 * t4;
+          *reinterpret_cast<double2*>(out + i * C::LDR + j) = make_double2(acc[blk][0], acc[blk][1]);
+          if (ib != jb) {  // mirror into the lower triangle
+            out[j * C::LDR + i] = acc[blk][0];
+            out[(j + 1) * C::LDR + i] = acc[blk][1];
+          }
+        }
+    }
+    if (C::REM > 0) {
+      constexpr int R0 = 8 * C::NBF;
+#pragma unroll
+      for (int ib = 0; ib < C::NBF; ++ib) {
+        const int i = ib * 8 + g;
+#pragma unroll
+        for (int r = 0; r < C::REM; ++r)
+          if (t4 == r) { out[i * C::LDR + R0 + r] = pr[ib][r]; out[(R0 + r) * C::LDR + i] = pr[ib][r]; }
+      }
+      if (g < C::REM) {
+#pragma unroll
+        for (int r = 0; r < C::REM; ++r)
+          if (t4 == r) out[(R0 + g) * C::LDR + R0 + r] = pr[C::NB - 1][r];
+      }
+    }
+    __syncwarp();
+  }
+}
+
+template <int NPE, int NQ, int WARPS>
+int launch_poisson(feasm_ctx* ctx, const feasm_params& p, const double* d_f, int64_t e0, int64_t e1, double* d_kf) {
+  using C = ElemCfg<NPE, NQ>;
+  const size_t smem = sizeof(double) * (size_t)C::SMEM_DBL(WARPS);
+  auto kern = k_elem_poisson<NPE, NQ, WARPS>;
+  FEASM_CUDA(ctx, cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+  int64_t blocks = (e1 - e0 + WARPS - 1) / WARPS;
+  if (blocks > ctx->sm_count) blocks = ctx->sm_count;
+  if (blocks < 1) blocks = 1;
+  kern<<<(unsigned)blocks, WARPS * 32, smem, ctx->stream>>>(ctx->d_xyz, ctx->d_conn, ctx->d_tab, p.forcing, d_f, e0, e1, d_kf,
+                                                           ctx->d_flags);
+  FEASM_CUDA(ctx, cudaGetLastError());
+  return FEASM_OK;
+}
+
+}  // namespace
+
+int feasm_launch_element_kernel(feasm_ctx* ctx, const feasm_params& p, const double* d_f, int64_t e0, int64_t e1,
+                                double* d_kf) {
+  if (p.problem == FEASM_POISSON) {
+    if (ctx->elem_type == FEASM_HEX27 && ctx->tab_nq == 27) return launch_poisson<27, 27, 12>(ctx, p, d_f, e0, e1, d_kf);
+    if (ctx->elem_type == FEASM_HEX8 && ctx->tab_nq == 8) return launch_poisson<8, 8, 16>(ctx, p, d_f, e0, e1, d_kf);
+    if (ctx->elem_type == FEASM_HEX8 && ctx->tab_nq == 27) return launch_poisson<8, 27, 16>(ctx, p, d_f, e0, e1, d_kf);
+    if (ctx->elem_type == FEASM_TET10 && ctx->tab_nq == 14) return launch_poisson<10, 14, 16>(ctx, p, d_f, e0, e1, d_kf);
+    return feasm_fail(ctx, FEASM_ERR_ARG, "no Poisson kernel for this element type / quadrature order");
+  }
+  return feasm_fail(ctx, FEASM_ERR_ARG, "problem not implemented");
+}

@@ -22,6 +22,14 @@ struct FeasmTables {
 };
 bool feasm_make_tables(int elem_type, int qorder, FeasmTables& t, std::string& err);
 
+// Element buffer KF[e][a][LDR]: row a of element e = Ke(a, 0..nd-1) followed by Fe(a) at column nd, padded to a
+// whole number of 32 B sectors (HEX27: 28 doubles = 224 B).  One row is what one (element, local dof) pair
+// contributes to one CSR row, so the row reduction reads it as one contiguous run.
+constexpr int feasm_ldr(int nd) { return (nd + 1 + 3) & ~3; }
+// Position map pos[e][a][PLD]: row stride padded to whole sectors; entry = column position inside the CSR row,
+// top bit = "column dof is constrained".  uint8 when every row has <= 128 entries, else uint16.
+constexpr int feasm_pld(int nd, int pos_bytes) { return ((nd * pos_bytes + 31) & ~31) / pos_bytes; }
+
 struct feasm_ctx {
   int device = 0;
   cudaStream_t stream = nullptr;
@@ -46,6 +54,7 @@ struct feasm_ctx {
   uint8_t* d_con_flag = nullptr;
   double* d_con_val = nullptr;
   int64_t n_con = 0;
+  std::vector<uint8_t> h_con_flag;  // host mirror of d_con_flag (detects a changed constrained set)
 
   // pattern + system
   uint64_t nnz = 0;
@@ -57,14 +66,15 @@ struct feasm_ctx {
 
   // scatter maps (built by feasm_prepare)
   bool prepared = false;
-  uint16_t* d_pos = nullptr;      // [n_elem][nd][nd] row-relative column position
+  void* d_pos = nullptr;          // [n_elem][nd][feasm_pld] row-relative column position | constrained-column flag
+  int pos_bytes = 2;
+  bool pos_flags_valid = false;   // top bits reflect the current constrained set
   uint64_t* d_inc_ptr = nullptr;  // [n_rows+1]
   uint32_t* d_inc = nullptr;      // [n_elem*nd] = e*nd + a, ascending within a row
   uint32_t max_inc = 0;
 
   // element buffers
-  double* d_ke = nullptr;  // [n_elem][nd*nd]
-  double* d_fe = nullptr;  // [n_elem][nd]
+  double* d_kf = nullptr;  // [n_elem][nd][feasm_ldr(nd)]: Ke rows with Fe in column nd
   int* d_flags = nullptr;  // [0] degenerate count, [1] pattern misses
 
   // tables on device, keyed by quadrature order
@@ -103,9 +113,15 @@ int feasm_build_incidence(feasm_ctx* ctx);
 int feasm_device_build_pattern(feasm_ctx* ctx);
 int feasm_build_pos(feasm_ctx* ctx);
 // feasm_assemble.cu
-int feasm_launch_element_kernel(feasm_ctx* ctx, const feasm_params& p, int qorder, const double* d_f, int64_t e0,
-                                int64_t e1, int constrained, double* d_ke, double* d_fe);
-int feasm_launch_row_reduce(feasm_ctx* ctx);
+int feasm_launch_element_kernel(feasm_ctx* ctx, const feasm_params& p, const double* d_f, int64_t e0, int64_t e1,
+                                double* d_kf);
+// applies the Dirichlet constraints to element rows in place (element-level API only; the assembly applies them
+// inside the row reduction)
+int feasm_launch_constrain_elements(feasm_ctx* ctx, int constrain_mode, int64_t e0, int64_t e1, double* d_kf);
+int feasm_launch_pos_flags(feasm_ctx* ctx);
+// d_row_list == nullptr: every row; else the n_list rows listed
+int feasm_launch_row_reduce(feasm_ctx* ctx, int constrain_mode, const uint32_t* d_row_list, int64_t n_list,
+                            cudaStream_t stream);
 int feasm_launch_pack(feasm_ctx* ctx);
 int feasm_launch_unpack(feasm_ctx* ctx);
 int feasm_launch_add_matrix(feasm_ctx* ctx, const double* d_dm, const uint32_t* d_rows, int nr, const uint32_t* d_cols,

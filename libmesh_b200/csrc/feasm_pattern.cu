@@ -102,17 +102,20 @@ __global__ void k_counts_to_u64(const uint32_t* __restrict__ c, uint64_t* out, i
   if (i < n) out[i] = c[i];
 }
 
-// pos[e][a][b] = index of column gid(dof_b) inside row dof_a.
-__global__ void k_build_pos(const uint32_t* __restrict__ elem_dofs, const uint32_t* __restrict__ gid, int nd,
+// pos[e][a][b] = index of column gid(dof_b) inside row dof_a (row stride pld; the top bit is the constrained-column
+// flag, written later by feasm_launch_pos_flags).
+template <typename PosT>
+__global__ void k_build_pos(const uint32_t* __restrict__ elem_dofs, const uint32_t* __restrict__ gid, int nd, int pld,
                             int64_t n_elem, const uint64_t* __restrict__ row_ptr, const uint32_t* __restrict__ col_idx,
-                            uint16_t* __restrict__ pos, int* flags) {
+                            PosT* __restrict__ pos, int* flags) {
   const uint64_t i = blockIdx.x * (uint64_t)blockDim.x + threadIdx.x;
-  const uint64_t total = (uint64_t)n_elem * nd * nd;
+  const uint64_t total = (uint64_t)n_elem * nd * pld;
   if (i >= total) return;
-  const uint64_t e = i / ((uint64_t)nd * nd);
-  const int ab = (int)(i % ((uint64_t)nd * nd));
-  const int a = ab / nd, b = ab % nd;
-  const uint32_t row = elem_dofs[e * nd + a];
+  const uint64_t ea = i / pld;
+  const int b = (int)(i % pld);
+  if (b >= nd) { pos[i] = 0; return; }
+  const uint64_t e = ea / nd;
+  const uint32_t row = elem_dofs[ea];
   const uint32_t dcol = elem_dofs[e * nd + b];
   const uint32_t col = gid ? gid[dcol] : dcol;
   const uint32_t* c = col_idx + row_ptr[row];
@@ -125,7 +128,7 @@ __global__ void k_build_pos(const uint32_t* __restrict__ elem_dofs, const uint32
     atomicAdd(&flags[1], 1);
     lo = 0;
   }
-  pos[i] = (uint16_t)lo;
+  pos[i] = (PosT)lo;
 }
 
 inline unsigned grid_for(uint64_t n, int block) { return (unsigned)((n + block - 1) / block); }
@@ -207,7 +210,6 @@ int feasm_device_build_pattern(feasm_ctx* ctx) {
 }
 
 int feasm_build_pos(feasm_ctx* ctx) {
-  const uint64_t total = (uint64_t)ctx->n_elem * ctx->nd * ctx->nd;
   unsigned int* d_max = nullptr;
   FEASM_CUDA(ctx, cudaMalloc(&d_max, sizeof(unsigned int)));
   FEASM_CUDA(ctx, cudaMemsetAsync(d_max, 0, sizeof(unsigned int), ctx->stream));
@@ -215,12 +217,23 @@ int feasm_build_pos(feasm_ctx* ctx) {
   FEASM_CUDA(ctx, cudaMemcpyAsync(&ctx->max_row_len, d_max, sizeof(unsigned int), cudaMemcpyDeviceToHost, ctx->stream));
   FEASM_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
   cudaFree(d_max);
-  if (ctx->max_row_len > 65535u) return feasm_fail(ctx, FEASM_ERR_ARG, "row longer than 65535 entries: uint16 position map overflows");
+  if (ctx->max_row_len > 32768u) return feasm_fail(ctx, FEASM_ERR_ARG, "row longer than 32768 entries: position map overflows");
+  ctx->pos_bytes = ctx->max_row_len <= 128u ? 1 : 2;
+  const int pld = feasm_pld(ctx->nd, ctx->pos_bytes);
+  const uint64_t total = (uint64_t)ctx->n_elem * ctx->nd * pld;
   if (ctx->d_pos) cudaFree(ctx->d_pos);
-  FEASM_CUDA(ctx, cudaMalloc(&ctx->d_pos, sizeof(uint16_t) * total));
+  ctx->d_pos = nullptr;
+  FEASM_CUDA(ctx, cudaMalloc(&ctx->d_pos, (size_t)ctx->pos_bytes * (total ? total : 1)));
   FEASM_CUDA(ctx, cudaMemsetAsync(ctx->d_flags, 0, 2 * sizeof(int), ctx->stream));
-  k_build_pos<<<grid_for(total, 256), 256, 0, ctx->stream>>>(ctx->d_elem_dofs, ctx->d_gid, ctx->nd, ctx->n_elem,
-                                                             ctx->d_row_ptr, ctx->d_col_idx, ctx->d_pos, ctx->d_flags);
+  if (total) {
+    if (ctx->pos_bytes == 1)
+      k_build_pos<uint8_t><<<grid_for(total, 256), 256, 0, ctx->stream>>>(ctx->d_elem_dofs, ctx->d_gid, ctx->nd, pld, ctx->n_elem,
+                                                                         ctx->d_row_ptr, ctx->d_col_idx, (uint8_t*)ctx->d_pos, ctx->d_flags);
+    else
+      k_build_pos<uint16_t><<<grid_for(total, 256), 256, 0, ctx->stream>>>(ctx->d_elem_dofs, ctx->d_gid, ctx->nd, pld, ctx->n_elem,
+                                                                          ctx->d_row_ptr, ctx->d_col_idx, (uint16_t*)ctx->d_pos, ctx->d_flags);
+  }
+  ctx->pos_flags_valid = false;
   int flags[2] = {0, 0};
   FEASM_CUDA(ctx, cudaMemcpyAsync(flags, ctx->d_flags, sizeof(flags), cudaMemcpyDeviceToHost, ctx->stream));
   FEASM_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
