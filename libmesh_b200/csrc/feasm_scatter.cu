@@ -19,149 +19,157 @@ template <typename PosT> struct PosBits;
 template <> struct PosBits<uint8_t> { static constexpr unsigned FLAG = 0x80u, MASK = 0x7fu; };
 template <> struct PosBits<uint16_t> { static constexpr unsigned FLAG = 0x8000u, MASK = 0x7fffu; };
 
-// A warp owns a batch of 32 consecutive entries of the row list (or 32 consecutive rows).  Lane l holds the
-// pointers of row l of the batch; the contributors of the batch are walked in chunks of U as a three-stage software
-// pipeline — incidence ids of chunk c+2, element rows + positions of chunk c+1 in flight while chunk c is
-// accumulated into the row image in shared memory — so several KB per warp are outstanding at any time.
-template <typename PosT, int NDC, int WARPS>
-__global__ void __launch_bounds__(WARPS * 32, 2)
+__device__ __forceinline__ void cp_async16(void* smem_dst, const void* gsrc) {
+  const unsigned d = (unsigned)__cvta_generic_to_shared(smem_dst);
+  asm volatile("cp.async.cg.shared.global [%0], [%1], 16;\n" ::"r"(d), "l"(gsrc) : "memory");  // SASS LDGSTS, L1 bypass
+}
+__device__ __forceinline__ void cp_async_commit() { asm volatile("cp.async.commit_group;\n" ::: "memory"); }
+template <int N>
+__device__ __forceinline__ void cp_async_wait() { asm volatile("cp.async.wait_group %0;\n" ::"n"(N) : "memory"); }
+
+// A warp owns a batch of RB consecutive entries of the row list (or RB consecutive rows); lane l holds the pointers
+// of row l of the batch.  The incidence ids of the whole batch are loaded into shared memory in one round trip;
+// then the element rows KF[e][a][:] (ldrb bytes) and their position-map rows (pldb bytes) stream through a
+// per-warp ring of NG x G slots filled by cp.async (LDGSTS, 16 B per lane, no register staging): NG-1 stages —
+// several KB per warp — are in flight while one is accumulated into the CSR row image in shared memory.  Rows are
+// finished strictly in order and every row is summed in element order, so the result is bitwise reproducible.
+constexpr int RR_NG = 4;
+template <typename PosT, int WARPS>
+__global__ void __launch_bounds__(WARPS * 32)
 k_row_reduce(const uint64_t* __restrict__ row_ptr, const uint64_t* __restrict__ inc_ptr, const uint32_t* __restrict__ inc,
-             const PosT* __restrict__ pos, const double* __restrict__ kf, int nd, int ldr, int pld,
-             const uint32_t* __restrict__ row_list, int64_t n_list, int cap, const uint8_t* __restrict__ con_flag,
-             const double* __restrict__ con_val, const uint32_t* __restrict__ elem_dofs, int mode,
-             double* __restrict__ values, double* __restrict__ rhs) {
-  constexpr int U = 8 / NDC;
-  constexpr unsigned FULL = 0xffffffffu, INVALID = 0xffffffffu;
-  extern __shared__ double s_img[];
+             const unsigned char* __restrict__ pos, const unsigned char* __restrict__ kf, int nd, int ldrb, int pldb, int G,
+             int RB, int lcap, int cap, const uint32_t* __restrict__ row_list, int64_t n_list,
+             const uint8_t* __restrict__ con_flag, const double* __restrict__ con_val,
+             const uint32_t* __restrict__ elem_dofs, int mode, double* __restrict__ values, double* __restrict__ rhs) {
+  constexpr unsigned FULL = 0xffffffffu;
+  extern __shared__ __align__(16) unsigned char s_raw[];
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-  const int64_t base = (blockIdx.x * (int64_t)WARPS + warp) * 32;
+  const int64_t base = (blockIdx.x * (int64_t)WARPS + warp) * RB;
   if (base >= n_list) return;
-  const int nrows = (int)(n_list - base < 32 ? n_list - base : 32);
-  double* img = s_img + (size_t)warp * cap;
+  const int nrows = (int)(n_list - base < RB ? n_list - base : RB);
+  const int slotb = ldrb + pldb;
+  const size_t warp_bytes = (size_t)RR_NG * G * slotb + (size_t)cap * 8 + (size_t)lcap * 4;
+  unsigned char* ring = s_raw + warp * warp_bytes;
+  double* img = reinterpret_cast<double*>(ring + (size_t)RR_NG * G * slotb);
+  uint32_t* list = reinterpret_cast<uint32_t*>(img + cap);
   for (int t = lane; t < cap; t += 32) img[t] = 0.;
 
   // ---- per-lane row descriptors ---------------------------------------------------------------------------
-  uint32_t my_r = 0;
-  uint32_t my_ip0 = 0;  // incidence offsets fit 32 bits (n_elem*nd < 2^32 is checked at setup)
+  uint32_t my_r = 0, my_ip0 = 0;  // incidence offsets fit 32 bits (n_elem*nd < 2^32 is checked at setup)
   uint64_t my_rp0 = 0;
   int my_cnt = 0, my_len = 0, my_cf = 0;
   double my_g = 0.;
   if (lane < nrows) {
     my_r = row_list ? row_list[base + lane] : (uint32_t)(base + lane);
-    my_ip0 = (uint32_t)inc_ptr[my_r];
-    my_cnt = (int)(inc_ptr[my_r + 1] - inc_ptr[my_r]);
-    my_rp0 = row_ptr[my_r];
-    my_len = (int)(row_ptr[my_r + 1] - my_rp0);
+    const uint64_t i0 = inc_ptr[my_r], i1 = inc_ptr[my_r + 1], p0 = row_ptr[my_r], p1 = row_ptr[my_r + 1];
+    my_ip0 = (uint32_t)i0; my_cnt = (int)(i1 - i0);
+    my_rp0 = p0; my_len = (int)(p1 - p0);
     my_cf = con_flag[my_r];
     if (my_cf && mode == FEASM_CONSTRAIN_HETEROGENEOUS) my_g = con_val[my_r];
   }
+  // exclusive prefix of the contributor counts -> offset of row l inside the batch list
+  int my_off = my_cnt;
+#pragma unroll
+  for (int o = 1; o < 32; o <<= 1) {
+    const int v = __shfl_up_sync(FULL, my_off, o);
+    if (lane >= o) my_off += v;
+  }
+  const int T = __shfl_sync(FULL, my_off, 31);  // <= lcap by the host's choice of RB
+  my_off -= my_cnt;
+  for (int j = 0; j < nrows; ++j) {
+    const int cj = __shfl_sync(FULL, my_cnt, j), oj = __shfl_sync(FULL, my_off, j);
+    const uint32_t ij = __shfl_sync(FULL, my_ip0, j);
+    for (int t = lane; t < cj; t += 32) list[oj + t] = inc[ij + t];
+  }
   __syncwarp();
 
-  struct It { int j, k, cnt; uint32_t ip0; };
-  auto load_row = [&](It& it) {
-    it.cnt = __shfl_sync(FULL, my_cnt, it.j);
-    it.ip0 = __shfl_sync(FULL, my_ip0, it.j);
-  };
-  auto advance = [&](It& it) {
-    it.k += U;
-    if (it.k >= it.cnt) { ++it.j; it.k = 0; if (it.j < nrows) load_row(it); }
-  };
-  auto stage1 = [&](const It& it) -> uint32_t {
-    return (lane < U && it.k + lane < it.cnt) ? inc[it.ip0 + it.k + lane] : INVALID;
-  };
-  double vN[U][NDC];
-  unsigned pN[U][NDC];
-  double fN = 0.;
-  auto stage2 = [&](uint32_t ea) {
-    fN = (ea != INVALID) ? __ldcs(kf + (uint64_t)ea * ldr + nd) : 0.;
-#pragma unroll
-    for (int u = 0; u < U; ++u) {
-      const uint32_t eu = __shfl_sync(FULL, ea, u);
-#pragma unroll
-      for (int c = 0; c < NDC; ++c) {
-        const int b = lane + 32 * c;
-        vN[u][c] = 0.; pN[u][c] = 0;
-        if (eu != INVALID && b < nd) {
-          vN[u][c] = __ldcs(kf + (uint64_t)eu * ldr + b);
-          pN[u][c] = pos[(uint64_t)eu * pld + b];
+  // lane -> (contributor within an issue instruction, 16 B chunk of its slot)
+  const int ct = slotb >> 4, ck = ldrb >> 4;
+  const int per = ct <= 32 ? 32 / ct : 1;
+  const int my_c = ct <= 32 ? lane / ct : 0, my_ch = ct <= 32 ? lane % ct : lane;
+  auto issue = [&](int k) {  // stage k: contributors [k*G, k*G+G) -> ring slots (k % NG)*G ..
+    const int t0 = k * G;
+    unsigned char* sbase = ring + (size_t)(k % RR_NG) * G * slotb;
+    for (int c0 = 0; c0 < G; c0 += per) {
+      const int c = c0 + my_c, t = t0 + c;
+      if (my_c < per && c < G && t < T) {
+        const uint64_t ea = list[t];
+        unsigned char* dst = sbase + (size_t)c * slotb;
+        for (int ch = my_ch; ch < ct; ch += 32) {
+          const unsigned char* src = ch < ck ? kf + ea * ldrb + (ch << 4) : pos + ea * pldb + ((ch - ck) << 4);
+          cp_async16(dst + (ch << 4), src);
         }
       }
     }
+    cp_async_commit();
   };
+  const int nstages = (T + G - 1) / G;
+#pragma unroll
+  for (int k = 0; k < RR_NG - 1; ++k) issue(k);  // empty groups past the end keep the group count uniform
 
-  It i1{0, 0, 0, 0}, i2, i3;
-  load_row(i1);
-  i2 = i1; i3 = i1;
-  uint32_t ea1 = stage1(i1), ea2, ea3;
-  advance(i1);
-  ea2 = ea1;
-  stage2(ea2);
-  ea1 = INVALID;
-  if (i1.j < nrows) { ea1 = stage1(i1); advance(i1); }
-
-  double bsum = 0., corr = 0.;
-  while (i3.j < nrows) {
-    double vC[U][NDC];
-    unsigned pC[U][NDC];
+  int j = 0, left = 0, row_con = 0;
+  double row_g = 0., bsum = 0., corr = 0.;
+  auto flush = [&]() {  // write row j out and clear the image
+    const uint64_t rp0 = __shfl_sync(FULL, my_rp0, j);
+    const int len = __shfl_sync(FULL, my_len, j);
+    const uint32_t r = __shfl_sync(FULL, my_r, j);
+    if (__any_sync(FULL, corr != 0.)) {
 #pragma unroll
-    for (int u = 0; u < U; ++u)
-#pragma unroll
-      for (int c = 0; c < NDC; ++c) { vC[u][c] = vN[u][c]; pC[u][c] = pN[u][c]; }
-    const double fC = fN;
-    ea3 = ea2;
-    // issue the loads of the next chunk, then the incidence ids of the one after
-    advance(i2);
-    if (i2.j < nrows) { ea2 = ea1; stage2(ea2); }
-    if (i1.j < nrows) { ea1 = stage1(i1); advance(i1); } else ea1 = INVALID;
-
-    // ---- accumulate chunk i3 into the row image ------------------------------------------------------------
-    const int row_con = __shfl_sync(FULL, my_cf, i3.j);
-    const double row_g = __shfl_sync(FULL, my_g, i3.j);
-#pragma unroll
-    for (int u = 0; u < U; ++u) {
-      const uint32_t eu = __shfl_sync(FULL, ea3, u);
-      const double fu = __shfl_sync(FULL, fC, u);
-      if (eu != INVALID) {  // warp-uniform
-        const int a = (int)(eu % (uint32_t)nd);
-#pragma unroll
-        for (int c = 0; c < NDC; ++c) {
-          const int b = lane + 32 * c;
-          if (b < nd) {
-            double val = vC[u][c];
-            const unsigned pp = pC[u][c];
-            if (row_con) {
-              val = (b == a) ? 1. : 0.;
-            } else if (pp & PosBits<PosT>::FLAG) {
-              if (mode == FEASM_CONSTRAIN_HETEROGENEOUS) corr += val * con_val[elem_dofs[(uint64_t)(eu / (uint32_t)nd) * nd + b]];
-              val = 0.;
-            }
-            img[pp & PosBits<PosT>::MASK] += val;  // positions within one element row are distinct
-          }
-        }
-        bsum += row_con ? row_g : fu;
-        __syncwarp();
-      }
+      for (int o = 16; o > 0; o >>= 1) corr += __shfl_xor_sync(FULL, corr, o);
+      bsum -= corr;
     }
-    // ---- last chunk of the row: write the row out -------------------------------------------------------------
-    if (i3.k + U >= i3.cnt) {
-      const uint64_t rp0 = __shfl_sync(FULL, my_rp0, i3.j);
-      const int len = __shfl_sync(FULL, my_len, i3.j);
-      const uint32_t r = __shfl_sync(FULL, my_r, i3.j);
-      if (__any_sync(FULL, corr != 0.)) {
-#pragma unroll
-        for (int o = 16; o > 0; o >>= 1) corr += __shfl_xor_sync(FULL, corr, o);
-        bsum -= corr;
+    for (int t = lane; t < len; t += 32) {
+      __stcs(values + rp0 + t, img[t]);
+      img[t] = 0.;
+    }
+    if (lane == 0) rhs[r] = bsum;
+    bsum = 0.; corr = 0.;
+    __syncwarp();
+  };
+  auto next_row = [&]() {  // advance to the next row that has contributors, flushing empty rows on the way
+    for (;;) {
+      left = __shfl_sync(FULL, my_cnt, j);
+      row_con = __shfl_sync(FULL, my_cf, j);
+      row_g = __shfl_sync(FULL, my_g, j);
+      if (left > 0) return;
+      flush();
+      if (++j >= nrows) return;
+    }
+  };
+  next_row();
+  for (int k = 0; k < nstages; ++k) {
+    issue(k + RR_NG - 1);
+    cp_async_wait<RR_NG - 1>();
+    __syncwarp();
+    const unsigned char* sbase = ring + (size_t)(k % RR_NG) * G * slotb;
+    const int cend = T - k * G < G ? T - k * G : G;
+    for (int c = 0; c < cend; ++c) {
+      const uint32_t ea = list[k * G + c];
+      const unsigned char* slot = sbase + (size_t)c * slotb;
+      const double* kv = reinterpret_cast<const double*>(slot);
+      const PosT* pv = reinterpret_cast<const PosT*>(slot + ldrb);
+      const int a = (int)(ea % (uint32_t)nd);
+      for (int b = lane; b < nd; b += 32) {
+        double val = kv[b];
+        const unsigned pp = pv[b];
+        if (row_con) {
+          val = (b == a) ? 1. : 0.;
+        } else if (pp & PosBits<PosT>::FLAG) {
+          if (mode == FEASM_CONSTRAIN_HETEROGENEOUS) corr += val * con_val[elem_dofs[(uint64_t)(ea / (uint32_t)nd) * nd + b]];
+          val = 0.;
+        }
+        img[pp & PosBits<PosT>::MASK] += val;  // positions within one element row are distinct
       }
-      for (int t = lane; t < len; t += 32) {
-        __stcs(values + rp0 + t, img[t]);
-        img[t] = 0.;
-      }
-      if (lane == 0) rhs[r] = bsum;
-      bsum = 0.; corr = 0.;
+      bsum += row_con ? row_g : kv[nd];
       __syncwarp();
+      if (--left == 0) {
+        flush();
+        if (++j < nrows) next_row();
+      }
     }
-    advance(i3);
+    __syncwarp();  // the slots of this stage are refilled by the next issue
   }
+  cp_async_wait<0>();
 }
 
 // Fallback for rows longer than the shared-memory budget: accumulate straight into the (zeroed) global row.
@@ -283,41 +291,39 @@ __global__ void k_add_matrix(const double* __restrict__ dm, const uint32_t* __re
   else if (v != 0.) atomicAdd(&flags[1], 1);  // zero may be "added" to a missing entry (sparse_matrix.h:300-303)
 }
 
-template <typename PosT, int NDC>
-int launch_row_reduce_t(feasm_ctx* ctx, int mode, const uint32_t* d_row_list, int64_t n_list, cudaStream_t stream) {
-  constexpr int WARPS = 8;
-  const int cap = (int)ctx->max_row_len;
-  const size_t smem = sizeof(double) * (size_t)WARPS * cap;
+template <typename PosT>
+int launch_row_reduce(feasm_ctx* ctx, int mode, const uint32_t* d_row_list, int64_t n_list, cudaStream_t stream) {
+  constexpr int WARPS = 4;
+  const int cap = ((int)ctx->max_row_len + 1) & ~1;  // even: every warp's ring stays 16 B aligned
   const int ldr = feasm_ldr(ctx->nd), pld = feasm_pld(ctx->nd, (int)sizeof(PosT));
-  const PosT* pos = static_cast<const PosT*>(ctx->d_pos);
-  if (smem <= ctx->smem_optin) {
-    auto kern = k_row_reduce<PosT, NDC, WARPS>;
+  const int ldrb = ldr * 8, pldb = pld * (int)sizeof(PosT), slotb = ldrb + pldb;
+  // ring: about 12 contributors in flight per warp, at least 2 per stage, at most ~8 KB
+  int G = 4;
+  while (G > 2 && RR_NG * G * slotb > 8192) --G;
+  const int lcap = 256;
+  int RB = ctx->max_inc ? (int)(lcap / ctx->max_inc) : 32;
+  if (RB > 32) RB = 32;
+  const size_t warp_bytes = (size_t)RR_NG * G * slotb + (size_t)cap * 8 + (size_t)lcap * 4;
+  const size_t smem = WARPS * warp_bytes;
+  if (RB >= 1 && smem <= ctx->smem_optin && (warp_bytes % 16) == 0) {
+    auto kern = k_row_reduce<PosT, WARPS>;
     FEASM_CUDA(ctx, cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-    const int64_t batches = (n_list + 31) / 32;
+    const int64_t batches = (n_list + RB - 1) / RB;
     const unsigned grid = (unsigned)((batches + WARPS - 1) / WARPS);
     if (grid)
-      kern<<<grid, WARPS * 32, smem, stream>>>(ctx->d_row_ptr, ctx->d_inc_ptr, ctx->d_inc, pos, ctx->d_kf, ctx->nd, ldr, pld,
-                                               d_row_list, n_list, cap, ctx->d_con_flag, ctx->d_con_val, ctx->d_elem_dofs,
-                                               mode, ctx->d_values, ctx->d_rhs);
+      kern<<<grid, WARPS * 32, smem, stream>>>(ctx->d_row_ptr, ctx->d_inc_ptr, ctx->d_inc, (const unsigned char*)ctx->d_pos,
+                                               (const unsigned char*)ctx->d_kf, ctx->nd, ldrb, pldb, G, RB, lcap, cap, d_row_list,
+                                               n_list, ctx->d_con_flag, ctx->d_con_val, ctx->d_elem_dofs, mode, ctx->d_values,
+                                               ctx->d_rhs);
   } else {
     if (d_row_list) return feasm_fail(ctx, FEASM_ERR_NOMEM, "rows too long for the shared-memory row reduction");
     const unsigned grid = (unsigned)((ctx->n_rows * 32 + 255) / 256);
-    k_row_reduce_global<PosT><<<grid, 256, 0, stream>>>(ctx->d_row_ptr, ctx->d_inc_ptr, ctx->d_inc, pos, ctx->d_kf, ctx->nd, ldr,
-                                                        pld, ctx->n_rows, ctx->d_con_flag, ctx->d_con_val, ctx->d_elem_dofs,
-                                                        mode, ctx->d_values, ctx->d_rhs);
+    k_row_reduce_global<PosT><<<grid, 256, 0, stream>>>(ctx->d_row_ptr, ctx->d_inc_ptr, ctx->d_inc, (const PosT*)ctx->d_pos, ctx->d_kf,
+                                                        ctx->nd, ldr, pld, ctx->n_rows, ctx->d_con_flag, ctx->d_con_val,
+                                                        ctx->d_elem_dofs, mode, ctx->d_values, ctx->d_rhs);
   }
   FEASM_CUDA(ctx, cudaGetLastError());
   return FEASM_OK;
-}
-
-template <typename PosT>
-int launch_row_reduce(feasm_ctx* ctx, int mode, const uint32_t* d_row_list, int64_t n_list, cudaStream_t stream) {
-  const int ndc = (ctx->nd + 31) / 32;
-  if (ndc == 1) return launch_row_reduce_t<PosT, 1>(ctx, mode, d_row_list, n_list, stream);
-  if (ndc == 2) return launch_row_reduce_t<PosT, 2>(ctx, mode, d_row_list, n_list, stream);
-  if (ndc == 3) return launch_row_reduce_t<PosT, 3>(ctx, mode, d_row_list, n_list, stream);
-  if (ndc == 4) return launch_row_reduce_t<PosT, 4>(ctx, mode, d_row_list, n_list, stream);
-  return feasm_fail(ctx, FEASM_ERR_ARG, "more than 128 dofs per element");
 }
 
 }  // namespace
