@@ -81,26 +81,61 @@ __device__ __forceinline__ bool affine_check_lane(const double* X, int lane) {
   return nd <= 1e-12 * (na + nb);
 }
 
+// sin (add = 0) or cos (add = 1) of a moderate argument, branch free so that the nine evaluations of one forcing
+// value interleave in the FP64 pipe: round-to-nearest quadrant via the 1.5*2^52 magic add, three-term Cody-Waite
+// reduction with FMA (pi/2 split into correctly rounded hi/mid/lo), then the classic fdlibm kernel polynomials with
+// the coefficient set selected per lane.  Max error 1 ulp against glibc over |a| < 1e3 (checked on the host,
+// oracle/check_trig.c); callers guard |a| <= 6e4 and use the library functions beyond.
+__device__ __forceinline__ double trig_fast(double a, int add) {
+  const double MAGIC = 6755399441055744.0;
+  const double q = __fma_rn(a, 0x1.45f306dc9c883p-1, MAGIC);
+  const int n = __double2loint(q) + add;
+  const double j = __dadd_rn(q, -MAGIC);
+  double r = __fma_rn(-j, 0x1.921fb54442d18p+0, a);
+  r = __fma_rn(-j, 0x1.1a62633145c07p-54, r);
+  r = __fma_rn(-j, -0x1.f1976b7ed8fbcp-110, r);
+  const double x2 = __dmul_rn(r, r);
+  const bool odd = n & 1;
+  double z = odd ? -1.13596475577881948265e-11 : 1.58969099521155010221e-10;
+  z = __fma_rn(z, x2, odd ? 2.08757232129817482790e-09 : -2.50507602534068634195e-08);
+  z = __fma_rn(z, x2, odd ? -2.75573143513906633035e-07 : 2.75573137070700676789e-06);
+  z = __fma_rn(z, x2, odd ? 2.48015872894767294178e-05 : -1.98412698298579493134e-04);
+  z = __fma_rn(z, x2, odd ? -1.38888888888741095749e-03 : 8.33333333332248946124e-03);
+  z = __fma_rn(z, x2, odd ? 4.16666666666666019037e-02 : -1.66666666666666324348e-01);
+  const double w = __fma_rn(z, x2, odd ? -0.5 : 0.0);
+  const double res = __fma_rn(w, odd ? x2 : r, odd ? 1.0 : r);
+  return (n & 2) ? -res : res;
+}
+
 // introduction_ex4.C:500-537 with exact_solution of introduction_ex3/exact_solution.C:40-47.  The seven
 // exact_solution() calls share nine distinct trig values; every product below is evaluated in the example's order
-// ((cos * sin) * cos), so the result equals the literal seven-call form bit for bit.
-__device__ __forceinline__ double ex4_forcing_dev(double x, double y, double z) {
-  // explicit _rn intrinsics: no FMA contraction, so only the libm sin/cos can differ from the host evaluation
+// ((cos * sin) * cos), so the result equals the literal seven-call form bit for bit up to the last bit of sin/cos.
+// Explicit _rn intrinsics: no FMA contraction.  x / eps is evaluated as the correctly rounded quotient through
+// q0 = x*(1/eps), r = fma(-q0, eps, x), q = fma(r, 1/eps, q0) (Markstein; checked exhaustively-at-random on the host).
+template <bool FAST>
+__device__ __forceinline__ double ex4_forcing_t(double x, double y, double z) {
   const double hp = .5 * 3.141592653589793;  // .5 * acos(-1.)
   const double eps = 1.e-3;
-  const double cx0 = cos(__dmul_rn(hp, x)), cxm = cos(__dmul_rn(hp, __dadd_rn(x, -eps))), cxp = cos(__dmul_rn(hp, __dadd_rn(x, eps)));
-  const double sy0 = sin(__dmul_rn(hp, y)), sym = sin(__dmul_rn(hp, __dadd_rn(y, -eps))), syp = sin(__dmul_rn(hp, __dadd_rn(y, eps)));
-  const double cz0 = cos(__dmul_rn(hp, z)), czm = cos(__dmul_rn(hp, __dadd_rn(z, -eps))), czp = cos(__dmul_rn(hp, __dadd_rn(z, eps)));
+  auto cs = [](double a) { return FAST ? trig_fast(a, 1) : cos(a); };
+  auto sn = [](double a) { return FAST ? trig_fast(a, 0) : sin(a); };
+  const double cx0 = cs(__dmul_rn(hp, x)), cxm = cs(__dmul_rn(hp, __dadd_rn(x, -eps))), cxp = cs(__dmul_rn(hp, __dadd_rn(x, eps)));
+  const double sy0 = sn(__dmul_rn(hp, y)), sym = sn(__dmul_rn(hp, __dadd_rn(y, -eps))), syp = sn(__dmul_rn(hp, __dadd_rn(y, eps)));
+  const double cz0 = cs(__dmul_rn(hp, z)), czm = cs(__dmul_rn(hp, __dadd_rn(z, -eps))), czp = cs(__dmul_rn(hp, __dadd_rn(z, eps)));
   auto u = [](double a, double b, double c) { return __dmul_rn(__dmul_rn(a, b), c); };
-  auto fd = [eps](double m, double p, double u0) {
-    return __ddiv_rn(__ddiv_rn(__dadd_rn(__dadd_rn(m, p), __dmul_rn(-2., u0)), eps), eps);
+  auto dv = [eps](double a) {
+    if (!FAST) return __ddiv_rn(a, eps);
+    const double rc = 1. / eps;  // folded at compile time
+    const double q0 = __dmul_rn(a, rc);
+    return __fma_rn(__fma_rn(-q0, eps, a), rc, q0);
   };
+  auto fd = [&](double m, double p, double u0) { return dv(dv(__dadd_rn(__dadd_rn(m, p), __dmul_rn(-2., u0)))); };
   const double u0 = u(cx0, sy0, cz0);
   const double uxx = fd(u(cxm, sy0, cz0), u(cxp, sy0, cz0), u0);
   const double uyy = fd(u(cx0, sym, cz0), u(cx0, syp, cz0), u0);
   const double uzz = fd(u(cx0, sy0, czm), u(cx0, sy0, czp), u0);
   return -__dadd_rn(__dadd_rn(uxx, uyy), uzz);
 }
+__device__ __noinline__ double ex4_forcing_lib(double x, double y, double z) { return ex4_forcing_t<false>(x, y, z); }
 
 template <int NPE, int NQ, int WARPS>
 __global__ void __launch_bounds__(WARPS * 32, 1)
@@ -154,19 +189,37 @@ k_elem_poisson(const double* __restrict__ xyz, const uint32_t* __restrict__ conn
       if (affine) {
         // compute_affine_map (fe_map.C:1167-1244): the Jacobian at qp 0 only — lane c < 9 sums component c —
         // and xyz at every qp (:1190-1197)
+        // (sums split three ways: independent FP64 chains instead of one 27-deep dependent chain)
         double d = 0.;
         if (lane < 9) {
           const double* tabd = s_dxi + (lane / 3) * (NPE * NQ);
           const int cd = lane % 3;
-#pragma unroll 9
-          for (int i = 0; i < NPE; ++i) d += tabd[i * NQ] * X[3 * i + cd];
+          double d0 = 0., d1 = 0., d2 = 0.;
+#pragma unroll
+          for (int i = 0; i + 2 < NPE; i += 3) {
+            d0 += tabd[i * NQ] * X[3 * i + cd];
+            d1 += tabd[(i + 1) * NQ] * X[3 * (i + 1) + cd];
+            d2 += tabd[(i + 2) * NQ] * X[3 * (i + 2) + cd];
+          }
+#pragma unroll
+          for (int i = NPE - NPE % 3; i < NPE; ++i) d0 += tabd[i * NQ] * X[3 * i + cd];
+          d = (d0 + d1) + d2;
         }
         if (forcing == FEASM_FORCING_EX4_FD) {
-#pragma unroll 9
-          for (int i = 0; i < NPE; ++i) {
+          double x1 = 0., y1 = 0., z1 = 0., x2 = 0., y2 = 0., z2 = 0.;
+#pragma unroll
+          for (int i = 0; i + 2 < NPE; i += 3) {
+            const double p0 = s_phi[i * NQ + q], p1 = s_phi[(i + 1) * NQ + q], p2 = s_phi[(i + 2) * NQ + q];
+            x += p0 * X[3 * i]; y += p0 * X[3 * i + 1]; z += p0 * X[3 * i + 2];
+            x1 += p1 * X[3 * i + 3]; y1 += p1 * X[3 * i + 4]; z1 += p1 * X[3 * i + 5];
+            x2 += p2 * X[3 * i + 6]; y2 += p2 * X[3 * i + 7]; z2 += p2 * X[3 * i + 8];
+          }
+#pragma unroll
+          for (int i = NPE - NPE % 3; i < NPE; ++i) {
             const double p = s_phi[i * NQ + q];
             x += p * X[3 * i]; y += p * X[3 * i + 1]; z += p * X[3 * i + 2];
           }
+          x = (x + x1) + x2; y = (y + y1) + y2; z = (z + z1) + z2;
         }
         xa = __shfl_sync(0xffffffffu, d, 0); ya = __shfl_sync(0xffffffffu, d, 1); za = __shfl_sync(0xffffffffu, d, 2);
         xb = __shfl_sync(0xffffffffu, d, 3); yb = __shfl_sync(0xffffffffu, d, 4); zb = __shfl_sync(0xffffffffu, d, 5);
@@ -195,9 +248,12 @@ k_elem_poisson(const double* __restrict__ xyz, const uint32_t* __restrict__ conn
       S[3] = (za * yc - ya * zc) * s; S[4] = (xa * zc - za * xc) * s; S[5] = (ya * xc - xa * yc) * s;
       S[6] = (ya * zb - za * yb) * s; S[7] = (za * xb - xa * zb) * s; S[8] = (xa * yb - ya * xb) * s;
       double f = 0.;
-      if (lane < NQ) {
-        if (forcing == FEASM_FORCING_EX4_FD) f = ex4_forcing_dev(x, y, z);
-        else if (forcing == FEASM_FORCING_TABULATED) f = f_tab[e * NQ + lane];
+      if (forcing == FEASM_FORCING_EX4_FD) {
+        // every lane evaluates (pad lanes repeat qp 0): no divergence; huge coordinates take the library path
+        const bool big = !(fabs(x) + fabs(y) + fabs(z) < 2.e4);
+        f = __any_sync(0xffffffffu, big) ? ex4_forcing_lib(x, y, z) : ex4_forcing_t<true>(x, y, z);
+      } else if (forcing == FEASM_FORCING_TABULATED && lane < NQ) {
+        f = f_tab[e * NQ + lane];
       }
       fw[lane] = lane < NQ ? JxW * f : 0.;
     }
@@ -264,8 +320,16 @@ k_elem_poisson(const double* __restrict__ xyz, const uint32_t* __restrict__ conn
     if (lane < NPE) {
       double Fe = 0.;
       if (forcing != FEASM_FORCING_NONE) {
-#pragma unroll 3
-        for (int q = 0; q < NQ; ++q) Fe += fw[q] * s_phi[lane * NQ + q];
+        double f1 = 0., f2 = 0.;
+#pragma unroll
+        for (int q = 0; q + 2 < NQ; q += 3) {
+          Fe += fw[q] * s_phi[lane * NQ + q];
+          f1 += fw[q + 1] * s_phi[lane * NQ + q + 1];
+          f2 += fw[q + 2] * s_phi[lane * NQ + q + 2];
+        }
+#pragma unroll
+        for (int q = NQ - NQ % 3; q < NQ; ++q) Fe += fw[q] * s_phi[lane * NQ + q];
+        Fe = (Fe + f1) + f2;
       }
       out[lane * C::LDR + NPE] = Fe;
     }
