@@ -25,10 +25,15 @@ bool feasm_make_tables(int elem_type, int qorder, FeasmTables& t, std::string& e
 // Element buffer KF[e][a][LDR]: row a of element e = Ke(a, 0..nd-1) followed by Fe(a) at column nd, padded to a
 // whole number of 32 B sectors (HEX27: 28 doubles = 224 B).  One row is what one (element, local dof) pair
 // contributes to one CSR row, so the row reduction reads it as one contiguous run.
-constexpr int feasm_ldr(int nd) { return (nd + 1 + 3) & ~3; }
+#ifdef __CUDACC__
+#define FEASM_HD __host__ __device__
+#else
+#define FEASM_HD
+#endif
+FEASM_HD constexpr int feasm_ldr(int nd) { return (nd + 1 + 3) & ~3; }
 // Position map pos[e][a][PLD]: row stride padded to whole sectors; entry = column position inside the CSR row,
 // top bit = "column dof is constrained".  uint8 when every row has <= 128 entries, else uint16.
-constexpr int feasm_pld(int nd, int pos_bytes) { return ((nd * pos_bytes + 31) & ~31) / pos_bytes; }
+FEASM_HD constexpr int feasm_pld(int nd, int pos_bytes) { return ((nd * pos_bytes + 31) & ~31) / pos_bytes; }
 
 struct feasm_ctx {
   int device = 0;

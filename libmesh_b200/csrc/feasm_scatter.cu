@@ -34,20 +34,31 @@ __device__ __forceinline__ void cp_async_wait() { asm volatile("cp.async.wait_gr
 // several KB per warp — are in flight while one is accumulated into the CSR row image in shared memory.  Rows are
 // finished strictly in order and every row is summed in element order, so the result is bitwise reproducible.
 constexpr int RR_NG = 4;
-template <typename PosT, int WARPS>
+// ring geometry for a compile-time element size: about 12 contributors in flight per warp, ring <= 8 KB
+__host__ __device__ constexpr int rr_stage(int slotb) {
+  int g = 4;
+  while (g > 2 && RR_NG * g * slotb > 8192) --g;
+  return g;
+}
+// ND = dofs per element when known at compile time (strides, the lane loops and the division by nd fold away),
+// 0 = generic (runtime nd).
+template <typename PosT, int ND, int WARPS>
 __global__ void __launch_bounds__(WARPS * 32)
 k_row_reduce(const uint64_t* __restrict__ row_ptr, const uint64_t* __restrict__ inc_ptr, const uint32_t* __restrict__ inc,
-             const unsigned char* __restrict__ pos, const unsigned char* __restrict__ kf, int nd, int ldrb, int pldb, int G,
-             int RB, int lcap, int cap, const uint32_t* __restrict__ row_list, int64_t n_list,
-             const uint8_t* __restrict__ con_flag, const double* __restrict__ con_val,
-             const uint32_t* __restrict__ elem_dofs, int mode, double* __restrict__ values, double* __restrict__ rhs) {
+             const unsigned char* __restrict__ pos, const unsigned char* __restrict__ kf, int nd_rt, int RB, int lcap, int cap,
+             const uint32_t* __restrict__ row_list, int64_t n_list, const uint8_t* __restrict__ con_flag,
+             const double* __restrict__ con_val, const uint32_t* __restrict__ elem_dofs, int mode,
+             double* __restrict__ values, double* __restrict__ rhs) {
   constexpr unsigned FULL = 0xffffffffu;
+  const int nd = ND ? ND : nd_rt;
+  const int ldrb = feasm_ldr(nd) * 8, pldb = feasm_pld(nd, (int)sizeof(PosT)) * (int)sizeof(PosT), slotb = ldrb + pldb;
+  const int G = rr_stage(slotb);
+  constexpr int NDC = ND ? (ND + 31) / 32 : 4;  // lane passes over one element row
   extern __shared__ __align__(16) unsigned char s_raw[];
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const int64_t base = (blockIdx.x * (int64_t)WARPS + warp) * RB;
   if (base >= n_list) return;
   const int nrows = (int)(n_list - base < RB ? n_list - base : RB);
-  const int slotb = ldrb + pldb;
   const size_t warp_bytes = (size_t)RR_NG * G * slotb + (size_t)cap * 8 + (size_t)lcap * 4;
   unsigned char* ring = s_raw + warp * warp_bytes;
   double* img = reinterpret_cast<double*>(ring + (size_t)RR_NG * G * slotb);
@@ -76,10 +87,16 @@ k_row_reduce(const uint64_t* __restrict__ row_ptr, const uint64_t* __restrict__ 
   }
   const int T = __shfl_sync(FULL, my_off, 31);  // <= lcap by the host's choice of RB
   my_off -= my_cnt;
-  for (int j = 0; j < nrows; ++j) {
-    const int cj = __shfl_sync(FULL, my_cnt, j), oj = __shfl_sync(FULL, my_off, j);
-    const uint32_t ij = __shfl_sync(FULL, my_ip0, j);
-    for (int t = lane; t < cj; t += 32) list[oj + t] = inc[ij + t];
+  if (row_list == nullptr) {
+    // consecutive rows: the batch's incidence ids are one contiguous run
+    const uint32_t i0 = __shfl_sync(FULL, my_ip0, 0);
+    for (int t = lane; t < T; t += 32) list[t] = inc[i0 + t];
+  } else {
+    for (int j = 0; j < nrows; ++j) {
+      const int cj = __shfl_sync(FULL, my_cnt, j), oj = __shfl_sync(FULL, my_off, j);
+      const uint32_t ij = __shfl_sync(FULL, my_ip0, j);
+      for (int t = lane; t < cj; t += 32) list[oj + t] = inc[ij + t];
+    }
   }
   __syncwarp();
 
@@ -90,11 +107,12 @@ k_row_reduce(const uint64_t* __restrict__ row_ptr, const uint64_t* __restrict__ 
   auto issue = [&](int k) {  // stage k: contributors [k*G, k*G+G) -> ring slots (k % NG)*G ..
     const int t0 = k * G;
     unsigned char* sbase = ring + (size_t)(k % RR_NG) * G * slotb;
+#pragma unroll
     for (int c0 = 0; c0 < G; c0 += per) {
       const int c = c0 + my_c, t = t0 + c;
       if (my_c < per && c < G && t < T) {
         const uint64_t ea = list[t];
-        unsigned char* dst = sbase + (size_t)c * slotb;
+        unsigned char* dst = sbase + c * slotb;
         for (int ch = my_ch; ch < ct; ch += 32) {
           const unsigned char* src = ch < ck ? kf + ea * ldrb + (ch << 4) : pos + ea * pldb + ((ch - ck) << 4);
           cp_async16(dst + (ch << 4), src);
@@ -118,8 +136,9 @@ k_row_reduce(const uint64_t* __restrict__ row_ptr, const uint64_t* __restrict__ 
       for (int o = 16; o > 0; o >>= 1) corr += __shfl_xor_sync(FULL, corr, o);
       bsum -= corr;
     }
+    double* dst = values + rp0;
     for (int t = lane; t < len; t += 32) {
-      __stcs(values + rp0 + t, img[t]);
+      __stcs(dst + t, img[t]);
       img[t] = 0.;
     }
     if (lane == 0) rhs[r] = bsum;
@@ -141,26 +160,38 @@ k_row_reduce(const uint64_t* __restrict__ row_ptr, const uint64_t* __restrict__ 
     issue(k + RR_NG - 1);
     cp_async_wait<RR_NG - 1>();
     __syncwarp();
-    const unsigned char* sbase = ring + (size_t)(k % RR_NG) * G * slotb;
+    const unsigned char* sbase = ring + (k % RR_NG) * G * slotb;
     const int cend = T - k * G < G ? T - k * G : G;
-    for (int c = 0; c < cend; ++c) {
-      const uint32_t ea = list[k * G + c];
-      const unsigned char* slot = sbase + (size_t)c * slotb;
+#pragma unroll
+    for (int c = 0; c < G; ++c) {
+      if (c >= cend) break;
+      const unsigned char* slot = sbase + c * slotb;
       const double* kv = reinterpret_cast<const double*>(slot);
       const PosT* pv = reinterpret_cast<const PosT*>(slot + ldrb);
-      const int a = (int)(ea % (uint32_t)nd);
-      for (int b = lane; b < nd; b += 32) {
-        double val = kv[b];
-        const unsigned pp = pv[b];
-        if (row_con) {
-          val = (b == a) ? 1. : 0.;
-        } else if (pp & PosBits<PosT>::FLAG) {
-          if (mode == FEASM_CONSTRAIN_HETEROGENEOUS) corr += val * con_val[elem_dofs[(uint64_t)(ea / (uint32_t)nd) * nd + b]];
-          val = 0.;
+      if (!row_con) {
+#pragma unroll
+        for (int bb = 0; bb < NDC; ++bb) {
+          const int b = lane + 32 * bb;
+          if (b < nd) {
+            double val = kv[b];
+            const unsigned pp = pv[b];
+            if (pp & PosBits<PosT>::FLAG) {  // column dof constrained (rare)
+              if (mode == FEASM_CONSTRAIN_HETEROGENEOUS) {
+                const uint32_t ea = list[k * G + c];
+                corr += val * con_val[elem_dofs[(uint64_t)(ea / (uint32_t)nd) * nd + b]];
+              }
+              val = 0.;
+            }
+            img[pp & PosBits<PosT>::MASK] += val;  // positions within one element row are distinct
+          }
         }
-        img[pp & PosBits<PosT>::MASK] += val;  // positions within one element row are distinct
+        bsum += kv[nd];
+      } else {
+        // constrained row: this element contributes K(a,a) = 1, F(a) = g
+        const int a = (int)(list[k * G + c] % (uint32_t)nd);
+        if (lane == (a & 31)) img[pv[a] & PosBits<PosT>::MASK] += 1.;
+        bsum += row_g;
       }
-      bsum += row_con ? row_g : kv[nd];
       __syncwarp();
       if (--left == 0) {
         flush();
@@ -291,30 +322,27 @@ __global__ void k_add_matrix(const double* __restrict__ dm, const uint32_t* __re
   else if (v != 0.) atomicAdd(&flags[1], 1);  // zero may be "added" to a missing entry (sparse_matrix.h:300-303)
 }
 
-template <typename PosT>
-int launch_row_reduce(feasm_ctx* ctx, int mode, const uint32_t* d_row_list, int64_t n_list, cudaStream_t stream) {
+template <typename PosT, int ND>
+int launch_row_reduce_t(feasm_ctx* ctx, int mode, const uint32_t* d_row_list, int64_t n_list, cudaStream_t stream) {
   constexpr int WARPS = 4;
   const int cap = ((int)ctx->max_row_len + 1) & ~1;  // even: every warp's ring stays 16 B aligned
   const int ldr = feasm_ldr(ctx->nd), pld = feasm_pld(ctx->nd, (int)sizeof(PosT));
-  const int ldrb = ldr * 8, pldb = pld * (int)sizeof(PosT), slotb = ldrb + pldb;
-  // ring: about 12 contributors in flight per warp, at least 2 per stage, at most ~8 KB
-  int G = 4;
-  while (G > 2 && RR_NG * G * slotb > 8192) --G;
+  const int slotb = ldr * 8 + pld * (int)sizeof(PosT);
+  const int G = rr_stage(slotb);
   const int lcap = 256;
   int RB = ctx->max_inc ? (int)(lcap / ctx->max_inc) : 32;
   if (RB > 32) RB = 32;
   const size_t warp_bytes = (size_t)RR_NG * G * slotb + (size_t)cap * 8 + (size_t)lcap * 4;
   const size_t smem = WARPS * warp_bytes;
-  if (RB >= 1 && smem <= ctx->smem_optin && (warp_bytes % 16) == 0) {
-    auto kern = k_row_reduce<PosT, WARPS>;
+  if (RB >= 1 && smem <= ctx->smem_optin && ctx->nd <= 128) {
+    auto kern = k_row_reduce<PosT, ND, WARPS>;
     FEASM_CUDA(ctx, cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
     const int64_t batches = (n_list + RB - 1) / RB;
     const unsigned grid = (unsigned)((batches + WARPS - 1) / WARPS);
     if (grid)
       kern<<<grid, WARPS * 32, smem, stream>>>(ctx->d_row_ptr, ctx->d_inc_ptr, ctx->d_inc, (const unsigned char*)ctx->d_pos,
-                                               (const unsigned char*)ctx->d_kf, ctx->nd, ldrb, pldb, G, RB, lcap, cap, d_row_list,
-                                               n_list, ctx->d_con_flag, ctx->d_con_val, ctx->d_elem_dofs, mode, ctx->d_values,
-                                               ctx->d_rhs);
+                                               (const unsigned char*)ctx->d_kf, ctx->nd, RB, lcap, cap, d_row_list, n_list,
+                                               ctx->d_con_flag, ctx->d_con_val, ctx->d_elem_dofs, mode, ctx->d_values, ctx->d_rhs);
   } else {
     if (d_row_list) return feasm_fail(ctx, FEASM_ERR_NOMEM, "rows too long for the shared-memory row reduction");
     const unsigned grid = (unsigned)((ctx->n_rows * 32 + 255) / 256);
@@ -324,6 +352,17 @@ int launch_row_reduce(feasm_ctx* ctx, int mode, const uint32_t* d_row_list, int6
   }
   FEASM_CUDA(ctx, cudaGetLastError());
   return FEASM_OK;
+}
+
+template <typename PosT>
+int launch_row_reduce(feasm_ctx* ctx, int mode, const uint32_t* d_row_list, int64_t n_list, cudaStream_t stream) {
+  switch (ctx->nd) {
+    case 8: return launch_row_reduce_t<PosT, 8>(ctx, mode, d_row_list, n_list, stream);
+    case 10: return launch_row_reduce_t<PosT, 10>(ctx, mode, d_row_list, n_list, stream);
+    case 27: return launch_row_reduce_t<PosT, 27>(ctx, mode, d_row_list, n_list, stream);
+    case 81: return launch_row_reduce_t<PosT, 81>(ctx, mode, d_row_list, n_list, stream);
+    default: return launch_row_reduce_t<PosT, 0>(ctx, mode, d_row_list, n_list, stream);
+  }
 }
 
 }  // namespace
