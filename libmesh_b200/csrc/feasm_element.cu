@@ -15,6 +15,8 @@
 //      they are contracted with plain DFMA against fragments broadcast by shuffle.
 //   D. Fe, then fragments stored straight to the element buffer KF[e][i][LDR] (Ke row | Fe), mirrored for the
 //      lower triangle.  Constraints are NOT applied here: the row reduction applies them (feasm_scatter.cu).
+#include <cstdlib>
+
 #include "feasm_internal.h"
 
 namespace {
@@ -162,19 +164,22 @@ k_elem_poisson(const double* __restrict__ xyz, const uint32_t* __restrict__ conn
 
   const int64_t stride = (int64_t)gridDim.x * WARPS;
   int64_t e = e0 + (int64_t)blockIdx.x * WARPS + warp;
-  // prefetch registers: node `lane` of the next element
+  // prefetch registers: coordinates of node `lane` of the next element, node id of the element after it (the
+  // dependent conn -> xyz load chain is split across two iterations, so neither load is waited for)
   double nx = 0., ny = 0., nz = 0.;
+  uint32_t nnode = 0;
   if (e < e1 && lane < NPE) {
     const uint64_t node = conn[e * NPE + lane];
     nx = xyz[node * 3]; ny = xyz[node * 3 + 1]; nz = xyz[node * 3 + 2];
+    if (e + stride < e1) nnode = conn[(e + stride) * NPE + lane];
   }
   for (; e < e1; e += stride) {
-    if (lane < NPE) { X[3 * lane] = nx; X[3 * lane + 1] = ny; X[3 * lane + 2] = nz; }
-    {
-      const int64_t en = e + stride;
-      if (en < e1 && lane < NPE) {
-        const uint64_t node = conn[en * NPE + lane];
+    if (lane < NPE) {
+      X[3 * lane] = nx; X[3 * lane + 1] = ny; X[3 * lane + 2] = nz;
+      if (e + stride < e1) {
+        const uint64_t node = nnode;
         nx = xyz[node * 3]; ny = xyz[node * 3 + 1]; nz = xyz[node * 3 + 2];
+        if (e + 2 * stride < e1) nnode = conn[(e + 2 * stride) * NPE + lane];
       }
     }
     __syncwarp();
@@ -243,7 +248,7 @@ k_elem_poisson(const double* __restrict__ xyz, const uint32_t* __restrict__ conn
       const bool bad = !(jac > 0.);
       if (bad && lane < NQ) atomicAdd(&flags[0], 1);  // check_for_degenerate_map, fe_map.C:467-506
       const double JxW = (affine && q != 0) ? jac * s_qw[0] / s_qw[0] * s_qw[q] : jac * s_qw[q];  // fe_map.C:1242 / :1052
-      const double s = bad ? 0. : sqrt(jac) / jac;
+      const double s = bad ? 0. : rsqrt(jac);  // sqrt(jac) / jac
       S[0] = (yb * zc - zb * yc) * s; S[1] = (zb * xc - xb * zc) * s; S[2] = (xb * yc - yb * xc) * s;
       S[3] = (za * yc - ya * zc) * s; S[4] = (xa * zc - za * xc) * s; S[5] = (ya * xc - xa * yc) * s;
       S[6] = (ya * zb - za * yb) * s; S[7] = (za * xb - xa * zb) * s; S[8] = (xa * yb - ya * xb) * s;
@@ -386,7 +391,11 @@ int launch_poisson(feasm_ctx* ctx, const feasm_params& p, const double* d_f, int
 int feasm_launch_element_kernel(feasm_ctx* ctx, const feasm_params& p, const double* d_f, int64_t e0, int64_t e1,
                                 double* d_kf) {
   if (p.problem == FEASM_POISSON) {
-    if (ctx->elem_type == FEASM_HEX27 && ctx->tab_nq == 27) return launch_poisson<27, 27, 12>(ctx, p, d_f, e0, e1, d_kf);
+    if (ctx->elem_type == FEASM_HEX27 && ctx->tab_nq == 27) {
+      static const int warps = getenv("FEASM_ELEM_WARPS") ? atoi(getenv("FEASM_ELEM_WARPS")) : 16;  // tuning knob
+      if (warps == 12) return launch_poisson<27, 27, 12>(ctx, p, d_f, e0, e1, d_kf);
+      return launch_poisson<27, 27, 16>(ctx, p, d_f, e0, e1, d_kf);
+    }
     if (ctx->elem_type == FEASM_HEX8 && ctx->tab_nq == 8) return launch_poisson<8, 8, 16>(ctx, p, d_f, e0, e1, d_kf);
     if (ctx->elem_type == FEASM_HEX8 && ctx->tab_nq == 27) return launch_poisson<8, 27, 16>(ctx, p, d_f, e0, e1, d_kf);
     if (ctx->elem_type == FEASM_TET10 && ctx->tab_nq == 14) return launch_poisson<10, 14, 16>(ctx, p, d_f, e0, e1, d_kf);

@@ -35,6 +35,9 @@ FEASM_HD constexpr int feasm_ldr(int nd) { return (nd + 1 + 3) & ~3; }
 // top bit = "column dof is constrained".  uint8 when every row has <= 128 entries, else uint16.
 FEASM_HD constexpr int feasm_pld(int nd, int pos_bytes) { return ((nd * pos_bytes + 31) & ~31) / pos_bytes; }
 
+// incidence id = e*nd + a in the low 31 bits; bit 31 = the element touches a constrained dof
+constexpr uint32_t FEASM_INC_SLOW = 0x80000000u, FEASM_INC_MASK = 0x7fffffffu;
+
 struct feasm_ctx {
   int device = 0;
   cudaStream_t stream = nullptr;

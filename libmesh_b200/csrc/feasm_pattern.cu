@@ -65,7 +65,7 @@ __global__ void k_row_pattern(const uint32_t* __restrict__ elem_dofs, const uint
   for (int t = lane; t < p2; t += 32) {
     uint32_t v = 0xffffffffu;
     if (t < n) {
-      const uint32_t ea = inc[k0 + t / nd];
+      const uint32_t ea = inc[k0 + t / nd] & FEASM_INC_MASK;
       const uint32_t dof = elem_dofs[(uint64_t)(ea / nd) * nd + (t % nd)];
       v = gid ? gid[dof] : dof;
     }
@@ -138,7 +138,7 @@ inline unsigned grid_for(uint64_t n, int block) { return (unsigned)((n + block -
 int feasm_build_incidence(feasm_ctx* ctx) {
   if (ctx->d_inc_ptr) return FEASM_OK;
   const uint64_t total = (uint64_t)ctx->n_elem * ctx->nd;
-  if (total >= 0xffffffffull) return feasm_fail(ctx, FEASM_ERR_ARG, "n_elem*nd exceeds 2^32 incidence ids");
+  if (total >= 0x80000000ull) return feasm_fail(ctx, FEASM_ERR_ARG, "n_elem*nd exceeds 2^31 incidence ids");
   const int64_t nr = ctx->n_rows;
   unsigned long long* d_cnt = nullptr;
   FEASM_CUDA(ctx, cudaMalloc(&d_cnt, sizeof(unsigned long long) * (nr + 1)));

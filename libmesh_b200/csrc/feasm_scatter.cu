@@ -19,13 +19,64 @@ template <typename PosT> struct PosBits;
 template <> struct PosBits<uint8_t> { static constexpr unsigned FLAG = 0x80u, MASK = 0x7fu; };
 template <> struct PosBits<uint16_t> { static constexpr unsigned FLAG = 0x8000u, MASK = 0x7fffu; };
 
-__device__ __forceinline__ void cp_async16(void* smem_dst, const void* gsrc) {
-  const unsigned d = (unsigned)__cvta_generic_to_shared(smem_dst);
-  asm volatile("cp.async.cg.shared.global [%0], [%1], 16;\n" ::"r"(d), "l"(gsrc) : "memory");  // SASS LDGSTS, L1 bypass
+// Shared memory is addressed through explicit 32-bit shared-window addresses: every access below is an immediate
+// offset from a register, no generic-pointer conversion in the loops.
+__device__ __forceinline__ void cp_async16(uint32_t smem_dst, const void* gsrc) {
+  asm volatile("cp.async.cg.shared.global [%0], [%1], 16;\n" ::"r"(smem_dst), "l"(gsrc) : "memory");  // SASS LDGSTS, L1 bypass
 }
 __device__ __forceinline__ void cp_async_commit() { asm volatile("cp.async.commit_group;\n" ::: "memory"); }
 template <int N>
 __device__ __forceinline__ void cp_async_wait() { asm volatile("cp.async.wait_group %0;\n" ::"n"(N) : "memory"); }
+__device__ __forceinline__ double lds_f64(uint32_t a) { double v; asm volatile("ld.shared.f64 %0, [%1];\n" : "=d"(v) : "r"(a) : "memory"); return v; }
+__device__ __forceinline__ void sts_f64(uint32_t a, double v) { asm volatile("st.shared.f64 [%0], %1;\n" ::"r"(a), "d"(v) : "memory"); }
+__device__ __forceinline__ uint32_t lds_u32(uint32_t a) { uint32_t v; asm volatile("ld.shared.u32 %0, [%1];\n" : "=r"(v) : "r"(a) : "memory"); return v; }
+__device__ __forceinline__ void sts_u32(uint32_t a, uint32_t v) { asm volatile("st.shared.u32 [%0], %1;\n" ::"r"(a), "r"(v) : "memory"); }
+template <typename PosT>
+__device__ __forceinline__ unsigned lds_pos(uint32_t a) {
+  unsigned v;
+  if (sizeof(PosT) == 1) asm volatile("ld.shared.u8 %0, [%1];\n" : "=r"(v) : "r"(a) : "memory");
+  else asm volatile("ld.shared.u16 %0, [%1];\n" : "=r"(v) : "r"(a) : "memory");
+  return v;
+}
+
+constexpr int RR_NG = 4;
+// ring geometry: about 12 contributors in flight per warp, ring <= 8 KB
+__host__ __device__ constexpr int rr_stage(int slotb) {
+  int g = 4;
+  while (g > 2 && RR_NG * g * slotb > 8192) --g;
+  return g;
+}
+
+// The uncommon contributor: its CSR row is a Dirichlet row, or some of its columns are.  Kept out of line so the
+// common path stays short (the compiler would otherwise predicate all of this into it).
+template <typename PosT>
+__device__ __noinline__ double2 rr_constrained_contributor(uint32_t slot, uint32_t img_a, int lane, int nd, int ldrb, int row_con,
+                                                            double row_g, uint32_t ea, int mode, const double* __restrict__ con_val,
+                                                            const uint32_t* __restrict__ elem_dofs) {
+  // returns (addend of the row's RHS sum, addend of this lane's K(a,b) g_b correction)
+  if (row_con) {
+    // this element contributes K(a,a) = 1, F(a) = g
+    const int a = (int)(ea % (uint32_t)nd);
+    if (lane == 0) {
+      const uint32_t ia = img_a + ((lds_pos<PosT>(slot + ldrb + a * (int)sizeof(PosT)) & PosBits<PosT>::MASK) << 3);
+      sts_f64(ia, lds_f64(ia) + 1.);
+    }
+    return make_double2(row_g, 0.);
+  }
+  double corr = 0.;
+  const uint64_t e = ea / (uint32_t)nd;
+  for (int b = lane; b < nd; b += 32) {
+    double val = lds_f64(slot + 8 * b);
+    const unsigned pp = lds_pos<PosT>(slot + ldrb + b * (int)sizeof(PosT));
+    if (pp & PosBits<PosT>::FLAG) {
+      if (mode == FEASM_CONSTRAIN_HETEROGENEOUS) corr += val * con_val[elem_dofs[e * nd + b]];
+      val = 0.;
+    }
+    const uint32_t ia = img_a + ((pp & PosBits<PosT>::MASK) << 3);
+    sts_f64(ia, lds_f64(ia) + val);
+  }
+  return make_double2(lds_f64(slot + 8 * nd), corr);
+}
 
 // A warp owns a batch of RB consecutive entries of the row list (or RB consecutive rows); lane l holds the pointers
 // of row l of the batch.  The incidence ids of the whole batch are loaded into shared memory in one round trip;
@@ -33,15 +84,7 @@ __device__ __forceinline__ void cp_async_wait() { asm volatile("cp.async.wait_gr
 // per-warp ring of NG x G slots filled by cp.async (LDGSTS, 16 B per lane, no register staging): NG-1 stages —
 // several KB per warp — are in flight while one is accumulated into the CSR row image in shared memory.  Rows are
 // finished strictly in order and every row is summed in element order, so the result is bitwise reproducible.
-constexpr int RR_NG = 4;
-// ring geometry for a compile-time element size: about 12 contributors in flight per warp, ring <= 8 KB
-__host__ __device__ constexpr int rr_stage(int slotb) {
-  int g = 4;
-  while (g > 2 && RR_NG * g * slotb > 8192) --g;
-  return g;
-}
-// ND = dofs per element when known at compile time (strides, the lane loops and the division by nd fold away),
-// 0 = generic (runtime nd).
+// ND = dofs per element when known at compile time (strides and lane loops fold away), 0 = generic (runtime nd).
 template <typename PosT, int ND, int WARPS>
 __global__ void __launch_bounds__(WARPS * 32)
 k_row_reduce(const uint64_t* __restrict__ row_ptr, const uint64_t* __restrict__ inc_ptr, const uint32_t* __restrict__ inc,
@@ -59,11 +102,11 @@ k_row_reduce(const uint64_t* __restrict__ row_ptr, const uint64_t* __restrict__ 
   const int64_t base = (blockIdx.x * (int64_t)WARPS + warp) * RB;
   if (base >= n_list) return;
   const int nrows = (int)(n_list - base < RB ? n_list - base : RB);
-  const size_t warp_bytes = (size_t)RR_NG * G * slotb + (size_t)cap * 8 + (size_t)lcap * 4;
-  unsigned char* ring = s_raw + warp * warp_bytes;
-  double* img = reinterpret_cast<double*>(ring + (size_t)RR_NG * G * slotb);
-  uint32_t* list = reinterpret_cast<uint32_t*>(img + cap);
-  for (int t = lane; t < cap; t += 32) img[t] = 0.;
+  const uint32_t warp_bytes = (uint32_t)(RR_NG * G * slotb + cap * 8 + lcap * 4);
+  const uint32_t ring_a = (uint32_t)__cvta_generic_to_shared(s_raw) + warp * warp_bytes;
+  const uint32_t img_a = ring_a + RR_NG * G * slotb;
+  const uint32_t list_a = img_a + cap * 8;
+  for (int t = lane; t < cap; t += 32) sts_f64(img_a + 8 * t, 0.);
 
   // ---- per-lane row descriptors ---------------------------------------------------------------------------
   uint32_t my_r = 0, my_ip0 = 0;  // incidence offsets fit 32 bits (n_elem*nd < 2^32 is checked at setup)
@@ -90,32 +133,36 @@ k_row_reduce(const uint64_t* __restrict__ row_ptr, const uint64_t* __restrict__ 
   if (row_list == nullptr) {
     // consecutive rows: the batch's incidence ids are one contiguous run
     const uint32_t i0 = __shfl_sync(FULL, my_ip0, 0);
-    for (int t = lane; t < T; t += 32) list[t] = inc[i0 + t];
+    for (int t = lane; t < T; t += 32) sts_u32(list_a + 4 * t, inc[i0 + t]);
   } else {
     for (int j = 0; j < nrows; ++j) {
       const int cj = __shfl_sync(FULL, my_cnt, j), oj = __shfl_sync(FULL, my_off, j);
       const uint32_t ij = __shfl_sync(FULL, my_ip0, j);
-      for (int t = lane; t < cj; t += 32) list[oj + t] = inc[ij + t];
+      for (int t = lane; t < cj; t += 32) sts_u32(list_a + 4 * (oj + t), inc[ij + t]);
     }
   }
   __syncwarp();
 
-  // lane -> (contributor within an issue instruction, 16 B chunk of its slot)
+  // lane -> (contributor within an issue instruction, 16 B chunk of its slot); a lane always copies the same chunk
+  // of a slot, so its source is one base pointer plus (incidence id) * (row stride of the array it reads)
   const int ct = slotb >> 4, ck = ldrb >> 4;
   const int per = ct <= 32 ? 32 / ct : 1;
   const int my_c = ct <= 32 ? lane / ct : 0, my_ch = ct <= 32 ? lane % ct : lane;
-  auto issue = [&](int k) {  // stage k: contributors [k*G, k*G+G) -> ring slots (k % NG)*G ..
+  const unsigned char* my_src = my_ch < ck ? kf + (my_ch << 4) : pos + ((my_ch - ck) << 4);
+  const uint32_t my_stride = my_ch < ck ? ldrb : pldb;
+  auto issue = [&](int k, int rg) {  // stage k: contributors [k*G, k*G+G) -> ring group rg
     const int t0 = k * G;
-    unsigned char* sbase = ring + (size_t)(k % RR_NG) * G * slotb;
+    const uint32_t sbase = ring_a + rg * G * slotb + (my_ch << 4);
 #pragma unroll
     for (int c0 = 0; c0 < G; c0 += per) {
       const int c = c0 + my_c, t = t0 + c;
       if (my_c < per && c < G && t < T) {
-        const uint64_t ea = list[t];
-        unsigned char* dst = sbase + c * slotb;
-        for (int ch = my_ch; ch < ct; ch += 32) {
-          const unsigned char* src = ch < ck ? kf + ea * ldrb + (ch << 4) : pos + ea * pldb + ((ch - ck) << 4);
-          cp_async16(dst + (ch << 4), src);
+        const uint64_t ea = lds_u32(list_a + 4 * t) & FEASM_INC_MASK;
+        cp_async16(sbase + c * slotb, my_src + ea * my_stride);
+        if (ct > 32) {  // wide element rows: further 16 B chunks of the same slot
+          for (int ch = my_ch + 32; ch < ct; ch += 32)
+            cp_async16(sbase + c * slotb + ((ch - my_ch) << 4),
+                       ch < ck ? kf + ea * ldrb + (ch << 4) : pos + ea * pldb + ((ch - ck) << 4));
         }
       }
     }
@@ -123,7 +170,7 @@ k_row_reduce(const uint64_t* __restrict__ row_ptr, const uint64_t* __restrict__ 
   };
   const int nstages = (T + G - 1) / G;
 #pragma unroll
-  for (int k = 0; k < RR_NG - 1; ++k) issue(k);  // empty groups past the end keep the group count uniform
+  for (int k = 0; k < RR_NG - 1; ++k) issue(k, k);  // empty groups past the end keep the group count uniform
 
   int j = 0, left = 0, row_con = 0;
   double row_g = 0., bsum = 0., corr = 0.;
@@ -138,8 +185,8 @@ k_row_reduce(const uint64_t* __restrict__ row_ptr, const uint64_t* __restrict__ 
     }
     double* dst = values + rp0;
     for (int t = lane; t < len; t += 32) {
-      __stcs(dst + t, img[t]);
-      img[t] = 0.;
+      __stcs(dst + t, lds_f64(img_a + 8 * t));
+      sts_f64(img_a + 8 * t, 0.);
     }
     if (lane == 0) rhs[r] = bsum;
     bsum = 0.; corr = 0.;
@@ -156,41 +203,34 @@ k_row_reduce(const uint64_t* __restrict__ row_ptr, const uint64_t* __restrict__ 
     }
   };
   next_row();
+  int rg = 0;  // ring group of stage k
   for (int k = 0; k < nstages; ++k) {
-    issue(k + RR_NG - 1);
+    issue(k + RR_NG - 1, rg == 0 ? RR_NG - 1 : rg - 1);
     cp_async_wait<RR_NG - 1>();
     __syncwarp();
-    const unsigned char* sbase = ring + (k % RR_NG) * G * slotb;
+    const uint32_t sbase = ring_a + rg * G * slotb;
     const int cend = T - k * G < G ? T - k * G : G;
 #pragma unroll
     for (int c = 0; c < G; ++c) {
       if (c >= cend) break;
-      const unsigned char* slot = sbase + c * slotb;
-      const double* kv = reinterpret_cast<const double*>(slot);
-      const PosT* pv = reinterpret_cast<const PosT*>(slot + ldrb);
-      if (!row_con) {
+      const uint32_t slot = sbase + c * slotb;
+      // bit 31 of the incidence id: this element touches a constrained dof (set by feasm_launch_pos_flags)
+      const uint32_t ea = lds_u32(list_a + 4 * (k * G + c));
+      if (ea & FEASM_INC_SLOW) {
+        const double2 add = rr_constrained_contributor<PosT>(slot, img_a, lane, nd, ldrb, row_con, row_g, ea & FEASM_INC_MASK,
+                                                             mode, con_val, elem_dofs);
+        bsum += add.x; corr += add.y;
+      } else {
 #pragma unroll
         for (int bb = 0; bb < NDC; ++bb) {
           const int b = lane + 32 * bb;
-          if (b < nd) {
-            double val = kv[b];
-            const unsigned pp = pv[b];
-            if (pp & PosBits<PosT>::FLAG) {  // column dof constrained (rare)
-              if (mode == FEASM_CONSTRAIN_HETEROGENEOUS) {
-                const uint32_t ea = list[k * G + c];
-                corr += val * con_val[elem_dofs[(uint64_t)(ea / (uint32_t)nd) * nd + b]];
-              }
-              val = 0.;
-            }
-            img[pp & PosBits<PosT>::MASK] += val;  // positions within one element row are distinct
+          if (b < nd) {  // positions within one element row are distinct
+            const uint32_t ia = img_a + (lds_pos<PosT>(slot + ldrb + b * (int)sizeof(PosT)) << 3);
+            const double val = lds_f64(slot + 8 * b);
+            sts_f64(ia, lds_f64(ia) + val);
           }
         }
-        bsum += kv[nd];
-      } else {
-        // constrained row: this element contributes K(a,a) = 1, F(a) = g
-        const int a = (int)(list[k * G + c] % (uint32_t)nd);
-        if (lane == (a & 31)) img[pv[a] & PosBits<PosT>::MASK] += 1.;
-        bsum += row_g;
+        bsum += lds_f64(slot + 8 * nd);
       }
       __syncwarp();
       if (--left == 0) {
@@ -199,6 +239,7 @@ k_row_reduce(const uint64_t* __restrict__ row_ptr, const uint64_t* __restrict__ 
       }
     }
     __syncwarp();  // the slots of this stage are refilled by the next issue
+    rg = rg == RR_NG - 1 ? 0 : rg + 1;
   }
   cp_async_wait<0>();
 }
@@ -222,7 +263,7 @@ __global__ void k_row_reduce_global(const uint64_t* __restrict__ row_ptr, const 
   const double row_g = (row_con && mode == FEASM_CONSTRAIN_HETEROGENEOUS) ? con_val[r] : 0.;
   double b = 0., corr = 0.;
   for (uint64_t k = inc_ptr[r]; k < inc_ptr[r + 1]; ++k) {
-    const uint64_t ea = inc[k];
+    const uint64_t ea = inc[k] & FEASM_INC_MASK;
     const int a = (int)(ea % nd);
     for (int t = lane; t < nd; t += 32) {
       double val = kf[ea * ldr + t];
@@ -281,6 +322,19 @@ __global__ void k_pos_flags(const uint32_t* __restrict__ elem_dofs, const uint8_
   const uint64_t e = ea / nd;
   const unsigned p = pos[i] & PosBits<PosT>::MASK;
   pos[i] = (PosT)(p | (con_flag[elem_dofs[e * nd + b]] ? PosBits<PosT>::FLAG : 0u));
+}
+
+// Bit 31 of an incidence id = "the element touches a constrained dof": its rows take the out-of-line path of the row
+// reduction.  Refreshed together with the position-map flags.
+__global__ void k_inc_flags(const uint32_t* __restrict__ elem_dofs, const uint8_t* __restrict__ con_flag, int nd, uint64_t total,
+                            uint32_t* __restrict__ inc) {
+  const uint64_t k = blockIdx.x * (uint64_t)blockDim.x + threadIdx.x;
+  if (k >= total) return;
+  const uint32_t ea = inc[k] & FEASM_INC_MASK;
+  const uint32_t* d = elem_dofs + (uint64_t)(ea / (uint32_t)nd) * nd;
+  unsigned any = 0;
+  for (int b = 0; b < nd; ++b) any |= con_flag[d[b]];
+  inc[k] = ea | (any ? FEASM_INC_SLOW : 0u);
 }
 
 __global__ void k_pack(const uint64_t* __restrict__ slots, uint64_t n, uint64_t nnz, const double* __restrict__ values,
@@ -390,6 +444,7 @@ int feasm_launch_pos_flags(feasm_ctx* ctx) {
     else
       k_pos_flags<uint16_t><<<grid, 256, 0, ctx->stream>>>(ctx->d_elem_dofs, ctx->d_con_flag, ctx->nd, pld, rows_e, (uint16_t*)ctx->d_pos);
   }
+  if (rows_e) k_inc_flags<<<(unsigned)((rows_e + 255) / 256), 256, 0, ctx->stream>>>(ctx->d_elem_dofs, ctx->d_con_flag, ctx->nd, rows_e, ctx->d_inc);
   FEASM_CUDA(ctx, cudaGetLastError());
   ctx->pos_flags_valid = true;
   return FEASM_OK;
