@@ -1,0 +1,297 @@
+"""Multi-GPU assembly: one process per GPU, mesh split by element owner, ghost rows summed on their owner.
+
+Mirrors libMesh's parallel assembly model: every rank assembles its ``active_local`` elements; a row
+belongs to the rank that owns its dof (dof ranges are contiguous per rank, src/base/dof_map.C:999-1015; node owner =
+min rank of the touching elements, src/geom/node.C:99-102); contributions to rows of another rank are summed by the
+owner at ``close()`` (src/numerics/distributed_vector.C:399-470, PETSc's MatAssemblyBegin/End stash).  Here:
+
+  setup     each rank localises its elements (owned rows first, then ghost rows in ascending global id), builds the
+            local sparsity pattern on its GPU, ships the column lists of its ghost rows to their owners (the mirror of
+            SparsityPattern::Build::parallel_sync, src/base/sparsity_pattern.C:446-575), merges what it receives into
+            its owned rows and fixes a send/receive slot plan;
+  per step  feasm_assemble -> feasm_pack_ghost -> one grouped send/recv per neighbour (ncclSend/ncclRecv through
+            torch.distributed.batch_isend_irecv on the library's stream) -> feasm_unpack_ghost, peers added in fixed
+            order, so the result is bitwise reproducible.
+
+The host logic is plain numpy + torch.distributed and is exercised on CPU with the gloo backend in tests/.
+"""
+from __future__ import annotations
+
+import numpy as np
+
+
+# ---- partitioning and localisation (pure numpy) ------------------------------------------------------------
+def linear_partition(n_elem: int, n_parts: int) -> np.ndarray:
+    """Contiguous element-id slabs = LinearPartitioner (src/partitioning/linear_partitioner.C:60-75): blksize =
+    n_elem / n_parts, element e goes to part e / blksize, and the remainder elements fall back to processor 0."""
+    pid = np.zeros(n_elem, dtype=np.int32)
+    if n_parts > 1:
+        blk = max(n_elem // n_parts, 1)
+        p = np.arange(n_elem, dtype=np.int64) // blk
+        pid = np.where(p < n_parts, p, 0).astype(np.int32)
+    return pid
+
+
+class RankProblem:
+    """Everything one rank hands to libfeasm, in local numbering."""
+
+    def __init__(self, rank, n_parts, xyz, conn, node_base, first_dof, elem_pid, n_vars=1, con_dofs=None, con_vals=None):
+        self.rank, self.n_parts, self.n_vars = rank, n_parts, n_vars
+        self.first_dof = np.asarray(first_dof, dtype=np.int64)
+        f0, f1 = int(self.first_dof[rank]), int(self.first_dof[rank + 1])
+        self.f0, self.n_owned = f0, f1 - f0
+        self.elems = np.nonzero(np.asarray(elem_pid) == rank)[0]
+        gconn = conn[self.elems].astype(np.int64)
+        self.nodes, lconn = np.unique(gconn, return_inverse=True)  # local node ids = rank in the sorted global ids
+        self.conn = lconn.reshape(gconn.shape).astype(np.uint32)
+        self.xyz = np.ascontiguousarray(xyz[self.nodes])
+        nb = node_base.astype(np.int64)[gconn]
+        gdofs = np.concatenate([nb + v for v in range(n_vars)], axis=1)  # variable-major (dof_map.C:2280-2308)
+        touched = np.unique(gdofs)
+        owned = (touched >= f0) & (touched < f1)
+        if int(owned.sum()) != self.n_owned:
+            raise ValueError("a rank must touch every dof it owns (node owner = min touching rank)")
+        self.ghosts = touched[~owned]  # ascending global id
+        self.n_rows = self.n_owned + len(self.ghosts)
+        self.global_ids = np.concatenate([np.arange(f0, f1, dtype=np.int64), self.ghosts]).astype(np.uint32)
+        self.elem_dofs = self.to_local(gdofs).astype(np.uint32)
+        self.ghost_owner = (np.searchsorted(self.first_dof, self.ghosts, side="right") - 1).astype(np.int32)
+        if con_dofs is not None and len(con_dofs):
+            cd = np.asarray(con_dofs, dtype=np.int64)
+            here = np.isin(cd, touched)
+            self.con_rows = self.to_local(cd[here]).astype(np.uint32)
+            self.con_vals = np.asarray(con_vals, dtype=np.float64)[here]
+        else:
+            self.con_rows, self.con_vals = np.zeros(0, dtype=np.uint32), np.zeros(0)
+
+    def to_local(self, g):
+        g = np.asarray(g, dtype=np.int64)
+        own = (g >= self.f0) & (g < self.f0 + self.n_owned)
+        out = np.where(own, g - self.f0, 0)
+        if (~own).any():
+            k = np.searchsorted(self.ghosts, g[~own])
+            if (k >= len(self.ghosts)).any() or (self.ghosts[np.minimum(k, len(self.ghosts) - 1)] != g[~own]).any():
+                raise ValueError("dof is neither owned nor a ghost of this rank")
+            out[~own] = self.n_owned + k
+        return out
+
+    @property
+    def peers(self):
+        """Ranks this rank sends ghost rows to (ascending)."""
+        return np.unique(self.ghost_owner)
+
+
+def csr_rows(rp, ci, rows):
+    """Concatenated column lists of `rows`: (lens, cols, slots)."""
+    rows = np.asarray(rows, dtype=np.int64)
+    lo = rp[rows].astype(np.int64)
+    lens = (rp[rows + 1].astype(np.int64) - lo)
+    tot = int(lens.sum())
+    off = np.zeros(len(rows) + 1, dtype=np.int64)
+    np.cumsum(lens, out=off[1:])
+    slots = np.repeat(lo - off[:-1], lens) + np.arange(tot, dtype=np.int64)
+    return lens, ci[slots], slots
+
+
+def merge_rows(rp, ci, add_rows, add_lens, add_cols):
+    """Union the column lists (add_rows[k] gets add_cols segment k) into the CSR pattern; returns (rp, ci)."""
+    n = len(rp) - 1
+    if len(add_rows) == 0:
+        return rp, ci
+    rp = rp.astype(np.int64)
+    old_len = np.diff(rp)
+    aff = np.unique(add_rows)
+    # new column lists of the affected rows
+    seg = np.zeros(len(add_rows) + 1, dtype=np.int64)
+    np.cumsum(add_lens, out=seg[1:])
+    order = np.argsort(add_rows, kind="stable")
+    new_cols = {}
+    i = 0
+    sr = np.asarray(add_rows)[order]
+    while i < len(order):
+        j = i
+        parts = [ci[rp[sr[i]]:rp[sr[i] + 1]]]
+        while j < len(order) and sr[j] == sr[i]:
+            k = order[j]
+            parts.append(add_cols[seg[k]:seg[k + 1]])
+            j += 1
+        new_cols[int(sr[i])] = np.unique(np.concatenate(parts))
+        i = j
+    new_len = old_len.copy()
+    for r, c in new_cols.items():
+        new_len[r] = len(c)
+    nrp = np.zeros(n + 1, dtype=np.int64)
+    np.cumsum(new_len, out=nrp[1:])
+    nci = np.empty(int(nrp[-1]), dtype=ci.dtype)
+    is_aff = np.zeros(n, dtype=bool)
+    is_aff[aff] = True
+    row_of = np.repeat(np.arange(n, dtype=np.int64), old_len)
+    keep = ~is_aff[row_of]
+    within = np.arange(len(ci), dtype=np.int64) - rp[row_of]
+    nci[nrp[row_of[keep]] + within[keep]] = ci[keep]
+    for r, c in new_cols.items():
+        nci[nrp[r]:nrp[r] + len(c)] = c
+    return nrp.astype(np.uint64), nci
+
+
+# ---- setup exchange and per-step exchange (torch.distributed) -------------------------------------------------
+class DevArray:
+    """A raw device pointer exposed through __cuda_array_interface__ so torch can wrap it without a copy."""
+
+    def __init__(self, ptr, n, typestr="<f8"):
+        self.__cuda_array_interface__ = {"shape": (int(n),), "typestr": typestr, "data": (int(ptr), False), "version": 2}
+
+
+def _exchange_arrays(dist, group, rank, send: dict):
+    """Variable-size uint32 array exchange on the host: send[p] -> p for every p in send; peers are symmetric for
+    sizes (a rank that receives nothing gets an empty array).  Returns {q: array}."""
+    import torch
+
+    world = dist.get_world_size(group)
+    sizes = torch.zeros(world, dtype=torch.int64)
+    for p, a in send.items():
+        sizes[p] = len(a)
+    all_sizes = [torch.zeros(world, dtype=torch.int64) for _ in range(world)]
+    dist.all_gather(all_sizes, sizes, group=group)
+    ops, bufs, keep = [], {}, []
+    for q in range(world):
+        n = int(all_sizes[q][rank])
+        if q != rank and n:
+            bufs[q] = torch.empty(n, dtype=torch.int64)
+            ops.append(dist.P2POp(dist.irecv, bufs[q], q, group=group))
+    for p, a in send.items():
+        if p != rank and len(a):
+            t = torch.from_numpy(np.ascontiguousarray(a, dtype=np.int64))
+            keep.append(t)
+            ops.append(dist.P2POp(dist.isend, t, p, group=group))
+    if ops:
+        for w in dist.batch_isend_irecv(ops):
+            w.wait()
+    return {q: b.numpy() for q, b in bufs.items()}
+
+
+class DistributedAssembly:
+    """One rank of a multi-GPU assembly.  `ctx` is a libmesh_b200.capi.Context (or, in CPU tests, an object with the
+    same pattern / plan methods); `host_group` is a gloo group for the setup exchange, `dev_group` the group the
+    per-step exchange runs on (NCCL on GPUs)."""
+
+    def __init__(self, ctx, prob: RankProblem, dist, host_group=None, dev_group=None):
+        self.ctx, self.p, self.dist = ctx, prob, dist
+        self.host_group, self.dev_group = host_group, dev_group
+        self.rank = prob.rank
+
+    # -- setup ---------------------------------------------------------------------------------------------
+    def setup(self, constrain=True):
+        p, ctx = self.p, self.ctx
+        ctx.set_mesh(p.conn.shape[1], p.xyz, p.conn)
+        ctx.set_dofs(p.elem_dofs, p.n_rows, n_vars=p.n_vars, n_owned=p.n_owned, global_ids=p.global_ids)
+        if constrain:
+            ctx.set_constraints(p.con_rows, p.con_vals)
+        ctx.build_pattern()
+        rp, ci = ctx.get_pattern()
+        self.merge_and_plan(rp, ci)
+
+    def merge_and_plan(self, rp, ci):
+        """Ship ghost-row column lists to their owners, merge, and derive the slot plan.  Also usable stand-alone with a
+        host-built local pattern (CPU tests)."""
+        send = self.ghost_messages(rp, ci)
+        got = _exchange_arrays(self.dist, self.host_group, self.rank, send)
+        self.finish_plan(rp, ci, got)
+
+    def ghost_messages(self, rp, ci):
+        """{owner rank: [n_rows, global row ids, row lengths, columns]} for the ghost rows of this rank."""
+        p = self.p
+        send = {}
+        self._ghost_rows = {}
+        for q in p.peers:
+            rows = p.n_owned + np.nonzero(p.ghost_owner == q)[0]  # local ghost rows owned by q, ascending global id
+            lens, cols, _ = csr_rows(rp, ci, rows)
+            self._ghost_rows[int(q)] = rows
+            send[int(q)] = np.concatenate([[len(rows)], p.global_ids[rows].astype(np.int64), lens, cols.astype(np.int64)])
+        return send
+
+    def finish_plan(self, rp, ci, got):
+        """Merge the received ghost-row patterns into the owned rows and fix the send/receive slot plan."""
+        p, ctx = self.p, self.ctx
+        add_rows, add_lens, add_cols, self._recv_desc = [], [], [], {}
+        for q in sorted(got):
+            a = got[q]
+            n = int(a[0])
+            grow, lens, cols = a[1:1 + n], a[1 + n:1 + 2 * n], a[1 + 2 * n:]
+            lrow = grow - p.f0
+            if (lrow < 0).any() or (lrow >= p.n_owned).any():
+                raise ValueError("peer sent a row this rank does not own")
+            add_rows.append(lrow); add_lens.append(lens); add_cols.append(cols.astype(ci.dtype))
+            self._recv_desc[q] = (lrow, lens, cols)
+        if add_rows:
+            rp, ci = merge_rows(rp, ci, np.concatenate(add_rows), np.concatenate(add_lens), np.concatenate(add_cols))
+            ctx.set_pattern(rp, ci)  # SparseMatrix::update_sparsity_pattern route: the merged graph
+        self.row_ptr, self.col_idx = np.asarray(rp, dtype=np.uint64), ci
+        nnz = int(self.row_ptr[-1])
+        # slot plan: per peer, all value slots of its rows (row-major) followed by the rows' RHS slots
+        peers = sorted(set(self._ghost_rows) | set(self._recv_desc))
+        send_ptr, recv_ptr, send_slots, recv_slots = [0], [0], [], []
+        rp64 = self.row_ptr.astype(np.int64)
+        for q in peers:
+            if q in self._ghost_rows:
+                rows = self._ghost_rows[q]
+                _, _, slots = csr_rows(rp64, self.col_idx, rows)
+                send_slots += [slots, nnz + rows.astype(np.int64)]
+            send_ptr.append(send_ptr[-1] + (sum(len(x) for x in send_slots[-2:]) if q in self._ghost_rows else 0))
+            if q in self._recv_desc:
+                lrow, lens, cols = self._recv_desc[q]
+                rows_rep = np.repeat(lrow, lens)
+                # position of each received column inside its (merged, sorted) owned row: search on row*2^32 + col keys
+                _, mycols, myslots = csr_rows(rp64, self.col_idx, lrow)
+                mylens = rp64[lrow + 1] - rp64[lrow]
+                mykeys = (np.repeat(lrow, mylens).astype(np.int64) << 32) | mycols.astype(np.int64)
+                keys = (rows_rep.astype(np.int64) << 32) | cols.astype(np.int64)
+                order = np.argsort(mykeys, kind="stable")
+                k = np.searchsorted(mykeys[order], keys)
+                if (mykeys[order][k] != keys).any():
+                    raise ValueError("received column missing from the merged pattern")
+                recv_slots += [myslots[order][k], nnz + lrow.astype(np.int64)]
+            recv_ptr.append(recv_ptr[-1] + (sum(len(x) for x in recv_slots[-2:]) if q in self._recv_desc else 0))
+        self.peers = peers
+        self.send_ptr, self.recv_ptr = np.asarray(send_ptr, dtype=np.uint64), np.asarray(recv_ptr, dtype=np.uint64)
+        self.send_slots = np.concatenate(send_slots).astype(np.uint64) if send_slots else np.zeros(0, dtype=np.uint64)
+        self.recv_slots = np.concatenate(recv_slots).astype(np.uint64) if recv_slots else np.zeros(0, dtype=np.uint64)
+        ctx.set_exchange_plan(np.asarray(peers, dtype=np.int32), self.send_ptr, self.send_slots, self.recv_ptr, self.recv_slots)
+        ctx.prepare()
+
+    # -- per step --------------------------------------------------------------------------------------------
+    def exchange(self):
+        """pack -> grouped send/recv with every neighbour -> unpack (fixed peer order).  Runs on the library's stream."""
+        import torch
+
+        ctx, dist = self.ctx, self.dist
+        sptr, ns = ctx.pack_ghost()
+        rptr, nr = ctx.recv_buffer()
+        if not self.peers:
+            return
+        sbuf = torch.as_tensor(DevArray(sptr, max(ns, 1)), device="cuda")
+        rbuf = torch.as_tensor(DevArray(rptr, max(nr, 1)), device="cuda")
+        ops = []
+        for i, q in enumerate(self.peers):
+            r0, r1 = int(self.recv_ptr[i]), int(self.recv_ptr[i + 1])
+            if r1 > r0:
+                ops.append(dist.P2POp(dist.irecv, rbuf[r0:r1], q, group=self.dev_group))
+        for i, q in enumerate(self.peers):
+            s0, s1 = int(self.send_ptr[i]), int(self.send_ptr[i + 1])
+            if s1 > s0:
+                ops.append(dist.P2POp(dist.isend, sbuf[s0:s1], q, group=self.dev_group))
+        with torch.cuda.stream(torch.cuda.ExternalStream(ctx.stream())):
+            for w in dist.batch_isend_irecv(ops):
+                w.wait()  # stream-ordered for NCCL: makes the library's stream wait for the transfer
+        ctx.unpack_ghost()
+
+    def assemble(self, params, sync=True):
+        self.ctx.assemble(params, sync=False)
+        self.exchange()
+        if sync:
+            self.ctx.synchronize()
+
+    def owned_values(self):
+        """(values of the owned rows, owned rhs) on the host."""
+        v, b = self.ctx.get_values()
+        return v[: int(self.row_ptr[self.p.n_owned])], b[: self.p.n_owned]
