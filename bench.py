@@ -110,7 +110,7 @@ def build_problem(F, etype: int, n: int, rank: int = 0, world: int = 1):
     # Dirichlet data g = exact_solution at boundary nodes (introduction_ex3/exact_solution.C:40-47) — input data
     g = np.cos(.5 * np.pi * xyz[bn, 0]) * np.sin(.5 * np.pi * xyz[bn, 1]) * np.cos(.5 * np.pi * xyz[bn, 2])
     return dict(xyz=xyz, conn=conn, elem_dofs=elem_dofs, n_dofs=n_dofs, con_rows=base[bn].astype(np.uint32), con_vals=g,
-                host_gen_s=time.time() - t0)
+                con_dofs_nodes_base=lambda node_base: node_base[bn].astype(np.int64), host_gen_s=time.time() - t0)
 
 
 def run_ours(args):
