@@ -1,0 +1,119 @@
+// gpu_assemble.C — see gpu_assemble.h.  Flattens what the reference reaches through pointers (Elem -> Node ->
+// DofObject, src/fe/fe_map.C:1361-1366, src/base/dof_map.C:2201-2314) into the arrays libfeasm takes, once per mesh,
+// then runs the assembly on the GPU and hands the RHS back to the system's NumericVector.
+#include "gpu_assemble.h"
+
+#include <unordered_map>
+
+namespace feasm_libmesh {
+using namespace libMesh;
+
+namespace {
+int feasm_type(ElemType t) {
+  switch (t) {
+    case HEX8: return FEASM_HEX8;
+    case HEX27: return FEASM_HEX27;
+    case TET10: return FEASM_TET10;
+    default: libmesh_error_msg("libfeasm supports HEX8, HEX27 and TET10 elements; got ElemType " << (int)t);
+  }
+}
+
+// one flattening per (matrix, mesh size): the adaptor owns the context, this caches what was uploaded
+struct Uploaded { const MeshBase* mesh = nullptr; std::size_t n_elem = 0; };
+std::unordered_map<const void*, Uploaded>& cache() {
+  static std::unordered_map<const void*, Uploaded> c;
+  return c;
+}
+}  // namespace
+
+void assemble(EquationSystems& es, const std::string& system_name, const feasm_params& params) {
+  LinearImplicitSystem& system = es.get_system<LinearImplicitSystem>(system_name);
+  auto* A = dynamic_cast<GpuSparseMatrix<Number>*>(system.matrix);
+  if (!A) libmesh_error_msg("feasm_libmesh::assemble: system.matrix is not a GpuSparseMatrix; add it with "
+                            "system.add_matrix<GpuSparseMatrix>(\"System Matrix\") before EquationSystems::init()");
+  if (A->n_processors() > 1)
+    libmesh_not_implemented();  // the multi-rank protocol is implemented in libmesh_b200/multi.py; see INTEGRATION.md
+  std::lock_guard<std::mutex> lock(A->mutex());
+  const MeshBase& mesh = system.get_mesh();
+  DofMap& dof_map = system.get_dof_map();
+  feasm_ctx* ctx = A->ctx();
+  const dof_id_type first = dof_map.first_dof(), n_local = dof_map.end_dof() - first;
+
+  // ---- flatten the mesh and the dof map (first call, or a different / refined mesh) ---------------------------
+  std::size_t n_elem = 0;
+  for (const Elem* e : mesh.active_local_element_ptr_range()) { (void)e; ++n_elem; }
+  Uploaded& up = cache()[A];
+  if (up.mesh != &mesh || up.n_elem != n_elem) {
+    std::unordered_map<dof_id_type, uint32_t> local_node;
+    std::vector<double> xyz;
+    std::vector<uint32_t> conn, elem_dofs;
+    std::vector<dof_id_type> di;
+    int type = 0, nd = 0;
+    for (const Elem* elem : mesh.active_local_element_ptr_range()) {
+      const int t = feasm_type(elem->type());
+      if (type && t != type) libmesh_error_msg("libfeasm assembles one element type per context");
+      type = t;
+      for (unsigned a = 0; a < elem->n_nodes(); ++a) {  // element-local node order, as FEMap::compute_map reads it
+        const Node* node = elem->node_ptr(a);
+        auto it = local_node.find(node->id());
+        if (it == local_node.end()) {
+          it = local_node.emplace(node->id(), (uint32_t)local_node.size()).first;
+          xyz.push_back((*node)(0)); xyz.push_back((*node)(1)); xyz.push_back((*node)(2));
+        }
+        conn.push_back(it->second);
+      }
+      dof_map.dof_indices(elem, di);  // variable-major (src/base/dof_map.C:2280-2308)
+      if (nd && (int)di.size() != nd) libmesh_error_msg("libfeasm needs the same number of dofs on every element");
+      nd = (int)di.size();
+      for (dof_id_type d : di) {
+        if (d < first || d >= first + n_local) libmesh_error_msg("dof outside the local range on a one-rank run");
+        elem_dofs.push_back(d - first);
+      }
+    }
+    if (!n_elem) libmesh_error_msg("no local elements");
+    A->check(feasm_set_mesh(ctx, type, (int64_t)n_elem, (int64_t)local_node.size(), xyz.data(), conn.data()));
+    A->check(feasm_set_dofs(ctx, nd / type, n_local, n_local, elem_dofs.data(), nullptr));
+    A->send_pattern();
+    up.mesh = &mesh; up.n_elem = n_elem;
+  }
+
+  // ---- Dirichlet constraints: DofMap::is_constrained_dof + primal constraint values (empty constraint rows) ----
+  std::vector<uint32_t> con_rows;
+  std::vector<double> con_vals;
+  const DofConstraintValueMap& vals = dof_map.get_primal_constraint_values();
+  for (dof_id_type d = first; d < first + n_local; ++d)
+    if (dof_map.is_constrained_dof(d)) {
+      const auto it = vals.find(d);
+      con_rows.push_back(d - first);
+      con_vals.push_back(it == vals.end() ? 0. : it->second);
+    }
+  A->check(feasm_set_constraints(ctx, (int64_t)con_rows.size(), con_rows.data(), con_vals.data()));
+
+  // ---- the hot path -----------------------------------------------------------------------------------------------
+  A->check(feasm_assemble(ctx, &params));
+  std::vector<Number> rhs(n_local);
+  A->check(feasm_get_values(ctx, nullptr, rhs.data()));  // synchronises; throws on a degenerate map like FEMap does
+  A->invalidate_host_copy();
+  *system.rhs = rhs;      // NumericVector::operator=(const std::vector<T>&), include/numerics/numeric_vector.h:295
+  system.rhs->close();
+}
+
+void assemble_poisson_ex4(EquationSystems& es, const std::string& name) {
+  feasm_params p{};
+  p.problem = FEASM_POISSON; p.quadrature_order = 5; p.forcing = FEASM_FORCING_EX4_FD; p.constrain = FEASM_CONSTRAIN_HETEROGENEOUS;
+  assemble(es, name, p);
+}
+void assemble_laplace(EquationSystems& es, const std::string& name) {
+  feasm_params p{};
+  p.problem = FEASM_POISSON; p.quadrature_order = 5; p.forcing = FEASM_FORCING_NONE; p.constrain = FEASM_CONSTRAIN_HETEROGENEOUS;
+  assemble(es, name, p);
+}
+void assemble_elasticity_ex6(EquationSystems& es, const std::string& name) {
+  feasm_params p{};
+  p.problem = FEASM_ELASTICITY; p.constrain = FEASM_CONSTRAIN_HOMOGENEOUS;
+  assemble(es, name, p);
+}
+}  // namespace feasm_libmesh
+
+// explicit instantiation: every virtual of the adaptor is compiled in this translation unit
+template class libMesh::GpuSparseMatrix<libMesh::Number>;

@@ -1,0 +1,26 @@
+// gpu_assemble.h — the batched assemble hooks a libMesh application attaches with
+// System::attach_assemble_function (include/systems/system.h:1470; signature void(EquationSystems&, const std::string&),
+// src/systems/system.C:1959-1972).  Each replaces the whole per-element loop of the named example with one call into
+// libfeasm.  The system's matrix must be a GpuSparseMatrix (see gpu_sparse_matrix.h).
+#ifndef FEASM_GPU_ASSEMBLE_H
+#define FEASM_GPU_ASSEMBLE_H
+
+#include <string>
+
+#include "gpu_sparse_matrix.h"
+#ifndef FEASM_SHIM_MOCK
+#include "libmesh/equation_systems.h"
+#include "libmesh/linear_implicit_system.h"
+#endif
+
+namespace feasm_libmesh {
+// examples/introduction/introduction_ex4/introduction_ex4.C:313-563 (assemble_poisson)
+void assemble_poisson_ex4(libMesh::EquationSystems& es, const std::string& system_name);
+// the same loop with f = 0 (config 4)
+void assemble_laplace(libMesh::EquationSystems& es, const std::string& system_name);
+// examples/systems_of_equations/systems_of_equations_ex6/systems_of_equations_ex6.C:156-264, volume terms
+void assemble_elasticity_ex6(libMesh::EquationSystems& es, const std::string& system_name);
+// generic entry: feasm_params as in include/feasm.h
+void assemble(libMesh::EquationSystems& es, const std::string& system_name, const feasm_params& params);
+}  // namespace feasm_libmesh
+#endif

@@ -1,0 +1,190 @@
+// gpu_sparse_matrix.h — libMesh-side adaptor: a SparseMatrix<Number> whose storage and assembly live on a B200
+// behind the libfeasm C ABI (include/feasm.h).
+//
+// How a libMesh application uses it (INTEGRATION.md has the full recipe):
+//     system.add_matrix<libMesh::GpuSparseMatrix>("System Matrix");     // include/systems/system.h:1904, :2646-2665
+//     system.attach_assemble_function(feasm_libmesh::assemble_poisson_ex4);   // system.h:1470
+// ImplicitSystem::add_matrices then points ImplicitSystem::matrix at this object (src/systems/implicit_system.C:113-128);
+// DofMap::attach_matrix calls attach_dof_map, update_sparsity_pattern (because need_full_sparsity_pattern() is true,
+// src/base/dof_map.C:280-287) and init() (dof_map.C:240-254).
+//
+// Compiled against the real headers in a libMesh build, against libmesh_mock.h (-DFEASM_SHIM_MOCK) in this repo's
+// build check.  Errors of the C ABI become libmesh_error_msg exceptions, like every other back-end.
+#ifndef FEASM_GPU_SPARSE_MATRIX_H
+#define FEASM_GPU_SPARSE_MATRIX_H
+
+#ifdef FEASM_SHIM_MOCK
+#include "libmesh_mock.h"
+#else
+#include "libmesh/dense_matrix.h"
+#include "libmesh/dof_map.h"
+#include "libmesh/numeric_vector.h"
+#include "libmesh/sparse_matrix.h"
+#endif
+
+#include <cmath>
+#include <mutex>
+
+#include "feasm.h"
+
+namespace libMesh {
+
+template <typename T>
+class GpuSparseMatrix : public SparseMatrix<T> {
+ public:
+  explicit GpuSparseMatrix(const Parallel::Communicator& comm) : SparseMatrix<T>(comm) {}
+  ~GpuSparseMatrix() override { this->clear(); }
+
+  SolverPackage solver_package() override { return INVALID_SOLVER_PACKAGE; }  // storage only: a solver copies it out
+  bool need_full_sparsity_pattern() const override { return true; }           // as LaspackMatrix, laspack_matrix.h:96
+
+  // SparseMatrix::update_sparsity_pattern (sparse_matrix.h:175): keep the Graph as CSR until the context has the dofs
+  void update_sparsity_pattern(const SparsityPattern::Graph& g) override {
+    _row_ptr.assign(1, 0);
+    _col_idx.clear();
+    for (const auto& row : g) {
+      _col_idx.insert(_col_idx.end(), row.begin(), row.end());  // rows of the Graph are sorted and unique
+      _row_ptr.push_back(_col_idx.size());
+    }
+    _pattern_sent = false;
+  }
+
+  void init(const numeric_index_type m, const numeric_index_type n, const numeric_index_type m_l, const numeric_index_type n_l,
+            const numeric_index_type = 30, const numeric_index_type = 10, const numeric_index_type = 1) override {
+    _m = m; _n = n; _row_start = 0; _row_stop = m_l; (void)n_l;
+    this->_is_initialized = true;
+  }
+  void init(ParallelType = PARALLEL) override {
+    if (!this->_dof_map) libmesh_error_msg("GpuSparseMatrix::init: no DofMap attached");
+    _m = _n = this->_dof_map->n_dofs();
+    _row_start = this->_dof_map->first_dof();
+    _row_stop = this->_dof_map->end_dof();
+    this->_is_initialized = true;
+  }
+  void clear() override {
+    if (_ctx) feasm_destroy(_ctx);
+    _ctx = nullptr;
+    _row_ptr.clear(); _col_idx.clear(); _host_values.clear();
+    _pattern_sent = false; _closed = false; this->_is_initialized = false;
+  }
+  void zero() override { if (_ctx && _pattern_sent) check(feasm_zero(_ctx)); _host_valid = false; }
+  std::unique_ptr<SparseMatrix<T>> zero_clone() const override { libmesh_not_implemented(); }
+  std::unique_ptr<SparseMatrix<T>> clone() const override { libmesh_not_implemented(); }
+  void close() override { if (_ctx) check(feasm_synchronize(_ctx)); _closed = true; }
+  bool closed() const override { return _closed; }
+
+  numeric_index_type m() const override { return _m; }
+  numeric_index_type n() const override { return _n; }
+  numeric_index_type row_start() const override { return _row_start; }
+  numeric_index_type row_stop() const override { return _row_stop; }
+  numeric_index_type col_start() const override { return _row_start; }
+  numeric_index_type col_stop() const override { return _row_stop; }
+
+  void set(const numeric_index_type, const numeric_index_type, const T) override { libmesh_not_implemented(); }
+  void add(const numeric_index_type i, const numeric_index_type j, const T value) override {
+    std::lock_guard<std::mutex> lock(_mutex);
+    const uint32_t r = i - _row_start, c = j;
+    check(feasm_add_matrix(ctx(), &value, &r, 1, &c, 1));
+    _host_valid = false; _closed = false;
+  }
+  // sparse_matrix.h:312 — the per-element route stays functional (one small kernel per call); the batched hook
+  // (gpu_assemble.C) is the fast path.  Thread safe like PetscMatrix::add_matrix (src/numerics/petsc_matrix.C:747).
+  void add_matrix(const DenseMatrix<T>& dm, const std::vector<numeric_index_type>& rows,
+                  const std::vector<numeric_index_type>& cols) override {
+    std::lock_guard<std::mutex> lock(_mutex);
+    if (dm.m() != rows.size() || dm.n() != cols.size()) libmesh_error_msg("add_matrix: size mismatch");
+    std::vector<uint32_t> lr(rows.size());
+    for (std::size_t k = 0; k < rows.size(); ++k) lr[k] = rows[k] - _row_start;
+    check(feasm_add_matrix(ctx(), dm.get_values().data(), lr.data(), (int)lr.size(), cols.data(), (int)cols.size()));
+    _host_valid = false; _closed = false;
+  }
+  void add_matrix(const DenseMatrix<T>& dm, const std::vector<numeric_index_type>& dof_indices) override {
+    this->add_matrix(dm, dof_indices, dof_indices);
+  }
+  void add(const T, const SparseMatrix<T>&) override { libmesh_not_implemented(); }
+
+  T operator()(const numeric_index_type i, const numeric_index_type j) const override {
+    mirror();
+    const uint64_t lo = _row_ptr[i - _row_start], hi = _row_ptr[i - _row_start + 1];
+    for (uint64_t k = lo; k < hi; ++k) if (_col_idx[k] == j) return _host_values[k];
+    return 0.;
+  }
+  Real l1_norm() const override {  // max column sum (sparse_matrix.h:379), serial
+    mirror();
+    std::vector<Real> col(_n, 0.);
+    for (std::size_t k = 0; k < _col_idx.size(); ++k) col[_col_idx[k]] += std::abs(_host_values[k]);
+    Real mx = 0.;
+    for (Real v : col) mx = std::max(mx, v);
+    return mx;
+  }
+  Real linfty_norm() const override {  // max row sum (sparse_matrix.h:391)
+    mirror();
+    Real mx = 0.;
+    for (std::size_t r = 0; r + 1 < _row_ptr.size(); ++r) {
+      Real s = 0.;
+      for (uint64_t k = _row_ptr[r]; k < _row_ptr[r + 1]; ++k) s += std::abs(_host_values[k]);
+      mx = std::max(mx, s);
+    }
+    return mx;
+  }
+  void print_personal(std::ostream& os = libMesh::out) const override {
+    mirror();
+    for (std::size_t r = 0; r + 1 < _row_ptr.size(); ++r)
+      for (uint64_t k = _row_ptr[r]; k < _row_ptr[r + 1]; ++k) os << r + _row_start << " " << _col_idx[k] << " " << _host_values[k] << "\n";
+  }
+  void get_diagonal(NumericVector<T>& dest) const override {
+    mirror();
+    for (std::size_t r = 0; r + 1 < _row_ptr.size(); ++r) dest.set(r + _row_start, (*this)(r + _row_start, r + _row_start));
+    dest.close();
+  }
+  void get_transpose(SparseMatrix<T>&) const override { libmesh_not_implemented(); }
+  void get_row(numeric_index_type i, std::vector<numeric_index_type>& indices, std::vector<T>& values) const override {
+    mirror();  // ascending columns, as tests/numerics/sparse_matrix_test.h:88-149 expects
+    const uint64_t lo = _row_ptr[i - _row_start], hi = _row_ptr[i - _row_start + 1];
+    indices.assign(_col_idx.begin() + lo, _col_idx.begin() + hi);
+    values.assign(_host_values.begin() + lo, _host_values.begin() + hi);
+  }
+
+  // ---- what the batched hook needs ---------------------------------------------------------------------------
+  feasm_ctx* ctx() {
+    if (!_ctx) {
+      const char* dev = std::getenv("FEASM_DEVICE");
+      if (feasm_create(dev ? std::atoi(dev) : (int)this->processor_id(), &_ctx)) libmesh_error_msg("libfeasm: " << feasm_last_error(nullptr));
+    }
+    return _ctx;
+  }
+  // after feasm_set_mesh / feasm_set_dofs: hand the stored Graph to the context (host-pattern route)
+  void send_pattern() {
+    if (_pattern_sent) return;
+    if (_row_ptr.empty()) libmesh_error_msg("GpuSparseMatrix: update_sparsity_pattern was never called");
+    check(feasm_set_pattern(ctx(), _row_ptr.data(), _col_idx.data()));
+    _pattern_sent = true;
+  }
+  void check(int rc) const { if (rc) libmesh_error_msg("libfeasm error " << rc << ": " << feasm_last_error(_ctx)); }
+  void invalidate_host_copy() { _host_valid = false; _closed = false; }
+  std::mutex& mutex() { return _mutex; }
+  const std::vector<uint64_t>& row_ptr() const { return _row_ptr; }
+  const std::vector<uint32_t>& col_idx() const { return _col_idx; }
+  // host copy of the CSR values (what a CPU LinearSolver reads after close())
+  const std::vector<T>& host_values() const { mirror(); return _host_values; }
+
+ private:
+  void mirror() const {
+    if (_host_valid) return;
+    if (!_ctx || !_pattern_sent) libmesh_error_msg("GpuSparseMatrix: matrix has no values yet");
+    _host_values.resize(_col_idx.size());
+    check(feasm_get_values(_ctx, _host_values.data(), nullptr));
+    _host_valid = true;
+  }
+  feasm_ctx* _ctx = nullptr;
+  numeric_index_type _m = 0, _n = 0, _row_start = 0, _row_stop = 0;
+  std::vector<uint64_t> _row_ptr;
+  std::vector<uint32_t> _col_idx;
+  mutable std::vector<T> _host_values;
+  mutable bool _host_valid = false;
+  bool _pattern_sent = false, _closed = false;
+  std::mutex _mutex;
+};
+
+}  // namespace libMesh
+#endif

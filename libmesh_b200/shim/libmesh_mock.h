@@ -1,0 +1,156 @@
+// libmesh_mock.h — SIGNATURE MOCK of the libMesh declarations the adaptor classes use, so that
+// gpu_sparse_matrix.h / gpu_assemble.C compile in a container where libMesh itself cannot be built (its TIMPI and
+// MetaPhysicL submodules are empty).  Every declaration cites the reference header it mirrors; bodies are stubs.
+// A real build defines nothing of this: it includes the libmesh/ headers instead (see gpu_sparse_matrix.h).
+#ifndef FEASM_LIBMESH_MOCK_H
+#define FEASM_LIBMESH_MOCK_H
+
+#include <cstdint>
+#include <iostream>
+#include <map>
+#include <memory>
+#include <sstream>
+#include <stdexcept>
+#include <string>
+#include <vector>
+
+namespace libMesh {
+typedef double Real;                    // include/base/libmesh_common.h:144
+typedef Real Number;                    // libmesh_common.h:217 (real build)
+typedef uint32_t numeric_index_type;    // include/base/id_types.h:99
+typedef uint32_t dof_id_type;           // id_types.h:66-76
+typedef uint32_t processor_id_type;     // id_types.h:104
+typedef int8_t boundary_id_type;
+static std::ostream& out = std::cout;
+struct LogicError : std::logic_error { using std::logic_error::logic_error; };
+struct NotImplemented : std::logic_error { using std::logic_error::logic_error; };
+#define libmesh_error_msg(msg) do { std::ostringstream s__; s__ << msg; throw libMesh::LogicError(s__.str()); } while (0)
+#define libmesh_not_implemented() throw libMesh::NotImplemented(std::string("not implemented: ") + __func__)
+#define libmesh_assert(x) ((void)0)
+
+enum ParallelType { AUTOMATIC = 0, SERIAL, PARALLEL, GHOSTED };     // include/enums/enum_parallel_type.h
+enum SolverPackage { PETSC_SOLVERS = 0, TRILINOS_SOLVERS, LASPACK_SOLVERS, SLEPC_SOLVERS, EIGEN_SOLVERS, NLOPT_SOLVERS, INVALID_SOLVER_PACKAGE };
+enum ElemType { HEX8 = 10, HEX27 = 12, TET10 = 9, INVALID_ELEM = 99 };  // include/enums/enum_elem_type.h
+
+namespace Parallel { struct Communicator { processor_id_type rank() const { return 0; } processor_id_type size() const { return 1; } }; }
+struct ParallelObject {                                              // include/parallel/parallel_object.h
+  explicit ParallelObject(const Parallel::Communicator& c) : _communicator(c) {}
+  const Parallel::Communicator& comm() const { return _communicator; }
+  processor_id_type n_processors() const { return _communicator.size(); }
+  processor_id_type processor_id() const { return _communicator.rank(); }
+  const Parallel::Communicator& _communicator;
+};
+
+struct Point { Real c[3]; Real operator()(unsigned i) const { return c[i]; } };   // include/geom/point.h
+struct Node : Point { dof_id_type _id; dof_id_type id() const { return _id; } };  // include/geom/node.h
+struct Elem {                                                                      // include/geom/elem.h
+  ElemType _type; std::vector<const Node*> _nodes; dof_id_type _id; processor_id_type _pid;
+  ElemType type() const { return _type; }
+  unsigned int n_nodes() const { return (unsigned)_nodes.size(); }
+  const Node* node_ptr(unsigned i) const { return _nodes[i]; }
+  dof_id_type node_id(unsigned i) const { return _nodes[i]->id(); }
+  dof_id_type id() const { return _id; }
+  processor_id_type processor_id() const { return _pid; }
+};
+struct MeshBase {                                                                  // include/mesh/mesh_base.h
+  std::vector<const Elem*> _local;
+  const std::vector<const Elem*>& active_local_element_ptr_range() const { return _local; }  // mesh_base.h:1484
+  dof_id_type n_nodes() const { return 0; }
+  dof_id_type max_node_id() const { return 0; }
+};
+
+template <typename T> struct DenseMatrix {                                         // include/numerics/dense_matrix.h
+  unsigned _m = 0, _n = 0; std::vector<T> _val;
+  unsigned m() const { return _m; } unsigned n() const { return _n; }
+  const std::vector<T>& get_values() const { return _val; }                        // dense_matrix.h:382 (row-major, :953-978)
+};
+namespace SparsityPattern {                                                        // include/base/sparsity_pattern.h:55-57
+typedef std::vector<dof_id_type> Row;
+typedef std::vector<Row> Graph;
+}
+typedef std::map<dof_id_type, Number> DofConstraintValueMap;                       // include/base/dof_map.h:123
+
+template <typename T> class SparseMatrix;
+class DofMap {                                                                     // include/base/dof_map.h
+ public:
+  dof_id_type n_dofs() const { return 0; }                                         // dof_map_base.h
+  dof_id_type first_dof() const { return 0; }                                      // dof_map_base.h:185
+  dof_id_type end_dof() const { return 0; }                                        // dof_map_base.h:191
+  dof_id_type n_local_dofs() const { return end_dof() - first_dof(); }
+  void dof_indices(const Elem*, std::vector<dof_id_type>&) const {}                // dof_map.h:2201 / src/base/dof_map.C:2201
+  bool is_constrained_dof(dof_id_type) const { return false; }                     // dof_map.h:2426
+  DofConstraintValueMap& get_primal_constraint_values() { return _vals; }          // dof_map.h:1263
+  unsigned int n_variables() const { return 1; }
+  DofConstraintValueMap _vals;
+};
+
+template <typename T> class NumericVector {                                        // include/numerics/numeric_vector.h
+ public:
+  virtual ~NumericVector() = default;
+  virtual void close() {}                                                          // :177
+  virtual void zero() {}
+  virtual numeric_index_type first_local_index() const { return 0; }               // :500
+  virtual numeric_index_type last_local_index() const { return 0; }
+  virtual void set(const numeric_index_type, const T) {}                           // :508
+  virtual NumericVector<T>& operator=(const std::vector<T>&) { return *this; }     // :295
+};
+
+template <typename T> class SparseMatrix : public ParallelObject {                  // include/numerics/sparse_matrix.h
+ public:
+  explicit SparseMatrix(const Parallel::Communicator& c) : ParallelObject(c) {}     // :78
+  virtual ~SparseMatrix() = default;
+  virtual SolverPackage solver_package() = 0;                                       // :127
+  virtual bool initialized() const { return _is_initialized; }                      // :133
+  void attach_dof_map(const DofMap& d) { _dof_map = &d; }                           // :138
+  virtual bool need_full_sparsity_pattern() const { return false; }                 // :162
+  virtual void update_sparsity_pattern(const SparsityPattern::Graph&) {}            // :175
+  virtual void init(const numeric_index_type m, const numeric_index_type n, const numeric_index_type m_l,
+                    const numeric_index_type n_l, const numeric_index_type nnz = 30, const numeric_index_type noz = 10,
+                    const numeric_index_type blocksize = 1) = 0;                    // :189
+  virtual void init(ParallelType type = PARALLEL) = 0;                              // :201
+  virtual void clear() = 0;                                                         // :206
+  virtual void zero() = 0;                                                          // :211
+  virtual std::unique_ptr<SparseMatrix<T>> zero_clone() const = 0;                  // :219
+  virtual std::unique_ptr<SparseMatrix<T>> clone() const = 0;                       // :226
+  virtual void close() = 0;                                                         // :237
+  virtual numeric_index_type m() const = 0;                                         // :249
+  virtual numeric_index_type n() const = 0;                                         // :264
+  virtual numeric_index_type row_start() const = 0;                                 // :270
+  virtual numeric_index_type row_stop() const = 0;                                  // :276
+  virtual numeric_index_type col_start() const = 0;                                 // :282
+  virtual numeric_index_type col_stop() const = 0;                                  // :288
+  virtual void set(const numeric_index_type i, const numeric_index_type j, const T value) = 0;   // :295
+  virtual void add(const numeric_index_type i, const numeric_index_type j, const T value) = 0;   // :304
+  virtual void add_matrix(const DenseMatrix<T>& dm, const std::vector<numeric_index_type>& rows,
+                          const std::vector<numeric_index_type>& cols) = 0;         // :312
+  virtual void add_matrix(const DenseMatrix<T>& dm, const std::vector<numeric_index_type>& dof_indices) = 0;  // :320
+  virtual void add(const T a, const SparseMatrix<T>& X) = 0;                        // :344
+  virtual T operator()(const numeric_index_type i, const numeric_index_type j) const = 0;       // :368
+  virtual Real l1_norm() const = 0;                                                 // :379
+  virtual Real linfty_norm() const = 0;                                             // :391
+  virtual bool closed() const = 0;                                                  // :401
+  virtual void print_personal(std::ostream& os = libMesh::out) const = 0;           // :448
+  virtual void get_diagonal(NumericVector<T>& dest) const = 0;                      // :592
+  virtual void get_transpose(SparseMatrix<T>& dest) const = 0;                      // :598
+  virtual void get_row(numeric_index_type i, std::vector<numeric_index_type>& indices, std::vector<T>& values) const = 0;  // :607
+ protected:
+  const DofMap* _dof_map = nullptr;                                                 // :676
+  bool _is_initialized = false;                                                     // :687
+};
+
+class System {                                                                      // include/systems/system.h
+ public:
+  const MeshBase& get_mesh() const { return *_mesh; }                               // :2359
+  DofMap& get_dof_map() { return *_dof; }                                           // :2375
+  const MeshBase* _mesh = nullptr; DofMap* _dof = nullptr;
+};
+class ExplicitSystem : public System { public: NumericVector<Number>* rhs = nullptr; };          // include/systems/explicit_system.h:124
+class ImplicitSystem : public ExplicitSystem { public: SparseMatrix<Number>* matrix = nullptr; };  // include/systems/implicit_system.h:311
+class LinearImplicitSystem : public ImplicitSystem {};
+class EquationSystems {                                                             // include/systems/equation_systems.h
+ public:
+  template <typename S> S& get_system(const std::string&) { return *static_cast<S*>(_sys); }    // :757
+  System* _sys = nullptr;
+};
+}  // namespace libMesh
+#endif
