@@ -139,6 +139,85 @@ __device__ __forceinline__ double ex4_forcing_t(double x, double y, double z) {
 }
 __device__ __noinline__ double ex4_forcing_lib(double x, double y, double z) { return ex4_forcing_t<false>(x, y, z); }
 
+// Phase A of an element, lane = quadrature point: FEMap::compute_map.  Returns has_affine_map; fills
+// S = sqrt(det J) * (dxidx dxidy dxidz | detadx .. | dzetadx ..), JxW and (when want_xyz, or always on the general
+// branch) the physical point.  X = node coordinates of the element in shared memory.
+template <int NPE, int NQ>
+__device__ __forceinline__ bool geom_phase(const double* X, const double* s_tab, int lane, bool want_xyz, int* flags, double (&S)[9],
+                                           double& JxW, double& x, double& y, double& z) {
+  const double* s_phi = s_tab;
+  const double* s_dxi = s_tab + NPE * NQ;
+  const double* s_qw = s_tab + 4 * NPE * NQ;
+  const bool affine = __all_sync(0xffffffffu, affine_check_lane<NPE>(X, lane));
+  {
+      x = 0; y = 0; z = 0;
+      double xa = 0, ya = 0, za = 0, xb = 0, yb = 0, zb = 0, xc = 0, yc = 0, zc = 0;
+      const int q = lane < NQ ? lane : 0;
+      if (affine) {
+        // compute_affine_map (fe_map.C:1167-1244): the Jacobian at qp 0 only — lane c < 9 sums component c —
+        // and xyz at every qp (:1190-1197)
+        // (sums split three ways: independent FP64 chains instead of one 27-deep dependent chain)
+        double d = 0.;
+        if (lane < 9) {
+          const double* tabd = s_dxi + (lane / 3) * (NPE * NQ);
+          const int cd = lane % 3;
+          double d0 = 0., d1 = 0., d2 = 0.;
+#pragma unroll
+          for (int i = 0; i + 2 < NPE; i += 3) {
+            d0 += tabd[i * NQ] * X[3 * i + cd];
+            d1 += tabd[(i + 1) * NQ] * X[3 * (i + 1) + cd];
+            d2 += tabd[(i + 2) * NQ] * X[3 * (i + 2) + cd];
+          }
+#pragma unroll
+          for (int i = NPE - NPE % 3; i < NPE; ++i) d0 += tabd[i * NQ] * X[3 * i + cd];
+          d = (d0 + d1) + d2;
+        }
+        if (want_xyz) {
+          double x1 = 0., y1 = 0., z1 = 0., x2 = 0., y2 = 0., z2 = 0.;
+#pragma unroll
+          for (int i = 0; i + 2 < NPE; i += 3) {
+            const double p0 = s_phi[i * NQ + q], p1 = s_phi[(i + 1) * NQ + q], p2 = s_phi[(i + 2) * NQ + q];
+            x += p0 * X[3 * i]; y += p0 * X[3 * i + 1]; z += p0 * X[3 * i + 2];
+            x1 += p1 * X[3 * i + 3]; y1 += p1 * X[3 * i + 4]; z1 += p1 * X[3 * i + 5];
+            x2 += p2 * X[3 * i + 6]; y2 += p2 * X[3 * i + 7]; z2 += p2 * X[3 * i + 8];
+          }
+#pragma unroll
+          for (int i = NPE - NPE % 3; i < NPE; ++i) {
+            const double p = s_phi[i * NQ + q];
+            x += p * X[3 * i]; y += p * X[3 * i + 1]; z += p * X[3 * i + 2];
+          }
+          x = (x + x1) + x2; y = (y + y1) + y2; z = (z + z1) + z2;
+        }
+        xa = __shfl_sync(0xffffffffu, d, 0); ya = __shfl_sync(0xffffffffu, d, 1); za = __shfl_sync(0xffffffffu, d, 2);
+        xb = __shfl_sync(0xffffffffu, d, 3); yb = __shfl_sync(0xffffffffu, d, 4); zb = __shfl_sync(0xffffffffu, d, 5);
+        xc = __shfl_sync(0xffffffffu, d, 6); yc = __shfl_sync(0xffffffffu, d, 7); zc = __shfl_sync(0xffffffffu, d, 8);
+      } else {
+        // general branch: compute_single_point_map per qp (fe_map.C:994-1026)
+        const double* s_deta = s_dxi + NPE * NQ;
+        const double* s_dzeta = s_deta + NPE * NQ;
+#pragma unroll 3
+        for (int i = 0; i < NPE; ++i) {
+          const double px = X[3 * i], py = X[3 * i + 1], pz = X[3 * i + 2];
+          const double p = s_phi[i * NQ + q], a = s_dxi[i * NQ + q], b = s_deta[i * NQ + q], c = s_dzeta[i * NQ + q];
+          x += p * px; y += p * py; z += p * pz;
+          xa += a * px; ya += a * py; za += a * pz;
+          xb += b * px; yb += b * py; zb += b * pz;
+          xc += c * px; yc += c * py; zc += c * pz;
+        }
+      }
+      // det J in the order of fe_map.C:1046-1048, inverse rows :1056-1068
+      const double jac = (xa * (yb * zc - zb * yc) + ya * (zb * xc - xb * zc) + za * (xb * yc - yb * xc));
+      const bool bad = !(jac > 0.);
+      if (bad && lane < NQ) atomicAdd(&flags[0], 1);  // check_for_degenerate_map, fe_map.C:467-506
+      JxW = (affine && q != 0) ? jac * s_qw[0] / s_qw[0] * s_qw[q] : jac * s_qw[q];  // fe_map.C:1242 / :1052
+      const double s = bad ? 0. : rsqrt(jac);  // sqrt(jac) / jac
+      S[0] = (yb * zc - zb * yc) * s; S[1] = (zb * xc - xb * zc) * s; S[2] = (xb * yc - yb * xc) * s;
+      S[3] = (za * yc - ya * zc) * s; S[4] = (xa * zc - za * xc) * s; S[5] = (ya * xc - xa * yc) * s;
+      S[6] = (ya * zb - za * yb) * s; S[7] = (za * xb - xa * zb) * s; S[8] = (xa * yb - ya * xb) * s;
+  }
+  return affine;
+}
+
 template <int NPE, int NQ, int WARPS>
 __global__ void __launch_bounds__(WARPS * 32, 1)
 k_elem_poisson(const double* __restrict__ xyz, const uint32_t* __restrict__ conn, const double* __restrict__ tab,
@@ -185,73 +264,9 @@ k_elem_poisson(const double* __restrict__ xyz, const uint32_t* __restrict__ conn
     __syncwarp();
 
     // ---- A: reference -> physical map at quadrature point q = lane ---------------------------------------
-    const bool affine = __all_sync(0xffffffffu, affine_check_lane<NPE>(X, lane));
-    double S[9];  // sqrt(det J) * (dxidx dxidy dxidz | detadx .. | dzetadx ..)
+    double S[9], JxW, x, y, z;
+    const bool affine = geom_phase<NPE, NQ>(X, s_tab, lane, forcing == FEASM_FORCING_EX4_FD, flags, S, JxW, x, y, z);
     {
-      double x = 0, y = 0, z = 0;
-      double xa = 0, ya = 0, za = 0, xb = 0, yb = 0, zb = 0, xc = 0, yc = 0, zc = 0;
-      const int q = lane < NQ ? lane : 0;
-      if (affine) {
-        // compute_affine_map (fe_map.C:1167-1244): the Jacobian at qp 0 only — lane c < 9 sums component c —
-        // and xyz at every qp (:1190-1197)
-        // (sums split three ways: independent FP64 chains instead of one 27-deep dependent chain)
-        double d = 0.;
-        if (lane < 9) {
-          const double* tabd = s_dxi + (lane / 3) * (NPE * NQ);
-          const int cd = lane % 3;
-          double d0 = 0., d1 = 0., d2 = 0.;
-#pragma unroll
-          for (int i = 0; i + 2 < NPE; i += 3) {
-            d0 += tabd[i * NQ] * X[3 * i + cd];
-            d1 += tabd[(i + 1) * NQ] * X[3 * (i + 1) + cd];
-            d2 += tabd[(i + 2) * NQ] * X[3 * (i + 2) + cd];
-          }
-#pragma unroll
-          for (int i = NPE - NPE % 3; i < NPE; ++i) d0 += tabd[i * NQ] * X[3 * i + cd];
-          d = (d0 + d1) + d2;
-        }
-        if (forcing == FEASM_FORCING_EX4_FD) {
-          double x1 = 0., y1 = 0., z1 = 0., x2 = 0., y2 = 0., z2 = 0.;
-#pragma unroll
-          for (int i = 0; i + 2 < NPE; i += 3) {
-            const double p0 = s_phi[i * NQ + q], p1 = s_phi[(i + 1) * NQ + q], p2 = s_phi[(i + 2) * NQ + q];
-            x += p0 * X[3 * i]; y += p0 * X[3 * i + 1]; z += p0 * X[3 * i + 2];
-            x1 += p1 * X[3 * i + 3]; y1 += p1 * X[3 * i + 4]; z1 += p1 * X[3 * i + 5];
-            x2 += p2 * X[3 * i + 6]; y2 += p2 * X[3 * i + 7]; z2 += p2 * X[3 * i + 8];
-          }
-#pragma unroll
-          for (int i = NPE - NPE % 3; i < NPE; ++i) {
-            const double p = s_phi[i * NQ + q];
-            x += p * X[3 * i]; y += p * X[3 * i + 1]; z += p * X[3 * i + 2];
-          }
-          x = (x + x1) + x2; y = (y + y1) + y2; z = (z + z1) + z2;
-        }
-        xa = __shfl_sync(0xffffffffu, d, 0); ya = __shfl_sync(0xffffffffu, d, 1); za = __shfl_sync(0xffffffffu, d, 2);
-        xb = __shfl_sync(0xffffffffu, d, 3); yb = __shfl_sync(0xffffffffu, d, 4); zb = __shfl_sync(0xffffffffu, d, 5);
-        xc = __shfl_sync(0xffffffffu, d, 6); yc = __shfl_sync(0xffffffffu, d, 7); zc = __shfl_sync(0xffffffffu, d, 8);
-      } else {
-        // general branch: compute_single_point_map per qp (fe_map.C:994-1026)
-        const double* s_deta = s_dxi + NPE * NQ;
-        const double* s_dzeta = s_deta + NPE * NQ;
-#pragma unroll 3
-        for (int i = 0; i < NPE; ++i) {
-          const double px = X[3 * i], py = X[3 * i + 1], pz = X[3 * i + 2];
-          const double p = s_phi[i * NQ + q], a = s_dxi[i * NQ + q], b = s_deta[i * NQ + q], c = s_dzeta[i * NQ + q];
-          x += p * px; y += p * py; z += p * pz;
-          xa += a * px; ya += a * py; za += a * pz;
-          xb += b * px; yb += b * py; zb += b * pz;
-          xc += c * px; yc += c * py; zc += c * pz;
-        }
-      }
-      // det J in the order of fe_map.C:1046-1048, inverse rows :1056-1068
-      const double jac = (xa * (yb * zc - zb * yc) + ya * (zb * xc - xb * zc) + za * (xb * yc - yb * xc));
-      const bool bad = !(jac > 0.);
-      if (bad && lane < NQ) atomicAdd(&flags[0], 1);  // check_for_degenerate_map, fe_map.C:467-506
-      const double JxW = (affine && q != 0) ? jac * s_qw[0] / s_qw[0] * s_qw[q] : jac * s_qw[q];  // fe_map.C:1242 / :1052
-      const double s = bad ? 0. : rsqrt(jac);  // sqrt(jac) / jac
-      S[0] = (yb * zc - zb * yc) * s; S[1] = (zb * xc - xb * zc) * s; S[2] = (xb * yc - yb * xc) * s;
-      S[3] = (za * yc - ya * zc) * s; S[4] = (xa * zc - za * xc) * s; S[5] = (ya * xc - xa * yc) * s;
-      S[6] = (ya * zb - za * yb) * s; S[7] = (za * xb - xa * zb) * s; S[8] = (xa * yb - ya * xb) * s;
       double f = 0.;
       if (forcing == FEASM_FORCING_EX4_FD) {
         // every lane evaluates (pad lanes repeat qp 0): no divergence; huge coordinates take the library path
@@ -386,20 +401,175 @@ int launch_poisson(feasm_ctx* ctx, const feasm_params& p, const double* d_f, int
   return FEASM_OK;
 }
 
+
+// ---- 3-variable isotropic linear elasticity (systems_of_equations_ex6.C:220-237) --------------------------------
+// Ke[(i,a),(k,b)] = sum_q JxW sum_jl C_ijkl dphi_b,l dphi_a,j with C_ijkl = l1 d_ij d_kl + l2 (d_ik d_jl + d_il d_jk)
+//                 = l1 P_ik[a][b] + l2 P_ki[a][b] + l2 d_ik (P_00 + P_11 + P_22)[a][b],
+// P_dd'[a][b] = sum_q G_d[a][q] G_d'[b][q], G as in the Poisson kernel.  So the 81x81 element matrix needs only the
+// six distinct 27x27 products P_dd' (d <= d'; P_d'd = P_dd'^T): 7 k-steps of DMMA each instead of a 168-long
+// contraction over 81 rows — the isotropic structure cuts the tensor work ninefold (SURVEY a7 allows either count;
+// bench/DESIGN quote the flops of THIS algorithm).  One warp per element; each P goes through a shared-memory tile
+// (odd row stride: row and column reads are both conflict free) from which the nine variable blocks are combined
+// and stored.  Fe_(i,a) = f_i sum_q JxW phi_a(q) (body force; the traction term is omitted).
+template <int NPE, int NQ, int WARPS>
+__global__ void __launch_bounds__(WARPS * 32, 1)
+k_elem_elasticity(const double* __restrict__ xyz, const uint32_t* __restrict__ conn, const double* __restrict__ tab, double lam1,
+                  double lam2, double f0, double f1, double f2, int64_t e0, int64_t e1, double* __restrict__ kf, int* flags) {
+  using C = ElemCfg<NPE, NQ>;
+  constexpr int NBP = (NPE + 7) / 8;   // 8-row blocks, padded (all go through DMMA here)
+  constexpr int ND = 3 * NPE, LDR = feasm_ldr(ND);
+  constexpr int TLD = NPE | 1;          // odd tile stride
+  constexpr int TILE = ((NPE * TLD + 1) & ~1);
+  extern __shared__ double smem[];
+  double* s_tab = smem;
+  double* s_tw = smem + C::TAB_SZ;      // [c][row][TS], rows padded to NBP*8
+  constexpr int TWE = 3 * NBP * 8 * C::TS;
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  for (int t = threadIdx.x; t < C::TAB; t += WARPS * 32) s_tab[t] = tab[t];
+  for (int t = threadIdx.x; t < TWE; t += WARPS * 32) {
+    const int c = t / (NBP * 8 * C::TS), row = (t / C::TS) % (NBP * 8), q = t % C::TS;
+    s_tw[t] = (row < NPE && q < NQ) ? sqrt(tab[4 * NPE * NQ + q]) * tab[(1 + c) * NPE * NQ + row * NQ + q] : 0.;
+  }
+  const double* s_phi = s_tab;
+  double* X = s_tw + TWE + (size_t)warp * (C::X_SZ + 32 + 3 * TILE);
+  double* fw = X + C::X_SZ;
+  double* tile = fw + 32;  // three tiles: P_00, P_11, P_22, then reused for the off-diagonal products
+  const int g = lane >> 2, t4 = lane & 3;
+  const double* twp = s_tw + g * C::TS + t4;
+  __syncthreads();
+
+  const int64_t stride = (int64_t)gridDim.x * WARPS;
+  for (int64_t e = e0 + (int64_t)blockIdx.x * WARPS + warp; e < e1; e += stride) {
+    if (lane < NPE) {
+      const uint64_t node = conn[e * NPE + lane];
+      X[3 * lane] = xyz[node * 3]; X[3 * lane + 1] = xyz[node * 3 + 1]; X[3 * lane + 2] = xyz[node * 3 + 2];
+    }
+    __syncwarp();
+    double S[9], JxW, x, y, z;
+    const bool affine = geom_phase<NPE, NQ>(X, s_tab, lane, false, flags, S, JxW, x, y, z);
+    fw[lane] = lane < NQ ? JxW : 0.;
+    double* out = kf + (uint64_t)(e - e0) * (ND * LDR);
+
+    // P_dd' for one (d, d') pair -> tile[a*TLD + b]
+    auto product = [&](int d, int dp, double* T) {
+      double acc[NBP][NBP][2];
+#pragma unroll
+      for (int ib = 0; ib < NBP; ++ib)
+#pragma unroll
+        for (int jb = 0; jb < NBP; ++jb) { acc[ib][jb][0] = 0.; acc[ib][jb][1] = 0.; }
+#pragma unroll 1
+      for (int qg = 0; qg < C::QG; ++qg) {
+        double s0 = S[d], s1 = S[3 + d], s2 = S[6 + d], r0 = S[dp], r1 = S[3 + dp], r2 = S[6 + dp];
+        if (!affine) {
+          const int src = 4 * qg + t4;
+          s0 = __shfl_sync(0xffffffffu, s0, src); s1 = __shfl_sync(0xffffffffu, s1, src); s2 = __shfl_sync(0xffffffffu, s2, src);
+          r0 = __shfl_sync(0xffffffffu, r0, src); r1 = __shfl_sync(0xffffffffu, r1, src); r2 = __shfl_sync(0xffffffffu, r2, src);
+        }
+        double A[NBP], B[NBP];
+#pragma unroll
+        for (int ib = 0; ib < NBP; ++ib) {
+          const double a = twp[ib * 8 * C::TS + 4 * qg];
+          const double b = twp[NBP * 8 * C::TS + ib * 8 * C::TS + 4 * qg];
+          const double c = twp[2 * NBP * 8 * C::TS + ib * 8 * C::TS + 4 * qg];
+          A[ib] = a * s0 + b * s1 + c * s2;
+          B[ib] = a * r0 + b * r1 + c * r2;
+        }
+#pragma unroll
+        for (int ib = 0; ib < NBP; ++ib)
+#pragma unroll
+          for (int jb = 0; jb < NBP; ++jb) dmma884(acc[ib][jb][0], acc[ib][jb][1], A[ib], B[jb]);
+      }
+#pragma unroll
+      for (int ib = 0; ib < NBP; ++ib)
+#pragma unroll
+        for (int jb = 0; jb < NBP; ++jb) {
+          const int i = ib * 8 + g, j = jb * 8 + 2 * t4;
+          if (i < NPE && j < NPE) T[i * TLD + j] = acc[ib][jb][0];
+          if (i < NPE && j + 1 < NPE) T[i * TLD + j + 1] = acc[ib][jb][1];
+        }
+    };
+
+    // diagonal variable blocks: K_dd = (l1 + l2) P_dd + l2 (P_00 + P_11 + P_22)
+    product(0, 0, tile);
+    product(1, 1, tile + TILE);
+    product(2, 2, tile + 2 * TILE);
+    __syncwarp();
+    if (lane < NPE) {
+      for (int a = 0; a < NPE; ++a) {
+        const double p0 = tile[a * TLD + lane], p1 = tile[TILE + a * TLD + lane], p2 = tile[2 * TILE + a * TLD + lane];
+        const double tr = lam2 * ((p0 + p1) + p2);
+        out[(0 * NPE + a) * LDR + 0 * NPE + lane] = (lam1 + lam2) * p0 + tr;
+        out[(1 * NPE + a) * LDR + 1 * NPE + lane] = (lam1 + lam2) * p1 + tr;
+        out[(2 * NPE + a) * LDR + 2 * NPE + lane] = (lam1 + lam2) * p2 + tr;
+      }
+      // Fe (systems_of_equations_ex6.C:233-236): body force f_i, same for every variable up to the factor
+      double m = 0.;
+      for (int q = 0; q < NQ; ++q) m += fw[q] * s_phi[lane * NQ + q];
+      out[(0 * NPE + lane) * LDR + ND] = f0 * m;
+      out[(1 * NPE + lane) * LDR + ND] = f1 * m;
+      out[(2 * NPE + lane) * LDR + ND] = f2 * m;
+    }
+    __syncwarp();
+    // off-diagonal variable blocks: K_ik = l1 P_ik + l2 P_ik^T, K_ki = l2 P_ik + l1 P_ik^T   (i < k)
+#pragma unroll
+    for (int pair = 0; pair < 3; ++pair) {
+      const int i = pair == 2 ? 1 : 0, k = pair == 0 ? 1 : 2;
+      product(i, k, tile);
+      __syncwarp();
+      if (lane < NPE) {
+        for (int a = 0; a < NPE; ++a) {
+          const double p = tile[a * TLD + lane], pt = tile[lane * TLD + a];
+          out[(i * NPE + a) * LDR + k * NPE + lane] = lam1 * p + lam2 * pt;
+          out[(k * NPE + a) * LDR + i * NPE + lane] = lam2 * p + lam1 * pt;
+        }
+      }
+      __syncwarp();
+    }
+  }
+}
+
+template <int NPE, int NQ, int WARPS>
+int launch_elasticity(feasm_ctx* ctx, const feasm_params& p, int64_t e0, int64_t e1, double* d_kf) {
+  using C = ElemCfg<NPE, NQ>;
+  constexpr int NBP = (NPE + 7) / 8, TLD = NPE | 1, TILE = ((NPE * TLD + 1) & ~1);
+  const size_t smem = sizeof(double) * (size_t)(C::TAB_SZ + 3 * NBP * 8 * C::TS + WARPS * (C::X_SZ + 32 + 3 * TILE));
+  auto kern = k_elem_elasticity<NPE, NQ, WARPS>;
+  FEASM_CUDA(ctx, cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+  // systems_of_equations_ex6.C:136-151
+  const double E = p.young_modulus != 0. ? p.young_modulus : 1., nu = p.poisson_ratio != 0. ? p.poisson_ratio : 0.3;
+  const double lam1 = (E * nu) / ((1. + nu) * (1. - 2. * nu)), lam2 = E / (2. * (1. + nu));
+  double f[3] = {p.body_force[0], p.body_force[1], p.body_force[2]};
+  if (f[0] == 0. && f[1] == 0. && f[2] == 0.) f[2] = -1.;
+  int64_t blocks = (e1 - e0 + WARPS - 1) / WARPS;
+  if (blocks > ctx->sm_count) blocks = ctx->sm_count;
+  if (blocks < 1) blocks = 1;
+  kern<<<(unsigned)blocks, WARPS * 32, smem, ctx->stream>>>(ctx->d_xyz, ctx->d_conn, ctx->d_tab, lam1, lam2, f[0], f[1], f[2], e0, e1,
+                                                           d_kf, ctx->d_flags);
+  FEASM_CUDA(ctx, cudaGetLastError());
+  return FEASM_OK;
+}
+
 }  // namespace
 
 int feasm_launch_element_kernel(feasm_ctx* ctx, const feasm_params& p, const double* d_f, int64_t e0, int64_t e1,
                                 double* d_kf) {
   if (p.problem == FEASM_POISSON) {
     if (ctx->elem_type == FEASM_HEX27 && ctx->tab_nq == 27) {
-      static const int warps = getenv("FEASM_ELEM_WARPS") ? atoi(getenv("FEASM_ELEM_WARPS")) : 16;  // tuning knob
-      if (warps == 12) return launch_poisson<27, 27, 12>(ctx, p, d_f, e0, e1, d_kf);
-      return launch_poisson<27, 27, 16>(ctx, p, d_f, e0, e1, d_kf);
+      static const int warps = getenv("FEASM_ELEM_WARPS") ? atoi(getenv("FEASM_ELEM_WARPS")) : 12;  // tuning knob
+      if (warps == 16) return launch_poisson<27, 27, 16>(ctx, p, d_f, e0, e1, d_kf);
+      return launch_poisson<27, 27, 12>(ctx, p, d_f, e0, e1, d_kf);
     }
     if (ctx->elem_type == FEASM_HEX8 && ctx->tab_nq == 8) return launch_poisson<8, 8, 16>(ctx, p, d_f, e0, e1, d_kf);
     if (ctx->elem_type == FEASM_HEX8 && ctx->tab_nq == 27) return launch_poisson<8, 27, 16>(ctx, p, d_f, e0, e1, d_kf);
     if (ctx->elem_type == FEASM_TET10 && ctx->tab_nq == 14) return launch_poisson<10, 14, 16>(ctx, p, d_f, e0, e1, d_kf);
     return feasm_fail(ctx, FEASM_ERR_ARG, "no Poisson kernel for this element type / quadrature order");
+  }
+  if (p.problem == FEASM_ELASTICITY) {
+    if (ctx->n_vars != 3) return feasm_fail(ctx, FEASM_ERR_ARG, "elasticity needs 3 variables per node");
+    if (ctx->elem_type == FEASM_HEX27 && ctx->tab_nq == 27) return launch_elasticity<27, 27, 8>(ctx, p, e0, e1, d_kf);
+    if (ctx->elem_type == FEASM_HEX8 && ctx->tab_nq == 8) return launch_elasticity<8, 8, 16>(ctx, p, e0, e1, d_kf);
+    if (ctx->elem_type == FEASM_TET10 && ctx->tab_nq == 14) return launch_elasticity<10, 14, 16>(ctx, p, e0, e1, d_kf);
+    return feasm_fail(ctx, FEASM_ERR_ARG, "no elasticity kernel for this element type / quadrature order");
   }
   return feasm_fail(ctx, FEASM_ERR_ARG, "problem not implemented");
 }

@@ -208,3 +208,39 @@ def test_argument_errors():
     with pytest.raises(F.FeasmError):
         ctx.set_dofs(ed, s.n_dofs - 1)  # dof id out of range
     ctx.close()
+
+
+# ---- config 5: systems_of_equations_ex6 linear elasticity (3 variables, homogeneous Dirichlet on min-x) -----------
+ELAST = [
+    ("hex27_ex6", 27, (4, 2, 2), None),
+    ("hex27_ex6_skew", 27, (3, 2, 2), (1, 0.004, 7)),
+    ("hex8_ex6", 8, (5, 3, 2), None),
+    ("tet10_ex6", 10, (3, 2, 1), None),
+]
+
+
+@pytest.mark.parametrize("name,etype,dims,skew", ELAST, ids=[c[0] for c in ELAST])
+def test_elasticity_ex6(name, etype, dims, skew):
+    F, O = _mods()
+    m, s = make_case(etype, dims, bounds=(0, 1, 0, 0.3, 0, 0.1), n_vars=3, skew=skew, dirichlet=(4,), kind=1)
+    ctx = make_ctx(m, s)
+    rp, ci = s.sparsity()
+    rp2, ci2 = ctx.get_pattern()
+    assert np.array_equal(rp, rp2) and np.array_equal(ci, ci2)
+    vo, ro, _ = s.assemble(O.ELASTICITY_EX6)
+    p = F.make_params(F.ELASTICITY, 0, F.FORCING_NONE, F.CONSTRAIN_HOMOGENEOUS)
+    ctx.assemble(p)
+    v, r = ctx.get_values()
+    assert csr_parity_error(v, vo, rp) < PARITY_TOL
+    assert vec_parity_error(r, ro) < PARITY_TOL
+    Ko, Fo = s.element_matrices(O.ELASTICITY_EX6, constrained=False)
+    K, Fv = ctx.element_matrices(p, constrained=False)
+    assert dense_parity_error(K, Ko) < PARITY_TOL
+    assert vec_parity_error(Fv.reshape(-1), Fo.reshape(-1)) < PARITY_TOL
+    # rigid-body translations are in the null space of the unconstrained element matrix
+    nd = K.shape[1]
+    for var in range(3):
+        t = np.zeros(nd)
+        t[var * (nd // 3):(var + 1) * (nd // 3)] = 1.0
+        assert np.abs(K @ t).max() < 1e-12 * np.abs(K).max()
+    ctx.close()
