@@ -17,209 +17,12 @@
 //      lower triangle.  Constraints are NOT applied here: the row reduction applies them (feasm_scatter.cu).
 #include <cstdlib>
 
-#include "feasm_internal.h"
+#include "feasm_elem_dev.cuh"
 
 namespace {
-
-__device__ __forceinline__ void dmma884(double& c0, double& c1, double a, double b) {
-  asm volatile("mma.sync.aligned.m8n8k4.row.col.f64.f64.f64.f64 {%0,%1}, {%2}, {%3}, {%0,%1};\n"
-               : "+d"(c0), "+d"(c1)
-               : "d"(a), "d"(b));
-}
-
-constexpr int table_stride(int nqp) {
-  // lane (g = lane>>2, t = lane&3) reads T[row0+g][q0+t]: conflict-free 64-bit LDS needs stride = 4 or 12 (mod 16)
-  int s = nqp;
-  while (s % 16 != 4 && s % 16 != 12) ++s;
-  return s;
-}
-
-template <int NPE, int NQ>
-struct ElemCfg {
-  static constexpr int NBF = NPE / 8;               // full 8-row blocks of Ke: DMMA
-  static constexpr int REM = NPE - 8 * NBF;         // leftover rows: DFMA
-  static constexpr int NB = NBF + (REM ? 1 : 0);    // fragment row blocks a lane generates
-  static constexpr int NQP = (NQ + 3) & ~3;         // quadrature points padded to the MMA k step
-  static constexpr int QG = NQP / 4;
-  static constexpr int TS = table_stride(NQP);      // row stride of the scaled-gradient table
-  static constexpr int NBLK = NBF * (NBF + 1) / 2;
-  static constexpr int LDR = feasm_ldr(NPE);
-  static constexpr int TAB = 4 * NPE * NQ + NQ;     // phi | dxi | deta | dzeta | qw  (global layout, [i][q])
-  static constexpr int TAB_SZ = (TAB + 1) & ~1;
-  static constexpr int TW_SZ = 3 * NB * 8 * TS;     // sqrt(w_q) dref_c[i][q], zero padded
-  static constexpr int X_SZ = (NPE * 3 + 1) & ~1;
-  static constexpr int WARP_DBL = X_SZ + 32;        // X | fw
-  static constexpr int SMEM_DBL(int warps) { return TAB_SZ + TW_SZ + warps * WARP_DBL; }
-  static_assert(NQP <= 32, "lane = quadrature point needs nq <= 32");
-  static_assert(NPE <= 32, "lane = shape function needs npe <= 32");
-  static_assert(REM <= 4, "leftover rows beyond 4 should become a DMMA block");
-};
-
-// Elem::has_affine_map as a list of vector comparisons (a1-a0)*sa ~ (b1-b0)*sb with relative_fuzzy_equals at
-// affine_tol = TOLERANCE^2 (include/geom/elem.h:2070, include/utils/fuzzy_equals.h:96-112); one lane per check.
-struct AffineCheck { signed char a1, a0, b1, b0; float sa, sb; };
-__constant__ AffineCheck c_affine_hex8[4] = {{1, 0, 2, 3, 1, 1}, {1, 0, 5, 4, 1, 1}, {1, 0, 6, 7, 1, 1}, {4, 0, 7, 3, 1, 1}};  // cell_hex8.C:121-135
-__constant__ AffineCheck c_affine_hex27[23] = {  // cell_hex27.C:125-166
-    {1, 0, 2, 3, 1, 1},     {1, 0, 5, 4, 1, 1},     {1, 0, 6, 7, 1, 1},     {1, 0, 8, 0, .5f, 1},   {1, 0, 10, 3, .5f, 1},
-    {1, 0, 16, 4, .5f, 1},  {1, 0, 18, 7, .5f, 1},  {1, 0, 20, 11, .5f, 1}, {1, 0, 21, 12, .5f, 1}, {1, 0, 23, 15, .5f, 1},
-    {1, 0, 25, 19, .5f, 1}, {1, 0, 26, 24, .5f, 1}, {4, 0, 7, 3, 1, 1},     {4, 0, 12, 0, .5f, 1},  {4, 0, 13, 1, .5f, 1},
-    {4, 0, 14, 2, .5f, 1},  {4, 0, 15, 3, .5f, 1},  {4, 0, 22, 9, .5f, 1},  {4, 0, 24, 11, .5f, 1}, {3, 0, 11, 0, .5f, 1},
-    {3, 0, 9, 1, .5f, 1},   {3, 0, 17, 5, .5f, 1},  {3, 0, 19, 4, .5f, 1}};
-__constant__ AffineCheck c_affine_tet10[6] = {{1, 0, 4, 0, 1, 2}, {2, 1, 5, 1, 1, 2}, {2, 0, 6, 0, 1, 2},  // cell_tet10.C:143-170
-                                              {3, 0, 7, 0, 1, 2}, {3, 1, 8, 1, 1, 2}, {3, 2, 9, 2, 1, 2}};
-
-template <int NPE>
-__device__ __forceinline__ bool affine_check_lane(const double* X, int lane) {
-  constexpr int N = NPE == 27 ? 23 : (NPE == 8 ? 4 : 6);
-  if (lane >= N) return true;
-  const AffineCheck c = NPE == 27 ? c_affine_hex27[lane] : (NPE == 8 ? c_affine_hex8[lane] : c_affine_tet10[lane]);
-  double na = 0., nb = 0., nd = 0.;
-#pragma unroll
-  for (int d = 0; d < 3; ++d) {
-    const double a = (X[3 * c.a1 + d] - X[3 * c.a0 + d]) * (double)c.sa;
-    const double b = (X[3 * c.b1 + d] - X[3 * c.b0 + d]) * (double)c.sb;
-    na += fabs(a); nb += fabs(b); nd += fabs(a - b);
-  }
-  return nd <= 1e-12 * (na + nb);
-}
-
-// sin (add = 0) or cos (add = 1) of a moderate argument, branch free so that the nine evaluations of one forcing
-// value interleave in the FP64 pipe: round-to-nearest quadrant via the 1.5*2^52 magic add, three-term Cody-Waite
-// reduction with FMA (pi/2 split into correctly rounded hi/mid/lo), then the classic fdlibm kernel polynomials with
-// the coefficient set selected per lane.  Max error 1 ulp against glibc over |a| < 1e3 (checked on the host,
-// oracle/check_trig.c); callers guard |a| <= 6e4 and use the library functions beyond.
-__device__ __forceinline__ double trig_fast(double a, int add) {
-  const double MAGIC = 6755399441055744.0;
-  const double q = __fma_rn(a, 0x1.45f306dc9c883p-1, MAGIC);
-  const int n = __double2loint(q) + add;
-  const double j = __dadd_rn(q, -MAGIC);
-  double r = __fma_rn(-j, 0x1.921fb54442d18p+0, a);
-  r = __fma_rn(-j, 0x1.1a62633145c07p-54, r);
-  r = __fma_rn(-j, -0x1.f1976b7ed8fbcp-110, r);
-  const double x2 = __dmul_rn(r, r);
-  const bool odd = n & 1;
-  double z = odd ? -1.13596475577881948265e-11 : 1.58969099521155010221e-10;
-  z = __fma_rn(z, x2, odd ? 2.08757232129817482790e-09 : -2.50507602534068634195e-08);
-  z = __fma_rn(z, x2, odd ? -2.75573143513906633035e-07 : 2.75573137070700676789e-06);
-  z = __fma_rn(z, x2, odd ? 2.48015872894767294178e-05 : -1.98412698298579493134e-04);
-  z = __fma_rn(z, x2, odd ? -1.38888888888741095749e-03 : 8.33333333332248946124e-03);
-  z = __fma_rn(z, x2, odd ? 4.16666666666666019037e-02 : -1.66666666666666324348e-01);
-  const double w = __fma_rn(z, x2, odd ? -0.5 : 0.0);
-  const double res = __fma_rn(w, odd ? x2 : r, odd ? 1.0 : r);
-  return (n & 2) ? -res : res;
-}
-
-// introduction_ex4.C:500-537 with exact_solution of introduction_ex3/exact_solution.C:40-47.  The seven
-// exact_solution() calls share nine distinct trig values; every product below is evaluated in the example's order
-// ((cos * sin) * cos), so the result equals the literal seven-call form bit for bit up to the last bit of sin/cos.
-// Explicit _rn intrinsics: no FMA contraction.  x / eps is evaluated as the correctly rounded quotient through
-// q0 = x*(1/eps), r = fma(-q0, eps, x), q = fma(r, 1/eps, q0) (Markstein; checked exhaustively-at-random on the host).
-template <bool FAST>
-__device__ __forceinline__ double ex4_forcing_t(double x, double y, double z) {
-  const double hp = .5 * 3.141592653589793;  // .5 * acos(-1.)
-  const double eps = 1.e-3;
-  auto cs = [](double a) { return FAST ? trig_fast(a, 1) : cos(a); };
-  auto sn = [](double a) { return FAST ? trig_fast(a, 0) : sin(a); };
-  const double cx0 = cs(__dmul_rn(hp, x)), cxm = cs(__dmul_rn(hp, __dadd_rn(x, -eps))), cxp = cs(__dmul_rn(hp, __dadd_rn(x, eps)));
-  const double sy0 = sn(__dmul_rn(hp, y)), sym = sn(__dmul_rn(hp, __dadd_rn(y, -eps))), syp = sn(__dmul_rn(hp, __dadd_rn(y, eps)));
-  const double cz0 = cs(__dmul_rn(hp, z)), czm = cs(__dmul_rn(hp, __dadd_rn(z, -eps))), czp = cs(__dmul_rn(hp, __dadd_rn(z, eps)));
-  auto u = [](double a, double b, double c) { return __dmul_rn(__dmul_rn(a, b), c); };
-  auto dv = [eps](double a) {
-    if (!FAST) return __ddiv_rn(a, eps);
-    const double rc = 1. / eps;  // folded at compile time
-    const double q0 = __dmul_rn(a, rc);
-    return __fma_rn(__fma_rn(-q0, eps, a), rc, q0);
-  };
-  auto fd = [&](double m, double p, double u0) { return dv(dv(__dadd_rn(__dadd_rn(m, p), __dmul_rn(-2., u0)))); };
-  const double u0 = u(cx0, sy0, cz0);
-  const double uxx = fd(u(cxm, sy0, cz0), u(cxp, sy0, cz0), u0);
-  const double uyy = fd(u(cx0, sym, cz0), u(cx0, syp, cz0), u0);
-  const double uzz = fd(u(cx0, sy0, czm), u(cx0, sy0, czp), u0);
-  return -__dadd_rn(__dadd_rn(uxx, uyy), uzz);
-}
-__device__ __noinline__ double ex4_forcing_lib(double x, double y, double z) { return ex4_forcing_t<false>(x, y, z); }
-
-// Phase A of an element, lane = quadrature point: FEMap::compute_map.  Returns has_affine_map; fills
-// S = sqrt(det J) * (dxidx dxidy dxidz | detadx .. | dzetadx ..), JxW and (when want_xyz, or always on the general
-// branch) the physical point.  X = node coordinates of the element in shared memory.
-template <int NPE, int NQ>
-__device__ __forceinline__ bool geom_phase(const double* X, const double* s_tab, int lane, bool want_xyz, int* flags, double (&S)[9],
-                                           double& JxW, double& x, double& y, double& z) {
-  const double* s_phi = s_tab;
-  const double* s_dxi = s_tab + NPE * NQ;
-  const double* s_qw = s_tab + 4 * NPE * NQ;
-  const bool affine = __all_sync(0xffffffffu, affine_check_lane<NPE>(X, lane));
-  {
-      x = 0; y = 0; z = 0;
-      double xa = 0, ya = 0, za = 0, xb = 0, yb = 0, zb = 0, xc = 0, yc = 0, zc = 0;
-      const int q = lane < NQ ? lane : 0;
-      if (affine) {
-        // compute_affine_map (fe_map.C:1167-1244): the Jacobian at qp 0 only — lane c < 9 sums component c —
-        // and xyz at every qp (:1190-1197)
-        // (sums split three ways: independent FP64 chains instead of one 27-deep dependent chain)
-        double d = 0.;
-        if (lane < 9) {
-          const double* tabd = s_dxi + (lane / 3) * (NPE * NQ);
-          const int cd = lane % 3;
-          double d0 = 0., d1 = 0., d2 = 0.;
-#pragma unroll
-          for (int i = 0; i + 2 < NPE; i += 3) {
-            d0 += tabd[i * NQ] * X[3 * i + cd];
-            d1 += tabd[(i + 1) * NQ] * X[3 * (i + 1) + cd];
-            d2 += tabd[(i + 2) * NQ] * X[3 * (i + 2) + cd];
-          }
-#pragma unroll
-          for (int i = NPE - NPE % 3; i < NPE; ++i) d0 += tabd[i * NQ] * X[3 * i + cd];
-          d = (d0 + d1) + d2;
-        }
-        if (want_xyz) {
-          double x1 = 0., y1 = 0., z1 = 0., x2 = 0., y2 = 0., z2 = 0.;
-#pragma unroll
-          for (int i = 0; i + 2 < NPE; i += 3) {
-            const double p0 = s_phi[i * NQ + q], p1 = s_phi[(i + 1) * NQ + q], p2 = s_phi[(i + 2) * NQ + q];
-            x += p0 * X[3 * i]; y += p0 * X[3 * i + 1]; z += p0 * X[3 * i + 2];
-            x1 += p1 * X[3 * i + 3]; y1 += p1 * X[3 * i + 4]; z1 += p1 * X[3 * i + 5];
-            x2 += p2 * X[3 * i + 6]; y2 += p2 * X[3 * i + 7]; z2 += p2 * X[3 * i + 8];
-          }
-#pragma unroll
-          for (int i = NPE - NPE % 3; i < NPE; ++i) {
-            const double p = s_phi[i * NQ + q];
-            x += p * X[3 * i]; y += p * X[3 * i + 1]; z += p * X[3 * i + 2];
-          }
-          x = (x + x1) + x2; y = (y + y1) + y2; z = (z + z1) + z2;
-        }
-        xa = __shfl_sync(0xffffffffu, d, 0); ya = __shfl_sync(0xffffffffu, d, 1); za = __shfl_sync(0xffffffffu, d, 2);
-        xb = __shfl_sync(0xffffffffu, d, 3); yb = __shfl_sync(0xffffffffu, d, 4); zb = __shfl_sync(0xffffffffu, d, 5);
-        xc = __shfl_sync(0xffffffffu, d, 6); yc = __shfl_sync(0xffffffffu, d, 7); zc = __shfl_sync(0xffffffffu, d, 8);
-      } else {
-        // general branch: compute_single_point_map per qp (fe_map.C:994-1026)
-        const double* s_deta = s_dxi + NPE * NQ;
-        const double* s_dzeta = s_deta + NPE * NQ;
-#pragma unroll 3
-        for (int i = 0; i < NPE; ++i) {
-          const double px = X[3 * i], py = X[3 * i + 1], pz = X[3 * i + 2];
-          const double p = s_phi[i * NQ + q], a = s_dxi[i * NQ + q], b = s_deta[i * NQ + q], c = s_dzeta[i * NQ + q];
-          x += p * px; y += p * py; z += p * pz;
-          xa += a * px; ya += a * py; za += a * pz;
-          xb += b * px; yb += b * py; zb += b * pz;
-          xc += c * px; yc += c * py; zc += c * pz;
-        }
-      }
-      // det J in the order of fe_map.C:1046-1048, inverse rows :1056-1068
-      const double jac = (xa * (yb * zc - zb * yc) + ya * (zb * xc - xb * zc) + za * (xb * yc - yb * xc));
-      const bool bad = !(jac > 0.);
-      if (bad && lane < NQ) atomicAdd(&flags[0], 1);  // check_for_degenerate_map, fe_map.C:467-506
-      JxW = (affine && q != 0) ? jac * s_qw[0] / s_qw[0] * s_qw[q] : jac * s_qw[q];  // fe_map.C:1242 / :1052
-      const double s = bad ? 0. : rsqrt(jac);  // sqrt(jac) / jac
-      S[0] = (yb * zc - zb * yc) * s; S[1] = (zb * xc - xb * zc) * s; S[2] = (xb * yc - yb * xc) * s;
-      S[3] = (za * yc - ya * zc) * s; S[4] = (xa * zc - za * xc) * s; S[5] = (ya * xc - xa * yc) * s;
-      S[6] = (ya * zb - za * yb) * s; S[7] = (za * xb - xa * zb) * s; S[8] = (xa * yb - ya * xb) * s;
-  }
-  return affine;
-}
-
 template <int NPE, int NQ, int WARPS>
-__global__ void __launch_bounds__(WARPS * 32, 1)
+// (the 8-warp variant is held to the 12-warp register budget so that reduction CTAs fit beside it: chunked pipeline)
+__global__ void __launch_bounds__(WARPS == 8 ? 384 : WARPS * 32, 1)
 k_elem_poisson(const double* __restrict__ xyz, const uint32_t* __restrict__ conn, const double* __restrict__ tab,
                int forcing, const double* __restrict__ f_tab, int64_t e0, int64_t e1, double* __restrict__ kf, int* flags) {
   using C = ElemCfg<NPE, NQ>;
@@ -227,18 +30,10 @@ k_elem_poisson(const double* __restrict__ xyz, const uint32_t* __restrict__ conn
   double* s_tab = smem;               // phi | dxi | deta | dzeta | qw, [i][q]: lane = q reads are conflict free
   double* s_tw = smem + C::TAB_SZ;    // [c][row][TS]: sqrt(w_q) * d phi_row / d xi_c (q), zero padded
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-  for (int t = threadIdx.x; t < C::TAB; t += WARPS * 32) s_tab[t] = tab[t];
-  for (int t = threadIdx.x; t < C::TW_SZ; t += WARPS * 32) {
-    const int c = t / (C::NB * 8 * C::TS), row = (t / C::TS) % (C::NB * 8), q = t % C::TS;
-    s_tw[t] = (row < NPE && q < NQ) ? sqrt(tab[4 * NPE * NQ + q]) * tab[(1 + c) * NPE * NQ + row * NQ + q] : 0.;
-  }
-  const double* s_phi = s_tab;
-  const double* s_dxi = s_tab + NPE * NQ;
-  const double* s_qw = s_tab + 4 * NPE * NQ;
+  elem_load_tables<NPE, NQ>(s_tab, s_tw, tab, threadIdx.x, WARPS * 32);
   double* X = s_tw + C::TW_SZ + (size_t)warp * C::WARP_DBL;  // node coordinates of the current element
   double* fw = X + C::X_SZ;                                  // JxW_q * f(x_q)
-  const int g = lane >> 2, t4 = lane & 3;
-  const double* twp = s_tw + g * C::TS + t4;  // + c*NB*8*TS + ib*8*TS + 4*qg
+  const double* twp = s_tw + (lane >> 2) * C::TS + (lane & 3);  // + c*NB*8*TS + ib*8*TS + 4*qg
   __syncthreads();
 
   const int64_t stride = (int64_t)gridDim.x * WARPS;
@@ -263,125 +58,8 @@ k_elem_poisson(const double* __restrict__ xyz, const uint32_t* __restrict__ conn
     }
     __syncwarp();
 
-    // ---- A: reference -> physical map at quadrature point q = lane ---------------------------------------
-    double S[9], JxW, x, y, z;
-    const bool affine = geom_phase<NPE, NQ>(X, s_tab, lane, forcing == FEASM_FORCING_EX4_FD, flags, S, JxW, x, y, z);
-    {
-      double f = 0.;
-      if (forcing == FEASM_FORCING_EX4_FD) {
-        // every lane evaluates (pad lanes repeat qp 0): no divergence; huge coordinates take the library path
-        const bool big = !(fabs(x) + fabs(y) + fabs(z) < 2.e4);
-        f = __any_sync(0xffffffffu, big) ? ex4_forcing_lib(x, y, z) : ex4_forcing_t<true>(x, y, z);
-      } else if (forcing == FEASM_FORCING_TABULATED && lane < NQ) {
-        f = f_tab[e * NQ + lane];
-      }
-      fw[lane] = lane < NQ ? JxW * f : 0.;
-    }
-
-    // ---- B+C: Ke = G G^T; fragments generated in registers -------------------------------------------------
-    double acc[C::NBLK > 0 ? C::NBLK : 1][2];
-    double pr[C::NB][C::REM > 0 ? C::REM : 1];  // leftover rows: partial (over k = t4 mod 4) K[ib*8+g][8*NBF+r]
-#pragma unroll
-    for (int b = 0; b < C::NBLK; ++b) { acc[b][0] = 0.; acc[b][1] = 0.; }
-#pragma unroll
-    for (int ib = 0; ib < C::NB; ++ib)
-#pragma unroll
-      for (int r = 0; r < (C::REM > 0 ? C::REM : 1); ++r) pr[ib][r] = 0.;
-#pragma unroll
-    for (int qg = 0; qg < C::QG; ++qg) {
-      double Sq[9];
-      if (affine) {
-#pragma unroll
-        for (int k = 0; k < 9; ++k) Sq[k] = S[k];
-      } else {
-#pragma unroll
-        for (int k = 0; k < 9; ++k) Sq[k] = __shfl_sync(0xffffffffu, S[k], 4 * qg + t4);
-      }
-      double G[C::NB][3];
-#pragma unroll
-      for (int ib = 0; ib < C::NB; ++ib) {
-        const double a = twp[ib * 8 * C::TS + 4 * qg];
-        const double b = twp[C::NB * 8 * C::TS + ib * 8 * C::TS + 4 * qg];
-        const double c = twp[2 * C::NB * 8 * C::TS + ib * 8 * C::TS + 4 * qg];
-        // h1_fe_transformation.C:150-187: dphi/dx_d = dphi/dxi dxi/dx_d + dphi/deta deta/dx_d + dphi/dzeta dzeta/dx_d
-        G[ib][0] = a * Sq[0] + b * Sq[3] + c * Sq[6];
-        G[ib][1] = a * Sq[1] + b * Sq[4] + c * Sq[7];
-        G[ib][2] = a * Sq[2] + b * Sq[5] + c * Sq[8];
-      }
-#pragma unroll
-      for (int d = 0; d < 3; ++d) {
-        int blk = 0;
-#pragma unroll
-        for (int jb = 0; jb < C::NBF; ++jb)
-#pragma unroll
-          for (int ib = 0; ib <= jb; ++ib) { dmma884(acc[blk][0], acc[blk][1], G[ib][d], G[jb][d]); ++blk; }
-        if (C::REM > 0) {
-#pragma unroll
-          for (int r = 0; r < C::REM; ++r) {
-            const double gr = __shfl_sync(0xffffffffu, G[C::NB - 1][d], 4 * r + t4);
-#pragma unroll
-            for (int ib = 0; ib < C::NB; ++ib) pr[ib][r] += G[ib][d] * gr;
-          }
-        }
-      }
-    }
-    if (C::REM > 0) {
-#pragma unroll
-      for (int ib = 0; ib < C::NB; ++ib)
-#pragma unroll
-        for (int r = 0; r < C::REM; ++r) {
-          pr[ib][r] += __shfl_xor_sync(0xffffffffu, pr[ib][r], 1);
-          pr[ib][r] += __shfl_xor_sync(0xffffffffu, pr[ib][r], 2);
-        }
-    }
-
-    // ---- D: Fe (introduction_ex4.C:536-537) and the stores ----------------------------------------------------
-    double* out = kf + (uint64_t)(e - e0) * (NPE * C::LDR);
-    if (lane < NPE) {
-      double Fe = 0.;
-      if (forcing != FEASM_FORCING_NONE) {
-        double f1 = 0., f2 = 0.;
-#pragma unroll
-        for (int q = 0; q + 2 < NQ; q += 3) {
-          Fe += fw[q] * s_phi[lane * NQ + q];
-          f1 += fw[q + 1] * s_phi[lane * NQ + q + 1];
-          f2 += fw[q + 2] * s_phi[lane * NQ + q + 2];
-        }
-#pragma unroll
-        for (int q = NQ - NQ % 3; q < NQ; ++q) Fe += fw[q] * s_phi[lane * NQ + q];
-        Fe = (Fe + f1) + f2;
-      }
-      out[lane * C::LDR + NPE] = Fe;
-    }
-    {
-      int blk = 0;
-#pragma unroll
-      for (int jb = 0; jb < C::NBF; ++jb)
-#pragma unroll
-        for (int ib = 0; ib <= jb; ++ib, ++blk) {
-          const int i = ib * 8 + g, j = jb * 8 + 2 * t4;
-          *reinterpret_cast<double2*>(out + i * C::LDR + j) = make_double2(acc[blk][0], acc[blk][1]);
-          if (ib != jb) {  // mirror into the lower triangle
-            out[j * C::LDR + i] = acc[blk][0];
-            out[(j + 1) * C::LDR + i] = acc[blk][1];
-          }
-        }
-    }
-    if (C::REM > 0) {
-      constexpr int R0 = 8 * C::NBF;
-#pragma unroll
-      for (int ib = 0; ib < C::NBF; ++ib) {
-        const int i = ib * 8 + g;
-#pragma unroll
-        for (int r = 0; r < C::REM; ++r)
-          if (t4 == r) { out[i * C::LDR + R0 + r] = pr[ib][r]; out[(R0 + r) * C::LDR + i] = pr[ib][r]; }
-      }
-      if (g < C::REM) {
-#pragma unroll
-        for (int r = 0; r < C::REM; ++r)
-          if (t4 == r) out[(R0 + g) * C::LDR + R0 + r] = pr[C::NB - 1][r];
-      }
-    }
+    elem_process<NPE, NQ>(X, fw, s_tab, twp, lane, forcing, f_tab ? f_tab + e * NQ : nullptr, flags,
+                          kf + (uint64_t)(e - e0) * (NPE * C::LDR));
     __syncwarp();
   }
 }
@@ -557,6 +235,7 @@ int feasm_launch_element_kernel(feasm_ctx* ctx, const feasm_params& p, const dou
     if (ctx->elem_type == FEASM_HEX27 && ctx->tab_nq == 27) {
       static const int warps = getenv("FEASM_ELEM_WARPS") ? atoi(getenv("FEASM_ELEM_WARPS")) : 12;  // tuning knob
       if (warps == 16) return launch_poisson<27, 27, 16>(ctx, p, d_f, e0, e1, d_kf);
+      if (warps == 8) return launch_poisson<27, 27, 8>(ctx, p, d_f, e0, e1, d_kf);
       return launch_poisson<27, 27, 12>(ctx, p, d_f, e0, e1, d_kf);
     }
     if (ctx->elem_type == FEASM_HEX8 && ctx->tab_nq == 8) return launch_poisson<8, 8, 16>(ctx, p, d_f, e0, e1, d_kf);
