@@ -31,7 +31,10 @@ void release(T*& p) {
 
 void drop_maps(feasm_ctx* ctx) {
   ctx->prepared = false;
-  release(ctx->d_pos);
+  release(ctx->d_elem_flag);
+  release(ctx->d_con_elems);
+  ctx->n_con_elems = 0;
+  ctx->elem_flag_valid = false;
   release(ctx->d_inc_ptr);
   release(ctx->d_inc);
   release(ctx->d_kf);
@@ -212,7 +215,7 @@ int feasm_set_constraints(feasm_ctx* ctx, int64_t n, const uint32_t* rows, const
   }
   // the constrained SET is baked into the position map's flag bits; new values alone leave it valid
   if (flag != ctx->h_con_flag) {
-    ctx->pos_flags_valid = false;
+    ctx->elem_flag_valid = false;
     FEASM_CUDA(ctx, cudaMemcpyAsync(ctx->d_con_flag, flag.data(), flag.size(), cudaMemcpyHostToDevice, ctx->stream));
   }
   FEASM_CUDA(ctx, cudaMemcpyAsync(ctx->d_con_val, val.data(), sizeof(double) * val.size(), cudaMemcpyHostToDevice, ctx->stream));
@@ -238,7 +241,6 @@ int feasm_set_pattern(feasm_ctx* ctx, const uint64_t* row_ptr, const uint32_t* c
       if (col_idx[k] <= col_idx[k - 1]) return feasm_fail(ctx, FEASM_ERR_ARG, "columns of a row must be strictly ascending");
   }
   ctx->prepared = false;
-  release(ctx->d_pos);
   ctx->nnz = row_ptr[ctx->n_rows];
   int rc = upload(ctx, &ctx->d_row_ptr, row_ptr, (size_t)ctx->n_rows + 1);
   if (rc) return rc;
@@ -254,7 +256,6 @@ int feasm_build_pattern(feasm_ctx* ctx) {
   if (!ctx || !ctx->d_elem_dofs) return feasm_fail(ctx, FEASM_ERR_STATE, "set_dofs first");
   FEASM_CUDA(ctx, cudaSetDevice(ctx->device));
   ctx->prepared = false;
-  release(ctx->d_pos);
   int rc = feasm_device_build_pattern(ctx);
   if (rc) return rc;
   return alloc_values(ctx);
@@ -281,8 +282,6 @@ int feasm_prepare(feasm_ctx* ctx) {
   if (rc) return rc;
   rc = feasm_build_batch_need(ctx);
   if (rc) return rc;
-  release(ctx->d_kf);
-  FEASM_CUDA(ctx, cudaMalloc(&ctx->d_kf, sizeof(double) * ((size_t)ctx->n_elem * ctx->nd * feasm_ldr(ctx->nd) + 1)));
   ctx->prepared = true;
   return FEASM_OK;
 }
@@ -302,8 +301,9 @@ int feasm_assemble(feasm_ctx* ctx, const feasm_params* params) {
   FEASM_CUDA(ctx, cudaMemsetAsync(ctx->d_flags, 0, 2 * sizeof(int), ctx->stream));
   FEASM_CUDA(ctx, cudaEventRecord(ctx->ev[0], ctx->stream));
   int launches = 2;
-  if (!ctx->pos_flags_valid) {
-    rc = feasm_launch_pos_flags(ctx);
+  const int rs = feasm_recb(ctx->nd, ctx->pos_bytes) / 8;  // doubles per element record
+  if (!ctx->elem_flag_valid) {
+    rc = feasm_launch_elem_flags(ctx);
     if (rc) return rc;
     ++launches;
   }
@@ -333,7 +333,7 @@ int feasm_assemble(feasm_ctx* ctx, const feasm_params* params) {
     launches = launches - 2;
     for (int c = 0; c < n_chunks; ++c) {
       const int64_t e0 = ctx->n_elem * c / n_chunks, e1 = ctx->n_elem * (c + 1) / n_chunks;
-      rc = feasm_launch_element_kernel(ctx, *params, d_f, e0, e1, ctx->d_kf + (size_t)e0 * ctx->nd * feasm_ldr(ctx->nd));
+      rc = feasm_launch_element_kernel(ctx, *params, d_f, e0, e1, ctx->d_kf + (size_t)e0 * ctx->nd * rs, rs, params->constrain);
       if (rc) return rc;
       ++launches;
       FEASM_CUDA(ctx, cudaEventRecord(ctx->chunk_ev[c], ctx->stream));
@@ -344,7 +344,7 @@ int feasm_assemble(feasm_ctx* ctx, const feasm_params* params) {
       }
       if (row1 > row0) {
         FEASM_CUDA(ctx, cudaStreamWaitEvent(ctx->stream2, ctx->chunk_ev[c], 0));
-        rc = feasm_launch_row_reduce(ctx, params->constrain, nullptr, row1, ctx->stream2, row0);
+        rc = feasm_launch_row_reduce(ctx, nullptr, row1, ctx->stream2, row0);
         if (rc) return rc;
         ++launches;
         row0 = row1;
@@ -354,10 +354,11 @@ int feasm_assemble(feasm_ctx* ctx, const feasm_params* params) {
     FEASM_CUDA(ctx, cudaEventRecord(ctx->chunk_ev[n_chunks], ctx->stream2));
     FEASM_CUDA(ctx, cudaStreamWaitEvent(ctx->stream, ctx->chunk_ev[n_chunks], 0));
   } else {
-    rc = feasm_launch_element_kernel(ctx, *params, d_f, 0, ctx->n_elem, ctx->d_kf);
+    rc = feasm_launch_element_kernel(ctx, *params, d_f, 0, ctx->n_elem, ctx->d_kf, rs, params->constrain);
     if (rc) return rc;
     FEASM_CUDA(ctx, cudaEventRecord(ctx->ev[1], ctx->stream));
-    rc = feasm_launch_row_reduce(ctx, params->constrain, nullptr, ctx->n_rows, ctx->stream);
+    static const bool skip_rr = getenv("FEASM_SKIP_RR") != nullptr;  // timing experiments only
+    rc = skip_rr ? 0 : feasm_launch_row_reduce(ctx, nullptr, ctx->n_rows, ctx->stream);
     if (rc) return rc;
   }
   FEASM_CUDA(ctx, cudaEventRecord(ctx->ev[2], ctx->stream));
@@ -394,11 +395,14 @@ int feasm_element_matrices(feasm_ctx* ctx, const feasm_params* params, int64_t e
   rc = resolve_forcing(ctx, *params, ctx->tab_nq, &d_f);
   if (rc) return rc;
   const size_t ne = (size_t)(e1 - e0), nd = ctx->nd, ldr = feasm_ldr(ctx->nd);
-  double* d_kf = nullptr;
+  if (constrained && ctx->n_con > 0 && !ctx->elem_flag_valid) {
+    rc = feasm_launch_elem_flags(ctx);
+    if (rc) return rc;
+  }
+  double* d_kf = nullptr;  // scratch records without a position row (record stride = ldr doubles)
   FEASM_CUDA(ctx, cudaMalloc(&d_kf, sizeof(double) * ne * nd * ldr));
   FEASM_CUDA(ctx, cudaMemsetAsync(ctx->d_flags, 0, 2 * sizeof(int), ctx->stream));
-  rc = feasm_launch_element_kernel(ctx, *params, d_f, e0, e1, d_kf);
-  if (!rc && constrained) rc = feasm_launch_constrain_elements(ctx, params->constrain, e0, e1, d_kf);
+  rc = feasm_launch_element_kernel(ctx, *params, d_f, e0, e1, d_kf, (int)ldr, constrained ? params->constrain : -1);
   if (!rc) {
     // KF rows are (Ke row | Fe | pad): strip the padding on the way out
     if (Ke) cudaMemcpy2DAsync(Ke, sizeof(double) * nd, d_kf, sizeof(double) * ldr, sizeof(double) * nd, ne * nd, cudaMemcpyDeviceToHost, ctx->stream);

@@ -5,6 +5,15 @@
 #include "feasm_internal.h"
 
 namespace {
+// What the element kernels need to apply Dirichlet constraints in place (elem_flag == nullptr: none).
+struct ElemConArgs {
+  const uint8_t* elem_flag;   // [n_elem] element touches a constrained dof
+  const uint32_t* elem_dofs;  // [n_elem][nd]
+  const uint8_t* con_flag;    // [n_rows]
+  const double* con_val;      // [n_rows]
+  int mode;
+};
+
 
 __device__ __forceinline__ void dmma884(double& c0, double& c1, double a, double b) {
   asm volatile("mma.sync.aligned.m8n8k4.row.col.f64.f64.f64.f64 {%0,%1}, {%2}, {%3}, {%0,%1};\n"
@@ -204,10 +213,12 @@ __device__ __forceinline__ bool geom_phase(const double* X, const double* s_tab,
 }
 
 // One element by one warp: phases A-D of the header comment.  X holds the element's node coordinates, fw is a 32-double
-// scratch, twp = s_tw + (lane>>2)*TS + (lane&3); `out` is the element's KF block [NPE][LDR].
+// scratch, twp = s_tw + (lane>>2)*TS + (lane&3); `out` is the element's block of NPE records, rs doubles apart (row a =
+// Ke(a,:) then Fe(a) at column NPE).
 template <int NPE, int NQ>
 __device__ __forceinline__ void elem_process(const double* X, double* fw, const double* s_tab, const double* twp, int lane,
-                                             int forcing, const double* __restrict__ f_tab_e, int* flags, double* __restrict__ out) {
+                                             int forcing, const double* __restrict__ f_tab_e, int* flags, double* __restrict__ out,
+                                             const int rs) {
   using C = ElemCfg<NPE, NQ>;
   const double* s_phi = s_tab;
   const int g = lane >> 2, t4 = lane & 3;
@@ -298,7 +309,7 @@ __device__ __forceinline__ void elem_process(const double* X, double* fw, const 
       for (int q = NQ - NQ % 3; q < NQ; ++q) Fe += fw[q] * s_phi[lane * NQ + q];
       Fe = (Fe + f1) + f2;
     }
-    out[lane * C::LDR + NPE] = Fe;
+    out[lane * rs + NPE] = Fe;
   }
   {
     int blk = 0;
@@ -307,10 +318,10 @@ __device__ __forceinline__ void elem_process(const double* X, double* fw, const 
 #pragma unroll
       for (int ib = 0; ib <= jb; ++ib, ++blk) {
         const int i = ib * 8 + g, j = jb * 8 + 2 * t4;
-        *reinterpret_cast<double2*>(out + i * C::LDR + j) = make_double2(acc[blk][0], acc[blk][1]);
+        *reinterpret_cast<double2*>(out + i * rs + j) = make_double2(acc[blk][0], acc[blk][1]);
         if (ib != jb) {  // mirror into the lower triangle
-          out[j * C::LDR + i] = acc[blk][0];
-          out[(j + 1) * C::LDR + i] = acc[blk][1];
+          out[j * rs + i] = acc[blk][0];
+          out[(j + 1) * rs + i] = acc[blk][1];
         }
       }
   }
@@ -321,12 +332,12 @@ __device__ __forceinline__ void elem_process(const double* X, double* fw, const 
       const int i = ib * 8 + g;
 #pragma unroll
       for (int r = 0; r < C::REM; ++r)
-        if (t4 == r) { out[i * C::LDR + R0 + r] = pr[ib][r]; out[(R0 + r) * C::LDR + i] = pr[ib][r]; }
+        if (t4 == r) { out[i * rs + R0 + r] = pr[ib][r]; out[(R0 + r) * rs + i] = pr[ib][r]; }
     }
     if (g < C::REM) {
 #pragma unroll
       for (int r = 0; r < C::REM; ++r)
-        if (t4 == r) out[(R0 + g) * C::LDR + R0 + r] = pr[C::NB - 1][r];
+        if (t4 == r) out[(R0 + g) * rs + R0 + r] = pr[C::NB - 1][r];
     }
   }
 }
@@ -342,5 +353,49 @@ __device__ __forceinline__ void elem_load_tables(double* s_tab, double* s_tw, co
     s_tw[t] = (row < NPE && q < NQ) ? sqrt(tab[4 * NPE * NQ + q]) * tab[(1 + c) * NPE * NQ + row * NQ + q] : 0.;
   }
 }
+// Dirichlet constraints at element level, in place on the element's records right after they were written (called by
+// the whole warp for the few elements that touch a constrained dof).  This is
+// DofMap::heterogeneously_constrain_element_matrix_and_vector (dof_map_constraints.C:2518-2614) /
+// constrain_element_matrix_and_vector (:2034-2093) for C = diag(0 on constrained dofs, 1 else), H = g:
+//   unconstrained row i:  F(i) -= sum_{j constrained} K(i,j) g_j (heterogeneous only), K(i,j) = 0
+//   constrained row i:    K(i,:) = e_i, F(i) = g_i (heterogeneous) or 0
+__device__ __noinline__ void constrain_element(double* K, const int rs, const int nd, const uint32_t* __restrict__ dofs,
+                                               const uint8_t* __restrict__ con_flag, const double* __restrict__ con_val,
+                                               const int mode, const int lane) {
+  constexpr unsigned FULL = 0xffffffffu;
+  __syncwarp();  // the rows were written by other lanes
+  const bool hetero = mode == FEASM_CONSTRAIN_HETEROGENEOUS;
+  for (int j0 = 0; j0 < nd; j0 += 32) {  // constrained columns j0..j0+31
+    const int jm = j0 + lane;
+    uint32_t dj = 0; int cj = 0; double gj = 0.;
+    if (jm < nd) { dj = dofs[jm]; cj = con_flag[dj]; if (cj && hetero) gj = con_val[dj]; }
+    uint32_t mask = __ballot_sync(FULL, cj);
+    while (mask) {
+      const int jl = __ffs(mask) - 1, j = j0 + jl;
+      mask &= mask - 1;
+      const double g = __shfl_sync(FULL, gj, jl);
+      for (int i = lane; i < nd; i += 32) {  // column j of every row (row j itself is overwritten below)
+        const double kij = K[i * rs + j];
+        K[i * rs + j] = 0.;
+        if (hetero) K[i * rs + nd] -= kij * g;
+      }
+    }
+  }
+  __syncwarp();
+  for (int i0 = 0; i0 < nd; i0 += 32) {  // constrained rows
+    const int im = i0 + lane;
+    uint32_t di = 0; int ci = 0; double gi = 0.;
+    if (im < nd) { di = dofs[im]; ci = con_flag[di]; if (ci && hetero) gi = con_val[di]; }
+    uint32_t mask = __ballot_sync(FULL, ci);
+    while (mask) {
+      const int il = __ffs(mask) - 1, i = i0 + il;
+      mask &= mask - 1;
+      const double g = __shfl_sync(FULL, gi, il);
+      for (int t = lane; t <= nd; t += 32) K[i * rs + t] = t == i ? 1. : (t == nd ? g : 0.);
+    }
+  }
+  __syncwarp();
+}
 }  // namespace
+
 #endif

@@ -20,12 +20,14 @@
 #include "feasm_elem_dev.cuh"
 
 namespace {
-template <int NPE, int NQ, int WARPS>
+template <int NPE, int NQ, int WARPS, int RS>
 // (the 8-warp variant is held to the 12-warp register budget so that reduction CTAs fit beside it: chunked pipeline)
 __global__ void __launch_bounds__(WARPS == 8 ? 384 : WARPS * 32, 1)
 k_elem_poisson(const double* __restrict__ xyz, const uint32_t* __restrict__ conn, const double* __restrict__ tab,
-               int forcing, const double* __restrict__ f_tab, int64_t e0, int64_t e1, double* __restrict__ kf, int* flags) {
+               int forcing, const double* __restrict__ f_tab, int64_t e0, int64_t e1, double* __restrict__ kf, int rs_rt,
+               int* flags) {
   using C = ElemCfg<NPE, NQ>;
+  const int rs = RS ? RS : rs_rt;  // record stride in doubles: a compile-time constant for the common layout
   extern __shared__ double smem[];
   double* s_tab = smem;               // phi | dxi | deta | dzeta | qw, [i][q]: lane = q reads are conflict free
   double* s_tw = smem + C::TAB_SZ;    // [c][row][TS]: sqrt(w_q) * d phi_row / d xi_c (q), zero padded
@@ -58,23 +60,23 @@ k_elem_poisson(const double* __restrict__ xyz, const uint32_t* __restrict__ conn
     }
     __syncwarp();
 
-    elem_process<NPE, NQ>(X, fw, s_tab, twp, lane, forcing, f_tab ? f_tab + e * NQ : nullptr, flags,
-                          kf + (uint64_t)(e - e0) * (NPE * C::LDR));
+    double* out = kf + (uint64_t)(e - e0) * (NPE * rs);
+    elem_process<NPE, NQ>(X, fw, s_tab, twp, lane, forcing, f_tab ? f_tab + e * NQ : nullptr, flags, out, rs);
     __syncwarp();
   }
 }
 
-template <int NPE, int NQ, int WARPS>
-int launch_poisson(feasm_ctx* ctx, const feasm_params& p, const double* d_f, int64_t e0, int64_t e1, double* d_kf) {
+template <int NPE, int NQ, int WARPS, int RS = 0>
+int launch_poisson(feasm_ctx* ctx, const feasm_params& p, const double* d_f, int64_t e0, int64_t e1, double* d_kf, int rs) {
   using C = ElemCfg<NPE, NQ>;
   const size_t smem = sizeof(double) * (size_t)C::SMEM_DBL(WARPS);
-  auto kern = k_elem_poisson<NPE, NQ, WARPS>;
+  auto kern = k_elem_poisson<NPE, NQ, WARPS, RS>;
   FEASM_CUDA(ctx, cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
   int64_t blocks = (e1 - e0 + WARPS - 1) / WARPS;
   if (blocks > ctx->sm_count) blocks = ctx->sm_count;
   if (blocks < 1) blocks = 1;
   kern<<<(unsigned)blocks, WARPS * 32, smem, ctx->stream>>>(ctx->d_xyz, ctx->d_conn, ctx->d_tab, p.forcing, d_f, e0, e1, d_kf,
-                                                           ctx->d_flags);
+                                                           rs, ctx->d_flags);
   FEASM_CUDA(ctx, cudaGetLastError());
   return FEASM_OK;
 }
@@ -92,10 +94,12 @@ int launch_poisson(feasm_ctx* ctx, const feasm_params& p, const double* d_f, int
 template <int NPE, int NQ, int WARPS>
 __global__ void __launch_bounds__(WARPS * 32, 1)
 k_elem_elasticity(const double* __restrict__ xyz, const uint32_t* __restrict__ conn, const double* __restrict__ tab, double lam1,
-                  double lam2, double f0, double f1, double f2, int64_t e0, int64_t e1, double* __restrict__ kf, int* flags) {
+                  double lam2, double f0, double f1, double f2, int64_t e0, int64_t e1, double* __restrict__ kf, int rs,
+                  int* flags) {
   using C = ElemCfg<NPE, NQ>;
   constexpr int NBP = (NPE + 7) / 8;   // 8-row blocks, padded (all go through DMMA here)
-  constexpr int ND = 3 * NPE, LDR = feasm_ldr(ND);
+  constexpr int ND = 3 * NPE;
+  const int LDR = rs;  // record stride in doubles
   constexpr int TLD = NPE | 1;          // odd tile stride
   constexpr int TILE = ((NPE * TLD + 1) & ~1);
   extern __shared__ double smem[];
@@ -207,7 +211,7 @@ k_elem_elasticity(const double* __restrict__ xyz, const uint32_t* __restrict__ c
 }
 
 template <int NPE, int NQ, int WARPS>
-int launch_elasticity(feasm_ctx* ctx, const feasm_params& p, int64_t e0, int64_t e1, double* d_kf) {
+int launch_elasticity(feasm_ctx* ctx, const feasm_params& p, int64_t e0, int64_t e1, double* d_kf, int rs) {
   using C = ElemCfg<NPE, NQ>;
   constexpr int NBP = (NPE + 7) / 8, TLD = NPE | 1, TILE = ((NPE * TLD + 1) & ~1);
   const size_t smem = sizeof(double) * (size_t)(C::TAB_SZ + 3 * NBP * 8 * C::TS + WARPS * (C::X_SZ + 32 + 3 * TILE));
@@ -222,33 +226,82 @@ int launch_elasticity(feasm_ctx* ctx, const feasm_params& p, int64_t e0, int64_t
   if (blocks > ctx->sm_count) blocks = ctx->sm_count;
   if (blocks < 1) blocks = 1;
   kern<<<(unsigned)blocks, WARPS * 32, smem, ctx->stream>>>(ctx->d_xyz, ctx->d_conn, ctx->d_tab, lam1, lam2, f[0], f[1], f[2], e0, e1,
-                                                           d_kf, ctx->d_flags);
+                                                           d_kf, rs, ctx->d_flags);
   FEASM_CUDA(ctx, cudaGetLastError());
   return FEASM_OK;
 }
 
 }  // namespace
 
-int feasm_launch_element_kernel(feasm_ctx* ctx, const feasm_params& p, const double* d_f, int64_t e0, int64_t e1,
-                                double* d_kf) {
+// One warp per element of the constrained-element list: the element's records are staged through shared memory (whole
+// sectors in, whole sectors out — the constraint pass itself walks columns, which would be one sector per entry in
+// global memory), constrained there, and written back.
+__global__ void k_constrain_list(const uint32_t* __restrict__ list, int n_list, int64_t e0, int64_t e1, double* __restrict__ kf, int rs,
+                                 int nd, ElemConArgs con) {
+  extern __shared__ __align__(16) double s_k[];
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int w = blockIdx.x * (blockDim.x >> 5) + warp;
+  if (w >= n_list) return;
+  const int64_t e = list[w];
+  if (e < e0 || e >= e1) return;
+  const int ldr = feasm_ldr(nd), h = ldr >> 1;
+  double* S = s_k + (size_t)warp * nd * ldr;
+  double* K = kf + (uint64_t)(e - e0) * nd * rs;
+  for (int t = lane; t < nd * h; t += 32) {
+    const int row = t / h, c = t % h;
+    *reinterpret_cast<double2*>(S + row * ldr + 2 * c) = *reinterpret_cast<const double2*>(K + (size_t)row * rs + 2 * c);
+  }
+  constrain_element(S, ldr, nd, con.elem_dofs + (uint64_t)e * nd, con.con_flag, con.con_val, con.mode, lane);
+  for (int t = lane; t < nd * h; t += 32) {
+    const int row = t / h, c = t % h;
+    *reinterpret_cast<double2*>(K + (size_t)row * rs + 2 * c) = *reinterpret_cast<const double2*>(S + row * ldr + 2 * c);
+  }
+}
+
+static int launch_element_kernel(feasm_ctx* ctx, const feasm_params& p, const double* d_f, int64_t e0, int64_t e1, double* d_kf, int rs) {
   if (p.problem == FEASM_POISSON) {
     if (ctx->elem_type == FEASM_HEX27 && ctx->tab_nq == 27) {
       static const int warps = getenv("FEASM_ELEM_WARPS") ? atoi(getenv("FEASM_ELEM_WARPS")) : 12;  // tuning knob
-      if (warps == 16) return launch_poisson<27, 27, 16>(ctx, p, d_f, e0, e1, d_kf);
-      if (warps == 8) return launch_poisson<27, 27, 8>(ctx, p, d_f, e0, e1, d_kf);
-      return launch_poisson<27, 27, 12>(ctx, p, d_f, e0, e1, d_kf);
+      if (warps == 16) return launch_poisson<27, 27, 16>(ctx, p, d_f, e0, e1, d_kf, rs);
+      if (warps == 8) return launch_poisson<27, 27, 8>(ctx, p, d_f, e0, e1, d_kf, rs);
+      if (rs == 32) return launch_poisson<27, 27, 12, 32>(ctx, p, d_f, e0, e1, d_kf, rs);  // 256 B records (uint8 positions)
+      return launch_poisson<27, 27, 12>(ctx, p, d_f, e0, e1, d_kf, rs);
     }
-    if (ctx->elem_type == FEASM_HEX8 && ctx->tab_nq == 8) return launch_poisson<8, 8, 16>(ctx, p, d_f, e0, e1, d_kf);
-    if (ctx->elem_type == FEASM_HEX8 && ctx->tab_nq == 27) return launch_poisson<8, 27, 16>(ctx, p, d_f, e0, e1, d_kf);
-    if (ctx->elem_type == FEASM_TET10 && ctx->tab_nq == 14) return launch_poisson<10, 14, 16>(ctx, p, d_f, e0, e1, d_kf);
+    if (ctx->elem_type == FEASM_HEX8 && ctx->tab_nq == 8 && rs == 16) return launch_poisson<8, 8, 16, 16>(ctx, p, d_f, e0, e1, d_kf, rs);
+    if (ctx->elem_type == FEASM_HEX8 && ctx->tab_nq == 8) return launch_poisson<8, 8, 16>(ctx, p, d_f, e0, e1, d_kf, rs);
+    if (ctx->elem_type == FEASM_HEX8 && ctx->tab_nq == 27) return launch_poisson<8, 27, 16>(ctx, p, d_f, e0, e1, d_kf, rs);
+    if (ctx->elem_type == FEASM_TET10 && ctx->tab_nq == 14 && rs == 16) return launch_poisson<10, 14, 16, 16>(ctx, p, d_f, e0, e1, d_kf, rs);
+    if (ctx->elem_type == FEASM_TET10 && ctx->tab_nq == 14) return launch_poisson<10, 14, 16>(ctx, p, d_f, e0, e1, d_kf, rs);
     return feasm_fail(ctx, FEASM_ERR_ARG, "no Poisson kernel for this element type / quadrature order");
   }
   if (p.problem == FEASM_ELASTICITY) {
     if (ctx->n_vars != 3) return feasm_fail(ctx, FEASM_ERR_ARG, "elasticity needs 3 variables per node");
-    if (ctx->elem_type == FEASM_HEX27 && ctx->tab_nq == 27) return launch_elasticity<27, 27, 8>(ctx, p, e0, e1, d_kf);
-    if (ctx->elem_type == FEASM_HEX8 && ctx->tab_nq == 8) return launch_elasticity<8, 8, 16>(ctx, p, e0, e1, d_kf);
-    if (ctx->elem_type == FEASM_TET10 && ctx->tab_nq == 14) return launch_elasticity<10, 14, 16>(ctx, p, e0, e1, d_kf);
+    if (ctx->elem_type == FEASM_HEX27 && ctx->tab_nq == 27) return launch_elasticity<27, 27, 8>(ctx, p, e0, e1, d_kf, rs);
+    if (ctx->elem_type == FEASM_HEX8 && ctx->tab_nq == 8) return launch_elasticity<8, 8, 16>(ctx, p, e0, e1, d_kf, rs);
+    if (ctx->elem_type == FEASM_TET10 && ctx->tab_nq == 14) return launch_elasticity<10, 14, 16>(ctx, p, e0, e1, d_kf, rs);
     return feasm_fail(ctx, FEASM_ERR_ARG, "no elasticity kernel for this element type / quadrature order");
   }
   return feasm_fail(ctx, FEASM_ERR_ARG, "problem not implemented");
+}
+
+int feasm_launch_element_kernel(feasm_ctx* ctx, const feasm_params& p, const double* d_f, int64_t e0, int64_t e1,
+                                double* d_kf, int rs, int constrain_mode) {
+  static const int rs_env = getenv("FEASM_ELEM_RS") ? atoi(getenv("FEASM_ELEM_RS")) : 0;  // timing experiment only (wrong results)
+  int rc = launch_element_kernel(ctx, p, d_f, e0, e1, d_kf, rs_env ? rs_env : rs);
+  if (rc) return rc;
+  // Dirichlet constraints on the few elements that touch a constrained dof, as the reference applies them to Ke/Fe
+  // before add_matrix (constrain_mode < 0: leave Ke/Fe unconstrained)
+  if (constrain_mode >= 0 && ctx->n_con_elems > 0) {
+    const ElemConArgs con{ctx->d_elem_flag, ctx->d_elem_dofs, ctx->d_con_flag, ctx->d_con_val, constrain_mode};
+    const size_t per_warp = sizeof(double) * ctx->nd * feasm_ldr(ctx->nd);
+    int warps = (int)(32768 / per_warp);
+    warps = warps < 1 ? 1 : (warps > 8 ? 8 : warps);
+    const size_t smem = warps * per_warp;
+    if (smem > ctx->smem_optin) return feasm_fail(ctx, FEASM_ERR_NOMEM, "element too large for the constraint pass");
+    FEASM_CUDA(ctx, cudaFuncSetAttribute(k_constrain_list, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    k_constrain_list<<<(unsigned)((ctx->n_con_elems + warps - 1) / warps), warps * 32, smem, ctx->stream>>>(
+        ctx->d_con_elems, (int)ctx->n_con_elems, e0, e1, d_kf, rs, ctx->nd, con);
+    FEASM_CUDA(ctx, cudaGetLastError());
+  }
+  return FEASM_OK;
 }

@@ -31,10 +31,8 @@ template <int NPE, int NQ, typename PosT, int EW, int RW, int ER, int RR>
 __global__ void __launch_bounds__((EW + RW) * 32, 1)
 k_fused_poisson(int diag, const double* __restrict__ xyz, const uint32_t* __restrict__ conn, const double* __restrict__ tab, int forcing,
                 const double* __restrict__ f_tab, int64_t n_elem, double* __restrict__ kf, int* flags,
-                const uint64_t* __restrict__ row_ptr, const uint64_t* __restrict__ inc_ptr, const uint32_t* __restrict__ inc,
-                const unsigned char* __restrict__ pos, int64_t n_rows, int cap, const uint8_t* __restrict__ con_flag,
-                const double* __restrict__ con_val, const uint32_t* __restrict__ elem_dofs, int mode,
-                double* __restrict__ values, double* __restrict__ rhs, const uint32_t* __restrict__ batch_need,
+                int rs, ElemConArgs con, const uint64_t* __restrict__ row_ptr, const uint64_t* __restrict__ inc_ptr,
+                const uint32_t* __restrict__ inc, int64_t n_rows, int cap, int fe_cell, double* __restrict__ values, double* __restrict__ rhs, const uint32_t* __restrict__ batch_need,
                 uint32_t* done /* [n_waves] */, uint32_t* ticket) {
   using C = ElemCfg<NPE, NQ>;
   extern __shared__ __align__(16) double smem[];
@@ -71,7 +69,12 @@ k_fused_poisson(int diag, const double* __restrict__ xyz, const uint32_t* __rest
       }
       __syncwarp();
       if (diag != 2)
-        elem_process<NPE, NQ>(X, fw, s_tab, twp, lane, forcing, f_tab ? f_tab + e * NQ : nullptr, flags, kf + (uint64_t)e * (NPE * C::LDR));
+      {
+        double* out = kf + (uint64_t)e * (NPE * rs);
+        elem_process<NPE, NQ>(X, fw, s_tab, twp, lane, forcing, f_tab ? f_tab + e * NQ : nullptr, flags, out, rs);
+        if (con.elem_flag && con.elem_flag[e])
+          constrain_element(out, rs, NPE, con.elem_dofs + (uint64_t)e * NPE, con.con_flag, con.con_val, con.mode, lane);
+      }
       __threadfence();  // every lane: its KF stores are visible device-wide before the wave counter moves
       __syncwarp();
       if (lane == 0) atomicAdd(&done[k], 1u);
@@ -80,14 +83,18 @@ k_fused_poisson(int diag, const double* __restrict__ xyz, const uint32_t* __rest
     asm volatile("setmaxnreg.dec.sync.aligned.u32 %0;\n" ::"n"(RR));
     if (diag == 1) return;
     // ---- reduction role --------------------------------------------------------------------------------------------
-    constexpr int slotb = feasm_ldr(NPE) * 8 + feasm_pld(NPE, (int)sizeof(PosT)) * (int)sizeof(PosT);
+    constexpr int slotb = feasm_recb(NPE, (int)sizeof(PosT));
     constexpr int G = FUSED_RR_G, LCAP = 256;
-    const uint32_t warp_bytes = (uint32_t)(RR_NG * G * slotb + cap * 8 + LCAP * 4);
+    const uint32_t warp_bytes = (uint32_t)(RR_NG * G * slotb + cap * 8 + LCAP * 4 + 8 * RR_NG);
     const uint32_t rr0 = (uint32_t)__cvta_generic_to_shared(smem) + (uint32_t)((C::TAB_SZ + C::TW_SZ + EW * C::WARP_DBL) * 8);
     const uint32_t ring_a = rr0 + (warp - EW) * warp_bytes;
     const uint32_t img_a = ring_a + RR_NG * G * slotb;
     const uint32_t list_a = img_a + cap * 8;
+    const uint32_t bar_a = list_a + LCAP * 4;
+    uint32_t phase = 0;
     for (int t = lane; t < cap; t += 32) sts_f64(img_a + 8 * t, 0.);
+    if (lane < RR_NG) mbar_init(bar_a + 8 * lane, 1);
+    mbar_init_fence();
     __syncwarp();
     const int64_t n_batches = (n_rows + 31) / 32;
     const int64_t n_waves = (n_elem + W - 1) / W;
@@ -111,8 +118,8 @@ k_fused_poisson(int diag, const double* __restrict__ xyz, const uint32_t* __rest
       (void)n_waves;
       const int64_t base = (int64_t)b * 32;
       const int nrows = (int)(n_rows - base < 32 ? n_rows - base : 32);
-      rr_process_batch<PosT, NPE>(base, nrows, lane, ring_a, img_a, list_a, G, NPE, row_ptr, inc_ptr, inc, pos,
-                                  reinterpret_cast<const unsigned char*>(kf), nullptr, con_flag, con_val, elem_dofs, mode, values, rhs);
+      rr_process_batch<PosT, NPE, true>(base, nrows, lane, ring_a, img_a, list_a, G, NPE, fe_cell, row_ptr, inc_ptr, inc,
+                                        reinterpret_cast<const unsigned char*>(kf), nullptr, values, rhs, bar_a, phase);
     }
   }
 }
@@ -121,10 +128,10 @@ template <int NPE, int NQ, typename PosT, int EW, int RW, int ER, int RR>
 int launch_fused(feasm_ctx* ctx, const feasm_params& p, const double* d_f) {
   using C = ElemCfg<NPE, NQ>;
   static_assert(EW % 4 == 0 && RW % 4 == 0, "setmaxnreg works on whole warpgroups");
-  constexpr int slotb = feasm_ldr(NPE) * 8 + feasm_pld(NPE, (int)sizeof(PosT)) * (int)sizeof(PosT);
-  int cap = ((int)ctx->max_row_len + 1) & ~1;
+  constexpr int slotb = feasm_recb(NPE, (int)sizeof(PosT));
+  int cap = ((int)ctx->max_row_len + 2) & ~1, fe_cell = (int)ctx->max_row_len;
   const size_t smem = sizeof(double) * (size_t)(C::TAB_SZ + C::TW_SZ + EW * C::WARP_DBL) +
-                      (size_t)RW * (RR_NG * FUSED_RR_G * slotb + cap * 8 + 256 * 4);
+                      (size_t)RW * (RR_NG * FUSED_RR_G * slotb + cap * 8 + 256 * 4 + 8 * RR_NG);
   if (smem > ctx->smem_optin || ctx->max_inc * 32u > 256u) return 1;  // not eligible: caller falls back to two kernels
   auto kern = k_fused_poisson<NPE, NQ, PosT, EW, RW, ER, RR>;
   static const int diag_env = getenv("FEASM_FUSED_DIAG") ? atoi(getenv("FEASM_FUSED_DIAG")) : 0;
@@ -141,13 +148,13 @@ int launch_fused(feasm_ctx* ctx, const feasm_params& p, const double* d_f) {
   FEASM_CUDA(ctx, cudaMemsetAsync(ctx->d_sync, 0, sizeof(uint32_t) * (n_waves + 1), ctx->stream));
   const double* xyz = ctx->d_xyz; const uint32_t* conn = ctx->d_conn; const double* tab = ctx->d_tab;
   int forcing = p.forcing; int64_t n_elem = ctx->n_elem; double* kf = ctx->d_kf; int* flags = ctx->d_flags;
+  int rs = slotb / 8;
+  ElemConArgs con{ctx->n_con > 0 ? ctx->d_elem_flag : nullptr, ctx->d_elem_dofs, ctx->d_con_flag, ctx->d_con_val, p.constrain};
   const uint64_t* row_ptr = ctx->d_row_ptr; const uint64_t* inc_ptr = ctx->d_inc_ptr; const uint32_t* inc = ctx->d_inc;
-  const unsigned char* pos = (const unsigned char*)ctx->d_pos; int64_t n_rows = ctx->n_rows;
-  const uint8_t* con_flag = ctx->d_con_flag; const double* con_val = ctx->d_con_val; const uint32_t* elem_dofs = ctx->d_elem_dofs;
-  int mode = p.constrain; double* values = ctx->d_values; double* rhs = ctx->d_rhs; const uint32_t* need = ctx->d_batch_need;
+  int64_t n_rows = ctx->n_rows; double* values = ctx->d_values; double* rhs = ctx->d_rhs; const uint32_t* need = ctx->d_batch_need;
   uint32_t* done = ctx->d_sync + 1; uint32_t* ticket = ctx->d_sync;
-  void* args[] = {&diag, &xyz, &conn, &tab, &forcing, &d_f, &n_elem, &kf, &flags, &row_ptr, &inc_ptr, &inc, &pos, &n_rows, &cap, &con_flag,
-                  &con_val, &elem_dofs, &mode, &values, &rhs, &need, &done, &ticket};
+  void* args[] = {&diag, &xyz, &conn, &tab, &forcing, &d_f, &n_elem, &kf, &flags, &rs, &con, &row_ptr, &inc_ptr, &inc, &n_rows, &cap,
+                  &fe_cell, &values, &rhs, &need, &done, &ticket};
   // cooperative launch: fails instead of deadlocking if the grid cannot be co-resident
   FEASM_CUDA(ctx, cudaLaunchCooperativeKernel((void*)kern, dim3(grid), dim3((EW + RW) * 32), args, smem, ctx->stream));
   return FEASM_OK;

@@ -22,21 +22,22 @@ struct FeasmTables {
 };
 bool feasm_make_tables(int elem_type, int qorder, FeasmTables& t, std::string& err);
 
-// Element buffer KF[e][a][LDR]: row a of element e = Ke(a, 0..nd-1) followed by Fe(a) at column nd, padded to a
-// whole number of 32 B sectors (HEX27: 28 doubles = 224 B).  One row is what one (element, local dof) pair
-// contributes to one CSR row, so the row reduction reads it as one contiguous run.
+// Element records REC[e][a], feasm_recb bytes each: row a of element e = Ke(a, 0..nd-1) followed by Fe(a) at column
+// nd, padded to a whole number of 32 B sectors (HEX27: 28 doubles = 224 B), then the position-map row of the (e,a)
+// pair (HEX27: 32 B; 256 B per record).  One record is everything one (element, local dof) pair contributes to one CSR
+// row — values written by the element kernel every assembly, positions written once by feasm_prepare — so the row
+// reduction fetches it as ONE contiguous, sector-aligned run.
 #ifdef __CUDACC__
 #define FEASM_HD __host__ __device__
 #else
 #define FEASM_HD
 #endif
 FEASM_HD constexpr int feasm_ldr(int nd) { return (nd + 1 + 3) & ~3; }
-// Position map pos[e][a][PLD]: row stride padded to whole sectors; entry = column position inside the CSR row,
-// top bit = "column dof is constrained".  uint8 when every row has <= 128 entries, else uint16.
-FEASM_HD constexpr int feasm_pld(int nd, int pos_bytes) { return ((nd * pos_bytes + 31) & ~31) / pos_bytes; }
-
-// incidence id = e*nd + a in the low 31 bits; bit 31 = the element touches a constrained dof
-constexpr uint32_t FEASM_INC_SLOW = 0x80000000u, FEASM_INC_MASK = 0x7fffffffu;
+// Position-map row of a record, PLD entries (padded to whole sectors).  Entries 0..nd-1 = column position inside the
+// CSR row; entry nd = the image cell that collects Fe (= max_row_len, the cell behind the longest row); entry nd+1 =
+// flag of the (e,a) pair (RR_LAST, feasm_rr_dev.cuh).  uint8 when every row has <= 255 entries, else uint16.
+FEASM_HD constexpr int feasm_pld(int nd, int pos_bytes) { return (((nd + 2) * pos_bytes + 31) & ~31) / pos_bytes; }
+FEASM_HD constexpr int feasm_recb(int nd, int pos_bytes) { return feasm_ldr(nd) * 8 + feasm_pld(nd, pos_bytes) * pos_bytes; }
 
 struct feasm_ctx {
   int device = 0;
@@ -74,11 +75,13 @@ struct feasm_ctx {
 
   // scatter maps (built by feasm_prepare)
   bool prepared = false;
-  void* d_pos = nullptr;          // [n_elem][nd][feasm_pld] row-relative column position | constrained-column flag
   int pos_bytes = 2;
-  bool pos_flags_valid = false;   // top bits reflect the current constrained set
+  uint8_t* d_elem_flag = nullptr;  // [n_elem] element touches a constrained dof (feasm_launch_elem_flags)
+  bool elem_flag_valid = false;    // reflects the current constrained set
+  uint32_t* d_con_elems = nullptr; // the flagged elements, compacted (any order)
+  int64_t n_con_elems = 0;
   uint64_t* d_inc_ptr = nullptr;  // [n_rows+1]
-  uint32_t* d_inc = nullptr;      // [n_elem*nd] = e*nd + a, ascending within a row
+  uint32_t* d_inc = nullptr;      // [n_elem*nd] incidence ids e*nd + a, ascending within a row
   uint32_t max_inc = 0;
   uint32_t* d_batch_need = nullptr;  // [ceil(n_rows/32)]: 1 + largest element id contributing to the batch of 32 rows
   uint32_t* d_sync = nullptr;        // fused kernel: ticket counter + per-wave completion counters
@@ -88,7 +91,7 @@ struct feasm_ctx {
   std::vector<cudaEvent_t> chunk_ev;
 
   // element buffers
-  double* d_kf = nullptr;  // [n_elem][nd][feasm_ldr(nd)]: Ke rows with Fe in column nd
+  double* d_kf = nullptr;  // element records [n_elem][nd][feasm_recb bytes]
   int* d_flags = nullptr;  // [0] degenerate count, [1] pattern misses
 
   // tables on device, keyed by quadrature order
@@ -127,18 +130,16 @@ int feasm_build_incidence(feasm_ctx* ctx);
 int feasm_device_build_pattern(feasm_ctx* ctx);
 int feasm_build_pos(feasm_ctx* ctx);
 // feasm_assemble.cu
+// d_kf: records of elements [e0, e1), rs doubles per record; constrain_mode = FEASM_CONSTRAIN_* (applied in place by
+// the kernel to the elements flagged in d_elem_flag) or < 0 for none
 int feasm_launch_element_kernel(feasm_ctx* ctx, const feasm_params& p, const double* d_f, int64_t e0, int64_t e1,
-                                double* d_kf);
-// applies the Dirichlet constraints to element rows in place (element-level API only; the assembly applies them
-// inside the row reduction)
-int feasm_launch_constrain_elements(feasm_ctx* ctx, int constrain_mode, int64_t e0, int64_t e1, double* d_kf);
-int feasm_launch_pos_flags(feasm_ctx* ctx);
+                                double* d_kf, int rs, int constrain_mode);
+int feasm_launch_elem_flags(feasm_ctx* ctx);
 // feasm_fused.cu
 int feasm_launch_fused(feasm_ctx* ctx, const feasm_params& p, const double* d_f);
 int feasm_build_batch_need(feasm_ctx* ctx);
 // d_row_list == nullptr: every row; else the n_list rows listed
-int feasm_launch_row_reduce(feasm_ctx* ctx, int constrain_mode, const uint32_t* d_row_list, int64_t n_list,
-                            cudaStream_t stream, int64_t row0 = 0);
+int feasm_launch_row_reduce(feasm_ctx* ctx, const uint32_t* d_row_list, int64_t n_list, cudaStream_t stream, int64_t row0 = 0);
 int feasm_launch_pack(feasm_ctx* ctx);
 int feasm_launch_unpack(feasm_ctx* ctx);
 int feasm_launch_add_matrix(feasm_ctx* ctx, const double* d_dm, const uint32_t* d_rows, int nr, const uint32_t* d_cols,

@@ -66,7 +66,7 @@ __global__ void k_row_pattern(const uint32_t* __restrict__ elem_dofs, const uint
   for (int t = lane; t < p2; t += 32) {
     uint32_t v = 0xffffffffu;
     if (t < n) {
-      const uint32_t ea = inc[k0 + t / nd] & FEASM_INC_MASK;
+      const uint32_t ea = inc[k0 + t / nd];
       const uint32_t dof = elem_dofs[(uint64_t)(ea / nd) * nd + (t % nd)];
       v = gid ? gid[dof] : dof;
     }
@@ -103,20 +103,28 @@ __global__ void k_counts_to_u64(const uint32_t* __restrict__ c, uint64_t* out, i
   if (i < n) out[i] = c[i];
 }
 
-// pos[e][a][b] = index of column gid(dof_b) inside row dof_a (row stride pld; the top bit is the constrained-column
-// flag, written later by feasm_launch_pos_flags).
+// Position-map row of record (e,a): entry b < nd = index of column gid(dof_b) inside CSR row dof_a; entry nd = the Fe
+// cell; entry nd+1 = RR_LAST when (e,a) is the last contributor of its row (feasm_internal.h).
 template <typename PosT>
 __global__ void k_build_pos(const uint32_t* __restrict__ elem_dofs, const uint32_t* __restrict__ gid, int nd, int pld,
                             int64_t n_elem, const uint64_t* __restrict__ row_ptr, const uint32_t* __restrict__ col_idx,
-                            PosT* __restrict__ pos, int* flags) {
+                            const uint64_t* __restrict__ inc_ptr, const uint32_t* __restrict__ inc, unsigned fe_cell,
+                            unsigned char* __restrict__ rec, int recb, int pos_off, int* flags) {
   const uint64_t i = blockIdx.x * (uint64_t)blockDim.x + threadIdx.x;
   const uint64_t total = (uint64_t)n_elem * nd * pld;
   if (i >= total) return;
   const uint64_t ea = i / pld;
   const int b = (int)(i % pld);
-  if (b >= nd) { pos[i] = 0; return; }
-  const uint64_t e = ea / nd;
+  PosT* pos = reinterpret_cast<PosT*>(rec + ea * recb + pos_off) + b;
   const uint32_t row = elem_dofs[ea];
+  if (b >= nd) {
+    PosT v = 0;
+    if (b == nd) v = (PosT)fe_cell;
+    else if (b == nd + 1) v = (PosT)(inc[inc_ptr[row + 1] - 1] == (uint32_t)ea ? 1u : 0u);
+    *pos = v;
+    return;
+  }
+  const uint64_t e = ea / nd;
   const uint32_t dcol = elem_dofs[e * nd + b];
   const uint32_t col = gid ? gid[dcol] : dcol;
   const uint32_t* c = col_idx + row_ptr[row];
@@ -129,7 +137,7 @@ __global__ void k_build_pos(const uint32_t* __restrict__ elem_dofs, const uint32
     atomicAdd(&flags[1], 1);
     lo = 0;
   }
-  pos[i] = (PosT)lo;
+  *pos = (PosT)lo;
 }
 
 // batch_need[b] = 1 + the largest element id that contributes to rows [32b, 32b+32): incidence lists are ascending, so
@@ -141,7 +149,7 @@ __global__ void k_batch_need(const uint64_t* __restrict__ inc_ptr, const uint32_
   uint32_t mx = 0;
   for (int64_t r = b * 32; r < n_rows && r < b * 32 + 32; ++r)
     if (inc_ptr[r + 1] > inc_ptr[r]) {
-      const uint32_t e1 = (inc[inc_ptr[r + 1] - 1] & FEASM_INC_MASK) / (uint32_t)nd + 1;
+      const uint32_t e1 = inc[inc_ptr[r + 1] - 1] / (uint32_t)nd + 1;
       mx = e1 > mx ? e1 : mx;
     }
   need[b] = mx;
@@ -233,23 +241,29 @@ int feasm_build_pos(feasm_ctx* ctx) {
   FEASM_CUDA(ctx, cudaMemcpyAsync(&ctx->max_row_len, d_max, sizeof(unsigned int), cudaMemcpyDeviceToHost, ctx->stream));
   FEASM_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
   cudaFree(d_max);
-  if (ctx->max_row_len > 32768u) return feasm_fail(ctx, FEASM_ERR_ARG, "row longer than 32768 entries: position map overflows");
-  ctx->pos_bytes = ctx->max_row_len <= 128u ? 1 : 2;
-  const int pld = feasm_pld(ctx->nd, ctx->pos_bytes);
+  if (ctx->max_row_len > 32767u) return feasm_fail(ctx, FEASM_ERR_ARG, "row longer than 32767 entries: position map overflows");
+  ctx->pos_bytes = ctx->max_row_len <= 255u ? 1 : 2;  // positions and the Fe cell (= max_row_len) fit the entry
+  const int pld = feasm_pld(ctx->nd, ctx->pos_bytes), recb = feasm_recb(ctx->nd, ctx->pos_bytes);
   const uint64_t total = (uint64_t)ctx->n_elem * ctx->nd * pld;
-  if (ctx->d_pos) cudaFree(ctx->d_pos);
-  ctx->d_pos = nullptr;
-  FEASM_CUDA(ctx, cudaMalloc(&ctx->d_pos, (size_t)ctx->pos_bytes * (total ? total : 1)));
+  // the element records: values part rewritten by every assembly, position rows written here once
+  if (ctx->d_kf) cudaFree(ctx->d_kf);
+  ctx->d_kf = nullptr;
+  const size_t rec_bytes = (size_t)ctx->n_elem * ctx->nd * recb + 256;  // slack: the row reduction prefetches one record ahead
+  FEASM_CUDA(ctx, cudaMalloc(&ctx->d_kf, rec_bytes));
+  FEASM_CUDA(ctx, cudaMemsetAsync(ctx->d_kf, 0, rec_bytes, ctx->stream));
   FEASM_CUDA(ctx, cudaMemsetAsync(ctx->d_flags, 0, 2 * sizeof(int), ctx->stream));
   if (total) {
+    unsigned char* rec = reinterpret_cast<unsigned char*>(ctx->d_kf);
+    const int pos_off = feasm_ldr(ctx->nd) * 8;
     if (ctx->pos_bytes == 1)
       k_build_pos<uint8_t><<<grid_for(total, 256), 256, 0, ctx->stream>>>(ctx->d_elem_dofs, ctx->d_gid, ctx->nd, pld, ctx->n_elem,
-                                                                         ctx->d_row_ptr, ctx->d_col_idx, (uint8_t*)ctx->d_pos, ctx->d_flags);
+                                                                         ctx->d_row_ptr, ctx->d_col_idx, ctx->d_inc_ptr, ctx->d_inc,
+                                                                         ctx->max_row_len, rec, recb, pos_off, ctx->d_flags);
     else
       k_build_pos<uint16_t><<<grid_for(total, 256), 256, 0, ctx->stream>>>(ctx->d_elem_dofs, ctx->d_gid, ctx->nd, pld, ctx->n_elem,
-                                                                          ctx->d_row_ptr, ctx->d_col_idx, (uint16_t*)ctx->d_pos, ctx->d_flags);
+                                                                          ctx->d_row_ptr, ctx->d_col_idx, ctx->d_inc_ptr, ctx->d_inc,
+                                                                          ctx->max_row_len, rec, recb, pos_off, ctx->d_flags);
   }
-  ctx->pos_flags_valid = false;
   int flags[2] = {0, 0};
   FEASM_CUDA(ctx, cudaMemcpyAsync(flags, ctx->d_flags, sizeof(flags), cudaMemcpyDeviceToHost, ctx->stream));
   FEASM_CUDA(ctx, cudaStreamSynchronize(ctx->stream));

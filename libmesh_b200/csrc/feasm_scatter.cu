@@ -1,137 +1,84 @@
-// feasm_scatter.cu — the deterministic scatter: row reduction into CSR with the Dirichlet constraints fused in.
+// feasm_scatter.cu — the deterministic scatter: row reduction of the element records into CSR.
 //
 // Row reduction = SparseMatrix::add_matrix / NumericVector::add_vector (laspack_matrix.C:259-275,
-// numeric_vector.C:690-697) turned inside out: a warp sums, for each CSR row it owns, the element rows
-// KF[e][a][:] incident to that row in element order through the precomputed position map — no atomics, bitwise
-// reproducible, and the same accumulation order as the reference's serial element loop.
-// DofMap::heterogeneously_constrain_element_matrix_and_vector / constrain_element_matrix_and_vector
-// (src/base/dof_map_constraints.C:2518-2614, :2439-2514) with empty constraint rows act entry-wise on an element
-// row, so they are applied here while the row streams through registers:
-//   row dof constrained            -> the element contributes K(a,a) = 1 and F(a) = g_a (0 when homogeneous)
-//   column dof b constrained only  -> F(a) -= K(a,b) g_b (heterogeneous), K(a,b) = 0
-// The "column constrained" bit travels in the top bit of the position map, so the common unconstrained entry costs
-// nothing extra.
+// numeric_vector.C:690-697) turned inside out: a warp sums, for each CSR row it owns, the element records
+// REC[e][a] incident to that row in element order through the position row each record carries — no atomics, bitwise
+// reproducible, and the same accumulation order as the reference's serial element loop.  The Dirichlet constraints
+// (DofMap::heterogeneously_constrain_element_matrix_and_vector, src/base/dof_map_constraints.C:2518-2614) were applied
+// to the records by the element kernel, as the reference applies them to Ke/Fe before add_matrix.
+#include <cstdlib>
+
 #include "feasm_rr_dev.cuh"
 
 namespace {
 // Stand-alone row reduction: one batch of RB rows per warp.  ND = dofs per element when known at compile time
 // (strides and lane loops fold away), 0 = generic (runtime nd).
-template <typename PosT, int ND, int WARPS>
+template <typename PosT, int ND, int WARPS, bool BULK>
 __global__ void __launch_bounds__(WARPS * 32)
 k_row_reduce(const uint64_t* __restrict__ row_ptr, const uint64_t* __restrict__ inc_ptr, const uint32_t* __restrict__ inc,
-             const unsigned char* __restrict__ pos, const unsigned char* __restrict__ kf, int nd_rt, int RB, int lcap, int cap,
-             const uint32_t* __restrict__ row_list, int64_t row0, int64_t n_list, const uint8_t* __restrict__ con_flag,
-             const double* __restrict__ con_val, const uint32_t* __restrict__ elem_dofs, int mode,
-             double* __restrict__ values, double* __restrict__ rhs) {
+             const unsigned char* __restrict__ rec, int nd_rt, int RB, int lcap, int cap, int fe_cell, int G,
+             const uint32_t* __restrict__ row_list, int64_t row0, int64_t n_list, double* __restrict__ values,
+             double* __restrict__ rhs) {
   const int nd = ND ? ND : nd_rt;
-  const int slotb = feasm_ldr(nd) * 8 + feasm_pld(nd, (int)sizeof(PosT)) * (int)sizeof(PosT);
-  const int G = rr_stage(slotb);
+  const int recb = feasm_recb(nd, (int)sizeof(PosT));
   extern __shared__ __align__(16) unsigned char s_raw[];
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const int64_t base = row0 + (blockIdx.x * (int64_t)WARPS + warp) * RB;  // rows [row0, n_list) (positions, with a row list)
   if (base >= n_list) return;
   const int nrows = (int)(n_list - base < RB ? n_list - base : RB);
-  const uint32_t warp_bytes = (uint32_t)(RR_NG * G * slotb + cap * 8 + lcap * 4);
+  const uint32_t warp_bytes = (uint32_t)(RR_NG * G * recb + cap * 8 + lcap * 4 + 8 * RR_NG);
   const uint32_t ring_a = (uint32_t)__cvta_generic_to_shared(s_raw) + warp * warp_bytes;
-  const uint32_t img_a = ring_a + RR_NG * G * slotb;
+  const uint32_t img_a = ring_a + RR_NG * G * recb;
   const uint32_t list_a = img_a + cap * 8;
+  const uint32_t bar_a = list_a + lcap * 4;
   for (int t = lane; t < cap; t += 32) sts_f64(img_a + 8 * t, 0.);
+  if (BULK) {
+    if (lane < RR_NG) mbar_init(bar_a + 8 * lane, 1);
+    mbar_init_fence();
+  }
   __syncwarp();
-  rr_process_batch<PosT, ND>(base, nrows, lane, ring_a, img_a, list_a, G, nd_rt, row_ptr, inc_ptr, inc, pos, kf, row_list, con_flag,
-                             con_val, elem_dofs, mode, values, rhs);
+  uint32_t phase = 0;
+  rr_process_batch<PosT, ND, BULK>(base, nrows, lane, ring_a, img_a, list_a, G, nd_rt, fe_cell, row_ptr, inc_ptr, inc, rec, row_list,
+                                   values, rhs, bar_a, phase);
 }
 
-// Fallback for rows longer than the shared-memory budget: accumulate straight into the (zeroed) global row.
+// Fallback for rows longer than the shared-memory budget: one warp per row accumulates straight into the (zeroed)
+// global row, contributors in element order.
 template <typename PosT>
 __global__ void k_row_reduce_global(const uint64_t* __restrict__ row_ptr, const uint64_t* __restrict__ inc_ptr,
-                                    const uint32_t* __restrict__ inc, const PosT* __restrict__ pos,
-                                    const double* __restrict__ kf, int nd, int ldr, int pld, int64_t row0, int64_t n_rows,
-                                    const uint8_t* __restrict__ con_flag, const double* __restrict__ con_val,
-                                    const uint32_t* __restrict__ elem_dofs, int mode, double* __restrict__ values,
-                                    double* __restrict__ rhs) {
+                                    const uint32_t* __restrict__ inc, const unsigned char* __restrict__ rec, int nd,
+                                    int64_t row0, int64_t n_rows, double* __restrict__ values, double* __restrict__ rhs) {
   const int lane = threadIdx.x & 31;
   const int64_t r = row0 + ((blockIdx.x * (int64_t)blockDim.x + threadIdx.x) >> 5);
   if (r >= n_rows) return;
+  const int ldrb = feasm_ldr(nd) * 8, recb = feasm_recb(nd, (int)sizeof(PosT));
   double* row = values + row_ptr[r];
   const int len = (int)(row_ptr[r + 1] - row_ptr[r]);
   for (int t = lane; t < len; t += 32) row[t] = 0.;
   __syncwarp();
-  const int row_con = con_flag[r];
-  const double row_g = (row_con && mode == FEASM_CONSTRAIN_HETEROGENEOUS) ? con_val[r] : 0.;
-  double b = 0., corr = 0.;
+  double b = 0.;
   for (uint64_t k = inc_ptr[r]; k < inc_ptr[r + 1]; ++k) {
-    const uint64_t ea = inc[k] & FEASM_INC_MASK;
-    const int a = (int)(ea % nd);
-    for (int t = lane; t < nd; t += 32) {
-      double val = kf[ea * ldr + t];
-      const unsigned pp = pos[ea * pld + t];
-      if (row_con) val = (t == a) ? 1. : 0.;
-      else if (pp & PosBits<PosT>::FLAG) {
-        if (mode == FEASM_CONSTRAIN_HETEROGENEOUS) corr += val * con_val[elem_dofs[(ea / nd) * nd + t]];
-        val = 0.;
-      }
-      row[pp & PosBits<PosT>::MASK] += val;
-    }
-    b += row_con ? row_g : kf[ea * ldr + nd];
+    const unsigned char* rc = rec + (uint64_t)inc[k] * recb;
+    const double* val = reinterpret_cast<const double*>(rc);
+    const PosT* pp = reinterpret_cast<const PosT*>(rc + ldrb);
+    for (int t = lane; t < nd; t += 32) row[pp[t]] += val[t];
+    b += val[nd];
     __syncwarp();
   }
-  for (int o = 16; o > 0; o >>= 1) corr += __shfl_xor_sync(0xffffffffu, corr, o);
-  if (lane == 0) rhs[r] = b - corr;
+  if (lane == 0) rhs[r] = b;
 }
 
-// Element-level constraint application for feasm_element_matrices (tests / debugging): one warp per element,
-// in place on KF rows.  dof_map_constraints.C:2518-2614 with C = diag(0 on constrained, 1 else), H = g on constrained.
-__global__ void k_constrain_elements(const uint32_t* __restrict__ elem_dofs, const uint8_t* __restrict__ con_flag,
-                                     const double* __restrict__ con_val, int nd, int ldr, int mode, int64_t e0, int64_t e1,
-                                     double* __restrict__ kf) {
-  const int lane = threadIdx.x & 31;
-  const int64_t e = e0 + ((blockIdx.x * (int64_t)blockDim.x + threadIdx.x) >> 5);
-  if (e >= e1) return;
-  double* K = kf + (uint64_t)(e - e0) * nd * ldr;
-  const uint32_t* dofs = elem_dofs + (uint64_t)e * nd;
-  // Fe <- C^T (Fe - K H)
-  for (int i = lane; i < nd; i += 32) {
-    if (con_flag[dofs[i]]) continue;
-    if (mode != FEASM_CONSTRAIN_HETEROGENEOUS) continue;
-    double kh = 0.;
-    for (int j = 0; j < nd; ++j)
-      if (con_flag[dofs[j]]) kh += K[i * ldr + j] * con_val[dofs[j]];
-    K[i * ldr + nd] -= kh;
-  }
-  __syncwarp();
-  // K <- C^T K C, then K(i,i) = 1 and Fe(i) = H(i) on constrained rows
-  for (int t = lane; t < nd * nd; t += 32) {
-    const int i = t / nd, j = t % nd;
-    if (con_flag[dofs[i]] || con_flag[dofs[j]]) K[i * ldr + j] = (i == j) ? 1. : 0.;
-  }
-  for (int i = lane; i < nd; i += 32)
-    if (con_flag[dofs[i]]) K[i * ldr + nd] = (mode == FEASM_CONSTRAIN_HETEROGENEOUS) ? con_val[dofs[i]] : 0.;
-}
-
-// Refresh the "column dof is constrained" bit of every position-map entry from the current constrained set.
-template <typename PosT>
-__global__ void k_pos_flags(const uint32_t* __restrict__ elem_dofs, const uint8_t* __restrict__ con_flag, int nd, int pld,
-                            uint64_t n_rows_e /* n_elem*nd */, PosT* __restrict__ pos) {
-  const uint64_t i = blockIdx.x * (uint64_t)blockDim.x + threadIdx.x;
-  const uint64_t ea = i / pld;
-  const int b = (int)(i % pld);
-  if (ea >= n_rows_e || b >= nd) return;
-  const uint64_t e = ea / nd;
-  const unsigned p = pos[i] & PosBits<PosT>::MASK;
-  pos[i] = (PosT)(p | (con_flag[elem_dofs[e * nd + b]] ? PosBits<PosT>::FLAG : 0u));
-}
-
-// Bit 31 of an incidence id = "the element touches a constrained dof": its rows take the out-of-line path of the row
-// reduction.  Refreshed together with the position-map flags.
-__global__ void k_inc_flags(const uint32_t* __restrict__ elem_dofs, const uint8_t* __restrict__ con_flag, int nd, uint64_t total,
-                            uint32_t* __restrict__ inc) {
-  const uint64_t k = blockIdx.x * (uint64_t)blockDim.x + threadIdx.x;
-  if (k >= total) return;
-  const uint32_t ea = inc[k] & FEASM_INC_MASK;
-  const uint32_t* d = elem_dofs + (uint64_t)(ea / (uint32_t)nd) * nd;
+// elem_flag[e] = element e touches a constrained dof: its records get the in-place constraint pass of the element
+// kernel (constrain_element, feasm_elem_dev.cuh).  Refreshed when the constrained SET changes.
+__global__ void k_elem_flags(const uint32_t* __restrict__ elem_dofs, const uint8_t* __restrict__ con_flag, int nd, int64_t n_elem,
+                             uint8_t* __restrict__ elem_flag, uint32_t* __restrict__ list, unsigned* __restrict__ count) {
+  const int64_t e = blockIdx.x * (int64_t)blockDim.x + threadIdx.x;
+  if (e >= n_elem) return;
+  const uint32_t* d = elem_dofs + e * nd;
   unsigned any = 0;
   for (int b = 0; b < nd; ++b) any |= con_flag[d[b]];
-  inc[k] = ea | (any ? FEASM_INC_SLOW : 0u);
+  elem_flag[e] = (uint8_t)(any ? 1 : 0);
+  if (any) list[atomicAdd(count, 1u)] = (uint32_t)e;  // order is irrelevant: elements are constrained independently
 }
 
 __global__ void k_pack(const uint64_t* __restrict__ slots, uint64_t n, uint64_t nnz, const double* __restrict__ values,
@@ -174,77 +121,71 @@ __global__ void k_add_matrix(const double* __restrict__ dm, const uint32_t* __re
 }
 
 template <typename PosT, int ND>
-int launch_row_reduce_t(feasm_ctx* ctx, int mode, const uint32_t* d_row_list, int64_t n_list, cudaStream_t stream, int64_t row0) {
+int launch_row_reduce_t(feasm_ctx* ctx, const uint32_t* d_row_list, int64_t n_list, cudaStream_t stream, int64_t row0) {
   constexpr int WARPS = 4;
-  const int cap = ((int)ctx->max_row_len + 1) & ~1;  // even: every warp's ring stays 16 B aligned
-  const int ldr = feasm_ldr(ctx->nd), pld = feasm_pld(ctx->nd, (int)sizeof(PosT));
-  const int slotb = ldr * 8 + pld * (int)sizeof(PosT);
-  const int G = rr_stage(slotb);
+  const int cap = ((int)ctx->max_row_len + 2) & ~1;  // row cells + the Fe cell; even: every warp's ring stays 16 B aligned
+  const int recb = feasm_recb(ctx->nd, (int)sizeof(PosT));
+  static const int g_env = getenv("FEASM_RR_G") ? atoi(getenv("FEASM_RR_G")) : 0;  // tuning knob
+  const int G = g_env > 0 ? g_env : rr_stage(recb);
   const int lcap = 256;
   int RB = ctx->max_inc ? (int)(lcap / ctx->max_inc) : 32;
   if (RB > 32) RB = 32;
-  const size_t warp_bytes = (size_t)RR_NG * G * slotb + (size_t)cap * 8 + (size_t)lcap * 4;
+  const size_t warp_bytes = (size_t)RR_NG * G * recb + (size_t)cap * 8 + (size_t)lcap * 4 + 8 * RR_NG;
   const size_t smem = WARPS * warp_bytes;
+  const unsigned char* rec = reinterpret_cast<const unsigned char*>(ctx->d_kf);
   if (RB >= 1 && smem <= ctx->smem_optin && ctx->nd <= 128) {
-    auto kern = k_row_reduce<PosT, ND, WARPS>;
+    static const bool bulk = !(getenv("FEASM_RR_BULK") && atoi(getenv("FEASM_RR_BULK")) == 0);  // 0: cp.async ring fill
+    auto kern = bulk && G <= 32 ? k_row_reduce<PosT, ND, WARPS, true> : k_row_reduce<PosT, ND, WARPS, false>;
     FEASM_CUDA(ctx, cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
     const int64_t batches = (n_list - row0 + RB - 1) / RB;
     const unsigned grid = (unsigned)((batches + WARPS - 1) / WARPS);
     if (grid)
-      kern<<<grid, WARPS * 32, smem, stream>>>(ctx->d_row_ptr, ctx->d_inc_ptr, ctx->d_inc, (const unsigned char*)ctx->d_pos,
-                                               (const unsigned char*)ctx->d_kf, ctx->nd, RB, lcap, cap, d_row_list, row0, n_list,
-                                               ctx->d_con_flag, ctx->d_con_val, ctx->d_elem_dofs, mode, ctx->d_values, ctx->d_rhs);
+      kern<<<grid, WARPS * 32, smem, stream>>>(ctx->d_row_ptr, ctx->d_inc_ptr, ctx->d_inc, rec, ctx->nd, RB, lcap, cap,
+                                               (int)ctx->max_row_len, G, d_row_list, row0, n_list, ctx->d_values, ctx->d_rhs);
   } else {
     if (d_row_list) return feasm_fail(ctx, FEASM_ERR_NOMEM, "rows too long for the shared-memory row reduction");
     const unsigned grid = (unsigned)(((n_list - row0) * 32 + 255) / 256);
     if (grid)
-      k_row_reduce_global<PosT><<<grid, 256, 0, stream>>>(ctx->d_row_ptr, ctx->d_inc_ptr, ctx->d_inc, (const PosT*)ctx->d_pos, ctx->d_kf,
-                                                        ctx->nd, ldr, pld, row0, n_list, ctx->d_con_flag, ctx->d_con_val,
-                                                        ctx->d_elem_dofs, mode, ctx->d_values, ctx->d_rhs);
+      k_row_reduce_global<PosT><<<grid, 256, 0, stream>>>(ctx->d_row_ptr, ctx->d_inc_ptr, ctx->d_inc, rec, ctx->nd, row0, n_list,
+                                                          ctx->d_values, ctx->d_rhs);
   }
   FEASM_CUDA(ctx, cudaGetLastError());
   return FEASM_OK;
 }
 
 template <typename PosT>
-int launch_row_reduce(feasm_ctx* ctx, int mode, const uint32_t* d_row_list, int64_t n_list, cudaStream_t stream, int64_t row0) {
+int launch_row_reduce(feasm_ctx* ctx, const uint32_t* d_row_list, int64_t n_list, cudaStream_t stream, int64_t row0) {
   switch (ctx->nd) {
-    case 8: return launch_row_reduce_t<PosT, 8>(ctx, mode, d_row_list, n_list, stream, row0);
-    case 10: return launch_row_reduce_t<PosT, 10>(ctx, mode, d_row_list, n_list, stream, row0);
-    case 27: return launch_row_reduce_t<PosT, 27>(ctx, mode, d_row_list, n_list, stream, row0);
-    case 81: return launch_row_reduce_t<PosT, 81>(ctx, mode, d_row_list, n_list, stream, row0);
-    default: return launch_row_reduce_t<PosT, 0>(ctx, mode, d_row_list, n_list, stream, row0);
+    case 8: return launch_row_reduce_t<PosT, 8>(ctx, d_row_list, n_list, stream, row0);
+    case 10: return launch_row_reduce_t<PosT, 10>(ctx, d_row_list, n_list, stream, row0);
+    case 27: return launch_row_reduce_t<PosT, 27>(ctx, d_row_list, n_list, stream, row0);
+    case 81: return launch_row_reduce_t<PosT, 81>(ctx, d_row_list, n_list, stream, row0);
+    default: return launch_row_reduce_t<PosT, 0>(ctx, d_row_list, n_list, stream, row0);
   }
 }
 
 }  // namespace
 
-int feasm_launch_row_reduce(feasm_ctx* ctx, int mode, const uint32_t* d_row_list, int64_t n_list, cudaStream_t stream, int64_t row0) {
-  if (ctx->pos_bytes == 1) return launch_row_reduce<uint8_t>(ctx, mode, d_row_list, n_list, stream, row0);
-  return launch_row_reduce<uint16_t>(ctx, mode, d_row_list, n_list, stream, row0);
+int feasm_launch_row_reduce(feasm_ctx* ctx, const uint32_t* d_row_list, int64_t n_list, cudaStream_t stream, int64_t row0) {
+  if (ctx->pos_bytes == 1) return launch_row_reduce<uint8_t>(ctx, d_row_list, n_list, stream, row0);
+  return launch_row_reduce<uint16_t>(ctx, d_row_list, n_list, stream, row0);
 }
 
-int feasm_launch_constrain_elements(feasm_ctx* ctx, int mode, int64_t e0, int64_t e1, double* d_kf) {
-  const int64_t n = e1 - e0;
-  k_constrain_elements<<<(unsigned)((n * 32 + 255) / 256), 256, 0, ctx->stream>>>(ctx->d_elem_dofs, ctx->d_con_flag, ctx->d_con_val,
-                                                                                   ctx->nd, feasm_ldr(ctx->nd), mode, e0, e1, d_kf);
+int feasm_launch_elem_flags(feasm_ctx* ctx) {
+  const size_t ne = (size_t)(ctx->n_elem ? ctx->n_elem : 1);
+  if (!ctx->d_elem_flag) FEASM_CUDA(ctx, cudaMalloc(&ctx->d_elem_flag, ne));
+  if (!ctx->d_con_elems) FEASM_CUDA(ctx, cudaMalloc(&ctx->d_con_elems, sizeof(uint32_t) * (ne + 1)));
+  unsigned* d_count = ctx->d_con_elems + ne;  // the counter lives behind the list
+  FEASM_CUDA(ctx, cudaMemsetAsync(d_count, 0, sizeof(unsigned), ctx->stream));
+  if (ctx->n_elem)
+    k_elem_flags<<<(unsigned)((ctx->n_elem + 127) / 128), 128, 0, ctx->stream>>>(ctx->d_elem_dofs, ctx->d_con_flag, ctx->nd, ctx->n_elem,
+                                                                                 ctx->d_elem_flag, ctx->d_con_elems, d_count);
   FEASM_CUDA(ctx, cudaGetLastError());
-  return FEASM_OK;
-}
-
-int feasm_launch_pos_flags(feasm_ctx* ctx) {
-  const int pld = feasm_pld(ctx->nd, ctx->pos_bytes);
-  const uint64_t rows_e = (uint64_t)ctx->n_elem * ctx->nd, total = rows_e * pld;
-  const unsigned grid = (unsigned)((total + 255) / 256);
-  if (grid) {
-    if (ctx->pos_bytes == 1)
-      k_pos_flags<uint8_t><<<grid, 256, 0, ctx->stream>>>(ctx->d_elem_dofs, ctx->d_con_flag, ctx->nd, pld, rows_e, (uint8_t*)ctx->d_pos);
-    else
-      k_pos_flags<uint16_t><<<grid, 256, 0, ctx->stream>>>(ctx->d_elem_dofs, ctx->d_con_flag, ctx->nd, pld, rows_e, (uint16_t*)ctx->d_pos);
-  }
-  if (rows_e) k_inc_flags<<<(unsigned)((rows_e + 255) / 256), 256, 0, ctx->stream>>>(ctx->d_elem_dofs, ctx->d_con_flag, ctx->nd, rows_e, ctx->d_inc);
-  FEASM_CUDA(ctx, cudaGetLastError());
-  ctx->pos_flags_valid = true;
+  unsigned count = 0;
+  FEASM_CUDA(ctx, cudaMemcpyAsync(&count, d_count, sizeof(unsigned), cudaMemcpyDeviceToHost, ctx->stream));
+  FEASM_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
+  ctx->n_con_elems = count;
+  ctx->elem_flag_valid = true;
   return FEASM_OK;
 }
 
