@@ -153,7 +153,7 @@ def run_ours(args):
     clocks.start()
     ev0, ev1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
     torch.cuda.synchronize()
-    k_ms = np.zeros((args.steps, 3))
+    k_ms = np.zeros((args.steps, 4))
     launches = 0
     ev0.record(stream)
     for _ in range(args.steps):
@@ -201,7 +201,7 @@ def run_ours(args):
     nq = {27: 27, 8: 27 if args.qorder in (0, 5) else 8, 10: 14}[etype]
     flops_e, bytes_e = algorithmic_counts(etype, nq, nnz, P["n_dofs"], n_elem, P["xyz"].shape[0])
     hbm_peak, peak_src = peaks()
-    elem_ms, red_ms = float(np.median(k_ms[:, 0])), float(np.median(k_ms[:, 1]))
+    elem_ms, red_ms, con_ms = float(np.median(k_ms[:, 0])), float(np.median(k_ms[:, 1])), float(np.median(k_ms[:, 3]))
     fp64_peak = max(fp64["dmma_tflops"], fp64["dfma_tflops"])
     ach_tf = flops_e * n_elem / (elem_ms * 1e-3) / 1e12
     step_tf = flops_e * n_elem / (ms_per_step * 1e-3) / 1e12
@@ -225,7 +225,7 @@ def run_ours(args):
         "roofline": {"bound": "tensor", "kernel": "k_elem_poisson (FP64 DMMA contraction + geometry)", "achieved": ach_tf,
                      "peak": fp64_peak, "unit": "TFLOP/s", "frac": ach_tf / fp64_peak, "traffic": traffic,
                      "peak_source": "FP64 mma.sync/DFMA chain measured live by feasm_measure_fp64_peaks (MEASURED_PEAKS.json has no FP64 entry)",
-                     "kernel_ms": {"element": elem_ms, "row_reduce": red_ms},
+                     "kernel_ms": {"element": elem_ms, "constrain": con_ms, "row_reduce": red_ms},
                      "flops_per_element": flops_e, "bytes_per_element": bytes_e},
         "roofline_step": {"slower_of": "fp64" if t_fp64 >= t_hbm else "hbm", "fp64_tflops": step_tf, "fp64_frac": step_tf / fp64_peak,
                           "hbm_gbs": step_gbs, "hbm_frac": step_gbs / hbm_peak, "hbm_peak": hbm_peak, "hbm_peak_source": peak_src,

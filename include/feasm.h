@@ -160,8 +160,9 @@ int64_t feasm_distribute_dofs(int npe, int64_t n_elem, int64_t n_nodes, const ui
 
 /* ---- instrumentation ---------------------------------------------------------------------------- */
 /* Milliseconds of the kernels of the last feasm_assemble, measured with CUDA events on the context's stream:
- * [0] element kernel, [1] scatter/row reduction, [2] whole call.  Also the number of kernel launches. */
-int feasm_last_timing(feasm_ctx* ctx, float ms[3], int* launches);
+ * [0] element kernel, [1] scatter/row reduction, [2] whole call, [3] element-level constraint pass.  Also the
+ * number of kernel launches. */
+int feasm_last_timing(feasm_ctx* ctx, float ms[4], int* launches);
 /* FP64 pipe peaks of this device, measured now (register-resident DFMA chain and mma.sync.m8n8k4.f64 chain), in
  * TFLOP/s: the FP64 denominators of the roofline bench.py reports (MEASURED_PEAKS.json has no FP64 entry). */
 int feasm_measure_fp64_peaks(feasm_ctx* ctx, double* dfma_tflops, double* dmma_tflops);

@@ -264,10 +264,10 @@ class Context:
         return self.L.feasm_stream(self.h)
 
     def last_timing(self):
-        ms = (C.c_float * 3)()
+        ms = (C.c_float * 4)()
         n = C.c_int()
         self._ck(self.L.feasm_last_timing(self.h, ms, C.byref(n)))
-        return [ms[0], ms[1], ms[2]], n.value
+        return [ms[0], ms[1], ms[2], ms[3]], n.value
 
     def measure_fp64_peaks(self):
         a, b = C.c_double(), C.c_double()

@@ -38,7 +38,6 @@ void drop_maps(feasm_ctx* ctx) {
   release(ctx->d_inc_ptr);
   release(ctx->d_inc);
   release(ctx->d_kf);
-  release(ctx->d_batch_need);
 }
 
 int ensure_tables(feasm_ctx* ctx, int qorder) {
@@ -116,9 +115,7 @@ int feasm_create(int device, feasm_ctx** out) {
   ctx->device = device;
   ctx->sm_count = prop.multiProcessorCount;
   ctx->smem_optin = prop.sharedMemPerBlockOptin;
-  int prio_lo = 0, prio_hi = 0;  // the main stream outranks stream2 (chunked pipeline): element CTAs are placed first
-  cudaDeviceGetStreamPriorityRange(&prio_lo, &prio_hi);
-  if ((e = cudaStreamCreateWithPriority(&ctx->stream, cudaStreamNonBlocking, prio_hi)) != cudaSuccess) {
+  if ((e = cudaStreamCreateWithFlags(&ctx->stream, cudaStreamNonBlocking)) != cudaSuccess) {
     delete ctx;
     return feasm_fail(nullptr, FEASM_ERR_CUDA, cudaGetErrorString(e));
   }
@@ -140,10 +137,8 @@ void feasm_destroy(feasm_ctx* ctx) {
   release(ctx->d_xyz); release(ctx->d_conn); release(ctx->d_elem_dofs); release(ctx->d_gid);
   release(ctx->d_con_flag); release(ctx->d_con_val); release(ctx->d_row_ptr); release(ctx->d_col_idx);
   release(ctx->d_values); release(ctx->d_rhs); release(ctx->d_flags); release(ctx->d_tab); release(ctx->d_f);
-  release(ctx->d_sync); release(ctx->d_send_slots); release(ctx->d_recv_slots); release(ctx->d_send_buf); release(ctx->d_recv_buf);
+  release(ctx->d_send_slots); release(ctx->d_recv_slots); release(ctx->d_send_buf); release(ctx->d_recv_buf);
   for (auto& ev : ctx->ev) if (ev) cudaEventDestroy(ev);
-  for (auto& ev : ctx->chunk_ev) cudaEventDestroy(ev);
-  if (ctx->stream2) cudaStreamDestroy(ctx->stream2);
   cudaStreamDestroy(ctx->stream);
   delete ctx;
 }
@@ -280,8 +275,6 @@ int feasm_prepare(feasm_ctx* ctx) {
   if (rc) return rc;
   rc = feasm_build_pos(ctx);
   if (rc) return rc;
-  rc = feasm_build_batch_need(ctx);
-  if (rc) return rc;
   ctx->prepared = true;
   return FEASM_OK;
 }
@@ -307,60 +300,12 @@ int feasm_assemble(feasm_ctx* ctx, const feasm_params* params) {
     if (rc) return rc;
     ++launches;
   }
-  // FEASM_FUSED=1: one persistent kernel with element and reduction warps (experimental; slower than two kernels so far)
-  static const bool want_fused = getenv("FEASM_FUSED") && atoi(getenv("FEASM_FUSED")) >= 1;
-  static const int n_chunks = getenv("FEASM_CHUNKS") ? atoi(getenv("FEASM_CHUNKS")) : 0;
-  rc = want_fused ? feasm_launch_fused(ctx, *params, d_f) : 1;
-  if (rc < 0) return rc;
-  if (rc == FEASM_OK) {
-    --launches;
-    FEASM_CUDA(ctx, cudaEventRecord(ctx->ev[1], ctx->stream));
-  } else if (n_chunks > 1 && ctx->n_elem >= 2 * (int64_t)n_chunks && !ctx->h_need_pm.empty()) {
-    // Chunked pipeline: the element kernel of chunk c+1 (FP64-pipe bound, on ctx->stream) runs beside the row
-    // reduction of the rows chunk c completed (HBM / issue bound, on stream2).  A row is reduced by one launch only,
-    // after all of its contributors: same sums, same order as the unchunked path.
-    if (!ctx->stream2) {
-      int lo = 0, hi = 0;
-      FEASM_CUDA(ctx, cudaDeviceGetStreamPriorityRange(&lo, &hi));
-      FEASM_CUDA(ctx, cudaStreamCreateWithPriority(&ctx->stream2, cudaStreamNonBlocking, lo));
-    }
-    while ((int)ctx->chunk_ev.size() < n_chunks + 1) {
-      cudaEvent_t ev;
-      FEASM_CUDA(ctx, cudaEventCreateWithFlags(&ev, cudaEventDisableTiming));
-      ctx->chunk_ev.push_back(ev);
-    }
-    int64_t row0 = 0;
-    launches = launches - 2;
-    for (int c = 0; c < n_chunks; ++c) {
-      const int64_t e0 = ctx->n_elem * c / n_chunks, e1 = ctx->n_elem * (c + 1) / n_chunks;
-      rc = feasm_launch_element_kernel(ctx, *params, d_f, e0, e1, ctx->d_kf + (size_t)e0 * ctx->nd * rs, rs, params->constrain);
-      if (rc) return rc;
-      ++launches;
-      FEASM_CUDA(ctx, cudaEventRecord(ctx->chunk_ev[c], ctx->stream));
-      int64_t row1 = ctx->n_rows;
-      if (c + 1 < n_chunks) {
-        const auto it = std::upper_bound(ctx->h_need_pm.begin(), ctx->h_need_pm.end(), (uint32_t)e1);
-        row1 = std::min<int64_t>(ctx->n_rows, 32 * (int64_t)(it - ctx->h_need_pm.begin()));
-      }
-      if (row1 > row0) {
-        FEASM_CUDA(ctx, cudaStreamWaitEvent(ctx->stream2, ctx->chunk_ev[c], 0));
-        rc = feasm_launch_row_reduce(ctx, nullptr, row1, ctx->stream2, row0);
-        if (rc) return rc;
-        ++launches;
-        row0 = row1;
-      }
-    }
-    FEASM_CUDA(ctx, cudaEventRecord(ctx->ev[1], ctx->stream));
-    FEASM_CUDA(ctx, cudaEventRecord(ctx->chunk_ev[n_chunks], ctx->stream2));
-    FEASM_CUDA(ctx, cudaStreamWaitEvent(ctx->stream, ctx->chunk_ev[n_chunks], 0));
-  } else {
-    rc = feasm_launch_element_kernel(ctx, *params, d_f, 0, ctx->n_elem, ctx->d_kf, rs, params->constrain);
-    if (rc) return rc;
-    FEASM_CUDA(ctx, cudaEventRecord(ctx->ev[1], ctx->stream));
-    static const bool skip_rr = getenv("FEASM_SKIP_RR") != nullptr;  // timing experiments only
-    rc = skip_rr ? 0 : feasm_launch_row_reduce(ctx, nullptr, ctx->n_rows, ctx->stream);
-    if (rc) return rc;
-  }
+  rc = feasm_launch_element_kernel(ctx, *params, d_f, 0, ctx->n_elem, ctx->d_kf, rs, params->constrain);
+  if (rc) return rc;
+  if (ctx->n_con_elems > 0) ++launches;
+  FEASM_CUDA(ctx, cudaEventRecord(ctx->ev[1], ctx->stream));
+  rc = feasm_launch_row_reduce(ctx, nullptr, ctx->n_rows, ctx->stream);
+  if (rc) return rc;
   FEASM_CUDA(ctx, cudaEventRecord(ctx->ev[2], ctx->stream));
   ctx->last_launches = launches;
   return FEASM_OK;
@@ -372,10 +317,11 @@ int feasm_synchronize(feasm_ctx* ctx) {
   return check_flags(ctx);
 }
 
-int feasm_last_timing(feasm_ctx* ctx, float ms[3], int* launches) {
+int feasm_last_timing(feasm_ctx* ctx, float ms[4], int* launches) {
   if (!ctx) return FEASM_ERR_ARG;
   FEASM_CUDA(ctx, cudaEventSynchronize(ctx->ev[2]));
-  cudaEventElapsedTime(&ctx->last_ms[0], ctx->ev[0], ctx->ev[1]);
+  cudaEventElapsedTime(&ctx->last_ms[0], ctx->ev[0], ctx->ev[3]);
+  cudaEventElapsedTime(&ctx->last_ms[3], ctx->ev[3], ctx->ev[1]);
   cudaEventElapsedTime(&ctx->last_ms[1], ctx->ev[1], ctx->ev[2]);
   cudaEventElapsedTime(&ctx->last_ms[2], ctx->ev[0], ctx->ev[2]);
   if (ms) std::memcpy(ms, ctx->last_ms, sizeof(ctx->last_ms));

@@ -5,9 +5,8 @@
 #include "feasm_internal.h"
 
 namespace {
-// What the element kernels need to apply Dirichlet constraints in place (elem_flag == nullptr: none).
+// What the element-level constraint pass needs.
 struct ElemConArgs {
-  const uint8_t* elem_flag;   // [n_elem] element touches a constrained dof
   const uint32_t* elem_dofs;  // [n_elem][nd]
   const uint8_t* con_flag;    // [n_rows]
   const double* con_val;      // [n_rows]

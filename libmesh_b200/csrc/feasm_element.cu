@@ -21,8 +21,7 @@
 
 namespace {
 template <int NPE, int NQ, int WARPS, int RS>
-// (the 8-warp variant is held to the 12-warp register budget so that reduction CTAs fit beside it: chunked pipeline)
-__global__ void __launch_bounds__(WARPS == 8 ? 384 : WARPS * 32, 1)
+__global__ void __launch_bounds__(WARPS * 32, 1)
 k_elem_poisson(const double* __restrict__ xyz, const uint32_t* __restrict__ conn, const double* __restrict__ tab,
                int forcing, const double* __restrict__ f_tab, int64_t e0, int64_t e1, double* __restrict__ kf, int rs_rt,
                int* flags) {
@@ -263,7 +262,6 @@ static int launch_element_kernel(feasm_ctx* ctx, const feasm_params& p, const do
     if (ctx->elem_type == FEASM_HEX27 && ctx->tab_nq == 27) {
       static const int warps = getenv("FEASM_ELEM_WARPS") ? atoi(getenv("FEASM_ELEM_WARPS")) : 12;  // tuning knob
       if (warps == 16) return launch_poisson<27, 27, 16>(ctx, p, d_f, e0, e1, d_kf, rs);
-      if (warps == 8) return launch_poisson<27, 27, 8>(ctx, p, d_f, e0, e1, d_kf, rs);
       if (rs == 32) return launch_poisson<27, 27, 12, 32>(ctx, p, d_f, e0, e1, d_kf, rs);  // 256 B records (uint8 positions)
       return launch_poisson<27, 27, 12>(ctx, p, d_f, e0, e1, d_kf, rs);
     }
@@ -286,13 +284,13 @@ static int launch_element_kernel(feasm_ctx* ctx, const feasm_params& p, const do
 
 int feasm_launch_element_kernel(feasm_ctx* ctx, const feasm_params& p, const double* d_f, int64_t e0, int64_t e1,
                                 double* d_kf, int rs, int constrain_mode) {
-  static const int rs_env = getenv("FEASM_ELEM_RS") ? atoi(getenv("FEASM_ELEM_RS")) : 0;  // timing experiment only (wrong results)
-  int rc = launch_element_kernel(ctx, p, d_f, e0, e1, d_kf, rs_env ? rs_env : rs);
+  int rc = launch_element_kernel(ctx, p, d_f, e0, e1, d_kf, rs);
   if (rc) return rc;
+  FEASM_CUDA(ctx, cudaEventRecord(ctx->ev[3], ctx->stream));  // feasm_last_timing: element kernel | constraint pass
   // Dirichlet constraints on the few elements that touch a constrained dof, as the reference applies them to Ke/Fe
   // before add_matrix (constrain_mode < 0: leave Ke/Fe unconstrained)
   if (constrain_mode >= 0 && ctx->n_con_elems > 0) {
-    const ElemConArgs con{ctx->d_elem_flag, ctx->d_elem_dofs, ctx->d_con_flag, ctx->d_con_val, constrain_mode};
+    const ElemConArgs con{ctx->d_elem_dofs, ctx->d_con_flag, ctx->d_con_val, constrain_mode};
     const size_t per_warp = sizeof(double) * ctx->nd * feasm_ldr(ctx->nd);
     int warps = (int)(32768 / per_warp);
     warps = warps < 1 ? 1 : (warps > 8 ? 8 : warps);

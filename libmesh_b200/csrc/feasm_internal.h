@@ -83,12 +83,6 @@ struct feasm_ctx {
   uint64_t* d_inc_ptr = nullptr;  // [n_rows+1]
   uint32_t* d_inc = nullptr;      // [n_elem*nd] incidence ids e*nd + a, ascending within a row
   uint32_t max_inc = 0;
-  uint32_t* d_batch_need = nullptr;  // [ceil(n_rows/32)]: 1 + largest element id contributing to the batch of 32 rows
-  uint32_t* d_sync = nullptr;        // fused kernel: ticket counter + per-wave completion counters
-  size_t sync_cap = 0;
-  std::vector<uint32_t> h_need_pm;   // prefix maximum of batch_need (host): rows below 32*(b+1) are complete once elements [0, pm[b]) are
-  cudaStream_t stream2 = nullptr;    // the row reduction of chunk c runs here while ctx->stream computes chunk c+1
-  std::vector<cudaEvent_t> chunk_ev;
 
   // element buffers
   double* d_kf = nullptr;  // element records [n_elem][nd][feasm_recb bytes]
@@ -112,7 +106,7 @@ struct feasm_ctx {
   double* d_send_buf = nullptr;
   double* d_recv_buf = nullptr;
 
-  float last_ms[3] = {0, 0, 0};
+  float last_ms[4] = {0, 0, 0, 0};
   int last_launches = 0;
 };
 
@@ -135,9 +129,6 @@ int feasm_build_pos(feasm_ctx* ctx);
 int feasm_launch_element_kernel(feasm_ctx* ctx, const feasm_params& p, const double* d_f, int64_t e0, int64_t e1,
                                 double* d_kf, int rs, int constrain_mode);
 int feasm_launch_elem_flags(feasm_ctx* ctx);
-// feasm_fused.cu
-int feasm_launch_fused(feasm_ctx* ctx, const feasm_params& p, const double* d_f);
-int feasm_build_batch_need(feasm_ctx* ctx);
 // d_row_list == nullptr: every row; else the n_list rows listed
 int feasm_launch_row_reduce(feasm_ctx* ctx, const uint32_t* d_row_list, int64_t n_list, cudaStream_t stream, int64_t row0 = 0);
 int feasm_launch_pack(feasm_ctx* ctx);

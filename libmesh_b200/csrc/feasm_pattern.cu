@@ -140,21 +140,6 @@ __global__ void k_build_pos(const uint32_t* __restrict__ elem_dofs, const uint32
   *pos = (PosT)lo;
 }
 
-// batch_need[b] = 1 + the largest element id that contributes to rows [32b, 32b+32): incidence lists are ascending, so
-// the last entry of a row is its latest contributor.
-__global__ void k_batch_need(const uint64_t* __restrict__ inc_ptr, const uint32_t* __restrict__ inc, int nd, int64_t n_rows,
-                             int64_t n_batches, uint32_t* __restrict__ need) {
-  const int64_t b = blockIdx.x * (int64_t)blockDim.x + threadIdx.x;
-  if (b >= n_batches) return;
-  uint32_t mx = 0;
-  for (int64_t r = b * 32; r < n_rows && r < b * 32 + 32; ++r)
-    if (inc_ptr[r + 1] > inc_ptr[r]) {
-      const uint32_t e1 = inc[inc_ptr[r + 1] - 1] / (uint32_t)nd + 1;
-      mx = e1 > mx ? e1 : mx;
-    }
-  need[b] = mx;
-}
-
 inline unsigned grid_for(uint64_t n, int block) { return (unsigned)((n + block - 1) / block); }
 
 }  // namespace
@@ -268,20 +253,5 @@ int feasm_build_pos(feasm_ctx* ctx) {
   FEASM_CUDA(ctx, cudaMemcpyAsync(flags, ctx->d_flags, sizeof(flags), cudaMemcpyDeviceToHost, ctx->stream));
   FEASM_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
   if (flags[1]) return feasm_fail(ctx, FEASM_ERR_PATTERN, "element couples dofs that are not in the sparsity pattern");
-  return FEASM_OK;
-}
-
-int feasm_build_batch_need(feasm_ctx* ctx) {
-  const int64_t nb = (ctx->n_rows + 31) / 32;
-  if (ctx->d_batch_need) cudaFree(ctx->d_batch_need);
-  ctx->d_batch_need = nullptr;
-  FEASM_CUDA(ctx, cudaMalloc(&ctx->d_batch_need, sizeof(uint32_t) * (nb ? nb : 1)));
-  if (nb) k_batch_need<<<grid_for(nb, 128), 128, 0, ctx->stream>>>(ctx->d_inc_ptr, ctx->d_inc, ctx->nd, ctx->n_rows, nb, ctx->d_batch_need);
-  FEASM_CUDA(ctx, cudaGetLastError());
-  // host copy of the prefix maximum: the chunked pipeline of feasm_assemble cuts row ranges with it
-  ctx->h_need_pm.resize(nb);
-  if (nb) FEASM_CUDA(ctx, cudaMemcpyAsync(ctx->h_need_pm.data(), ctx->d_batch_need, sizeof(uint32_t) * nb, cudaMemcpyDeviceToHost, ctx->stream));
-  FEASM_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
-  for (int64_t b = 1; b < nb; ++b) ctx->h_need_pm[b] = std::max(ctx->h_need_pm[b], ctx->h_need_pm[b - 1]);
   return FEASM_OK;
 }

@@ -1,5 +1,5 @@
-// feasm_rr_dev.cuh — device code of the row reduction shared by feasm_scatter.cu (stand-alone kernel) and
-// feasm_fused.cu (element + row-reduction warps in one persistent kernel).  See feasm_scatter.cu for the design.
+// feasm_rr_dev.cuh — device code of the row reduction (feasm_scatter.cu): shared-memory helpers and the per-batch
+// routine one warp runs.
 #ifndef FEASM_RR_DEV_CUH
 #define FEASM_RR_DEV_CUH
 #include "feasm_internal.h"

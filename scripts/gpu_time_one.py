@@ -22,5 +22,5 @@ for _ in range(8):
     ctx.assemble(p); ms, nl = ctx.last_timing()
     best = ms if best is None or ms[2] < best[2] else best
 ne = conn.shape[0]
-print(f'{sys.argv[1]} n={n}: elem {best[0]:.3f} ms, row reduce {best[1]:.3f} ms, total {best[2]:.3f} ms -> {ne/best[2]*1e3/1e6:.2f} Melem/s')
+print(f'{sys.argv[1]} n={n}: elem {best[0]:.3f} ms, constrain {best[3]:.3f} ms, row reduce {best[1]:.3f} ms, total {best[2]:.3f} ms -> {ne/best[2]*1e3/1e6:.2f} Melem/s')
 ctx.close()
