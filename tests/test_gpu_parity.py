@@ -244,3 +244,73 @@ def test_elasticity_ex6(name, etype, dims, skew):
         t[var * (nd // 3):(var + 1) * (nd // 3)] = 1.0
         assert np.abs(K @ t).max() < 1e-12 * np.abs(K).max()
     ctx.close()
+
+
+def _superset_pattern(rp, ci, n_rows, dense_rows=(), extra_rows=0):
+    """A host pattern that contains the Graph and more: `dense_rows` get every column, `extra_rows` empty rows are
+    appended (dofs no element touches).  Returns (row_ptr, col_idx, index of every original entry in the new arrays)."""
+    rows = []
+    for r in range(n_rows):
+        cols = ci[rp[r]:rp[r + 1]]
+        rows.append(np.arange(n_rows + extra_rows, dtype=np.uint32) if r in dense_rows else cols)
+    rows += [np.zeros(0, np.uint32)] * extra_rows
+    rp2 = np.zeros(len(rows) + 1, np.uint64)
+    rp2[1:] = np.cumsum([len(c) for c in rows])
+    ci2 = np.concatenate(rows).astype(np.uint32)
+    where = np.concatenate([rp2[r] + np.searchsorted(rows[r], ci[rp[r]:rp[r + 1]]) for r in range(n_rows)]).astype(np.int64)
+    return rp2, ci2, where
+
+
+def test_rows_without_contributors_and_long_row_fallback():
+    """Host pattern (update_sparsity_pattern route) that is a superset of the Graph: (1) trailing dofs no element
+    touches give zero rows; (2) one dense row of > 7000 entries pushes the row image out of shared memory, so every row
+    goes through the global-memory fallback of the row reduction.  Values on the Graph entries equal the oracle's, all
+    other entries are exactly zero."""
+    F, O = _mods()
+    for etype, dims, dense, extra in [(27, (3, 3, 2), (), 5), (8, (20, 20, 19), (17,), 3)]:
+        m, s = make_case(etype, dims)
+        rp, ci = s.sparsity()
+        rp2, ci2, where = _superset_pattern(rp, ci, s.n_dofs, dense, extra)
+        xyz, conn, _ = m.arrays()
+        ed, _, _ = s.dofs()
+        cd, cv = s.constraints()
+        ctx = F.Context(0)
+        ctx.set_mesh(m.elem_type, xyz, conn)
+        ctx.set_dofs(ed, s.n_dofs + extra, n_vars=1)
+        ctx.set_constraints(cd, cv)
+        ctx.set_pattern(rp2, ci2)
+        q = 3 if etype == 8 else 0
+        f_tab, _ = s.forcing_at_qps(q)
+        vo, ro, _ = s.assemble(O.POISSON_EX4, qorder=q, forcing=O.FORCING_TABULATED, f_tab=f_tab)
+        ctx.assemble(F.make_params(F.POISSON, q, F.FORCING_TABULATED, f_host=f_tab))
+        v, r = ctx.get_values()
+        assert csr_parity_error(v[where], vo, rp) < PARITY_TOL
+        assert vec_parity_error(r[:s.n_dofs], ro) < PARITY_TOL
+        rest = np.ones(v.size, bool)
+        rest[where] = False
+        assert not v[rest].any() and not r[s.n_dofs:].any()
+        ctx.close()
+
+
+def test_cp_async_ring_fill_matches_bulk_copy(monkeypatch):
+    """FEASM_RR_BULK=0 selects the cp.async (LDGSTS) ring fill of the row reduction; same bits as the bulk-copy fill."""
+    import subprocess, sys, os, textwrap
+    code = textwrap.dedent("""
+        import sys, numpy as np
+        sys.path.insert(0, '.'); sys.path.insert(0, 'tests')
+        from test_gpu_parity import make_case, make_ctx, _mods
+        F, O = _mods()
+        m, s = make_case(27, (4, 3, 3))
+        ctx = make_ctx(m, s)
+        ctx.assemble(F.make_params(F.POISSON, 0, F.FORCING_EX4_FD))
+        v, r = ctx.get_values()
+        np.save(sys.argv[1], np.concatenate([v, r]))
+    """)
+    root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    outs = []
+    for bulk in ("1", "0"):
+        out = os.path.join(root, "build", f"rr_fill_{bulk}.npy")
+        os.makedirs(os.path.dirname(out), exist_ok=True)
+        subprocess.run([sys.executable, "-c", code, out], cwd=root, check=True, env={**os.environ, "FEASM_RR_BULK": bulk}, timeout=300)
+        outs.append(np.load(out))
+    assert np.array_equal(outs[0], outs[1])
