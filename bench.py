@@ -232,6 +232,25 @@ def run_ours(args):
                           "frac_of_slower_of": max(t_fp64, t_hbm) / (ms_per_step * 1e-3)},
         "fp64_peaks": fp64,
     }
+    # Extra (not the headline): the same step with feasm_params.affine_tensor = 1 — affine elements (all of build_cube)
+    # take the reference-tensor contraction instead of the quadrature loop; same result to 1e-12 (tests), fewer flops.
+    p_aff = F.make_params(F.POISSON, args.qorder, F.FORCING_EX4_FD, affine_tensor=1)
+    for _ in range(args.warmup):
+        ctx.assemble(p_aff, sync=False)
+    ctx.synchronize()
+    a0, a1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    a0.record(stream)
+    for _ in range(args.steps):
+        ctx.assemble(p_aff, sync=False)
+    a1.record(stream)
+    ctx.synchronize()
+    torch.cuda.synchronize()
+    aff_ms = a0.elapsed_time(a1) / args.steps
+    ctx.assemble(p_aff, sync=True)
+    ams, _ = ctx.last_timing()
+    out["affine_tensor_path"] = {"value": n_elem / (aff_ms * 1e-3), "unit": "elements/s", "ms_per_step": aff_ms,
+                                 "kernel_ms": {"element": ams[0], "constrain": ams[3], "row_reduce": ams[1]},
+                                 "note": "opt-in (feasm_params.affine_tensor); the headline value above runs the reference's quadrature loop on every element"}
     if not args.no_cpu:
         out["cpu_baseline"] = cpu_baseline(etype, args.qorder, threads=os.cpu_count() or 1, budget_s=12.0)
     ctx.close()

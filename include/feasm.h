@@ -67,6 +67,9 @@ typedef struct feasm_params {
   double young_modulus;  /* elasticity; 0 = the example's E = 1 */
   double poisson_ratio;  /* elasticity; 0 = the example's nu = 0.3 */
   double body_force[3];  /* elasticity; all zero = the example's (0,0,-1) */
+  int affine_tensor;     /* Poisson: 1 = elements with an affine map (Elem::has_affine_map) take the reference-tensor
+                            contraction Ke = sum_cc' G_cc' N_cc' (same Ke up to rounding, 1/5 of the FP64 work); the others
+                            still go through the quadrature loop.  0 = the reference's algorithm for every element */
 } feasm_params;
 
 /* ---- lifetime ------------------------------------------------------------------------------------ */

@@ -41,7 +41,7 @@ class Params(C.Structure):
     _fields_ = [
         ("problem", C.c_int), ("quadrature_order", C.c_int), ("forcing", C.c_int), ("constrain", C.c_int),
         ("f_host", C.c_void_p), ("f_device", C.c_void_p), ("young_modulus", C.c_double),
-        ("poisson_ratio", C.c_double), ("body_force", C.c_double * 3),
+        ("poisson_ratio", C.c_double), ("body_force", C.c_double * 3), ("affine_tensor", C.c_int),
     ]
 
 
@@ -107,7 +107,7 @@ def _c(a, dtype):
 
 
 def make_params(problem=POISSON, quadrature_order=0, forcing=FORCING_EX4_FD, constrain=CONSTRAIN_HETEROGENEOUS,
-                f_host=None, f_device=0, young_modulus=0.0, poisson_ratio=0.0, body_force=(0.0, 0.0, 0.0)):
+                f_host=None, f_device=0, young_modulus=0.0, poisson_ratio=0.0, body_force=(0.0, 0.0, 0.0), affine_tensor=0):
     p = Params()
     p.problem, p.quadrature_order, p.forcing, p.constrain = problem, quadrature_order, forcing, constrain
     p.f_host = None if f_host is None else f_host.ctypes.data
@@ -115,6 +115,7 @@ def make_params(problem=POISSON, quadrature_order=0, forcing=FORCING_EX4_FD, con
     p.young_modulus, p.poisson_ratio = young_modulus, poisson_ratio
     for i in range(3):
         p.body_force[i] = body_force[i]
+    p.affine_tensor = int(affine_tensor)
     p._keep = f_host
     return p
 

@@ -32,6 +32,7 @@ void release(T*& p) {
 void drop_maps(feasm_ctx* ctx) {
   ctx->prepared = false;
   release(ctx->d_elem_flag);
+  release(ctx->d_na_list);
   release(ctx->d_con_elems);
   ctx->n_con_elems = 0;
   ctx->elem_flag_valid = false;
@@ -303,6 +304,7 @@ int feasm_assemble(feasm_ctx* ctx, const feasm_params* params) {
   rc = feasm_launch_element_kernel(ctx, *params, d_f, 0, ctx->n_elem, ctx->d_kf, rs, params->constrain);
   if (rc) return rc;
   if (ctx->n_con_elems > 0) ++launches;
+  if (params->problem == FEASM_POISSON && params->affine_tensor) ++launches;  // the list kernel for non-affine elements
   FEASM_CUDA(ctx, cudaEventRecord(ctx->ev[1], ctx->stream));
   rc = feasm_launch_row_reduce(ctx, nullptr, ctx->n_rows, ctx->stream);
   if (rc) return rc;

@@ -81,6 +81,195 @@ int launch_poisson(feasm_ctx* ctx, const feasm_params& p, const double* d_f, int
 }
 
 
+// ---- affine elements: reference-tensor contraction (feasm_params.affine_tensor) ----------------------------------
+// On an element with an affine map (Elem::has_affine_map; FEMap::compute_affine_map, fe_map.C:1167-1244) the inverse
+// Jacobian is one matrix for all quadrature points and JxW_q = |J| w_q, so the quadrature loop of
+// introduction_ex4.C:464-467 factors:
+//   Ke(a,b) = sum_q JxW_q grad phi_a . grad phi_b = sum_{c,c'} G_cc' M_cc'(a,b),
+//   G_cc' = |J| sum_d dxi_c/dx_d dxi_c'/dx_d (3x3, symmetric),  M_cc'(a,b) = sum_q w_q d_c phi^_a(q) d_c' phi^_b(q).
+// The six tables N_k = M_cc (k = cc) and M_cc' + M_c'c (c < c') depend on the element TYPE only and live in shared
+// memory: an element costs 6 FMA per Ke entry instead of a 3*nq-long contraction (HEX27: 4.4 k instead of 59 k FMA), and
+// the kernel becomes a streaming write of the records.  Fe still needs the forcing at the quadrature points (same code
+// as the quadrature kernel).  Elements whose map is not affine are appended to a list and go through the quadrature
+// loop (k_elem_poisson_list).  Same Ke up to rounding: the parity tests hold it to the same 1e-12.
+template <int NPE, int NQ, int WARPS, int EB>
+__global__ void __launch_bounds__(WARPS * 32, 1)
+k_elem_poisson_affine(const double* __restrict__ xyz, const uint32_t* __restrict__ conn, const double* __restrict__ tab, int forcing,
+                      const double* __restrict__ f_tab, int64_t e0, int64_t e1, double* __restrict__ kf, int rs, int* flags,
+                      uint32_t* __restrict__ na_list, unsigned* na_count) {
+  using C = ElemCfg<NPE, NQ>;
+  constexpr int NLD = NPE + 1;  // row stride of the N tables
+  extern __shared__ double smem[];
+  double* s_tab = smem;
+  double* s_N = smem + C::TAB_SZ;  // [6][NPE][NLD]
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  for (int t = threadIdx.x; t < C::TAB; t += WARPS * 32) s_tab[t] = tab[t];
+  __syncthreads();
+  {
+    const double* s_qw = s_tab + 4 * NPE * NQ;
+    for (int t = threadIdx.x; t < 6 * NPE * NPE; t += WARPS * 32) {
+      const int k = t / (NPE * NPE), a = (t / NPE) % NPE, b = t % NPE;
+      const int c = k < 3 ? k : (k == 5 ? 1 : 0), cp = k < 3 ? k : (k == 3 ? 1 : 2);
+      const double* da = s_tab + (1 + c) * NPE * NQ;
+      const double* db = s_tab + (1 + cp) * NPE * NQ;
+      double m = 0.;
+      for (int q = 0; q < NQ; ++q) {
+        double term = da[a * NQ + q] * db[b * NQ + q];
+        if (c != cp) term += db[a * NQ + q] * da[b * NQ + q];
+        m += s_qw[q] * term;
+      }
+      s_N[(k * NPE + a) * NLD + b] = m;
+    }
+  }
+  double* X = s_N + 6 * NPE * NLD + (size_t)warp * C::WARP_DBL;
+  double* fw = X + C::X_SZ;
+  const double* s_phi = s_tab;
+  __syncthreads();
+
+  const int64_t stride = (int64_t)gridDim.x * WARPS;
+  int64_t e = e0 + (int64_t)blockIdx.x * WARPS + warp;
+  double nx = 0., ny = 0., nz = 0.;  // two-deep prefetch as in k_elem_poisson
+  uint32_t nnode = 0;
+  if (e < e1 && lane < NPE) {
+    const uint64_t node = conn[e * NPE + lane];
+    nx = xyz[node * 3]; ny = xyz[node * 3 + 1]; nz = xyz[node * 3 + 2];
+    if (e + stride < e1) nnode = conn[(e + stride) * NPE + lane];
+  }
+  // EB elements per pass: geometry and Fe one after the other, then ONE sweep over the N tables feeds all of them (the
+  // tables are 6*NPE*NPE*8 B of shared-memory reads per sweep; the LSU data pipe, not the FP64 pipe, bounds this kernel)
+  while (e < e1) {
+    double g[EB][6];
+    double* out[EB];
+#pragma unroll
+    for (int j = 0; j < EB; ++j) {
+      out[j] = nullptr;
+#pragma unroll
+      for (int k = 0; k < 6; ++k) g[j][k] = 0.;
+      if (e >= e1) continue;  // warp-uniform
+      if (lane < NPE) {
+        X[3 * lane] = nx; X[3 * lane + 1] = ny; X[3 * lane + 2] = nz;
+        if (e + stride < e1) {
+          const uint64_t node = nnode;
+          nx = xyz[node * 3]; ny = xyz[node * 3 + 1]; nz = xyz[node * 3 + 2];
+          if (e + 2 * stride < e1) nnode = conn[(e + 2 * stride) * NPE + lane];
+        }
+      }
+      __syncwarp();
+      double S[9], JxW, x, y, z;
+      const bool affine = geom_phase<NPE, NQ>(X, s_tab, lane, forcing == FEASM_FORCING_EX4_FD, flags, S, JxW, x, y, z);
+      if (!affine) {  // leave it to the quadrature loop
+        if (lane == 0) na_list[atomicAdd(na_count, 1u)] = (uint32_t)e;
+      } else {
+        double f = 0.;
+        if (forcing == FEASM_FORCING_EX4_FD) {
+          const bool big = !(fabs(x) + fabs(y) + fabs(z) < 2.e4);
+          f = __any_sync(0xffffffffu, big) ? ex4_forcing_lib(x, y, z) : ex4_forcing_t<true>(x, y, z);
+        } else if (forcing == FEASM_FORCING_TABULATED && lane < NQ) {
+          f = f_tab[e * NQ + lane];
+        }
+        fw[lane] = lane < NQ ? JxW * f : 0.;
+        __syncwarp();
+        // S = sqrt|J| * inverse-Jacobian rows (the same on every lane): G_cc' = sum_d S[c][d] S[c'][d]
+        g[j][0] = S[0] * S[0] + S[1] * S[1] + S[2] * S[2]; g[j][1] = S[3] * S[3] + S[4] * S[4] + S[5] * S[5];
+        g[j][2] = S[6] * S[6] + S[7] * S[7] + S[8] * S[8]; g[j][3] = S[0] * S[3] + S[1] * S[4] + S[2] * S[5];
+        g[j][4] = S[0] * S[6] + S[1] * S[7] + S[2] * S[8]; g[j][5] = S[3] * S[6] + S[4] * S[7] + S[5] * S[8];
+        out[j] = kf + (uint64_t)(e - e0) * (NPE * rs);
+        if (lane < NPE) {
+          double Fe = 0., f1 = 0., f2 = 0.;
+          if (forcing != FEASM_FORCING_NONE) {
+#pragma unroll
+            for (int q = 0; q + 2 < NQ; q += 3) {
+              Fe += fw[q] * s_phi[lane * NQ + q];
+              f1 += fw[q + 1] * s_phi[lane * NQ + q + 1];
+              f2 += fw[q + 2] * s_phi[lane * NQ + q + 2];
+            }
+#pragma unroll
+            for (int q = NQ - NQ % 3; q < NQ; ++q) Fe += fw[q] * s_phi[lane * NQ + q];
+            Fe = (Fe + f1) + f2;
+          }
+          out[j][lane * rs + NPE] = Fe;
+        }
+      }
+      __syncwarp();
+      e += stride;
+    }
+    if (lane < NPE) {
+      const double* Nl = s_N + lane;
+#pragma unroll 3
+      for (int a = 0; a < NPE; ++a) {
+        const double* r = Nl + a * NLD;
+        const double n0 = r[0], n1 = r[NPE * NLD], n2 = r[2 * NPE * NLD], n3 = r[3 * NPE * NLD], n4 = r[4 * NPE * NLD],
+                     n5 = r[5 * NPE * NLD];
+#pragma unroll
+        for (int j = 0; j < EB; ++j)
+          if (out[j])  // warp-uniform
+            out[j][a * rs + lane] = fma(g[j][5], n5, fma(g[j][4], n4, fma(g[j][3], n3, fma(g[j][2], n2, fma(g[j][1], n1, g[j][0] * n0)))));
+      }
+    }
+    __syncwarp();
+  }
+}
+
+// The quadrature kernel over a device-side element list (the non-affine leftovers of the kernel above).
+template <int NPE, int NQ, int WARPS>
+__global__ void __launch_bounds__(WARPS * 32, 1)
+k_elem_poisson_list(const double* __restrict__ xyz, const uint32_t* __restrict__ conn, const double* __restrict__ tab, int forcing,
+                    const double* __restrict__ f_tab, int64_t e0, double* __restrict__ kf, int rs, int* flags,
+                    const uint32_t* __restrict__ list, const unsigned* __restrict__ list_n) {
+  using C = ElemCfg<NPE, NQ>;
+  const unsigned n = *list_n;
+  if (n == 0) return;
+  extern __shared__ double smem[];
+  double* s_tab = smem;
+  double* s_tw = smem + C::TAB_SZ;
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  elem_load_tables<NPE, NQ>(s_tab, s_tw, tab, threadIdx.x, WARPS * 32);
+  double* X = s_tw + C::TW_SZ + (size_t)warp * C::WARP_DBL;
+  double* fw = X + C::X_SZ;
+  const double* twp = s_tw + (lane >> 2) * C::TS + (lane & 3);
+  __syncthreads();
+  for (unsigned i = blockIdx.x * WARPS + warp; i < n; i += gridDim.x * WARPS) {
+    const int64_t e = list[i];
+    if (lane < NPE) {
+      const uint64_t node = conn[e * NPE + lane];
+      X[3 * lane] = xyz[node * 3]; X[3 * lane + 1] = xyz[node * 3 + 1]; X[3 * lane + 2] = xyz[node * 3 + 2];
+    }
+    __syncwarp();
+    elem_process<NPE, NQ>(X, fw, s_tab, twp, lane, forcing, f_tab ? f_tab + e * NQ : nullptr, flags,
+                          kf + (uint64_t)(e - e0) * (NPE * rs), rs);
+    __syncwarp();
+  }
+}
+
+template <int NPE, int NQ, int WARPS, int LWARPS, int EB = 4>
+int launch_poisson_affine(feasm_ctx* ctx, const feasm_params& p, const double* d_f, int64_t e0, int64_t e1, double* d_kf, int rs) {
+  using C = ElemCfg<NPE, NQ>;
+  if (!ctx->d_na_list) FEASM_CUDA(ctx, cudaMalloc(&ctx->d_na_list, sizeof(uint32_t) * ((size_t)ctx->n_elem + 1)));
+  unsigned* d_count = ctx->d_na_list + ctx->n_elem;
+  FEASM_CUDA(ctx, cudaMemsetAsync(d_count, 0, sizeof(unsigned), ctx->stream));
+  {
+    const size_t smem = sizeof(double) * (size_t)(C::TAB_SZ + 6 * NPE * (NPE + 1) + WARPS * C::WARP_DBL);
+    auto kern = k_elem_poisson_affine<NPE, NQ, WARPS, EB>;
+    FEASM_CUDA(ctx, cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    int64_t blocks = (e1 - e0 + WARPS - 1) / WARPS;
+    if (blocks > ctx->sm_count) blocks = ctx->sm_count;
+    if (blocks < 1) blocks = 1;
+    kern<<<(unsigned)blocks, WARPS * 32, smem, ctx->stream>>>(ctx->d_xyz, ctx->d_conn, ctx->d_tab, p.forcing, d_f, e0, e1, d_kf, rs,
+                                                             ctx->d_flags, ctx->d_na_list, d_count);
+    FEASM_CUDA(ctx, cudaGetLastError());
+  }
+  {
+    const size_t smem = sizeof(double) * (size_t)C::SMEM_DBL(LWARPS);
+    auto kern = k_elem_poisson_list<NPE, NQ, LWARPS>;
+    FEASM_CUDA(ctx, cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    kern<<<(unsigned)ctx->sm_count, LWARPS * 32, smem, ctx->stream>>>(ctx->d_xyz, ctx->d_conn, ctx->d_tab, p.forcing, d_f, e0, d_kf, rs,
+                                                                     ctx->d_flags, ctx->d_na_list, d_count);
+    FEASM_CUDA(ctx, cudaGetLastError());
+  }
+  return FEASM_OK;
+}
+
+
 // ---- 3-variable isotropic linear elasticity (systems_of_equations_ex6.C:220-237) --------------------------------
 // Ke[(i,a),(k,b)] = sum_q JxW sum_jl C_ijkl dphi_b,l dphi_a,j with C_ijkl = l1 d_ij d_kl + l2 (d_ik d_jl + d_il d_jk)
 //                 = l1 P_ik[a][b] + l2 P_ki[a][b] + l2 d_ik (P_00 + P_11 + P_22)[a][b],
@@ -258,6 +447,12 @@ __global__ void k_constrain_list(const uint32_t* __restrict__ list, int n_list, 
 }
 
 static int launch_element_kernel(feasm_ctx* ctx, const feasm_params& p, const double* d_f, int64_t e0, int64_t e1, double* d_kf, int rs) {
+  if (p.problem == FEASM_POISSON && p.affine_tensor) {
+    if (ctx->elem_type == FEASM_HEX27 && ctx->tab_nq == 27) return launch_poisson_affine<27, 27, 16, 12, 2>(ctx, p, d_f, e0, e1, d_kf, rs);
+    if (ctx->elem_type == FEASM_HEX8 && ctx->tab_nq == 8) return launch_poisson_affine<8, 8, 16, 16>(ctx, p, d_f, e0, e1, d_kf, rs);
+    if (ctx->elem_type == FEASM_HEX8 && ctx->tab_nq == 27) return launch_poisson_affine<8, 27, 16, 16>(ctx, p, d_f, e0, e1, d_kf, rs);
+    if (ctx->elem_type == FEASM_TET10 && ctx->tab_nq == 14) return launch_poisson_affine<10, 14, 16, 16>(ctx, p, d_f, e0, e1, d_kf, rs);
+  }
   if (p.problem == FEASM_POISSON) {
     if (ctx->elem_type == FEASM_HEX27 && ctx->tab_nq == 27) {
       static const int warps = getenv("FEASM_ELEM_WARPS") ? atoi(getenv("FEASM_ELEM_WARPS")) : 12;  // tuning knob

@@ -84,6 +84,9 @@ struct feasm_ctx {
   uint32_t* d_inc = nullptr;      // [n_elem*nd] incidence ids e*nd + a, ascending within a row
   uint32_t max_inc = 0;
 
+  // elements the affine reference-tensor kernel left to the quadrature kernel (feasm_params.affine_tensor)
+  uint32_t* d_na_list = nullptr;  // [n_elem] element ids + the counter behind them
+
   // element buffers
   double* d_kf = nullptr;  // element records [n_elem][nd][feasm_recb bytes]
   int* d_flags = nullptr;  // [0] degenerate count, [1] pattern misses

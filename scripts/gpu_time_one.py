@@ -15,7 +15,7 @@ ctx.set_mesh(etype, xyz, conn); ctx.set_dofs(ed, nd)
 import os
 if not os.environ.get('NOCON'): ctx.set_constraints(base[bn], g)
 ctx.build_pattern(); ctx.prepare()
-p = F.make_params(F.POISSON, qorder, F.FORCING_EX4_FD)
+p = F.make_params(F.POISSON, qorder, F.FORCING_EX4_FD, affine_tensor=int(os.environ.get('AFFINE', '0')))
 for _ in range(3): ctx.assemble(p)
 best = None
 for _ in range(8):

@@ -20,7 +20,8 @@ g = np.cos(.5 * np.pi * xyz[bn, 0]) * np.sin(.5 * np.pi * xyz[bn, 1]) * np.cos(.
 ctx = F.Context(0)
 ctx.set_mesh(etype, xyz, conn); ctx.set_dofs(ed, nd); ctx.set_constraints(base[bn], g)
 ctx.build_pattern(); ctx.prepare()
-p = F.make_params(F.POISSON, 0, F.FORCING_EX4_FD)
+import os
+p = F.make_params(F.POISSON, 0, F.FORCING_EX4_FD, affine_tensor=int(os.environ.get('AFFINE', '0')))
 for _ in range(reps):
     ctx.assemble(p)
     print(ctx.last_timing())

@@ -314,3 +314,38 @@ def test_cp_async_ring_fill_matches_bulk_copy(monkeypatch):
         subprocess.run([sys.executable, "-c", code, out], cwd=root, check=True, env={**os.environ, "FEASM_RR_BULK": bulk}, timeout=300)
         outs.append(np.load(out))
     assert np.array_equal(outs[0], outs[1])
+
+
+AFFINE = [
+    ("hex27_ex4_6", 27, (6, 6, 6), None, 0),
+    ("hex27_skew", 27, (4, 4, 4), (1, 0.03, 12345), 0),   # every interior element non-affine: the list kernel does them
+    ("hex27_skewfunc", 27, (3, 3, 3), (0, 0.0, 0), 0),    # sheared but affine: full inverse Jacobian in G
+    ("hex27_box", 27, (3, 2, 4), None, 0),
+    ("hex8_q3", 8, (7, 5, 6), None, 3),
+    ("hex8_q5", 8, (6, 6, 6), None, 5),
+    ("tet10", 10, (3, 2, 2), None, 5),
+    ("tet10_skew", 10, (2, 2, 2), (1, 0.02, 99), 5),
+]
+
+
+@pytest.mark.parametrize("name,etype,dims,skew,qorder", AFFINE, ids=[c[0] for c in AFFINE])
+def test_affine_tensor_path_matches_the_quadrature_loop(name, etype, dims, skew, qorder):
+    """feasm_params.affine_tensor = 1: affine elements take Ke = sum G_cc' N_cc' (reference tensors), the others the
+    quadrature loop; the assembled system meets the same bar against the oracle, on element level and globally."""
+    F, O = _mods()
+    bounds = (-1, 1, -0.5, 0.7, 0, 3) if name == "hex27_box" else (-1, 1, -1, 1, -1, 1)
+    m, s = make_case(etype, dims, bounds=bounds, skew=skew)
+    ctx = make_ctx(m, s)
+    rp, _ = s.sparsity()
+    f_tab, _ = s.forcing_at_qps(qorder)
+    vo, ro, _ = s.assemble(O.POISSON_EX4, qorder=qorder, forcing=O.FORCING_TABULATED, f_tab=f_tab)
+    p = F.make_params(F.POISSON, qorder, F.FORCING_TABULATED, f_host=f_tab, affine_tensor=1)
+    ctx.assemble(p)
+    v, r = ctx.get_values()
+    assert csr_parity_error(v, vo, rp) < PARITY_TOL
+    assert vec_parity_error(r, ro) < PARITY_TOL
+    Ko, Fo = s.element_matrices(O.POISSON_EX4, qorder=qorder, forcing=O.FORCING_TABULATED, f_tab=f_tab, constrained=False)
+    K, Fe = ctx.element_matrices(p, constrained=False)
+    assert dense_parity_error(K, Ko) < PARITY_TOL
+    assert vec_parity_error(Fe.ravel(), Fo.ravel()) < PARITY_TOL
+    ctx.close()
