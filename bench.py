@@ -251,6 +251,24 @@ def run_ours(args):
     out["affine_tensor_path"] = {"value": n_elem / (aff_ms * 1e-3), "unit": "elements/s", "ms_per_step": aff_ms,
                                  "kernel_ms": {"element": ams[0], "constrain": ams[3], "row_reduce": ams[1]},
                                  "note": "opt-in (feasm_params.affine_tensor); the headline value above runs the reference's quadrature loop on every element"}
+    # Extra: the step after the path — y = A x on the assembled matrix, against the HBM roofline
+    dx = torch.ones(P["n_dofs"], dtype=torch.float64, device="cuda")
+    dy = torch.empty_like(dx)
+    torch.cuda.synchronize()
+    for _ in range(3):
+        ctx.vector_mult(dx.data_ptr(), dy.data_ptr())
+    s0, s1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    s0.record(stream)
+    for _ in range(10):
+        ctx.vector_mult(dx.data_ptr(), dy.data_ptr())
+    s1.record(stream)
+    ctx.synchronize()
+    torch.cuda.synchronize()
+    spmv_ms = s0.elapsed_time(s1) / 10
+    spmv_bytes = nnz * 12 + P["n_dofs"] * 32  # values + col_idx, row_ptr, x, y
+    out["vector_mult"] = {"ms": spmv_ms, "bytes": int(spmv_bytes), "gbs": spmv_bytes / (spmv_ms * 1e-3) / 1e9,
+                          "hbm_frac": spmv_bytes / (spmv_ms * 1e-3) / 1e9 / hbm_peak}
+    del dx, dy
     if not args.no_cpu:
         out["cpu_baseline"] = cpu_baseline(etype, args.qorder, threads=os.cpu_count() or 1, budget_s=12.0)
     ctx.close()

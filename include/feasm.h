@@ -137,6 +137,15 @@ double* feasm_device_values(feasm_ctx* ctx);                           /* device
 double* feasm_device_rhs(feasm_ctx* ctx);
 void* feasm_stream(feasm_ctx* ctx);                                    /* cudaStream_t */
 
+/* ---- the step after the path: SpMV and a Krylov solve on the device matrix ----- */
+/* SparseMatrix::vector_mult (sparse_matrix.h:579-587): y = A x, device pointers of n_rows doubles, on feasm_stream. */
+int feasm_vector_mult(feasm_ctx* ctx, const double* d_x, double* d_y);
+int feasm_vector_mult_host(feasm_ctx* ctx, const double* x, double* y); /* same with host arrays (H2D, product, D2H) */
+/* LinearSolver::solve with CG + Jacobi preconditioning on the assembled system A x = rhs.  x0 (host, may be NULL =
+ * zero) is the initial guess, x (host) receives the solution; stops at ||r|| <= rel_tol ||b|| or max_its. */
+int feasm_cg_solve(feasm_ctx* ctx, double rel_tol, int max_its, const double* x0, double* x, int* iterations,
+                   double* rel_residual);
+
 /* ---- multi-GPU ghost rows (DistributedVector::close / MatAssemblyBegin-End) -------------------- */
 /* After feasm_prepare on every rank: describe, per peer, which of this rank's ghost-row slots go to the peer
  * and which owned slots receive the peer's contributions.  send_slots / recv_slots index the CSR value array

@@ -27,7 +27,7 @@ SYMBOLS = [
     "feasm_synchronize", "feasm_element_matrices", "feasm_zero", "feasm_add_matrix", "feasm_add_vector",
     "feasm_get_values", "feasm_device_values", "feasm_device_rhs", "feasm_stream", "feasm_set_exchange_plan",
     "feasm_pack_ghost", "feasm_recv_buffer", "feasm_unpack_ghost", "feasm_cube_sizes", "feasm_build_cube",
-    "feasm_distribute_dofs", "feasm_last_timing", "feasm_measure_fp64_peaks",
+    "feasm_distribute_dofs", "feasm_last_timing", "feasm_measure_fp64_peaks", "feasm_vector_mult", "feasm_vector_mult_host", "feasm_cg_solve",
 ]
 
 
@@ -90,6 +90,9 @@ def lib():
         "feasm_distribute_dofs": (i64, [i32, i64, i64, vp, i32, i32, vp, vp, vp, vp]),
         "feasm_last_timing": (i32, [vp, vp, C.POINTER(i32)]),
         "feasm_measure_fp64_peaks": (i32, [vp, C.POINTER(C.c_double), C.POINTER(C.c_double)]),
+        "feasm_vector_mult": (i32, [vp, vp, vp]),
+        "feasm_vector_mult_host": (i32, [vp, vp, vp]),
+        "feasm_cg_solve": (i32, [vp, C.c_double, i32, vp, vp, C.POINTER(i32), C.POINTER(C.c_double)]),
     }
     for name, (res, args) in sig.items():
         fn = getattr(L, name)
@@ -269,6 +272,23 @@ class Context:
         n = C.c_int()
         self._ck(self.L.feasm_last_timing(self.h, ms, C.byref(n)))
         return [ms[0], ms[1], ms[2], ms[3]], n.value
+
+    def vector_mult(self, d_x, d_y):
+        """y = A x with device pointers (ints) of n_rows doubles."""
+        self._ck(self.L.feasm_vector_mult(self.h, C.c_void_p(d_x), C.c_void_p(d_y)))
+
+    def vector_mult_host(self, x):
+        xc = _c(x, np.float64)
+        y = np.empty(self.n_rows, np.float64)
+        self._ck(self.L.feasm_vector_mult_host(self.h, _p(xc), _p(y)))
+        return y
+
+    def cg_solve(self, rel_tol=1e-12, max_its=10000, x0=None):
+        x = np.empty(self.n_rows, np.float64)
+        x0c = _c(x0, np.float64)
+        its, rel = C.c_int(), C.c_double()
+        self._ck(self.L.feasm_cg_solve(self.h, rel_tol, max_its, _p(x0c), _p(x), C.byref(its), C.byref(rel)))
+        return x, its.value, rel.value
 
     def measure_fp64_peaks(self):
         a, b = C.c_double(), C.c_double()

@@ -1,0 +1,210 @@
+// feasm_solve.cu — the step right after the assembly path: y = A x on the assembled CSR matrix and
+// a Jacobi-preconditioned conjugate-gradient solve, so a LinearImplicitSystem::solve can finish without copying the
+// matrix back to the host.
+//
+//   feasm_vector_mult  = SparseMatrix::vector_mult (include/numerics/sparse_matrix.h:579-587)
+//   feasm_cg_solve     = LinearSolver<T>::solve with CG + JACOBI_PRECOND (include/solvers/linear_solver.h,
+//                        src/solvers/: the default Krylov route of the library back-ends)
+//
+// Everything is deterministic: the SpMV sums a row in column order by one warp with a fixed shuffle tree, the dot
+// products use a fixed two-level reduction (no atomics).  Single rank (column ids = local row ids).
+#include <cmath>
+#include <vector>
+
+#include "feasm_internal.h"
+
+namespace {
+
+// One warp per row: lanes stride over the row's entries, fixed shuffle tree.  HBM-bound: 12 B per non-zero.
+__global__ void k_spmv(const uint64_t* __restrict__ row_ptr, const uint32_t* __restrict__ col_idx, const double* __restrict__ values,
+                       const double* __restrict__ x, int64_t n_rows, double* __restrict__ y) {
+  const int lane = threadIdx.x & 31;
+  const int64_t r = (blockIdx.x * (int64_t)blockDim.x + threadIdx.x) >> 5;
+  if (r >= n_rows) return;
+  const uint64_t p0 = row_ptr[r], p1 = row_ptr[r + 1];
+  double s = 0.;
+  for (uint64_t k = p0 + lane; k < p1; k += 32) s += __ldcs(values + k) * x[__ldcs(col_idx + k)];
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) s += __shfl_xor_sync(0xffffffffu, s, o);
+  if (lane == 0) y[r] = s;
+}
+
+// 1 / A(r,r) (binary search of the diagonal in the sorted row); rows without a diagonal entry get 1.
+__global__ void k_inv_diag(const uint64_t* __restrict__ row_ptr, const uint32_t* __restrict__ col_idx, const double* __restrict__ values,
+                           const uint32_t* __restrict__ gid, int64_t n_rows, double* __restrict__ dinv) {
+  const int64_t r = blockIdx.x * (int64_t)blockDim.x + threadIdx.x;
+  if (r >= n_rows) return;
+  const uint32_t col = gid ? gid[r] : (uint32_t)r;
+  const uint32_t* c = col_idx + row_ptr[r];
+  int lo = 0, hi = (int)(row_ptr[r + 1] - row_ptr[r]);
+  const int len = hi;
+  while (lo < hi) {
+    const int mid = (lo + hi) >> 1;
+    if (c[mid] < col) lo = mid + 1; else hi = mid;
+  }
+  const double d = (lo < len && c[lo] == col) ? values[row_ptr[r] + lo] : 1.;
+  dinv[r] = d != 0. ? 1. / d : 1.;
+}
+
+constexpr int DOT_BLOCK = 256, DOT_GRID = 592;  // 4 CTAs per SM; partials reduced by one CTA in a fixed order
+
+__device__ __forceinline__ double block_sum(double v, double* sh) {
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
+  if ((threadIdx.x & 31) == 0) sh[threadIdx.x >> 5] = v;
+  __syncthreads();
+  double t = 0.;
+  if (threadIdx.x < 32) {
+    t = threadIdx.x < (blockDim.x >> 5) ? sh[threadIdx.x] : 0.;
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) t += __shfl_xor_sync(0xffffffffu, t, o);
+  }
+  __syncthreads();
+  return t;  // valid on thread 0
+}
+
+// partial[b] = sum over this CTA's grid-stride slice of a[i]*b[i] (b == nullptr: a[i]*a[i]*w[i] when w given)
+__global__ void k_dot_partial(const double* __restrict__ a, const double* __restrict__ b, int64_t n, double* __restrict__ partial) {
+  __shared__ double sh[32];
+  double s = 0.;
+  for (int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; i < n; i += (int64_t)gridDim.x * blockDim.x) s += a[i] * b[i];
+  s = block_sum(s, sh);
+  if (threadIdx.x == 0) partial[blockIdx.x] = s;
+}
+__global__ void k_dot_final(const double* __restrict__ partial, int n, double* __restrict__ out) {
+  __shared__ double sh[32];
+  double s = 0.;
+  for (int i = threadIdx.x; i < n; i += blockDim.x) s += partial[i];
+  s = block_sum(s, sh);
+  if (threadIdx.x == 0) *out = s;
+}
+
+// x += alpha p; r -= alpha q; z = dinv .* r     (alpha = rz / pq read from device scalars)
+__global__ void k_cg_update(int64_t n, const double* __restrict__ rz, const double* __restrict__ pq, const double* __restrict__ p,
+                            const double* __restrict__ q, const double* __restrict__ dinv, double* __restrict__ x, double* __restrict__ r,
+                            double* __restrict__ z) {
+  const double alpha = *rz / *pq;
+  for (int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; i < n; i += (int64_t)gridDim.x * blockDim.x) {
+    x[i] += alpha * p[i];
+    const double ri = r[i] - alpha * q[i];
+    r[i] = ri;
+    z[i] = dinv[i] * ri;
+  }
+}
+// p = z + (rz_new / rz_old) p
+__global__ void k_cg_direction(int64_t n, const double* __restrict__ rz_new, const double* __restrict__ rz_old, const double* __restrict__ z,
+                               double* __restrict__ p) {
+  const double beta = *rz_new / *rz_old;
+  for (int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; i < n; i += (int64_t)gridDim.x * blockDim.x) p[i] = z[i] + beta * p[i];
+}
+// r = b - q; z = dinv .* r; p = z
+__global__ void k_cg_start(int64_t n, const double* __restrict__ b, const double* __restrict__ q, const double* __restrict__ dinv,
+                           double* __restrict__ r, double* __restrict__ z, double* __restrict__ p) {
+  for (int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; i < n; i += (int64_t)gridDim.x * blockDim.x) {
+    const double ri = b[i] - q[i];
+    r[i] = ri;
+    const double zi = dinv[i] * ri;
+    z[i] = zi;
+    p[i] = zi;
+  }
+}
+
+int spmv(feasm_ctx* ctx, const double* d_x, double* d_y) {
+  const unsigned grid = (unsigned)((ctx->n_rows * 32 + 255) / 256);
+  if (grid) k_spmv<<<grid, 256, 0, ctx->stream>>>(ctx->d_row_ptr, ctx->d_col_idx, ctx->d_values, d_x, ctx->n_rows, d_y);
+  FEASM_CUDA(ctx, cudaGetLastError());
+  return FEASM_OK;
+}
+
+int dot(feasm_ctx* ctx, const double* a, const double* b, int64_t n, double* d_partial, double* d_out) {
+  k_dot_partial<<<DOT_GRID, DOT_BLOCK, 0, ctx->stream>>>(a, b, n, d_partial);
+  k_dot_final<<<1, DOT_BLOCK, 0, ctx->stream>>>(d_partial, DOT_GRID, d_out);
+  FEASM_CUDA(ctx, cudaGetLastError());
+  return FEASM_OK;
+}
+
+}  // namespace
+
+int feasm_vector_mult(feasm_ctx* ctx, const double* d_x, double* d_y) {
+  if (!ctx || !ctx->d_values) return feasm_fail(ctx, FEASM_ERR_STATE, "no matrix");
+  if (!d_x || !d_y) return feasm_fail(ctx, FEASM_ERR_ARG, "null vector");
+  if (ctx->d_gid || ctx->n_owned != ctx->n_rows) return feasm_fail(ctx, FEASM_ERR_STATE, "vector_mult: one rank per matrix in this version");
+  FEASM_CUDA(ctx, cudaSetDevice(ctx->device));
+  return spmv(ctx, d_x, d_y);
+}
+
+int feasm_vector_mult_host(feasm_ctx* ctx, const double* x, double* y) {
+  if (!ctx || !ctx->d_values) return feasm_fail(ctx, FEASM_ERR_STATE, "no matrix");
+  if (!x || !y) return feasm_fail(ctx, FEASM_ERR_ARG, "null vector");
+  FEASM_CUDA(ctx, cudaSetDevice(ctx->device));
+  const size_t nb = sizeof(double) * (size_t)(ctx->n_rows ? ctx->n_rows : 1);
+  double* w = nullptr;
+  FEASM_CUDA(ctx, cudaMalloc(&w, 2 * nb));
+  int rc = FEASM_OK;
+  if (cudaMemcpyAsync(w, x, nb, cudaMemcpyHostToDevice, ctx->stream) != cudaSuccess) rc = feasm_fail(ctx, FEASM_ERR_CUDA, "H2D x");
+  if (!rc) rc = feasm_vector_mult(ctx, w, w + ctx->n_rows);
+  if (!rc && (cudaMemcpyAsync(y, w + ctx->n_rows, nb, cudaMemcpyDeviceToHost, ctx->stream) != cudaSuccess ||
+              cudaStreamSynchronize(ctx->stream) != cudaSuccess))
+    rc = feasm_fail(ctx, FEASM_ERR_CUDA, "D2H y");
+  cudaFree(w);
+  return rc;
+}
+
+int feasm_cg_solve(feasm_ctx* ctx, double rel_tol, int max_its, const double* x0, double* x, int* iterations, double* rel_residual) {
+  if (!ctx || !ctx->d_values) return feasm_fail(ctx, FEASM_ERR_STATE, "no matrix");
+  if (!x || max_its < 0 || !(rel_tol >= 0.)) return feasm_fail(ctx, FEASM_ERR_ARG, "bad solver arguments");
+  if (ctx->d_gid || ctx->n_owned != ctx->n_rows) return feasm_fail(ctx, FEASM_ERR_STATE, "cg_solve: one rank per matrix in this version");
+  FEASM_CUDA(ctx, cudaSetDevice(ctx->device));
+  const int64_t n = ctx->n_rows;
+  if (n == 0) {
+    if (iterations) *iterations = 0;
+    if (rel_residual) *rel_residual = 0.;
+    return FEASM_OK;
+  }
+  const size_t nb = sizeof(double) * (size_t)(n ? n : 1);
+  double* w = nullptr;  // x | r | z | p | q | dinv | partials | scalars(4)
+  FEASM_CUDA(ctx, cudaMalloc(&w, 6 * nb + sizeof(double) * (DOT_GRID + 4)));
+  double *d_x = w, *d_r = w + n, *d_z = w + 2 * n, *d_p = w + 3 * n, *d_q = w + 4 * n, *d_dinv = w + 5 * n;
+  double* d_part = w + 6 * (n ? n : 1);
+  double* d_s = d_part + DOT_GRID;  // [0] rz, [1] pq, [2] rz_new, [3] rr
+  int rc = FEASM_OK, its = 0;
+  double rel = 0.;
+  auto fail = [&](int code) { cudaFree(w); return code; };
+  const unsigned vg = DOT_GRID;
+  if (x0) { if (cudaMemcpyAsync(d_x, x0, nb, cudaMemcpyHostToDevice, ctx->stream) != cudaSuccess) return fail(feasm_fail(ctx, FEASM_ERR_CUDA, "H2D x0")); }
+  else if (cudaMemsetAsync(d_x, 0, nb, ctx->stream) != cudaSuccess) return fail(feasm_fail(ctx, FEASM_ERR_CUDA, "memset x"));
+  k_inv_diag<<<(unsigned)((n + 255) / 256), 256, 0, ctx->stream>>>(ctx->d_row_ptr, ctx->d_col_idx, ctx->d_values, ctx->d_gid, n, d_dinv);
+  if ((rc = spmv(ctx, d_x, d_q))) return fail(rc);
+  k_cg_start<<<vg, 256, 0, ctx->stream>>>(n, ctx->d_rhs, d_q, d_dinv, d_r, d_z, d_p);
+  double h[4] = {0, 0, 0, 0};
+  // ||b|| for the relative test, r.z for the first direction
+  if ((rc = dot(ctx, ctx->d_rhs, ctx->d_rhs, n, d_part, d_s + 3))) return fail(rc);
+  if ((rc = dot(ctx, d_r, d_z, n, d_part, d_s + 0))) return fail(rc);
+  if (cudaMemcpyAsync(h, d_s, sizeof(h), cudaMemcpyDeviceToHost, ctx->stream) != cudaSuccess || cudaStreamSynchronize(ctx->stream) != cudaSuccess)
+    return fail(feasm_fail(ctx, FEASM_ERR_CUDA, "cg: scalar read"));
+  const double bnorm = std::sqrt(h[3]) > 0. ? std::sqrt(h[3]) : 1.;
+  if ((rc = dot(ctx, d_r, d_r, n, d_part, d_s + 3))) return fail(rc);
+  if (cudaMemcpyAsync(h, d_s, sizeof(h), cudaMemcpyDeviceToHost, ctx->stream) != cudaSuccess || cudaStreamSynchronize(ctx->stream) != cudaSuccess)
+    return fail(feasm_fail(ctx, FEASM_ERR_CUDA, "cg: scalar read"));
+  rel = std::sqrt(h[3]) / bnorm;
+  while (its < max_its && rel > rel_tol) {
+    if ((rc = spmv(ctx, d_p, d_q))) return fail(rc);
+    if ((rc = dot(ctx, d_p, d_q, n, d_part, d_s + 1))) return fail(rc);
+    k_cg_update<<<vg, 256, 0, ctx->stream>>>(n, d_s + 0, d_s + 1, d_p, d_q, d_dinv, d_x, d_r, d_z);
+    if ((rc = dot(ctx, d_r, d_z, n, d_part, d_s + 2))) return fail(rc);
+    if ((rc = dot(ctx, d_r, d_r, n, d_part, d_s + 3))) return fail(rc);
+    k_cg_direction<<<vg, 256, 0, ctx->stream>>>(n, d_s + 2, d_s + 0, d_z, d_p);
+    if (cudaMemcpyAsync(d_s + 0, d_s + 2, sizeof(double), cudaMemcpyDeviceToDevice, ctx->stream) != cudaSuccess ||
+        cudaMemcpyAsync(h, d_s, sizeof(h), cudaMemcpyDeviceToHost, ctx->stream) != cudaSuccess || cudaStreamSynchronize(ctx->stream) != cudaSuccess)
+      return fail(feasm_fail(ctx, FEASM_ERR_CUDA, "cg: scalar read"));
+    ++its;
+    rel = std::sqrt(h[3]) / bnorm;
+    if (!(h[1] > 0.)) break;  // p.Ap <= 0: the matrix is not positive definite on this direction
+  }
+  if (cudaMemcpyAsync(x, d_x, nb, cudaMemcpyDeviceToHost, ctx->stream) != cudaSuccess || cudaStreamSynchronize(ctx->stream) != cudaSuccess)
+    return fail(feasm_fail(ctx, FEASM_ERR_CUDA, "cg: D2H x"));
+  cudaFree(w);
+  if (iterations) *iterations = its;
+  if (rel_residual) *rel_residual = rel;
+  return FEASM_OK;
+}

@@ -145,6 +145,22 @@ class GpuSparseMatrix : public SparseMatrix<T> {
     values.assign(_host_values.begin() + lo, _host_values.begin() + hi);
   }
 
+  // ---- the step after assembly, on the device matrix -----------------------------------------
+  // y = A x: what NumericVector::add_vector(v, A) (numeric_vector.h:561) asks of a back-end; host vectors of the
+  // local size.  A GpuNumericVector subclass would call feasm_vector_mult with its device pointers instead.
+  void multiply(std::vector<T>& y, const std::vector<T>& x) {
+    y.resize(x.size());
+    check(feasm_vector_mult_host(ctx(), x.data(), y.data()));
+  }
+  // A x = b with the rhs the batched hook assembled: CG + Jacobi on the device (LinearSolver::solve analogue)
+  std::pair<unsigned int, Real> solve_cg(std::vector<T>& x, Real rel_tol, unsigned int max_its) {
+    int its = 0;
+    double rel = 0.;
+    x.resize(m());
+    check(feasm_cg_solve(ctx(), rel_tol, (int)max_its, nullptr, x.data(), &its, &rel));
+    return {(unsigned int)its, rel};
+  }
+
   // ---- what the batched hook needs ---------------------------------------------------------------------------
   feasm_ctx* ctx() {
     if (!_ctx) {
