@@ -23,7 +23,19 @@ __global__ void k_spmv(const uint64_t* __restrict__ row_ptr, const uint32_t* __r
   if (r >= n_rows) return;
   const uint64_t p0 = row_ptr[r], p1 = row_ptr[r + 1];
   double s = 0.;
-  for (uint64_t k = p0 + lane; k < p1; k += 32) s += __ldcs(values + k) * x[__ldcs(col_idx + k)];
+  for (uint64_t k0 = p0; k0 < p1; k0 += 128) {  // four independent (value, column, x) load chains per lane
+    double v[4];
+    uint32_t c[4];
+#pragma unroll
+    for (int u = 0; u < 4; ++u) {
+      const uint64_t k = k0 + lane + 32 * u;
+      const bool ok = k < p1;
+      v[u] = ok ? __ldcs(values + k) : 0.;
+      c[u] = ok ? __ldcs(col_idx + k) : 0u;
+    }
+#pragma unroll
+    for (int u = 0; u < 4; ++u) s += v[u] * x[c[u]];
+  }
 #pragma unroll
   for (int o = 16; o > 0; o >>= 1) s += __shfl_xor_sync(0xffffffffu, s, o);
   if (lane == 0) y[r] = s;
