@@ -178,20 +178,42 @@ def run_ours(args):
     val_pin = torch.empty(nnz, dtype=torch.float64).pin_memory()
     rhs_pin = torch.empty(P["n_dofs"], dtype=torch.float64).pin_memory()
     xyz_np, val_np, rhs_np = xyz_pin.numpy(), val_pin.numpy(), rhs_pin.numpy()
-    e2e_steps = max(2, min(args.steps, 5))
+    e2e_steps = max(3, min(args.steps, 8))
+
+    # The result leaves through the device-pointer accessors of the C ABI (feasm_device_values / feasm_device_rhs): a
+    # device-side snapshot on the library's stream, then the PCIe read on a second stream, so the D2H read of step i
+    # overlaps the H2D + assembly of step i+1 (every step still uploads its inputs and reads back its full result).
+    from libmesh_b200.multi import DevArray
+    d_val = torch.as_tensor(DevArray(ctx.device_values(), nnz), device="cuda")
+    d_rhs = torch.as_tensor(DevArray(ctx.device_rhs(), P["n_dofs"]), device="cuda")
+    snap_val, snap_rhs = torch.empty_like(d_val), torch.empty_like(d_rhs)
+    copy_stream = torch.cuda.Stream()
+    ev_ready, ev_done = torch.cuda.Event(), torch.cuda.Event()
+    ev_done.record(copy_stream)
 
     def e2e_step():
         ctx.update_coordinates(xyz_np)
         ctx.set_constraints(P["con_rows"], P["con_vals"])
         ctx.assemble(params, sync=False)
-        ctx.get_values(out_values=val_np, out_rhs=rhs_np)  # synchronises
+        with torch.cuda.stream(stream):
+            stream.wait_event(ev_done)            # the previous read has left the snapshot
+            snap_val.copy_(d_val, non_blocking=True)
+            snap_rhs.copy_(d_rhs, non_blocking=True)
+            ev_ready.record(stream)
+        with torch.cuda.stream(copy_stream):
+            copy_stream.wait_event(ev_ready)
+            val_pin.copy_(snap_val, non_blocking=True)
+            rhs_pin.copy_(snap_rhs, non_blocking=True)
+            ev_done.record(copy_stream)
 
     e2e_step()
     torch.cuda.synchronize()
+    ctx.synchronize()
     t_e = time.perf_counter()
     for _ in range(e2e_steps):
         e2e_step()
     torch.cuda.synchronize()
+    ctx.synchronize()  # raises if any step flagged a degenerate element
     e2e_s = (time.perf_counter() - t_e) / e2e_steps
     h2d = xyz_np.nbytes + P["con_rows"].nbytes + P["con_vals"].nbytes + P["n_dofs"] * 9  # flags+values arrays uploaded by set_constraints
     d2h = val_np.nbytes + rhs_np.nbytes
