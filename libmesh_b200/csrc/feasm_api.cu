@@ -352,7 +352,7 @@ int feasm_element_matrices(feasm_ctx* ctx, const feasm_params* params, int64_t e
   FEASM_CUDA(ctx, cudaMemsetAsync(ctx->d_flags, 0, 2 * sizeof(int), ctx->stream));
   rc = feasm_launch_element_kernel(ctx, *params, d_f, e0, e1, d_kf, (int)ldr, constrained ? params->constrain : -1);
   if (!rc) {
-    // KF rows are (Ke row | Fe | pad): strip the padding on the way out
+    // scratch records are (Ke row | Fe | pad): strip the padding on the way out
     if (Ke) cudaMemcpy2DAsync(Ke, sizeof(double) * nd, d_kf, sizeof(double) * ldr, sizeof(double) * nd, ne * nd, cudaMemcpyDeviceToHost, ctx->stream);
     if (Fe) cudaMemcpy2DAsync(Fe, sizeof(double), d_kf + nd, sizeof(double) * ldr, sizeof(double), ne * nd, cudaMemcpyDeviceToHost, ctx->stream);
     rc = check_flags(ctx);

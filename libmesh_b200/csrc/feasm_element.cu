@@ -13,8 +13,9 @@
 //      triangular 8x8 blocks of the first 8*floor(n/8) rows go through DMMA (A and B fragments are the same
 //      register); the n mod 8 leftover rows (3 for HEX27, 2 for TET10) would waste 5/8 of a DMMA block each, so
 //      they are contracted with plain DFMA against fragments broadcast by shuffle.
-//   D. Fe, then fragments stored straight to the element buffer KF[e][i][LDR] (Ke row | Fe), mirrored for the
-//      lower triangle.  Constraints are NOT applied here: the row reduction applies them (feasm_scatter.cu).
+//   D. Fe, then fragments stored straight into the values part of the element's records REC[e][i] (Ke row | Fe,
+//      feasm_internal.h), mirrored for the lower triangle.
+//   E. Dirichlet constraints: a second, small kernel (k_constrain_list) over the elements that touch a constrained dof.
 #include <cstdlib>
 
 #include "feasm_elem_dev.cuh"
