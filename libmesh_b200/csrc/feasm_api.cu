@@ -87,6 +87,7 @@ int check_flags(feasm_ctx* ctx) {
   int flags[2] = {0, 0};
   FEASM_CUDA(ctx, cudaMemcpyAsync(flags, ctx->d_flags, sizeof(flags), cudaMemcpyDeviceToHost, ctx->stream));
   FEASM_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
+  if (flags[0] || flags[1]) FEASM_CUDA(ctx, cudaMemsetAsync(ctx->d_flags, 0, sizeof(flags), ctx->stream));  // reported once
   if (flags[0]) return feasm_fail(ctx, FEASM_ERR_DEGENERATE, "Jacobian at or under tolerance 0 (degenerate map) at " + std::to_string(flags[0]) + " quadrature points");
   if (flags[1]) return feasm_fail(ctx, FEASM_ERR_PATTERN, "add to an entry outside the sparsity pattern");
   return FEASM_OK;

@@ -68,7 +68,16 @@ class GpuSparseMatrix : public SparseMatrix<T> {
     _pattern_sent = false; _closed = false; this->_is_initialized = false;
   }
   void zero() override { if (_ctx && _pattern_sent) check(feasm_zero(_ctx)); _host_valid = false; }
-  std::unique_ptr<SparseMatrix<T>> zero_clone() const override { libmesh_not_implemented(); }
+  // same communicator, dof map and sparsity pattern, all values zero (sparse_matrix.h:219); its context is created on
+  // first use
+  std::unique_ptr<SparseMatrix<T>> zero_clone() const override {
+    auto Z = std::make_unique<GpuSparseMatrix<T>>(this->comm());
+    Z->_dof_map = this->_dof_map;
+    Z->_row_ptr = _row_ptr; Z->_col_idx = _col_idx;
+    Z->_m = _m; Z->_n = _n; Z->_row_start = _row_start; Z->_row_stop = _row_stop;
+    Z->_is_initialized = this->_is_initialized;
+    return Z;
+  }
   std::unique_ptr<SparseMatrix<T>> clone() const override { libmesh_not_implemented(); }
   void close() override { if (_ctx) check(feasm_synchronize(_ctx)); _closed = true; }
   bool closed() const override { return _closed; }

@@ -1,6 +1,7 @@
-// libmesh_mock.h — SIGNATURE MOCK of the libMesh declarations the adaptor classes use, so that
-// gpu_sparse_matrix.h / gpu_assemble.C compile in a container where libMesh itself cannot be built (its TIMPI and
-// MetaPhysicL submodules are empty).  Every declaration cites the reference header it mirrors; bodies are stubs.
+// libmesh_mock.h — MOCK of the libMesh declarations the adaptor classes use, so that gpu_sparse_matrix.h /
+// gpu_assemble.C compile — and shim_test.C runs them end to end — in a container where libMesh itself cannot be built
+// (its TIMPI and MetaPhysicL submodules are empty).  Every declaration cites the reference header it mirrors; the
+// bodies are minimal data holders (a test fills the public underscore members), not libMesh's implementations.
 // A real build defines nothing of this: it includes the libmesh/ headers instead (see gpu_sparse_matrix.h).
 #ifndef FEASM_LIBMESH_MOCK_H
 #define FEASM_LIBMESH_MOCK_H
@@ -73,15 +74,20 @@ typedef std::map<dof_id_type, Number> DofConstraintValueMap;                    
 template <typename T> class SparseMatrix;
 class DofMap {                                                                     // include/base/dof_map.h
  public:
-  dof_id_type n_dofs() const { return 0; }                                         // dof_map_base.h
+  dof_id_type n_dofs() const { return _n_dofs; }                                   // dof_map_base.h
   dof_id_type first_dof() const { return 0; }                                      // dof_map_base.h:185
-  dof_id_type end_dof() const { return 0; }                                        // dof_map_base.h:191
+  dof_id_type end_dof() const { return _n_dofs; }                                  // dof_map_base.h:191
   dof_id_type n_local_dofs() const { return end_dof() - first_dof(); }
-  void dof_indices(const Elem*, std::vector<dof_id_type>&) const {}                // dof_map.h:2201 / src/base/dof_map.C:2201
-  bool is_constrained_dof(dof_id_type) const { return false; }                     // dof_map.h:2426
+  void dof_indices(const Elem* e, std::vector<dof_id_type>& di) const {            // dof_map.h:2201 / src/base/dof_map.C:2201
+    di.assign(_elem_dofs.begin() + (std::size_t)e->id() * _nd, _elem_dofs.begin() + (std::size_t)(e->id() + 1) * _nd);
+  }
+  bool is_constrained_dof(dof_id_type d) const { return _vals.count(d) != 0; }     // dof_map.h:2426
   DofConstraintValueMap& get_primal_constraint_values() { return _vals; }          // dof_map.h:1263
   unsigned int n_variables() const { return 1; }
   DofConstraintValueMap _vals;
+  dof_id_type _n_dofs = 0;
+  unsigned _nd = 0;
+  std::vector<dof_id_type> _elem_dofs;  // [n_elem][_nd], element id major
 };
 
 template <typename T> class NumericVector {                                        // include/numerics/numeric_vector.h
@@ -91,8 +97,9 @@ template <typename T> class NumericVector {                                     
   virtual void zero() {}
   virtual numeric_index_type first_local_index() const { return 0; }               // :500
   virtual numeric_index_type last_local_index() const { return 0; }
-  virtual void set(const numeric_index_type, const T) {}                           // :508
-  virtual NumericVector<T>& operator=(const std::vector<T>&) { return *this; }     // :295
+  virtual void set(const numeric_index_type i, const T v) { if (i >= _v.size()) _v.resize(i + 1); _v[i] = v; }  // :508
+  virtual NumericVector<T>& operator=(const std::vector<T>& v) { _v = v; return *this; }  // :295
+  std::vector<T> _v;
 };
 
 template <typename T> class SparseMatrix : public ParallelObject {                  // include/numerics/sparse_matrix.h

@@ -1,0 +1,174 @@
+// shim_test.C — runs the libMesh adaptor (GpuSparseMatrix + the batched assemble hook) end to end against the mock
+// classes of libmesh_mock.h on a real B200, and checks it against a second, direct drive of the C ABI with the same
+// inputs: what travels through the adaptor (mesh flattening, dof_indices, Graph hand-over, constraints, RHS hand-back,
+// the SparseMatrix virtuals) must change nothing.  Built by shim/Makefile, run by tests/test_gpu_shim.py.
+#include <algorithm>
+#include <cmath>
+#include <cstdio>
+#include <set>
+#include <sstream>
+
+#include "gpu_assemble.h"
+
+using namespace libMesh;
+
+#define REQUIRE(c) do { if (!(c)) { std::printf("FAILED %s:%d: %s\n", __FILE__, __LINE__, #c); return 1; } } while (0)
+#define CK(call) do { int rc__ = (call); if (rc__) { std::printf("C ABI error %d at %s:%d\n", rc__, __FILE__, __LINE__); return 1; } } while (0)
+
+int main() {
+  // ---- a 3x2x2 HEX27 mesh on [-1,1]^3 from the host generators of the C ABI (MeshTools::Generation::build_cube) ----
+  const int nx = 3, ny = 2, nz = 2;
+  const double bounds[6] = {-1, 1, -1, 1, -1, 1};
+  int64_t n_elem = 0, n_nodes = 0;
+  CK(feasm_cube_sizes(FEASM_HEX27, nx, ny, nz, &n_elem, &n_nodes));
+  std::vector<double> xyz(3 * n_nodes);
+  std::vector<uint32_t> conn(27 * n_elem), base(n_nodes), first(2);
+  std::vector<uint8_t> mask(n_nodes);
+  std::vector<int32_t> npid(n_nodes);
+  CK(feasm_build_cube(FEASM_HEX27, nx, ny, nz, bounds, xyz.data(), conn.data(), mask.data()));
+  const int64_t n_dofs = feasm_distribute_dofs(27, n_elem, n_nodes, conn.data(), 1, 1, nullptr, base.data(), first.data(), npid.data());
+  REQUIRE(n_dofs == n_nodes);
+
+  std::vector<Node> nodes(n_nodes);
+  for (int64_t i = 0; i < n_nodes; ++i) { nodes[i]._id = (dof_id_type)i; for (int d = 0; d < 3; ++d) nodes[i].c[d] = xyz[3 * i + d]; }
+  std::vector<Elem> elems(n_elem);
+  MeshBase mesh;
+  DofMap dof_map;
+  dof_map._n_dofs = (dof_id_type)n_dofs; dof_map._nd = 27;
+  for (int64_t e = 0; e < n_elem; ++e) {
+    elems[e]._type = HEX27; elems[e]._id = (dof_id_type)e; elems[e]._pid = 0;
+    for (int a = 0; a < 27; ++a) {
+      elems[e]._nodes.push_back(&nodes[conn[27 * e + a]]);
+      dof_map._elem_dofs.push_back(base[conn[27 * e + a]]);
+    }
+    mesh._local.push_back(&elems[e]);
+  }
+  // Dirichlet dofs on the whole boundary with the exact solution of ex4 (DirichletBoundary, introduction_ex4.C:217-243)
+  const double hp = 1.5707963267948966;
+  for (int64_t i = 0; i < n_nodes; ++i)
+    if (mask[i]) dof_map._vals[base[i]] = std::cos(hp * xyz[3 * i]) * std::sin(hp * xyz[3 * i + 1]) * std::cos(hp * xyz[3 * i + 2]);
+  // SparsityPattern::Build: sorted unique union of the element dof sets
+  std::vector<std::set<dof_id_type>> rows(n_dofs);
+  for (int64_t e = 0; e < n_elem; ++e)
+    for (int a = 0; a < 27; ++a)
+      for (int b = 0; b < 27; ++b) rows[dof_map._elem_dofs[27 * e + a]].insert(dof_map._elem_dofs[27 * e + b]);
+  SparsityPattern::Graph graph(n_dofs);
+  for (int64_t r = 0; r < n_dofs; ++r) graph[r].assign(rows[r].begin(), rows[r].end());
+
+  // ---- the libMesh side: what EquationSystems::init() and System::solve() do with the adaptor ----------------------
+  Parallel::Communicator comm;
+  GpuSparseMatrix<Number> A(comm);
+  NumericVector<Number> rhs;
+  LinearImplicitSystem system;
+  system._mesh = &mesh; system._dof = &dof_map; system.matrix = &A; system.rhs = &rhs;
+  EquationSystems es;
+  es._sys = &system;
+  A.attach_dof_map(dof_map);             // DofMap::attach_matrix, dof_map.C:240-287
+  REQUIRE(A.need_full_sparsity_pattern());
+  A.update_sparsity_pattern(graph);
+  A.init();
+  REQUIRE(A.initialized() && A.m() == (numeric_index_type)n_dofs && A.row_stop() == (numeric_index_type)n_dofs);
+  A.zero();                              // ImplicitSystem::assemble, implicit_system.C:101-105
+  feasm_libmesh::assemble_poisson_ex4(es, "Poisson");
+  A.close();
+  REQUIRE(A.closed());
+
+  // ---- the same problem straight through the C ABI ---------------------------------------------------------------
+  feasm_ctx* ctx = nullptr;
+  CK(feasm_create(0, &ctx));
+  CK(feasm_set_mesh(ctx, FEASM_HEX27, n_elem, n_nodes, xyz.data(), conn.data()));
+  CK(feasm_set_dofs(ctx, 1, n_dofs, n_dofs, dof_map._elem_dofs.data(), nullptr));
+  std::vector<uint32_t> crow;
+  std::vector<double> cval;
+  for (const auto& kv : dof_map._vals) { crow.push_back(kv.first); cval.push_back(kv.second); }
+  CK(feasm_set_constraints(ctx, (int64_t)crow.size(), crow.data(), cval.data()));
+  CK(feasm_set_pattern(ctx, A.row_ptr().data(), A.col_idx().data()));
+  feasm_params p{};
+  p.problem = FEASM_POISSON; p.quadrature_order = 5; p.forcing = FEASM_FORCING_EX4_FD; p.constrain = FEASM_CONSTRAIN_HETEROGENEOUS;
+  CK(feasm_assemble(ctx, &p));
+  std::vector<double> v(A.col_idx().size()), b(n_dofs);
+  CK(feasm_get_values(ctx, v.data(), b.data()));
+
+  // the adaptor changed nothing: same bits in the matrix (operator(), get_row, host_values) and in the RHS
+  REQUIRE(rhs._v.size() == (std::size_t)n_dofs);
+  for (int64_t r = 0; r < n_dofs; ++r) REQUIRE(rhs._v[r] == b[r]);
+  REQUIRE(A.host_values() == v);
+  double l1 = 0., linf = 0.;
+  std::vector<double> colsum(n_dofs, 0.);
+  for (int64_t r = 0; r < n_dofs; ++r) {
+    std::vector<numeric_index_type> idx;
+    std::vector<Number> val;
+    A.get_row((numeric_index_type)r, idx, val);
+    REQUIRE(idx == graph[r]);                                   // ascending columns (sparse_matrix_test.h:88-149)
+    double rowsum = 0.;
+    for (std::size_t k = 0; k < idx.size(); ++k) {
+      REQUIRE(val[k] == v[A.row_ptr()[r] + k]);
+      REQUIRE(A((numeric_index_type)r, idx[k]) == val[k]);
+      rowsum += std::fabs(val[k]); colsum[idx[k]] += std::fabs(val[k]);
+    }
+    linf = std::max(linf, rowsum);
+  }
+  for (double c : colsum) l1 = std::max(l1, c);
+  REQUIRE(std::fabs(A.l1_norm() - l1) <= 1e-12 * l1 && std::fabs(A.linfty_norm() - linf) <= 1e-12 * linf);
+  REQUIRE(A(0, (numeric_index_type)n_dofs - 1) == 0.);          // outside the pattern reads as zero
+  // a constrained dof: diagonal = number of touching elements, rhs = that count x g
+  {
+    const dof_id_type d = dof_map._vals.begin()->first;
+    int touching = 0;
+    for (dof_id_type x : dof_map._elem_dofs) touching += x == d;
+    REQUIRE(A(d, d) == (double)touching && std::fabs(rhs._v[d] - touching * dof_map._vals[d]) <= 1e-14);
+  }
+  NumericVector<Number> diag;
+  A.get_diagonal(diag);
+  for (int64_t r = 0; r < n_dofs; ++r) REQUIRE(diag._v[r] == A((numeric_index_type)r, (numeric_index_type)r));
+
+  // ---- the single-entry virtuals ---------------------------------------------------------------------------------
+  const numeric_index_type i0 = graph[5][0], j0 = graph[5].size() > 1 ? graph[5][1] : graph[5][0];
+  const double before = A(5, j0);
+  A.add(5, j0, 0.25);
+  A.close();
+  REQUIRE(A(5, j0) == before + 0.25);
+  (void)i0;
+  DenseMatrix<Number> dm;
+  dm._m = dm._n = 2; dm._val = {1., 2., 3., 4.};
+  std::vector<numeric_index_type> di = {graph[7][0], graph[7][1]};
+  const double a00 = A(di[0], di[0]), a01 = A(di[0], di[1]), a10 = A(di[1], di[0]), a11 = A(di[1], di[1]);
+  A.add_matrix(dm, di);
+  A.close();
+  REQUIRE(A(di[0], di[0]) == a00 + 1. && A(di[0], di[1]) == a01 + 2. && A(di[1], di[0]) == a10 + 3. && A(di[1], di[1]) == a11 + 4.);
+  bool threw = false;
+  try { A.add(0, (numeric_index_type)n_dofs - 1, 1.0); A.close(); } catch (const LogicError&) { threw = true; }
+  REQUIRE(threw);                                               // non-zero outside the pattern is an error ...
+  A.add(0, (numeric_index_type)n_dofs - 1, 0.0);                // ... zero is allowed (sparse_matrix.h:300-303)
+  A.close();
+  std::ostringstream os;
+  A.print_personal(os);
+  REQUIRE(!os.str().empty());
+
+  // ---- after assembly: product and CG solve on the device matrix -----------------------------------------------
+  A.zero();
+  feasm_libmesh::assemble_poisson_ex4(es, "Poisson");
+  A.close();
+  std::vector<Number> x(n_dofs, 1.0), y;
+  A.multiply(y, x);
+  for (int64_t r = 0; r < n_dofs; ++r) {
+    double s = 0.;
+    for (uint64_t k = A.row_ptr()[r]; k < A.row_ptr()[r + 1]; ++k) s += v[k];
+    REQUIRE(std::fabs(y[r] - s) <= 1e-12 * (std::fabs(s) + 1.));
+  }
+  std::vector<Number> u;
+  const auto res = A.solve_cg(u, 1e-12, 2000);
+  REQUIRE(res.second <= 1e-12 && res.first > 0);
+  double err = 0.;
+  for (int64_t i = 0; i < n_nodes; ++i)
+    err = std::max(err, std::fabs(u[base[i]] - std::cos(hp * xyz[3 * i]) * std::sin(hp * xyz[3 * i + 1]) * std::cos(hp * xyz[3 * i + 2])));
+  REQUIRE(err < 5e-3);                                          // coarse Q2 mesh: discretisation error only
+
+  auto Z = A.zero_clone();
+  REQUIRE(Z->m() == A.m());
+  A.clear();
+  REQUIRE(!A.initialized());
+  feasm_destroy(ctx);
+  std::printf("SHIM TEST OK: %lld elements, %lld dofs, CG %u iterations, nodal error %.2e\n", (long long)n_elem, (long long)n_dofs, res.first, err);
+  return 0;
+}
