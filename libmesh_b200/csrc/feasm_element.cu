@@ -17,6 +17,7 @@
 //      feasm_internal.h), mirrored for the lower triangle.
 //   E. Dirichlet constraints: a second, small kernel (k_constrain_list) over the elements that touch a constrained dof.
 #include <cstdlib>
+#include <type_traits>
 
 #include "feasm_elem_dev.cuh"
 
@@ -322,7 +323,9 @@ k_elem_elasticity(const double* __restrict__ xyz, const uint32_t* __restrict__ c
     double* out = kf + (uint64_t)(e - e0) * (ND * LDR);
 
     // P_dd' for one (d, d') pair -> tile[a*TLD + b]
-    auto product = [&](int d, int dp, double* T) {
+    // SYM (d == d'): P is symmetric, only the blocks on and above the diagonal go through DMMA and are mirrored
+    auto product = [&](int d, int dp, double* T, auto sym) {
+      constexpr bool SYM = decltype(sym)::value;
       double acc[NBP][NBP][2];
 #pragma unroll
       for (int ib = 0; ib < NBP; ++ib)
@@ -348,22 +351,28 @@ k_elem_elasticity(const double* __restrict__ xyz, const uint32_t* __restrict__ c
 #pragma unroll
         for (int ib = 0; ib < NBP; ++ib)
 #pragma unroll
-          for (int jb = 0; jb < NBP; ++jb) dmma884(acc[ib][jb][0], acc[ib][jb][1], A[ib], B[jb]);
+          for (int jb = 0; jb < NBP; ++jb)
+            if (!SYM || ib <= jb) dmma884(acc[ib][jb][0], acc[ib][jb][1], A[ib], B[jb]);
       }
 #pragma unroll
       for (int ib = 0; ib < NBP; ++ib)
 #pragma unroll
         for (int jb = 0; jb < NBP; ++jb) {
+          if (SYM && ib > jb) continue;
           const int i = ib * 8 + g, j = jb * 8 + 2 * t4;
           if (i < NPE && j < NPE) T[i * TLD + j] = acc[ib][jb][0];
           if (i < NPE && j + 1 < NPE) T[i * TLD + j + 1] = acc[ib][jb][1];
+          if (SYM && ib < jb) {
+            if (i < NPE && j < NPE) T[j * TLD + i] = acc[ib][jb][0];
+            if (i < NPE && j + 1 < NPE) T[(j + 1) * TLD + i] = acc[ib][jb][1];
+          }
         }
     };
 
     // diagonal variable blocks: K_dd = (l1 + l2) P_dd + l2 (P_00 + P_11 + P_22)
-    product(0, 0, tile);
-    product(1, 1, tile + TILE);
-    product(2, 2, tile + 2 * TILE);
+    product(0, 0, tile, std::true_type{});
+    product(1, 1, tile + TILE, std::true_type{});
+    product(2, 2, tile + 2 * TILE, std::true_type{});
     __syncwarp();
     if (lane < NPE) {
       for (int a = 0; a < NPE; ++a) {
@@ -385,7 +394,7 @@ k_elem_elasticity(const double* __restrict__ xyz, const uint32_t* __restrict__ c
 #pragma unroll
     for (int pair = 0; pair < 3; ++pair) {
       const int i = pair == 2 ? 1 : 0, k = pair == 0 ? 1 : 2;
-      product(i, k, tile);
+      product(i, k, tile, std::false_type{});
       __syncwarp();
       if (lane < NPE) {
         for (int a = 0; a < NPE; ++a) {
