@@ -146,6 +146,32 @@ int feasm_vector_mult_host(feasm_ctx* ctx, const double* x, double* y); /* same 
 int feasm_cg_solve(feasm_ctx* ctx, double rel_tol, int max_its, const double* x0, double* x, int* iterations,
                    double* rel_residual);
 
+/* ---- device vectors: what a NumericVector back-end needs (numeric_vector.h:119-847; shim/gpu_numeric_vector.h) -- */
+/* Blocking calls on feasm_stream.  d_* are device pointers from feasm_vec_alloc (or feasm_device_rhs). */
+#define FEASM_COPY_H2D 0
+#define FEASM_COPY_D2H 1
+#define FEASM_COPY_D2D 2
+#define FEASM_VEC_MULT 0        /* pointwise: out = a .* b        (NumericVector::pointwise_mult, operator*=) */
+#define FEASM_VEC_DIV 1         /*            out = a ./ b        (pointwise_divide, operator/=) */
+#define FEASM_VEC_ABS 2         /*            out = |a|           (abs) */
+#define FEASM_VEC_RECIPROCAL 3  /*            out = 1 ./ a        (reciprocal) */
+#define FEASM_VEC_ADD_SCALAR 4  /*            out = a + s         (add(T)) */
+#define FEASM_VEC_SCALE 5       /*            out = s a           (scale) */
+#define FEASM_VEC_SUM 10        /* reductions (fixed tree, deterministic): sum, min, max, l1_norm, linfty_norm, dot */
+#define FEASM_VEC_MIN 11
+#define FEASM_VEC_MAX 12
+#define FEASM_VEC_L1 13
+#define FEASM_VEC_LINF 14
+#define FEASM_VEC_DOT 15
+double* feasm_vec_alloc(feasm_ctx* ctx, int64_t n); /* zero-initialised; NULL on failure */
+void feasm_vec_free(feasm_ctx* ctx, double* d_v);
+int feasm_vec_copy(feasm_ctx* ctx, int kind, void* dst, const void* src, int64_t n);
+int feasm_vec_fill(feasm_ctx* ctx, double* d_y, int64_t n, double value);
+int feasm_vec_axpy(feasm_ctx* ctx, double* d_y, double a, const double* d_x, int64_t n); /* y += a x */
+int feasm_vec_pointwise(feasm_ctx* ctx, int op, double* d_out, const double* d_a, const double* d_b, double s, int64_t n);
+int feasm_vec_reduce(feasm_ctx* ctx, int op, const double* d_x, const double* d_y, int64_t n, double* result);
+int feasm_vec_set_entry(feasm_ctx* ctx, double* d_y, int64_t i, double value, int add); /* set(i,v) / add(i,v) */
+
 /* ---- multi-GPU ghost rows (DistributedVector::close / MatAssemblyBegin-End) -------------------- */
 /* After feasm_prepare on every rank: describe, per peer, which of this rank's ghost-row slots go to the peer
  * and which owned slots receive the peer's contributions.  send_slots / recv_slots index the CSR value array

@@ -28,6 +28,8 @@ SYMBOLS = [
     "feasm_get_values", "feasm_device_values", "feasm_device_rhs", "feasm_stream", "feasm_set_exchange_plan",
     "feasm_pack_ghost", "feasm_recv_buffer", "feasm_unpack_ghost", "feasm_cube_sizes", "feasm_build_cube",
     "feasm_distribute_dofs", "feasm_last_timing", "feasm_measure_fp64_peaks", "feasm_vector_mult", "feasm_vector_mult_host", "feasm_cg_solve",
+    "feasm_vec_alloc", "feasm_vec_free", "feasm_vec_copy", "feasm_vec_fill", "feasm_vec_axpy", "feasm_vec_pointwise",
+    "feasm_vec_reduce", "feasm_vec_set_entry",
 ]
 
 
@@ -93,6 +95,14 @@ def lib():
         "feasm_vector_mult": (i32, [vp, vp, vp]),
         "feasm_vector_mult_host": (i32, [vp, vp, vp]),
         "feasm_cg_solve": (i32, [vp, C.c_double, i32, vp, vp, C.POINTER(i32), C.POINTER(C.c_double)]),
+        "feasm_vec_alloc": (vp, [vp, i64]),
+        "feasm_vec_free": (None, [vp, vp]),
+        "feasm_vec_copy": (i32, [vp, i32, vp, vp, i64]),
+        "feasm_vec_fill": (i32, [vp, vp, i64, C.c_double]),
+        "feasm_vec_axpy": (i32, [vp, vp, C.c_double, vp, i64]),
+        "feasm_vec_pointwise": (i32, [vp, i32, vp, vp, vp, C.c_double, i64]),
+        "feasm_vec_reduce": (i32, [vp, i32, vp, vp, i64, C.POINTER(C.c_double)]),
+        "feasm_vec_set_entry": (i32, [vp, vp, i64, C.c_double, i32]),
     }
     for name, (res, args) in sig.items():
         fn = getattr(L, name)

@@ -121,6 +121,58 @@ __global__ void k_cg_start(int64_t n, const double* __restrict__ b, const double
   }
 }
 
+// ---- device vector algebra behind NumericVector (include/numerics/numeric_vector.h) ------------------------------
+__global__ void k_vec_fill(double* __restrict__ y, int64_t n, double v) {
+  for (int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; i < n; i += (int64_t)gridDim.x * blockDim.x) y[i] = v;
+}
+__global__ void k_vec_axpy(double* __restrict__ y, double a, const double* __restrict__ x, int64_t n) {
+  for (int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; i < n; i += (int64_t)gridDim.x * blockDim.x) y[i] += a * x[i];
+}
+// out = a (op) b elementwise; ops that take one operand read a only
+__global__ void k_vec_pointwise(int op, double* __restrict__ out, const double* __restrict__ a, const double* __restrict__ b, double s, int64_t n) {
+  for (int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; i < n; i += (int64_t)gridDim.x * blockDim.x) {
+    double v = a[i];
+    switch (op) {
+      case FEASM_VEC_MULT: v = v * b[i]; break;
+      case FEASM_VEC_DIV: v = v / b[i]; break;
+      case FEASM_VEC_ABS: v = fabs(v); break;
+      case FEASM_VEC_RECIPROCAL: v = 1. / v; break;
+      case FEASM_VEC_ADD_SCALAR: v = v + s; break;
+      case FEASM_VEC_SCALE: v = v * s; break;
+    }
+    out[i] = v;
+  }
+}
+__device__ __forceinline__ double red_combine(int op, double a, double b) {
+  switch (op) {
+    case FEASM_VEC_MIN: return a < b ? a : b;
+    case FEASM_VEC_MAX: case FEASM_VEC_LINF: return a > b ? a : b;
+    default: return a + b;
+  }
+}
+__device__ __forceinline__ double red_identity(int op) {
+  return op == FEASM_VEC_MIN ? 1.7976931348623157e308 : (op == FEASM_VEC_MAX ? -1.7976931348623157e308 : 0.);
+}
+__device__ __forceinline__ double red_map(int op, double v) { return (op == FEASM_VEC_L1 || op == FEASM_VEC_LINF) ? fabs(v) : v; }
+// fixed two-level tree (deterministic): grid-stride partials, then one CTA over the partials (x == nullptr: partials in)
+__global__ void k_vec_reduce(int op, const double* __restrict__ x, int64_t n, double* __restrict__ out, bool final_pass) {
+  __shared__ double sh[32];
+  double v = red_identity(op);
+  for (int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; i < n; i += (int64_t)gridDim.x * blockDim.x)
+    v = red_combine(op, v, final_pass ? x[i] : red_map(op, x[i]));
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) v = red_combine(op, v, __shfl_xor_sync(0xffffffffu, v, o));
+  if ((threadIdx.x & 31) == 0) sh[threadIdx.x >> 5] = v;
+  __syncthreads();
+  if (threadIdx.x < 32) {
+    double t = threadIdx.x < (blockDim.x >> 5) ? sh[threadIdx.x] : red_identity(op);
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) t = red_combine(op, t, __shfl_xor_sync(0xffffffffu, t, o));
+    if (threadIdx.x == 0) out[blockIdx.x] = t;
+  }
+}
+__global__ void k_vec_set_one(double* __restrict__ y, int64_t i, double v, int add) { y[i] = add ? y[i] + v : v; }
+
 int spmv(feasm_ctx* ctx, const double* d_x, double* d_y) {
   const unsigned grid = (unsigned)((ctx->n_rows * 32 + 255) / 256);
   if (grid) k_spmv<<<grid, 256, 0, ctx->stream>>>(ctx->d_row_ptr, ctx->d_col_idx, ctx->d_values, d_x, ctx->n_rows, d_y);
@@ -218,5 +270,82 @@ int feasm_cg_solve(feasm_ctx* ctx, double rel_tol, int max_its, const double* x0
   cudaFree(w);
   if (iterations) *iterations = its;
   if (rel_residual) *rel_residual = rel;
+  return FEASM_OK;
+}
+
+
+// ---- device vectors for a NumericVector back-end (shim/gpu_numeric_vector.h).  Blocking calls: each returns after its
+// work on feasm_stream has completed, like the host-library back-ends. ------------------------------------------------
+double* feasm_vec_alloc(feasm_ctx* ctx, int64_t n) {
+  if (!ctx || n < 0) return nullptr;
+  if (cudaSetDevice(ctx->device) != cudaSuccess) return nullptr;
+  double* p = nullptr;
+  if (cudaMalloc(&p, sizeof(double) * (size_t)(n ? n : 1)) != cudaSuccess) { feasm_fail(ctx, FEASM_ERR_NOMEM, "feasm_vec_alloc"); return nullptr; }
+  cudaMemsetAsync(p, 0, sizeof(double) * (size_t)(n ? n : 1), ctx->stream);
+  cudaStreamSynchronize(ctx->stream);
+  return p;
+}
+void feasm_vec_free(feasm_ctx* ctx, double* d_v) {
+  if (!ctx || !d_v) return;
+  cudaSetDevice(ctx->device);
+  cudaStreamSynchronize(ctx->stream);
+  cudaFree(d_v);
+}
+int feasm_vec_copy(feasm_ctx* ctx, int kind, void* dst, const void* src, int64_t n) {
+  if (!ctx || !dst || !src || n < 0) return feasm_fail(ctx, FEASM_ERR_ARG, "feasm_vec_copy");
+  FEASM_CUDA(ctx, cudaSetDevice(ctx->device));
+  const cudaMemcpyKind k = kind == FEASM_COPY_H2D ? cudaMemcpyHostToDevice : (kind == FEASM_COPY_D2H ? cudaMemcpyDeviceToHost : cudaMemcpyDeviceToDevice);
+  FEASM_CUDA(ctx, cudaMemcpyAsync(dst, src, sizeof(double) * (size_t)n, k, ctx->stream));
+  FEASM_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
+  return FEASM_OK;
+}
+int feasm_vec_fill(feasm_ctx* ctx, double* d_y, int64_t n, double value) {
+  if (!ctx || !d_y) return feasm_fail(ctx, FEASM_ERR_ARG, "feasm_vec_fill");
+  FEASM_CUDA(ctx, cudaSetDevice(ctx->device));
+  if (n) k_vec_fill<<<DOT_GRID, 256, 0, ctx->stream>>>(d_y, n, value);
+  FEASM_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
+  return FEASM_OK;
+}
+int feasm_vec_axpy(feasm_ctx* ctx, double* d_y, double a, const double* d_x, int64_t n) {
+  if (!ctx || !d_y || !d_x) return feasm_fail(ctx, FEASM_ERR_ARG, "feasm_vec_axpy");
+  FEASM_CUDA(ctx, cudaSetDevice(ctx->device));
+  if (n) k_vec_axpy<<<DOT_GRID, 256, 0, ctx->stream>>>(d_y, a, d_x, n);
+  FEASM_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
+  return FEASM_OK;
+}
+int feasm_vec_pointwise(feasm_ctx* ctx, int op, double* d_out, const double* d_a, const double* d_b, double s, int64_t n) {
+  if (!ctx || !d_out || !d_a || op < FEASM_VEC_MULT || op > FEASM_VEC_SCALE) return feasm_fail(ctx, FEASM_ERR_ARG, "feasm_vec_pointwise");
+  if ((op == FEASM_VEC_MULT || op == FEASM_VEC_DIV) && !d_b) return feasm_fail(ctx, FEASM_ERR_ARG, "feasm_vec_pointwise: second operand");
+  FEASM_CUDA(ctx, cudaSetDevice(ctx->device));
+  if (n) k_vec_pointwise<<<DOT_GRID, 256, 0, ctx->stream>>>(op, d_out, d_a, d_b, s, n);
+  FEASM_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
+  return FEASM_OK;
+}
+int feasm_vec_reduce(feasm_ctx* ctx, int op, const double* d_x, const double* d_y, int64_t n, double* result) {
+  if (!ctx || !d_x || !result) return feasm_fail(ctx, FEASM_ERR_ARG, "feasm_vec_reduce");
+  FEASM_CUDA(ctx, cudaSetDevice(ctx->device));
+  double* w = nullptr;
+  FEASM_CUDA(ctx, cudaMalloc(&w, sizeof(double) * (DOT_GRID + 1)));
+  int rc = FEASM_OK;
+  if (op == FEASM_VEC_DOT) {
+    if (!d_y) { cudaFree(w); return feasm_fail(ctx, FEASM_ERR_ARG, "feasm_vec_reduce: dot needs two vectors"); }
+    rc = dot(ctx, d_x, d_y, n, w, w + DOT_GRID);
+  } else if (op >= FEASM_VEC_SUM && op <= FEASM_VEC_LINF) {
+    k_vec_reduce<<<DOT_GRID, DOT_BLOCK, 0, ctx->stream>>>(op, d_x, n, w, false);
+    k_vec_reduce<<<1, DOT_BLOCK, 0, ctx->stream>>>(op, w, DOT_GRID, w + DOT_GRID, true);
+  } else {
+    rc = feasm_fail(ctx, FEASM_ERR_ARG, "feasm_vec_reduce: unknown op");
+  }
+  if (!rc && (cudaMemcpyAsync(result, w + DOT_GRID, sizeof(double), cudaMemcpyDeviceToHost, ctx->stream) != cudaSuccess ||
+              cudaStreamSynchronize(ctx->stream) != cudaSuccess))
+    rc = feasm_fail(ctx, FEASM_ERR_CUDA, "feasm_vec_reduce");
+  cudaFree(w);
+  return rc;
+}
+int feasm_vec_set_entry(feasm_ctx* ctx, double* d_y, int64_t i, double value, int add) {
+  if (!ctx || !d_y || i < 0) return feasm_fail(ctx, FEASM_ERR_ARG, "feasm_vec_set_entry");
+  FEASM_CUDA(ctx, cudaSetDevice(ctx->device));
+  k_vec_set_one<<<1, 1, 0, ctx->stream>>>(d_y, i, value, add);
+  FEASM_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
   return FEASM_OK;
 }

@@ -91,10 +91,17 @@ void assemble(EquationSystems& es, const std::string& system_name, const feasm_p
 
   // ---- the hot path -----------------------------------------------------------------------------------------------
   A->check(feasm_assemble(ctx, &params));
-  std::vector<Number> rhs(n_local);
-  A->check(feasm_get_values(ctx, nullptr, rhs.data()));  // synchronises; throws on a degenerate map like FEMap does
   A->invalidate_host_copy();
-  *system.rhs = rhs;      // NumericVector::operator=(const std::vector<T>&), include/numerics/numeric_vector.h:295
+  if (auto* grhs = dynamic_cast<GpuNumericVector<Number>*>(system.rhs)) {
+    // route (2) of SURVEY 8b: the RHS never leaves the device
+    A->check(feasm_synchronize(ctx));  // throws on a degenerate map like FEMap does
+    grhs->assign_device(feasm_device_rhs(ctx), n_local);
+  } else {
+    // route (1): any NumericVector, through NumericVector::operator=(const std::vector<T>&), numeric_vector.h:295
+    std::vector<Number> rhs(n_local);
+    A->check(feasm_get_values(ctx, nullptr, rhs.data()));  // synchronises; throws on a degenerate map like FEMap does
+    *system.rhs = rhs;
+  }
   system.rhs->close();
 }
 
@@ -117,3 +124,4 @@ void assemble_elasticity_ex6(EquationSystems& es, const std::string& name) {
 
 // explicit instantiation: every virtual of the adaptor is compiled in this translation unit
 template class libMesh::GpuSparseMatrix<libMesh::Number>;
+template class libMesh::GpuNumericVector<libMesh::Number>;

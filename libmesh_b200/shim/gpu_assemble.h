@@ -7,6 +7,7 @@
 
 #include <string>
 
+#include "gpu_numeric_vector.h"
 #include "gpu_sparse_matrix.h"
 #ifndef FEASM_SHIM_MOCK
 #include "libmesh/equation_systems.h"

@@ -6,6 +6,8 @@
 #ifndef FEASM_LIBMESH_MOCK_H
 #define FEASM_LIBMESH_MOCK_H
 
+#include <algorithm>
+#include <cmath>
 #include <cstdint>
 #include <iostream>
 #include <map>
@@ -71,7 +73,6 @@ typedef std::vector<Row> Graph;
 }
 typedef std::map<dof_id_type, Number> DofConstraintValueMap;                       // include/base/dof_map.h:123
 
-template <typename T> class SparseMatrix;
 class DofMap {                                                                     // include/base/dof_map.h
  public:
   dof_id_type n_dofs() const { return _n_dofs; }                                   // dof_map_base.h
@@ -90,16 +91,73 @@ class DofMap {                                                                  
   std::vector<dof_id_type> _elem_dofs;  // [n_elem][_nd], element id major
 };
 
-template <typename T> class NumericVector {                                        // include/numerics/numeric_vector.h
+template <typename T> class SparseMatrix;
+// include/numerics/numeric_vector.h — every virtual the reference declares pure (cited by line) is declared here with a
+// host std::vector body, so that (a) `override` in GpuNumericVector checks each signature and (b) the mock itself is a
+// usable plain vector for the route-(1) test (system.rhs as an ordinary NumericVector).
+template <typename T> class NumericVector : public ParallelObject {
  public:
+  explicit NumericVector(const Parallel::Communicator& c, const ParallelType ptype = AUTOMATIC) : ParallelObject(c), _type(ptype) {}  // :84
   virtual ~NumericVector() = default;
-  virtual void close() {}                                                          // :177
-  virtual void zero() {}
-  virtual numeric_index_type first_local_index() const { return 0; }               // :500
-  virtual numeric_index_type last_local_index() const { return 0; }
-  virtual void set(const numeric_index_type i, const T v) { if (i >= _v.size()) _v.resize(i + 1); _v[i] = v; }  // :508
-  virtual NumericVector<T>& operator=(const std::vector<T>& v) { _v = v; return *this; }  // :295
+  virtual bool initialized() const { return _is_initialized; }                                    // :152
+  virtual bool closed() const { return _is_closed; }                                              // :183
+  ParallelType type() const { return _type; }                                                     // :157
+  virtual NumericVector<T>& operator=(const NumericVector<T>& v) { _v = v._v; return *this; }      // :119
+  virtual void close() { _is_closed = true; }                                                     // :216
+  virtual void zero() { std::fill(_v.begin(), _v.end(), T(0)); }                                   // :227
+  virtual std::unique_ptr<NumericVector<T>> zero_clone() const { auto p = std::make_unique<NumericVector<T>>(comm()); p->_v.assign(_v.size(), T(0)); return p; }  // :235
+  virtual std::unique_ptr<NumericVector<T>> clone() const { auto p = std::make_unique<NumericVector<T>>(comm()); p->_v = _v; return p; }  // :242
+  virtual void init(const numeric_index_type n, const numeric_index_type, const bool = false, const ParallelType = AUTOMATIC) { _v.assign(n, T(0)); _is_initialized = true; }  // :254
+  virtual void init(const numeric_index_type n, const bool = false, const ParallelType = AUTOMATIC) { _v.assign(n, T(0)); _is_initialized = true; }  // :262
+  virtual void init(const numeric_index_type n, const numeric_index_type, const std::vector<numeric_index_type>&, const bool = false,
+                    const ParallelType = AUTOMATIC) { _v.assign(n, T(0)); _is_initialized = true; }  // :270
+  virtual void init(const NumericVector<T>& other, const bool = false) { _v.assign(other.size(), T(0)); _is_initialized = true; }  // :280
+  virtual NumericVector<T>& operator=(const T s) { std::fill(_v.begin(), _v.end(), s); return *this; }  // :288
+  virtual NumericVector<T>& operator=(const std::vector<T>& v) { _v = v; return *this; }          // :295
+  virtual Real min() const { Real m = _v.empty() ? 0 : _v[0]; for (T x : _v) m = x < m ? x : m; return m; }  // :301
+  virtual Real max() const { Real m = _v.empty() ? 0 : _v[0]; for (T x : _v) m = x > m ? x : m; return m; }  // :307
+  virtual T sum() const { T s = 0; for (T x : _v) s += x; return s; }                              // :312
+  virtual Real l1_norm() const { Real s = 0; for (T x : _v) s += x < 0 ? -x : x; return s; }       // :318
+  virtual Real l2_norm() const { Real s = 0; for (T x : _v) s += x * x; return std::sqrt(s); }     // :324
+  virtual Real linfty_norm() const { Real s = 0; for (T x : _v) s = (x < 0 ? -x : x) > s ? (x < 0 ? -x : x) : s; return s; }  // :330
+  virtual numeric_index_type size() const { return (numeric_index_type)_v.size(); }               // :372
+  virtual numeric_index_type local_size() const { return (numeric_index_type)_v.size(); }         // :377
+  virtual numeric_index_type first_local_index() const { return 0; }                              // :385
+  virtual numeric_index_type last_local_index() const { return (numeric_index_type)_v.size(); }   // :393
+  virtual T operator()(const numeric_index_type i) const { return _v[i]; }                         // :398
+  virtual NumericVector<T>& operator+=(const NumericVector<T>& v) { add(T(1), v); return *this; }  // :430
+  virtual NumericVector<T>& operator-=(const NumericVector<T>& v) { add(T(-1), v); return *this; } // :439
+  virtual NumericVector<T>& operator*=(const NumericVector<T>& v) { for (std::size_t i = 0; i < _v.size(); ++i) _v[i] *= v(i); return *this; }  // :457
+  virtual NumericVector<T>& operator/=(const NumericVector<T>& v) { for (std::size_t i = 0; i < _v.size(); ++i) _v[i] /= v(i); return *this; }  // :474
+  virtual void reciprocal() { for (T& x : _v) x = T(1) / x; }                                      // :480
+  virtual void conjugate() {}                                                                      // :485
+  virtual void set(const numeric_index_type i, const T v) { if (i >= _v.size()) _v.resize(i + 1); _v[i] = v; }  // :491
+  virtual void add(const numeric_index_type i, const T v) { _v[i] += v; }                          // :497
+  virtual void add(const T s) { for (T& x : _v) x += s; }                                          // :503
+  virtual void add(const NumericVector<T>& v) { add(T(1), v); }                                    // :510
+  virtual void add(const T a, const NumericVector<T>& v) { for (std::size_t i = 0; i < _v.size(); ++i) _v[i] += a * v(i); }  // :517
+  virtual void add_vector(const NumericVector<T>&, const SparseMatrix<T>&) { libmesh_not_implemented(); }            // :561
+  virtual void add_vector_transpose(const NumericVector<T>&, const SparseMatrix<T>&) { libmesh_not_implemented(); }  // :577
+  virtual void scale(const T f) { for (T& x : _v) x *= f; }                                        // :618
+  virtual void abs() { for (T& x : _v) x = x < 0 ? -x : x; }                                       // :623
+  virtual T dot(const NumericVector<T>& v) const { T s = 0; for (std::size_t i = 0; i < _v.size(); ++i) s += _v[i] * v(i); return s; }  // :631
+  virtual void localize(std::vector<T>& v_local) const { v_local = _v; }                           // :637
+  virtual void localize(NumericVector<T>& v_local) const { v_local = _v; }                         // :643
+  virtual void localize(NumericVector<T>& v_local, const std::vector<numeric_index_type>&) const { v_local = _v; }  // :649
+  virtual void localize(std::vector<T>& v_local, const std::vector<numeric_index_type>& indices) const {            // :681
+    v_local.resize(indices.size());
+    for (std::size_t k = 0; k < indices.size(); ++k) v_local[k] = _v[indices[k]];
+  }
+  virtual void localize(const numeric_index_type, const numeric_index_type, const std::vector<numeric_index_type>&) {}  // :688
+  virtual void localize_to_one(std::vector<T>& v_local, const processor_id_type = 0) const { v_local = _v; }            // :697
+  virtual void pointwise_mult(const NumericVector<T>& a, const NumericVector<T>& b) { for (std::size_t i = 0; i < _v.size(); ++i) _v[i] = a(i) * b(i); }    // :729
+  virtual void pointwise_divide(const NumericVector<T>& a, const NumericVector<T>& b) { for (std::size_t i = 0; i < _v.size(); ++i) _v[i] = a(i) / b(i); }  // :737
+  virtual std::size_t max_allowed_id() const { return 0xffffffffu; }                               // :847
   std::vector<T> _v;
+ protected:
+  bool _is_closed = false;                                                                         // :854
+  bool _is_initialized = false;                                                                    // :860
+  ParallelType _type;                                                                              // :865
 };
 
 template <typename T> class SparseMatrix : public ParallelObject {                  // include/numerics/sparse_matrix.h

@@ -58,7 +58,7 @@ int main() {
   // ---- the libMesh side: what EquationSystems::init() and System::solve() do with the adaptor ----------------------
   Parallel::Communicator comm;
   GpuSparseMatrix<Number> A(comm);
-  NumericVector<Number> rhs;
+  NumericVector<Number> rhs(comm);
   LinearImplicitSystem system;
   system._mesh = &mesh; system._dof = &dof_map; system.matrix = &A; system.rhs = &rhs;
   EquationSystems es;
@@ -118,7 +118,7 @@ int main() {
     for (dof_id_type x : dof_map._elem_dofs) touching += x == d;
     REQUIRE(A(d, d) == (double)touching && std::fabs(rhs._v[d] - touching * dof_map._vals[d]) <= 1e-14);
   }
-  NumericVector<Number> diag;
+  NumericVector<Number> diag(comm);
   A.get_diagonal(diag);
   for (int64_t r = 0; r < n_dofs; ++r) REQUIRE(diag._v[r] == A((numeric_index_type)r, (numeric_index_type)r));
 
@@ -163,6 +163,83 @@ int main() {
   for (int64_t i = 0; i < n_nodes; ++i)
     err = std::max(err, std::fabs(u[base[i]] - std::cos(hp * xyz[3 * i]) * std::sin(hp * xyz[3 * i + 1]) * std::cos(hp * xyz[3 * i + 2])));
   REQUIRE(err < 5e-3);                                          // coarse Q2 mesh: discretisation error only
+
+  // ---- GpuNumericVector: route (2), the vector algebra against the host mock vector, a CG written on the interface ----
+  {
+    GpuNumericVector<Number> grhs(comm, (numeric_index_type)n_dofs);
+    system.rhs = &grhs;
+    A.zero();
+    feasm_libmesh::assemble_poisson_ex4(es, "Poisson");   // RHS handed over on the device
+    A.close();
+    std::vector<Number> hb;
+    grhs.localize(hb);
+    REQUIRE(hb == b);
+    system.rhs = &rhs;
+
+    std::vector<Number> ha(n_dofs), hc(n_dofs);
+    for (int64_t i = 0; i < n_dofs; ++i) { ha[i] = std::sin(0.37 * i) + 1.5; hc[i] = std::cos(0.11 * i) * 2.0 - 0.3; }
+    NumericVector<Number> ra(comm), rc(comm);
+    ra = ha; rc = hc;
+    GpuNumericVector<Number> ga(comm, (numeric_index_type)n_dofs), gc(comm, (numeric_index_type)n_dofs);
+    ga = ha; gc = hc;
+    auto close_to = [](double x, double y) { return std::fabs(x - y) <= 1e-12 * (std::fabs(y) + 1.); };
+    auto same = [&](const GpuNumericVector<Number>& g, const NumericVector<Number>& r) {
+      std::vector<Number> h;
+      g.localize(h);
+      for (std::size_t i = 0; i < h.size(); ++i) if (!close_to(h[i], r._v[i])) return false;
+      return true;
+    };
+    REQUIRE(ga.size() == (numeric_index_type)n_dofs && ga.local_size() == ga.size() && ga.initialized());
+    REQUIRE(close_to(ga.dot(gc), ra.dot(rc)) && close_to(ga.l2_norm(), ra.l2_norm()) && close_to(ga.l1_norm(), ra.l1_norm()));
+    REQUIRE(ga.linfty_norm() == ra.linfty_norm() && gc.min() == rc.min() && gc.max() == rc.max() && close_to(gc.sum(), rc.sum()));
+    REQUIRE(close_to(ga.dot(rc), ra.dot(rc)));                       // a host vector as the second operand
+    ga.add(2.5, gc); ra.add(2.5, rc); REQUIRE(same(ga, ra));
+    ga += gc; ra += rc; ga -= gc; ra -= rc; REQUIRE(same(ga, ra));
+    ga.scale(-0.75); ra.scale(-0.75); ga.add(0.125); ra.add(0.125); REQUIRE(same(ga, ra));
+    ga.abs(); ra.abs(); REQUIRE(same(ga, ra));
+    ga *= gc; ra *= rc; REQUIRE(same(ga, ra));
+    gc.add(10.); rc.add(10.); ga /= gc; ra /= rc; REQUIRE(same(ga, ra));
+    gc.reciprocal(); rc.reciprocal(); REQUIRE(same(gc, rc));
+    ga.pointwise_mult(gc, gc); ra.pointwise_mult(rc, rc); REQUIRE(same(ga, ra));
+    ga.pointwise_divide(gc, ga); ra.pointwise_divide(rc, ra); REQUIRE(same(ga, ra));
+    ga.set(3, 42.); ga.add(3, 0.5); ga.close(); REQUIRE(ga(3) == 42.5);
+    auto gcl = ga.clone();
+    REQUIRE(gcl->dot(*gcl) == ga.dot(ga));
+    auto gz = ga.zero_clone();
+    REQUIRE(gz->linfty_norm() == 0. && gz->size() == ga.size());
+    ga = 7.0; REQUIRE(ga.min() == 7.0 && ga.max() == 7.0);
+    ga = rc; REQUIRE(same(ga, rc));                                   // assignment from a host NumericVector
+    std::vector<Number> sub;
+    ga.localize(sub, std::vector<numeric_index_type>{5, 0, 9});
+    REQUIRE(sub.size() == 3 && sub[1] == ga(0));
+
+    // y = A x through the vector interface (what SparseMatrix::vector_mult resolves to), then CG on the interface
+    GpuNumericVector<Number> gx(comm, (numeric_index_type)n_dofs), gy(comm, (numeric_index_type)n_dofs);
+    gx = 1.0;
+    gy.add_vector(gx, A);
+    std::vector<Number> hy;
+    gy.localize(hy);
+    for (int64_t r = 0; r < n_dofs; ++r) REQUIRE(close_to(hy[r], y[r]));
+    GpuNumericVector<Number> xs(comm, (numeric_index_type)n_dofs), rr(comm, (numeric_index_type)n_dofs), pp(comm, (numeric_index_type)n_dofs),
+        qq(comm, (numeric_index_type)n_dofs);
+    rr = grhs; pp = rr;
+    double rho = rr.dot(rr);
+    const double stop = 1e-24 * rho;
+    int its = 0;
+    while (rho > stop && its < 2000) {
+      qq.zero(); qq.add_vector(pp, A);
+      const double alpha = rho / pp.dot(qq);
+      xs.add(alpha, pp); rr.add(-alpha, qq);
+      const double rho_new = rr.dot(rr);
+      pp.scale(rho_new / rho); pp.add(rr);
+      rho = rho_new; ++its;
+    }
+    std::vector<Number> hx;
+    xs.localize(hx);
+    double diff = 0.;
+    for (int64_t i = 0; i < n_dofs; ++i) diff = std::max(diff, std::fabs(hx[i] - u[i]));
+    REQUIRE(its > 0 && its < 2000 && diff < 1e-9);
+  }
 
   auto Z = A.zero_clone();
   REQUIRE(Z->m() == A.m());
