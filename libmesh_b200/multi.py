@@ -352,30 +352,56 @@ def bench_multi(args, F, rank, world, local):
     kms, nl = ctx.last_timing()
     clk = clocks.stop() if rank == 0 else None
 
-    # e2e: host buffers through the C ABI on every rank: coordinates + Dirichlet data in, owned rows out
+    # e2e: host buffers through the C ABI on every rank: coordinates + Dirichlet data in, the rank's OWNED rows out (the
+    # ghost rows were added into their owners by the exchange).  The result leaves through the device-pointer accessors:
+    # a device-side snapshot on the library's stream, then the PCIe read on a second stream, so the read of step i
+    # overlaps the upload + assembly + exchange of step i+1 (the same overlap as the single-GPU e2e leg of bench.py).
     nnz_local = int(da.row_ptr[-1])
+    nnz_owned = int(da.row_ptr[prob.n_owned])
     xyz_pin = torch.from_numpy(prob.xyz).pin_memory().numpy()
-    val_pin = torch.empty(nnz_local, dtype=torch.float64).pin_memory().numpy()
-    rhs_pin = torch.empty(prob.n_rows, dtype=torch.float64).pin_memory().numpy()
+    pipelined = os.environ.get("FEASM_E2E_PIPELINE", "1") != "0"  # 0: feasm_get_values of all local rows, synchronous
+    val_pin = torch.empty(max(nnz_owned if pipelined else nnz_local, 1), dtype=torch.float64).pin_memory()
+    rhs_pin = torch.empty(max(prob.n_owned if pipelined else prob.n_rows, 1), dtype=torch.float64).pin_memory()
+    d_val = torch.as_tensor(DevArray(ctx.device_values(), max(nnz_owned, 1)), device="cuda")
+    d_rhs = torch.as_tensor(DevArray(ctx.device_rhs(), max(prob.n_owned, 1)), device="cuda")
+    snap_val, snap_rhs = torch.empty_like(d_val), torch.empty_like(d_rhs)
+    copy_stream = torch.cuda.Stream()
+    ev_ready, ev_done = torch.cuda.Event(), torch.cuda.Event()
+    ev_done.record(copy_stream)
 
     def e2e_step():
         ctx.update_coordinates(xyz_pin)
         ctx.set_constraints(prob.con_rows, prob.con_vals)
         da.assemble(params, sync=False)
-        ctx.get_values(out_values=val_pin, out_rhs=rhs_pin)
+        if not pipelined:
+            ctx.get_values(out_values=val_pin.numpy(), out_rhs=rhs_pin.numpy())
+            return
+        with torch.cuda.stream(stream):
+            stream.wait_event(ev_done)  # the previous read has left the snapshot
+            snap_val.copy_(d_val, non_blocking=True)
+            snap_rhs.copy_(d_rhs, non_blocking=True)
+            ev_ready.record(stream)
+        with torch.cuda.stream(copy_stream):
+            copy_stream.wait_event(ev_ready)
+            val_pin.copy_(snap_val, non_blocking=True)
+            rhs_pin.copy_(snap_rhs, non_blocking=True)
+            ev_done.record(copy_stream)
 
     e2e_step()
+    torch.cuda.synchronize()
+    ctx.synchronize()
     dist.barrier()
     te = time.perf_counter()
-    e2e_steps = max(2, min(args.steps, 5))
+    e2e_steps = max(3, min(args.steps, 8))
     for _ in range(e2e_steps):
         e2e_step()
     torch.cuda.synchronize()
+    ctx.synchronize()  # raises if any step flagged a degenerate element
     dist.barrier()
     e2e_s = torch.tensor([(time.perf_counter() - te) / e2e_steps], device="cuda")
     dist.all_reduce(e2e_s, op=dist.ReduceOp.MAX)
     io = torch.tensor([float(xyz_pin.nbytes + prob.con_rows.nbytes + prob.con_vals.nbytes + prob.n_rows * 9),
-                       float(val_pin.nbytes + rhs_pin.nbytes), float(len(da.send_slots) * 8), float(nnz_local)], device="cuda")
+                       float(nnz_owned * 8 + prob.n_owned * 8), float(len(da.send_slots) * 8), float(nnz_local)], device="cuda")
     dist.all_reduce(io)
     if rank == 0:
         nq = {27: 27, 8: 27 if args.qorder in (0, 5) else 8, 10: 14}[etype]
