@@ -117,6 +117,14 @@ int feasm_prepare(feasm_ctx* ctx);
  * stream; feasm_synchronize or any getter waits. */
 int feasm_assemble(feasm_ctx* ctx, const feasm_params* params);
 int feasm_synchronize(feasm_ctx* ctx);
+/* The same assembly in two halves for multi-rank runs ("exchange while the interior assembles"; the role of
+ * MatAssemblyBegin/End around the stash, petsc_matrix.C close()): _begin runs the element phase, reduces the rows this
+ * rank does NOT own (local rows n_owned..n_rows) and packs them into the send buffer (feasm_pack_ghost's buffer; it
+ * must not be packed again); the caller starts its ncclSend/ncclRecv group, then _end reduces the owned rows while
+ * the transfer is in flight; feasm_unpack_ghost after both.  Results are identical to feasm_assemble + pack. */
+int feasm_assemble_begin(feasm_ctx* ctx, const feasm_params* params);
+int feasm_assemble_end(feasm_ctx* ctx);
+double* feasm_send_buffer(feasm_ctx* ctx, uint64_t* n_doubles); /* the packed buffer, without packing again */
 /* Element-level output for tests: Ke [e1-e0][nd*nd] row-major and Fe [e1-e0][nd], constraints applied iff
  * constrained != 0; host pointers. */
 int feasm_element_matrices(feasm_ctx* ctx, const feasm_params* params, int64_t e0, int64_t e1, int constrained,

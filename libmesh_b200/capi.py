@@ -26,7 +26,7 @@ SYMBOLS = [
     "feasm_build_pattern", "feasm_nnz", "feasm_get_pattern", "feasm_prepare", "feasm_assemble",
     "feasm_synchronize", "feasm_element_matrices", "feasm_zero", "feasm_add_matrix", "feasm_add_vector",
     "feasm_get_values", "feasm_device_values", "feasm_device_rhs", "feasm_stream", "feasm_set_exchange_plan",
-    "feasm_pack_ghost", "feasm_recv_buffer", "feasm_unpack_ghost", "feasm_cube_sizes", "feasm_build_cube",
+    "feasm_assemble_begin", "feasm_assemble_end", "feasm_send_buffer", "feasm_pack_ghost", "feasm_recv_buffer", "feasm_unpack_ghost", "feasm_cube_sizes", "feasm_build_cube",
     "feasm_distribute_dofs", "feasm_last_timing", "feasm_measure_fp64_peaks", "feasm_vector_mult", "feasm_vector_mult_host", "feasm_cg_solve",
     "feasm_vec_alloc", "feasm_vec_free", "feasm_vec_copy", "feasm_vec_fill", "feasm_vec_axpy", "feasm_vec_pointwise",
     "feasm_vec_reduce", "feasm_vec_set_entry",
@@ -84,6 +84,9 @@ def lib():
         "feasm_device_rhs": (vp, [vp]),
         "feasm_stream": (vp, [vp]),
         "feasm_set_exchange_plan": (i32, [vp, i32, vp, vp, vp, vp, vp]),
+        "feasm_assemble_begin": (i32, [vp, C.POINTER(Params)]),
+        "feasm_assemble_end": (i32, [vp]),
+        "feasm_send_buffer": (vp, [vp, C.POINTER(C.c_uint64)]),
         "feasm_pack_ghost": (vp, [vp, C.POINTER(C.c_uint64)]),
         "feasm_recv_buffer": (vp, [vp, C.POINTER(C.c_uint64)]),
         "feasm_unpack_ghost": (i32, [vp]),
@@ -238,6 +241,17 @@ class Context:
         self._ck(self.L.feasm_assemble(self.h, C.byref(params)))
         if sync:
             self._ck(self.L.feasm_synchronize(self.h))
+
+    def assemble_begin(self, params):
+        self._ck(self.L.feasm_assemble_begin(self.h, C.byref(params)))
+
+    def assemble_end(self):
+        self._ck(self.L.feasm_assemble_end(self.h))
+
+    def send_buffer(self):
+        n = C.c_uint64()
+        ptr = self.L.feasm_send_buffer(self.h, C.byref(n))
+        return ptr, n.value
 
     def synchronize(self):
         self._ck(self.L.feasm_synchronize(self.h))

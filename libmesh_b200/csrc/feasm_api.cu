@@ -281,7 +281,10 @@ int feasm_prepare(feasm_ctx* ctx) {
   return FEASM_OK;
 }
 
-int feasm_assemble(feasm_ctx* ctx, const feasm_params* params) {
+// mode 0: the whole assembly.  mode 1 (feasm_assemble_begin): element phase, then the rows this rank does not own
+// (local rows n_owned..n_rows) and the pack of the send buffer, so that the exchange can start while
+// feasm_assemble_end reduces the owned rows.
+static int assemble_impl(feasm_ctx* ctx, const feasm_params* params, int mode) {
   if (!ctx || !params) return FEASM_ERR_ARG;
   FEASM_CUDA(ctx, cudaSetDevice(ctx->device));
   int rc = feasm_prepare(ctx);
@@ -307,10 +310,38 @@ int feasm_assemble(feasm_ctx* ctx, const feasm_params* params) {
   if (ctx->n_con_elems > 0) ++launches;
   if (params->problem == FEASM_POISSON && params->affine_tensor) ++launches;  // the list kernel for non-affine elements
   FEASM_CUDA(ctx, cudaEventRecord(ctx->ev[1], ctx->stream));
-  rc = feasm_launch_row_reduce(ctx, nullptr, ctx->n_rows, ctx->stream);
+  ctx->last_launches = launches;
+  if (mode == 0) {
+    rc = feasm_launch_row_reduce(ctx, nullptr, ctx->n_rows, ctx->stream);
+    if (rc) return rc;
+    FEASM_CUDA(ctx, cudaEventRecord(ctx->ev[2], ctx->stream));
+    return FEASM_OK;
+  }
+  if (ctx->n_owned < ctx->n_rows) {
+    rc = feasm_launch_row_reduce(ctx, nullptr, ctx->n_rows, ctx->stream, ctx->n_owned);
+    if (rc) return rc;
+    ++ctx->last_launches;
+  }
+  if (ctx->d_send_buf) {
+    rc = feasm_launch_pack(ctx);
+    if (rc) return rc;
+    ++ctx->last_launches;
+  }
+  ctx->assemble_open = true;
+  return FEASM_OK;
+}
+
+int feasm_assemble(feasm_ctx* ctx, const feasm_params* params) { return assemble_impl(ctx, params, 0); }
+int feasm_assemble_begin(feasm_ctx* ctx, const feasm_params* params) { return assemble_impl(ctx, params, 1); }
+
+int feasm_assemble_end(feasm_ctx* ctx) {
+  if (!ctx) return FEASM_ERR_ARG;
+  if (!ctx->assemble_open) return feasm_fail(ctx, FEASM_ERR_STATE, "feasm_assemble_end without feasm_assemble_begin");
+  FEASM_CUDA(ctx, cudaSetDevice(ctx->device));
+  ctx->assemble_open = false;
+  const int rc = feasm_launch_row_reduce(ctx, nullptr, ctx->n_owned, ctx->stream);
   if (rc) return rc;
   FEASM_CUDA(ctx, cudaEventRecord(ctx->ev[2], ctx->stream));
-  ctx->last_launches = launches;
   return FEASM_OK;
 }
 
@@ -442,6 +473,12 @@ int feasm_set_exchange_plan(feasm_ctx* ctx, int n_peers, const int32_t* peer_ran
 double* feasm_pack_ghost(feasm_ctx* ctx, uint64_t* n_doubles) {
   if (!ctx || !ctx->d_send_buf) return nullptr;
   if (feasm_launch_pack(ctx)) return nullptr;
+  if (n_doubles) *n_doubles = ctx->send_ptr.empty() ? 0 : ctx->send_ptr.back();
+  return ctx->d_send_buf;
+}
+
+double* feasm_send_buffer(feasm_ctx* ctx, uint64_t* n_doubles) {
+  if (!ctx || !ctx->d_send_buf) return nullptr;
   if (n_doubles) *n_doubles = ctx->send_ptr.empty() ? 0 : ctx->send_ptr.back();
   return ctx->d_send_buf;
 }

@@ -111,6 +111,7 @@ struct feasm_ctx {
 
   float last_ms[4] = {0, 0, 0, 0};
   int last_launches = 0;
+  bool assemble_open = false;  // between feasm_assemble_begin and feasm_assemble_end
 };
 
 // error helpers

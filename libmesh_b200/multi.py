@@ -260,34 +260,66 @@ class DistributedAssembly:
         ctx.prepare()
 
     # -- per step --------------------------------------------------------------------------------------------
-    def exchange(self):
-        """pack -> grouped send/recv with every neighbour -> unpack (fixed peer order).  Runs on the library's stream."""
+    def _exchange_ops(self):
+        """The grouped send/recv of one step (built once: buffers and slot ranges are fixed at setup)."""
+        if getattr(self, "_ops", None) is None:
+            import torch
+
+            ctx, dist = self.ctx, self.dist
+            sptr, ns = ctx.send_buffer()
+            rptr, nr = ctx.recv_buffer()
+            sbuf = torch.as_tensor(DevArray(sptr, max(ns, 1)), device="cuda")
+            rbuf = torch.as_tensor(DevArray(rptr, max(nr, 1)), device="cuda")
+            ops = []
+            for i, q in enumerate(self.peers):
+                r0, r1 = int(self.recv_ptr[i]), int(self.recv_ptr[i + 1])
+                if r1 > r0:
+                    ops.append(dist.P2POp(dist.irecv, rbuf[r0:r1], q, group=self.dev_group))
+            for i, q in enumerate(self.peers):
+                s0, s1 = int(self.send_ptr[i]), int(self.send_ptr[i + 1])
+                if s1 > s0:
+                    ops.append(dist.P2POp(dist.isend, sbuf[s0:s1], q, group=self.dev_group))
+            self._ops, self._lib_stream = ops, torch.cuda.ExternalStream(ctx.stream())
+        return self._ops
+
+    def start_exchange(self):
+        """Issue the send/recv group behind what is on the library's stream now (the packed send buffer).  NCCL runs it
+        on its own stream, so kernels launched on the library's stream afterwards overlap the transfer."""
         import torch
 
-        ctx, dist = self.ctx, self.dist
-        sptr, ns = ctx.pack_ghost()
-        rptr, nr = ctx.recv_buffer()
+        if not self.peers:
+            return []
+        ops = self._exchange_ops()
+        with torch.cuda.stream(self._lib_stream):
+            return self.dist.batch_isend_irecv(ops)
+
+    def finish_exchange(self, works):
+        """Make the library's stream wait for the transfer, then add the received rows in fixed peer order."""
+        import torch
+
         if not self.peers:
             return
-        sbuf = torch.as_tensor(DevArray(sptr, max(ns, 1)), device="cuda")
-        rbuf = torch.as_tensor(DevArray(rptr, max(nr, 1)), device="cuda")
-        ops = []
-        for i, q in enumerate(self.peers):
-            r0, r1 = int(self.recv_ptr[i]), int(self.recv_ptr[i + 1])
-            if r1 > r0:
-                ops.append(dist.P2POp(dist.irecv, rbuf[r0:r1], q, group=self.dev_group))
-        for i, q in enumerate(self.peers):
-            s0, s1 = int(self.send_ptr[i]), int(self.send_ptr[i + 1])
-            if s1 > s0:
-                ops.append(dist.P2POp(dist.isend, sbuf[s0:s1], q, group=self.dev_group))
-        with torch.cuda.stream(torch.cuda.ExternalStream(ctx.stream())):
-            for w in dist.batch_isend_irecv(ops):
-                w.wait()  # stream-ordered for NCCL: makes the library's stream wait for the transfer
-        ctx.unpack_ghost()
+        with torch.cuda.stream(self._lib_stream):
+            for w in works:
+                w.wait()  # stream-ordered for NCCL
+        self.ctx.unpack_ghost()
 
-    def assemble(self, params, sync=True):
-        self.ctx.assemble(params, sync=False)
-        self.exchange()
+    def exchange(self):
+        """pack -> grouped send/recv with every neighbour -> unpack (fixed peer order), after a plain ctx.assemble."""
+        self.ctx.pack_ghost()
+        self.finish_exchange(self.start_exchange())
+
+    def assemble(self, params, sync=True, overlap=True):
+        """One assembly step of this rank.  overlap: rows owned by other ranks are reduced and sent first, the owned rows
+        are reduced while the transfer is in flight (feasm_assemble_begin / _end); the result is the same either way."""
+        if overlap:
+            self.ctx.assemble_begin(params)
+            works = self.start_exchange()
+            self.ctx.assemble_end()
+            self.finish_exchange(works)
+        else:
+            self.ctx.assemble(params, sync=False)
+            self.exchange()
         if sync:
             self.ctx.synchronize()
 
@@ -321,14 +353,21 @@ def bench_multi(args, F, rank, world, local):
     n_dofs, base, first, _ = F.distribute_dofs(P["conn"], P["xyz"].shape[0], 1, world, pid)
     prob = RankProblem(rank, world, P["xyz"], P["conn"], base, first, pid, 1, P["con_dofs_nodes_base"](base), P["con_vals"])
     ctx = F.Context(local)
-    da = DistributedAssembly(ctx, prob, dist, host_group=host_group, dev_group=None)
+    dev_group = None
+    if os.environ.get("FEASM_OVERLAP", "1") != "0":
+        # the transfer should take SM slots as they free up while the owned rows are being reduced: NCCL's stream at
+        # high priority
+        opts = dist.ProcessGroupNCCL.Options(is_high_priority_stream=True)
+        dev_group = dist.new_group(backend="nccl", pg_options=opts)
+    da = DistributedAssembly(ctx, prob, dist, host_group=host_group, dev_group=dev_group)
     da.setup()
     ctx.synchronize()
     setup_s = time.time() - t0
     params = F.make_params(F.POISSON, args.qorder, F.FORCING_EX4_FD)
     stream = torch.cuda.ExternalStream(ctx.stream())
+    overlap = os.environ.get("FEASM_OVERLAP", "1") != "0"  # 0: feasm_assemble, then pack / exchange / unpack in sequence
     for _ in range(args.warmup):
-        da.assemble(params, sync=False)
+        da.assemble(params, sync=False, overlap=overlap)
     ctx.synchronize()
     clocks = B.ClockSampler(local)
     if rank == 0:
@@ -338,8 +377,10 @@ def bench_multi(args, F, rank, world, local):
     dist.barrier()
     torch.cuda.synchronize()
     ev0.record(stream)
+    th = time.perf_counter()
     for _ in range(args.steps):
-        da.assemble(params, sync=False)
+        da.assemble(params, sync=False, overlap=overlap)
+    host_ms = (time.perf_counter() - th) * 1e3 / args.steps  # host time to ENQUEUE one step (launch-bound check)
     ev1.record(stream)
     ctx.synchronize()
     torch.cuda.synchronize()
@@ -348,8 +389,12 @@ def bench_multi(args, F, rank, world, local):
     dist.all_reduce(ms, op=dist.ReduceOp.MAX)
     ms_per_step = float(ms.item()) / args.steps
     # per-kernel times of this rank's last step (events inside the library)
-    da.assemble(params, sync=True)
+    da.assemble(params, sync=True, overlap=overlap)
     kms, nl = ctx.last_timing()
+    nl += len(da.peers) + (0 if overlap else 1)  # unpack launches (one per peer) and the separate pack
+    kall = [torch.zeros(4, device="cuda") for _ in range(world)]  # per-rank kernel times of that step
+    dist.all_gather(kall, torch.tensor([float(x) for x in kms], device="cuda"))
+    kall = [[round(float(v), 4) for v in k.tolist()] for k in kall]
     clk = clocks.stop() if rank == 0 else None
 
     # e2e: host buffers through the C ABI on every rank: coordinates + Dirichlet data in, the rank's OWNED rows out (the
@@ -372,7 +417,7 @@ def bench_multi(args, F, rank, world, local):
     def e2e_step():
         ctx.update_coordinates(xyz_pin)
         ctx.set_constraints(prob.con_rows, prob.con_vals)
-        da.assemble(params, sync=False)
+        da.assemble(params, sync=False, overlap=overlap)
         if not pipelined:
             ctx.get_values(out_values=val_pin.numpy(), out_rhs=rhs_pin.numpy())
             return
@@ -412,15 +457,18 @@ def bench_multi(args, F, rank, world, local):
             "warmup": args.warmup, "ms_per_step": ms_per_step, "higher_is_better": True, "scaling": "strong", "vs_baseline": None,
             "dtype": "f64", "data": "synthetic",
             "config": {"workload": f"introduction_ex4 3D Poisson, build_cube {args.n}^3 {args.elem.upper()} on [-1,1]^3, QGauss nq={nq}, "
-                                   f"LinearPartitioner slabs over {world} GPUs, ghost rows by NCCL send/recv", "n_elem": n_elem,
+                                   f"LinearPartitioner slabs over {world} GPUs, ghost rows by NCCL send/recv"
+                                   + (" overlapped with the reduction of the owned rows" if overlap else ""), "n_elem": n_elem,
                        "n_dofs": int(n_dofs), "l2": "per-rank CSR values larger than L2", "setup_s": round(setup_s, 3),
-                       "ghost_bytes_per_step_all_ranks": int(io[2].item())},
-            "clocks": clk, "gpu_launches": int(nl + 2) * args.steps,
+                       "ghost_bytes_per_step_all_ranks": int(io[2].item()), "host_enqueue_ms_per_step_rank0": round(host_ms, 4)},
+            "clocks": clk, "gpu_launches": int(nl) * args.steps,
             "e2e": {"value": n_elem / float(e2e_s.item()), "unit": "elements/s", "h2d_bytes_per_step": int(io[0].item()),
                     "d2h_bytes_per_step": int(io[1].item()), "ms_per_step": float(e2e_s.item()) * 1e3},
             "roofline": {"bound": "tensor", "kernel": "k_elem_poisson on rank 0 (FP64 DMMA contraction + geometry)",
                          "achieved": flops_e * len(prob.elems) / (kms[0] * 1e-3) / 1e12, "peak": None, "unit": "TFLOP/s", "frac": None,
-                         "traffic": None, "kernel_ms": {"element": kms[0], "row_reduce": kms[1]}, "flops_per_element": flops_e},
+                         "traffic": None, "kernel_ms": {"element": kms[0], "row_reduce": kms[1]}, "flops_per_element": flops_e,
+                         "kernel_ms_per_rank": {"element": [k[0] for k in kall], "constrain": [k[3] for k in kall],
+                                                "row_reduce": [k[1] for k in kall], "assemble": [k[2] for k in kall]}},
         }
         fp64 = ctx.measure_fp64_peaks()
         pk = max(fp64["dmma_tflops"], fp64["dfma_tflops"])

@@ -10,8 +10,11 @@ from conftest import PARITY_TOL, csr_parity_error, vec_parity_error
 pytestmark = pytest.mark.gpu
 
 
+@pytest.mark.parametrize("split", [False, True], ids=["assemble", "begin_end"])
 @pytest.mark.parametrize("world,etype,dims,scramble", [(2, 27, (4, 4, 4), 0), (3, 27, (4, 3, 3), 1), (4, 8, (6, 5, 4), 1), (2, 10, (2, 2, 2), 0)])
-def test_emulated_ranks_match_global_oracle(world, etype, dims, scramble):
+def test_emulated_ranks_match_global_oracle(world, etype, dims, scramble, split):
+    """split: feasm_assemble_begin (element phase, non-owned rows, pack) / feasm_assemble_end (owned rows) around the
+    exchange, the overlapped form bench.py --gpus N runs; otherwise feasm_assemble + feasm_pack_ghost."""
     from libmesh_b200 import capi as F
     from libmesh_b200 import multi as M
     from oracle import oracle as O
@@ -48,11 +51,15 @@ def test_emulated_ranks_match_global_oracle(world, etype, dims, scramble):
     for r, da in enumerate(das):
         da.finish_plan(*pats[r], {q: msgs[q][r] for q in range(world) if r in msgs[q]})
     for r, da in enumerate(das):
-        da.ctx.assemble(F.make_params(F.POISSON, qorder, F.FORCING_TABULATED, f_host=np.ascontiguousarray(f_tab[da.p.elems])))
+        params = F.make_params(F.POISSON, qorder, F.FORCING_TABULATED, f_host=np.ascontiguousarray(f_tab[da.p.elems]))
+        if split:
+            da.ctx.assemble_begin(params)
+        else:
+            da.ctx.assemble(params)
     # exchange: every rank packs, segments are copied peer to peer, every rank unpacks
     send = []
     for da in das:
-        ptr, n = da.ctx.pack_ghost()
+        ptr, n = da.ctx.send_buffer() if split else da.ctx.pack_ghost()
         da.ctx.synchronize()
         send.append(torch.as_tensor(M.DevArray(ptr, max(n, 1)), device="cuda"))
     for r, da in enumerate(das):
@@ -65,6 +72,8 @@ def test_emulated_ranks_match_global_oracle(world, etype, dims, scramble):
                 j = dq.peers.index(r)
                 rbuf[r0:r1].copy_(send[q][int(dq.send_ptr[j]):int(dq.send_ptr[j + 1])])
         torch.cuda.synchronize()
+        if split:
+            da.ctx.assemble_end()
         if da.peers:
             da.ctx.unpack_ghost()
         da.ctx.synchronize()
