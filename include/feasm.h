@@ -98,6 +98,15 @@ int feasm_set_dofs(feasm_ctx* ctx, int n_vars, int64_t n_rows, int64_t n_owned, 
  * local row index and value g. */
 int feasm_set_constraints(feasm_ctx* ctx, int64_t n_constraints, const uint32_t* rows, const double* values);
 
+/* Side (face) loads — the boundary-integral part of the assemble loop, systems_of_equations_ex6.C:240-257:
+ *   for the listed (element, side) pairs:  fe_face->reinit(elem, side)  (src/fe/fe_boundary.C:109-240, QGauss(dim-1) of
+ *   the volume rule's order)  and  Fe_var[i](a) += JxW_face[qp] * (g[i] * phi_face[a][qp]),
+ * added to Fe after the volume terms and before the element constraint in every following feasm_assemble /
+ * feasm_element_matrices.  The adaptor fills the list from BoundaryInfo::has_boundary_id(elem, side, id) for sides
+ * without a neighbour.  g: n_g = number of variables components (a traction; n_g = 1: a Neumann flux).  HEX8 / HEX27.
+ * n = 0 clears. */
+int feasm_set_side_loads(feasm_ctx* ctx, int64_t n, const uint32_t* elems, const uint8_t* sides, const double* g, int n_g);
+
 /* ---- sparsity pattern ---------------------------------------------------------------------------- */
 /* Host graph route = SparseMatrix::update_sparsity_pattern(const SparsityPattern::Graph&)
  * (include/numerics/sparse_matrix.h:175): CSR over the n_rows local rows, columns = global ids ascending. */

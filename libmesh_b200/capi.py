@@ -26,7 +26,7 @@ SYMBOLS = [
     "feasm_build_pattern", "feasm_nnz", "feasm_get_pattern", "feasm_prepare", "feasm_assemble",
     "feasm_synchronize", "feasm_element_matrices", "feasm_zero", "feasm_add_matrix", "feasm_add_vector",
     "feasm_get_values", "feasm_device_values", "feasm_device_rhs", "feasm_stream", "feasm_set_exchange_plan",
-    "feasm_assemble_begin", "feasm_assemble_end", "feasm_send_buffer", "feasm_pack_ghost", "feasm_recv_buffer", "feasm_unpack_ghost", "feasm_cube_sizes", "feasm_build_cube",
+    "feasm_set_side_loads", "feasm_assemble_begin", "feasm_assemble_end", "feasm_send_buffer", "feasm_pack_ghost", "feasm_recv_buffer", "feasm_unpack_ghost", "feasm_cube_sizes", "feasm_build_cube",
     "feasm_distribute_dofs", "feasm_last_timing", "feasm_measure_fp64_peaks", "feasm_vector_mult", "feasm_vector_mult_host", "feasm_cg_solve",
     "feasm_vec_alloc", "feasm_vec_free", "feasm_vec_copy", "feasm_vec_fill", "feasm_vec_axpy", "feasm_vec_pointwise",
     "feasm_vec_reduce", "feasm_vec_set_entry",
@@ -84,6 +84,7 @@ def lib():
         "feasm_device_rhs": (vp, [vp]),
         "feasm_stream": (vp, [vp]),
         "feasm_set_exchange_plan": (i32, [vp, i32, vp, vp, vp, vp, vp]),
+        "feasm_set_side_loads": (i32, [vp, i64, vp, vp, vp, i32]),
         "feasm_assemble_begin": (i32, [vp, C.POINTER(Params)]),
         "feasm_assemble_end": (i32, [vp]),
         "feasm_send_buffer": (vp, [vp, C.POINTER(C.c_uint64)]),
@@ -241,6 +242,14 @@ class Context:
         self._ck(self.L.feasm_assemble(self.h, C.byref(params)))
         if sync:
             self._ck(self.L.feasm_synchronize(self.h))
+
+    def set_side_loads(self, elems, sides, g):
+        """Boundary integral Fe_var[i](a) += JxW_face (g[i] phi_face[a]) on the listed (element, side) pairs
+        (systems_of_equations_ex6.C:240-257); empty lists clear."""
+        e, sd, gg = _c(elems, np.uint32), _c(sides, np.uint8), _c(np.atleast_1d(g), np.float64)
+        if len(e) != len(sd):
+            raise ValueError("elems and sides differ in length")
+        self._ck(self.L.feasm_set_side_loads(self.h, len(e), _p(e), _p(sd), _p(gg), len(gg)))
 
     def assemble_begin(self, params):
         self._ck(self.L.feasm_assemble_begin(self.h, C.byref(params)))

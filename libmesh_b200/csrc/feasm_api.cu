@@ -139,6 +139,7 @@ void feasm_destroy(feasm_ctx* ctx) {
   release(ctx->d_xyz); release(ctx->d_conn); release(ctx->d_elem_dofs); release(ctx->d_gid);
   release(ctx->d_con_flag); release(ctx->d_con_val); release(ctx->d_row_ptr); release(ctx->d_col_idx);
   release(ctx->d_values); release(ctx->d_rhs); release(ctx->d_flags); release(ctx->d_tab); release(ctx->d_f);
+  release(ctx->d_side_elems); release(ctx->d_side_mask); release(ctx->d_side_tab); release(ctx->d_side_nodes);
   release(ctx->d_send_slots); release(ctx->d_recv_slots); release(ctx->d_send_buf); release(ctx->d_recv_buf);
   for (auto& ev : ctx->ev) if (ev) cudaEventDestroy(ev);
   cudaStreamDestroy(ctx->stream);
@@ -156,6 +157,9 @@ int feasm_set_mesh(feasm_ctx* ctx, int elem_type, int64_t n_elem, int64_t n_node
   ctx->n_elem = n_elem;
   ctx->n_nodes = n_nodes;
   ctx->tab_qorder = -1;
+  ctx->side_qorder = -1;
+  release(ctx->d_side_elems); release(ctx->d_side_mask);  // element ids of the previous mesh
+  ctx->n_side_elems = 0;
   int rc = upload(ctx, &ctx->d_xyz, xyz, (size_t)n_nodes * 3);
   if (rc) return rc;
   rc = upload(ctx, &ctx->d_conn, conn, (size_t)n_elem * ctx->npe);

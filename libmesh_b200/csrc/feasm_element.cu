@@ -491,7 +491,10 @@ int feasm_launch_element_kernel(feasm_ctx* ctx, const feasm_params& p, const dou
                                 double* d_kf, int rs, int constrain_mode) {
   int rc = launch_element_kernel(ctx, p, d_f, e0, e1, d_kf, rs);
   if (rc) return rc;
-  FEASM_CUDA(ctx, cudaEventRecord(ctx->ev[3], ctx->stream));  // feasm_last_timing: element kernel | constraint pass
+  FEASM_CUDA(ctx, cudaEventRecord(ctx->ev[3], ctx->stream));  // feasm_last_timing: element kernel | side loads + constraint pass
+  // boundary integrals over the loaded sides (systems_of_equations_ex6.C:240-257), before the constraints like there
+  rc = feasm_launch_side_loads(ctx, ctx->tab_qorder, e0, e1, d_kf, rs);  // QGauss(dim-1) of the volume rule's order
+  if (rc) return rc;
   // Dirichlet constraints on the few elements that touch a constrained dof, as the reference applies them to Ke/Fe
   // before add_matrix (constrain_mode < 0: leave Ke/Fe unconstrained)
   if (constrain_mode >= 0 && ctx->n_con_elems > 0) {

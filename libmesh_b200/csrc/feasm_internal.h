@@ -21,6 +21,15 @@ struct FeasmTables {
   std::vector<double> dxi, deta, dzeta;
 };
 bool feasm_make_tables(int elem_type, int qorder, FeasmTables& t, std::string& err);
+// The same for the sides of an element type (FE::reinit(elem, side), src/fe/fe_boundary.C:109-240)
+struct FeasmSideTables {
+  int npe = 0, ns = 0, nqf = 0;    // parent nodes, side nodes, side quadrature points
+  std::vector<int> side_nodes;     // [6][ns] parent-local node of side node i
+  std::vector<double> qw;          // nqf
+  std::vector<double> psi, dxi, deta;  // [ns][nqf] the side's map functions and derivatives
+  std::vector<double> phi;         // [6][npe][nqf] parent shapes at the side points
+};
+bool feasm_make_side_tables(int elem_type, int qorder, FeasmSideTables& t, std::string& err);
 
 // Element records REC[e][a], feasm_recb bytes each: row a of element e = Ke(a, 0..nd-1) followed by Fe(a) at column
 // nd, padded to a whole number of 32 B sectors (HEX27: 28 doubles = 224 B), then the position-map row of the (e,a)
@@ -96,6 +105,16 @@ struct feasm_ctx {
   int tab_nq = 0;
   double* d_tab = nullptr;  // phi | dxi | deta | dzeta | qw  (4*npe*nq + nq doubles)
 
+  // side loads (feasm_set_side_loads): elements with at least one loaded side, ascending, and their side bits
+  int64_t n_side_elems = 0;
+  uint32_t* d_side_elems = nullptr;
+  uint8_t* d_side_mask = nullptr;
+  double side_g[3] = {0., 0., 0.};
+  int side_qorder = -1;            // the side tables on the device are for this order
+  int side_ns = 0, side_nqf = 0;
+  double* d_side_tab = nullptr;    // qw[nqf] | dxi[ns][nqf] | deta[ns][nqf] | phi[6][npe][nqf]
+  int* d_side_nodes = nullptr;     // [6][ns]
+
   // tabulated forcing copy
   double* d_f = nullptr;
   size_t d_f_cap = 0;
@@ -133,6 +152,8 @@ int feasm_build_pos(feasm_ctx* ctx);
 int feasm_launch_element_kernel(feasm_ctx* ctx, const feasm_params& p, const double* d_f, int64_t e0, int64_t e1,
                                 double* d_kf, int rs, int constrain_mode);
 int feasm_launch_elem_flags(feasm_ctx* ctx);
+// feasm_side.cu: adds the side loads to the Fe column of the records of elements [e0, e1) (no-op without loads)
+int feasm_launch_side_loads(feasm_ctx* ctx, int qorder, int64_t e0, int64_t e1, double* d_kf, int rs);
 // d_row_list == nullptr: every row; else the n_list rows listed
 int feasm_launch_row_reduce(feasm_ctx* ctx, const uint32_t* d_row_list, int64_t n_list, cudaStream_t stream, int64_t row0 = 0);
 int feasm_launch_pack(feasm_ctx* ctx);

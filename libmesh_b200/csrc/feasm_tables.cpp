@@ -43,6 +43,14 @@ int gauss1d(int qorder, double x[3], double w[3]) {
   return 0;
 }
 
+// Sides of a hex in libMesh's side order (0 = zeta-min, 1 = eta-min, 2 = xi-max, 3 = eta-max, 4 = xi-min, 5 = zeta-max):
+// parent-local node of side node i, for i in the QUAD4/QUAD9 node order (4 corners, 4 mid-edges, centre).
+// src/geom/cell_hex27.C:37-45; the first four columns are cell_hex8.C:42-50.
+const unsigned char kHexSide[6][9] = {{0, 3, 2, 1, 11, 10, 9, 8, 20},  {0, 1, 5, 4, 8, 13, 16, 12, 21}, {1, 2, 6, 5, 9, 14, 17, 13, 22},
+                                      {2, 3, 7, 6, 10, 15, 18, 14, 23}, {3, 0, 4, 7, 11, 12, 19, 15, 24}, {4, 5, 6, 7, 16, 17, 18, 19, 25}};
+// Reference coordinates of the QUAD9 nodes (QUAD4 = the first four)
+const signed char kQuadNode[9][2] = {{-1, -1}, {1, -1}, {1, 1}, {-1, 1}, {0, -1}, {1, 0}, {0, 1}, {-1, 0}, {0, 0}};
+
 // TET10: vertex pair of each mid-edge node 4..9
 const int kTetEdge[6][2] = {{0, 1}, {1, 2}, {0, 2}, {0, 3}, {1, 3}, {2, 3}};
 
@@ -119,4 +127,46 @@ bool feasm_make_tables(int elem_type, int qorder, FeasmTables& t, std::string& e
   }
   err = "unknown element type";
   return false;
+}
+
+// Side tables of a hex: the side element's Gauss rule (tensor rule, i fastest: quadrature.C:256-277), its Lagrange map
+// functions and their derivatives at those points (FEMap::init_face_shape_functions, fe_boundary.C:458-660), and for
+// each of the six sides the parent's shape functions at the side points carried into the parent's reference space
+// (FE::side_map, fe_boundary.C:347-400: sum over the side nodes of psi_i times the reference node).
+bool feasm_make_side_tables(int elem_type, int qorder, FeasmSideTables& t, std::string& err) {
+  t = FeasmSideTables();
+  if (elem_type != FEASM_HEX8 && elem_type != FEASM_HEX27) { err = "side loads: HEX8 / HEX27 sides only"; return false; }
+  const int deg = elem_type == FEASM_HEX8 ? 1 : 2;
+  t.npe = elem_type;
+  t.ns = deg == 1 ? 4 : 9;
+  double x[3], w[3];
+  const int n1 = gauss1d(qorder, x, w);
+  if (!n1) { err = "unsupported Gauss order for a side"; return false; }
+  t.nqf = n1 * n1;
+  t.qw.resize(t.nqf);
+  t.psi.resize((size_t)t.ns * t.nqf); t.dxi.resize(t.psi.size()); t.deta.resize(t.psi.size());
+  for (int p = 0; p < t.nqf; ++p) {
+    const int i = p % n1, j = p / n1;
+    t.qw[p] = w[i] * w[j];
+    for (int a = 0; a < t.ns; ++a) {
+      const V1 X = lagrange1d(deg, kQuadNode[a][0], x[i]), Y = lagrange1d(deg, kQuadNode[a][1], x[j]);
+      t.psi[(size_t)a * t.nqf + p] = X.v * Y.v;
+      t.dxi[(size_t)a * t.nqf + p] = X.d * Y.v;
+      t.deta[(size_t)a * t.nqf + p] = X.v * Y.d;
+    }
+  }
+  t.side_nodes.resize(6 * t.ns);
+  t.phi.assign((size_t)6 * t.npe * t.nqf, 0.);
+  for (int s = 0; s < 6; ++s) {
+    for (int a = 0; a < t.ns; ++a) t.side_nodes[s * t.ns + a] = kHexSide[s][a];
+    for (int p = 0; p < t.nqf; ++p) {
+      double r[3] = {0., 0., 0.};
+      for (int a = 0; a < t.ns; ++a)
+        for (int d = 0; d < 3; ++d) r[d] += t.psi[(size_t)a * t.nqf + p] * (double)kHexNode[kHexSide[s][a]][d];
+      for (int a = 0; a < t.npe; ++a)
+        t.phi[((size_t)s * t.npe + a) * t.nqf + p] =
+            lagrange1d(deg, kHexNode[a][0], r[0]).v * lagrange1d(deg, kHexNode[a][1], r[1]).v * lagrange1d(deg, kHexNode[a][2], r[2]).v;
+    }
+  }
+  return true;
 }

@@ -30,7 +30,8 @@ extern "C" {
 
 /* problems */
 #define ORC_POISSON_EX4 1    /* examples/introduction/introduction_ex4/introduction_ex4.C:313-563 */
-#define ORC_ELASTICITY_EX6 2 /* examples/systems_of_equations/systems_of_equations_ex6/systems_of_equations_ex6.C:156-264 (no traction) */
+#define ORC_ELASTICITY_EX6 2 /* examples/systems_of_equations/systems_of_equations_ex6/systems_of_equations_ex6.C:156-264; the traction
+                              * term :240-257 through orc_system_set_side_loads */
 #define ORC_LAPLACE 3        /* Poisson with f = 0 (config 4) */
 
 /* forcing selection for ORC_POISSON_EX4 */
@@ -51,6 +52,11 @@ int orc_shapes(int elem_type, int np, const double* ref_points, double* phi, dou
 int orc_fe_reinit(int elem_type, const double* node_xyz /*n*3*/, int np, const double* ref_points,
                   const double* weights, double* xyz, double* JxW, double* phi, double* dphi);
 int orc_has_affine_map(int elem_type, const double* node_xyz);
+/* FE::reinit(elem, side) with the side's own Gauss rule (src/fe/fe_boundary.C:109-240), HEX8/HEX27: returns the number
+ * of side quadrature points nqf (<= cap) and fills ref_points[nqf][3] (the points in the parent's reference space,
+ * FE::side_map), xyz[nqf][3], JxW[nqf], normals[nqf][3], phi[n][nqf] (any may be NULL); < 0 on error. */
+int orc_side_reinit(int elem_type, const double* node_xyz /*n*3*/, int side, int qorder, int cap, double* ref_points,
+                    double* xyz, double* JxW, double* normals, double* phi);
 
 /* ---- mesh (src/mesh/mesh_generation.C build_cube) ---- */
 orc_mesh* orc_mesh_build_cube(int elem_type, int nx, int ny, int nz, double xmin, double xmax, double ymin,
@@ -63,6 +69,8 @@ void orc_mesh_get(const orc_mesh*, double* xyz /*n_nodes*3*/, uint32_t* conn /*n
                   uint8_t* node_boundary_mask /*n_nodes, bit b = on boundary id b*/);
 /* tests/fe/fe_test.h:40-64 SkewFunc: x += 0.1*y ... ; kind 1 = seeded interior perturbation */
 void orc_mesh_skew(orc_mesh*, int kind, double amplitude, uint64_t seed);
+/* (element, side) pairs carrying one boundary id (BoundaryInfo after build_cube); returns the count (fills <= cap) */
+int64_t orc_mesh_boundary_sides(const orc_mesh*, int boundary_id, int64_t cap, uint32_t* elems, uint8_t* sides);
 /* LinearPartitioner (src/partitioning/linear_partitioner.C:36-80) */
 void orc_mesh_partition_linear(orc_mesh*, int n_parts);
 void orc_mesh_set_partition(orc_mesh*, int n_parts, const int32_t* elem_pid);
@@ -78,6 +86,10 @@ void orc_system_get_dofs(const orc_system*, uint32_t* elem_dofs /*n_elem*nd*/, u
 /* Dirichlet on the boundary ids in id_mask; kind 0: g = exact_solution (ex4), kind 1: g = 0 (ex6).  Returns count. */
 int64_t orc_system_add_dirichlet(orc_system*, uint32_t id_mask, int kind);
 void orc_system_get_constraints(const orc_system*, uint32_t* dofs, double* values);
+/* Side loads, systems_of_equations_ex6.C:240-257: Fe_var[i](a) += JxW_face[qp] * (g[i] * phi_face[a][qp]) on the listed
+ * sides (QGauss(dim-1) of the volume rule's order), added after the volume terms and before the element constraint.
+ * g has one component per variable.  n = 0 clears. */
+void orc_system_set_side_loads(orc_system*, int64_t n, const uint32_t* elems, const uint8_t* sides, const double* g);
 /* SparsityPattern::Build (src/base/sparsity_pattern.C:96-363): returns nnz */
 int64_t orc_system_build_sparsity(orc_system*);
 void orc_system_get_sparsity(const orc_system*, uint64_t* row_ptr /*n_dofs+1*/, uint32_t* col_idx /*nnz*/);

@@ -43,6 +43,9 @@ def _load(fast: bool):
         "orc_shapes": (C.c_int, [C.c_int, C.c_int, _f64p, vp, vp, vp, vp]),
         "orc_fe_reinit": (C.c_int, [C.c_int, _f64p, C.c_int, _f64p, _f64p, vp, vp, vp, vp]),
         "orc_has_affine_map": (C.c_int, [C.c_int, _f64p]),
+        "orc_side_reinit": (C.c_int, [C.c_int, _f64p, C.c_int, C.c_int, C.c_int, vp, vp, vp, vp, vp]),
+        "orc_mesh_boundary_sides": (C.c_int64, [vp, C.c_int, C.c_int64, vp, vp]),
+        "orc_system_set_side_loads": (None, [vp, C.c_int64, vp, vp, vp]),
         "orc_mesh_build_cube": (vp, [C.c_int] * 4 + [C.c_double] * 6 + [C.c_int]),
         "orc_mesh_free": (None, [vp]),
         "orc_mesh_n_elem": (C.c_int64, [vp]),
@@ -125,6 +128,17 @@ def fe_reinit(elem_type: int, node_xyz: np.ndarray, ref_points: np.ndarray, weig
     return dict(affine=bool(rc), xyz=xyz, JxW=JxW, phi=phi, dphi=dphi)
 
 
+def side_reinit(elem_type: int, node_xyz: np.ndarray, side: int, qorder: int):
+    """FE::reinit(elem, side): dict(ref, xyz, JxW, normals, phi[n][nqf])."""
+    X = np.ascontiguousarray(node_xyz, dtype=np.float64).reshape(elem_type, 3)
+    cap = 9
+    ref, xyz, JxW, nrm, phi = np.zeros((cap, 3)), np.zeros((cap, 3)), np.zeros(cap), np.zeros((cap, 3)), np.zeros(elem_type * cap)
+    nqf = lib().orc_side_reinit(elem_type, X, side, qorder, cap, _ptr(ref), _ptr(xyz), _ptr(JxW), _ptr(nrm), _ptr(phi))
+    if nqf < 0:
+        raise OracleError(lib().orc_last_error().decode())
+    return dict(ref=ref[:nqf], xyz=xyz[:nqf], JxW=JxW[:nqf], normals=nrm[:nqf], phi=phi[: elem_type * nqf].reshape(elem_type, nqf))
+
+
 def has_affine_map(elem_type: int, node_xyz: np.ndarray) -> bool:
     X = np.ascontiguousarray(node_xyz, dtype=np.float64).reshape(elem_type, 3)
     return bool(lib().orc_has_affine_map(elem_type, X))
@@ -169,6 +183,15 @@ class Mesh:
         mask = np.zeros(self.n_nodes, dtype=np.uint8)
         self.L.orc_mesh_get(self.h, _ptr(xyz), _ptr(conn), _ptr(mask))
         return xyz, conn, mask
+
+    def boundary_sides(self, boundary_id):
+        """(elems, sides) carrying the boundary id (BoundaryInfo after build_cube), element-major order."""
+        n = self.L.orc_mesh_boundary_sides(self.h, boundary_id, 0, None, None)
+        if n < 0:
+            raise OracleError("boundary sides: HEX8/HEX27 only")
+        e, s = np.zeros(n, dtype=np.uint32), np.zeros(n, dtype=np.uint8)
+        self.L.orc_mesh_boundary_sides(self.h, boundary_id, n, _ptr(e), _ptr(s))
+        return e, s
 
     def skew(self, kind=0, amplitude=0.0, seed=12345):
         self.L.orc_mesh_skew(self.h, kind, float(amplitude), seed)
@@ -230,6 +253,14 @@ class System:
         vals = np.zeros(n)
         self.L.orc_system_get_constraints(self.h, _ptr(dofs), _ptr(vals))
         return dofs, vals
+
+    def set_side_loads(self, elems, sides, g):
+        """systems_of_equations_ex6.C:240-257: traction g (one component per variable) on the listed sides."""
+        e = np.ascontiguousarray(elems, dtype=np.uint32)
+        sd = np.ascontiguousarray(sides, dtype=np.uint8)
+        gg = np.zeros(3)
+        gg[: self.n_vars] = np.asarray(g, dtype=np.float64).reshape(-1)[: self.n_vars]
+        self.L.orc_system_set_side_loads(self.h, len(e), _ptr(e), _ptr(sd), _ptr(gg))
 
     def build_sparsity(self):
         self.nnz = self.L.orc_system_build_sparsity(self.h)

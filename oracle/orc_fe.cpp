@@ -331,6 +331,105 @@ int fe_reinit(int type, const double* X, const ShapeTable& t, const double* qw, 
   return affine;
 }
 
+// ---- sides: FE<3,LAGRANGE>::reinit(elem, side) ------------------------------------------------------------------
+// src/fe/fe_boundary.C:109-240: the side's own Gauss rule (QBase::tensor_product_quad, quadrature.C:256-277), the
+// side's Lagrange map psi (init_face_shape_functions :458-660; QUAD4/QUAD9 tensor shapes fe_lagrange_shape_2D.C:355-356,
+// :488-489), FEMap::compute_face_map 3D (:885-1017: JxW = sqrt(g11 g22 - g12 g21) w), FE::side_map (:347-400: parent
+// reference points = sum_i psi_i refnode[local_side_node(s, i)]) and the parent's shapes at those points.
+static const int H27_SIDE[6][9] = {{0, 3, 2, 1, 11, 10, 9, 8, 20},  {0, 1, 5, 4, 8, 13, 16, 12, 21},   // cell_hex27.C:37-45
+                                   {1, 2, 6, 5, 9, 14, 17, 13, 22}, {2, 3, 7, 6, 10, 15, 18, 14, 23},
+                                   {3, 0, 4, 7, 11, 12, 19, 15, 24}, {4, 5, 6, 7, 16, 17, 18, 19, 25}};
+static const int H8_SIDE[6][4] = {{0, 3, 2, 1}, {0, 1, 5, 4}, {1, 2, 6, 5}, {2, 3, 7, 6}, {3, 0, 4, 7}, {4, 5, 6, 7}};  // cell_hex8.C:42-50
+static const int Q4_I0[4] = {0, 1, 1, 0}, Q4_I1[4] = {0, 0, 1, 1};
+static const int Q9_I0[9] = {0, 1, 1, 0, 2, 1, 2, 0, 2}, Q9_I1[9] = {0, 0, 1, 1, 0, 2, 1, 2, 2};
+
+int side_nodes(int elem_type, int side, int* nodes) {
+  if (side < 0 || side >= 6) return 0;
+  if (elem_type == ORC_HEX27) { for (int i = 0; i < 9; ++i) nodes[i] = H27_SIDE[side][i]; return 9; }
+  if (elem_type == ORC_HEX8) { for (int i = 0; i < 4; ++i) nodes[i] = H8_SIDE[side][i]; return 4; }
+  return 0;
+}
+
+int side_reinit(int elem_type, const double* X, int side, int qorder, SideData& sd) {
+  int sn[9];
+  const int ns = side_nodes(elem_type, side, sn);
+  if (!ns) { set_error("side_reinit: HEX8/HEX27 sides only"); return -1; }
+  const bool q2 = ns == 9;
+  double gx[3], gw[3];
+  const int np = gauss_1d(qorder, gx, gw);
+  if (!np) { set_error("unsupported side quadrature order"); return -1; }
+  const int nqf = np * np;
+  sd.nqf = nqf;
+  std::vector<double> pts(2 * nqf), qw(nqf);
+  {
+    int q = 0;
+    for (int j = 0; j < np; j++)
+      for (int i = 0; i < np; i++) {
+        pts[2 * q] = gx[i];
+        pts[2 * q + 1] = gx[j];
+        qw[q] = gw[i] * gw[j];
+        q++;
+      }
+  }
+  // psi_map, dpsidxi_map, dpsideta_map [i][p]
+  std::vector<double> psi(ns * nqf), dxi(ns * nqf), deta(ns * nqf);
+  for (int i = 0; i < ns; ++i)
+    for (int p = 0; p < nqf; ++p) {
+      const double xi = pts[2 * p], eta = pts[2 * p + 1];
+      if (q2) {
+        psi[i * nqf + p] = quad(Q9_I0[i], xi) * quad(Q9_I1[i], eta);
+        dxi[i * nqf + p] = dquad(Q9_I0[i], xi) * quad(Q9_I1[i], eta);
+        deta[i * nqf + p] = quad(Q9_I0[i], xi) * dquad(Q9_I1[i], eta);
+      } else {
+        psi[i * nqf + p] = lin(Q4_I0[i], xi) * lin(Q4_I1[i], eta);
+        dxi[i * nqf + p] = dlin(Q4_I0[i]) * lin(Q4_I1[i], eta);
+        deta[i * nqf + p] = lin(Q4_I0[i], xi) * dlin(Q4_I1[i]);
+      }
+    }
+  // compute_face_map, 3D case
+  sd.xyz.assign(3 * nqf, 0.);
+  sd.JxW.assign(nqf, 0.);
+  sd.normal.assign(3 * nqf, 0.);
+  std::vector<double> dxyzdxi(3 * nqf, 0.), dxyzdeta(3 * nqf, 0.);
+  for (int i = 0; i < ns; ++i) {
+    const double* sp = &X[3 * sn[i]];
+    for (int p = 0; p < nqf; ++p)
+      for (int d = 0; d < 3; ++d) {
+        sd.xyz[3 * p + d] += psi[i * nqf + p] * sp[d];
+        dxyzdxi[3 * p + d] += dxi[i * nqf + p] * sp[d];
+        dxyzdeta[3 * p + d] += deta[i * nqf + p] * sp[d];
+      }
+  }
+  for (int p = 0; p < nqf; ++p) {
+    const double* a = &dxyzdxi[3 * p];
+    const double* b = &dxyzdeta[3 * p];
+    const double n[3] = {a[1] * b[2] - a[2] * b[1], -a[0] * b[2] + a[2] * b[0], a[0] * b[1] - a[1] * b[0]};  // TypeVector::cross
+    const double len = std::sqrt(n[0] * n[0] + n[1] * n[1] + n[2] * n[2]);
+    for (int d = 0; d < 3; ++d) sd.normal[3 * p + d] = n[d] / len;
+    const double g11 = (a[0] * a[0] + a[1] * a[1] + a[2] * a[2]);
+    const double g12 = (a[0] * b[0] + a[1] * b[1] + a[2] * b[2]);
+    const double g21 = g12;
+    const double g22 = (b[0] * b[0] + b[1] * b[1] + b[2] * b[2]);
+    const double the_jac = std::sqrt(g11 * g22 - g12 * g21);
+    if (!(the_jac > 0.)) { set_error("degenerate side map"); return -1; }
+    sd.JxW[p] = the_jac * qw[p];
+  }
+  // side_map: the quadrature points in the parent's reference space (refspace nodes: fe_abstract.C get_refspace_nodes)
+  static const double REF[3] = {-1., 1., 0.};
+  sd.ref.assign(3 * nqf, 0.);
+  for (int i = 0; i < ns; ++i) {
+    const int a = sn[i];
+    const double node[3] = {REF[q2 ? H27_I0[a] : H8_I0[a]], REF[q2 ? H27_I1[a] : H8_I1[a]], REF[q2 ? H27_I2[a] : H8_I2[a]]};
+    for (int p = 0; p < nqf; ++p)
+      for (int d = 0; d < 3; ++d) sd.ref[3 * p + d] += psi[i * nqf + p] * node[d];
+  }
+  // this->reinit(elem, &qp): the parent's shape functions at the mapped points
+  ShapeTable t;
+  shape_table(elem_type, nqf, sd.ref.data(), t);
+  sd.phi = t.phi;
+  return nqf;
+}
+
 // examples/introduction/introduction_ex3/exact_solution.C:40-47
 double exact_solution(double x, double y, double z) {
   static const double pi = std::acos(-1.);
@@ -373,6 +472,20 @@ int orc_shapes(int elem_type, int np, const double* ref_points, double* phi, dou
   if (deta) std::memcpy(deta, t.deta.data(), b);
   if (dzeta) std::memcpy(dzeta, t.dzeta.data(), b);
   return t.n;
+}
+
+int orc_side_reinit(int elem_type, const double* node_xyz, int side, int qorder, int cap, double* ref_points, double* xyz,
+                    double* JxW, double* normals, double* phi) {
+  orc::SideData sd;
+  const int nqf = orc::side_reinit(elem_type, node_xyz, side, qorder, sd);
+  if (nqf < 0) return nqf;
+  if (nqf > cap) return -2;
+  if (ref_points) std::memcpy(ref_points, sd.ref.data(), sizeof(double) * 3 * nqf);
+  if (xyz) std::memcpy(xyz, sd.xyz.data(), sizeof(double) * 3 * nqf);
+  if (JxW) std::memcpy(JxW, sd.JxW.data(), sizeof(double) * nqf);
+  if (normals) std::memcpy(normals, sd.normal.data(), sizeof(double) * 3 * nqf);
+  if (phi) std::memcpy(phi, sd.phi.data(), sizeof(double) * elem_type * nqf);
+  return nqf;
 }
 
 int orc_has_affine_map(int elem_type, const double* node_xyz) { return orc::has_affine_map(elem_type, node_xyz) ? 1 : 0; }

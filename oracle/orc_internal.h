@@ -42,6 +42,18 @@ bool has_affine_map(int elem_type, const double* X /*n*3*/);
 // returns 1 affine, 0 general, -1 degenerate
 int fe_reinit(int elem_type, const double* X, const ShapeTable& tab, const double* qw, FEData& fe);
 
+// What FE::reinit(elem, side) leaves behind (fe_boundary.C:109-240)
+struct SideData {
+  int nqf = 0;
+  std::vector<double> ref;     // nqf*3: the side quadrature points in the parent's reference space (side_map)
+  std::vector<double> xyz;     // nqf*3
+  std::vector<double> JxW;     // nqf
+  std::vector<double> normal;  // nqf*3
+  std::vector<double> phi;     // n*nqf: parent shapes at ref
+};
+int side_nodes(int elem_type, int side, int* nodes);  // Elem::local_side_node; returns nodes per side (0: unsupported)
+int side_reinit(int elem_type, const double* X, int side, int qorder, SideData& sd);  // returns nqf or -1
+
 double exact_solution(double x, double y, double z);
 double ex4_forcing(double x, double y, double z);
 

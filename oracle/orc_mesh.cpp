@@ -237,6 +237,29 @@ void orc_mesh_skew(orc_mesh* h, int kind, double amplitude, uint64_t seed) {
   }
 }
 
+// The (element, side) pairs BoundaryInfo holds for one boundary id after build_cube (mesh_generation.C:1416-1432,
+// :1913-1926: side s of a lattice-edge element gets id s' iff the side lies in that face of the box), recovered from
+// the per-node masks: a side lies in face b iff all its nodes do.  Element-major, side-minor order.
+int64_t orc_mesh_boundary_sides(const orc_mesh* h, int boundary_id, int64_t cap, uint32_t* elems, uint8_t* sides) {
+  const orc::Mesh& m = h->m;
+  int sn[9];
+  if (!orc::side_nodes(m.type, 0, sn)) return -1;
+  int64_t k = 0;
+  for (int64_t e = 0; e < m.n_elem; ++e)
+    for (int s = 0; s < 6; ++s) {
+      const int ns = orc::side_nodes(m.type, s, sn);
+      bool all = true;
+      for (int i = 0; i < ns && all; ++i) all = (m.bmask[m.conn[e * m.npe + sn[i]]] >> boundary_id) & 1;
+      if (!all) continue;
+      if (k < cap) {
+        if (elems) elems[k] = (uint32_t)e;
+        if (sides) sides[k] = (uint8_t)s;
+      }
+      ++k;
+    }
+  return k;
+}
+
 void orc_mesh_partition_linear(orc_mesh* h, int n_parts) {
   orc::Mesh& m = h->m;
   m.n_parts = n_parts;

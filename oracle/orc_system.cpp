@@ -29,6 +29,10 @@ struct System {
   int64_t n_con = 0;
   std::vector<uint64_t> row_ptr;
   std::vector<uint32_t> col_idx;
+  // side loads (systems_of_equations_ex6.C:240-257): bit s of side_mask[e] = side s of element e carries the
+  // traction side_g (one component per variable)
+  std::vector<uint8_t> side_mask;
+  double side_g[3] = {0., 0., 0.};
 };
 
 static void distribute_dofs(System& s) {
@@ -114,12 +118,13 @@ static int64_t build_sparsity(System& s) {
 // ---- element matrices ------------------------------------------------------------------------------
 struct ElemWork {
   FEData fe;
+  SideData sd;
   std::vector<double> Ke, Fe, KH, X;
   std::vector<uint32_t> dofs;
 };
 
 struct Problem {
-  int problem, forcing;
+  int problem, forcing, qorder;
   const double* f_tab;
   QRule q;
   ShapeTable tab;
@@ -136,6 +141,7 @@ static bool setup_problem(const System& s, int problem, int qorder, int forcing,
   if (problem != ORC_ELASTICITY_EX6 && s.n_vars != 1) { set_error("Poisson needs 1 variable"); return false; }
   P.problem = problem;
   P.forcing = forcing;
+  P.qorder = qorder;
   P.f_tab = f_tab;
   if (!gauss_rule(m.type, qorder, P.q)) return false;
   shape_table(m.type, P.q.nq, P.q.pts.data(), P.tab);
@@ -230,6 +236,18 @@ static int element_matrix(const System& s, const Problem& P, int64_t e, ElemWork
     if (t) {
       t[0] += std::chrono::duration<double>(t1 - t0).count();
       t[1] += std::chrono::duration<double>(t2 - t1).count();
+    }
+  }
+  // assemble \int_\Gamma g_i v_i ds (systems_of_equations_ex6.C:240-257): fe_face->reinit(elem, side) with
+  // QGauss(dim-1, same order), then Fe_var[i](dof_i) += JxW_face[qp] * (g_vec(i) * phi_face[dof_i][qp])
+  if (!s.side_mask.empty() && s.side_mask[e]) {
+    for (int side = 0; side < 6; ++side) {
+      if (!(s.side_mask[e] >> side & 1)) continue;
+      if (side_reinit(m.type, w.X.data(), side, P.qorder, w.sd) < 0) return -1;
+      const int nqf = w.sd.nqf;
+      for (int qp = 0; qp < nqf; qp++)
+        for (int di = 0; di < n; di++)
+          for (int i = 0; i < s.n_vars; i++) w.Fe[i * n + di] += w.sd.JxW[qp] * (s.side_g[i] * w.sd.phi[di * nqf + qp]);
     }
   }
   return 0;
@@ -391,6 +409,15 @@ void orc_system_get_constraints(const orc_system* h, uint32_t* dofs, double* val
       if (values) values[k] = s.con_val[d];
       k++;
     }
+}
+
+void orc_system_set_side_loads(orc_system* h, int64_t n, const uint32_t* elems, const uint8_t* sides, const double* g) {
+  orc::System& s = h->s;
+  s.side_mask.clear();
+  if (n <= 0) return;
+  s.side_mask.assign(s.mesh->n_elem, 0);
+  for (int64_t k = 0; k < n; ++k) s.side_mask[elems[k]] |= (uint8_t)(1u << sides[k]);
+  for (int i = 0; i < 3; ++i) s.side_g[i] = i < s.n_vars ? g[i] : 0.;
 }
 
 int64_t orc_system_build_sparsity(orc_system* h) { return orc::build_sparsity(h->s); }

@@ -1,0 +1,90 @@
+"""GPU parity of the side (face) terms — feasm_set_side_loads — against the CPU oracle: the traction of
+systems_of_equations_ex6.C:240-257 on the max-x face, on affine and perturbed meshes, and a Neumann flux on a Poisson
+system where corner elements carry two loaded sides."""
+import numpy as np
+import pytest
+
+from conftest import PARITY_TOL, csr_parity_error, dense_parity_error, vec_parity_error
+from test_gpu_parity import _mods, make_case, make_ctx
+
+pytestmark = pytest.mark.gpu
+
+EX6 = [
+    ("hex27_ex6", 27, (4, 3, 2), None, (0.0, 0.0, -1.0)),
+    ("hex27_ex6_perturbed", 27, (3, 2, 2), (1, 0.004, 7), (0.3, -0.2, -1.0)),
+    ("hex8_ex6", 8, (5, 3, 2), None, (0.0, 0.0, -1.0)),
+    ("hex8_ex6_perturbed", 8, (4, 3, 3), (1, 0.004, 11), (0.3, -0.2, -1.0)),
+]
+
+
+@pytest.mark.parametrize("name,etype,dims,skew,g", EX6, ids=[c[0] for c in EX6])
+def test_ex6_with_the_traction_term(name, etype, dims, skew, g):
+    F, O = _mods()
+    m, s = make_case(etype, dims, bounds=(0, 1, 0, 0.3, 0, 0.1), n_vars=3, skew=skew, dirichlet=(4,), kind=1)
+    e, sd = m.boundary_sides(2)  # BOUNDARY_ID_MAX_X
+    s.set_side_loads(e, sd, g)
+    ctx = make_ctx(m, s)
+    ctx.set_side_loads(e, sd, g)
+    p = F.make_params(F.ELASTICITY, 0, F.FORCING_NONE, F.CONSTRAIN_HOMOGENEOUS)
+    vo, ro, _ = s.assemble(O.ELASTICITY_EX6)
+    ctx.assemble(p)
+    v, r = ctx.get_values()
+    rp, _ = s.sparsity()
+    assert csr_parity_error(v, vo, rp) < PARITY_TOL
+    assert vec_parity_error(r, ro) < PARITY_TOL
+    Ko, Fo = s.element_matrices(O.ELASTICITY_EX6, constrained=False)
+    K, Fv = ctx.element_matrices(p, constrained=False)
+    assert dense_parity_error(K, Ko) < PARITY_TOL
+    assert vec_parity_error(Fv.reshape(-1), Fo.reshape(-1)) < PARITY_TOL
+    # a sub-range that starts inside the loaded elements (records are offset by e0)
+    e0 = int(e[len(e) // 2])
+    _, F2 = ctx.element_matrices(p, e0=e0, e1=m.n_elem, constrained=True)
+    _, Fo2 = s.element_matrices(O.ELASTICITY_EX6, e0=e0, e1=m.n_elem, constrained=True)
+    assert vec_parity_error(F2.reshape(-1), Fo2.reshape(-1)) < PARITY_TOL
+    # the load really is there, and clearing the list takes it away again
+    s.set_side_loads([], [], g)
+    _, r0, _ = s.assemble(O.ELASTICITY_EX6)
+    assert np.abs(ro - r0).max() > 1e-4
+    ctx.set_side_loads([], [], g)
+    ctx.assemble(p)
+    _, r = ctx.get_values()
+    assert vec_parity_error(r, r0) < PARITY_TOL
+    ctx.close()
+
+
+@pytest.mark.parametrize("etype,dims,skew", [(27, (3, 3, 2), None), (27, (3, 2, 2), (1, 0.03, 5)), (8, (4, 4, 3), (1, 0.05, 9))])
+def test_neumann_flux_with_two_loaded_sides_per_corner_element(etype, dims, skew):
+    F, O = _mods()
+    m, s = make_case(etype, dims, skew=skew, dirichlet=(4,))
+    e2, s2 = m.boundary_sides(2)
+    e3, s3 = m.boundary_sides(3)
+    e, sd = np.concatenate([e3, e2]), np.concatenate([s3, s2])  # unsorted on purpose
+    assert len(np.intersect1d(e2, e3)) > 0
+    s.set_side_loads(e, sd, [1.7])
+    ctx = make_ctx(m, s)
+    ctx.set_side_loads(e, sd, [1.7])
+    qorder = 3 if etype == 8 else 5
+    f_tab, _ = s.forcing_at_qps(qorder)
+    vo, ro, _ = s.assemble(O.POISSON_EX4, qorder=qorder, forcing=O.FORCING_TABULATED, f_tab=f_tab)
+    ctx.assemble(F.make_params(F.POISSON, qorder, F.FORCING_TABULATED, f_host=f_tab))
+    v, r = ctx.get_values()
+    rp, _ = s.sparsity()
+    assert csr_parity_error(v, vo, rp) < PARITY_TOL
+    assert vec_parity_error(r, ro) < PARITY_TOL
+    ctx.close()
+
+
+def test_side_loads_reject_bad_input():
+    F, O = _mods()
+    m, s = make_case(10, (2, 2, 1))
+    ctx = make_ctx(m, s)
+    with pytest.raises(F.FeasmError):
+        ctx.set_side_loads([0], [0], [1.0])  # TET10 sides are not built
+    ctx.close()
+    m, s = make_case(8, (2, 2, 2))
+    ctx = make_ctx(m, s)
+    with pytest.raises(F.FeasmError):
+        ctx.set_side_loads([0], [6], [1.0])
+    with pytest.raises(F.FeasmError):
+        ctx.set_side_loads([m.n_elem], [0], [1.0])
+    ctx.close()
