@@ -26,7 +26,7 @@ std::unordered_map<const void*, Uploaded>& cache() {
 }
 }  // namespace
 
-void assemble(EquationSystems& es, const std::string& system_name, const feasm_params& params) {
+void assemble(EquationSystems& es, const std::string& system_name, const feasm_params& params, const SideLoad* side_load) {
   LinearImplicitSystem& system = es.get_system<LinearImplicitSystem>(system_name);
   auto* A = dynamic_cast<GpuSparseMatrix<Number>*>(system.matrix);
   if (!A) libmesh_error_msg("feasm_libmesh::assemble: system.matrix is not a GpuSparseMatrix; add it with "
@@ -77,6 +77,27 @@ void assemble(EquationSystems& es, const std::string& system_name, const feasm_p
     up.mesh = &mesh; up.n_elem = n_elem;
   }
 
+  // ---- loaded sides: the `if (elem->neighbor_ptr(side) == nullptr) ... has_boundary_id(elem, side, id)` test of
+  // systems_of_equations_ex6.C:243-251, evaluated once per call into an (element, side) list
+  {
+    std::vector<uint32_t> side_elems;
+    std::vector<uint8_t> side_ids;
+    if (side_load) {
+      const BoundaryInfo& bi = mesh.get_boundary_info();
+      uint32_t le = 0;  // index in active_local order = the element index handed to feasm_set_mesh
+      for (const Elem* elem : mesh.active_local_element_ptr_range()) {
+        for (auto side : elem->side_index_range())
+          if (elem->neighbor_ptr(side) == nullptr && bi.has_boundary_id(elem, side, side_load->id)) {
+            side_elems.push_back(le);
+            side_ids.push_back((uint8_t)side);
+          }
+        ++le;
+      }
+    }
+    A->check(feasm_set_side_loads(ctx, (int64_t)side_elems.size(), side_elems.data(), side_ids.data(),
+                                  side_load ? side_load->g.data() : nullptr, side_load ? (int)side_load->g.size() : 0));
+  }
+
   // ---- Dirichlet constraints: DofMap::is_constrained_dof + primal constraint values (empty constraint rows) ----
   std::vector<uint32_t> con_rows;
   std::vector<double> con_vals;
@@ -118,7 +139,8 @@ void assemble_laplace(EquationSystems& es, const std::string& name) {
 void assemble_elasticity_ex6(EquationSystems& es, const std::string& name) {
   feasm_params p{};
   p.problem = FEASM_ELASTICITY; p.constrain = FEASM_CONSTRAIN_HOMOGENEOUS;
-  assemble(es, name, p);
+  const SideLoad traction{2 /* BOUNDARY_ID_MAX_X */, {0., 0., -1.}};
+  assemble(es, name, p, &traction);
 }
 }  // namespace feasm_libmesh
 

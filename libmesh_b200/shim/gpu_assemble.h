@@ -12,6 +12,7 @@
 #ifndef FEASM_SHIM_MOCK
 #include "libmesh/equation_systems.h"
 #include "libmesh/linear_implicit_system.h"
+#include "libmesh/boundary_info.h"
 #endif
 
 namespace feasm_libmesh {
@@ -19,9 +20,17 @@ namespace feasm_libmesh {
 void assemble_poisson_ex4(libMesh::EquationSystems& es, const std::string& system_name);
 // the same loop with f = 0 (config 4)
 void assemble_laplace(libMesh::EquationSystems& es, const std::string& system_name);
-// examples/systems_of_equations/systems_of_equations_ex6/systems_of_equations_ex6.C:156-264, volume terms
+// A boundary integral  Fe_var[i](a) += JxW_face[qp] * (g[i] * phi_face[a][qp])  over the sides that have no neighbour
+// and carry boundary id `id` (the traction loop of systems_of_equations_ex6.C:240-257); g has one entry per variable.
+struct SideLoad {
+  libMesh::boundary_id_type id;
+  std::vector<libMesh::Real> g;
+};
+// examples/systems_of_equations/systems_of_equations_ex6/systems_of_equations_ex6.C:156-264: volume terms and the
+// traction (0, 0, -1) on BOUNDARY_ID_MAX_X (= 2, :79)
 void assemble_elasticity_ex6(libMesh::EquationSystems& es, const std::string& system_name);
-// generic entry: feasm_params as in include/feasm.h
-void assemble(libMesh::EquationSystems& es, const std::string& system_name, const feasm_params& params);
+// generic entry: feasm_params as in include/feasm.h; side_load may be null
+void assemble(libMesh::EquationSystems& es, const std::string& system_name, const feasm_params& params,
+              const SideLoad* side_load = nullptr);
 }  // namespace feasm_libmesh
 #endif

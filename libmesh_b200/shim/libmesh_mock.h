@@ -11,6 +11,8 @@
 #include <cstdint>
 #include <iostream>
 #include <map>
+#include <set>
+#include <tuple>
 #include <memory>
 #include <sstream>
 #include <stdexcept>
@@ -48,15 +50,31 @@ struct Point { Real c[3]; Real operator()(unsigned i) const { return c[i]; } }; 
 struct Node : Point { dof_id_type _id; dof_id_type id() const { return _id; } };  // include/geom/node.h
 struct Elem {                                                                      // include/geom/elem.h
   ElemType _type; std::vector<const Node*> _nodes; dof_id_type _id; processor_id_type _pid;
+  std::vector<const Elem*> _neighbors;                                             // one per side; nullptr = boundary
   ElemType type() const { return _type; }
+  unsigned int n_sides() const { return (unsigned)_neighbors.size(); }
+  std::vector<unsigned short> side_index_range() const {                           // elem.h:2710 (an IntRange there)
+    std::vector<unsigned short> r(_neighbors.size());
+    for (std::size_t i = 0; i < r.size(); ++i) r[i] = (unsigned short)i;
+    return r;
+  }
+  const Elem* neighbor_ptr(unsigned int side) const { return _neighbors[side]; }   // elem.h:2598
   unsigned int n_nodes() const { return (unsigned)_nodes.size(); }
   const Node* node_ptr(unsigned i) const { return _nodes[i]; }
   dof_id_type node_id(unsigned i) const { return _nodes[i]->id(); }
   dof_id_type id() const { return _id; }
   processor_id_type processor_id() const { return _pid; }
 };
+struct BoundaryInfo {                                                              // include/mesh/boundary_info.h
+  std::set<std::tuple<const Elem*, unsigned short, boundary_id_type>> _sides;
+  bool has_boundary_id(const Elem* e, unsigned short side, boundary_id_type id) const {  // boundary_info.h:521
+    return _sides.count(std::make_tuple(e, side, id)) != 0;
+  }
+};
 struct MeshBase {                                                                  // include/mesh/mesh_base.h
   std::vector<const Elem*> _local;
+  BoundaryInfo _bi;
+  const BoundaryInfo& get_boundary_info() const { return _bi; }                    // mesh_base.h:165
   const std::vector<const Elem*>& active_local_element_ptr_range() const { return _local; }  // mesh_base.h:1484
   dof_id_type n_nodes() const { return 0; }
   dof_id_type max_node_id() const { return 0; }

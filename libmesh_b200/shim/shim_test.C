@@ -33,6 +33,8 @@ int main() {
   for (int64_t i = 0; i < n_nodes; ++i) { nodes[i]._id = (dof_id_type)i; for (int d = 0; d < 3; ++d) nodes[i].c[d] = xyz[3 * i + d]; }
   std::vector<Elem> elems(n_elem);
   MeshBase mesh;
+  std::vector<uint32_t> load_elems;  // elements whose side 2 (x-max) lies on the box face: boundary id 2
+  std::vector<uint8_t> load_sides;
   DofMap dof_map;
   dof_map._n_dofs = (dof_id_type)n_dofs; dof_map._nd = 27;
   for (int64_t e = 0; e < n_elem; ++e) {
@@ -42,6 +44,14 @@ int main() {
       dof_map._elem_dofs.push_back(base[conn[27 * e + a]]);
     }
     mesh._local.push_back(&elems[e]);
+    // neighbours in build_cube's k-j-i element order; sides 0..5 = z-min, y-min, x-max, y-max, x-min, z-max
+    const int i = (int)(e % nx), j = (int)((e / nx) % ny), k = (int)(e / (nx * ny));
+    elems[e]._neighbors = {k > 0 ? &elems[e - nx * ny] : nullptr, j > 0 ? &elems[e - nx] : nullptr, i < nx - 1 ? &elems[e + 1] : nullptr,
+                           j < ny - 1 ? &elems[e + nx] : nullptr, i > 0 ? &elems[e - 1] : nullptr, k < nz - 1 ? &elems[e + nx * ny] : nullptr};
+    if (i == nx - 1) {
+      mesh._bi._sides.insert(std::make_tuple((const Elem*)&elems[e], (unsigned short)2, (boundary_id_type)2));
+      load_elems.push_back((uint32_t)e); load_sides.push_back(2);
+    }
   }
   // Dirichlet dofs on the whole boundary with the exact solution of ex4 (DirichletBoundary, introduction_ex4.C:217-243)
   const double hp = 1.5707963267948966;
@@ -239,6 +249,24 @@ int main() {
     double diff = 0.;
     for (int64_t i = 0; i < n_dofs; ++i) diff = std::max(diff, std::fabs(hx[i] - u[i]));
     REQUIRE(its > 0 && its < 2000 && diff < 1e-9);
+  }
+
+  // ---- a side load through the adaptor (BoundaryInfo + neighbor_ptr -> feasm_set_side_loads) vs the C ABI directly ----
+  {
+    const feasm_libmesh::SideLoad flux{2, {1.7}};
+    A.zero();
+    feasm_libmesh::assemble(es, "Poisson", p, &flux);
+    A.close();
+    const double g1 = 1.7;
+    CK(feasm_set_side_loads(ctx, (int64_t)load_elems.size(), load_elems.data(), load_sides.data(), &g1, 1));
+    CK(feasm_assemble(ctx, &p));
+    std::vector<double> b2(n_dofs);
+    CK(feasm_get_values(ctx, nullptr, b2.data()));
+    double moved = 0.;
+    for (int64_t r = 0; r < n_dofs; ++r) { REQUIRE(rhs._v[r] == b2[r]); moved = std::max(moved, std::fabs(b2[r] - b[r])); }
+    REQUIRE(moved > 1e-3);                                          // the flux is in the RHS ...
+    feasm_libmesh::assemble(es, "Poisson", p);                      // ... and a call without a load clears the list
+    for (int64_t r = 0; r < n_dofs; ++r) REQUIRE(rhs._v[r] == b[r]);
   }
 
   auto Z = A.zero_clone();
