@@ -143,6 +143,28 @@ def run_ours(args):
     t2 = time.time()
     params = F.make_params(F.POISSON, args.qorder, F.FORCING_EX4_FD)
     stream = torch.cuda.ExternalStream(ctx.stream())
+    # The same inputs generated on the device (feasm_generate_cube / _distribute_dofs_device / _generate_dirichlet,
+    # SURVEY 8f rank 2): timed (second run: the first loads the kernels) and compared with the host generators' arrays
+    # at full size.  Setup only; the timed steps below run on `ctx`.
+    ingest = None
+    if etype != F.TET10:
+        ing = F.Context(local)
+        for _ in range(2):
+            ti = time.time()
+            ing.generate_cube(etype, args.n, args.n, args.n, (-1.0, 1.0, -1.0, 1.0, -1.0, 1.0))
+            ing.distribute_dofs(1)
+            n_con_dev = ing.generate_dirichlet(0x3f, F.DIRICHLET_EX4_EXACT)
+            ing_s = time.time() - ti
+        xyz_d, conn_d, _ = ing.get_mesh(mask=False)
+        ed_d, _ = ing.get_dofs(node_base=False)
+        flag_d, val_d = ing.get_constraints()
+        ingest = {"seconds": round(ing_s, 4),
+                  "mesh_and_dofs_bit_identical_to_host_route": bool(np.array_equal(xyz_d, P["xyz"]) and np.array_equal(conn_d, P["conn"])
+                                                                    and np.array_equal(ed_d, P["elem_dofs"])),
+                  "dirichlet_rows_identical": bool(n_con_dev == len(P["con_rows"]) and np.array_equal(np.nonzero(flag_d)[0], np.sort(P["con_rows"]))),
+                  "dirichlet_max_abs_diff": float(np.max(np.abs(val_d[P["con_rows"]] - P["con_vals"])))}
+        del xyz_d, conn_d, ed_d, flag_d, val_d
+        ing.close()
     fp64 = ctx.measure_fp64_peaks()
 
     # ---- value: inputs resident in HBM -------------------------------------------------------------------
@@ -240,7 +262,7 @@ def run_ours(args):
         "config": {"workload": f"introduction_ex4 3D Poisson, build_cube {args.n}^3 {args.elem.upper()} on [-1,1]^3, QGauss nq={nq}, "
                                "Dirichlet on ids 0-5, FD forcing evaluated in-kernel", "n_elem": n_elem, "n_dofs": P["n_dofs"],
                    "nnz": nnz, "l2": "inputs and outputs larger than L2 (CSR values %.2f GB)" % (nnz * 8 / 1e9),
-                   "setup_s": {"host_mesh_dofs": round(P["host_gen_s"], 3), "upload": round(t1 - t0, 3), "pattern_and_maps": round(t2 - t1, 3)}},
+                   "setup_s": {"host_mesh_dofs": round(P["host_gen_s"], 3), "upload": round(t1 - t0, 3), "pattern_and_maps": round(t2 - t1, 3), "device_ingest": ingest}},
         "clocks": clk, "gpu_launches": int(launches),  # kernels of libfeasm.so launched inside the timed K steps
         "e2e": {"value": n_elem / e2e_s, "unit": "elements/s", "h2d_bytes_per_step": int(h2d), "d2h_bytes_per_step": int(d2h),
                 "ms_per_step": e2e_s * 1e3, "checksum_values": checksum},

@@ -213,6 +213,26 @@ int feasm_build_cube(int elem_type, int nx, int ny, int nz, const double bounds[
 int64_t feasm_distribute_dofs(int npe, int64_t n_elem, int64_t n_nodes, const uint32_t* conn, int n_vars, int n_parts,
                               const int32_t* elem_pid, uint32_t* node_dof_base, uint32_t* first_dof, int32_t* node_pid);
 
+/* ---- device-side mesh ingest (the step before the path, without the host) --------------- */
+/* MeshTools::Generation::build_cube (src/mesh/mesh_generation.C:1285-1340 nodes, :1399-1432 elements, :1779-1785
+ * rescale, :1416-1432 boundary ids) for HEX8 / HEX27, generated in the context's device arrays; replaces
+ * feasm_build_cube + feasm_set_mesh.  Same node ids, element order and coordinates bit for bit. */
+int feasm_generate_cube(feasm_ctx* ctx, int elem_type, int nx, int ny, int nz, const double bounds[6]);
+/* DofMap::distribute_dofs (src/base/dof_map.C:1445-1507, one rank, one variable group of n_vars LAGRANGE variables)
+ * + DofMap::dof_indices (:2280-2308) for every element, on the device, for whatever mesh the context holds
+ * (generated or feasm_set_mesh); replaces feasm_distribute_dofs + feasm_set_dofs.  Returns n_dofs (< 0: error code). */
+int64_t feasm_distribute_dofs_device(feasm_ctx* ctx, int n_vars);
+/* DirichletBoundary on the boundary ids in id_mask (bit b = id b) for the variables in var_mask, nodal interpolation
+ * of the boundary function (DofMap::create_dof_constraints, src/base/dof_map_constraints.C:1736);
+ * replaces feasm_set_constraints for generated meshes.  Returns the number of constrained dofs (< 0: error code). */
+#define FEASM_DIRICHLET_ZERO 0      /* g = 0 (ex6 clamped sides) */
+#define FEASM_DIRICHLET_EX4_EXACT 1 /* g = cos(pi x/2) sin(pi y/2) cos(pi z/2), introduction_ex3/exact_solution.C:40-47 */
+int64_t feasm_generate_dirichlet(feasm_ctx* ctx, unsigned id_mask, int kind, unsigned var_mask);
+/* Read-backs (D2H; any pointer may be NULL): what the context holds, however it got there. */
+int feasm_get_mesh(feasm_ctx* ctx, double* xyz, uint32_t* conn, uint8_t* node_boundary_mask);
+int feasm_get_dofs(feasm_ctx* ctx, uint32_t* elem_dofs, uint32_t* node_dof_base);
+int feasm_get_constraints(feasm_ctx* ctx, uint8_t* flag, double* value);
+
 /* ---- instrumentation ---------------------------------------------------------------------------- */
 /* Milliseconds of the kernels of the last feasm_assemble, measured with CUDA events on the context's stream:
  * [0] element kernel, [1] scatter/row reduction, [2] whole call, [3] element-level constraint pass.  Also the

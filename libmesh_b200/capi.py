@@ -18,6 +18,7 @@ HEX8, HEX27, TET10 = 8, 27, 10
 POISSON, ELASTICITY = 1, 2
 FORCING_NONE, FORCING_EX4_FD, FORCING_TABULATED = 0, 1, 2
 CONSTRAIN_HETEROGENEOUS, CONSTRAIN_HOMOGENEOUS = 0, 1
+DIRICHLET_ZERO, DIRICHLET_EX4_EXACT = 0, 1
 
 # every symbol include/feasm.h declares (tests check the library exports each of them)
 SYMBOLS = [
@@ -30,6 +31,8 @@ SYMBOLS = [
     "feasm_distribute_dofs", "feasm_last_timing", "feasm_measure_fp64_peaks", "feasm_vector_mult", "feasm_vector_mult_host", "feasm_cg_solve",
     "feasm_vec_alloc", "feasm_vec_free", "feasm_vec_copy", "feasm_vec_fill", "feasm_vec_axpy", "feasm_vec_pointwise",
     "feasm_vec_reduce", "feasm_vec_set_entry",
+    "feasm_generate_cube", "feasm_distribute_dofs_device", "feasm_generate_dirichlet", "feasm_get_mesh", "feasm_get_dofs",
+    "feasm_get_constraints",
 ]
 
 
@@ -107,6 +110,12 @@ def lib():
         "feasm_vec_pointwise": (i32, [vp, i32, vp, vp, vp, C.c_double, i64]),
         "feasm_vec_reduce": (i32, [vp, i32, vp, vp, i64, C.POINTER(C.c_double)]),
         "feasm_vec_set_entry": (i32, [vp, vp, i64, C.c_double, i32]),
+        "feasm_generate_cube": (i32, [vp, i32, i32, i32, i32, vp]),
+        "feasm_distribute_dofs_device": (i64, [vp, i32]),
+        "feasm_generate_dirichlet": (i64, [vp, C.c_uint, i32, C.c_uint]),
+        "feasm_get_mesh": (i32, [vp, vp, vp, vp]),
+        "feasm_get_dofs": (i32, [vp, vp, vp]),
+        "feasm_get_constraints": (i32, [vp, vp, vp]),
     }
     for name, (res, args) in sig.items():
         fn = getattr(L, name)
@@ -203,6 +212,7 @@ class Context:
         xyz, conn = _c(xyz, np.float64), _c(conn, np.uint32)
         self.elem_type, self.n_elem, self.n_nodes = elem_type, conn.shape[0], xyz.shape[0]
         self._ck(self.L.feasm_set_mesh(self.h, elem_type, conn.shape[0], xyz.shape[0], _p(xyz), _p(conn)))
+        self.n_nodes = xyz.shape[0]
 
     def update_coordinates(self, xyz):
         self._ck(self.L.feasm_update_coordinates(self.h, _p(xyz)))
@@ -212,6 +222,46 @@ class Context:
         gid = _c(global_ids, np.uint32)
         self.n_rows, self.nd = int(n_rows), ed.shape[1]
         self._ck(self.L.feasm_set_dofs(self.h, n_vars, n_rows, n_rows if n_owned is None else n_owned, _p(ed), _p(gid)))
+
+    # ---- device-side ingest (no host arrays): build_cube, distribute_dofs + dof_indices, DirichletBoundary ----
+    def generate_cube(self, elem_type, nx, ny, nz, bounds=(0.0, 1.0, 0.0, 1.0, 0.0, 1.0)):
+        b = np.asarray(bounds, dtype=np.float64)
+        self._ck(self.L.feasm_generate_cube(self.h, elem_type, nx, ny, nz, _p(b)))
+        ne, nn = C.c_int64(), C.c_int64()
+        self.L.feasm_cube_sizes(elem_type, nx, ny, nz, C.byref(ne), C.byref(nn))
+        self.elem_type, self.n_elem, self.n_nodes = elem_type, ne.value, nn.value
+
+    def distribute_dofs(self, n_vars=1):
+        n = int(self.L.feasm_distribute_dofs_device(self.h, n_vars))
+        if n < 0:
+            self._ck(n)
+        self.n_rows, self.nd, self.n_vars = n, self.elem_type * n_vars, n_vars
+        return n
+
+    def generate_dirichlet(self, id_mask=0x3f, kind=1, var_mask=0xff):
+        n = int(self.L.feasm_generate_dirichlet(self.h, id_mask, kind, var_mask))
+        if n < 0:
+            self._ck(n)
+        return n
+
+    def get_mesh(self, mask=True):
+        xyz = np.empty((self.n_nodes, 3))
+        conn = np.empty((self.n_elem, self.elem_type), dtype=np.uint32)
+        m = np.empty(self.n_nodes, dtype=np.uint8) if mask else None
+        self._ck(self.L.feasm_get_mesh(self.h, _p(xyz), _p(conn), _p(m)))
+        return xyz, conn, m
+
+    def get_dofs(self, node_base=True):
+        ed = np.empty((self.n_elem, self.nd), dtype=np.uint32)
+        nb = np.empty(self.n_nodes, dtype=np.uint32) if node_base else None
+        self._ck(self.L.feasm_get_dofs(self.h, _p(ed), _p(nb)))
+        return ed, nb
+
+    def get_constraints(self):
+        f = np.empty(self.n_rows, dtype=np.uint8)
+        v = np.empty(self.n_rows)
+        self._ck(self.L.feasm_get_constraints(self.h, _p(f), _p(v)))
+        return f, v
 
     def set_constraints(self, rows, values):
         r, v = _c(rows, np.uint32), _c(values, np.float64)

@@ -137,6 +137,7 @@ void feasm_destroy(feasm_ctx* ctx) {
   cudaStreamSynchronize(ctx->stream);
   drop_maps(ctx);
   release(ctx->d_xyz); release(ctx->d_conn); release(ctx->d_elem_dofs); release(ctx->d_gid);
+  release(ctx->d_node_mask); release(ctx->d_node_base);
   release(ctx->d_con_flag); release(ctx->d_con_val); release(ctx->d_row_ptr); release(ctx->d_col_idx);
   release(ctx->d_values); release(ctx->d_rhs); release(ctx->d_flags); release(ctx->d_tab); release(ctx->d_f);
   release(ctx->d_side_elems); release(ctx->d_side_mask); release(ctx->d_side_tab); release(ctx->d_side_nodes);
@@ -151,15 +152,7 @@ int feasm_set_mesh(feasm_ctx* ctx, int elem_type, int64_t n_elem, int64_t n_node
   if (elem_type != FEASM_HEX8 && elem_type != FEASM_HEX27 && elem_type != FEASM_TET10) return feasm_fail(ctx, FEASM_ERR_ARG, "unsupported element type");
   if (n_elem < 0 || n_nodes <= 0 || !xyz || !conn) return feasm_fail(ctx, FEASM_ERR_ARG, "bad mesh arguments");
   FEASM_CUDA(ctx, cudaSetDevice(ctx->device));
-  drop_maps(ctx);
-  ctx->elem_type = elem_type;
-  ctx->npe = elem_type;
-  ctx->n_elem = n_elem;
-  ctx->n_nodes = n_nodes;
-  ctx->tab_qorder = -1;
-  ctx->side_qorder = -1;
-  release(ctx->d_side_elems); release(ctx->d_side_mask);  // element ids of the previous mesh
-  ctx->n_side_elems = 0;
+  feasm_reset_mesh(ctx, elem_type, n_elem, n_nodes);
   int rc = upload(ctx, &ctx->d_xyz, xyz, (size_t)n_nodes * 3);
   if (rc) return rc;
   rc = upload(ctx, &ctx->d_conn, conn, (size_t)n_elem * ctx->npe);
@@ -178,18 +171,40 @@ int feasm_set_dofs(feasm_ctx* ctx, int n_vars, int64_t n_rows, int64_t n_owned, 
   if (!ctx || !ctx->d_conn) return feasm_fail(ctx, FEASM_ERR_STATE, "set_mesh first");
   if (n_vars < 1 || n_rows <= 0 || n_owned < 0 || n_owned > n_rows || !elem_dofs) return feasm_fail(ctx, FEASM_ERR_ARG, "bad dof arguments");
   if (n_rows >= 0xffffffffll) return feasm_fail(ctx, FEASM_ERR_ARG, "dof ids are 32-bit (dof_id_type)");
-  drop_maps(ctx);
-  ctx->n_vars = n_vars;
-  ctx->nd = ctx->npe * n_vars;
-  ctx->n_rows = n_rows;
-  ctx->n_owned = n_owned;
-  const size_t n = (size_t)ctx->n_elem * ctx->nd;
+  const size_t n = (size_t)ctx->n_elem * ctx->npe * n_vars;
   for (size_t i = 0; i < n; ++i)
     if (elem_dofs[i] >= (uint64_t)n_rows) return feasm_fail(ctx, FEASM_ERR_ARG, "elem_dofs entry out of range");
   int rc = upload(ctx, &ctx->d_elem_dofs, elem_dofs, n);
   if (rc) return rc;
   release(ctx->d_gid);
   if (global_ids) { rc = upload(ctx, &ctx->d_gid, global_ids, (size_t)n_rows); if (rc) return rc; }
+  release(ctx->d_node_base);  // numbering supplied by the caller: no node -> dof table
+  return feasm_reset_dofs(ctx, n_vars, n_rows, n_owned);
+}
+
+}  // extern "C"
+
+// The bookkeeping of feasm_set_mesh / feasm_set_dofs without the uploads (shared with the device-side ingest,
+// feasm_ingest.cu).
+void feasm_reset_mesh(feasm_ctx* ctx, int elem_type, int64_t n_elem, int64_t n_nodes) {
+  drop_maps(ctx);
+  ctx->elem_type = elem_type;
+  ctx->npe = elem_type;
+  ctx->n_elem = n_elem;
+  ctx->n_nodes = n_nodes;
+  ctx->tab_qorder = -1;
+  ctx->side_qorder = -1;
+  release(ctx->d_side_elems); release(ctx->d_side_mask);  // element ids of the previous mesh
+  ctx->n_side_elems = 0;
+  release(ctx->d_node_mask); release(ctx->d_node_base);
+}
+
+int feasm_reset_dofs(feasm_ctx* ctx, int n_vars, int64_t n_rows, int64_t n_owned) {
+  drop_maps(ctx);
+  ctx->n_vars = n_vars;
+  ctx->nd = ctx->npe * n_vars;
+  ctx->n_rows = n_rows;
+  ctx->n_owned = n_owned;
   release(ctx->d_con_flag); release(ctx->d_con_val);
   FEASM_CUDA(ctx, cudaMalloc(&ctx->d_con_flag, n_rows));
   FEASM_CUDA(ctx, cudaMalloc(&ctx->d_con_val, sizeof(double) * n_rows));
@@ -203,6 +218,8 @@ int feasm_set_dofs(feasm_ctx* ctx, int n_vars, int64_t n_rows, int64_t n_owned, 
   ctx->h_con_flag.assign((size_t)n_rows, 0);
   return FEASM_OK;
 }
+
+extern "C" {
 
 int feasm_set_constraints(feasm_ctx* ctx, int64_t n, const uint32_t* rows, const double* values) {
   if (!ctx || !ctx->d_con_flag) return feasm_fail(ctx, FEASM_ERR_STATE, "set_dofs first");

@@ -61,6 +61,8 @@ struct feasm_ctx {
   int64_t n_elem = 0, n_nodes = 0;
   double* d_xyz = nullptr;
   uint32_t* d_conn = nullptr;
+  uint8_t* d_node_mask = nullptr;   // [n_nodes] bit b = node lies on boundary id b (feasm_generate_cube only)
+  uint32_t* d_node_base = nullptr;  // [n_nodes] first dof of the node (feasm_distribute_dofs_device only)
 
   // dofs
   int n_vars = 0, nd = 0;
@@ -142,6 +144,9 @@ int feasm_fail(feasm_ctx* ctx, int code, const std::string& msg);
       return feasm_fail(ctx, FEASM_ERR_CUDA, std::string(#call) + ": " + cudaGetErrorString(e__));    \
   } while (0)
 
+// feasm_api.cu: bookkeeping shared by the host-array and the device-side ingest
+void feasm_reset_mesh(feasm_ctx* ctx, int elem_type, int64_t n_elem, int64_t n_nodes);
+int feasm_reset_dofs(feasm_ctx* ctx, int n_vars, int64_t n_rows, int64_t n_owned);
 // feasm_pattern.cu
 int feasm_build_incidence(feasm_ctx* ctx);
 int feasm_device_build_pattern(feasm_ctx* ctx);
