@@ -12,7 +12,7 @@ import os
 import numpy as np
 
 _HERE = os.path.dirname(os.path.abspath(__file__))
-LIB_PATH = os.path.join(_HERE, "libfeasm.so")
+LIB_PATH = os.environ.get("FEASM_LIB") or os.path.join(_HERE, "libfeasm.so")  # FEASM_LIB: development builds
 
 HEX8, HEX27, TET10 = 8, 27, 10
 POISSON, ELASTICITY = 1, 2

@@ -222,8 +222,17 @@ __device__ __forceinline__ void elem_process(const double* X, double* fw, const 
   const double* s_phi = s_tab;
   const int g = lane >> 2, t4 = lane & 3;
   // ---- A: reference -> physical map at quadrature point q = lane ---------------------------------------
+  // FEASM_ABLATE (never defined in product builds; scripts/gpu_ablate.py): 2 = no contraction, 3 = no Fe /
+  // stores, 4 = no geometry / forcing — timing probes of the phases of this function.
   double S[9], JxW, x, y, z;
+#if defined(FEASM_ABLATE) && FEASM_ABLATE == 4
+  const bool affine = true;
+  for (int k = 0; k < 9; ++k) S[k] = X[k] + k;
+  JxW = 1.; x = y = z = 0.;
+  if (false)
+#else
   const bool affine = geom_phase<NPE, NQ>(X, s_tab, lane, forcing == FEASM_FORCING_EX4_FD, flags, S, JxW, x, y, z);
+#endif
   {
     double f = 0.;
     if (forcing == FEASM_FORCING_EX4_FD) {
@@ -245,6 +254,9 @@ __device__ __forceinline__ void elem_process(const double* X, double* fw, const 
   for (int ib = 0; ib < C::NB; ++ib)
 #pragma unroll
     for (int r = 0; r < (C::REM > 0 ? C::REM : 1); ++r) pr[ib][r] = 0.;
+#if defined(FEASM_ABLATE) && FEASM_ABLATE == 2
+  if (forcing == 99)
+#endif
 #pragma unroll
   for (int qg = 0; qg < C::QG; ++qg) {
     double Sq[9];
@@ -294,6 +306,9 @@ __device__ __forceinline__ void elem_process(const double* X, double* fw, const 
   }
 
   // ---- D: Fe (introduction_ex4.C:536-537) and the stores ----------------------------------------------------
+#if defined(FEASM_ABLATE) && FEASM_ABLATE == 3
+  if (forcing != 99) return;
+#endif
   if (lane < NPE) {
     double Fe = 0.;
     if (forcing != FEASM_FORCING_NONE) {
