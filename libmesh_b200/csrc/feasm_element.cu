@@ -83,6 +83,153 @@ int launch_poisson(feasm_ctx* ctx, const feasm_params& p, const double* d_f, int
 }
 
 
+// ---- HEX8 with the 2x2x2 rule: four elements per warp ---------------------------------------------------------------
+// With "lane = quadrature point" an element of 8 points uses a quarter of the warp in phase A, and phase A (map + the
+// nine sin/cos of the FD forcing per point) is where a HEX8 element spends its time: k_elem_poisson<8,8> ran 128^3 HEX8
+// at the per-element cost of HEX27's phase A.  Here lane = (element slot s = lane>>3, quadrature point / node q = lane&7):
+// one pass of phase A serves four consecutive elements at full lane use; the 8x8 contractions (6 DMMA k steps each)
+// follow one element after the other, each taking the S of its points from the slot's lanes by shuffle; Fe and the
+// stores are again slot-parallel.  Same reference semantics as elem_process (affine test, compute_affine_map's
+// "Jacobian of point 0", JxW[p] = JxW[0]/qw[0]*qw[p]); sums run in node order.
+template <int WARPS, int RS>
+__global__ void __launch_bounds__(WARPS * 32, 1)
+k_elem_poisson_hex8x4(const double* __restrict__ xyz, const uint32_t* __restrict__ conn, const double* __restrict__ tab, int forcing,
+                      const double* __restrict__ f_tab, int64_t e0, int64_t e1, double* __restrict__ kf, int rs_rt, int* flags) {
+  constexpr int NPE = 8, NQ = 8;
+  using C = ElemCfg<NPE, NQ>;
+  constexpr unsigned FULL = 0xffffffffu;
+  const int rs = RS ? RS : rs_rt;
+  extern __shared__ double smem[];
+  double* s_tab = smem;
+  double* s_tw = smem + C::TAB_SZ;
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  elem_load_tables<NPE, NQ>(s_tab, s_tw, tab, threadIdx.x, WARPS * 32);
+  double* Xw = s_tw + C::TW_SZ + (size_t)warp * (4 * 24 + 32);  // [slot][node][3] | fw[slot][q]
+  double* fw = Xw + 4 * 24;
+  const int slot = lane >> 3, q = lane & 7, g = lane >> 2, t4 = lane & 3;
+  const double* X = Xw + slot * 24;
+  const double* twp = s_tw + g * C::TS + t4;
+  const double* s_phi = s_tab;
+  const double* s_dxi = s_tab + NPE * NQ;
+  const double* s_deta = s_dxi + NPE * NQ;
+  const double* s_dzeta = s_deta + NPE * NQ;
+  const double* s_qw = s_tab + 4 * NPE * NQ;
+  __syncthreads();
+
+  const int64_t stride = (int64_t)gridDim.x * WARPS * 4;
+  int64_t eb = e0 + ((int64_t)blockIdx.x * WARPS + warp) * 4;  // first element of this warp's group
+  // one group ahead: coordinates of node q of element slot; two ahead: its node id (as in k_elem_poisson)
+  auto elem_of = [&](int64_t base) { const int64_t e = base + slot; return e < e1 ? e : e1 - 1; };
+  double nx = 0., ny = 0., nz = 0.;
+  uint32_t nnode = 0;
+  if (eb < e1) {
+    const uint64_t node = conn[elem_of(eb) * NPE + q];
+    nx = xyz[node * 3]; ny = xyz[node * 3 + 1]; nz = xyz[node * 3 + 2];
+    if (eb + stride < e1) nnode = conn[elem_of(eb + stride) * NPE + q];
+  }
+  for (; eb < e1; eb += stride) {
+    const int64_t e = eb + slot;
+    const bool valid = e < e1;  // a short last group recomputes element e1-1 in the spare slots and stores nothing
+    Xw[slot * 24 + 3 * q] = nx; Xw[slot * 24 + 3 * q + 1] = ny; Xw[slot * 24 + 3 * q + 2] = nz;
+    if (eb + stride < e1) {
+      const uint64_t node = nnode;
+      nx = xyz[node * 3]; ny = xyz[node * 3 + 1]; nz = xyz[node * 3 + 2];
+      if (eb + 2 * stride < e1) nnode = conn[elem_of(eb + 2 * stride) * NPE + q];
+    }
+    __syncwarp();
+
+    // ---- A: lane = (slot, point) -----------------------------------------------------------------------------------
+    const unsigned okmask = __ballot_sync(FULL, affine_check_lane<NPE>(X, q));
+    const bool affine = ((okmask >> (8 * slot)) & 0xffu) == 0xffu;
+    const int qj = affine ? 0 : q;  // compute_affine_map: the Jacobian of point 0 serves every point (fe_map.C:1167-1244)
+    double x = 0., y = 0., z = 0., xa = 0., ya = 0., za = 0., xb = 0., yb = 0., zb = 0., xc = 0., yc = 0., zc = 0.;
+#pragma unroll
+    for (int i = 0; i < NPE; ++i) {
+      const double px = X[3 * i], py = X[3 * i + 1], pz = X[3 * i + 2];
+      const double p = s_phi[i * NQ + q], a = s_dxi[i * NQ + qj], b = s_deta[i * NQ + qj], c = s_dzeta[i * NQ + qj];
+      x += p * px; y += p * py; z += p * pz;
+      xa += a * px; ya += a * py; za += a * pz;
+      xb += b * px; yb += b * py; zb += b * pz;
+      xc += c * px; yc += c * py; zc += c * pz;
+    }
+    const double jac = (xa * (yb * zc - zb * yc) + ya * (zb * xc - xb * zc) + za * (xb * yc - yb * xc));  // fe_map.C:1046-1048
+    const bool bad = !(jac > 0.);
+    if (bad && valid) atomicAdd(&flags[0], 1);
+    const double JxW = (affine && q != 0) ? jac * s_qw[0] / s_qw[0] * s_qw[q] : jac * s_qw[q];
+    const double sc = bad ? 0. : rsqrt(jac);
+    double S[9];
+    S[0] = (yb * zc - zb * yc) * sc; S[1] = (zb * xc - xb * zc) * sc; S[2] = (xb * yc - yb * xc) * sc;
+    S[3] = (za * yc - ya * zc) * sc; S[4] = (xa * zc - za * xc) * sc; S[5] = (ya * xc - xa * yc) * sc;
+    S[6] = (ya * zb - za * yb) * sc; S[7] = (za * xb - xa * zb) * sc; S[8] = (xa * yb - ya * xb) * sc;
+    {
+      double f = 0.;
+      if (forcing == FEASM_FORCING_EX4_FD) {
+        const bool big = !(fabs(x) + fabs(y) + fabs(z) < 2.e4);
+        f = __any_sync(FULL, big) ? ex4_forcing_lib(x, y, z) : ex4_forcing_t<true>(x, y, z);
+      } else if (forcing == FEASM_FORCING_TABULATED) {
+        f = f_tab[(valid ? e : e1 - 1) * NQ + q];
+      }
+      fw[lane] = JxW * f;
+    }
+
+    // ---- B+C: Ke_s = G_s G_s^T, one slot after the other (h1_fe_transformation.C:150-187, introduction_ex4.C:464-467) ----
+    double ta[C::QG], tb[C::QG], tc[C::QG];  // the lane's entries of the scaled reference-gradient table: the same for all slots
+#pragma unroll
+    for (int qg = 0; qg < C::QG; ++qg) {
+      ta[qg] = twp[4 * qg]; tb[qg] = twp[8 * C::TS + 4 * qg]; tc[qg] = twp[16 * C::TS + 4 * qg];
+    }
+    double acc[4][2];
+#pragma unroll
+    for (int s4 = 0; s4 < 4; ++s4) {
+      acc[s4][0] = 0.; acc[s4][1] = 0.;
+#pragma unroll
+      for (int qg = 0; qg < C::QG; ++qg) {
+        const int src = 8 * s4 + 4 * qg + t4;
+        double Sq[9];
+#pragma unroll
+        for (int k = 0; k < 9; ++k) Sq[k] = __shfl_sync(FULL, S[k], src);
+#pragma unroll
+        for (int d = 0; d < 3; ++d) {
+          const double G = ta[qg] * Sq[d] + tb[qg] * Sq[3 + d] + tc[qg] * Sq[6 + d];
+          dmma884(acc[s4][0], acc[s4][1], G, G);
+        }
+      }
+    }
+    __syncwarp();  // fw
+
+    // ---- D: Fe (lane = (slot, shape function)) and the stores ------------------------------------------------------------
+    double* out = kf + (uint64_t)(eb - e0) * (NPE * rs);
+    if (valid) {
+      double Fe = 0.;
+      if (forcing != FEASM_FORCING_NONE) {
+#pragma unroll
+        for (int k = 0; k < NQ; ++k) Fe += fw[8 * slot + k] * s_phi[q * NQ + k];
+      }
+      out[(uint64_t)slot * (NPE * rs) + q * rs + NPE] = Fe;
+    }
+#pragma unroll
+    for (int s4 = 0; s4 < 4; ++s4)
+      if (eb + s4 < e1)
+        *reinterpret_cast<double2*>(out + (uint64_t)s4 * (NPE * rs) + g * rs + 2 * t4) = make_double2(acc[s4][0], acc[s4][1]);
+    __syncwarp();
+  }
+}
+
+template <int WARPS, int RS>
+int launch_poisson_hex8x4(feasm_ctx* ctx, const feasm_params& p, const double* d_f, int64_t e0, int64_t e1, double* d_kf, int rs) {
+  using C = ElemCfg<8, 8>;
+  const size_t smem = sizeof(double) * (size_t)(C::TAB_SZ + C::TW_SZ + WARPS * (4 * 24 + 32));
+  auto kern = k_elem_poisson_hex8x4<WARPS, RS>;
+  FEASM_CUDA(ctx, cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+  int64_t blocks = (e1 - e0 + 4 * WARPS - 1) / (4 * WARPS);
+  if (blocks > ctx->sm_count) blocks = ctx->sm_count;
+  if (blocks < 1) blocks = 1;
+  kern<<<(unsigned)blocks, WARPS * 32, smem, ctx->stream>>>(ctx->d_xyz, ctx->d_conn, ctx->d_tab, p.forcing, d_f, e0, e1, d_kf, rs, ctx->d_flags);
+  FEASM_CUDA(ctx, cudaGetLastError());
+  return FEASM_OK;
+}
+
+
 // ---- affine elements: reference-tensor contraction (feasm_params.affine_tensor) ----------------------------------
 // On an element with an affine map (Elem::has_affine_map; FEMap::compute_affine_map, fe_map.C:1167-1244) the inverse
 // Jacobian is one matrix for all quadrature points and JxW_q = |J| w_q, so the quadrature loop of
@@ -470,8 +617,15 @@ static int launch_element_kernel(feasm_ctx* ctx, const feasm_params& p, const do
       if (rs == 32) return launch_poisson<27, 27, 12, 32>(ctx, p, d_f, e0, e1, d_kf, rs);  // 256 B records (uint8 positions)
       return launch_poisson<27, 27, 12>(ctx, p, d_f, e0, e1, d_kf, rs);
     }
-    if (ctx->elem_type == FEASM_HEX8 && ctx->tab_nq == 8 && rs == 16) return launch_poisson<8, 8, 16, 16>(ctx, p, d_f, e0, e1, d_kf, rs);
-    if (ctx->elem_type == FEASM_HEX8 && ctx->tab_nq == 8) return launch_poisson<8, 8, 16>(ctx, p, d_f, e0, e1, d_kf, rs);
+    if (ctx->elem_type == FEASM_HEX8 && ctx->tab_nq == 8) {
+      static const bool one_per_warp = getenv("FEASM_HEX8_PACK") && atoi(getenv("FEASM_HEX8_PACK")) == 0;  // A/B knob
+      if (!one_per_warp) {
+        if (rs == 16) return launch_poisson_hex8x4<16, 16>(ctx, p, d_f, e0, e1, d_kf, rs);
+        return launch_poisson_hex8x4<16, 0>(ctx, p, d_f, e0, e1, d_kf, rs);
+      }
+      if (rs == 16) return launch_poisson<8, 8, 16, 16>(ctx, p, d_f, e0, e1, d_kf, rs);
+      return launch_poisson<8, 8, 16>(ctx, p, d_f, e0, e1, d_kf, rs);
+    }
     if (ctx->elem_type == FEASM_HEX8 && ctx->tab_nq == 27) return launch_poisson<8, 27, 16>(ctx, p, d_f, e0, e1, d_kf, rs);
     if (ctx->elem_type == FEASM_TET10 && ctx->tab_nq == 14 && rs == 16) return launch_poisson<10, 14, 16, 16>(ctx, p, d_f, e0, e1, d_kf, rs);
     if (ctx->elem_type == FEASM_TET10 && ctx->tab_nq == 14) return launch_poisson<10, 14, 16>(ctx, p, d_f, e0, e1, d_kf, rs);
