@@ -107,6 +107,16 @@ int feasm_set_constraints(feasm_ctx* ctx, int64_t n_constraints, const uint32_t*
  * n = 0 clears. */
 int feasm_set_side_loads(feasm_ctx* ctx, int64_t n, const uint32_t* elems, const uint8_t* sides, const double* g, int n_g);
 
+/* Dirichlet data by the penalty method — the boundary loop of introduction_ex3.C:386-455 on the listed (element, side)
+ * pairs (there: every side with neighbor_ptr(side) == nullptr):
+ *   Ke(i,j) += JxW_face[qp]*penalty*phi_face[i][qp]*phi_face[j][qp];   Fe(i) += JxW_face[qp]*penalty*value*phi_face[i][qp];
+ * value = the given constant or the exact solution at the side point (introduction_ex3/exact_solution.C:40-47); with
+ * several variables every variable's diagonal block gets the term.  Added after the volume terms and the side loads,
+ * before the element constraint.  HEX8 / HEX27.  n = 0 clears. */
+#define FEASM_PENALTY_CONSTANT 0
+#define FEASM_PENALTY_EX4_EXACT 1
+int feasm_set_side_penalty(feasm_ctx* ctx, int64_t n, const uint32_t* elems, const uint8_t* sides, double penalty, int kind, double value);
+
 /* ---- sparsity pattern ---------------------------------------------------------------------------- */
 /* Host graph route = SparseMatrix::update_sparsity_pattern(const SparsityPattern::Graph&)
  * (include/numerics/sparse_matrix.h:175): CSR over the n_rows local rows, columns = global ids ascending. */

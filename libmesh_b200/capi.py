@@ -19,6 +19,7 @@ POISSON, ELASTICITY = 1, 2
 FORCING_NONE, FORCING_EX4_FD, FORCING_TABULATED = 0, 1, 2
 CONSTRAIN_HETEROGENEOUS, CONSTRAIN_HOMOGENEOUS = 0, 1
 DIRICHLET_ZERO, DIRICHLET_EX4_EXACT = 0, 1
+PENALTY_CONSTANT, PENALTY_EX4_EXACT = 0, 1
 
 # every symbol include/feasm.h declares (tests check the library exports each of them)
 SYMBOLS = [
@@ -32,7 +33,7 @@ SYMBOLS = [
     "feasm_vec_alloc", "feasm_vec_free", "feasm_vec_copy", "feasm_vec_fill", "feasm_vec_axpy", "feasm_vec_pointwise",
     "feasm_vec_reduce", "feasm_vec_set_entry",
     "feasm_generate_cube", "feasm_distribute_dofs_device", "feasm_generate_dirichlet", "feasm_get_mesh", "feasm_get_dofs",
-    "feasm_get_constraints",
+    "feasm_get_constraints", "feasm_set_side_penalty",
 ]
 
 
@@ -116,6 +117,7 @@ def lib():
         "feasm_get_mesh": (i32, [vp, vp, vp, vp]),
         "feasm_get_dofs": (i32, [vp, vp, vp]),
         "feasm_get_constraints": (i32, [vp, vp, vp]),
+        "feasm_set_side_penalty": (i32, [vp, i64, vp, vp, C.c_double, i32, C.c_double]),
     }
     for name, (res, args) in sig.items():
         fn = getattr(L, name)
@@ -300,6 +302,11 @@ class Context:
         if len(e) != len(sd):
             raise ValueError("elems and sides differ in length")
         self._ck(self.L.feasm_set_side_loads(self.h, len(e), _p(e), _p(sd), _p(gg), len(gg)))
+
+    def set_side_penalty(self, elems, sides, penalty=1e10, kind=1, value=0.0):
+        """introduction_ex3.C:386-455 penalty boundary term on the listed (element, side) pairs; empty lists clear."""
+        e, sd = _c(elems, np.uint32), _c(sides, np.uint8)
+        self._ck(self.L.feasm_set_side_penalty(self.h, len(e), _p(e), _p(sd), float(penalty), int(kind), float(value)))
 
     def assemble_begin(self, params):
         self._ck(self.L.feasm_assemble_begin(self.h, C.byref(params)))

@@ -141,6 +141,7 @@ void feasm_destroy(feasm_ctx* ctx) {
   release(ctx->d_con_flag); release(ctx->d_con_val); release(ctx->d_row_ptr); release(ctx->d_col_idx);
   release(ctx->d_values); release(ctx->d_rhs); release(ctx->d_flags); release(ctx->d_tab); release(ctx->d_f);
   release(ctx->d_side_elems); release(ctx->d_side_mask); release(ctx->d_side_tab); release(ctx->d_side_nodes);
+  release(ctx->d_pen_elems); release(ctx->d_pen_mask);
   release(ctx->d_send_slots); release(ctx->d_recv_slots); release(ctx->d_send_buf); release(ctx->d_recv_buf);
   for (auto& ev : ctx->ev) if (ev) cudaEventDestroy(ev);
   cudaStreamDestroy(ctx->stream);
@@ -196,6 +197,8 @@ void feasm_reset_mesh(feasm_ctx* ctx, int elem_type, int64_t n_elem, int64_t n_n
   ctx->side_qorder = -1;
   release(ctx->d_side_elems); release(ctx->d_side_mask);  // element ids of the previous mesh
   ctx->n_side_elems = 0;
+  release(ctx->d_pen_elems); release(ctx->d_pen_mask);
+  ctx->n_pen_elems = 0;
   release(ctx->d_node_mask); release(ctx->d_node_base);
 }
 

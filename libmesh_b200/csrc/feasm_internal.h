@@ -112,6 +112,12 @@ struct feasm_ctx {
   uint32_t* d_side_elems = nullptr;
   uint8_t* d_side_mask = nullptr;
   double side_g[3] = {0., 0., 0.};
+  // penalty sides (feasm_set_side_penalty), same list form
+  int64_t n_pen_elems = 0;
+  uint32_t* d_pen_elems = nullptr;
+  uint8_t* d_pen_mask = nullptr;
+  double penalty = 0., pen_value = 0.;
+  int pen_kind = 0;
   int side_qorder = -1;            // the side tables on the device are for this order
   int side_ns = 0, side_nqf = 0;
   double* d_side_tab = nullptr;    // qw[nqf] | dxi[ns][nqf] | deta[ns][nqf] | phi[6][npe][nqf]

@@ -90,6 +90,9 @@ void orc_system_get_constraints(const orc_system*, uint32_t* dofs, double* value
  * sides (QGauss(dim-1) of the volume rule's order), added after the volume terms and before the element constraint.
  * g has one component per variable.  n = 0 clears. */
 void orc_system_set_side_loads(orc_system*, int64_t n, const uint32_t* elems, const uint8_t* sides, const double* g);
+/* Penalty sides, introduction_ex3.C:386-455: Ke(i,j) += JxW_face*penalty*phi_i*phi_j, Fe(i) += JxW_face*penalty*value*phi_i;
+ * kind 0: value constant, kind 1: value = exact_solution at the side quadrature point.  n = 0 clears. */
+void orc_system_set_side_penalty(orc_system*, int64_t n, const uint32_t* elems, const uint8_t* sides, double penalty, int kind, double value);
 /* SparsityPattern::Build (src/base/sparsity_pattern.C:96-363): returns nnz */
 int64_t orc_system_build_sparsity(orc_system*);
 void orc_system_get_sparsity(const orc_system*, uint64_t* row_ptr /*n_dofs+1*/, uint32_t* col_idx /*nnz*/);

@@ -46,6 +46,7 @@ def _load(fast: bool):
         "orc_side_reinit": (C.c_int, [C.c_int, _f64p, C.c_int, C.c_int, C.c_int, vp, vp, vp, vp, vp]),
         "orc_mesh_boundary_sides": (C.c_int64, [vp, C.c_int, C.c_int64, vp, vp]),
         "orc_system_set_side_loads": (None, [vp, C.c_int64, vp, vp, vp]),
+        "orc_system_set_side_penalty": (None, [vp, C.c_int64, vp, vp, C.c_double, C.c_int, C.c_double]),
         "orc_mesh_build_cube": (vp, [C.c_int] * 4 + [C.c_double] * 6 + [C.c_int]),
         "orc_mesh_free": (None, [vp]),
         "orc_mesh_n_elem": (C.c_int64, [vp]),
@@ -261,6 +262,12 @@ class System:
         gg = np.zeros(3)
         gg[: self.n_vars] = np.asarray(g, dtype=np.float64).reshape(-1)[: self.n_vars]
         self.L.orc_system_set_side_loads(self.h, len(e), _ptr(e), _ptr(sd), _ptr(gg))
+
+    def set_side_penalty(self, elems, sides, penalty=1e10, kind=1, value=0.0):
+        """introduction_ex3.C:386-455: penalty boundary term on the listed sides (kind 1: exact solution, 0: constant)."""
+        e = np.ascontiguousarray(elems, dtype=np.uint32)
+        sd = np.ascontiguousarray(sides, dtype=np.uint8)
+        self.L.orc_system_set_side_penalty(self.h, len(e), _ptr(e), _ptr(sd), float(penalty), int(kind), float(value))
 
     def build_sparsity(self):
         self.nnz = self.L.orc_system_build_sparsity(self.h)

@@ -33,6 +33,10 @@ struct System {
   // traction side_g (one component per variable)
   std::vector<uint8_t> side_mask;
   double side_g[3] = {0., 0., 0.};
+  // penalty sides (introduction_ex3.C:386-455): bit s of pen_mask[e] = side s of element e carries the penalty term
+  std::vector<uint8_t> pen_mask;
+  double penalty = 0., pen_value = 0.;
+  int pen_kind = 0;  // 0: value = pen_value, 1: value = exact_solution at the side point
 };
 
 static void distribute_dofs(System& s) {
@@ -250,6 +254,26 @@ static int element_matrix(const System& s, const Problem& P, int64_t e, ElemWork
           for (int i = 0; i < s.n_vars; i++) w.Fe[i * n + di] += w.sd.JxW[qp] * (s.side_g[i] * w.sd.phi[di * nqf + qp]);
     }
   }
+  // Dirichlet data by the penalty method, introduction_ex3.C:386-455 (there in 2D; the same loop on the sides of a 3D
+  // element): for every side without a neighbour
+  //   Ke(i,j) += JxW_face[qp]*penalty*phi_face[i][qp]*phi_face[j][qp];   Fe(i) += JxW_face[qp]*penalty*value*phi_face[i][qp];
+  // with several variables the term is applied to every variable's diagonal block (this restatement's extension).
+  if (!s.pen_mask.empty() && s.pen_mask[e]) {
+    for (int side = 0; side < 6; ++side) {
+      if (!(s.pen_mask[e] >> side & 1)) continue;
+      if (side_reinit(m.type, w.X.data(), side, P.qorder, w.sd) < 0) return -1;
+      const int nqf = w.sd.nqf;
+      for (int qp = 0; qp < nqf; qp++) {
+        const double value = s.pen_kind == 1 ? exact_solution(w.sd.xyz[3 * qp], w.sd.xyz[3 * qp + 1], w.sd.xyz[3 * qp + 2]) : s.pen_value;
+        for (int v = 0; v < s.n_vars; v++) {
+          for (int i = 0; i < n; i++)
+            for (int j = 0; j < n; j++)
+              w.Ke[(size_t)(v * n + i) * nd + (v * n + j)] += w.sd.JxW[qp] * s.penalty * w.sd.phi[i * nqf + qp] * w.sd.phi[j * nqf + qp];
+          for (int i = 0; i < n; i++) w.Fe[v * n + i] += w.sd.JxW[qp] * s.penalty * value * w.sd.phi[i * nqf + qp];
+        }
+      }
+    }
+  }
   return 0;
 }
 
@@ -418,6 +442,15 @@ void orc_system_set_side_loads(orc_system* h, int64_t n, const uint32_t* elems, 
   s.side_mask.assign(s.mesh->n_elem, 0);
   for (int64_t k = 0; k < n; ++k) s.side_mask[elems[k]] |= (uint8_t)(1u << sides[k]);
   for (int i = 0; i < 3; ++i) s.side_g[i] = i < s.n_vars ? g[i] : 0.;
+}
+
+void orc_system_set_side_penalty(orc_system* h, int64_t n, const uint32_t* elems, const uint8_t* sides, double penalty, int kind, double value) {
+  orc::System& s = h->s;
+  s.pen_mask.clear();
+  if (n <= 0) return;
+  s.pen_mask.assign(s.mesh->n_elem, 0);
+  for (int64_t k = 0; k < n; ++k) s.pen_mask[elems[k]] |= (uint8_t)(1u << sides[k]);
+  s.penalty = penalty; s.pen_kind = kind; s.pen_value = value;
 }
 
 int64_t orc_system_build_sparsity(orc_system* h) { return orc::build_sparsity(h->s); }

@@ -88,3 +88,67 @@ def test_side_loads_reject_bad_input():
     with pytest.raises(F.FeasmError):
         ctx.set_side_loads([m.n_elem], [0], [1.0])
     ctx.close()
+
+
+def _all_boundary_sides(m):
+    es, ss = zip(*(m.boundary_sides(b) for b in range(6)))
+    return np.concatenate(es), np.concatenate(ss)
+
+
+@pytest.mark.parametrize("etype,dims,skew,qorder", [(27, (4, 3, 2), None, 0), (27, (3, 3, 3), (1, 0.04, 7), 0), (8, (5, 4, 3), (1, 0.05, 3), 3)])
+def test_penalty_sides_match_the_ex3_loop(etype, dims, skew, qorder):
+    """feasm_set_side_penalty (introduction_ex3.C:386-455 on HEX sides) against the oracle: element matrices and the
+    assembled system of the penalty form of ex4 (no constraint rows; penalty 1e10 on every boundary side)."""
+    from libmesh_b200 import capi as F
+    from oracle import oracle as O
+
+    m = O.Mesh(etype, *dims, bounds=(-1, 1, -1, 1, -1, 1))
+    if skew:
+        m.skew(*skew)
+    s = O.System(m, 1)
+    e, sd = _all_boundary_sides(m)
+    s.set_side_penalty(e, sd, penalty=1e10, kind=1)
+    s.build_sparsity()
+    xyz, conn, _ = m.arrays()
+    ctx = F.Context(0)
+    ctx.set_mesh(etype, xyz, conn)
+    ctx.set_dofs(s.dofs()[0], s.n_dofs)
+    ctx.build_pattern()
+    ctx.set_side_penalty(e, sd, penalty=1e10, kind=F.PENALTY_EX4_EXACT)
+    f_tab, _ = s.forcing_at_qps(qorder)
+    p = F.make_params(F.POISSON, qorder, F.FORCING_TABULATED, f_host=f_tab)
+    Ko, Fo = s.element_matrices(O.POISSON_EX4, constrained=False, qorder=qorder, forcing=O.FORCING_TABULATED, f_tab=f_tab)
+    K, Fv = ctx.element_matrices(p, constrained=False)
+    assert dense_parity_error(K, Ko) < PARITY_TOL
+    assert vec_parity_error(Fv.ravel(), Fo.ravel()) < PARITY_TOL
+    vo, ro, _ = s.assemble(O.POISSON_EX4, qorder=qorder, forcing=O.FORCING_TABULATED, f_tab=f_tab)
+    ctx.assemble(p)
+    v, r = ctx.get_values()
+    rp, _ = s.sparsity()
+    assert csr_parity_error(v, vo, rp) < PARITY_TOL
+    assert vec_parity_error(r, ro) < PARITY_TOL
+    # clearing the list gives the plain volume system back
+    ctx.set_side_penalty([], [])
+    K2, _ = ctx.element_matrices(p, constrained=False)
+    K0, _ = O.System(m, 1).element_matrices(O.POISSON_EX4, constrained=False, qorder=qorder, forcing=O.FORCING_TABULATED, f_tab=f_tab)
+    assert dense_parity_error(K2, K0) < PARITY_TOL
+
+
+def test_penalty_constant_value_on_every_variable():
+    from libmesh_b200 import capi as F
+    from oracle import oracle as O
+
+    m = O.Mesh(27, 3, 2, 2, bounds=(0, 1, 0, 0.3, 0, 0.1))
+    s = O.System(m, 3)
+    e, sd = m.boundary_sides(4)  # clamp x-min by penalty instead of the constraint rows
+    s.set_side_penalty(e, sd, penalty=1e8, kind=0, value=0.25)
+    xyz, conn, _ = m.arrays()
+    ctx = F.Context(0)
+    ctx.set_mesh(27, xyz, conn)
+    ctx.set_dofs(s.dofs()[0], s.n_dofs, n_vars=3)
+    ctx.set_side_penalty(e, sd, penalty=1e8, kind=F.PENALTY_CONSTANT, value=0.25)
+    p = F.make_params(F.ELASTICITY, 0, F.FORCING_NONE, F.CONSTRAIN_HOMOGENEOUS)
+    Ko, Fo = s.element_matrices(O.ELASTICITY_EX6, constrained=False)
+    K, Fv = ctx.element_matrices(p, constrained=False)
+    assert dense_parity_error(K, Ko) < PARITY_TOL
+    assert vec_parity_error(Fv.ravel(), Fo.ravel()) < PARITY_TOL

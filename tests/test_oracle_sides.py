@@ -92,3 +92,69 @@ def test_ex6_traction_face_and_total_load(etype, dims):
     assert abs(dF[:, 2].sum() + 0.03) < 1e-15                             # int_Gamma g_z ds
     untouched = np.setdiff1d(np.arange(m.n_elem), e)
     assert np.abs(dF[untouched]).max() == 0.0
+
+
+def _exact(x, y, z):  # introduction_ex3/exact_solution.C:40-47, independent of the oracle
+    return np.cos(.5 * np.pi * x) * np.sin(.5 * np.pi * y) * np.cos(.5 * np.pi * z)
+
+
+def _all_boundary_sides(m):
+    es, ss = [], []
+    for b in range(6):
+        e, s = m.boundary_sides(b)
+        es.append(e)
+        ss.append(s)
+    return np.concatenate(es), np.concatenate(ss)
+
+
+@pytest.mark.parametrize("etype,qorder,nv", [(O.HEX27, 5, 1), (O.HEX8, 3, 1), (O.HEX8, 3, 3)])
+def test_penalty_term_is_the_ex3_loop(etype, qorder, nv):
+    """introduction_ex3.C:437-453 on the sides of a 3D element, against an independent numpy evaluation from side_reinit."""
+    m = _mesh(etype, (3, 2, 2), "perturbed")
+    e, sd = _all_boundary_sides(m)
+    xyz, conn, _ = m.arrays()
+    prob = O.POISSON_EX4 if nv == 1 else O.ELASTICITY_EX6
+    s0, s1 = O.System(m, nv), O.System(m, nv)
+    s1.set_side_penalty(e, sd, penalty=1e10, kind=1)
+    (K0, F0), (K1, F1) = (s.element_matrices(prob, constrained=False, qorder=qorder) for s in (s0, s1))
+    n = etype
+    for el in range(m.n_elem):
+        dK, dF = np.zeros((n, n)), np.zeros(n)
+        for k in np.nonzero(e == el)[0]:
+            d = O.side_reinit(etype, xyz[conn[el]], int(sd[k]), qorder)
+            val = _exact(d["xyz"][:, 0], d["xyz"][:, 1], d["xyz"][:, 2])
+            dK += 1e10 * np.einsum("q,iq,jq->ij", d["JxW"], d["phi"], d["phi"])
+            dF += 1e10 * (d["phi"] * (d["JxW"] * val)).sum(1)
+        for v in range(nv):
+            blk = (K1[el] - K0[el]).reshape(nv * n, nv * n)[v * n:(v + 1) * n, v * n:(v + 1) * n]
+            assert np.abs(blk - dK).max() <= 1e-12 * max(1.0, np.abs(dK).max())
+            assert np.abs((F1[el] - F0[el]).reshape(nv, n)[v] - dF).max() <= 1e-12 * max(1.0, np.abs(dF).max())
+        if nv > 1:  # off-diagonal variable blocks are untouched
+            full = (K1[el] - K0[el]).reshape(nv * n, nv * n)
+            assert np.abs(full[:n, n:2 * n]).max() <= 1e-6 * max(1.0, np.abs(dK).max()) * 1e-9
+
+
+def test_penalty_enforces_the_boundary_values_like_ex3():
+    """The point of the method (introduction_ex3.C:386-400): with penalty 1e10 the solution takes the exact solution's
+    values on the boundary; on the ex4 problem the whole nodal error is then the discretisation error."""
+    import scipy.sparse as sp
+    import scipy.sparse.linalg as spla
+
+    errs = []
+    for nn in (2, 4):
+        m = O.Mesh(O.HEX27, nn, nn, nn, bounds=(-1, 1, -1, 1, -1, 1), renumber_nodes=False)
+        s = O.System(m, 1)
+        s.set_side_penalty(*_all_boundary_sides(m), penalty=1e10, kind=1)
+        s.build_sparsity()
+        v, r, _ = s.assemble(O.POISSON_EX4)
+        rp, ci = s.sparsity()
+        A = sp.csr_matrix((v, ci.astype(np.int64), rp.astype(np.int64)), shape=(s.n_dofs, s.n_dofs))
+        u = spla.spsolve(A.tocsc(), r)
+        xyz, _, mask = m.arrays()
+        _, nb, _ = s.dofs()
+        exact = _exact(xyz[:, 0], xyz[:, 1], xyz[:, 2])
+        err = np.abs(u[nb] - exact)
+        errs.append((err[mask != 0].max(), err.max()))
+    # boundary nodes carry the L2 projection of the exact solution onto the Q2 faces: O(h^3); 0.044 at h = 1
+    assert errs[0][0] < 0.06 and errs[1][0] < errs[0][0] / 5
+    assert errs[1][1] < errs[0][1] / 4
