@@ -21,7 +21,7 @@ ctx = F.Context(0)
 ctx.set_mesh(etype, xyz, conn); ctx.set_dofs(ed, nd); ctx.set_constraints(base[bn], g)
 ctx.build_pattern(); ctx.prepare()
 import os
-p = F.make_params(F.POISSON, 0, F.FORCING_EX4_FD, affine_tensor=int(os.environ.get('AFFINE', '0')))
+p = F.make_params(F.POISSON, int(os.environ.get('QORDER', '0')), F.FORCING_EX4_FD, affine_tensor=int(os.environ.get('AFFINE', '0')))
 for _ in range(reps):
     ctx.assemble(p)
     print(ctx.last_timing())
