@@ -44,6 +44,67 @@ k_row_reduce(const uint64_t* __restrict__ row_ptr, const uint64_t* __restrict__ 
 
 // Fallback for rows longer than the shared-memory budget: one warp per row accumulates straight into the (zeroed)
 // global row, contributors in element order.
+// ---- 8 dofs per element (HEX8, one variable): four rows per warp instruction ---------------------------------------------
+// With lane = local dof only 9 of 32 lanes carry a contributor and the ring kernel above is instruction-bound for HEX8
+// (ncu: issue slots 87 % busy at half the HBM peak).  Here an 8-lane group owns a row: lane = local dof b of the
+// contributor; the incidence ids of up to 8 contributors are fetched by the group's lanes and broadcast with a
+// width-8 shuffle, all their record entries (value, position byte; lane 0 also Fe) are loaded straight from global
+// memory — 16 independent loads per lane in flight, no staging ring — and then added into the group's row image in
+// shared memory strictly in element order (bitwise the same sums as k_row_reduce).  Rows are dealt to consecutive
+// groups, so a warp writes four consecutive CSR rows.
+template <typename PosT>
+__global__ void __launch_bounds__(256)
+k_row_reduce_nd8(const uint64_t* __restrict__ row_ptr, const uint64_t* __restrict__ inc_ptr, const uint32_t* __restrict__ inc,
+                 const unsigned char* __restrict__ rec, int img_cells, const uint32_t* __restrict__ row_list, int64_t row0,
+                 int64_t n_list, double* __restrict__ values, double* __restrict__ rhs) {
+  constexpr int ND = 8;
+  constexpr int ldrb = feasm_ldr(ND) * 8, recb = feasm_recb(ND, (int)sizeof(PosT));
+  extern __shared__ double s_img[];  // [groups of the block][img_cells]
+  const int lane = threadIdx.x & 31, gl = lane & 7;
+  const unsigned gmask = 0xffu << (lane & 24);
+  double* img = s_img + (threadIdx.x >> 3) * img_cells;
+  for (int t = gl; t < img_cells; t += 8) img[t] = 0.;
+  __syncwarp(gmask);
+  const int64_t n_groups = (int64_t)gridDim.x * (blockDim.x >> 3);
+  for (int64_t i = row0 + blockIdx.x * (int64_t)(blockDim.x >> 3) + (threadIdx.x >> 3); i < n_list; i += n_groups) {
+    const uint32_t r = row_list ? row_list[i] : (uint32_t)i;
+    const uint64_t i0 = inc_ptr[r], p0 = row_ptr[r];
+    const int cnt = (int)(inc_ptr[r + 1] - i0), len = (int)(row_ptr[r + 1] - p0);
+    double fe = 0.;
+    for (int c0 = 0; c0 < cnt; c0 += 8) {
+      const int n = cnt - c0 < 8 ? cnt - c0 : 8;
+      const uint32_t my_id = gl < n ? inc[i0 + c0 + gl] : 0u;
+      double v[8], f[8];
+      unsigned pp[8];
+#pragma unroll
+      for (int c = 0; c < 8; ++c) {
+        const uint32_t id = __shfl_sync(gmask, my_id, c, 8);
+        v[c] = 0.; f[c] = 0.; pp[c] = 0;
+        if (c < n) {
+          const unsigned char* R = rec + (uint64_t)id * (uint32_t)recb;
+          v[c] = reinterpret_cast<const double*>(R)[gl];
+          pp[c] = reinterpret_cast<const PosT*>(R + ldrb)[gl];
+          if (gl == 0) f[c] = reinterpret_cast<const double*>(R)[ND];
+        }
+      }
+#pragma unroll
+      for (int c = 0; c < 8; ++c) {
+        if (c < n) {  // positions within one record are distinct; contributors follow one another in element order
+          img[pp[c]] += v[c];
+          fe += f[c];
+        }
+        __syncwarp(gmask);
+      }
+    }
+    for (int t = gl; t < len; t += 8) {
+      __stcs(values + p0 + t, img[t]);
+      img[t] = 0.;
+    }
+    if (gl == 0) rhs[r] = fe;
+    __syncwarp(gmask);
+  }
+}
+
 template <typename PosT>
 __global__ void k_row_reduce_global(const uint64_t* __restrict__ row_ptr, const uint64_t* __restrict__ inc_ptr,
                                     const uint32_t* __restrict__ inc, const unsigned char* __restrict__ rec, int nd,
@@ -122,6 +183,23 @@ __global__ void k_add_matrix(const double* __restrict__ dm, const uint32_t* __re
 
 template <typename PosT, int ND>
 int launch_row_reduce_t(feasm_ctx* ctx, const uint32_t* d_row_list, int64_t n_list, cudaStream_t stream, int64_t row0) {
+  if (ND == 8) {
+    static const bool ring = getenv("FEASM_RR_ND8") && atoi(getenv("FEASM_RR_ND8")) == 0;  // A/B knob: 0 = the ring kernel
+    const int img_cells = (int)ctx->max_row_len + 1;
+    const size_t smem = sizeof(double) * 32 * (size_t)img_cells;
+    if (!ring && smem <= 48 * 1024) {
+      const int64_t rows = n_list - row0;
+      int64_t grid = (rows + 31) / 32;
+      const int64_t cap = (int64_t)ctx->sm_count * 8 * 4;  // 8 resident blocks per SM, a few rows per group
+      if (grid > cap) grid = cap;
+      if (grid > 0)
+        k_row_reduce_nd8<PosT><<<(unsigned)grid, 256, smem, stream>>>(ctx->d_row_ptr, ctx->d_inc_ptr, ctx->d_inc,
+                                                                      reinterpret_cast<const unsigned char*>(ctx->d_kf), img_cells, d_row_list,
+                                                                      row0, n_list, ctx->d_values, ctx->d_rhs);
+      FEASM_CUDA(ctx, cudaGetLastError());
+      return FEASM_OK;
+    }
+  }
   constexpr int WARPS = 4;
   const int cap = ((int)ctx->max_row_len + 2) & ~1;  // row cells + the Fe cell; even: every warp's ring stays 16 B aligned
   const int recb = feasm_recb(ctx->nd, (int)sizeof(PosT));
