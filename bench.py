@@ -147,7 +147,7 @@ def run_ours(args):
     # SURVEY 8f rank 2): timed (second run: the first loads the kernels) and compared with the host generators' arrays
     # at full size.  Setup only; the timed steps below run on `ctx`.
     ingest = None
-    if etype != F.TET10:
+    if True:
         ing = F.Context(local)
         for _ in range(2):
             ti = time.time()

@@ -225,7 +225,8 @@ int64_t feasm_distribute_dofs(int npe, int64_t n_elem, int64_t n_nodes, const ui
 
 /* ---- device-side mesh ingest (the step before the path, without the host) --------------- */
 /* MeshTools::Generation::build_cube (src/mesh/mesh_generation.C:1285-1340 nodes, :1399-1432 elements, :1779-1785
- * rescale, :1416-1432 boundary ids) for HEX8 / HEX27, generated in the context's device arrays; replaces
+ * rescale, :1416-1432 boundary ids; TET10: the 24-tet split + all_second_order of :1795-1907) for HEX8 / HEX27 / TET10,
+ * generated in the context's device arrays; replaces
  * feasm_build_cube + feasm_set_mesh.  Same node ids, element order and coordinates bit for bit. */
 int feasm_generate_cube(feasm_ctx* ctx, int elem_type, int nx, int ny, int nz, const double bounds[6]);
 /* DofMap::distribute_dofs (src/base/dof_map.C:1445-1507, one rank, one variable group of n_vars LAGRANGE variables)

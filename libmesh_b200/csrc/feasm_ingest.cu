@@ -1,6 +1,6 @@
 // feasm_ingest.cu — device-side mesh ingest: the step immediately BEFORE the assembly path.
 //
-//   feasm_generate_cube          MeshTools::Generation::build_cube for HEX8 / HEX27 (src/mesh/mesh_generation.C:
+//   feasm_generate_cube          MeshTools::Generation::build_cube for HEX8 / HEX27 / TET10 (src/mesh/mesh_generation.C:
 //                                1285-1340 nodes, :1399-1432 / :1575-1626 elements, :1779-1785 rescale, :1416-1432
 //                                boundary ids) written straight into the context's device arrays: one thread per
 //                                node / per (element, local node), closed form over the lattice.
@@ -18,6 +18,7 @@
 // Product code: never includes oracle/.  Setup path, HBM-bound and tiny next to one assembly (96^3 HEX27: 7.2 M
 // nodes, 24 M incidences — well under a millisecond of traffic); kernels are plain grid-stride loops with coalesced
 // stores.
+#include <algorithm>
 #include <cub/cub.cuh>
 
 #include "feasm_internal.h"
@@ -117,6 +118,100 @@ __global__ void k_dirichlet(uint8_t* __restrict__ con_flag, double* __restrict__
   if (mine) atomicAdd(count, mine);
 }
 
+// ---- build_cube(TET10) (src/mesh/mesh_generation.C:1795-1907) ------------------------------------------------------------
+// Every HEX27 cell is cut into 24 tets (side vertex `sub`, side centre, side vertex `sub+1`, cell centre), then
+// all_second_order() gives every tet edge one new node at FIRST SIGHT while walking the tets in order.  On the device:
+// vertices = lattice nodes that are not HEX27 mid-edge nodes, compacted by a scan; "first sight" = the smallest
+// (tet, edge) sequence number among the occurrences of an edge key, found by a stable radix sort of the keys; the new
+// node ids are the ranks of those first sequence numbers (a second sort).
+__constant__ signed char c_side5[6][5] = {{0, 3, 2, 1, 20}, {0, 1, 5, 4, 21}, {1, 2, 6, 5, 22}, {2, 3, 7, 6, 23}, {3, 0, 4, 7, 24}, {4, 5, 6, 7, 25}};
+__constant__ signed char c_tet_edge[6][2] = {{0, 1}, {1, 2}, {0, 2}, {0, 3}, {1, 3}, {2, 3}};  // cell_tet10.C edge_nodes_map
+
+__global__ void k_tet_vertex_flags(uint32_t* __restrict__ flag, const Lattice L, const int64_t n_lat) {
+  for (int64_t id = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; id < n_lat; id += (int64_t)gridDim.x * blockDim.x) {
+    const int odd = (int)((id % L.sx) & 1) + (int)(((id / L.sx) % L.sy) & 1) + (int)((id / (L.sx * L.sy)) & 1);
+    flag[id] = odd != 1;  // corners (0 odd), side centres (2), cell centres (3); mid-edges (1) are orphans
+  }
+}
+
+__global__ void k_tet_vertices(double* __restrict__ xyz, uint8_t* __restrict__ mask, const uint32_t* __restrict__ flag,
+                               const uint32_t* __restrict__ lat_new, const Lattice L, const int64_t n_lat) {
+  for (int64_t id = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; id < n_lat; id += (int64_t)gridDim.x * blockDim.x) {
+    if (!flag[id]) continue;
+    const int64_t i = id % L.sx, j = (id / L.sx) % L.sy, k = id / (L.sx * L.sy);
+    const uint32_t n = lat_new[id];
+    xyz[3 * (size_t)n + 0] = __dadd_rn(__dmul_rn(__ddiv_rn((double)i, (double)L.gx), __dadd_rn(L.b[1], -L.b[0])), L.b[0]);
+    xyz[3 * (size_t)n + 1] = __dadd_rn(__dmul_rn(__ddiv_rn((double)j, (double)L.gy), __dadd_rn(L.b[3], -L.b[2])), L.b[2]);
+    xyz[3 * (size_t)n + 2] = __dadd_rn(__dmul_rn(__ddiv_rn((double)k, (double)L.gz), __dadd_rn(L.b[5], -L.b[4])), L.b[4]);
+    mask[n] = (uint8_t)((k == 0) << 0 | (j == 0) << 1 | (i == L.gx) << 2 | (j == L.gy) << 3 | (i == 0) << 4 | (k == L.gz) << 5);
+  }
+}
+
+// vertices of tet t into conn[t][0..3]; the six edge keys (min vertex << 32 | max vertex) with their sequence numbers
+__global__ void k_tet_vertices_and_keys(uint32_t* __restrict__ conn, uint64_t* __restrict__ key, uint32_t* __restrict__ seq,
+                                        const uint32_t* __restrict__ lat_new, const Lattice L, const int64_t n_tet) {
+  for (int64_t t = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; t < n_tet; t += (int64_t)gridDim.x * blockDim.x) {
+    const int64_t c = t / 24;
+    const int s = (int)((t % 24) / 4), sub = (int)(t % 4);
+    const int64_t ci = c % L.nx, cj = (c / L.nx) % L.ny, ck = c / (L.nx * L.ny);
+    const int64_t corner = 2 * ci + L.sx * (2 * cj + L.sy * (2 * ck));
+    auto lat = [&](int a) { return corner + (c_ref[a][0] + 1) + L.sx * ((c_ref[a][1] + 1) + L.sy * (int64_t)(c_ref[a][2] + 1)); };
+    uint32_t v[4];
+    v[0] = lat_new[lat(c_side5[s][sub])];
+    v[1] = lat_new[lat(c_side5[s][4])];
+    v[2] = lat_new[lat(c_side5[s][(sub + 1) & 3])];
+    v[3] = lat_new[lat(26)];
+#pragma unroll
+    for (int a = 0; a < 4; ++a) conn[t * 10 + a] = v[a];
+#pragma unroll
+    for (int e = 0; e < 6; ++e) {
+      uint32_t p = v[c_tet_edge[e][0]], q = v[c_tet_edge[e][1]];
+      if (p > q) { const uint32_t w = p; p = q; q = w; }
+      key[t * 6 + e] = ((uint64_t)p << 32) | q;
+      seq[t * 6 + e] = (uint32_t)(t * 6 + e);
+    }
+  }
+}
+
+// sorted by key (stable): head[k] = 1 where a new key starts; the head's seq is the edge's first sight
+__global__ void k_edge_heads(uint32_t* __restrict__ head, const uint64_t* __restrict__ key_s, const int64_t n) {
+  for (int64_t k = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; k < n; k += (int64_t)gridDim.x * blockDim.x)
+    head[k] = k == 0 || key_s[k] != key_s[k - 1];
+}
+
+// compact the heads: first_seq[u] = seq of the head of segment u, seg_id[u] = u
+__global__ void k_edge_first(uint32_t* __restrict__ first_seq, uint32_t* __restrict__ seg_id, const uint32_t* __restrict__ head,
+                             const uint32_t* __restrict__ seg_of, const uint32_t* __restrict__ seq_s, const int64_t n) {
+  for (int64_t k = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; k < n; k += (int64_t)gridDim.x * blockDim.x)
+    if (head[k]) { first_seq[seg_of[k]] = seq_s[k]; seg_id[seg_of[k]] = seg_of[k]; }
+}
+
+// segments sorted by first sight: the r-th one gets node n_vert + r
+__global__ void k_edge_rank(uint32_t* __restrict__ rank_of_seg, const uint32_t* __restrict__ seg_sorted, const int64_t n_seg) {
+  for (int64_t r = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; r < n_seg; r += (int64_t)gridDim.x * blockDim.x)
+    rank_of_seg[seg_sorted[r]] = (uint32_t)r;
+}
+
+// every (tet, edge) occurrence learns its node; the head of a segment also creates it (midpoint, boundary bits)
+__global__ void k_edge_nodes(uint32_t* __restrict__ conn, double* __restrict__ xyz, uint8_t* __restrict__ mask,
+                             const uint64_t* __restrict__ key_s, const uint32_t* __restrict__ seq_s, const uint32_t* __restrict__ head,
+                             const uint32_t* __restrict__ seg_of, const uint32_t* __restrict__ rank_of_seg, const uint32_t n_vert,
+                             const int64_t n) {
+  for (int64_t k = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; k < n; k += (int64_t)gridDim.x * blockDim.x) {
+    // seg_of is the exclusive scan of head: the segment of entry k is seg_of[k] + head[k] - 1
+    const uint32_t seg = seg_of[k] + head[k] - 1u;
+    const uint32_t node = n_vert + rank_of_seg[seg];
+    const uint32_t sq = seq_s[k];
+    conn[(uint64_t)(sq / 6) * 10 + 4 + sq % 6] = node;
+    if (head[k]) {
+      const uint32_t p = (uint32_t)(key_s[k] >> 32), q = (uint32_t)key_s[k];
+#pragma unroll
+      for (int d = 0; d < 3; ++d) xyz[3 * (size_t)node + d] = __ddiv_rn(__dadd_rn(xyz[3 * (size_t)p + d], xyz[3 * (size_t)q + d]), 2.0);
+      mask[node] = mask[p] & mask[q];
+    }
+  }
+}
+
 int grid_for(const feasm_ctx* ctx, int64_t n) {
   const int64_t want = (n + 255) / 256, cap = (int64_t)ctx->sm_count * 16;
   return (int)(want < 1 ? 1 : (want < cap ? want : cap));
@@ -133,10 +228,79 @@ int dev_alloc(feasm_ctx* ctx, T** p, size_t n) {
 
 extern "C" {
 
+// build_cube(TET10) on the device; see the kernels above
+static int generate_tet10_cube(feasm_ctx* ctx, const Lattice& L, int64_t n_elem, int64_t n_nodes) {
+  const int64_t n_lat = L.sx * L.sy * (L.gz + 1), n_occ = n_elem * 6;
+  if (n_occ >= 0x7fffffffll) return feasm_fail(ctx, FEASM_ERR_ARG, "mesh too large for 32-bit edge sequence numbers");
+  uint32_t *d_flag = nullptr, *d_lat_new = nullptr, *d_seq = nullptr, *d_seq_s = nullptr, *d_head = nullptr, *d_seg_of = nullptr,
+           *d_first = nullptr, *d_first_s = nullptr, *d_seg = nullptr, *d_seg_s = nullptr, *d_rank = nullptr;
+  uint64_t *d_key = nullptr, *d_key_s = nullptr;
+  void* d_tmp = nullptr;
+  auto cleanup = [&]() {
+    cudaFree(d_flag); cudaFree(d_lat_new); cudaFree(d_seq); cudaFree(d_seq_s); cudaFree(d_head); cudaFree(d_seg_of); cudaFree(d_first);
+    cudaFree(d_first_s); cudaFree(d_seg); cudaFree(d_seg_s); cudaFree(d_rank); cudaFree(d_key); cudaFree(d_key_s); cudaFree(d_tmp);
+  };
+  auto body = [&]() -> int {
+    cudaStream_t st = ctx->stream;
+    FEASM_CUDA(ctx, cudaMalloc(&d_flag, sizeof(uint32_t) * (n_lat + 1)));
+    FEASM_CUDA(ctx, cudaMalloc(&d_lat_new, sizeof(uint32_t) * (n_lat + 1)));
+    FEASM_CUDA(ctx, cudaMalloc(&d_key, sizeof(uint64_t) * n_occ));
+    FEASM_CUDA(ctx, cudaMalloc(&d_key_s, sizeof(uint64_t) * n_occ));
+    FEASM_CUDA(ctx, cudaMalloc(&d_seq, sizeof(uint32_t) * n_occ));
+    FEASM_CUDA(ctx, cudaMalloc(&d_seq_s, sizeof(uint32_t) * n_occ));
+    FEASM_CUDA(ctx, cudaMalloc(&d_head, sizeof(uint32_t) * (n_occ + 1)));
+    FEASM_CUDA(ctx, cudaMalloc(&d_seg_of, sizeof(uint32_t) * (n_occ + 1)));
+    size_t b0 = 0, b1 = 0, b2 = 0, b3 = 0;
+    FEASM_CUDA(ctx, cub::DeviceScan::ExclusiveSum(nullptr, b0, d_flag, d_lat_new, n_lat + 1, st));
+    FEASM_CUDA(ctx, cub::DeviceRadixSort::SortPairs(nullptr, b1, d_key, d_key_s, d_seq, d_seq_s, n_occ, 0, 64, st));
+    FEASM_CUDA(ctx, cub::DeviceScan::ExclusiveSum(nullptr, b2, d_head, d_seg_of, n_occ + 1, st));
+    FEASM_CUDA(ctx, cub::DeviceRadixSort::SortPairs(nullptr, b3, d_first, d_first_s, d_seg, d_seg_s, n_occ, 0, 32, st));
+    const size_t tmp_bytes = std::max(std::max(b0, b1), std::max(b2, b3));
+    FEASM_CUDA(ctx, cudaMalloc(&d_tmp, tmp_bytes));
+    size_t tb = tmp_bytes;
+    // vertices: lattice nodes that are not HEX27 mid-edge nodes, ids compacted in ascending lattice order
+    FEASM_CUDA(ctx, cudaMemsetAsync(d_flag + n_lat, 0, sizeof(uint32_t), st));
+    k_tet_vertex_flags<<<grid_for(ctx, n_lat), 256, 0, st>>>(d_flag, L, n_lat);
+    FEASM_CUDA(ctx, cub::DeviceScan::ExclusiveSum(d_tmp, tb, d_flag, d_lat_new, n_lat + 1, st));
+    uint32_t n_vert = 0;
+    FEASM_CUDA(ctx, cudaMemcpyAsync(&n_vert, d_lat_new + n_lat, sizeof(uint32_t), cudaMemcpyDeviceToHost, st));
+    k_tet_vertices<<<grid_for(ctx, n_lat), 256, 0, st>>>(ctx->d_xyz, ctx->d_node_mask, d_flag, d_lat_new, L, n_lat);
+    k_tet_vertices_and_keys<<<grid_for(ctx, n_elem), 256, 0, st>>>(ctx->d_conn, d_key, d_seq, d_lat_new, L, n_elem);
+    // first sight of every edge: stable sort by key, the head of each run carries the smallest sequence number
+    tb = tmp_bytes;
+    FEASM_CUDA(ctx, cub::DeviceRadixSort::SortPairs(d_tmp, tb, d_key, d_key_s, d_seq, d_seq_s, n_occ, 0, 64, st));
+    FEASM_CUDA(ctx, cudaMemsetAsync(d_head + n_occ, 0, sizeof(uint32_t), st));
+    k_edge_heads<<<grid_for(ctx, n_occ), 256, 0, st>>>(d_head, d_key_s, n_occ);
+    tb = tmp_bytes;
+    FEASM_CUDA(ctx, cub::DeviceScan::ExclusiveSum(d_tmp, tb, d_head, d_seg_of, n_occ + 1, st));
+    uint32_t n_seg = 0;
+    FEASM_CUDA(ctx, cudaMemcpyAsync(&n_seg, d_seg_of + n_occ, sizeof(uint32_t), cudaMemcpyDeviceToHost, st));
+    FEASM_CUDA(ctx, cudaStreamSynchronize(st));
+    if ((int64_t)n_vert + n_seg != n_nodes) return feasm_fail(ctx, FEASM_ERR_STATE, "tet split: node count differs from feasm_cube_sizes");
+    FEASM_CUDA(ctx, cudaMalloc(&d_first, sizeof(uint32_t) * n_seg));
+    FEASM_CUDA(ctx, cudaMalloc(&d_first_s, sizeof(uint32_t) * n_seg));
+    FEASM_CUDA(ctx, cudaMalloc(&d_seg, sizeof(uint32_t) * n_seg));
+    FEASM_CUDA(ctx, cudaMalloc(&d_seg_s, sizeof(uint32_t) * n_seg));
+    FEASM_CUDA(ctx, cudaMalloc(&d_rank, sizeof(uint32_t) * n_seg));
+    k_edge_first<<<grid_for(ctx, n_occ), 256, 0, st>>>(d_first, d_seg, d_head, d_seg_of, d_seq_s, n_occ);
+    tb = tmp_bytes;
+    FEASM_CUDA(ctx, cub::DeviceRadixSort::SortPairs(d_tmp, tb, d_first, d_first_s, d_seg, d_seg_s, (int64_t)n_seg, 0, 32, st));
+    k_edge_rank<<<grid_for(ctx, n_seg), 256, 0, st>>>(d_rank, d_seg_s, n_seg);
+    k_edge_nodes<<<grid_for(ctx, n_occ), 256, 0, st>>>(ctx->d_conn, ctx->d_xyz, ctx->d_node_mask, d_key_s, d_seq_s, d_head, d_seg_of, d_rank,
+                                                        n_vert, n_occ);
+    FEASM_CUDA(ctx, cudaGetLastError());
+    FEASM_CUDA(ctx, cudaStreamSynchronize(st));
+    return FEASM_OK;
+  };
+  const int rc = body();
+  cudaStreamSynchronize(ctx->stream);
+  cleanup();
+  return rc;
+}
+
 int feasm_generate_cube(feasm_ctx* ctx, int elem_type, int nx, int ny, int nz, const double bounds[6]) {
   if (!ctx) return FEASM_ERR_ARG;
-  if (elem_type != FEASM_HEX8 && elem_type != FEASM_HEX27)
-    return feasm_fail(ctx, FEASM_ERR_ARG, "feasm_generate_cube: HEX8 / HEX27 (the TET10 split stays on the host: feasm_build_cube)");
+  if (elem_type != FEASM_HEX8 && elem_type != FEASM_HEX27 && elem_type != FEASM_TET10) return feasm_fail(ctx, FEASM_ERR_ARG, "feasm_generate_cube: HEX8 / HEX27 / TET10");
   int64_t n_elem = 0, n_nodes = 0;
   if (!bounds || feasm_cube_sizes(elem_type, nx, ny, nz, &n_elem, &n_nodes)) return feasm_fail(ctx, FEASM_ERR_ARG, "bad build_cube arguments");
   if (n_nodes >= 0xffffffffll || n_elem * elem_type >= 0xffffffffll) return feasm_fail(ctx, FEASM_ERR_ARG, "mesh too large for 32-bit ids");
@@ -152,6 +316,7 @@ int feasm_generate_cube(feasm_ctx* ctx, int elem_type, int nx, int ny, int nz, c
   if ((rc = dev_alloc(ctx, &ctx->d_xyz, (size_t)n_nodes * 3))) return rc;
   if ((rc = dev_alloc(ctx, &ctx->d_conn, (size_t)n_elem * elem_type))) return rc;
   if ((rc = dev_alloc(ctx, &ctx->d_node_mask, (size_t)n_nodes))) return rc;
+  if (elem_type == FEASM_TET10) return generate_tet10_cube(ctx, L, n_elem, n_nodes);
   k_cube_nodes<<<grid_for(ctx, n_nodes), 256, 0, ctx->stream>>>(ctx->d_xyz, ctx->d_node_mask, L, n_nodes);
   k_cube_conn<<<grid_for(ctx, n_elem * elem_type), 256, 0, ctx->stream>>>(ctx->d_conn, L, elem_type, n_elem * elem_type);
   FEASM_CUDA(ctx, cudaGetLastError());

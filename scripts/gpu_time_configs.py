@@ -13,18 +13,9 @@ from libmesh_b200 import capi as F
 def time_case(name, etype, n, problem, qorder, n_vars=1, bounds=(-1, 1, -1, 1, -1, 1), dirichlet=0x3f, reps=6):
     ctx = F.Context(0)
     t0 = time.time()
-    if etype == F.TET10:
-        xyz, conn, mask = F.build_cube(etype, n, n, n, bounds)
-        ctx.set_mesh(etype, xyz, conn)
-        ctx.distribute_dofs(n_vars)
-        _, nb = ctx.get_dofs()
-        bn = np.nonzero(mask & dirichlet)[0]
-        g = np.cos(.5 * np.pi * xyz[bn, 0]) * np.sin(.5 * np.pi * xyz[bn, 1]) * np.cos(.5 * np.pi * xyz[bn, 2])
-        ctx.set_constraints(nb[bn], g)
-    else:
-        ctx.generate_cube(etype, n, n, n, bounds)
-        ctx.distribute_dofs(n_vars)
-        ctx.generate_dirichlet(dirichlet, F.DIRICHLET_EX4_EXACT if problem == F.POISSON else F.DIRICHLET_ZERO)
+    ctx.generate_cube(etype, n, n, n, bounds)
+    ctx.distribute_dofs(n_vars)
+    ctx.generate_dirichlet(dirichlet, F.DIRICHLET_EX4_EXACT if problem == F.POISSON else F.DIRICHLET_ZERO)
     nnz = ctx.build_pattern()
     ctx.prepare()
     ctx.synchronize()

@@ -31,6 +31,31 @@ def test_generated_cube_is_build_cube_bit_for_bit(etype, dims, bounds):
     assert np.array_equal(xyz, xh) and np.array_equal(conn, ch) and np.array_equal(mask, mh)
 
 
+@pytest.mark.parametrize("dims,bounds", [((3, 2, 2), (-1, 1, -1, 1, -1, 1)), ((1, 1, 1), (0, 1, 0, 1, 0, 1)), ((4, 5, 3), (-1, 1, 0, 0.3, 0, 0.1))])
+def test_generated_tet10_cube_is_the_24_tet_split_bit_for_bit(dims, bounds):
+    """build_cube(TET10): 24 tets per cell + all_second_order's first-sight edge nodes, by sorts on the device."""
+    F, O = _mods()
+    ctx = F.Context(0)
+    ctx.generate_cube(F.TET10, *dims, bounds=bounds)
+    xyz, conn, mask = ctx.get_mesh()
+    xh, ch, mh = F.build_cube(F.TET10, *dims, bounds)
+    assert conn.shape == ch.shape == (24 * dims[0] * dims[1] * dims[2], 10)
+    assert np.array_equal(conn, ch), "tet connectivity / edge-node numbering differs from the host split"
+    assert np.array_equal(xyz, xh) and np.array_equal(mask, mh)
+    m = O.Mesh(O.TET10, *dims, bounds=bounds, renumber_nodes=False)
+    xo, co, mo = m.arrays()
+    assert np.array_equal(xyz, xo) and np.array_equal(conn, co) and np.array_equal(mask, mo)
+    # and the dof numbering + Dirichlet set on top of it
+    n = ctx.distribute_dofs(1)
+    s = O.System(m, 1)
+    assert n == s.n_dofs and np.array_equal(ctx.get_dofs()[0], s.dofs()[0])
+    ctx.generate_dirichlet(0x3f, F.DIRICHLET_EX4_EXACT)
+    s.add_dirichlet((0, 1, 2, 3, 4, 5), 0)
+    rows, vals = s.constraints()
+    flag, val = ctx.get_constraints()
+    assert np.array_equal(np.nonzero(flag)[0], np.sort(rows)) and np.max(np.abs(val[rows] - vals)) <= 4e-16
+
+
 @pytest.mark.parametrize("etype,dims,nv", [(27, (4, 3, 3), 1), (27, (4, 3, 3), 3), (8, (6, 2, 5), 1), (8, (3, 3, 3), 3)])
 def test_device_dof_numbering_is_first_touch(etype, dims, nv):
     F, O = _mods()
@@ -122,7 +147,7 @@ def test_ingest_errors_are_loud():
     F, O = _mods()
     ctx = F.Context(0)
     with pytest.raises(F.FeasmError):
-        ctx.generate_cube(F.TET10, 2, 2, 2)        # the tet split stays on the host
+        ctx.generate_cube(20, 2, 2, 2)              # HEX20: not an element type of this path
     with pytest.raises(F.FeasmError):
         ctx.distribute_dofs(1)                      # no mesh yet
     xyz, conn, _ = F.build_cube(F.HEX8, 2, 2, 2)
