@@ -22,6 +22,9 @@ from __future__ import annotations
 import argparse
 import json
 import os
+
+# stdout carries the JSON line and nothing else: NCCL's banner ("NCCL version ..." when NCCL_DEBUG is set on the box) goes to stderr
+os.environ.setdefault("NCCL_DEBUG_FILE", "/dev/stderr")
 import subprocess
 import sys
 import threading

@@ -230,6 +230,179 @@ int launch_poisson_hex8x4(feasm_ctx* ctx, const feasm_params& p, const double* d
 }
 
 
+// ---- TET10 with the 14-point rule: two elements per warp -----------------------------------------------------------------
+// The same idea as k_elem_poisson_hex8x4 for 14 quadrature points / 10 nodes: lane = (slot = lane>>4, point or node
+// lane&15).  Phase A serves two consecutive tets per pass; the contraction (one 8x8 DMMA block + two leftover rows by
+// DFMA, as in elem_process) runs slot after slot inside each k group so the table entries are loaded once.
+template <int WARPS, int RS>
+__global__ void __launch_bounds__(WARPS * 32, 1)
+k_elem_poisson_tet10x2(const double* __restrict__ xyz, const uint32_t* __restrict__ conn, const double* __restrict__ tab, int forcing,
+                       const double* __restrict__ f_tab, int64_t e0, int64_t e1, double* __restrict__ kf, int rs_rt, int* flags) {
+  constexpr int NPE = 10, NQ = 14;
+  using C = ElemCfg<NPE, NQ>;
+  static_assert(C::NBF == 1 && C::REM == 2 && C::NB == 2 && C::QG == 4, "layout assumed below");
+  constexpr unsigned FULL = 0xffffffffu;
+  const int rs = RS ? RS : rs_rt;
+  extern __shared__ double smem[];
+  double* s_tab = smem;
+  double* s_tw = smem + C::TAB_SZ;
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  elem_load_tables<NPE, NQ>(s_tab, s_tw, tab, threadIdx.x, WARPS * 32);
+  double* Xw = s_tw + C::TW_SZ + (size_t)warp * (2 * 30 + 32);  // [slot][node][3] | fw[slot][16]
+  double* fw = Xw + 2 * 30;
+  const int slot = lane >> 4, l16 = lane & 15, g = lane >> 2, t4 = lane & 3;
+  const int q = l16 < NQ ? l16 : 0;  // pad lanes repeat point 0; their table columns are zero
+  const double* X = Xw + slot * 30;
+  const double* twp = s_tw + g * C::TS + t4;
+  const double* s_phi = s_tab;
+  const double* s_dxi = s_tab + NPE * NQ;
+  const double* s_deta = s_dxi + NPE * NQ;
+  const double* s_dzeta = s_deta + NPE * NQ;
+  const double* s_qw = s_tab + 4 * NPE * NQ;
+  __syncthreads();
+
+  const int64_t stride = (int64_t)gridDim.x * WARPS * 2;
+  int64_t eb = e0 + ((int64_t)blockIdx.x * WARPS + warp) * 2;
+  auto elem_of = [&](int64_t base) { const int64_t e = base + slot; return e < e1 ? e : e1 - 1; };
+  double nx = 0., ny = 0., nz = 0.;
+  uint32_t nnode = 0;
+  if (eb < e1 && l16 < NPE) {
+    const uint64_t node = conn[elem_of(eb) * NPE + l16];
+    nx = xyz[node * 3]; ny = xyz[node * 3 + 1]; nz = xyz[node * 3 + 2];
+    if (eb + stride < e1) nnode = conn[elem_of(eb + stride) * NPE + l16];
+  }
+  for (; eb < e1; eb += stride) {
+    const int64_t e = eb + slot;
+    const bool valid = e < e1;
+    if (l16 < NPE) {
+      Xw[slot * 30 + 3 * l16] = nx; Xw[slot * 30 + 3 * l16 + 1] = ny; Xw[slot * 30 + 3 * l16 + 2] = nz;
+      if (eb + stride < e1) {
+        const uint64_t node = nnode;
+        nx = xyz[node * 3]; ny = xyz[node * 3 + 1]; nz = xyz[node * 3 + 2];
+        if (eb + 2 * stride < e1) nnode = conn[elem_of(eb + 2 * stride) * NPE + l16];
+      }
+    }
+    __syncwarp();
+
+    // ---- A: lane = (slot, point) -----------------------------------------------------------------------------------
+    const unsigned okmask = __ballot_sync(FULL, affine_check_lane<NPE>(X, l16));
+    const bool affine = ((okmask >> (16 * slot)) & 0xffffu) == 0xffffu;
+    const int qj = affine ? 0 : q;
+    double x = 0., y = 0., z = 0., xa = 0., ya = 0., za = 0., xb = 0., yb = 0., zb = 0., xc = 0., yc = 0., zc = 0.;
+#pragma unroll
+    for (int i = 0; i < NPE; ++i) {
+      const double px = X[3 * i], py = X[3 * i + 1], pz = X[3 * i + 2];
+      const double p = s_phi[i * NQ + q], a = s_dxi[i * NQ + qj], b = s_deta[i * NQ + qj], c = s_dzeta[i * NQ + qj];
+      x += p * px; y += p * py; z += p * pz;
+      xa += a * px; ya += a * py; za += a * pz;
+      xb += b * px; yb += b * py; zb += b * pz;
+      xc += c * px; yc += c * py; zc += c * pz;
+    }
+    const double jac = (xa * (yb * zc - zb * yc) + ya * (zb * xc - xb * zc) + za * (xb * yc - yb * xc));
+    const bool bad = !(jac > 0.);
+    if (bad && valid && l16 < NQ) atomicAdd(&flags[0], 1);
+    const double JxW = (affine && q != 0) ? jac * s_qw[0] / s_qw[0] * s_qw[q] : jac * s_qw[q];
+    const double sc = bad ? 0. : rsqrt(jac);
+    double S[9];
+    S[0] = (yb * zc - zb * yc) * sc; S[1] = (zb * xc - xb * zc) * sc; S[2] = (xb * yc - yb * xc) * sc;
+    S[3] = (za * yc - ya * zc) * sc; S[4] = (xa * zc - za * xc) * sc; S[5] = (ya * xc - xa * yc) * sc;
+    S[6] = (ya * zb - za * yb) * sc; S[7] = (za * xb - xa * zb) * sc; S[8] = (xa * yb - ya * xb) * sc;
+    {
+      double f = 0.;
+      if (forcing == FEASM_FORCING_EX4_FD) {
+        const bool big = !(fabs(x) + fabs(y) + fabs(z) < 2.e4);
+        f = __any_sync(FULL, big) ? ex4_forcing_lib(x, y, z) : ex4_forcing_t<true>(x, y, z);
+      } else if (forcing == FEASM_FORCING_TABULATED && l16 < NQ) {
+        f = f_tab[(valid ? e : e1 - 1) * NQ + l16];
+      }
+      fw[lane] = l16 < NQ ? JxW * f : 0.;
+    }
+
+    // ---- B+C: Ke_s = G_s G_s^T; rows 0-7 by DMMA, rows 8-9 by DFMA against shuffled fragments -----------------------------
+    double acc[2][2] = {{0., 0.}, {0., 0.}};
+    double pr[2][2][2] = {{{0., 0.}, {0., 0.}}, {{0., 0.}, {0., 0.}}};  // [slot][row block][leftover row]
+#pragma unroll
+    for (int qg = 0; qg < C::QG; ++qg) {
+      double ta[2], tb[2], tc[2];
+#pragma unroll
+      for (int ib = 0; ib < 2; ++ib) {
+        ta[ib] = twp[ib * 8 * C::TS + 4 * qg];
+        tb[ib] = twp[2 * 8 * C::TS + ib * 8 * C::TS + 4 * qg];
+        tc[ib] = twp[4 * 8 * C::TS + ib * 8 * C::TS + 4 * qg];
+      }
+#pragma unroll
+      for (int s2 = 0; s2 < 2; ++s2) {
+        const int src = 16 * s2 + 4 * qg + t4;
+        double Sq[9];
+#pragma unroll
+        for (int k = 0; k < 9; ++k) Sq[k] = __shfl_sync(FULL, S[k], src);
+#pragma unroll
+        for (int d = 0; d < 3; ++d) {
+          const double G0 = ta[0] * Sq[d] + tb[0] * Sq[3 + d] + tc[0] * Sq[6 + d];
+          const double G1 = ta[1] * Sq[d] + tb[1] * Sq[3 + d] + tc[1] * Sq[6 + d];
+          dmma884(acc[s2][0], acc[s2][1], G0, G0);
+#pragma unroll
+          for (int r = 0; r < 2; ++r) {
+            const double gr = __shfl_sync(FULL, G1, 4 * r + t4);
+            pr[s2][0][r] += G0 * gr;
+            pr[s2][1][r] += G1 * gr;
+          }
+        }
+      }
+    }
+#pragma unroll
+    for (int s2 = 0; s2 < 2; ++s2)
+#pragma unroll
+      for (int ib = 0; ib < 2; ++ib)
+#pragma unroll
+        for (int r = 0; r < 2; ++r) {
+          pr[s2][ib][r] += __shfl_xor_sync(FULL, pr[s2][ib][r], 1);
+          pr[s2][ib][r] += __shfl_xor_sync(FULL, pr[s2][ib][r], 2);
+        }
+    __syncwarp();  // fw
+
+    // ---- D: Fe (lane = (slot, shape function)) and the stores ------------------------------------------------------------
+    double* out = kf + (uint64_t)(eb - e0) * (NPE * rs);
+    if (valid && l16 < NPE) {
+      double Fe = 0.;
+      if (forcing != FEASM_FORCING_NONE) {
+#pragma unroll
+        for (int k = 0; k < NQ; ++k) Fe += fw[16 * slot + k] * s_phi[l16 * NQ + k];
+      }
+      out[(uint64_t)slot * (NPE * rs) + l16 * rs + NPE] = Fe;
+    }
+#pragma unroll
+    for (int s2 = 0; s2 < 2; ++s2) {
+      if (eb + s2 >= e1) continue;
+      double* o = out + (uint64_t)s2 * (NPE * rs);
+      *reinterpret_cast<double2*>(o + g * rs + 2 * t4) = make_double2(acc[s2][0], acc[s2][1]);
+#pragma unroll
+      for (int r = 0; r < 2; ++r)
+        if (t4 == r) {
+          o[g * rs + 8 + r] = pr[s2][0][r];
+          o[(8 + r) * rs + g] = pr[s2][0][r];
+          if (g < 2) o[(8 + g) * rs + 8 + r] = pr[s2][1][r];
+        }
+    }
+    __syncwarp();
+  }
+}
+
+template <int WARPS, int RS>
+int launch_poisson_tet10x2(feasm_ctx* ctx, const feasm_params& p, const double* d_f, int64_t e0, int64_t e1, double* d_kf, int rs) {
+  using C = ElemCfg<10, 14>;
+  const size_t smem = sizeof(double) * (size_t)(C::TAB_SZ + C::TW_SZ + WARPS * (2 * 30 + 32));
+  auto kern = k_elem_poisson_tet10x2<WARPS, RS>;
+  FEASM_CUDA(ctx, cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+  int64_t blocks = (e1 - e0 + 2 * WARPS - 1) / (2 * WARPS);
+  if (blocks > ctx->sm_count) blocks = ctx->sm_count;
+  if (blocks < 1) blocks = 1;
+  kern<<<(unsigned)blocks, WARPS * 32, smem, ctx->stream>>>(ctx->d_xyz, ctx->d_conn, ctx->d_tab, p.forcing, d_f, e0, e1, d_kf, rs, ctx->d_flags);
+  FEASM_CUDA(ctx, cudaGetLastError());
+  return FEASM_OK;
+}
+
+
 // ---- affine elements: reference-tensor contraction (feasm_params.affine_tensor) ----------------------------------
 // On an element with an affine map (Elem::has_affine_map; FEMap::compute_affine_map, fe_map.C:1167-1244) the inverse
 // Jacobian is one matrix for all quadrature points and JxW_q = |J| w_q, so the quadrature loop of
@@ -627,8 +800,15 @@ static int launch_element_kernel(feasm_ctx* ctx, const feasm_params& p, const do
       return launch_poisson<8, 8, 16>(ctx, p, d_f, e0, e1, d_kf, rs);
     }
     if (ctx->elem_type == FEASM_HEX8 && ctx->tab_nq == 27) return launch_poisson<8, 27, 16>(ctx, p, d_f, e0, e1, d_kf, rs);
-    if (ctx->elem_type == FEASM_TET10 && ctx->tab_nq == 14 && rs == 16) return launch_poisson<10, 14, 16, 16>(ctx, p, d_f, e0, e1, d_kf, rs);
-    if (ctx->elem_type == FEASM_TET10 && ctx->tab_nq == 14) return launch_poisson<10, 14, 16>(ctx, p, d_f, e0, e1, d_kf, rs);
+    if (ctx->elem_type == FEASM_TET10 && ctx->tab_nq == 14) {
+      static const bool one_per_warp = getenv("FEASM_TET10_PACK") && atoi(getenv("FEASM_TET10_PACK")) == 0;  // A/B knob
+      if (!one_per_warp) {
+        if (rs == 16) return launch_poisson_tet10x2<16, 16>(ctx, p, d_f, e0, e1, d_kf, rs);
+        return launch_poisson_tet10x2<16, 0>(ctx, p, d_f, e0, e1, d_kf, rs);
+      }
+      if (rs == 16) return launch_poisson<10, 14, 16, 16>(ctx, p, d_f, e0, e1, d_kf, rs);
+      return launch_poisson<10, 14, 16>(ctx, p, d_f, e0, e1, d_kf, rs);
+    }
     return feasm_fail(ctx, FEASM_ERR_ARG, "no Poisson kernel for this element type / quadrature order");
   }
   if (p.problem == FEASM_ELASTICITY) {
