@@ -44,29 +44,30 @@ k_row_reduce(const uint64_t* __restrict__ row_ptr, const uint64_t* __restrict__ 
 
 // Fallback for rows longer than the shared-memory budget: one warp per row accumulates straight into the (zeroed)
 // global row, contributors in element order.
-// ---- 8 dofs per element (HEX8, one variable): four rows per warp instruction ---------------------------------------------
+// ---- 8 or 10 dofs per element (HEX8 / TET10, one variable): four or two rows per warp instruction ------------------------
 // With lane = local dof only 9 of 32 lanes carry a contributor and the ring kernel above is instruction-bound for HEX8
-// (ncu: issue slots 87 % busy at half the HBM peak).  Here an 8-lane group owns a row: lane = local dof b of the
+// (ncu: issue slots 87 % busy at half the HBM peak).  Here a group of 8 (16 for TET10) lanes owns a row: lane = local dof b of the
 // contributor; the incidence ids of up to 8 contributors are fetched by the group's lanes and broadcast with a
 // width-8 shuffle, all their record entries (value, position byte; lane 0 also Fe) are loaded straight from global
 // memory — 16 independent loads per lane in flight, no staging ring — and then added into the group's row image in
 // shared memory strictly in element order (bitwise the same sums as k_row_reduce).  Rows are dealt to consecutive
 // groups, so a warp writes four consecutive CSR rows.
-template <typename PosT>
+template <typename PosT, int ND, int GROUP>
 __global__ void __launch_bounds__(256)
-k_row_reduce_nd8(const uint64_t* __restrict__ row_ptr, const uint64_t* __restrict__ inc_ptr, const uint32_t* __restrict__ inc,
+k_row_reduce_group(const uint64_t* __restrict__ row_ptr, const uint64_t* __restrict__ inc_ptr, const uint32_t* __restrict__ inc,
                  const unsigned char* __restrict__ rec, int img_cells, const uint32_t* __restrict__ row_list, int64_t row0,
                  int64_t n_list, double* __restrict__ values, double* __restrict__ rhs) {
-  constexpr int ND = 8;
+  static_assert((GROUP == 8 || GROUP == 16) && ND <= GROUP, "a group of 8 or 16 lanes, one lane per local dof");
   constexpr int ldrb = feasm_ldr(ND) * 8, recb = feasm_recb(ND, (int)sizeof(PosT));
+  constexpr int GPB = 256 / GROUP;  // groups per block
   extern __shared__ double s_img[];  // [groups of the block][img_cells]
-  const int lane = threadIdx.x & 31, gl = lane & 7;
-  const unsigned gmask = 0xffu << (lane & 24);
-  double* img = s_img + (threadIdx.x >> 3) * img_cells;
-  for (int t = gl; t < img_cells; t += 8) img[t] = 0.;
+  const int lane = threadIdx.x & 31, gl = lane & (GROUP - 1);
+  const unsigned gmask = (GROUP == 8 ? 0xffu : 0xffffu) << (lane & ~(GROUP - 1));
+  double* img = s_img + (threadIdx.x / GROUP) * img_cells;
+  for (int t = gl; t < img_cells; t += GROUP) img[t] = 0.;
   __syncwarp(gmask);
-  const int64_t n_groups = (int64_t)gridDim.x * (blockDim.x >> 3);
-  for (int64_t i = row0 + blockIdx.x * (int64_t)(blockDim.x >> 3) + (threadIdx.x >> 3); i < n_list; i += n_groups) {
+  const int64_t n_groups = (int64_t)gridDim.x * GPB;
+  for (int64_t i = row0 + blockIdx.x * (int64_t)GPB + (threadIdx.x / GROUP); i < n_list; i += n_groups) {
     const uint32_t r = row_list ? row_list[i] : (uint32_t)i;
     const uint64_t i0 = inc_ptr[r], p0 = row_ptr[r];
     const int cnt = (int)(inc_ptr[r + 1] - i0), len = (int)(row_ptr[r + 1] - p0);
@@ -78,9 +79,9 @@ k_row_reduce_nd8(const uint64_t* __restrict__ row_ptr, const uint64_t* __restric
       unsigned pp[8];
 #pragma unroll
       for (int c = 0; c < 8; ++c) {
-        const uint32_t id = __shfl_sync(gmask, my_id, c, 8);
+        const uint32_t id = __shfl_sync(gmask, my_id, c, GROUP);
         v[c] = 0.; f[c] = 0.; pp[c] = 0;
-        if (c < n) {
+        if (c < n && gl < ND) {
           const unsigned char* R = rec + (uint64_t)id * (uint32_t)recb;
           v[c] = reinterpret_cast<const double*>(R)[gl];
           pp[c] = reinterpret_cast<const PosT*>(R + ldrb)[gl];
@@ -89,14 +90,14 @@ k_row_reduce_nd8(const uint64_t* __restrict__ row_ptr, const uint64_t* __restric
       }
 #pragma unroll
       for (int c = 0; c < 8; ++c) {
-        if (c < n) {  // positions within one record are distinct; contributors follow one another in element order
+        if (c < n && gl < ND) {  // positions within one record are distinct; contributors follow one another in element order
           img[pp[c]] += v[c];
           fe += f[c];
         }
         __syncwarp(gmask);
       }
     }
-    for (int t = gl; t < len; t += 8) {
+    for (int t = gl; t < len; t += GROUP) {
       __stcs(values + p0 + t, img[t]);
       img[t] = 0.;
     }
@@ -183,19 +184,22 @@ __global__ void k_add_matrix(const double* __restrict__ dm, const uint32_t* __re
 
 template <typename PosT, int ND>
 int launch_row_reduce_t(feasm_ctx* ctx, const uint32_t* d_row_list, int64_t n_list, cudaStream_t stream, int64_t row0) {
+  // nd = 10 (TET10, 16-lane groups) was tried and is slower than the ring kernel (0.75 vs 0.52 ms at 786 k tets): rows have
+  // 2..48 contributors there, the two groups of a warp wait for each other
   if (ND == 8) {
-    static const bool ring = getenv("FEASM_RR_ND8") && atoi(getenv("FEASM_RR_ND8")) == 0;  // A/B knob: 0 = the ring kernel
+    constexpr int GROUP = ND == 8 ? 8 : 16, GPB = 256 / GROUP;
+    static const bool ring = getenv("FEASM_RR_GROUP") && atoi(getenv("FEASM_RR_GROUP")) == 0;  // A/B knob: 0 = the ring kernel
     const int img_cells = (int)ctx->max_row_len + 1;
-    const size_t smem = sizeof(double) * 32 * (size_t)img_cells;
+    const size_t smem = sizeof(double) * GPB * (size_t)img_cells;
     if (!ring && smem <= 48 * 1024) {
       const int64_t rows = n_list - row0;
-      int64_t grid = (rows + 31) / 32;
-      const int64_t cap = (int64_t)ctx->sm_count * 8 * 4;  // 8 resident blocks per SM, a few rows per group
+      int64_t grid = (rows + GPB - 1) / GPB;
+      const int64_t cap = (int64_t)ctx->sm_count * 8 * 4;  // a few rows per group
       if (grid > cap) grid = cap;
       if (grid > 0)
-        k_row_reduce_nd8<PosT><<<(unsigned)grid, 256, smem, stream>>>(ctx->d_row_ptr, ctx->d_inc_ptr, ctx->d_inc,
-                                                                      reinterpret_cast<const unsigned char*>(ctx->d_kf), img_cells, d_row_list,
-                                                                      row0, n_list, ctx->d_values, ctx->d_rhs);
+        k_row_reduce_group<PosT, (ND == 8 || ND == 10) ? ND : 8, GROUP><<<(unsigned)grid, 256, smem, stream>>>(
+            ctx->d_row_ptr, ctx->d_inc_ptr, ctx->d_inc, reinterpret_cast<const unsigned char*>(ctx->d_kf), img_cells, d_row_list, row0, n_list,
+            ctx->d_values, ctx->d_rhs);
       FEASM_CUDA(ctx, cudaGetLastError());
       return FEASM_OK;
     }
