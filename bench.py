@@ -25,6 +25,8 @@ import os
 
 # stdout carries the JSON line and nothing else: NCCL's banner ("NCCL version ..." when NCCL_DEBUG is set on the box) goes to stderr
 os.environ.setdefault("NCCL_DEBUG_FILE", "/dev/stderr")
+if os.environ.get("NCCL_DEBUG", "").upper() == "VERSION":  # at this level NCCL ignores NCCL_DEBUG_FILE and prints to stdout
+    del os.environ["NCCL_DEBUG"]
 import subprocess
 import sys
 import threading
