@@ -21,7 +21,15 @@
 
 #include "feasm_elem_dev.cuh"
 
+#ifndef FEASM_ELAST_WARPS
+#define FEASM_ELAST_WARPS 8
+#endif
+#ifndef FEASM_ELAST_UNROLL
+#define FEASM_ELAST_UNROLL 1
+#endif
+
 namespace {
+constexpr int kElastUnroll = FEASM_ELAST_UNROLL;  // k groups unrolled in the elasticity products (tuning knob)
 template <int NPE, int NQ, int WARPS, int RS>
 __global__ void __launch_bounds__(WARPS * 32, 1)
 k_elem_poisson(const double* __restrict__ xyz, const uint32_t* __restrict__ conn, const double* __restrict__ tab,
@@ -651,7 +659,7 @@ k_elem_elasticity(const double* __restrict__ xyz, const uint32_t* __restrict__ c
       for (int ib = 0; ib < NBP; ++ib)
 #pragma unroll
         for (int jb = 0; jb < NBP; ++jb) { acc[ib][jb][0] = 0.; acc[ib][jb][1] = 0.; }
-#pragma unroll 1
+#pragma unroll kElastUnroll
       for (int qg = 0; qg < C::QG; ++qg) {
         double s0 = S[d], s1 = S[3 + d], s2 = S[6 + d], r0 = S[dp], r1 = S[3 + dp], r2 = S[6 + dp];
         if (!affine) {
@@ -813,7 +821,7 @@ static int launch_element_kernel(feasm_ctx* ctx, const feasm_params& p, const do
   }
   if (p.problem == FEASM_ELASTICITY) {
     if (ctx->n_vars != 3) return feasm_fail(ctx, FEASM_ERR_ARG, "elasticity needs 3 variables per node");
-    if (ctx->elem_type == FEASM_HEX27 && ctx->tab_nq == 27) return launch_elasticity<27, 27, 8>(ctx, p, e0, e1, d_kf, rs);
+    if (ctx->elem_type == FEASM_HEX27 && ctx->tab_nq == 27) return launch_elasticity<27, 27, FEASM_ELAST_WARPS>(ctx, p, e0, e1, d_kf, rs);
     if (ctx->elem_type == FEASM_HEX8 && ctx->tab_nq == 8) return launch_elasticity<8, 8, 16>(ctx, p, e0, e1, d_kf, rs);
     if (ctx->elem_type == FEASM_TET10 && ctx->tab_nq == 14) return launch_elasticity<10, 14, 16>(ctx, p, e0, e1, d_kf, rs);
     return feasm_fail(ctx, FEASM_ERR_ARG, "no elasticity kernel for this element type / quadrature order");
