@@ -2,7 +2,7 @@
 //   Fe_var[i](a) += JxW_face[qp] * (g_i * phi_face[a][qp])
 // of systems_of_equations_ex6.C:240-257 (a traction; with one variable, a Neumann flux), added to the Fe column of the
 // element's records after the volume kernel and before the element-level constraint pass — the place the reference
-// adds it.  SURVEY 8f rank 3; HEX8 / HEX27 (QUAD4 / QUAD9 sides).
+// adds it.  SURVEY 8f rank 3; HEX8 / HEX27 (QUAD4 / QUAD9 sides) and TET10 (TRI6 sides, tables for four sides).
 //
 // What FE::reinit(elem, side) computes (src/fe/fe_boundary.C:109-240) splits into a part that depends on the element
 // TYPE and the side number only — the side's Gauss rule, its map functions psi and the parent's shape functions at the
@@ -207,7 +207,8 @@ static int upload_side_list(feasm_ctx* ctx, int64_t n, const uint32_t* elems, co
                             int64_t* n_out) {
   std::vector<std::pair<uint32_t, uint8_t>> es((size_t)n);
   for (int64_t k = 0; k < n; ++k) {
-    if ((int64_t)elems[k] >= ctx->n_elem || sides[k] >= 6) return feasm_fail(ctx, FEASM_ERR_ARG, "side list: element or side out of range");
+    if ((int64_t)elems[k] >= ctx->n_elem || sides[k] >= (ctx->elem_type == FEASM_TET10 ? 4 : 6))
+      return feasm_fail(ctx, FEASM_ERR_ARG, "side list: element or side out of range");
     es[(size_t)k] = {elems[k], (uint8_t)(1u << sides[k])};
   }
   std::sort(es.begin(), es.end());
@@ -236,7 +237,6 @@ extern "C" int feasm_set_side_penalty(feasm_ctx* ctx, int64_t n, const uint32_t*
   ctx->n_pen_elems = 0;
   if (n <= 0) return FEASM_OK;
   if (!elems || !sides || (kind != FEASM_PENALTY_CONSTANT && kind != FEASM_PENALTY_EX4_EXACT)) return feasm_fail(ctx, FEASM_ERR_ARG, "bad side penalty arguments");
-  if (ctx->elem_type != FEASM_HEX8 && ctx->elem_type != FEASM_HEX27) return feasm_fail(ctx, FEASM_ERR_ARG, "side penalty: HEX8 / HEX27 sides only");
   const int rc = upload_side_list(ctx, n, elems, sides, &ctx->d_pen_elems, &ctx->d_pen_mask, &ctx->n_pen_elems);
   if (rc) return rc;
   ctx->penalty = penalty; ctx->pen_kind = kind; ctx->pen_value = value;
@@ -253,7 +253,6 @@ extern "C" int feasm_set_side_loads(feasm_ctx* ctx, int64_t n, const uint32_t* e
   ctx->n_side_elems = 0;
   if (n <= 0) return FEASM_OK;
   if (!elems || !sides || !g || n_g < 1 || n_g > 3) return feasm_fail(ctx, FEASM_ERR_ARG, "bad side load arguments");
-  if (ctx->elem_type != FEASM_HEX8 && ctx->elem_type != FEASM_HEX27) return feasm_fail(ctx, FEASM_ERR_ARG, "side loads: HEX8 / HEX27 sides only");
   const int rc = upload_side_list(ctx, n, elems, sides, &ctx->d_side_elems, &ctx->d_side_mask, &ctx->n_side_elems);
   if (rc) return rc;
   for (int i = 0; i < 3; ++i) ctx->side_g[i] = i < n_g ? g[i] : 0.;

@@ -133,9 +133,64 @@ bool feasm_make_tables(int elem_type, int qorder, FeasmTables& t, std::string& e
 // functions and their derivatives at those points (FEMap::init_face_shape_functions, fe_boundary.C:458-660), and for
 // each of the six sides the parent's shape functions at the side points carried into the parent's reference space
 // (FE::side_map, fe_boundary.C:347-400: sum over the side nodes of psi_i times the reference node).
+// TET10: TRI6 sides (Tet10::side_nodes_map, cell_tet10.C:37-43), the degree-5 triangle rule of QGauss(2, FIFTH)
+// (quadrature_gauss_2D.C:234-257 via dunavant_rule2: centroid, then the orbits (a,a), (a,1-2a), (1-2a,a)), the TRI6 map
+// functions (fe_lagrange_shape_2D.C:499-530, :920-975) and the parent's shapes at the side points carried into the
+// reference tet (reference nodes fe_abstract.C:488-501).  Tables are laid out for six sides (sides 4, 5 stay zero) so
+// the kernels address them like a hex's.
+static bool make_tet10_side_tables(int qorder, FeasmSideTables& t, std::string& err) {
+  if (qorder != 5) { err = "TET10 sides: only the FIFTH-order rule is built"; return false; }
+  static const int kSide[4][6] = {{0, 2, 1, 6, 5, 4}, {0, 1, 3, 4, 8, 7}, {1, 2, 3, 5, 9, 8}, {2, 0, 3, 6, 7, 9}};
+  static const double kRefNode[10][3] = {{0, 0, 0}, {1, 0, 0}, {0, 1, 0}, {0, 0, 1}, {.5, 0, 0}, {.5, .5, 0}, {0, .5, 0}, {0, 0, .5}, {.5, 0, .5}, {0, .5, .5}};
+  t.npe = 10; t.ns = 6; t.nqf = 7;
+  const double wts[3] = {9. / 80, 31. / 480 + std::sqrt(15.) / 2400, 31. / 480 - std::sqrt(15.) / 2400};
+  const double aa[3] = {0., 2. / 7 + std::sqrt(15.) / 21, 2. / 7 - std::sqrt(15.) / 21};
+  double pts[7][2];
+  t.qw.resize(7);
+  int q = 0;
+  pts[0][0] = 1. / 3; pts[0][1] = 1. / 3; t.qw[q++] = wts[0];
+  for (int o = 1; o < 3; ++o) {
+    pts[q][0] = aa[o]; pts[q][1] = aa[o]; t.qw[q++] = wts[o];
+    pts[q][0] = aa[o]; pts[q][1] = 1 - 2 * aa[o]; t.qw[q++] = wts[o];
+    pts[q][0] = 1 - 2 * aa[o]; pts[q][1] = aa[o]; t.qw[q++] = wts[o];
+  }
+  t.psi.resize(42); t.dxi.resize(42); t.deta.resize(42);
+  for (int p = 0; p < 7; ++p) {
+    const double z1 = pts[p][0], z2 = pts[p][1], z0 = 1. - z1 - z2;
+    const double z[3] = {z0, z1, z2}, dx[3] = {-1., 1., 0.}, de[3] = {-1., 0., 1.};
+    for (int v = 0; v < 3; ++v) {
+      t.psi[(size_t)v * 7 + p] = 2. * z[v] * (z[v] - 0.5);
+      t.dxi[(size_t)v * 7 + p] = (4. * z[v] - 1.) * dx[v];
+      t.deta[(size_t)v * 7 + p] = (4. * z[v] - 1.) * de[v];
+    }
+    const int eu[3] = {0, 1, 2}, ev[3] = {1, 2, 0};  // mid-side nodes 3, 4, 5: 4 z0 z1, 4 z1 z2, 4 z2 z0
+    for (int e = 0; e < 3; ++e) {
+      const int u = eu[e], v = ev[e];
+      t.psi[(size_t)(3 + e) * 7 + p] = 4. * z[u] * z[v];
+      t.dxi[(size_t)(3 + e) * 7 + p] = 4. * z[v] * dx[u] + 4. * z[u] * dx[v];
+      t.deta[(size_t)(3 + e) * 7 + p] = 4. * z[v] * de[u] + 4. * z[u] * de[v];
+    }
+  }
+  t.side_nodes.assign(6 * t.ns, 0);
+  t.phi.assign((size_t)6 * t.npe * t.nqf, 0.);
+  for (int s = 0; s < 4; ++s) {
+    for (int a = 0; a < 6; ++a) t.side_nodes[s * t.ns + a] = kSide[s][a];
+    for (int p = 0; p < 7; ++p) {
+      double r[3] = {0., 0., 0.};
+      for (int a = 0; a < 6; ++a)
+        for (int d = 0; d < 3; ++d) r[d] += t.psi[(size_t)a * 7 + p] * kRefNode[kSide[s][a]][d];
+      const double L[4] = {1. - r[0] - r[1] - r[2], r[0], r[1], r[2]};
+      for (int v = 0; v < 4; ++v) t.phi[((size_t)s * 10 + v) * 7 + p] = L[v] * (2. * L[v] - 1.);
+      for (int e = 0; e < 6; ++e) t.phi[((size_t)s * 10 + 4 + e) * 7 + p] = 4. * L[kTetEdge[e][0]] * L[kTetEdge[e][1]];
+    }
+  }
+  return true;
+}
+
 bool feasm_make_side_tables(int elem_type, int qorder, FeasmSideTables& t, std::string& err) {
   t = FeasmSideTables();
-  if (elem_type != FEASM_HEX8 && elem_type != FEASM_HEX27) { err = "side loads: HEX8 / HEX27 sides only"; return false; }
+  if (elem_type == FEASM_TET10) return make_tet10_side_tables(qorder, t, err);
+  if (elem_type != FEASM_HEX8 && elem_type != FEASM_HEX27) { err = "side terms: HEX8 / HEX27 / TET10 sides only"; return false; }
   const int deg = elem_type == FEASM_HEX8 ? 1 : 2;
   t.npe = elem_type;
   t.ns = deg == 1 ? 4 : 9;

@@ -343,25 +343,61 @@ static const int H8_SIDE[6][4] = {{0, 3, 2, 1}, {0, 1, 5, 4}, {1, 2, 6, 5}, {2, 
 static const int Q4_I0[4] = {0, 1, 1, 0}, Q4_I1[4] = {0, 0, 1, 1};
 static const int Q9_I0[9] = {0, 1, 1, 0, 2, 1, 2, 0, 2}, Q9_I1[9] = {0, 0, 1, 1, 0, 2, 1, 2, 2};
 
+// TET10: TRI6 sides (cell_tet10.C:37-43), the TRI6 Lagrange map (fe_lagrange_shape_2D.C:499-530, derivatives :920-975),
+// the 7-point degree-5 triangle rule (quadrature_gauss_2D.C:234-257 through QGauss::dunavant_rule2,
+// quadrature_gauss.C:195-265: centroid, then (a,a), (a,1-2a), (1-2a,a) per orbit), reference nodes fe_abstract.C:488-501.
+static const int T10_SIDE[4][6] = {{0, 2, 1, 6, 5, 4}, {0, 1, 3, 4, 8, 7}, {1, 2, 3, 5, 9, 8}, {2, 0, 3, 6, 7, 9}};
+static const double T10_REF[10][3] = {{0, 0, 0}, {1, 0, 0}, {0, 1, 0}, {0, 0, 1}, {.5, 0, 0}, {.5, .5, 0}, {0, .5, 0}, {0, 0, .5}, {.5, 0, .5}, {0, .5, .5}};
+
+static int tri_rule_fifth(double* pts /*7*2*/, double* w /*7*/) {
+  const double wts[3] = {9. / 80, 31. / 480 + std::sqrt(15.) / 2400, 31. / 480 - std::sqrt(15.) / 2400};
+  const double a[3] = {0., 2. / 7 + std::sqrt(15.) / 21, 2. / 7 - std::sqrt(15.) / 21};
+  int q = 0;
+  pts[0] = 1. / 3; pts[1] = 1. / 3; w[q++] = wts[0];
+  for (int p = 1; p < 3; ++p) {
+    pts[2 * q] = a[p]; pts[2 * q + 1] = a[p]; w[q++] = wts[p];
+    pts[2 * q] = a[p]; pts[2 * q + 1] = 1 - 2 * a[p]; w[q++] = wts[p];
+    pts[2 * q] = 1 - 2 * a[p]; pts[2 * q + 1] = a[p]; w[q++] = wts[p];
+  }
+  return q;
+}
+
+static void tri6_shape(int i, double xi, double eta, double& v, double& dxi, double& deta) {
+  const double z1 = xi, z2 = eta, z0 = 1. - z1 - z2;
+  const double d0x = -1., d1x = 1., d2x = 0., d0e = -1., d1e = 0., d2e = 1.;
+  switch (i) {
+    case 0: v = 2. * z0 * (z0 - 0.5); dxi = (4. * z0 - 1.) * d0x; deta = (4. * z0 - 1.) * d0e; break;
+    case 1: v = 2. * z1 * (z1 - 0.5); dxi = (4. * z1 - 1.) * d1x; deta = (4. * z1 - 1.) * d1e; break;
+    case 2: v = 2. * z2 * (z2 - 0.5); dxi = (4. * z2 - 1.) * d2x; deta = (4. * z2 - 1.) * d2e; break;
+    case 3: v = 4. * z0 * z1; dxi = 4. * z1 * d0x + 4. * z0 * d1x; deta = 4. * z1 * d0e + 4. * z0 * d1e; break;
+    case 4: v = 4. * z1 * z2; dxi = 4. * z2 * d1x + 4. * z1 * d2x; deta = 4. * z2 * d1e + 4. * z1 * d2e; break;
+    default: v = 4. * z2 * z0; dxi = 4. * z2 * d0x + 4 * z0 * d2x; deta = 4. * z2 * d0e + 4 * z0 * d2e; break;
+  }
+}
+
 int side_nodes(int elem_type, int side, int* nodes) {
   if (side < 0 || side >= 6) return 0;
   if (elem_type == ORC_HEX27) { for (int i = 0; i < 9; ++i) nodes[i] = H27_SIDE[side][i]; return 9; }
   if (elem_type == ORC_HEX8) { for (int i = 0; i < 4; ++i) nodes[i] = H8_SIDE[side][i]; return 4; }
+  if (elem_type == ORC_TET10 && side < 4) { for (int i = 0; i < 6; ++i) nodes[i] = T10_SIDE[side][i]; return 6; }
   return 0;
 }
 
 int side_reinit(int elem_type, const double* X, int side, int qorder, SideData& sd) {
   int sn[9];
   const int ns = side_nodes(elem_type, side, sn);
-  if (!ns) { set_error("side_reinit: HEX8/HEX27 sides only"); return -1; }
-  const bool q2 = ns == 9;
+  if (!ns) { set_error("side_reinit: HEX8/HEX27/TET10 sides only"); return -1; }
+  const bool q2 = ns == 9, tri = ns == 6;
   double gx[3], gw[3];
-  const int np = gauss_1d(qorder, gx, gw);
-  if (!np) { set_error("unsupported side quadrature order"); return -1; }
-  const int nqf = np * np;
+  const int np = tri ? 0 : gauss_1d(qorder, gx, gw);
+  if (tri && qorder != 5 && qorder != 0) { set_error("TRI6 sides: QGauss FIFTH only"); return -1; }
+  if (!tri && !np) { set_error("unsupported side quadrature order"); return -1; }
+  const int nqf = tri ? 7 : np * np;
   sd.nqf = nqf;
   std::vector<double> pts(2 * nqf), qw(nqf);
-  {
+  if (tri) {
+    tri_rule_fifth(pts.data(), qw.data());
+  } else {
     int q = 0;
     for (int j = 0; j < np; j++)
       for (int i = 0; i < np; i++) {
@@ -376,7 +412,9 @@ int side_reinit(int elem_type, const double* X, int side, int qorder, SideData& 
   for (int i = 0; i < ns; ++i)
     for (int p = 0; p < nqf; ++p) {
       const double xi = pts[2 * p], eta = pts[2 * p + 1];
-      if (q2) {
+      if (tri) {
+        tri6_shape(i, xi, eta, psi[i * nqf + p], dxi[i * nqf + p], deta[i * nqf + p]);
+      } else if (q2) {
         psi[i * nqf + p] = quad(Q9_I0[i], xi) * quad(Q9_I1[i], eta);
         dxi[i * nqf + p] = dquad(Q9_I0[i], xi) * quad(Q9_I1[i], eta);
         deta[i * nqf + p] = quad(Q9_I0[i], xi) * dquad(Q9_I1[i], eta);
@@ -419,7 +457,9 @@ int side_reinit(int elem_type, const double* X, int side, int qorder, SideData& 
   sd.ref.assign(3 * nqf, 0.);
   for (int i = 0; i < ns; ++i) {
     const int a = sn[i];
-    const double node[3] = {REF[q2 ? H27_I0[a] : H8_I0[a]], REF[q2 ? H27_I1[a] : H8_I1[a]], REF[q2 ? H27_I2[a] : H8_I2[a]]};
+    double node[3];
+    if (tri) { node[0] = T10_REF[a][0]; node[1] = T10_REF[a][1]; node[2] = T10_REF[a][2]; }
+    else { node[0] = REF[q2 ? H27_I0[a] : H8_I0[a]]; node[1] = REF[q2 ? H27_I1[a] : H8_I1[a]]; node[2] = REF[q2 ? H27_I2[a] : H8_I2[a]]; }
     for (int p = 0; p < nqf; ++p)
       for (int d = 0; d < 3; ++d) sd.ref[3 * p + d] += psi[i * nqf + p] * node[d];
   }

@@ -79,7 +79,7 @@ def test_side_loads_reject_bad_input():
     m, s = make_case(10, (2, 2, 1))
     ctx = make_ctx(m, s)
     with pytest.raises(F.FeasmError):
-        ctx.set_side_loads([0], [0], [1.0])  # TET10 sides are not built
+        ctx.set_side_loads([0], [4], [1.0])  # a tet has sides 0..3
     ctx.close()
     m, s = make_case(8, (2, 2, 2))
     ctx = make_ctx(m, s)
@@ -152,3 +152,43 @@ def test_penalty_constant_value_on_every_variable():
     K, Fv = ctx.element_matrices(p, constrained=False)
     assert dense_parity_error(K, Ko) < PARITY_TOL
     assert vec_parity_error(Fv.ravel(), Fo.ravel()) < PARITY_TOL
+
+
+@pytest.mark.parametrize("skew", [None, (1, 0.02, 5)])
+def test_tet10_side_load_and_penalty(skew):
+    """TRI6 sides of TET10 (QGauss(2, FIFTH), 7 points): a Neumann flux on box face 2 and the ex3 penalty term on the other
+    five faces, element vectors / matrices and the assembled system against the oracle."""
+    from libmesh_b200 import capi as F
+    from oracle import oracle as O
+    from test_oracle_sides import tet_boundary_sides
+
+    m = O.Mesh(O.TET10, 3, 2, 2, bounds=(-1, 1, -1, 1, -1, 1))
+    if skew:
+        m.skew(*skew)
+    s = O.System(m, 1)
+    le, ls = tet_boundary_sides(m, 2)
+    pe, ps = zip(*(tet_boundary_sides(m, b) for b in (0, 1, 3, 4, 5)))
+    pe, ps = np.concatenate(pe), np.concatenate(ps)
+    s.set_side_loads(le, ls, [1.7])
+    s.set_side_penalty(pe, ps, penalty=1e10, kind=1)
+    s.build_sparsity()
+    xyz, conn, _ = m.arrays()
+    ctx = F.Context(0)
+    ctx.set_mesh(F.TET10, xyz, conn)
+    ctx.set_dofs(s.dofs()[0], s.n_dofs)
+    ctx.build_pattern()
+    ctx.set_side_loads(le, ls, [1.7])
+    ctx.set_side_penalty(pe, ps, penalty=1e10, kind=F.PENALTY_EX4_EXACT)
+    f_tab, _ = s.forcing_at_qps(5)
+    p = F.make_params(F.POISSON, 5, F.FORCING_TABULATED, f_host=f_tab)
+    Ko, Fo = s.element_matrices(O.POISSON_EX4, constrained=False, qorder=5, forcing=O.FORCING_TABULATED, f_tab=f_tab)
+    K, Fv = ctx.element_matrices(p, constrained=False)
+    assert dense_parity_error(K, Ko) < PARITY_TOL
+    assert vec_parity_error(Fv.ravel(), Fo.ravel()) < PARITY_TOL
+    vo, ro, _ = s.assemble(O.POISSON_EX4, qorder=5, forcing=O.FORCING_TABULATED, f_tab=f_tab)
+    ctx.assemble(p)
+    v, r = ctx.get_values()
+    assert csr_parity_error(v, vo, s.sparsity()[0]) < PARITY_TOL
+    assert vec_parity_error(r, ro) < PARITY_TOL
+    with pytest.raises(F.FeasmError):
+        ctx.set_side_loads([0], [4], [1.0])  # a tet has four sides

@@ -158,3 +158,75 @@ def test_penalty_enforces_the_boundary_values_like_ex3():
     # boundary nodes carry the L2 projection of the exact solution onto the Q2 faces: O(h^3); 0.044 at h = 1
     assert errs[0][0] < 0.06 and errs[1][0] < errs[0][0] / 5
     assert errs[1][1] < errs[0][1] / 4
+
+
+# ---- TET10 sides (TRI6, the 7-point degree-5 rule) --------------------------------------------------------------------
+def test_tri_side_rule_is_the_degree_5_dunavant_rule():
+    """quadrature_gauss_2D.C:234-257: 7 points, weights sum to the reference triangle's area, exact for x^a y^b, a+b <= 5
+    (tests/quadrature/quadrature_test.C checks monomials the same way).  Seen through side 0 of the reference tet, whose
+    side map is affine: side (xi, eta) -> parent (eta, xi, 0)."""
+    from math import factorial
+    X = np.array([[0, 0, 0], [1, 0, 0], [0, 1, 0], [0, 0, 1], [.5, 0, 0], [.5, .5, 0], [0, .5, 0], [0, 0, .5], [.5, 0, .5], [0, .5, .5]], dtype=float)
+    d = O.side_reinit(O.TET10, X, 0, 5)
+    assert d["JxW"].shape == (7,) and abs(d["JxW"].sum() - 0.5) < 1e-15
+    assert np.abs(d["xyz"][:, 2]).max() == 0.0 and np.abs(d["normals"] - [0, 0, -1]).max() < 1e-15   # outward: -z
+    assert np.abs(d["xyz"][0] - [1 / 3, 1 / 3, 0]).max() < 1e-15                                        # centroid first
+    for a in range(6):
+        for b in range(6 - a):
+            exact = factorial(a) * factorial(b) / factorial(a + b + 2)
+            assert abs((d["JxW"] * d["xyz"][:, 0] ** a * d["xyz"][:, 1] ** b).sum() - exact) < 1e-15
+
+
+@pytest.mark.parametrize("skew", [None, "perturbed"])
+def test_tet_side_shapes_and_closed_surface(skew):
+    """fe_side_test.C on TET10: side shapes reproduce linear and quadratic functions of the side points; and the
+    divergence theorem over the four sides ties JxW_face and the normals to the volume map."""
+    m = _mesh(O.TET10, (2, 1, 1), skew)
+    xyz, conn, _ = m.arrays()
+    lin = lambda p: p[..., 0] + 0.25 * p[..., 1] + 0.0625 * p[..., 2]
+    quad = lambda p: p[..., 0] ** 2 + 0.5 * p[..., 1] ** 2 + 0.25 * p[..., 2] ** 2 + 0.125 * p[..., 0] * p[..., 1]
+    pts, w = O.quadrature(O.TET10, 5)
+    for e in range(0, m.n_elem, 3):
+        X = xyz[conn[e]]
+        vol = O.fe_reinit(O.TET10, X, pts, w)["JxW"].sum()
+        n_int, flux = np.zeros(3), 0.0
+        for s in range(4):
+            d = O.side_reinit(O.TET10, X, s, 5)
+            assert d["phi"].shape == (10, 7)
+            assert np.abs(d["phi"].sum(0) - 1).max() < 1e-14
+            assert np.abs(d["phi"].T @ X - d["xyz"]).max() < 1e-14
+            assert np.abs(d["phi"].T @ lin(X) - lin(d["xyz"])).max() < 1e-13
+            if skew is None:
+                assert np.abs(d["phi"].T @ quad(X) - quad(d["xyz"])).max() < 1e-13
+            n_int += (d["JxW"][:, None] * d["normals"]).sum(0)
+            flux += (d["JxW"] * (d["xyz"] * d["normals"]).sum(1)).sum()
+        assert np.abs(n_int).max() < 1e-13
+        assert abs(flux - 3 * vol) < 1e-12 * max(1.0, abs(vol))
+
+
+def tet_boundary_sides(m, bid):
+    """(element, side) pairs of a TET10 cube whose six side nodes all lie on box face `bid` (BoundaryInfo of build_cube)."""
+    sides = [[0, 2, 1, 6, 5, 4], [0, 1, 3, 4, 8, 7], [1, 2, 3, 5, 9, 8], [2, 0, 3, 6, 7, 9]]  # cell_tet10.C:37-43
+    _, conn, mask = m.arrays()
+    on = (mask >> bid) & 1
+    es, ss = [], []
+    for s, nodes in enumerate(sides):
+        hit = on[conn[:, nodes]].all(axis=1)
+        es.append(np.nonzero(hit)[0])
+        ss.append(np.full(hit.sum(), s))
+    e, sd = np.concatenate(es), np.concatenate(ss)
+    o = np.argsort(e, kind="stable")
+    return e[o].astype(np.uint32), sd[o].astype(np.uint8)
+
+
+def test_tet_traction_face_area():
+    m = O.Mesh(O.TET10, 3, 2, 2, bounds=(0, 1, 0, 0.3, 0, 0.1))
+    e, sd = tet_boundary_sides(m, 2)
+    assert len(e) == 4 * 2 * 2                       # four tets of each boundary cell face
+    xyz, conn, _ = m.arrays()
+    area = sum(O.side_reinit(O.TET10, xyz[conn[ee]], int(s), 5)["JxW"].sum() for ee, s in zip(e, sd))
+    assert abs(area - 0.03) < 1e-15
+    s0, s1 = O.System(m, 1), O.System(m, 1)
+    s1.set_side_loads(e, sd, [1.7])
+    (_, F0), (_, F1) = (s.element_matrices(O.POISSON_EX4, constrained=False) for s in (s0, s1))
+    assert abs((F1 - F0).sum() - 1.7 * 0.03) < 1e-15
