@@ -174,6 +174,14 @@ int feasm_vector_mult_host(feasm_ctx* ctx, const double* x, double* y); /* same 
 int feasm_cg_solve(feasm_ctx* ctx, double rel_tol, int max_its, const double* x0, double* x, int* iterations,
                    double* rel_residual);
 
+/* Residual without the global matrix: R = K(u) u - F summed straight from the constrained element
+ * matrices, r_i = sum over the (element, local dof) pairs of row i of ( Ke(a,:) . u_e - Fe(a) ) in element order — the
+ * work of NonlinearImplicitSystem::ComputeResidual::residual(X, R, S) (include/systems/nonlinear_implicit_system.h:
+ * 90-101) / FEMSystem::assembly(get_residual = true, get_jacobian = false) (src/systems/fem_system.C:875) for the
+ * linear problems of this library: no CSR values are written or read.  d_u, d_r: device vectors of n_rows entries
+ * (feasm_vec_alloc).  Runs the element phase, then one row-parallel pass over the element records.  One rank. */
+int feasm_residual(feasm_ctx* ctx, const feasm_params* params, const double* d_u, double* d_r);
+
 /* ---- device vectors: what a NumericVector back-end needs (numeric_vector.h:119-847; shim/gpu_numeric_vector.h) -- */
 /* Blocking calls on feasm_stream.  d_* are device pointers from feasm_vec_alloc (or feasm_device_rhs). */
 #define FEASM_COPY_H2D 0

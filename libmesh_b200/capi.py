@@ -33,7 +33,7 @@ SYMBOLS = [
     "feasm_vec_alloc", "feasm_vec_free", "feasm_vec_copy", "feasm_vec_fill", "feasm_vec_axpy", "feasm_vec_pointwise",
     "feasm_vec_reduce", "feasm_vec_set_entry",
     "feasm_generate_cube", "feasm_distribute_dofs_device", "feasm_generate_dirichlet", "feasm_get_mesh", "feasm_get_dofs",
-    "feasm_get_constraints", "feasm_set_side_penalty",
+    "feasm_get_constraints", "feasm_set_side_penalty", "feasm_residual",
 ]
 
 
@@ -118,6 +118,7 @@ def lib():
         "feasm_get_dofs": (i32, [vp, vp, vp]),
         "feasm_get_constraints": (i32, [vp, vp, vp]),
         "feasm_set_side_penalty": (i32, [vp, i64, vp, vp, C.c_double, i32, C.c_double]),
+        "feasm_residual": (i32, [vp, C.POINTER(Params), vp, vp]),
     }
     for name, (res, args) in sig.items():
         fn = getattr(L, name)
@@ -366,6 +367,21 @@ class Context:
     def vector_mult(self, d_x, d_y):
         """y = A x with device pointers (ints) of n_rows doubles."""
         self._ck(self.L.feasm_vector_mult(self.h, C.c_void_p(d_x), C.c_void_p(d_y)))
+
+    def residual_host(self, params, u):
+        """R = K(u) u - F from the element records (feasm_residual), host arrays in and out."""
+        L, n = self.L, self.n_rows
+        uc = _c(u, np.float64)
+        out = np.empty(n, np.float64)
+        d_u, d_r = L.feasm_vec_alloc(self.h, n), L.feasm_vec_alloc(self.h, n)
+        try:
+            self._ck(L.feasm_vec_copy(self.h, 0, C.c_void_p(d_u), _p(uc), n))
+            self._ck(L.feasm_residual(self.h, C.byref(params), C.c_void_p(d_u), C.c_void_p(d_r)))
+            self._ck(L.feasm_vec_copy(self.h, 1, _p(out), C.c_void_p(d_r), n))
+        finally:
+            L.feasm_vec_free(self.h, C.c_void_p(d_u))
+            L.feasm_vec_free(self.h, C.c_void_p(d_r))
+        return out
 
     def vector_mult_host(self, x):
         xc = _c(x, np.float64)

@@ -355,6 +355,29 @@ static int assemble_impl(feasm_ctx* ctx, const feasm_params* params, int mode) {
   return FEASM_OK;
 }
 
+int feasm_residual(feasm_ctx* ctx, const feasm_params* params, const double* d_u, double* d_r) {
+  if (!ctx || !params) return FEASM_ERR_ARG;
+  if (!d_u || !d_r) return feasm_fail(ctx, FEASM_ERR_ARG, "null vector");
+  if (ctx->d_gid || ctx->n_owned != ctx->n_rows) return feasm_fail(ctx, FEASM_ERR_STATE, "residual: one rank per system in this version");
+  FEASM_CUDA(ctx, cudaSetDevice(ctx->device));
+  int rc = feasm_prepare(ctx);
+  if (rc) return rc;
+  rc = ensure_tables(ctx, resolve_qorder(ctx, *params));
+  if (rc) return rc;
+  const double* d_f = nullptr;
+  rc = resolve_forcing(ctx, *params, ctx->tab_nq, &d_f);
+  if (rc) return rc;
+  FEASM_CUDA(ctx, cudaMemsetAsync(ctx->d_flags, 0, 2 * sizeof(int), ctx->stream));
+  if (!ctx->elem_flag_valid) {
+    rc = feasm_launch_elem_flags(ctx);
+    if (rc) return rc;
+  }
+  const int rs = feasm_recb(ctx->nd, ctx->pos_bytes) / 8;
+  rc = feasm_launch_element_kernel(ctx, *params, d_f, 0, ctx->n_elem, ctx->d_kf, rs, params->constrain);
+  if (rc) return rc;
+  return feasm_launch_row_residual(ctx, d_u, d_r);
+}
+
 int feasm_assemble(feasm_ctx* ctx, const feasm_params* params) { return assemble_impl(ctx, params, 0); }
 int feasm_assemble_begin(feasm_ctx* ctx, const feasm_params* params) { return assemble_impl(ctx, params, 1); }
 

@@ -167,6 +167,7 @@ int feasm_launch_elem_flags(feasm_ctx* ctx);
 int feasm_launch_side_loads(feasm_ctx* ctx, int qorder, int64_t e0, int64_t e1, double* d_kf, int rs);
 // d_row_list == nullptr: every row; else the n_list rows listed
 int feasm_launch_row_reduce(feasm_ctx* ctx, const uint32_t* d_row_list, int64_t n_list, cudaStream_t stream, int64_t row0 = 0);
+int feasm_launch_row_residual(feasm_ctx* ctx, const double* d_u, double* d_r);
 int feasm_launch_pack(feasm_ctx* ctx);
 int feasm_launch_unpack(feasm_ctx* ctx);
 int feasm_launch_add_matrix(feasm_ctx* ctx, const double* d_dm, const uint32_t* d_rows, int nr, const uint32_t* d_cols,

@@ -106,6 +106,30 @@ k_row_reduce_group(const uint64_t* __restrict__ row_ptr, const uint64_t* __restr
   }
 }
 
+// Residual without the global matrix: r_i = sum over the (e, a) pairs of row i of ( Ke(a,:) . u_e - Fe(a) ), straight from
+// the element records (the rows of the constrained element matrices), in element order — what a
+// NonlinearImplicitSystem::ComputeResidual / FEMSystem::assembly(get_residual = true, get_jacobian = false) computes
+// for this linear problem, R = K(u) u - F.  One warp per row; lanes stride over the element's dofs, fixed shuffle tree.
+__global__ void k_row_residual(const uint64_t* __restrict__ inc_ptr, const uint32_t* __restrict__ inc, const unsigned char* __restrict__ rec,
+                               int recb, const uint32_t* __restrict__ elem_dofs, int nd, const double* __restrict__ u, int64_t n_rows,
+                               double* __restrict__ r) {
+  const int lane = threadIdx.x & 31;
+  const int64_t row = (blockIdx.x * (int64_t)blockDim.x + threadIdx.x) >> 5;
+  if (row >= n_rows) return;
+  double acc = 0.;
+  for (uint64_t k = inc_ptr[row]; k < inc_ptr[row + 1]; ++k) {
+    const uint32_t id = inc[k];
+    const double* R = reinterpret_cast<const double*>(rec + (uint64_t)id * (uint32_t)recb);
+    const uint32_t* dofs = elem_dofs + (uint64_t)(id / (uint32_t)nd) * nd;
+    double s = 0.;
+    for (int b = lane; b < nd; b += 32) s += R[b] * u[dofs[b]];
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) s += __shfl_xor_sync(0xffffffffu, s, o);
+    acc += s - R[nd];
+  }
+  if (lane == 0) r[row] = acc;
+}
+
 template <typename PosT>
 __global__ void k_row_reduce_global(const uint64_t* __restrict__ row_ptr, const uint64_t* __restrict__ inc_ptr,
                                     const uint32_t* __restrict__ inc, const unsigned char* __restrict__ rec, int nd,
@@ -251,6 +275,16 @@ int launch_row_reduce(feasm_ctx* ctx, const uint32_t* d_row_list, int64_t n_list
 int feasm_launch_row_reduce(feasm_ctx* ctx, const uint32_t* d_row_list, int64_t n_list, cudaStream_t stream, int64_t row0) {
   if (ctx->pos_bytes == 1) return launch_row_reduce<uint8_t>(ctx, d_row_list, n_list, stream, row0);
   return launch_row_reduce<uint16_t>(ctx, d_row_list, n_list, stream, row0);
+}
+
+int feasm_launch_row_residual(feasm_ctx* ctx, const double* d_u, double* d_r) {
+  const int recb = feasm_recb(ctx->nd, ctx->pos_bytes);
+  const unsigned grid = (unsigned)((ctx->n_rows * 32 + 255) / 256);
+  if (grid)
+    k_row_residual<<<grid, 256, 0, ctx->stream>>>(ctx->d_inc_ptr, ctx->d_inc, reinterpret_cast<const unsigned char*>(ctx->d_kf), recb,
+                                                  ctx->d_elem_dofs, ctx->nd, d_u, ctx->n_rows, d_r);
+  FEASM_CUDA(ctx, cudaGetLastError());
+  return FEASM_OK;
 }
 
 int feasm_launch_elem_flags(feasm_ctx* ctx) {

@@ -86,3 +86,47 @@ def test_vector_mult_host_variant():
     y = ctx.vector_mult_host(x)
     assert np.abs(y - A @ x).max() <= 1e-13 * np.abs(A @ x).max()
     ctx.close()
+
+
+@pytest.mark.parametrize("etype,dims,problem,nv", [(27, (4, 3, 3), "poisson", 1), (8, (5, 4, 3), "poisson", 1), (10, (2, 2, 2), "poisson", 1),
+                                                   (27, (3, 2, 2), "elasticity", 3)])
+def test_residual_without_the_global_matrix(etype, dims, problem, nv):
+    """feasm_residual: R = K(u) u - F from the constrained element records, against A u - b of the oracle's assembled
+    system for a random u (scale per row: |A| |u| + |b|)."""
+    import scipy.sparse as sp
+
+    from libmesh_b200 import capi as F
+    from oracle import oracle as O
+
+    elast = problem == "elasticity"
+    m = O.Mesh(etype, *dims, bounds=(0, 1, 0, 0.3, 0, 0.1) if elast else (-1, 1, -1, 1, -1, 1))
+    m.skew(1, 0.004 if elast else 0.02, 3)
+    s = O.System(m, nv)
+    s.add_dirichlet((4,), 1) if elast else s.add_dirichlet((0, 1, 2, 3, 4, 5), 0)
+    s.build_sparsity()
+    xyz, conn, _ = m.arrays()
+    cd, cv = s.constraints()
+    ctx = F.Context(0)
+    ctx.set_mesh(etype, xyz, conn)
+    ctx.set_dofs(s.dofs()[0], s.n_dofs, n_vars=nv)
+    ctx.set_constraints(cd, cv)
+    ctx.build_pattern()
+    if elast:
+        vo, ro, _ = s.assemble(O.ELASTICITY_EX6)
+        p = F.make_params(F.ELASTICITY, 0, F.FORCING_NONE, F.CONSTRAIN_HOMOGENEOUS)
+    else:
+        q = 3 if etype == 8 else 5
+        f_tab, _ = s.forcing_at_qps(q)
+        vo, ro, _ = s.assemble(O.POISSON_EX4, qorder=q, forcing=O.FORCING_TABULATED, f_tab=f_tab)
+        p = F.make_params(F.POISSON, q, F.FORCING_TABULATED, f_host=f_tab)
+    rp, ci = s.sparsity()
+    A = sp.csr_matrix((vo, ci.astype(np.int64), rp.astype(np.int64)), shape=(s.n_dofs, s.n_dofs))
+    u = np.random.default_rng(7).uniform(-1, 1, s.n_dofs)
+    want = A @ u - ro
+    scale = abs(A) @ np.abs(u) + np.abs(ro)
+    got = ctx.residual_host(p, u)
+    assert np.max(np.abs(got - want) / np.maximum(scale, 1e-300)) < 1e-12
+    # at the solution of the linear system the residual vanishes
+    import scipy.sparse.linalg as spla
+    us = spla.spsolve(A.tocsc(), ro)
+    assert np.max(np.abs(ctx.residual_host(p, us)) / np.maximum(abs(A) @ np.abs(us) + np.abs(ro), 1e-300)) < 1e-10
