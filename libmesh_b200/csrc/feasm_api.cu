@@ -39,6 +39,8 @@ void drop_maps(feasm_ctx* ctx) {
   release(ctx->d_inc_ptr);
   release(ctx->d_inc);
   release(ctx->d_kf);
+  release(ctx->d_y);
+  ctx->d_y_cap = 0;
 }
 
 int ensure_tables(feasm_ctx* ctx, int qorder) {
@@ -141,7 +143,7 @@ void feasm_destroy(feasm_ctx* ctx) {
   release(ctx->d_con_flag); release(ctx->d_con_val); release(ctx->d_row_ptr); release(ctx->d_col_idx);
   release(ctx->d_values); release(ctx->d_rhs); release(ctx->d_flags); release(ctx->d_tab); release(ctx->d_f);
   release(ctx->d_side_elems); release(ctx->d_side_mask); release(ctx->d_side_tab); release(ctx->d_side_nodes);
-  release(ctx->d_pen_elems); release(ctx->d_pen_mask);
+  release(ctx->d_pen_elems); release(ctx->d_pen_mask); release(ctx->d_y);
   release(ctx->d_send_slots); release(ctx->d_recv_slots); release(ctx->d_send_buf); release(ctx->d_recv_buf);
   for (auto& ev : ctx->ev) if (ev) cudaEventDestroy(ev);
   cudaStreamDestroy(ctx->stream);

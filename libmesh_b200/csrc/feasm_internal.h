@@ -100,6 +100,8 @@ struct feasm_ctx {
 
   // element buffers
   double* d_kf = nullptr;  // element records [n_elem][nd][feasm_recb bytes]
+  double* d_y = nullptr;   // feasm_residual: y(e,a) = Ke(a,:) . u_e - Fe(a), [n_elem][nd]
+  size_t d_y_cap = 0;
   int* d_flags = nullptr;  // [0] degenerate count, [1] pattern misses
 
   // tables on device, keyed by quadrature order
