@@ -349,3 +349,24 @@ def test_affine_tensor_path_matches_the_quadrature_loop(name, etype, dims, skew,
     assert dense_parity_error(K, Ko) < PARITY_TOL
     assert vec_parity_error(Fe.ravel(), Fo.ravel()) < PARITY_TOL
     ctx.close()
+
+
+@pytest.mark.parametrize("etype,dims,qorder", [(8, (3, 3, 3), 3), (10, (2, 1, 1), 5)])
+def test_packed_element_kernels_on_ragged_ranges(etype, dims, qorder):
+    """HEX8 (four per warp) and TET10 (two per warp): element ranges whose length and start are not multiples of the pack
+    width — short last groups, spare slots — against the oracle, FD forcing in the kernel included."""
+    F, O = _mods()
+    m, s = make_case(etype, dims, skew=(1, 0.03, 11))
+    ctx = make_ctx(m, s)
+    f_tab, _ = s.forcing_at_qps(qorder)
+    p = F.make_params(F.POISSON, qorder, F.FORCING_TABULATED, f_host=f_tab)
+    Ko, Fo = s.element_matrices(O.POISSON_EX4, constrained=True, qorder=qorder, forcing=O.FORCING_TABULATED, f_tab=f_tab)
+    for e0, e1 in ((0, 1), (1, 4), (3, 8), (m.n_elem - 5, m.n_elem), (0, m.n_elem)):
+        K, Fv = ctx.element_matrices(p, e0=e0, e1=e1, constrained=True)
+        assert dense_parity_error(K, Ko[e0:e1]) < PARITY_TOL, (e0, e1)
+        assert vec_parity_error(Fv.ravel(), Fo[e0:e1].ravel()) < PARITY_TOL, (e0, e1)
+    pf = F.make_params(F.POISSON, qorder, F.FORCING_EX4_FD)
+    Kf, Ff = ctx.element_matrices(pf, e0=1, e1=m.n_elem, constrained=False)
+    _, Fo_fd = s.element_matrices(O.POISSON_EX4, constrained=False, qorder=qorder)
+    # FD forcing: one ulp of sin/cos is ~1e-10 in f (the difference quotient divides by 1e-6), times JxW ~ 0.3 on this mesh
+    assert np.abs(Ff - Fo_fd[1:]).max() <= 1e-10
