@@ -773,9 +773,19 @@ __global__ void k_constrain_list(const uint32_t* __restrict__ list, int n_list, 
   const int ldr = feasm_ldr(nd), h = ldr >> 1;
   double* S = s_k + (size_t)warp * nd * ldr;
   double* K = kf + (uint64_t)(e - e0) * nd * rs;
-  for (int t = lane; t < nd * h; t += 32) {
-    const int row = t / h, c = t % h;
-    *reinterpret_cast<double2*>(S + row * ldr + 2 * c) = *reinterpret_cast<const double2*>(K + (size_t)row * rs + 2 * c);
+  // eight 16 B loads in flight per lane (the rolled loop waited for every load before the next went out)
+  for (int t0 = 0; t0 < nd * h; t0 += 256) {
+    double2 v[8];
+#pragma unroll
+    for (int j = 0; j < 8; ++j) {
+      const int t = t0 + 32 * j + lane;
+      if (t < nd * h) v[j] = *reinterpret_cast<const double2*>(K + (size_t)(t / h) * rs + 2 * (t % h));
+    }
+#pragma unroll
+    for (int j = 0; j < 8; ++j) {
+      const int t = t0 + 32 * j + lane;
+      if (t < nd * h) *reinterpret_cast<double2*>(S + (t / h) * ldr + 2 * (t % h)) = v[j];
+    }
   }
   constrain_element(S, ldr, nd, con.elem_dofs + (uint64_t)e * nd, con.con_flag, con.con_val, con.mode, lane);
   for (int t = lane; t < nd * h; t += 32) {
