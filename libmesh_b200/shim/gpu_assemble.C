@@ -26,7 +26,8 @@ std::unordered_map<const void*, Uploaded>& cache() {
 }
 }  // namespace
 
-void assemble(EquationSystems& es, const std::string& system_name, const feasm_params& params, const SideLoad* side_load) {
+void assemble(EquationSystems& es, const std::string& system_name, const feasm_params& params, const SideLoad* side_load,
+              const SidePenalty* side_penalty) {
   LinearImplicitSystem& system = es.get_system<LinearImplicitSystem>(system_name);
   auto* A = dynamic_cast<GpuSparseMatrix<Number>*>(system.matrix);
   if (!A) libmesh_error_msg("feasm_libmesh::assemble: system.matrix is not a GpuSparseMatrix; add it with "
@@ -96,6 +97,26 @@ void assemble(EquationSystems& es, const std::string& system_name, const feasm_p
     }
     A->check(feasm_set_side_loads(ctx, (int64_t)side_elems.size(), side_elems.data(), side_ids.data(),
                                   side_load ? side_load->g.data() : nullptr, side_load ? (int)side_load->g.size() : 0));
+  }
+
+  // ---- penalty sides: the `if (elem->neighbor_ptr(side) == nullptr)` loop of introduction_ex3.C:403-455 ----
+  {
+    std::vector<uint32_t> pen_elems;
+    std::vector<uint8_t> pen_sides;
+    if (side_penalty) {
+      uint32_t le = 0;
+      for (const Elem* elem : mesh.active_local_element_ptr_range()) {
+        for (auto side : elem->side_index_range())
+          if (elem->neighbor_ptr(side) == nullptr) {
+            pen_elems.push_back(le);
+            pen_sides.push_back((uint8_t)side);
+          }
+        ++le;
+      }
+    }
+    A->check(feasm_set_side_penalty(ctx, (int64_t)pen_elems.size(), pen_elems.data(), pen_sides.data(),
+                                    side_penalty ? side_penalty->penalty : 0., side_penalty ? side_penalty->kind : 0,
+                                    side_penalty ? side_penalty->value : 0.));
   }
 
   // ---- Dirichlet constraints: DofMap::is_constrained_dof + primal constraint values (empty constraint rows) ----

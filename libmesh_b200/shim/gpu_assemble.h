@@ -26,11 +26,19 @@ struct SideLoad {
   libMesh::boundary_id_type id;
   std::vector<libMesh::Real> g;
 };
+// Dirichlet data by the penalty method on every side without a neighbour (introduction_ex3.C:386-455):
+//   Ke(i,j) += JxW_face*penalty*phi_face[i]*phi_face[j],  Fe(i) += JxW_face*penalty*value*phi_face[i];
+// kind = FEASM_PENALTY_CONSTANT (value) or FEASM_PENALTY_EX4_EXACT (the exact solution at the side point).
+struct SidePenalty {
+  libMesh::Real penalty;
+  int kind;
+  libMesh::Real value;
+};
 // examples/systems_of_equations/systems_of_equations_ex6/systems_of_equations_ex6.C:156-264: volume terms and the
 // traction (0, 0, -1) on BOUNDARY_ID_MAX_X (= 2, :79)
 void assemble_elasticity_ex6(libMesh::EquationSystems& es, const std::string& system_name);
 // generic entry: feasm_params as in include/feasm.h; side_load may be null
 void assemble(libMesh::EquationSystems& es, const std::string& system_name, const feasm_params& params,
-              const SideLoad* side_load = nullptr);
+              const SideLoad* side_load = nullptr, const SidePenalty* side_penalty = nullptr);
 }  // namespace feasm_libmesh
 #endif

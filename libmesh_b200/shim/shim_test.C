@@ -277,6 +277,38 @@ int main() {
     for (int64_t r = 0; r < n_dofs; ++r) REQUIRE(rhs._v[r] == b[r]);
   }
 
+  // ---- the ex3 penalty loop through the adaptor (every side without a neighbour) vs the C ABI directly ----
+  {
+    std::vector<uint32_t> pe;
+    std::vector<uint8_t> ps;
+    for (int64_t e = 0; e < n_elem; ++e)
+      for (unsigned s = 0; s < 6; ++s)
+        if (elems[e]._neighbors[s] == nullptr) { pe.push_back((uint32_t)e); ps.push_back((uint8_t)s); }
+    REQUIRE(pe.size() == (size_t)(2 * (nx * ny + ny * nz + nx * nz)));
+    const feasm_libmesh::SidePenalty pen{1.e10, FEASM_PENALTY_EX4_EXACT, 0.};
+    A.zero();
+    feasm_libmesh::assemble(es, "Poisson", p, nullptr, &pen);
+    A.close();
+    CK(feasm_set_side_penalty(ctx, (int64_t)pe.size(), pe.data(), ps.data(), 1.e10, FEASM_PENALTY_EX4_EXACT, 0.));
+    CK(feasm_assemble(ctx, &p));
+    std::vector<double> b3(n_dofs);
+    CK(feasm_get_values(ctx, nullptr, b3.data()));
+    double moved = 0.;
+    for (int64_t r = 0; r < n_dofs; ++r) { REQUIRE(rhs._v[r] == b3[r]); moved = std::max(moved, std::fabs(b3[r] - b[r])); }
+    REQUIRE(moved == 0.);  // every boundary dof is a Dirichlet row here: the constraint pass overwrites the penalised rows
+    std::vector<double> k1(27 * 27), f1(27), k0(27 * 27), f0(27);
+    CK(feasm_element_matrices(ctx, &p, 0, 1, 0, k1.data(), f1.data()));
+    CK(feasm_set_side_penalty(ctx, 0, nullptr, nullptr, 0., 0, 0.));
+    CK(feasm_element_matrices(ctx, &p, 0, 1, 0, k0.data(), f0.data()));
+    double dk = 0.;
+    for (int i = 0; i < 27 * 27; ++i) dk += k1[i] - k0[i];
+    // element 0 has three boundary sides of area (2/ny)(2/nz), (2/nx)(2/nz), (2/nx)(2/ny): sum_ij phi_i phi_j = 1
+    const double area = (2. / ny) * (2. / nz) + (2. / nx) * (2. / nz) + (2. / nx) * (2. / ny);
+    REQUIRE(std::fabs(dk - 1.e10 * area) < 1e-3 * 1.e10 * 1e-9);
+    feasm_libmesh::assemble(es, "Poisson", p);  // and a call without the term clears the adaptor's list
+    for (int64_t r = 0; r < n_dofs; ++r) REQUIRE(rhs._v[r] == b[r]);
+  }
+
   auto Z = A.zero_clone();
   REQUIRE(Z->m() == A.m());
   A.clear();
