@@ -158,6 +158,17 @@ int feasm_zero(feasm_ctx* ctx);
 int feasm_add_matrix(feasm_ctx* ctx, const double* dm, const uint32_t* rows, int n_rows, const uint32_t* cols,
                      int n_cols);
 int feasm_add_vector(feasm_ctx* ctx, const double* v, const uint32_t* rows, int n);
+/* feasm_add_matrix without any device allocation.  NO COUNTERPART IN THE REFERENCE: added
+ * for callers that cannot call cudaMalloc (tight serving loops, harnesses that forbid it, code meant for CUDA
+ * graph capture).  Same arguments, same result as feasm_add_matrix; the staging buffers are a fixed file-scope device
+ * array of FEASM_NOALLOC_SCRATCH_BYTES that every GPU loading the library holds until the process exits.  Blocks with
+ * n_rows or n_cols > FEASM_NOALLOC_MAX_DIM are rejected with FEASM_ERR_ARG (use feasm_add_matrix).  The call performs no
+ * cudaMalloc / cudaFree; it blocks until the add has completed.  All calls on one device share the scratch: calls that
+ * overlap on the GPU (two contexts of one device driven concurrently) race — serialise them per device. */
+#define FEASM_NOALLOC_MAX_DIM 128
+#define FEASM_NOALLOC_SCRATCH_BYTES (8 * 128 * 128 + 2 * 4 * 128)
+int feasm_add_matrix_noalloc(feasm_ctx* ctx, const double* dm, const uint32_t* rows, int n_rows, const uint32_t* cols,
+                             int n_cols);
 
 /* ---- outputs ------------------------------------------------------------------------------------ */
 int feasm_get_values(feasm_ctx* ctx, double* csr_values, double* rhs); /* D2H, either may be NULL */

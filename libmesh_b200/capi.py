@@ -33,7 +33,7 @@ SYMBOLS = [
     "feasm_vec_alloc", "feasm_vec_free", "feasm_vec_copy", "feasm_vec_fill", "feasm_vec_axpy", "feasm_vec_pointwise",
     "feasm_vec_reduce", "feasm_vec_set_entry",
     "feasm_generate_cube", "feasm_distribute_dofs_device", "feasm_generate_dirichlet", "feasm_get_mesh", "feasm_get_dofs",
-    "feasm_get_constraints", "feasm_set_side_penalty", "feasm_residual",
+    "feasm_get_constraints", "feasm_set_side_penalty", "feasm_residual", "feasm_add_matrix_noalloc",
 ]
 
 
@@ -83,6 +83,7 @@ def lib():
         "feasm_zero": (i32, [vp]),
         "feasm_add_matrix": (i32, [vp, vp, vp, i32, vp, i32]),
         "feasm_add_vector": (i32, [vp, vp, vp, i32]),
+        "feasm_add_matrix_noalloc": (i32, [vp, vp, vp, i32, vp, i32]),
         "feasm_get_values": (i32, [vp, vp, vp]),
         "feasm_device_values": (vp, [vp]),
         "feasm_device_rhs": (vp, [vp]),
@@ -338,6 +339,13 @@ class Context:
         r = _c(rows, np.uint32)
         c = r if cols is None else _c(cols, np.uint32)
         self._ck(self.L.feasm_add_matrix(self.h, _p(dm), _p(r), len(r), _p(c), len(c)))
+
+    def add_matrix_noalloc(self, dm, rows, cols=None):
+        """feasm_add_matrix_noalloc: the same add through the library's fixed device scratch (no device allocation)."""
+        dm = _c(dm, np.float64)
+        r = _c(rows, np.uint32)
+        c = r if cols is None else _c(cols, np.uint32)
+        self._ck(self.L.feasm_add_matrix_noalloc(self.h, _p(dm), _p(r), len(r), _p(c), len(c)))
 
     def add_vector(self, v, rows):
         v, r = _c(v, np.float64), _c(rows, np.uint32)
