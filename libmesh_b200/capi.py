@@ -151,6 +151,14 @@ def make_params(problem=POISSON, quadrature_order=0, forcing=FORCING_EX4_FD, con
 
 
 # ---- host-side generators (no GPU needed) ---------------------------------------------------------
+def cube_sizes(elem_type, nx, ny, nz):
+    """(n_elem, n_nodes) of build_cube."""
+    ne, nn = C.c_int64(), C.c_int64()
+    if lib().feasm_cube_sizes(elem_type, nx, ny, nz, C.byref(ne), C.byref(nn)):
+        raise FeasmError(-1, "bad build_cube arguments")
+    return int(ne.value), int(nn.value)
+
+
 def build_cube(elem_type, nx, ny, nz, bounds=(0.0, 1.0, 0.0, 1.0, 0.0, 1.0)):
     L = lib()
     ne, nn = C.c_int64(), C.c_int64()

@@ -323,158 +323,11 @@ class DistributedAssembly:
         if sync:
             self.ctx.synchronize()
 
+    def unpack_launches(self):
+        """Kernel launches of one feasm_unpack_ghost (for the launch count bench.py reports)."""
+        return len(self.peers)
+
     def owned_values(self):
         """(values of the owned rows, owned rhs) on the host."""
         v, b = self.ctx.get_values()
         return v[: int(self.row_ptr[self.p.n_owned])], b[: self.p.n_owned]
-
-
-# ---- bench.py --gpus N ------------------------------------------------------------------------------------------
-def bench_multi(args, F, rank, world, local):
-    """One rank of `bench.py --gpus N` (launched by torch.distributed.run): strong scaling of the BASELINE.json job —
-    the same build_cube mesh split over N GPUs — timed with CUDA events on the library's stream, max over ranks."""
-    import json
-    import os
-    import time
-
-    import torch
-    import torch.distributed as dist
-
-    import bench as B
-
-    torch.cuda.set_device(local)
-    dist.init_process_group("nccl", rank=rank, world_size=world, device_id=torch.device("cuda", local))
-    host_group = dist.new_group(backend="gloo")
-    etype = B.ELEM[args.elem]
-    t0 = time.time()
-    P = B.build_problem(F, etype, args.n)  # replicated host mesh, like libMesh's ReplicatedMesh
-    n_elem = P["conn"].shape[0]
-    pid = linear_partition(n_elem, world)
-    n_dofs, base, first, _ = F.distribute_dofs(P["conn"], P["xyz"].shape[0], 1, world, pid)
-    prob = RankProblem(rank, world, P["xyz"], P["conn"], base, first, pid, 1, P["con_dofs_nodes_base"](base), P["con_vals"])
-    ctx = F.Context(local)
-    dev_group = None
-    if os.environ.get("FEASM_OVERLAP", "1") != "0":
-        # the transfer should take SM slots as they free up while the owned rows are being reduced: NCCL's stream at
-        # high priority
-        opts = dist.ProcessGroupNCCL.Options(is_high_priority_stream=True)
-        dev_group = dist.new_group(backend="nccl", pg_options=opts)
-    da = DistributedAssembly(ctx, prob, dist, host_group=host_group, dev_group=dev_group)
-    da.setup()
-    ctx.synchronize()
-    setup_s = time.time() - t0
-    params = F.make_params(F.POISSON, args.qorder, F.FORCING_EX4_FD)
-    stream = torch.cuda.ExternalStream(ctx.stream())
-    overlap = os.environ.get("FEASM_OVERLAP", "1") != "0"  # 0: feasm_assemble, then pack / exchange / unpack in sequence
-    for _ in range(args.warmup):
-        da.assemble(params, sync=False, overlap=overlap)
-    ctx.synchronize()
-    clocks = B.ClockSampler(local)
-    if rank == 0:
-        clocks.start()
-    ev0, ev1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-    torch.cuda.synchronize()
-    dist.barrier()
-    torch.cuda.synchronize()
-    ev0.record(stream)
-    th = time.perf_counter()
-    for _ in range(args.steps):
-        da.assemble(params, sync=False, overlap=overlap)
-    host_ms = (time.perf_counter() - th) * 1e3 / args.steps  # host time to ENQUEUE one step (launch-bound check)
-    ev1.record(stream)
-    ctx.synchronize()
-    torch.cuda.synchronize()
-    dist.barrier()
-    ms = torch.tensor([ev0.elapsed_time(ev1)], device="cuda")
-    dist.all_reduce(ms, op=dist.ReduceOp.MAX)
-    ms_per_step = float(ms.item()) / args.steps
-    # per-kernel times of this rank's last step (events inside the library)
-    da.assemble(params, sync=True, overlap=overlap)
-    kms, nl = ctx.last_timing()
-    nl += len(da.peers) + (0 if overlap else 1)  # unpack launches (one per peer) and the separate pack
-    kall = [torch.zeros(4, device="cuda") for _ in range(world)]  # per-rank kernel times of that step
-    dist.all_gather(kall, torch.tensor([float(x) for x in kms], device="cuda"))
-    kall = [[round(float(v), 4) for v in k.tolist()] for k in kall]
-    clk = clocks.stop() if rank == 0 else None
-
-    # e2e: host buffers through the C ABI on every rank: coordinates + Dirichlet data in, the rank's OWNED rows out (the
-    # ghost rows were added into their owners by the exchange).  The result leaves through the device-pointer accessors:
-    # a device-side snapshot on the library's stream, then the PCIe read on a second stream, so the read of step i
-    # overlaps the upload + assembly + exchange of step i+1 (the same overlap as the single-GPU e2e leg of bench.py).
-    nnz_local = int(da.row_ptr[-1])
-    nnz_owned = int(da.row_ptr[prob.n_owned])
-    xyz_pin = torch.from_numpy(prob.xyz).pin_memory().numpy()
-    pipelined = os.environ.get("FEASM_E2E_PIPELINE", "1") != "0"  # 0: feasm_get_values of all local rows, synchronous
-    val_pin = torch.empty(max(nnz_owned if pipelined else nnz_local, 1), dtype=torch.float64).pin_memory()
-    rhs_pin = torch.empty(max(prob.n_owned if pipelined else prob.n_rows, 1), dtype=torch.float64).pin_memory()
-    d_val = torch.as_tensor(DevArray(ctx.device_values(), max(nnz_owned, 1)), device="cuda")
-    d_rhs = torch.as_tensor(DevArray(ctx.device_rhs(), max(prob.n_owned, 1)), device="cuda")
-    snap_val, snap_rhs = torch.empty_like(d_val), torch.empty_like(d_rhs)
-    copy_stream = torch.cuda.Stream()
-    ev_ready, ev_done = torch.cuda.Event(), torch.cuda.Event()
-    ev_done.record(copy_stream)
-
-    def e2e_step():
-        ctx.update_coordinates(xyz_pin)
-        ctx.set_constraints(prob.con_rows, prob.con_vals)
-        da.assemble(params, sync=False, overlap=overlap)
-        if not pipelined:
-            ctx.get_values(out_values=val_pin.numpy(), out_rhs=rhs_pin.numpy())
-            return
-        with torch.cuda.stream(stream):
-            stream.wait_event(ev_done)  # the previous read has left the snapshot
-            snap_val.copy_(d_val, non_blocking=True)
-            snap_rhs.copy_(d_rhs, non_blocking=True)
-            ev_ready.record(stream)
-        with torch.cuda.stream(copy_stream):
-            copy_stream.wait_event(ev_ready)
-            val_pin.copy_(snap_val, non_blocking=True)
-            rhs_pin.copy_(snap_rhs, non_blocking=True)
-            ev_done.record(copy_stream)
-
-    e2e_step()
-    torch.cuda.synchronize()
-    ctx.synchronize()
-    dist.barrier()
-    te = time.perf_counter()
-    e2e_steps = max(3, min(args.steps, 8))
-    for _ in range(e2e_steps):
-        e2e_step()
-    torch.cuda.synchronize()
-    ctx.synchronize()  # raises if any step flagged a degenerate element
-    dist.barrier()
-    e2e_s = torch.tensor([(time.perf_counter() - te) / e2e_steps], device="cuda")
-    dist.all_reduce(e2e_s, op=dist.ReduceOp.MAX)
-    io = torch.tensor([float(xyz_pin.nbytes + prob.con_rows.nbytes + prob.con_vals.nbytes + prob.n_rows * 9),
-                       float(nnz_owned * 8 + prob.n_owned * 8), float(len(da.send_slots) * 8), float(nnz_local)], device="cuda")
-    dist.all_reduce(io)
-    if rank == 0:
-        nq = {27: 27, 8: 27 if args.qorder in (0, 5) else 8, 10: 14}[etype]
-        nnz_g = int(io[3].item())  # includes ghost-row copies
-        flops_e, bytes_e = B.algorithmic_counts(etype, nq, nnz_g, n_dofs, n_elem, P["xyz"].shape[0])
-        out = {
-            "metric": B.METRIC, "value": n_elem / (ms_per_step * 1e-3), "unit": "elements/s", "n_gpus": world, "steps": args.steps,
-            "warmup": args.warmup, "ms_per_step": ms_per_step, "higher_is_better": True, "scaling": "strong", "vs_baseline": None,
-            "dtype": "f64", "data": "synthetic",
-            "config": {"workload": f"introduction_ex4 3D Poisson, build_cube {args.n}^3 {args.elem.upper()} on [-1,1]^3, QGauss nq={nq}, "
-                                   f"LinearPartitioner slabs over {world} GPUs, ghost rows by NCCL send/recv"
-                                   + (" overlapped with the reduction of the owned rows" if overlap else ""), "n_elem": n_elem,
-                       "n_dofs": int(n_dofs), "l2": "per-rank CSR values larger than L2", "setup_s": round(setup_s, 3),
-                       "ghost_bytes_per_step_all_ranks": int(io[2].item()), "host_enqueue_ms_per_step_rank0": round(host_ms, 4)},
-            "clocks": clk, "gpu_launches": int(nl) * args.steps,
-            "e2e": {"value": n_elem / float(e2e_s.item()), "unit": "elements/s", "h2d_bytes_per_step": int(io[0].item()),
-                    "d2h_bytes_per_step": int(io[1].item()), "ms_per_step": float(e2e_s.item()) * 1e3},
-            "roofline": {"bound": "tensor", "kernel": "k_elem_poisson on rank 0 (FP64 DMMA contraction + geometry)",
-                         "achieved": flops_e * len(prob.elems) / (kms[0] * 1e-3) / 1e12, "peak": None, "unit": "TFLOP/s", "frac": None,
-                         "traffic": None, "kernel_ms": {"element": kms[0], "row_reduce": kms[1]}, "flops_per_element": flops_e,
-                         "kernel_ms_per_rank": {"element": [k[0] for k in kall], "constrain": [k[3] for k in kall],
-                                                "row_reduce": [k[1] for k in kall], "assemble": [k[2] for k in kall]}},
-        }
-        fp64 = ctx.measure_fp64_peaks()
-        pk = max(fp64["dmma_tflops"], fp64["dfma_tflops"])
-        out["roofline"]["peak"], out["roofline"]["frac"] = pk, out["roofline"]["achieved"] / pk
-        out["roofline"]["peak_source"] = "FP64 mma.sync/DFMA chain measured live (MEASURED_PEAKS.json has no FP64 entry)"
-        print(json.dumps(out), flush=True)
-    ctx.close()
-    dist.barrier()
-    dist.destroy_process_group()
