@@ -429,7 +429,7 @@ def run_ours(args):
     torch.cuda.synchronize()
     ctx.synchronize()  # raises if any step flagged a degenerate element
     e2e_s = (time.perf_counter() - t_e) / e2e_steps
-    h2d = xyz_np.nbytes + con_rows.nbytes + P["con_vals"].nbytes + P["n_dofs"] * 9  # flags+values arrays uploaded by set_constraints
+    h2d = xyz_np.nbytes + con_rows.nbytes + P["con_vals"].nbytes  # what feasm_update_coordinates / feasm_set_constraints upload
     d2h = val_np.nbytes + rhs_np.nbytes
     checksum = float(val_np.sum())
     del snap_val, snap_rhs, val_pin, rhs_pin, val_np, rhs_np, d_val, d_rhs
@@ -672,7 +672,7 @@ def run_multi(args, F, rank, world, local):
     dist.all_reduce(e2e_s, op=dist.ReduceOp.MAX)
     csum = torch.tensor([float(val_pin[:nnz_owned].sum().item())], dtype=torch.float64, device="cuda")  # owned rows tile the global matrix
     dist.all_reduce(csum)
-    io = torch.tensor([float(xyz_pin.nbytes + prob.con_rows.nbytes + prob.con_vals.nbytes + prob.n_rows * 9),
+    io = torch.tensor([float(xyz_pin.nbytes + prob.con_rows.nbytes + prob.con_vals.nbytes),
                        float(nnz_owned * 8 + prob.n_owned * 8), float(len(da.send_slots) * 8), float(nnz_local)], device="cuda")
     dist.all_reduce(io)
     if rank == 0:

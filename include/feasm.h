@@ -54,6 +54,8 @@ extern "C" {
 #define FEASM_ERR_DEGENERATE -4 /* det J <= 0 somewhere: libMesh's DegenerateMap, fe_map.C:467-506 */
 #define FEASM_ERR_PATTERN -5    /* add to an entry outside the sparsity pattern (sparse_matrix.h:300-303) */
 #define FEASM_ERR_NOMEM -6
+#define FEASM_ERR_BREAKDOWN -7 /* feasm_cg_solve: p.Ap <= 0 */
+#define FEASM_NOT_CONVERGED 1  /* feasm_cg_solve: max_its reached above the tolerance (x, iterations, residual are valid) */
 
 typedef struct feasm_ctx feasm_ctx;
 
@@ -181,7 +183,8 @@ void* feasm_stream(feasm_ctx* ctx);                                    /* cudaSt
 int feasm_vector_mult(feasm_ctx* ctx, const double* d_x, double* d_y);
 int feasm_vector_mult_host(feasm_ctx* ctx, const double* x, double* y); /* same with host arrays (H2D, product, D2H) */
 /* LinearSolver::solve with CG + Jacobi preconditioning on the assembled system A x = rhs.  x0 (host, may be NULL =
- * zero) is the initial guess, x (host) receives the solution; stops at ||r|| <= rel_tol ||b|| or max_its. */
+ * zero) is the initial guess, x (host) receives the solution; stops at ||r|| <= rel_tol ||b|| or max_its.  Returns
+ * FEASM_OK (converged), FEASM_NOT_CONVERGED (max_its reached; outputs valid) or FEASM_ERR_BREAKDOWN. */
 int feasm_cg_solve(feasm_ctx* ctx, double rel_tol, int max_its, const double* x0, double* x, int* iterations,
                    double* rel_residual);
 

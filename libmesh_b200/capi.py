@@ -409,7 +409,9 @@ class Context:
         x = np.empty(self.n_rows, np.float64)
         x0c = _c(x0, np.float64)
         its, rel = C.c_int(), C.c_double()
-        self._ck(self.L.feasm_cg_solve(self.h, rel_tol, max_its, _p(x0c), _p(x), C.byref(its), C.byref(rel)))
+        rc = self.L.feasm_cg_solve(self.h, rel_tol, max_its, _p(x0c), _p(x), C.byref(its), C.byref(rel))
+        if rc < 0:  # FEASM_NOT_CONVERGED (+1) is a status: x, its, rel are valid and rel > rel_tol says so
+            self._ck(rc)
         return x, its.value, rel.value
 
     def measure_fp64_peaks(self):

@@ -140,7 +140,9 @@ void feasm_destroy(feasm_ctx* ctx) {
   drop_maps(ctx);
   release(ctx->d_xyz); release(ctx->d_conn); release(ctx->d_elem_dofs); release(ctx->d_gid);
   release(ctx->d_node_mask); release(ctx->d_node_base);
-  release(ctx->d_con_flag); release(ctx->d_con_val); release(ctx->d_row_ptr); release(ctx->d_col_idx);
+  release(ctx->d_con_flag); release(ctx->d_con_val); release(ctx->d_con_rows); release(ctx->d_con_vals_list);
+  release(ctx->d_unpack_perm); release(ctx->d_unpack_seg); release(ctx->d_unpack_slot);
+  release(ctx->d_row_ptr); release(ctx->d_col_idx);
   release(ctx->d_values); release(ctx->d_rhs); release(ctx->d_flags); release(ctx->d_tab); release(ctx->d_f);
   release(ctx->d_side_elems); release(ctx->d_side_mask); release(ctx->d_side_tab); release(ctx->d_side_nodes);
   release(ctx->d_pen_elems); release(ctx->d_pen_mask); release(ctx->d_y);
@@ -206,6 +208,16 @@ void feasm_reset_mesh(feasm_ctx* ctx, int elem_type, int64_t n_elem, int64_t n_n
 
 int feasm_reset_dofs(feasm_ctx* ctx, int n_vars, int64_t n_rows, int64_t n_owned) {
   drop_maps(ctx);
+  // the pattern, the values and the exchange plan belong to the previous dof set: feasm_prepare / feasm_assemble return
+  // FEASM_ERR_STATE until feasm_set_pattern / feasm_build_pattern is called again
+  release(ctx->d_row_ptr); release(ctx->d_col_idx); release(ctx->d_values);
+  ctx->nnz = 0;
+  ctx->max_row_len = 0;
+  release(ctx->d_send_slots); release(ctx->d_recv_slots); release(ctx->d_send_buf); release(ctx->d_recv_buf);
+  release(ctx->d_unpack_perm); release(ctx->d_unpack_seg); release(ctx->d_unpack_slot);
+  ctx->n_unpack_slots = 0;
+  ctx->n_peers = 0;
+  ctx->peer_rank.clear(); ctx->send_ptr.clear(); ctx->recv_ptr.clear();
   ctx->n_vars = n_vars;
   ctx->nd = ctx->npe * n_vars;
   ctx->n_rows = n_rows;
@@ -220,7 +232,11 @@ int feasm_reset_dofs(feasm_ctx* ctx, int n_vars, int64_t n_rows, int64_t n_owned
   FEASM_CUDA(ctx, cudaMemsetAsync(ctx->d_rhs, 0, sizeof(double) * n_rows, ctx->stream));
   FEASM_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
   ctx->n_con = 0;
-  ctx->h_con_flag.assign((size_t)n_rows, 0);
+  ctx->h_con_rows.clear();
+  release(ctx->d_con_rows); release(ctx->d_con_vals_list);
+  ctx->d_con_rows_cap = 0;
+  ctx->n_con_dev_prev = 0;
+  ctx->con_flags_untracked = false;
   return FEASM_OK;
 }
 
@@ -229,21 +245,41 @@ extern "C" {
 int feasm_set_constraints(feasm_ctx* ctx, int64_t n, const uint32_t* rows, const double* values) {
   if (!ctx || !ctx->d_con_flag) return feasm_fail(ctx, FEASM_ERR_STATE, "set_dofs first");
   if (n < 0 || (n && (!rows || !values))) return feasm_fail(ctx, FEASM_ERR_ARG, "bad constraint arguments");
-  std::vector<uint8_t> flag(ctx->n_rows, 0);
-  std::vector<double> val(ctx->n_rows, 0.);
-  for (int64_t i = 0; i < n; ++i) {
+  for (int64_t i = 0; i < n; ++i)
     if (rows[i] >= (uint64_t)ctx->n_rows) return feasm_fail(ctx, FEASM_ERR_ARG, "constraint row out of range");
-    flag[rows[i]] = 1;
-    val[rows[i]] = values[i];
+  FEASM_CUDA(ctx, cudaSetDevice(ctx->device));
+  // Only the (row, value) LIST crosses the bus (the dense flag / value arrays live on the device and are scattered
+  // there).  The constrained SET decides which elements take the element-level constraint pass; when the same rows
+  // come again in the same order — every assemble of a steady problem — only the values are refreshed.
+  const bool same_set = !ctx->con_flags_untracked && (size_t)n == ctx->h_con_rows.size() &&
+                        (n == 0 || std::memcmp(rows, ctx->h_con_rows.data(), sizeof(uint32_t) * n) == 0);
+  if ((size_t)n > ctx->d_con_rows_cap || ctx->con_flags_untracked) {
+    if ((size_t)n > ctx->d_con_rows_cap) {
+      release(ctx->d_con_rows); release(ctx->d_con_vals_list);
+      FEASM_CUDA(ctx, cudaMalloc(&ctx->d_con_rows, sizeof(uint32_t) * 2 * n));  // new list | previous list
+      FEASM_CUDA(ctx, cudaMalloc(&ctx->d_con_vals_list, sizeof(double) * n));
+      ctx->d_con_rows_cap = (size_t)n;
+    }
+    // the previous list on the device went with the buffer (or never existed): clear flags and values wholesale
+    FEASM_CUDA(ctx, cudaMemsetAsync(ctx->d_con_flag, 0, ctx->n_rows, ctx->stream));
+    FEASM_CUDA(ctx, cudaMemsetAsync(ctx->d_con_val, 0, sizeof(double) * ctx->n_rows, ctx->stream));
+    ctx->n_con_dev_prev = 0;
+    ctx->con_flags_untracked = false;
   }
-  // the constrained SET is baked into the position map's flag bits; new values alone leave it valid
-  if (flag != ctx->h_con_flag) {
+  if (n) FEASM_CUDA(ctx, cudaMemcpyAsync(ctx->d_con_vals_list, values, sizeof(double) * n, cudaMemcpyHostToDevice, ctx->stream));
+  if (!same_set) {
+    // previous rows -> second half, new rows -> first half; the kernel clears the old flags, then sets the new ones
+    if (ctx->n_con_dev_prev)
+      FEASM_CUDA(ctx, cudaMemcpyAsync(ctx->d_con_rows + ctx->d_con_rows_cap, ctx->d_con_rows, sizeof(uint32_t) * ctx->n_con_dev_prev,
+                                      cudaMemcpyDeviceToDevice, ctx->stream));
+    if (n) FEASM_CUDA(ctx, cudaMemcpyAsync(ctx->d_con_rows, rows, sizeof(uint32_t) * n, cudaMemcpyHostToDevice, ctx->stream));
     ctx->elem_flag_valid = false;
-    FEASM_CUDA(ctx, cudaMemcpyAsync(ctx->d_con_flag, flag.data(), flag.size(), cudaMemcpyHostToDevice, ctx->stream));
   }
-  FEASM_CUDA(ctx, cudaMemcpyAsync(ctx->d_con_val, val.data(), sizeof(double) * val.size(), cudaMemcpyHostToDevice, ctx->stream));
-  FEASM_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
-  ctx->h_con_flag.swap(flag);
+  int rc = feasm_launch_scatter_constraints(ctx, n, same_set ? 0 : ctx->n_con_dev_prev, !same_set);
+  if (rc) return rc;
+  FEASM_CUDA(ctx, cudaStreamSynchronize(ctx->stream));  // the caller's arrays may go away
+  if (!same_set) ctx->h_con_rows.assign(rows, rows + n);
+  ctx->n_con_dev_prev = n;
   ctx->n_con = n;
   return FEASM_OK;
 }
@@ -321,8 +357,9 @@ static int assemble_impl(feasm_ctx* ctx, const feasm_params* params, int mode) {
   const double* d_f = nullptr;
   rc = resolve_forcing(ctx, *params, ctx->tab_nq, &d_f);
   if (rc) return rc;
-  // matrix->zero(); rhs->zero() (implicit_system.C:101-105) is implied: the row reduction overwrites every slot
-  FEASM_CUDA(ctx, cudaMemsetAsync(ctx->d_flags, 0, 2 * sizeof(int), ctx->stream));
+  // matrix->zero(); rhs->zero() (implicit_system.C:101-105) is implied: the row reduction overwrites every slot.
+  // d_flags is NOT cleared here: a degenerate-map / pattern-miss flag raised by step i must survive the launch of
+  // step i+1 until feasm_synchronize / a getter reports (and clears) it.
   FEASM_CUDA(ctx, cudaEventRecord(ctx->ev[0], ctx->stream));
   int launches = 2;
   const int rs = feasm_recb(ctx->nd, ctx->pos_bytes) / 8;  // doubles per element record
@@ -369,7 +406,6 @@ int feasm_residual(feasm_ctx* ctx, const feasm_params* params, const double* d_u
   const double* d_f = nullptr;
   rc = resolve_forcing(ctx, *params, ctx->tab_nq, &d_f);
   if (rc) return rc;
-  FEASM_CUDA(ctx, cudaMemsetAsync(ctx->d_flags, 0, 2 * sizeof(int), ctx->stream));
   if (!ctx->elem_flag_valid) {
     rc = feasm_launch_elem_flags(ctx);
     if (rc) return rc;
@@ -430,7 +466,6 @@ int feasm_element_matrices(feasm_ctx* ctx, const feasm_params* params, int64_t e
   }
   double* d_kf = nullptr;  // scratch records without a position row (record stride = ldr doubles)
   FEASM_CUDA(ctx, cudaMalloc(&d_kf, sizeof(double) * ne * nd * ldr));
-  FEASM_CUDA(ctx, cudaMemsetAsync(ctx->d_flags, 0, 2 * sizeof(int), ctx->stream));
   rc = feasm_launch_element_kernel(ctx, *params, d_f, e0, e1, d_kf, (int)ldr, constrained ? params->constrain : -1);
   if (!rc) {
     // scratch records are (Ke row | Fe | pad): strip the padding on the way out
@@ -515,7 +550,25 @@ int feasm_set_exchange_plan(feasm_ctx* ctx, int n_peers, const int32_t* peer_ran
   release(ctx->d_send_buf); release(ctx->d_recv_buf);
   FEASM_CUDA(ctx, cudaMalloc(&ctx->d_send_buf, sizeof(double) * (ns ? ns : 1)));
   FEASM_CUDA(ctx, cudaMalloc(&ctx->d_recv_buf, sizeof(double) * (nr ? nr : 1)));
-  FEASM_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
+  // One unpack launch for all peers: the received entries are grouped by destination slot, each group in receive-buffer
+  // (= peer) order, and one thread adds a group to its slot — the same sums, in the same order, as one launch per peer.
+  {
+    std::vector<uint64_t> perm(nr);
+    for (uint64_t i = 0; i < nr; ++i) perm[i] = i;
+    std::stable_sort(perm.begin(), perm.end(), [&](uint64_t a, uint64_t b) { return recv_slots[a] < recv_slots[b]; });
+    std::vector<uint64_t> uslot, seg;
+    for (uint64_t i = 0; i < nr; ++i)
+      if (i == 0 || recv_slots[perm[i]] != recv_slots[perm[i - 1]]) { uslot.push_back(recv_slots[perm[i]]); seg.push_back(i); }
+    seg.push_back(nr);
+    ctx->n_unpack_slots = uslot.size();
+    rc = upload(ctx, &ctx->d_unpack_perm, perm.data(), perm.size());
+    if (rc) return rc;
+    rc = upload(ctx, &ctx->d_unpack_slot, uslot.data(), uslot.size());
+    if (rc) return rc;
+    rc = upload(ctx, &ctx->d_unpack_seg, seg.data(), seg.size());
+    if (rc) return rc;
+    FEASM_CUDA(ctx, cudaStreamSynchronize(ctx->stream));  // the vectors go out of scope
+  }
   return FEASM_OK;
 }
 

@@ -382,9 +382,10 @@ int64_t feasm_generate_dirichlet(feasm_ctx* ctx, unsigned id_mask, int kind, uns
                                                                      ctx->d_xyz, id_mask, var_mask, kind, ctx->n_vars, ctx->n_nodes);
   unsigned long long n = 0;
   cudaMemcpyAsync(&n, d_count, sizeof(n), cudaMemcpyDeviceToHost, ctx->stream);
-  // host mirror of the constrained set (feasm_set_constraints compares against it)
-  ctx->h_con_flag.resize((size_t)ctx->n_rows);
-  cudaMemcpyAsync(ctx->h_con_flag.data(), ctx->d_con_flag, (size_t)ctx->n_rows, cudaMemcpyDeviceToHost, ctx->stream);
+  // the flags on the device no longer mirror a host-given list: a later feasm_set_constraints clears them wholesale
+  ctx->h_con_rows.clear();
+  ctx->n_con_dev_prev = 0;
+  ctx->con_flags_untracked = true;
   cudaError_t e = cudaStreamSynchronize(ctx->stream);
   cudaFree(d_count);
   if (e != cudaSuccess) return feasm_fail(ctx, FEASM_ERR_CUDA, cudaGetErrorString(e));

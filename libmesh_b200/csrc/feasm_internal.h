@@ -74,7 +74,12 @@ struct feasm_ctx {
   uint8_t* d_con_flag = nullptr;
   double* d_con_val = nullptr;
   int64_t n_con = 0;
-  std::vector<uint8_t> h_con_flag;  // host mirror of d_con_flag (detects a changed constrained set)
+  std::vector<uint32_t> h_con_rows;  // the constrained rows as last given (detects a changed constrained set)
+  uint32_t* d_con_rows = nullptr;    // [2 * cap]: the current (row) list | the previous one (to clear its flags)
+  double* d_con_vals_list = nullptr; // [cap] the values of the current list
+  size_t d_con_rows_cap = 0;
+  int64_t n_con_dev_prev = 0;        // length of the list the device flags currently reflect
+  bool con_flags_untracked = false;  // flags were set on the device without a list (feasm_generate_dirichlet)
 
   // pattern + system
   uint64_t nnz = 0;
@@ -137,6 +142,11 @@ struct feasm_ctx {
   uint64_t* d_recv_slots = nullptr;
   double* d_send_buf = nullptr;
   double* d_recv_buf = nullptr;
+  // unpack in ONE launch: the received entries grouped by destination slot, each group in peer order
+  uint64_t n_unpack_slots = 0;
+  uint64_t* d_unpack_slot = nullptr;  // [n_unpack_slots] destination slot
+  uint64_t* d_unpack_seg = nullptr;   // [n_unpack_slots+1] group boundaries in d_unpack_perm
+  uint64_t* d_unpack_perm = nullptr;  // [n_recv] index into the receive buffer
 
   float last_ms[4] = {0, 0, 0, 0};
   int last_launches = 0;
@@ -165,6 +175,9 @@ int feasm_build_pos(feasm_ctx* ctx);
 int feasm_launch_element_kernel(feasm_ctx* ctx, const feasm_params& p, const double* d_f, int64_t e0, int64_t e1,
                                 double* d_kf, int rs, int constrain_mode);
 int feasm_launch_elem_flags(feasm_ctx* ctx);
+// d_con_rows[0..n) / d_con_vals_list -> d_con_flag / d_con_val; when set_flags, the n_prev rows of the previous list
+// (second half of d_con_rows) are cleared first
+int feasm_launch_scatter_constraints(feasm_ctx* ctx, int64_t n, int64_t n_prev, bool set_flags);
 // feasm_side.cu: adds the side loads to the Fe column of the records of elements [e0, e1) (no-op without loads)
 int feasm_launch_side_loads(feasm_ctx* ctx, int qorder, int64_t e0, int64_t e1, double* d_kf, int rs);
 // d_row_list == nullptr: every row; else the n_list rows listed

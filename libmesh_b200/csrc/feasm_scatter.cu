@@ -204,13 +204,28 @@ __global__ void k_pack(const uint64_t* __restrict__ slots, uint64_t n, uint64_t 
   }
 }
 
-__global__ void k_unpack(const uint64_t* __restrict__ slots, uint64_t n, uint64_t nnz, const double* __restrict__ in,
-                         double* __restrict__ values, double* __restrict__ rhs) {
-  const uint64_t i = blockIdx.x * (uint64_t)blockDim.x + threadIdx.x;
-  if (i < n) {
-    const uint64_t s = slots[i];  // slots of one peer are distinct
-    if (s < nnz) values[s] += in[i]; else rhs[s - nnz] += in[i];
-  }
+// One thread per destination slot: the entries the peers sent for it are added in receive-buffer (= fixed peer) order.
+__global__ void k_unpack(const uint64_t* __restrict__ uslot, const uint64_t* __restrict__ seg, const uint64_t* __restrict__ perm,
+                         uint64_t n_slots, uint64_t nnz, const double* __restrict__ in, double* __restrict__ values,
+                         double* __restrict__ rhs) {
+  const uint64_t k = blockIdx.x * (uint64_t)blockDim.x + threadIdx.x;
+  if (k >= n_slots) return;
+  const uint64_t s = uslot[k];
+  double* dst = s < nnz ? values + s : rhs + (s - nnz);
+  double acc = *dst;
+  for (uint64_t i = seg[k]; i < seg[k + 1]; ++i) acc += in[perm[i]];
+  *dst = acc;
+}
+
+// feasm_set_constraints on the device: clear the flags of the previous list, then scatter the new (row, value) list
+__global__ void k_clear_constraints(const uint32_t* __restrict__ rows, int64_t n, uint8_t* __restrict__ flag, double* __restrict__ val) {
+  const int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x;
+  if (i < n) { flag[rows[i]] = 0; val[rows[i]] = 0.; }
+}
+__global__ void k_scatter_constraints(const uint32_t* __restrict__ rows, const double* __restrict__ vals, int64_t n, bool set_flags,
+                                      uint8_t* __restrict__ flag, double* __restrict__ val) {
+  const int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x;
+  if (i < n) { if (set_flags) flag[rows[i]] = 1; val[rows[i]] = vals[i]; }
 }
 
 // SparseMatrix::add_matrix for one host-supplied dense block (slow route; one thread per entry, entries of one
@@ -352,12 +367,21 @@ int feasm_launch_pack(feasm_ctx* ctx) {
 }
 
 int feasm_launch_unpack(feasm_ctx* ctx) {
-  // one launch per peer, in peer order: two peers may hit the same owned slot, the order of the adds is fixed
-  for (int p = 0; p < ctx->n_peers; ++p) {
-    const uint64_t b = ctx->recv_ptr[p], n = ctx->recv_ptr[p + 1] - b;
-    if (!n) continue;
-    k_unpack<<<(unsigned)((n + 255) / 256), 256, 0, ctx->stream>>>(ctx->d_recv_slots + b, n, ctx->nnz, ctx->d_recv_buf + b, ctx->d_values, ctx->d_rhs);
-  }
+  const uint64_t n = ctx->n_unpack_slots;
+  if (n)
+    k_unpack<<<(unsigned)((n + 255) / 256), 256, 0, ctx->stream>>>(ctx->d_unpack_slot, ctx->d_unpack_seg, ctx->d_unpack_perm, n, ctx->nnz,
+                                                                    ctx->d_recv_buf, ctx->d_values, ctx->d_rhs);
+  FEASM_CUDA(ctx, cudaGetLastError());
+  return FEASM_OK;
+}
+
+int feasm_launch_scatter_constraints(feasm_ctx* ctx, int64_t n, int64_t n_prev, bool set_flags) {
+  if (set_flags && n_prev)
+    k_clear_constraints<<<(unsigned)((n_prev + 255) / 256), 256, 0, ctx->stream>>>(ctx->d_con_rows + ctx->d_con_rows_cap, n_prev, ctx->d_con_flag,
+                                                                                    ctx->d_con_val);
+  if (n)
+    k_scatter_constraints<<<(unsigned)((n + 255) / 256), 256, 0, ctx->stream>>>(ctx->d_con_rows, ctx->d_con_vals_list, n, set_flags,
+                                                                                 ctx->d_con_flag, ctx->d_con_val);
   FEASM_CUDA(ctx, cudaGetLastError());
   return FEASM_OK;
 }

@@ -31,10 +31,11 @@ __global__ void k_spmv(const uint64_t* __restrict__ row_ptr, const uint32_t* __r
       const uint64_t k = k0 + lane + 32 * u;
       const bool ok = k < p1;
       v[u] = ok ? __ldcs(values + k) : 0.;
-      c[u] = ok ? __ldcs(col_idx + k) : 0u;
+      c[u] = ok ? __ldcs(col_idx + k) : 0xffffffffu;
     }
 #pragma unroll
-    for (int u = 0; u < 4; ++u) s += v[u] * x[c[u]];
+    for (int u = 0; u < 4; ++u)
+      if (c[u] != 0xffffffffu) s += v[u] * x[c[u]];  // padding lanes add nothing (0 * x[0] would spread a non-finite x[0])
   }
 #pragma unroll
   for (int o = 16; o > 0; o >>= 1) s += __shfl_xor_sync(0xffffffffu, s, o);
@@ -95,7 +96,9 @@ __global__ void k_dot_final(const double* __restrict__ partial, int n, double* _
 __global__ void k_cg_update(int64_t n, const double* __restrict__ rz, const double* __restrict__ pq, const double* __restrict__ p,
                             const double* __restrict__ q, const double* __restrict__ dinv, double* __restrict__ x, double* __restrict__ r,
                             double* __restrict__ z) {
-  const double alpha = *rz / *pq;
+  const double pqv = *pq;
+  if (!(pqv > 0.)) return;  // breakdown (p.Ap <= 0): leave x and r as they are; the host reads pq and reports it
+  const double alpha = *rz / pqv;
   for (int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; i < n; i += (int64_t)gridDim.x * blockDim.x) {
     x[i] += alpha * p[i];
     const double ri = r[i] - alpha * q[i];
@@ -233,6 +236,7 @@ int feasm_cg_solve(feasm_ctx* ctx, double rel_tol, int max_its, const double* x0
   double* d_s = d_part + DOT_GRID;  // [0] rz, [1] pq, [2] rz_new, [3] rr
   int rc = FEASM_OK, its = 0;
   double rel = 0.;
+  bool breakdown = false;
   auto fail = [&](int code) { cudaFree(w); return code; };
   const unsigned vg = DOT_GRID;
   if (x0) { if (cudaMemcpyAsync(d_x, x0, nb, cudaMemcpyHostToDevice, ctx->stream) != cudaSuccess) return fail(feasm_fail(ctx, FEASM_ERR_CUDA, "H2D x0")); }
@@ -261,16 +265,17 @@ int feasm_cg_solve(feasm_ctx* ctx, double rel_tol, int max_its, const double* x0
     if (cudaMemcpyAsync(d_s + 0, d_s + 2, sizeof(double), cudaMemcpyDeviceToDevice, ctx->stream) != cudaSuccess ||
         cudaMemcpyAsync(h, d_s, sizeof(h), cudaMemcpyDeviceToHost, ctx->stream) != cudaSuccess || cudaStreamSynchronize(ctx->stream) != cudaSuccess)
       return fail(feasm_fail(ctx, FEASM_ERR_CUDA, "cg: scalar read"));
+    if (!(h[1] > 0.)) { breakdown = true; break; }  // p.Ap <= 0: not positive definite on this direction; x, r untouched by this step
     ++its;
     rel = std::sqrt(h[3]) / bnorm;
-    if (!(h[1] > 0.)) break;  // p.Ap <= 0: the matrix is not positive definite on this direction
   }
   if (cudaMemcpyAsync(x, d_x, nb, cudaMemcpyDeviceToHost, ctx->stream) != cudaSuccess || cudaStreamSynchronize(ctx->stream) != cudaSuccess)
     return fail(feasm_fail(ctx, FEASM_ERR_CUDA, "cg: D2H x"));
   cudaFree(w);
   if (iterations) *iterations = its;
   if (rel_residual) *rel_residual = rel;
-  return FEASM_OK;
+  if (breakdown) return feasm_fail(ctx, FEASM_ERR_BREAKDOWN, "cg: p.Ap <= 0 (matrix not positive definite on the search direction); x holds the last good iterate");
+  return rel > rel_tol ? FEASM_NOT_CONVERGED : FEASM_OK;
 }
 
 

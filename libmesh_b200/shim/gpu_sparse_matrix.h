@@ -166,7 +166,8 @@ class GpuSparseMatrix : public SparseMatrix<T> {
     int its = 0;
     double rel = 0.;
     x.resize(m());
-    check(feasm_cg_solve(ctx(), rel_tol, (int)max_its, nullptr, x.data(), &its, &rel));
+    const int rc = feasm_cg_solve(ctx(), rel_tol, (int)max_its, nullptr, x.data(), &its, &rel);
+    if (rc < 0) check(rc);  // FEASM_NOT_CONVERGED (> 0) is reported through the returned residual, like LinearSolver::solve
     return {(unsigned int)its, rel};
   }
 
