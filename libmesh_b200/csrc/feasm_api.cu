@@ -1,6 +1,7 @@
 // feasm_api.cu — the C ABI of libfeasm (include/feasm.h): context, uploads, pattern, assemble, outputs.
 #include <algorithm>
 #include <cstdlib>
+#include <cstdio>
 #include <cstring>
 #include <mutex>
 

@@ -1,5 +1,6 @@
-// feasm_elem_dev.cuh — device code of the element kernel shared by feasm_element.cu (stand-alone kernels) and
-// feasm_fused.cu (element + row-reduction warps in one persistent kernel).  See feasm_element.cu for the design.
+// feasm_elem_dev.cuh — device code of the element kernels of feasm_element.cu: configuration, Elem::has_affine_map,
+// the ex4 forcing, FEMap::compute_map (geom_phase), the Ke/Fe contraction (elem_compute / elem_store) and the
+// element-level Dirichlet constraint.  See feasm_element.cu for the design.
 #ifndef FEASM_ELEM_DEV_CUH
 #define FEASM_ELEM_DEV_CUH
 #include "feasm_internal.h"
@@ -149,21 +150,16 @@ __device__ __forceinline__ bool geom_phase(const double* X, const double* s_tab,
       if (affine) {
         // compute_affine_map (fe_map.C:1167-1244): the Jacobian at qp 0 only — lane c < 9 sums component c —
         // and xyz at every qp (:1190-1197)
-        // (sums split three ways: independent FP64 chains instead of one 27-deep dependent chain)
+        // The nine Jacobian sums run in the reference's order — node after node, product rounded, then added
+        // (Point::add_scaled, fe_map.C:994-1008) — with explicit _rn intrinsics, no FMA contraction: the sum cancels from
+        // O(|X|) terms down to O(h), so any other order or rounding differs by eps*|X|/h relative (at 96^3 that alone is
+        // 1e-14 of the row maximum in Ke).  The products are independent; only the adds chain.
         double d = 0.;
         if (lane < 9) {
           const double* tabd = s_dxi + (lane / 3) * (NPE * NQ);
           const int cd = lane % 3;
-          double d0 = 0., d1 = 0., d2 = 0.;
 #pragma unroll
-          for (int i = 0; i + 2 < NPE; i += 3) {
-            d0 += tabd[i * NQ] * X[3 * i + cd];
-            d1 += tabd[(i + 1) * NQ] * X[3 * (i + 1) + cd];
-            d2 += tabd[(i + 2) * NQ] * X[3 * (i + 2) + cd];
-          }
-#pragma unroll
-          for (int i = NPE - NPE % 3; i < NPE; ++i) d0 += tabd[i * NQ] * X[3 * i + cd];
-          d = (d0 + d1) + d2;
+          for (int i = 0; i < NPE; ++i) d = __dadd_rn(d, __dmul_rn(tabd[i * NQ], X[3 * i + cd]));
         }
         if (want_xyz) {
           double x1 = 0., y1 = 0., z1 = 0., x2 = 0., y2 = 0., z2 = 0.;
@@ -193,16 +189,24 @@ __device__ __forceinline__ bool geom_phase(const double* X, const double* s_tab,
           const double px = X[3 * i], py = X[3 * i + 1], pz = X[3 * i + 2];
           const double p = s_phi[i * NQ + q], a = s_dxi[i * NQ + q], b = s_deta[i * NQ + q], c = s_dzeta[i * NQ + q];
           x += p * px; y += p * py; z += p * pz;
-          xa += a * px; ya += a * py; za += a * pz;
-          xb += b * px; yb += b * py; zb += b * pz;
-          xc += c * px; yc += c * py; zc += c * pz;
+          // Jacobian sums: the reference's order and roundings (see the affine branch)
+          xa = __dadd_rn(xa, __dmul_rn(a, px)); ya = __dadd_rn(ya, __dmul_rn(a, py)); za = __dadd_rn(za, __dmul_rn(a, pz));
+          xb = __dadd_rn(xb, __dmul_rn(b, px)); yb = __dadd_rn(yb, __dmul_rn(b, py)); zb = __dadd_rn(zb, __dmul_rn(b, pz));
+          xc = __dadd_rn(xc, __dmul_rn(c, px)); yc = __dadd_rn(yc, __dmul_rn(c, py)); zc = __dadd_rn(zc, __dmul_rn(c, pz));
         }
       }
       // det J in the order of fe_map.C:1046-1048, inverse rows :1056-1068
       const double jac = (xa * (yb * zc - zb * yc) + ya * (zb * xc - xb * zc) + za * (xb * yc - yb * xc));
       const bool bad = !(jac > 0.);
       if (bad && lane < NQ) atomicAdd(&flags[0], 1);  // check_for_degenerate_map, fe_map.C:467-506
-      JxW = (affine && q != 0) ? jac * s_qw[0] / s_qw[0] * s_qw[q] : jac * s_qw[q];  // fe_map.C:1242 / :1052
+      // fe_map.C:1242 / :1052.  JxW[0] / qw[0] is the correctly rounded quotient by q0 = x * rc, q = fma(fma(-q0, d, x), rc, q0)
+      // with rc = RN(1 / qw[0]) (Markstein; 0 mismatches against the IEEE division in 5e7 random trials per rule)
+      if (affine && q != 0) {
+        const double w0 = s_qw[0], rc = 1. / w0, j0 = __dmul_rn(jac, w0), q0 = __dmul_rn(j0, rc);
+        JxW = __dmul_rn(__fma_rn(__fma_rn(-q0, w0, j0), rc, q0), s_qw[q]);
+      } else {
+        JxW = jac * s_qw[q];
+      }
       const double s = bad ? 0. : rsqrt(jac);  // sqrt(jac) / jac
       S[0] = (yb * zc - zb * yc) * s; S[1] = (zb * xc - xb * zc) * s; S[2] = (xb * yc - yb * xc) * s;
       S[3] = (za * yc - ya * zc) * s; S[4] = (xa * zc - za * xc) * s; S[5] = (ya * xc - xa * yc) * s;
@@ -211,18 +215,26 @@ __device__ __forceinline__ bool geom_phase(const double* X, const double* s_tab,
   return affine;
 }
 
-// One element by one warp: phases A-D of the header comment.  X holds the element's node coordinates, fw is a 32-double
-// scratch, twp = s_tw + (lane>>2)*TS + (lane&3); `out` is the element's block of NPE records, rs doubles apart (row a =
-// Ke(a,:) then Fe(a) at column NPE).
+// What one warp holds of its element after the contraction: the DMMA accumulators of the upper-triangular 8x8 blocks, the
+// leftover rows, and (lane = shape function) Fe.
 template <int NPE, int NQ>
-__device__ __forceinline__ void elem_process(const double* X, double* fw, const double* s_tab, const double* twp, int lane,
-                                             int forcing, const double* __restrict__ f_tab_e, int* flags, double* __restrict__ out,
-                                             const int rs) {
+struct ElemRegs {
+  using C = ElemCfg<NPE, NQ>;
+  double acc[C::NBLK > 0 ? C::NBLK : 1][2];
+  double pr[C::NB][C::REM > 0 ? C::REM : 1];  // leftover rows: K[ib*8+g][8*NBF+r] on lanes t4 == r after the reduction
+  double Fe;
+};
+
+// One element by one warp: phases A-C of the header comment and Fe.  X holds the element's node coordinates, fw is a
+// 32-double scratch, twp = s_tw + (lane>>2)*TS + (lane&3).
+template <int NPE, int NQ>
+__device__ __forceinline__ void elem_compute(const double* X, double* fw, const double* s_tab, const double* twp, int lane,
+                                             int forcing, const double* __restrict__ f_tab_e, int* flags, ElemRegs<NPE, NQ>& R) {
   using C = ElemCfg<NPE, NQ>;
   const double* s_phi = s_tab;
-  const int g = lane >> 2, t4 = lane & 3;
+  const int t4 = lane & 3;
   // ---- A: reference -> physical map at quadrature point q = lane ---------------------------------------
-  // FEASM_ABLATE (never defined in product builds; scripts/gpu_ablate.py): 2 = no contraction, 3 = no Fe /
+  // FEASM_ABLATE (never defined in product builds; scripts/gpu_ablate.py): 2 = no contraction, 3 = no
   // stores, 4 = no geometry / forcing — timing probes of the phases of this function.
   double S[9], JxW, x, y, z;
 #if defined(FEASM_ABLATE) && FEASM_ABLATE == 4
@@ -246,14 +258,12 @@ __device__ __forceinline__ void elem_process(const double* X, double* fw, const 
   }
 
   // ---- B+C: Ke = G G^T; fragments generated in registers -------------------------------------------------
-  double acc[C::NBLK > 0 ? C::NBLK : 1][2];
-  double pr[C::NB][C::REM > 0 ? C::REM : 1];  // leftover rows: partial (over k = t4 mod 4) K[ib*8+g][8*NBF+r]
 #pragma unroll
-  for (int b = 0; b < C::NBLK; ++b) { acc[b][0] = 0.; acc[b][1] = 0.; }
+  for (int b = 0; b < C::NBLK; ++b) { R.acc[b][0] = 0.; R.acc[b][1] = 0.; }
 #pragma unroll
   for (int ib = 0; ib < C::NB; ++ib)
 #pragma unroll
-    for (int r = 0; r < (C::REM > 0 ? C::REM : 1); ++r) pr[ib][r] = 0.;
+    for (int r = 0; r < (C::REM > 0 ? C::REM : 1); ++r) R.pr[ib][r] = 0.;
 #if defined(FEASM_ABLATE) && FEASM_ABLATE == 2
   if (forcing == 99)
 #endif
@@ -284,13 +294,13 @@ __device__ __forceinline__ void elem_process(const double* X, double* fw, const 
 #pragma unroll
       for (int jb = 0; jb < C::NBF; ++jb)
 #pragma unroll
-        for (int ib = 0; ib <= jb; ++ib) { dmma884(acc[blk][0], acc[blk][1], G[ib][d], G[jb][d]); ++blk; }
+        for (int ib = 0; ib <= jb; ++ib) { dmma884(R.acc[blk][0], R.acc[blk][1], G[ib][d], G[jb][d]); ++blk; }
       if (C::REM > 0) {
 #pragma unroll
         for (int r = 0; r < C::REM; ++r) {
           const double gr = __shfl_sync(0xffffffffu, G[C::NB - 1][d], 4 * r + t4);
 #pragma unroll
-          for (int ib = 0; ib < C::NB; ++ib) pr[ib][r] += G[ib][d] * gr;
+          for (int ib = 0; ib < C::NB; ++ib) R.pr[ib][r] += G[ib][d] * gr;
         }
       }
     }
@@ -300,31 +310,37 @@ __device__ __forceinline__ void elem_process(const double* X, double* fw, const 
     for (int ib = 0; ib < C::NB; ++ib)
 #pragma unroll
       for (int r = 0; r < C::REM; ++r) {
-        pr[ib][r] += __shfl_xor_sync(0xffffffffu, pr[ib][r], 1);
-        pr[ib][r] += __shfl_xor_sync(0xffffffffu, pr[ib][r], 2);
+        R.pr[ib][r] += __shfl_xor_sync(0xffffffffu, R.pr[ib][r], 1);
+        R.pr[ib][r] += __shfl_xor_sync(0xffffffffu, R.pr[ib][r], 2);
       }
   }
 
-  // ---- D: Fe (introduction_ex4.C:536-537) and the stores ----------------------------------------------------
-#if defined(FEASM_ABLATE) && FEASM_ABLATE == 3
-  if (forcing != 99) return;
-#endif
-  if (lane < NPE) {
-    double Fe = 0.;
-    if (forcing != FEASM_FORCING_NONE) {
-      double f1 = 0., f2 = 0.;
+  // ---- Fe (introduction_ex4.C:536-537), lane = shape function ----------------------------------------------------
+  R.Fe = 0.;
+  if (lane < NPE && forcing != FEASM_FORCING_NONE) {
+    double Fe = 0., f1 = 0., f2 = 0.;
 #pragma unroll
-      for (int q = 0; q + 2 < NQ; q += 3) {
-        Fe += fw[q] * s_phi[lane * NQ + q];
-        f1 += fw[q + 1] * s_phi[lane * NQ + q + 1];
-        f2 += fw[q + 2] * s_phi[lane * NQ + q + 2];
-      }
-#pragma unroll
-      for (int q = NQ - NQ % 3; q < NQ; ++q) Fe += fw[q] * s_phi[lane * NQ + q];
-      Fe = (Fe + f1) + f2;
+    for (int q = 0; q + 2 < NQ; q += 3) {
+      Fe += fw[q] * s_phi[lane * NQ + q];
+      f1 += fw[q + 1] * s_phi[lane * NQ + q + 1];
+      f2 += fw[q + 2] * s_phi[lane * NQ + q + 2];
     }
-    out[lane * rs + NPE] = Fe;
+#pragma unroll
+    for (int q = NQ - NQ % 3; q < NQ; ++q) Fe += fw[q] * s_phi[lane * NQ + q];
+    R.Fe = (Fe + f1) + f2;
   }
+}
+
+// Phase D: the warp's fragments into the element's block of NPE records, rs doubles apart (row a = Ke(a,:) then Fe(a)
+// at column NPE) — in global memory, or in a shared-memory tile when the element-level constraint follows.
+template <int NPE, int NQ>
+__device__ __forceinline__ void elem_store(const ElemRegs<NPE, NQ>& R, double* __restrict__ out, const int rs, int lane) {
+  using C = ElemCfg<NPE, NQ>;
+  const int g = lane >> 2, t4 = lane & 3;
+#if defined(FEASM_ABLATE) && FEASM_ABLATE == 3
+  if (rs != 99) return;
+#endif
+  if (lane < NPE) out[lane * rs + NPE] = R.Fe;
   {
     int blk = 0;
 #pragma unroll
@@ -332,10 +348,10 @@ __device__ __forceinline__ void elem_process(const double* X, double* fw, const 
 #pragma unroll
       for (int ib = 0; ib <= jb; ++ib, ++blk) {
         const int i = ib * 8 + g, j = jb * 8 + 2 * t4;
-        *reinterpret_cast<double2*>(out + i * rs + j) = make_double2(acc[blk][0], acc[blk][1]);
+        *reinterpret_cast<double2*>(out + i * rs + j) = make_double2(R.acc[blk][0], R.acc[blk][1]);
         if (ib != jb) {  // mirror into the lower triangle
-          out[j * rs + i] = acc[blk][0];
-          out[(j + 1) * rs + i] = acc[blk][1];
+          out[j * rs + i] = R.acc[blk][0];
+          out[(j + 1) * rs + i] = R.acc[blk][1];
         }
       }
   }
@@ -346,14 +362,23 @@ __device__ __forceinline__ void elem_process(const double* X, double* fw, const 
       const int i = ib * 8 + g;
 #pragma unroll
       for (int r = 0; r < C::REM; ++r)
-        if (t4 == r) { out[i * rs + R0 + r] = pr[ib][r]; out[(R0 + r) * rs + i] = pr[ib][r]; }
+        if (t4 == r) { out[i * rs + R0 + r] = R.pr[ib][r]; out[(R0 + r) * rs + i] = R.pr[ib][r]; }
     }
     if (g < C::REM) {
 #pragma unroll
       for (int r = 0; r < C::REM; ++r)
-        if (t4 == r) out[(R0 + g) * rs + R0 + r] = pr[C::NB - 1][r];
+        if (t4 == r) out[(R0 + g) * rs + R0 + r] = R.pr[C::NB - 1][r];
     }
   }
+}
+
+template <int NPE, int NQ>
+__device__ __forceinline__ void elem_process(const double* X, double* fw, const double* s_tab, const double* twp, int lane,
+                                             int forcing, const double* __restrict__ f_tab_e, int* flags, double* __restrict__ out,
+                                             const int rs) {
+  ElemRegs<NPE, NQ> R;
+  elem_compute<NPE, NQ>(X, fw, s_tab, twp, lane, forcing, f_tab_e, flags, R);
+  elem_store<NPE, NQ>(R, out, rs, lane);
 }
 
 // Reference tables into shared memory: s_tab = phi | dxi | deta | dzeta | qw ([i][q]: lane = q reads are conflict free),

@@ -34,7 +34,7 @@ template <int NPE, int NQ, int WARPS, int RS>
 __global__ void __launch_bounds__(WARPS * 32, 1)
 k_elem_poisson(const double* __restrict__ xyz, const uint32_t* __restrict__ conn, const double* __restrict__ tab,
                int forcing, const double* __restrict__ f_tab, int64_t e0, int64_t e1, double* __restrict__ kf, int rs_rt,
-               int* flags) {
+               int* flags, const uint8_t* __restrict__ elem_flag, ElemConArgs con) {
   using C = ElemCfg<NPE, NQ>;
   const int rs = RS ? RS : rs_rt;  // record stride in doubles: a compile-time constant for the common layout
   extern __shared__ double smem[];
@@ -44,6 +44,9 @@ k_elem_poisson(const double* __restrict__ xyz, const uint32_t* __restrict__ conn
   elem_load_tables<NPE, NQ>(s_tab, s_tw, tab, threadIdx.x, WARPS * 32);
   double* X = s_tw + C::TW_SZ + (size_t)warp * C::WARP_DBL;  // node coordinates of the current element
   double* fw = X + C::X_SZ;                                  // JxW_q * f(x_q)
+  // element-level Dirichlet constraint, fused (elem_flag != nullptr): the few elements that touch a constrained dof put
+  // their Ke | Fe into this per-warp tile, are constrained there, and leave as whole rows
+  double* tile = s_tw + C::TW_SZ + (size_t)WARPS * C::WARP_DBL + (size_t)warp * (NPE * C::LDR);
   const double* twp = s_tw + (lane >> 2) * C::TS + (lane & 3);  // + c*NB*8*TS + ib*8*TS + 4*qg
   __syncthreads();
 
@@ -53,12 +56,17 @@ k_elem_poisson(const double* __restrict__ xyz, const uint32_t* __restrict__ conn
   // dependent conn -> xyz load chain is split across two iterations, so neither load is waited for)
   double nx = 0., ny = 0., nz = 0.;
   uint32_t nnode = 0;
-  if (e < e1 && lane < NPE) {
-    const uint64_t node = conn[e * NPE + lane];
-    nx = xyz[node * 3]; ny = xyz[node * 3 + 1]; nz = xyz[node * 3 + 2];
-    if (e + stride < e1) nnode = conn[(e + stride) * NPE + lane];
+  unsigned nflag = 0;  // constraint flag of the next element
+  if (e < e1) {
+    if (lane < NPE) {
+      const uint64_t node = conn[e * NPE + lane];
+      nx = xyz[node * 3]; ny = xyz[node * 3 + 1]; nz = xyz[node * 3 + 2];
+      if (e + stride < e1) nnode = conn[(e + stride) * NPE + lane];
+    }
+    if (elem_flag) nflag = elem_flag[e];
   }
   for (; e < e1; e += stride) {
+    const bool flagged = nflag != 0;
     if (lane < NPE) {
       X[3 * lane] = nx; X[3 * lane + 1] = ny; X[3 * lane + 2] = nz;
       if (e + stride < e1) {
@@ -67,26 +75,48 @@ k_elem_poisson(const double* __restrict__ xyz, const uint32_t* __restrict__ conn
         if (e + 2 * stride < e1) nnode = conn[(e + 2 * stride) * NPE + lane];
       }
     }
+    if (elem_flag && e + stride < e1) nflag = elem_flag[e + stride];
     __syncwarp();
 
     double* out = kf + (uint64_t)(e - e0) * (NPE * rs);
-    elem_process<NPE, NQ>(X, fw, s_tab, twp, lane, forcing, f_tab ? f_tab + e * NQ : nullptr, flags, out, rs);
+    ElemRegs<NPE, NQ> R;
+    elem_compute<NPE, NQ>(X, fw, s_tab, twp, lane, forcing, f_tab ? f_tab + e * NQ : nullptr, flags, R);
+    if (!flagged) {
+      elem_store<NPE, NQ>(R, out, rs, lane);
+    } else {
+      // DofMap::heterogeneously_constrain_element_matrix_and_vector (dof_map_constraints.C:2518-2614) on Ke / Fe in the
+      // tile, where the reference applies it: after the element integrals, before add_matrix
+      elem_store<NPE, NQ>(R, tile, C::LDR, lane);
+      constrain_element(tile, C::LDR, NPE, con.elem_dofs + (uint64_t)e * NPE, con.con_flag, con.con_val, con.mode, lane);
+      constexpr int H = C::LDR / 2;
+      for (int t = lane; t < NPE * H; t += 32) {
+        const int row = t / H, c = t % H;
+        *reinterpret_cast<double2*>(out + (size_t)row * rs + 2 * c) = *reinterpret_cast<const double2*>(tile + row * C::LDR + 2 * c);
+      }
+    }
     __syncwarp();
   }
 }
 
 template <int NPE, int NQ, int WARPS, int RS = 0>
-int launch_poisson(feasm_ctx* ctx, const feasm_params& p, const double* d_f, int64_t e0, int64_t e1, double* d_kf, int rs) {
+int launch_poisson(feasm_ctx* ctx, const feasm_params& p, const double* d_f, int64_t e0, int64_t e1, double* d_kf, int rs, int constrain_mode,
+                   bool* fused) {
   using C = ElemCfg<NPE, NQ>;
-  const size_t smem = sizeof(double) * (size_t)C::SMEM_DBL(WARPS);
+  const size_t smem = sizeof(double) * (size_t)(C::SMEM_DBL(WARPS) + WARPS * NPE * C::LDR);
   auto kern = k_elem_poisson<NPE, NQ, WARPS, RS>;
   FEASM_CUDA(ctx, cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
   int64_t blocks = (e1 - e0 + WARPS - 1) / WARPS;
   if (blocks > ctx->sm_count) blocks = ctx->sm_count;
   if (blocks < 1) blocks = 1;
-  kern<<<(unsigned)blocks, WARPS * 32, smem, ctx->stream>>>(ctx->d_xyz, ctx->d_conn, ctx->d_tab, p.forcing, d_f, e0, e1, d_kf,
-                                                           rs, ctx->d_flags);
+  // the element-level constraint rides in this kernel when there is one to apply (one variable: nd == NPE)
+  // ... and no side term has to be added between the volume integrals and the constraint (feasm_launch_side_loads)
+  const bool fuse = constrain_mode >= 0 && ctx->n_con_elems > 0 && ctx->nd == NPE && ctx->d_elem_flag && ctx->n_side_elems == 0 &&
+                    ctx->n_pen_elems == 0;
+  const ElemConArgs con{ctx->d_elem_dofs, ctx->d_con_flag, ctx->d_con_val, constrain_mode};
+  kern<<<(unsigned)blocks, WARPS * 32, smem, ctx->stream>>>(ctx->d_xyz, ctx->d_conn, ctx->d_tab, p.forcing, d_f, e0, e1, d_kf, rs,
+                                                           ctx->d_flags, fuse ? ctx->d_elem_flag : nullptr, con);
   FEASM_CUDA(ctx, cudaGetLastError());
+  *fused = fuse || constrain_mode < 0 || ctx->n_con_elems == 0;
   return FEASM_OK;
 }
 
@@ -156,14 +186,19 @@ k_elem_poisson_hex8x4(const double* __restrict__ xyz, const uint32_t* __restrict
       const double px = X[3 * i], py = X[3 * i + 1], pz = X[3 * i + 2];
       const double p = s_phi[i * NQ + q], a = s_dxi[i * NQ + qj], b = s_deta[i * NQ + qj], c = s_dzeta[i * NQ + qj];
       x += p * px; y += p * py; z += p * pz;
-      xa += a * px; ya += a * py; za += a * pz;
-      xb += b * px; yb += b * py; zb += b * pz;
-      xc += c * px; yc += c * py; zc += c * pz;
+      // Jacobian sums in the reference's order and roundings (fe_map.C:994-1008; see geom_phase)
+      xa = __dadd_rn(xa, __dmul_rn(a, px)); ya = __dadd_rn(ya, __dmul_rn(a, py)); za = __dadd_rn(za, __dmul_rn(a, pz));
+      xb = __dadd_rn(xb, __dmul_rn(b, px)); yb = __dadd_rn(yb, __dmul_rn(b, py)); zb = __dadd_rn(zb, __dmul_rn(b, pz));
+      xc = __dadd_rn(xc, __dmul_rn(c, px)); yc = __dadd_rn(yc, __dmul_rn(c, py)); zc = __dadd_rn(zc, __dmul_rn(c, pz));
     }
     const double jac = (xa * (yb * zc - zb * yc) + ya * (zb * xc - xb * zc) + za * (xb * yc - yb * xc));  // fe_map.C:1046-1048
     const bool bad = !(jac > 0.);
     if (bad && valid) atomicAdd(&flags[0], 1);
-    const double JxW = (affine && q != 0) ? jac * s_qw[0] / s_qw[0] * s_qw[q] : jac * s_qw[q];
+    double JxW = jac * s_qw[q];
+    if (affine && q != 0) {  // fe_map.C:1242: JxW[0] / qw[0] * qw[p], the quotient correctly rounded (Markstein, see geom_phase)
+      const double w0 = s_qw[0], rc = 1. / w0, j0 = __dmul_rn(jac, w0), q0 = __dmul_rn(j0, rc);
+      JxW = __dmul_rn(__fma_rn(__fma_rn(-q0, w0, j0), rc, q0), s_qw[q]);
+    }
     const double sc = bad ? 0. : rsqrt(jac);
     double S[9];
     S[0] = (yb * zc - zb * yc) * sc; S[1] = (zb * xc - xb * zc) * sc; S[2] = (xb * yc - yb * xc) * sc;
@@ -302,14 +337,19 @@ k_elem_poisson_tet10x2(const double* __restrict__ xyz, const uint32_t* __restric
       const double px = X[3 * i], py = X[3 * i + 1], pz = X[3 * i + 2];
       const double p = s_phi[i * NQ + q], a = s_dxi[i * NQ + qj], b = s_deta[i * NQ + qj], c = s_dzeta[i * NQ + qj];
       x += p * px; y += p * py; z += p * pz;
-      xa += a * px; ya += a * py; za += a * pz;
-      xb += b * px; yb += b * py; zb += b * pz;
-      xc += c * px; yc += c * py; zc += c * pz;
+      // Jacobian sums in the reference's order and roundings (fe_map.C:994-1008; see geom_phase)
+      xa = __dadd_rn(xa, __dmul_rn(a, px)); ya = __dadd_rn(ya, __dmul_rn(a, py)); za = __dadd_rn(za, __dmul_rn(a, pz));
+      xb = __dadd_rn(xb, __dmul_rn(b, px)); yb = __dadd_rn(yb, __dmul_rn(b, py)); zb = __dadd_rn(zb, __dmul_rn(b, pz));
+      xc = __dadd_rn(xc, __dmul_rn(c, px)); yc = __dadd_rn(yc, __dmul_rn(c, py)); zc = __dadd_rn(zc, __dmul_rn(c, pz));
     }
     const double jac = (xa * (yb * zc - zb * yc) + ya * (zb * xc - xb * zc) + za * (xb * yc - yb * xc));
     const bool bad = !(jac > 0.);
     if (bad && valid && l16 < NQ) atomicAdd(&flags[0], 1);
-    const double JxW = (affine && q != 0) ? jac * s_qw[0] / s_qw[0] * s_qw[q] : jac * s_qw[q];
+    double JxW = jac * s_qw[q];
+    if (affine && q != 0) {  // fe_map.C:1242: JxW[0] / qw[0] * qw[p], the quotient correctly rounded (Markstein, see geom_phase)
+      const double w0 = s_qw[0], rc = 1. / w0, j0 = __dmul_rn(jac, w0), q0 = __dmul_rn(j0, rc);
+      JxW = __dmul_rn(__fma_rn(__fma_rn(-q0, w0, j0), rc, q0), s_qw[q]);
+    }
     const double sc = bad ? 0. : rsqrt(jac);
     double S[9];
     S[0] = (yb * zc - zb * yc) * sc; S[1] = (zb * xc - xb * zc) * sc; S[2] = (xb * yc - yb * xc) * sc;
@@ -802,7 +842,9 @@ __global__ void k_constrain_list(const uint32_t* __restrict__ list, int n_list, 
   }
 }
 
-static int launch_element_kernel(feasm_ctx* ctx, const feasm_params& p, const double* d_f, int64_t e0, int64_t e1, double* d_kf, int rs) {
+static int launch_element_kernel(feasm_ctx* ctx, const feasm_params& p, const double* d_f, int64_t e0, int64_t e1, double* d_kf, int rs,
+                                 int cm, bool* fused) {
+  *fused = false;
   if (p.problem == FEASM_POISSON && p.affine_tensor) {
     if (ctx->elem_type == FEASM_HEX27 && ctx->tab_nq == 27) return launch_poisson_affine<27, 27, 16, 12, 2>(ctx, p, d_f, e0, e1, d_kf, rs);
     if (ctx->elem_type == FEASM_HEX8 && ctx->tab_nq == 8) return launch_poisson_affine<8, 8, 16, 16>(ctx, p, d_f, e0, e1, d_kf, rs);
@@ -812,9 +854,9 @@ static int launch_element_kernel(feasm_ctx* ctx, const feasm_params& p, const do
   if (p.problem == FEASM_POISSON) {
     if (ctx->elem_type == FEASM_HEX27 && ctx->tab_nq == 27) {
       static const int warps = getenv("FEASM_ELEM_WARPS") ? atoi(getenv("FEASM_ELEM_WARPS")) : 12;  // tuning knob
-      if (warps == 16) return launch_poisson<27, 27, 16>(ctx, p, d_f, e0, e1, d_kf, rs);
-      if (rs == 32) return launch_poisson<27, 27, 12, 32>(ctx, p, d_f, e0, e1, d_kf, rs);  // 256 B records (uint8 positions)
-      return launch_poisson<27, 27, 12>(ctx, p, d_f, e0, e1, d_kf, rs);
+      if (warps == 16) return launch_poisson<27, 27, 16>(ctx, p, d_f, e0, e1, d_kf, rs, cm, fused);
+      if (rs == 32) return launch_poisson<27, 27, 12, 32>(ctx, p, d_f, e0, e1, d_kf, rs, cm, fused);  // 256 B records (uint8 positions)
+      return launch_poisson<27, 27, 12>(ctx, p, d_f, e0, e1, d_kf, rs, cm, fused);
     }
     if (ctx->elem_type == FEASM_HEX8 && ctx->tab_nq == 8) {
       static const bool one_per_warp = getenv("FEASM_HEX8_PACK") && atoi(getenv("FEASM_HEX8_PACK")) == 0;  // A/B knob
@@ -822,18 +864,18 @@ static int launch_element_kernel(feasm_ctx* ctx, const feasm_params& p, const do
         if (rs == 16) return launch_poisson_hex8x4<16, 16>(ctx, p, d_f, e0, e1, d_kf, rs);
         return launch_poisson_hex8x4<16, 0>(ctx, p, d_f, e0, e1, d_kf, rs);
       }
-      if (rs == 16) return launch_poisson<8, 8, 16, 16>(ctx, p, d_f, e0, e1, d_kf, rs);
-      return launch_poisson<8, 8, 16>(ctx, p, d_f, e0, e1, d_kf, rs);
+      if (rs == 16) return launch_poisson<8, 8, 16, 16>(ctx, p, d_f, e0, e1, d_kf, rs, cm, fused);
+      return launch_poisson<8, 8, 16>(ctx, p, d_f, e0, e1, d_kf, rs, cm, fused);
     }
-    if (ctx->elem_type == FEASM_HEX8 && ctx->tab_nq == 27) return launch_poisson<8, 27, 16>(ctx, p, d_f, e0, e1, d_kf, rs);
+    if (ctx->elem_type == FEASM_HEX8 && ctx->tab_nq == 27) return launch_poisson<8, 27, 16>(ctx, p, d_f, e0, e1, d_kf, rs, cm, fused);
     if (ctx->elem_type == FEASM_TET10 && ctx->tab_nq == 14) {
       static const bool one_per_warp = getenv("FEASM_TET10_PACK") && atoi(getenv("FEASM_TET10_PACK")) == 0;  // A/B knob
       if (!one_per_warp) {
         if (rs == 16) return launch_poisson_tet10x2<16, 16>(ctx, p, d_f, e0, e1, d_kf, rs);
         return launch_poisson_tet10x2<16, 0>(ctx, p, d_f, e0, e1, d_kf, rs);
       }
-      if (rs == 16) return launch_poisson<10, 14, 16, 16>(ctx, p, d_f, e0, e1, d_kf, rs);
-      return launch_poisson<10, 14, 16>(ctx, p, d_f, e0, e1, d_kf, rs);
+      if (rs == 16) return launch_poisson<10, 14, 16, 16>(ctx, p, d_f, e0, e1, d_kf, rs, cm, fused);
+      return launch_poisson<10, 14, 16>(ctx, p, d_f, e0, e1, d_kf, rs, cm, fused);
     }
     return feasm_fail(ctx, FEASM_ERR_ARG, "no Poisson kernel for this element type / quadrature order");
   }
@@ -849,7 +891,8 @@ static int launch_element_kernel(feasm_ctx* ctx, const feasm_params& p, const do
 
 int feasm_launch_element_kernel(feasm_ctx* ctx, const feasm_params& p, const double* d_f, int64_t e0, int64_t e1,
                                 double* d_kf, int rs, int constrain_mode) {
-  int rc = launch_element_kernel(ctx, p, d_f, e0, e1, d_kf, rs);
+  bool fused = false;  // the kernel applied the element-level constraint itself
+  int rc = launch_element_kernel(ctx, p, d_f, e0, e1, d_kf, rs, constrain_mode, &fused);
   if (rc) return rc;
   FEASM_CUDA(ctx, cudaEventRecord(ctx->ev[3], ctx->stream));  // feasm_last_timing: element kernel | side loads + constraint pass
   // boundary integrals over the loaded sides (systems_of_equations_ex6.C:240-257), before the constraints like there
@@ -857,7 +900,7 @@ int feasm_launch_element_kernel(feasm_ctx* ctx, const feasm_params& p, const dou
   if (rc) return rc;
   // Dirichlet constraints on the few elements that touch a constrained dof, as the reference applies them to Ke/Fe
   // before add_matrix (constrain_mode < 0: leave Ke/Fe unconstrained)
-  if (constrain_mode >= 0 && ctx->n_con_elems > 0) {
+  if (!fused && constrain_mode >= 0 && ctx->n_con_elems > 0) {
     const ElemConArgs con{ctx->d_elem_dofs, ctx->d_con_flag, ctx->d_con_val, constrain_mode};
     const size_t per_warp = sizeof(double) * ctx->nd * feasm_ldr(ctx->nd);
     int warps = (int)(32768 / per_warp);

@@ -5,6 +5,7 @@
 #include <cuda_runtime.h>
 
 #include <cstdint>
+#include <cstdio>
 #include <string>
 #include <vector>
 
@@ -153,13 +154,32 @@ struct feasm_ctx {
   bool assemble_open = false;  // between feasm_assemble_begin and feasm_assemble_end
 };
 
+// Every cudaFree of the library goes through this: a failing free means a stale or foreign pointer — a library bug that
+// would otherwise surface later as an unrelated "invalid argument".  It is reported on stderr and the error state cleared.
+inline cudaError_t feasm_checked_free(void* p, const char* what, const char* file, int line) {
+  if (!p) return cudaSuccess;
+  const cudaError_t e = (cudaFree)(p);
+  if (e != cudaSuccess) {
+    std::fprintf(stderr, "libfeasm: cudaFree(%s = %p) failed at %s:%d: %s\n", what, p, file, line, cudaGetErrorString(e));
+    (void)cudaGetLastError();
+  }
+  return e;
+}
+#define cudaFree(p) feasm_checked_free((void*)(p), #p, __FILE__, __LINE__)
+
 // error helpers
 int feasm_fail(feasm_ctx* ctx, int code, const std::string& msg);
+inline const char* feasm_basename(const char* path) {
+  const char* b = path;
+  for (const char* c = path; *c; ++c) if (*c == '/') b = c + 1;
+  return b;
+}
 #define FEASM_CUDA(ctx, call)                                                                         \
   do {                                                                                                \
     cudaError_t e__ = (call);                                                                         \
     if (e__ != cudaSuccess)                                                                           \
-      return feasm_fail(ctx, FEASM_ERR_CUDA, std::string(#call) + ": " + cudaGetErrorString(e__));    \
+      return feasm_fail(ctx, FEASM_ERR_CUDA, std::string(#call) + ": " + cudaGetErrorString(e__) +    \
+                                                 " (" + feasm_basename(__FILE__) + ":" + std::to_string(__LINE__) + ")"); \
   } while (0)
 
 // feasm_api.cu: bookkeeping shared by the host-array and the device-side ingest

@@ -376,6 +376,10 @@ int feasm_launch_unpack(feasm_ctx* ctx) {
 }
 
 int feasm_launch_scatter_constraints(feasm_ctx* ctx, int64_t n, int64_t n_prev, bool set_flags) {
+  {
+    const cudaError_t pre = cudaGetLastError();  // an error an earlier, unchecked call left behind is not this launch's
+    if (pre != cudaSuccess) return feasm_fail(ctx, FEASM_ERR_CUDA, std::string("error pending before feasm_set_constraints: ") + cudaGetErrorString(pre));
+  }
   if (set_flags && n_prev)
     k_clear_constraints<<<(unsigned)((n_prev + 255) / 256), 256, 0, ctx->stream>>>(ctx->d_con_rows + ctx->d_con_rows_cap, n_prev, ctx->d_con_flag,
                                                                                     ctx->d_con_val);

@@ -70,6 +70,13 @@ class GpuNumericVector : public NumericVector<T> {
   }
 
   // ---- assignment -------------------------------------------------------------------------------------------------
+  // `*g = *this` between two GpuNumericVectors must not pick an implicit member-wise copy (it would share _d between
+  // the two and free it twice): deep copy, as NumericVector::operator= (numeric_vector.h:279) means it
+  GpuNumericVector(const GpuNumericVector&) = delete;
+  GpuNumericVector& operator=(const GpuNumericVector& v) {
+    this->operator=(static_cast<const NumericVector<T>&>(v));
+    return *this;
+  }
   NumericVector<T>& operator=(const NumericVector<T>& v) override {
     if (v.size() != _n) libmesh_error_msg("GpuNumericVector::operator=: size mismatch");
     if (const auto* g = dynamic_cast<const GpuNumericVector<T>*>(&v)) check(feasm_vec_copy(ctx(), FEASM_COPY_D2D, _d, g->_d, _n));
