@@ -125,11 +125,11 @@ int feasm_create(int device, feasm_ctx** out) {
     return feasm_fail(nullptr, FEASM_ERR_CUDA, cudaGetErrorString(e));
   }
   for (auto& ev : ctx->ev) cudaEventCreate(&ev);
-  if (cudaMalloc(&ctx->d_flags, 2 * sizeof(int)) != cudaSuccess) {
+  if (cudaMalloc(&ctx->d_flags, 4 * sizeof(int)) != cudaSuccess) {  // [0..1] flags, [2] the element kernel's ticket counter
     delete ctx;
     return feasm_fail(nullptr, FEASM_ERR_CUDA, "cudaMalloc failed");
   }
-  cudaMemset(ctx->d_flags, 0, 2 * sizeof(int));
+  cudaMemset(ctx->d_flags, 0, 4 * sizeof(int));
   *out = ctx;
   return FEASM_OK;
 }

@@ -158,8 +158,21 @@ __device__ __forceinline__ bool geom_phase(const double* X, const double* s_tab,
         if (lane < 9) {
           const double* tabd = s_dxi + (lane / 3) * (NPE * NQ);
           const int cd = lane % 3;
+#ifdef FEASM_DEV_JAC3
+          double d0 = 0., d1 = 0., d2 = 0.;
+#pragma unroll
+          for (int i = 0; i + 2 < NPE; i += 3) {
+            d0 += tabd[i * NQ] * X[3 * i + cd];
+            d1 += tabd[(i + 1) * NQ] * X[3 * (i + 1) + cd];
+            d2 += tabd[(i + 2) * NQ] * X[3 * (i + 2) + cd];
+          }
+#pragma unroll
+          for (int i = NPE - NPE % 3; i < NPE; ++i) d0 += tabd[i * NQ] * X[3 * i + cd];
+          d = (d0 + d1) + d2;
+#else
 #pragma unroll
           for (int i = 0; i < NPE; ++i) d = __dadd_rn(d, __dmul_rn(tabd[i * NQ], X[3 * i + cd]));
+#endif
         }
         if (want_xyz) {
           double x1 = 0., y1 = 0., z1 = 0., x2 = 0., y2 = 0., z2 = 0.;
@@ -392,6 +405,31 @@ __device__ __forceinline__ void elem_load_tables(double* s_tab, double* s_tw, co
     s_tw[t] = (row < NPE && q < NQ) ? sqrt(tab[4 * NPE * NQ + q]) * tab[(1 + c) * NPE * NQ + row * NQ + q] : 0.;
   }
 }
+// The same constraint for one variable per node (nd = NPE <= 32) on a shared-memory tile T[NPE][LDR] (row a = Ke(a,:), Fe(a) at
+// column NPE), with the element's constraint data already in registers: lane a holds "dof a is constrained" (bit a of
+// `mask`) and its value g_a (0 when homogeneous).  Same operations in the same order as constrain_element below.
+template <int NPE, int LDR>
+__device__ __forceinline__ void constrain_tile(double* T, const unsigned mask, const double g_lane, const int lane) {
+  constexpr unsigned FULL = 0xffffffffu;
+  __syncwarp();  // the tile was written by other lanes
+  const int row = lane < NPE ? lane : 0;
+  double fe = T[row * LDR + NPE];
+  for (unsigned m = mask; m; m &= m - 1) {  // constrained columns: K(i,j) -> 0, F(i) -= K(i,j) g_j
+    const int j = __ffs(m) - 1;
+    const double g = __shfl_sync(FULL, g_lane, j);
+    const double kij = T[row * LDR + j];
+    if (lane < NPE) T[row * LDR + j] = 0.;
+    fe -= kij * g;
+  }
+  __syncwarp();
+  for (unsigned m = mask; m; m &= m - 1) {  // constrained rows: K(i,:) = e_i
+    const int i = __ffs(m) - 1;
+    if (lane < NPE) T[i * LDR + lane] = lane == i ? 1. : 0.;
+  }
+  if (lane < NPE) T[lane * LDR + NPE] = ((mask >> lane) & 1u) ? g_lane : fe;  // F(i) = g_i on constrained rows
+  __syncwarp();
+}
+
 // Dirichlet constraints at element level, in place on the element's records right after they were written (called by
 // the whole warp for the few elements that touch a constrained dof).  This is
 // DofMap::heterogeneously_constrain_element_matrix_and_vector (dof_map_constraints.C:2518-2614) /

@@ -34,7 +34,7 @@ template <int NPE, int NQ, int WARPS, int RS>
 __global__ void __launch_bounds__(WARPS * 32, 1)
 k_elem_poisson(const double* __restrict__ xyz, const uint32_t* __restrict__ conn, const double* __restrict__ tab,
                int forcing, const double* __restrict__ f_tab, int64_t e0, int64_t e1, double* __restrict__ kf, int rs_rt,
-               int* flags, const uint8_t* __restrict__ elem_flag, ElemConArgs con) {
+               int* flags, const uint8_t* __restrict__ elem_flag, ElemConArgs con, unsigned* ticket) {
   using C = ElemCfg<NPE, NQ>;
   const int rs = RS ? RS : rs_rt;  // record stride in doubles: a compile-time constant for the common layout
   extern __shared__ double smem[];
@@ -50,35 +50,62 @@ k_elem_poisson(const double* __restrict__ xyz, const uint32_t* __restrict__ conn
   const double* twp = s_tw + (lane >> 2) * C::TS + (lane & 3);  // + c*NB*8*TS + ib*8*TS + 4*qg
   __syncthreads();
 
-  const int64_t stride = (int64_t)gridDim.x * WARPS;
-  int64_t e = e0 + (int64_t)blockIdx.x * WARPS + warp;
-  // prefetch registers: coordinates of node `lane` of the next element, node id of the element after it (the
-  // dependent conn -> xyz load chain is split across two iterations, so neither load is waited for)
+  // Elements are dealt out by a ticket counter, one element per ticket (dynamic: a static round-robin puts every
+  // boundary element of a structured mesh on the same few warps whenever the stride and a mesh dimension share a factor,
+  // and boundary elements cost more — the constraint below).  Three tickets are in flight per warp: the element being
+  // computed (coordinates in registers), the next one (node ids in registers), and one whose ticket is being fetched,
+  // so neither the atomic nor the dependent conn -> xyz load chain is waited for.
+  const int64_t n_todo = e1 - e0;
+#ifdef FEASM_DEV_STATIC  // development A/B: static round-robin
+  int64_t next_static = (int64_t)blockIdx.x * WARPS + warp;
+  auto take = [&]() -> int64_t { const int64_t t = next_static; next_static += (int64_t)gridDim.x * WARPS; return t; };
+#else
+  auto take = [&]() -> int64_t {
+    unsigned t = 0;
+    if (lane == 0) t = atomicAdd(ticket, 1u);
+    return (int64_t)__shfl_sync(0xffffffffu, t, 0);
+  };
+#endif
+  int64_t ta = take(), tb = take(), tc = take();
   double nx = 0., ny = 0., nz = 0.;
   uint32_t nnode = 0;
-  unsigned nflag = 0;  // constraint flag of the next element
-  if (e < e1) {
+  unsigned nflag = 0;  // constraint flag of the element whose coordinates are in nx, ny, nz
+  if (ta < n_todo) {
     if (lane < NPE) {
-      const uint64_t node = conn[e * NPE + lane];
+      const uint64_t node = conn[(e0 + ta) * NPE + lane];
       nx = xyz[node * 3]; ny = xyz[node * 3 + 1]; nz = xyz[node * 3 + 2];
-      if (e + stride < e1) nnode = conn[(e + stride) * NPE + lane];
+      if (tb < n_todo) nnode = conn[(e0 + tb) * NPE + lane];
     }
-    if (elem_flag) nflag = elem_flag[e];
+    if (elem_flag) nflag = elem_flag[e0 + ta];
   }
-  for (; e < e1; e += stride) {
+  while (ta < n_todo) {
+    const int64_t e = e0 + ta;
     const bool flagged = nflag != 0;
     if (lane < NPE) {
       X[3 * lane] = nx; X[3 * lane + 1] = ny; X[3 * lane + 2] = nz;
-      if (e + stride < e1) {
+      if (tb < n_todo) {
         const uint64_t node = nnode;
         nx = xyz[node * 3]; ny = xyz[node * 3 + 1]; nz = xyz[node * 3 + 2];
-        if (e + 2 * stride < e1) nnode = conn[(e + 2 * stride) * NPE + lane];
+        if (tc < n_todo) nnode = conn[(e0 + tc) * NPE + lane];
       }
     }
-    if (elem_flag && e + stride < e1) nflag = elem_flag[e + stride];
+    if (elem_flag && tb < n_todo) nflag = elem_flag[e0 + tb];
+    const int64_t td = take();
+    // a flagged element's constraint data (dof -> constrained? -> value), fetched now, used after the integrals
+    unsigned cmask = 0;
+    double g_lane = 0.;
+    if (flagged) {
+      int cj = 0;
+      if (lane < NPE) {
+        const uint32_t dj = con.elem_dofs[(uint64_t)e * NPE + lane];
+        cj = con.con_flag[dj];
+        if (cj && con.mode == FEASM_CONSTRAIN_HETEROGENEOUS) g_lane = con.con_val[dj];
+      }
+      cmask = __ballot_sync(0xffffffffu, cj);
+    }
     __syncwarp();
 
-    double* out = kf + (uint64_t)(e - e0) * (NPE * rs);
+    double* out = kf + (uint64_t)ta * (NPE * rs);
     ElemRegs<NPE, NQ> R;
     elem_compute<NPE, NQ>(X, fw, s_tab, twp, lane, forcing, f_tab ? f_tab + e * NQ : nullptr, flags, R);
     if (!flagged) {
@@ -87,7 +114,7 @@ k_elem_poisson(const double* __restrict__ xyz, const uint32_t* __restrict__ conn
       // DofMap::heterogeneously_constrain_element_matrix_and_vector (dof_map_constraints.C:2518-2614) on Ke / Fe in the
       // tile, where the reference applies it: after the element integrals, before add_matrix
       elem_store<NPE, NQ>(R, tile, C::LDR, lane);
-      constrain_element(tile, C::LDR, NPE, con.elem_dofs + (uint64_t)e * NPE, con.con_flag, con.con_val, con.mode, lane);
+      constrain_tile<NPE, C::LDR>(tile, cmask, g_lane, lane);
       constexpr int H = C::LDR / 2;
       for (int t = lane; t < NPE * H; t += 32) {
         const int row = t / H, c = t % H;
@@ -95,6 +122,7 @@ k_elem_poisson(const double* __restrict__ xyz, const uint32_t* __restrict__ conn
       }
     }
     __syncwarp();
+    ta = tb; tb = tc; tc = td;
   }
 }
 
@@ -110,13 +138,25 @@ int launch_poisson(feasm_ctx* ctx, const feasm_params& p, const double* d_f, int
   if (blocks < 1) blocks = 1;
   // the element-level constraint rides in this kernel when there is one to apply (one variable: nd == NPE)
   // ... and no side term has to be added between the volume integrals and the constraint (feasm_launch_side_loads)
-  const bool fuse = constrain_mode >= 0 && ctx->n_con_elems > 0 && ctx->nd == NPE && ctx->d_elem_flag && ctx->n_side_elems == 0 &&
+#ifdef FEASM_DEV_NOFUSE
+  const bool fuse = false;
+  if (false) (void)0;
+#endif
+  const bool fuse_ok = constrain_mode >= 0 && ctx->n_con_elems > 0 && ctx->nd == NPE && ctx->d_elem_flag && ctx->n_side_elems == 0 &&
                     ctx->n_pen_elems == 0;
+#ifndef FEASM_DEV_NOFUSE
+  const bool fuse = fuse_ok;
+#else
+  (void)fuse_ok;
+#endif
   const ElemConArgs con{ctx->d_elem_dofs, ctx->d_con_flag, ctx->d_con_val, constrain_mode};
+  if (e1 - e0 + 3ll * blocks * WARPS >= 0xffffffffll) return feasm_fail(ctx, FEASM_ERR_ARG, "element range exceeds the 32-bit ticket counter");
+  unsigned* ticket = reinterpret_cast<unsigned*>(ctx->d_flags + 2);
+  FEASM_CUDA(ctx, cudaMemsetAsync(ticket, 0, sizeof(unsigned), ctx->stream));
   kern<<<(unsigned)blocks, WARPS * 32, smem, ctx->stream>>>(ctx->d_xyz, ctx->d_conn, ctx->d_tab, p.forcing, d_f, e0, e1, d_kf, rs,
-                                                           ctx->d_flags, fuse ? ctx->d_elem_flag : nullptr, con);
+                                                           ctx->d_flags, fuse ? ctx->d_elem_flag : nullptr, con, ticket);
   FEASM_CUDA(ctx, cudaGetLastError());
-  *fused = fuse || constrain_mode < 0 || ctx->n_con_elems == 0;
+  *fused = fuse;
   return FEASM_OK;
 }
 

@@ -108,7 +108,7 @@ struct feasm_ctx {
   double* d_kf = nullptr;  // element records [n_elem][nd][feasm_recb bytes]
   double* d_y = nullptr;   // feasm_residual: y(e,a) = Ke(a,:) . u_e - Fe(a), [n_elem][nd]
   size_t d_y_cap = 0;
-  int* d_flags = nullptr;  // [0] degenerate count, [1] pattern misses
+  int* d_flags = nullptr;  // [0] degenerate count, [1] pattern misses, [2] ticket counter of the element kernel
 
   // tables on device, keyed by quadrature order
   int tab_qorder = -1;

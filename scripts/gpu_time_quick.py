@@ -1,34 +1,33 @@
-"""Quick timing probe at bench sizes using only the product (development aid)."""
-import sys, time
+"""Development aid: kernel times of one configuration (element / constraint / row reduction / total, ms, best of 8).
+    python scripts/gpu_time_quick.py [hex27|hex8|tet10] [n] [fd|tab|none] [poisson|elasticity]
+FEASM_LIB=<path> selects a development build of the library."""
+import sys
 import numpy as np
 sys.path.insert(0, '.')
 from libmesh_b200 import capi as F
 
-def run(etype, n, qorder=0, reps=5):
-    t0 = time.time()
-    xyz, conn, mask = F.build_cube(etype, n, n, n, (-1, 1, -1, 1, -1, 1))
-    nd, base, first, _ = F.distribute_dofs(conn, xyz.shape[0])
-    ed = F.elem_dofs_from_nodes(conn, base)
-    bn = np.nonzero(mask)[0]
-    g = np.cos(.5 * np.pi * xyz[bn, 0]) * np.sin(.5 * np.pi * xyz[bn, 1]) * np.cos(.5 * np.pi * xyz[bn, 2])
-    t1 = time.time()
-    ctx = F.Context(0)
-    ctx.set_mesh(etype, xyz, conn); ctx.set_dofs(ed, nd); ctx.set_constraints(base[bn], g)
-    t2 = time.time()
-    nnz = ctx.build_pattern(); t3 = time.time()
-    ctx.prepare(); ctx.synchronize(); t4 = time.time()
-    p = F.make_params(F.POISSON, qorder, F.FORCING_EX4_FD)
-    for _ in range(3): ctx.assemble(p)
-    best = None
-    for _ in range(reps):
-        ctx.assemble(p); ms, nl = ctx.last_timing()
-        best = ms if best is None or ms[2] < best[2] else best
-    ne = conn.shape[0]
-    print(f'type {etype} n {n}: elems {ne} dofs {nd} nnz {nnz} host-gen {t1-t0:.2f}s upload {t2-t1:.2f}s pattern {t3-t2:.2f}s prepare {t4-t3:.2f}s')
-    print(f'   elem kernel {best[0]:.3f} ms, row reduce {best[1]:.3f} ms, total {best[2]:.3f} ms -> {ne/best[2]*1e3/1e6:.2f} Melem/s')
-    ctx.close()
-
-run(F.HEX27, 48)
-run(F.HEX27, 96)
-run(F.HEX8, 128, qorder=3)
-run(F.HEX8, 128, qorder=5)
+et = {"hex27": 27, "hex8": 8, "tet10": 10}[sys.argv[1] if len(sys.argv) > 1 else "hex27"]
+n = int(sys.argv[2]) if len(sys.argv) > 2 else 96
+forcing = {"fd": F.FORCING_EX4_FD, "tab": F.FORCING_TABULATED, "none": F.FORCING_NONE}[sys.argv[3] if len(sys.argv) > 3 else "fd"]
+elast = len(sys.argv) > 4 and sys.argv[4] == "elasticity"
+ctx = F.Context(0)
+b = (0, 1, 0, 0.3, 0, 0.1) if elast else (-1, 1, -1, 1, -1, 1)
+ctx.generate_cube(et, n, n, n, b)
+ctx.distribute_dofs(3 if elast else 1)
+ctx.generate_dirichlet(0x10 if elast else 0x3f, F.DIRICHLET_ZERO if elast else F.DIRICHLET_EX4_EXACT)
+ctx.build_pattern()
+ctx.prepare()
+qo = 3 if et == 8 else 0
+if elast:
+    p = F.make_params(F.ELASTICITY, 0, F.FORCING_NONE, F.CONSTRAIN_HOMOGENEOUS)
+else:
+    ftab = np.ones((ctx.n_elem, {27: 27, 8: 8, 10: 14}[et])) if forcing == F.FORCING_TABULATED else None
+    p = F.make_params(F.POISSON, qo, forcing, f_host=ftab)
+for _ in range(3):
+    ctx.assemble(p)
+ms = []
+for _ in range(8):
+    ctx.assemble(p)
+    ms.append(ctx.last_timing()[0])
+ms = np.array(ms)
+print(f"{F.LIB_PATH.split('/')[-1]} {sys.argv[1:]} n_elem {ctx.n_elem}: element {ms[:,0].min():.3f} ms  constrain {ms[:,3].min():.3f}  row_reduce {ms[:,1].min():.3f}  total {ms[:,2].min():.3f}")
