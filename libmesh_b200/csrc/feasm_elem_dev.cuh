@@ -238,18 +238,16 @@ struct ElemRegs {
   double Fe;
 };
 
-// One element by one warp: phases A-C of the header comment and Fe.  X holds the element's node coordinates, fw is a
-// 32-double scratch, twp = s_tw + (lane>>2)*TS + (lane&3).
+// Phase A of one element by one warp, and Fe: FEMap::compute_map at quadrature point q = lane, the forcing, then
+// Fe(a) on lane a (introduction_ex4.C:536-537).  X holds the element's node coordinates, fw is a 32-double scratch.
+// Returns has_affine_map; S = sqrt(det J) * inverse-Jacobian rows (the same on every lane when affine).
 template <int NPE, int NQ>
-__device__ __forceinline__ void elem_compute(const double* X, double* fw, const double* s_tab, const double* twp, int lane,
-                                             int forcing, const double* __restrict__ f_tab_e, int* flags, ElemRegs<NPE, NQ>& R) {
-  using C = ElemCfg<NPE, NQ>;
+__device__ __forceinline__ bool elem_geom(const double* X, double* fw, const double* s_tab, int lane, int forcing,
+                                          const double* __restrict__ f_tab_e, int* flags, double (&S)[9], double& Fe_out) {
   const double* s_phi = s_tab;
-  const int t4 = lane & 3;
-  // ---- A: reference -> physical map at quadrature point q = lane ---------------------------------------
   // FEASM_ABLATE (never defined in product builds; scripts/gpu_ablate.py): 2 = no contraction, 3 = no
-  // stores, 4 = no geometry / forcing — timing probes of the phases of this function.
-  double S[9], JxW, x, y, z;
+  // stores, 4 = no geometry / forcing — timing probes of the phases.
+  double JxW, x, y, z;
 #if defined(FEASM_ABLATE) && FEASM_ABLATE == 4
   const bool affine = true;
   for (int k = 0; k < 9; ++k) S[k] = X[k] + k;
@@ -269,8 +267,29 @@ __device__ __forceinline__ void elem_compute(const double* X, double* fw, const 
     }
     fw[lane] = lane < NQ ? JxW * f : 0.;
   }
+  __syncwarp();
+  Fe_out = 0.;
+  if (lane < NPE && forcing != FEASM_FORCING_NONE) {
+    double Fe = 0., f1 = 0., f2 = 0.;
+#pragma unroll
+    for (int q = 0; q + 2 < NQ; q += 3) {
+      Fe += fw[q] * s_phi[lane * NQ + q];
+      f1 += fw[q + 1] * s_phi[lane * NQ + q + 1];
+      f2 += fw[q + 2] * s_phi[lane * NQ + q + 2];
+    }
+#pragma unroll
+    for (int q = NQ - NQ % 3; q < NQ; ++q) Fe += fw[q] * s_phi[lane * NQ + q];
+    Fe_out = (Fe + f1) + f2;
+  }
+  return affine;
+}
 
-  // ---- B+C: Ke = G G^T; fragments generated in registers -------------------------------------------------
+// Phases B+C: Ke = G G^T, G[i][(d,q)] = sqrt(JxW_q) dphi_i/dx_d(q), fragments generated in registers from S and the
+// scaled reference-gradient table (twp = s_tw + (lane>>2)*TS + (lane&3)).
+template <int NPE, int NQ>
+__device__ __forceinline__ void elem_contract(const double (&S)[9], const bool affine, const double* twp, int lane, ElemRegs<NPE, NQ>& R) {
+  using C = ElemCfg<NPE, NQ>;
+  const int t4 = lane & 3;
 #pragma unroll
   for (int b = 0; b < C::NBLK; ++b) { R.acc[b][0] = 0.; R.acc[b][1] = 0.; }
 #pragma unroll
@@ -278,7 +297,7 @@ __device__ __forceinline__ void elem_compute(const double* X, double* fw, const 
 #pragma unroll
     for (int r = 0; r < (C::REM > 0 ? C::REM : 1); ++r) R.pr[ib][r] = 0.;
 #if defined(FEASM_ABLATE) && FEASM_ABLATE == 2
-  if (forcing == 99)
+  if (lane == 99)
 #endif
 #pragma unroll
   for (int qg = 0; qg < C::QG; ++qg) {
@@ -327,21 +346,14 @@ __device__ __forceinline__ void elem_compute(const double* X, double* fw, const 
         R.pr[ib][r] += __shfl_xor_sync(0xffffffffu, R.pr[ib][r], 2);
       }
   }
+}
 
-  // ---- Fe (introduction_ex4.C:536-537), lane = shape function ----------------------------------------------------
-  R.Fe = 0.;
-  if (lane < NPE && forcing != FEASM_FORCING_NONE) {
-    double Fe = 0., f1 = 0., f2 = 0.;
-#pragma unroll
-    for (int q = 0; q + 2 < NQ; q += 3) {
-      Fe += fw[q] * s_phi[lane * NQ + q];
-      f1 += fw[q + 1] * s_phi[lane * NQ + q + 1];
-      f2 += fw[q + 2] * s_phi[lane * NQ + q + 2];
-    }
-#pragma unroll
-    for (int q = NQ - NQ % 3; q < NQ; ++q) Fe += fw[q] * s_phi[lane * NQ + q];
-    R.Fe = (Fe + f1) + f2;
-  }
+template <int NPE, int NQ>
+__device__ __forceinline__ void elem_compute(const double* X, double* fw, const double* s_tab, const double* twp, int lane,
+                                             int forcing, const double* __restrict__ f_tab_e, int* flags, ElemRegs<NPE, NQ>& R) {
+  double S[9];
+  const bool affine = elem_geom<NPE, NQ>(X, fw, s_tab, lane, forcing, f_tab_e, flags, S, R.Fe);
+  elem_contract<NPE, NQ>(S, affine, twp, lane, R);
 }
 
 // Phase D: the warp's fragments into the element's block of NPE records, rs doubles apart (row a = Ke(a,:) then Fe(a)

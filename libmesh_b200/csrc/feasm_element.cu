@@ -31,7 +31,7 @@
 namespace {
 constexpr int kElastUnroll = FEASM_ELAST_UNROLL;  // k groups unrolled in the elasticity products (tuning knob)
 template <int NPE, int NQ, int WARPS, int RS>
-__global__ void __launch_bounds__(WARPS * 32, 1)
+__global__ void __maxnreg__(WARPS > 12 ? 128 : 168)  // 12 warps x 168 registers fill the register file; 16 x 128 for the small elements
 k_elem_poisson(const double* __restrict__ xyz, const uint32_t* __restrict__ conn, const double* __restrict__ tab,
                int forcing, const double* __restrict__ f_tab, int64_t e0, int64_t e1, double* __restrict__ kf, int rs_rt,
                int* flags, const uint8_t* __restrict__ elem_flag, ElemConArgs con, unsigned* ticket) {
@@ -59,12 +59,12 @@ k_elem_poisson(const double* __restrict__ xyz, const uint32_t* __restrict__ conn
 #ifdef FEASM_DEV_STATIC  // development A/B: static round-robin
   int64_t next_static = (int64_t)blockIdx.x * WARPS + warp;
   auto take = [&]() -> int64_t { const int64_t t = next_static; next_static += (int64_t)gridDim.x * WARPS; return t; };
+  auto take_raw = [&]() -> unsigned { return (unsigned)take(); };
+  auto bcast = [&](unsigned t) -> int64_t { return (int64_t)t; };
 #else
-  auto take = [&]() -> int64_t {
-    unsigned t = 0;
-    if (lane == 0) t = atomicAdd(ticket, 1u);
-    return (int64_t)__shfl_sync(0xffffffffu, t, 0);
-  };
+  auto take_raw = [&]() -> unsigned { return lane == 0 ? atomicAdd(ticket, 1u) : 0u; };  // lane 0 holds the ticket ...
+  auto bcast = [&](unsigned t) -> int64_t { return (int64_t)__shfl_sync(0xffffffffu, t, 0); };  // ... until it is needed
+  auto take = [&]() -> int64_t { return bcast(take_raw()); };
 #endif
   int64_t ta = take(), tb = take(), tc = take();
   double nx = 0., ny = 0., nz = 0.;
@@ -90,7 +90,7 @@ k_elem_poisson(const double* __restrict__ xyz, const uint32_t* __restrict__ conn
       }
     }
     if (elem_flag && tb < n_todo) nflag = elem_flag[e0 + tb];
-    const int64_t td = take();
+    const unsigned td_raw = take_raw();  // the atomic is in flight during the element; its value is broadcast at the end
     // a flagged element's constraint data (dof -> constrained? -> value), fetched now, used after the integrals
     unsigned cmask = 0;
     double g_lane = 0.;
@@ -103,10 +103,10 @@ k_elem_poisson(const double* __restrict__ xyz, const uint32_t* __restrict__ conn
       }
       cmask = __ballot_sync(0xffffffffu, cj);
     }
-    __syncwarp();
 
     double* out = kf + (uint64_t)ta * (NPE * rs);
     ElemRegs<NPE, NQ> R;
+    __syncwarp();
     elem_compute<NPE, NQ>(X, fw, s_tab, twp, lane, forcing, f_tab ? f_tab + e * NQ : nullptr, flags, R);
     if (!flagged) {
       elem_store<NPE, NQ>(R, out, rs, lane);
@@ -122,7 +122,7 @@ k_elem_poisson(const double* __restrict__ xyz, const uint32_t* __restrict__ conn
       }
     }
     __syncwarp();
-    ta = tb; tb = tc; tc = td;
+    ta = tb; tb = tc; tc = bcast(td_raw);
   }
 }
 
@@ -138,16 +138,13 @@ int launch_poisson(feasm_ctx* ctx, const feasm_params& p, const double* d_f, int
   if (blocks < 1) blocks = 1;
   // the element-level constraint rides in this kernel when there is one to apply (one variable: nd == NPE)
   // ... and no side term has to be added between the volume integrals and the constraint (feasm_launch_side_loads)
+  const bool fuse_ok = constrain_mode >= 0 && ctx->n_con_elems > 0 && ctx->nd == NPE && ctx->d_elem_flag && ctx->n_side_elems == 0 &&
+                       ctx->n_pen_elems == 0;
 #ifdef FEASM_DEV_NOFUSE
   const bool fuse = false;
-  if (false) (void)0;
-#endif
-  const bool fuse_ok = constrain_mode >= 0 && ctx->n_con_elems > 0 && ctx->nd == NPE && ctx->d_elem_flag && ctx->n_side_elems == 0 &&
-                    ctx->n_pen_elems == 0;
-#ifndef FEASM_DEV_NOFUSE
-  const bool fuse = fuse_ok;
-#else
   (void)fuse_ok;
+#else
+  const bool fuse = fuse_ok;
 #endif
   const ElemConArgs con{ctx->d_elem_dofs, ctx->d_con_flag, ctx->d_con_val, constrain_mode};
   if (e1 - e0 + 3ll * blocks * WARPS >= 0xffffffffll) return feasm_fail(ctx, FEASM_ERR_ARG, "element range exceeds the 32-bit ticket counter");
@@ -893,8 +890,6 @@ static int launch_element_kernel(feasm_ctx* ctx, const feasm_params& p, const do
   }
   if (p.problem == FEASM_POISSON) {
     if (ctx->elem_type == FEASM_HEX27 && ctx->tab_nq == 27) {
-      static const int warps = getenv("FEASM_ELEM_WARPS") ? atoi(getenv("FEASM_ELEM_WARPS")) : 12;  // tuning knob
-      if (warps == 16) return launch_poisson<27, 27, 16>(ctx, p, d_f, e0, e1, d_kf, rs, cm, fused);
       if (rs == 32) return launch_poisson<27, 27, 12, 32>(ctx, p, d_f, e0, e1, d_kf, rs, cm, fused);  // 256 B records (uint8 positions)
       return launch_poisson<27, 27, 12>(ctx, p, d_f, e0, e1, d_kf, rs, cm, fused);
     }
