@@ -31,7 +31,7 @@
 namespace {
 constexpr int kElastUnroll = FEASM_ELAST_UNROLL;  // k groups unrolled in the elasticity products (tuning knob)
 template <int NPE, int NQ, int WARPS, int RS>
-__global__ void __maxnreg__(WARPS > 12 ? 128 : 168)  // 12 warps x 168 registers fill the register file; 16 x 128 for the small elements
+__global__ void __launch_bounds__(WARPS * 32, 1)
 k_elem_poisson(const double* __restrict__ xyz, const uint32_t* __restrict__ conn, const double* __restrict__ tab,
                int forcing, const double* __restrict__ f_tab, int64_t e0, int64_t e1, double* __restrict__ kf, int rs_rt,
                int* flags, const uint8_t* __restrict__ elem_flag, ElemConArgs con, unsigned* ticket) {
