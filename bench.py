@@ -570,7 +570,12 @@ def run_multi(args, F, rank, world, local):
     prob = RankProblem(rank, world, P["xyz"], P["conn"], base, first, pid, n_vars, P["con_dofs"], P["con_vals"])
     ctx = F.Context(local)
     dev_group = None
-    if os.environ.get("FEASM_OVERLAP", "1") != "0":
+    native = os.environ.get("FEASM_NATIVE_COMM", "1") != "0"  # 1: the library issues ncclSend/ncclRecv itself (feasm_exchange_begin / _end)
+    if native:
+        ids = [F.Context.comm_unique_id() if rank == 0 else None]
+        dist.broadcast_object_list(ids, src=0, group=host_group)  # torch.distributed only carries the 128 bootstrap bytes
+        ctx.comm_init(world, rank, ids[0])
+    elif os.environ.get("FEASM_OVERLAP", "1") != "0":
         # the transfer should take SM slots as they free up while the owned rows are being reduced: NCCL's stream at
         # high priority
         opts = dist.ProcessGroupNCCL.Options(is_high_priority_stream=True)
@@ -684,7 +689,7 @@ def run_multi(args, F, rank, world, local):
             "metric": metric_name(args), "value": n_elem / (ms_per_step * 1e-3), "unit": "elements/s", "n_gpus": world, "steps": args.steps,
             "warmup": args.warmup, "ms_per_step": ms_per_step, "higher_is_better": True, "scaling": "strong", "vs_baseline": None,
             "dtype": "f64", "data": "synthetic",
-            "config": {"workload": workload_name(args) + f"; LinearPartitioner slabs over {world} GPUs, ghost rows by NCCL send/recv"
+            "config": {"workload": workload_name(args) + f"; LinearPartitioner slabs over {world} GPUs, ghost rows by ncclSend/ncclRecv " + ("issued by libfeasm" if native else "through torch.distributed")
                                    + (" overlapped with the reduction of the owned rows" if overlap else ""), "n_elem": n_elem,
                        "n_dofs": int(n_dofs), "l2": "per-rank CSR values larger than L2", "setup_s": round(setup_s, 3),
                        "ghost_bytes_per_step_all_ranks": int(io[2].item()), "host_enqueue_ms_per_step_rank0": round(host_ms, 4)},

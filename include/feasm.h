@@ -55,6 +55,7 @@ extern "C" {
 #define FEASM_ERR_PATTERN -5    /* add to an entry outside the sparsity pattern (sparse_matrix.h:300-303) */
 #define FEASM_ERR_NOMEM -6
 #define FEASM_ERR_BREAKDOWN -7 /* feasm_cg_solve: p.Ap <= 0 */
+#define FEASM_ERR_COMM -8      /* NCCL missing or an NCCL call failed */
 #define FEASM_NOT_CONVERGED 1  /* feasm_cg_solve: max_its reached above the tolerance (x, iterations, residual are valid) */
 
 typedef struct feasm_ctx feasm_ctx;
@@ -234,6 +235,29 @@ double* feasm_pack_ghost(feasm_ctx* ctx, uint64_t* n_doubles);
 double* feasm_recv_buffer(feasm_ctx* ctx, uint64_t* n_doubles);
 /* Adds the received buffer into the owned slots in fixed peer order (deterministic). */
 int feasm_unpack_ghost(feasm_ctx* ctx);
+
+/* The exchange itself, below the C ABI (feasm_create(device, ncclComm_t) / feasm_exchange_ghost_rows).  NCCL is
+ * bound at run time (libnccl.so.2 of the process, e.g. the one an MPI + NCCL host or torch already loaded).
+ *   feasm_set_communicator : hand in an ncclComm_t the host owns (one rank of the communicator per context; NULL = back to
+ *                            one rank).  The role of ParallelObject::comm() for the GpuSparseMatrix.
+ *   feasm_comm_unique_id / feasm_comm_init : for hosts without an NCCL communicator of their own: rank 0 makes the
+ *                            FEASM_COMM_ID_BYTES bootstrap id (ncclGetUniqueId), the host broadcasts the bytes by whatever
+ *                            means it has (MPI_Bcast, a file, torch.distributed), every rank calls feasm_comm_init
+ *                            (ncclCommInitRank; collective).  The context owns and destroys that communicator.
+ *   feasm_exchange_begin   : after feasm_assemble_begin (or feasm_assemble + feasm_pack_ghost): one grouped ncclSend /
+ *                            ncclRecv per neighbour of the plan, on the context's high-priority communication stream,
+ *                            ordered behind the pack by an event.  Returns at once; the caller goes on to feasm_assemble_end.
+ *   feasm_exchange_end     : makes feasm_stream wait for the transfer and adds the received rows (feasm_unpack_ghost).
+ *   feasm_exchange_ghost_rows = begin + end (DistributedVector::close, distributed_vector.C:399-470).
+ *   feasm_comm_allgather_u64 : setup helper (dof ownership ranges, counts): n values from every rank to every rank. */
+#define FEASM_COMM_ID_BYTES 128
+int feasm_set_communicator(feasm_ctx* ctx, void* nccl_comm, int n_ranks, int rank);
+int feasm_comm_unique_id(void* id_bytes);
+int feasm_comm_init(feasm_ctx* ctx, int n_ranks, int rank, const void* id_bytes);
+int feasm_exchange_begin(feasm_ctx* ctx);
+int feasm_exchange_end(feasm_ctx* ctx);
+int feasm_exchange_ghost_rows(feasm_ctx* ctx);
+int feasm_comm_allgather_u64(feasm_ctx* ctx, const uint64_t* send, int n, uint64_t* recv);
 
 /* ---- host-side generators for stand-alone runs (no libMesh present) ---------------------------- */
 /* MeshTools::Generation::build_cube (src/mesh/mesh_generation.C:317-1937) for HEX8/HEX27/TET10: fills caller arrays.

@@ -34,6 +34,8 @@ SYMBOLS = [
     "feasm_vec_reduce", "feasm_vec_set_entry",
     "feasm_generate_cube", "feasm_distribute_dofs_device", "feasm_generate_dirichlet", "feasm_get_mesh", "feasm_get_dofs",
     "feasm_get_constraints", "feasm_set_side_penalty", "feasm_residual", "feasm_add_matrix_noalloc",
+    "feasm_set_communicator", "feasm_comm_unique_id", "feasm_comm_init", "feasm_exchange_begin", "feasm_exchange_end",
+    "feasm_exchange_ghost_rows", "feasm_comm_allgather_u64",
 ]
 
 
@@ -84,6 +86,13 @@ def lib():
         "feasm_add_matrix": (i32, [vp, vp, vp, i32, vp, i32]),
         "feasm_add_vector": (i32, [vp, vp, vp, i32]),
         "feasm_add_matrix_noalloc": (i32, [vp, vp, vp, i32, vp, i32]),
+        "feasm_set_communicator": (i32, [vp, vp, i32, i32]),
+        "feasm_comm_unique_id": (i32, [vp]),
+        "feasm_comm_init": (i32, [vp, i32, i32, vp]),
+        "feasm_exchange_begin": (i32, [vp]),
+        "feasm_exchange_end": (i32, [vp]),
+        "feasm_exchange_ghost_rows": (i32, [vp]),
+        "feasm_comm_allgather_u64": (i32, [vp, vp, i32, vp]),
         "feasm_get_values": (i32, [vp, vp, vp]),
         "feasm_device_values": (vp, [vp]),
         "feasm_device_rhs": (vp, [vp]),
@@ -207,6 +216,8 @@ class Context:
         self.n_rows = 0
         self.nd = 0
         self.n_elem = 0
+        self.has_comm = False
+        self.comm_size = 1
 
     def close(self):
         if getattr(self, "h", None):
@@ -424,6 +435,36 @@ class Context:
         sp, ss = _c(send_ptr, np.uint64), _c(send_slots, np.uint64)
         rp, rs = _c(recv_ptr, np.uint64), _c(recv_slots, np.uint64)
         self._ck(self.L.feasm_set_exchange_plan(self.h, len(pr), _p(pr), _p(sp), _p(ss), _p(rp), _p(rs)))
+
+    # -- NCCL below the C ABI ------------------------------------------------------------------------------------------
+    @staticmethod
+    def comm_unique_id():
+        """The bootstrap id rank 0 makes (ncclGetUniqueId); broadcast its bytes to every rank by any means."""
+        buf = C.create_string_buffer(128)
+        rc = lib().feasm_comm_unique_id(buf)
+        if rc:
+            raise FeasmError(rc, lib().feasm_last_error(None).decode())
+        return bytes(buf.raw)
+
+    def comm_init(self, n_ranks, rank, id_bytes):
+        buf = C.create_string_buffer(bytes(id_bytes), 128)
+        self._ck(self.L.feasm_comm_init(self.h, n_ranks, rank, buf))
+        self.has_comm, self.comm_size = True, n_ranks
+
+    def exchange_begin(self):
+        self._ck(self.L.feasm_exchange_begin(self.h))
+
+    def exchange_end(self):
+        self._ck(self.L.feasm_exchange_end(self.h))
+
+    def exchange_ghost_rows(self):
+        self._ck(self.L.feasm_exchange_ghost_rows(self.h))
+
+    def comm_allgather(self, values):
+        v = _c(values, np.uint64)
+        out = np.empty((self.comm_size, len(v)), dtype=np.uint64)
+        self._ck(self.L.feasm_comm_allgather_u64(self.h, _p(v), len(v), _p(out)))
+        return out
 
     def pack_ghost(self):
         n = C.c_uint64()

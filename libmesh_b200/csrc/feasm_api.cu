@@ -138,6 +138,7 @@ void feasm_destroy(feasm_ctx* ctx) {
   if (!ctx) return;
   cudaSetDevice(ctx->device);
   cudaStreamSynchronize(ctx->stream);
+  feasm_comm_release(ctx);
   drop_maps(ctx);
   release(ctx->d_xyz); release(ctx->d_conn); release(ctx->d_elem_dofs); release(ctx->d_gid);
   release(ctx->d_node_mask); release(ctx->d_node_base);

@@ -6,6 +6,7 @@
 
 #include <cstdint>
 #include <cstdio>
+#include <cstring>
 #include <string>
 #include <vector>
 
@@ -149,6 +150,14 @@ struct feasm_ctx {
   uint64_t* d_unpack_seg = nullptr;   // [n_unpack_slots+1] group boundaries in d_unpack_perm
   uint64_t* d_unpack_perm = nullptr;  // [n_recv] index into the receive buffer
 
+  // NCCL exchange below the C ABI (feasm_comm.cu)
+  void* comm = nullptr;        // ncclComm_t
+  bool comm_owned = false;     // created by feasm_comm_init (destroyed with the context) or handed in by the host
+  int comm_rank = 0, comm_size = 1;
+  cudaStream_t comm_stream = nullptr;  // high priority
+  cudaEvent_t ev_packed = nullptr, ev_exchanged = nullptr;
+  bool exchange_open = false;
+
   float last_ms[4] = {0, 0, 0, 0};
   int last_launches = 0;
   bool assemble_open = false;  // between feasm_assemble_begin and feasm_assemble_end
@@ -205,6 +214,8 @@ int feasm_launch_row_reduce(feasm_ctx* ctx, const uint32_t* d_row_list, int64_t 
 int feasm_launch_row_residual(feasm_ctx* ctx, const double* d_u, double* d_r);
 int feasm_launch_pack(feasm_ctx* ctx);
 int feasm_launch_unpack(feasm_ctx* ctx);
+// feasm_comm.cu: destroys an owned communicator and the communication stream
+void feasm_comm_release(feasm_ctx* ctx);
 int feasm_launch_add_matrix(feasm_ctx* ctx, const double* d_dm, const uint32_t* d_rows, int nr, const uint32_t* d_cols,
                             int nc);
 

@@ -284,21 +284,29 @@ class DistributedAssembly:
 
     def start_exchange(self):
         """Issue the send/recv group behind what is on the library's stream now (the packed send buffer).  NCCL runs it
-        on its own stream, so kernels launched on the library's stream afterwards overlap the transfer."""
-        import torch
-
+        on its own stream, so kernels launched on the library's stream afterwards overlap the transfer.  With a
+        communicator inside the context (feasm_comm_init) the library issues the group itself (feasm_exchange_begin);
+        otherwise torch.distributed does (the route of the CPU tests and of hosts that own the process group)."""
         if not self.peers:
             return []
+        if getattr(self.ctx, "has_comm", False):
+            self.ctx.exchange_begin()
+            return None
+        import torch
+
         ops = self._exchange_ops()
         with torch.cuda.stream(self._lib_stream):
             return self.dist.batch_isend_irecv(ops)
 
     def finish_exchange(self, works):
         """Make the library's stream wait for the transfer, then add the received rows in fixed peer order."""
-        import torch
-
         if not self.peers:
             return
+        if works is None:
+            self.ctx.exchange_end()  # waits for the transfer on the library's stream, then feasm_unpack_ghost
+            return
+        import torch
+
         with torch.cuda.stream(self._lib_stream):
             for w in works:
                 w.wait()  # stream-ordered for NCCL

@@ -22,7 +22,7 @@ from oracle import oracle as O  # noqa: E402
 from oracle.parity import TOL, csr_compare, vec_compare  # noqa: E402
 
 
-def run_case(rank, world, local, host_group, etype, dims, n_vars, scramble):
+def run_case(rank, world, local, host_group, etype, dims, n_vars, scramble, native=False):
     m = O.Mesh(etype, *dims, bounds=(-1, 1, -1, 1, -1, 1) if n_vars == 1 else (0, 1, 0, 0.3, 0, 0.1))
     if scramble:
         pid = ((np.arange(m.n_elem) // 5) % world).astype(np.int32)
@@ -44,6 +44,12 @@ def run_case(rank, world, local, host_group, etype, dims, n_vars, scramble):
         gv, gb, _ = s.assemble(O.ELASTICITY_EX6, n_threads=4)
     prob = M.RankProblem(rank, world, xyz, conn, nb, fd, pid, n_vars, cd, cv)
     ctx = F.Context(local)
+    if native:  # the communicator lives inside the library: feasm_comm_init + feasm_exchange_begin / _end
+        ids = [F.Context.comm_unique_id() if rank == 0 else None]
+        dist.broadcast_object_list(ids, src=0, group=host_group)
+        ctx.comm_init(world, rank, ids[0])
+        gathered = ctx.comm_allgather([rank + 10, prob.n_owned])
+        assert [int(x) for x in gathered[:, 0]] == [r + 10 for r in range(world)] and int(gathered[:, 1].sum()) == s.n_dofs
     da = M.DistributedAssembly(ctx, prob, dist, host_group=host_group)
     da.setup()
     if n_vars == 1:
@@ -66,7 +72,7 @@ def run_case(rank, world, local, host_group, etype, dims, n_vars, scramble):
     cv_, cr_ = csr_compare(v, gv[lo:hi], da.row_ptr[: n_own + 1]), vec_compare(b, gb[f0:f0 + n_own])
     assert cv_["max_rel_err"] < TOL and cr_["max_rel_err"] < TOL, (cv_, cr_)
     ctx.close()
-    print(f"rank {rank}: etype {etype} dims {dims} vars {n_vars} scramble {scramble}: {len(prob.elems)} elements, {n_own} owned + "
+    print(f"rank {rank}: etype {etype} dims {dims} vars {n_vars} scramble {scramble} native {native}: {len(prob.elems)} elements, {n_own} owned + "
           f"{len(prob.ghosts)} ghost rows, values max rel {cv_['max_rel_err']:.2e}, rhs {cr_['max_rel_err']:.2e}", flush=True)
 
 
@@ -79,6 +85,9 @@ def main():
     run_case(rank, world, local, host_group, 27, (8, 7, 6), 1, 1)
     run_case(rank, world, local, host_group, 8, (20, 16, 12), 1, 1)
     run_case(rank, world, local, host_group, 27, (8, 4, 4), 3, 0)
+    run_case(rank, world, local, host_group, 27, (12, 12, 12), 1, 0, native=True)
+    run_case(rank, world, local, host_group, 27, (8, 7, 6), 1, 1, native=True)
+    run_case(rank, world, local, host_group, 27, (8, 4, 4), 3, 0, native=True)
     dist.barrier()
     if rank == 0:
         print("NCCL_PARITY_OK", flush=True)
