@@ -161,6 +161,14 @@ int feasm_zero(feasm_ctx* ctx);
 int feasm_add_matrix(feasm_ctx* ctx, const double* dm, const uint32_t* rows, int n_rows, const uint32_t* cols,
                      int n_cols);
 int feasm_add_vector(feasm_ctx* ctx, const double* v, const uint32_t* rows, int n);
+/* SparseMatrix::set(i, j, value) (sparse_matrix.h:295) for a block: A(rows[i], cols[j]) = dm(i,j). */
+int feasm_set_matrix(feasm_ctx* ctx, const double* dm, const uint32_t* rows, int n_rows, const uint32_t* cols, int n_cols);
+/* A context that holds a matrix only — pattern, values, right-hand side, no mesh: SparseMatrix::init (sparse_matrix.h:189)
+ * with a known Graph, the target of clone() / get_transpose().  The per-element virtuals, feasm_zero, the getters,
+ * feasm_set_values and feasm_vector_mult work on it; feasm_assemble needs feasm_set_mesh / feasm_set_dofs. */
+int feasm_init_matrix(feasm_ctx* ctx, int64_t n_rows, int64_t n_owned, const uint64_t* row_ptr, const uint32_t* col_idx);
+/* H2D upload of the CSR values and / or the right-hand side (either may be NULL): the inverse of feasm_get_values. */
+int feasm_set_values(feasm_ctx* ctx, const double* csr_values, const double* rhs);
 /* feasm_add_matrix without any device allocation.  NO COUNTERPART IN THE REFERENCE: added
  * for callers that cannot call cudaMalloc (tight serving loops, harnesses that forbid it, code meant for CUDA
  * graph capture).  Same arguments, same result as feasm_add_matrix; the staging buffers are a fixed file-scope device

@@ -35,7 +35,7 @@ SYMBOLS = [
     "feasm_generate_cube", "feasm_distribute_dofs_device", "feasm_generate_dirichlet", "feasm_get_mesh", "feasm_get_dofs",
     "feasm_get_constraints", "feasm_set_side_penalty", "feasm_residual", "feasm_add_matrix_noalloc",
     "feasm_set_communicator", "feasm_comm_unique_id", "feasm_comm_init", "feasm_exchange_begin", "feasm_exchange_end",
-    "feasm_exchange_ghost_rows", "feasm_comm_allgather_u64",
+    "feasm_exchange_ghost_rows", "feasm_comm_allgather_u64", "feasm_set_matrix", "feasm_init_matrix", "feasm_set_values",
 ]
 
 
@@ -86,6 +86,9 @@ def lib():
         "feasm_add_matrix": (i32, [vp, vp, vp, i32, vp, i32]),
         "feasm_add_vector": (i32, [vp, vp, vp, i32]),
         "feasm_add_matrix_noalloc": (i32, [vp, vp, vp, i32, vp, i32]),
+        "feasm_set_matrix": (i32, [vp, vp, vp, i32, vp, i32]),
+        "feasm_init_matrix": (i32, [vp, i64, i64, vp, vp]),
+        "feasm_set_values": (i32, [vp, vp, vp]),
         "feasm_set_communicator": (i32, [vp, vp, i32, i32]),
         "feasm_comm_unique_id": (i32, [vp]),
         "feasm_comm_init": (i32, [vp, i32, i32, vp]),
@@ -358,6 +361,22 @@ class Context:
         r = _c(rows, np.uint32)
         c = r if cols is None else _c(cols, np.uint32)
         self._ck(self.L.feasm_add_matrix(self.h, _p(dm), _p(r), len(r), _p(c), len(c)))
+
+    def set_matrix(self, dm, rows, cols=None):
+        dm = _c(dm, np.float64)
+        r = _c(rows, np.uint32)
+        c = r if cols is None else _c(cols, np.uint32)
+        self._ck(self.L.feasm_set_matrix(self.h, _p(dm), _p(r), len(r), _p(c), len(c)))
+
+    def init_matrix(self, row_ptr, col_idx, n_owned=None):
+        rp, ci = _c(row_ptr, np.uint64), _c(col_idx, np.uint32)
+        n = len(rp) - 1
+        self._ck(self.L.feasm_init_matrix(self.h, n, n if n_owned is None else n_owned, _p(rp), _p(ci)))
+        self.n_rows = n
+
+    def set_values(self, values=None, rhs=None):
+        v, b = _c(values, np.float64), _c(rhs, np.float64)
+        self._ck(self.L.feasm_set_values(self.h, _p(v), _p(b)))
 
     def add_matrix_noalloc(self, dm, rows, cols=None):
         """feasm_add_matrix_noalloc: the same add through the library's fixed device scratch (no device allocation)."""

@@ -149,6 +149,8 @@ void feasm_destroy(feasm_ctx* ctx) {
   release(ctx->d_side_elems); release(ctx->d_side_mask); release(ctx->d_side_tab); release(ctx->d_side_nodes);
   release(ctx->d_pen_elems); release(ctx->d_pen_mask); release(ctx->d_y);
   release(ctx->d_send_slots); release(ctx->d_recv_slots); release(ctx->d_send_buf); release(ctx->d_recv_buf);
+  if (ctx->h_stage) cudaFreeHost(ctx->h_stage);
+  release(ctx->d_stage);
   for (auto& ev : ctx->ev) if (ev) cudaEventDestroy(ev);
   cudaStreamDestroy(ctx->stream);
   delete ctx;
@@ -186,6 +188,7 @@ int feasm_set_dofs(feasm_ctx* ctx, int n_vars, int64_t n_rows, int64_t n_owned, 
   release(ctx->d_gid);
   if (global_ids) { rc = upload(ctx, &ctx->d_gid, global_ids, (size_t)n_rows); if (rc) return rc; }
   release(ctx->d_node_base);  // numbering supplied by the caller: no node -> dof table
+  ctx->matrix_only = false;
   return feasm_reset_dofs(ctx, n_vars, n_rows, n_owned);
 }
 
@@ -294,7 +297,7 @@ static int alloc_values(feasm_ctx* ctx) {
 }
 
 int feasm_set_pattern(feasm_ctx* ctx, const uint64_t* row_ptr, const uint32_t* col_idx) {
-  if (!ctx || !ctx->d_elem_dofs) return feasm_fail(ctx, FEASM_ERR_STATE, "set_dofs first");
+  if (!ctx || (!ctx->d_elem_dofs && !ctx->matrix_only)) return feasm_fail(ctx, FEASM_ERR_STATE, "set_dofs first");
   if (!row_ptr || !col_idx || row_ptr[0] != 0) return feasm_fail(ctx, FEASM_ERR_ARG, "bad pattern");
   for (int64_t r = 0; r < ctx->n_rows; ++r) {
     if (row_ptr[r + 1] < row_ptr[r]) return feasm_fail(ctx, FEASM_ERR_ARG, "row_ptr not monotone");
@@ -350,6 +353,7 @@ int feasm_prepare(feasm_ctx* ctx) {
 // feasm_assemble_end reduces the owned rows.
 static int assemble_impl(feasm_ctx* ctx, const feasm_params* params, int mode) {
   if (!ctx || !params) return FEASM_ERR_ARG;
+  if (!ctx->d_conn || !ctx->d_elem_dofs) return feasm_fail(ctx, FEASM_ERR_STATE, "set_mesh / set_dofs first (this context holds a matrix only)");
   FEASM_CUDA(ctx, cudaSetDevice(ctx->device));
   int rc = feasm_prepare(ctx);
   if (rc) return rc;
@@ -486,38 +490,89 @@ int feasm_zero(feasm_ctx* ctx) {
   return FEASM_OK;
 }
 
-int feasm_add_matrix(feasm_ctx* ctx, const double* dm, const uint32_t* rows, int nr, const uint32_t* cols, int nc) {
+// Staging area of the per-element compat route: one pinned host block and one device block, grown on demand and kept, so a
+// call costs one packed H2D copy and one kernel — no cudaMalloc / cudaFree per call.
+static int stage_block(feasm_ctx* ctx, size_t bytes, unsigned char** h, unsigned char** d) {
+  if (ctx->stage_cap < bytes) {
+    FEASM_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
+    if (ctx->h_stage) cudaFreeHost(ctx->h_stage);
+    release(ctx->d_stage);
+    ctx->h_stage = nullptr; ctx->stage_cap = 0;
+    size_t cap = 64 * 1024;
+    while (cap < bytes) cap *= 2;
+    FEASM_CUDA(ctx, cudaMallocHost(&ctx->h_stage, cap));
+    FEASM_CUDA(ctx, cudaMalloc(&ctx->d_stage, cap));
+    ctx->stage_cap = cap;
+  }
+  *h = ctx->h_stage; *d = ctx->d_stage;
+  return FEASM_OK;
+}
+
+// mode 0: add (SparseMatrix::add_matrix, sparse_matrix.h:312), mode 1: set (SparseMatrix::set, :295)
+static int put_block(feasm_ctx* ctx, const double* dm, const uint32_t* rows, int nr, const uint32_t* cols, int nc, int mode) {
   if (!ctx || !ctx->d_values) return feasm_fail(ctx, FEASM_ERR_STATE, "no matrix");
   if (!dm || !rows || !cols || nr <= 0 || nc <= 0) return feasm_fail(ctx, FEASM_ERR_ARG, "bad add_matrix arguments");
   for (int i = 0; i < nr; ++i)
     if (rows[i] >= (uint64_t)ctx->n_rows) return feasm_fail(ctx, FEASM_ERR_ARG, "row out of range");
-  double* d_dm = nullptr;
-  uint32_t *d_r = nullptr, *d_c = nullptr;
-  FEASM_CUDA(ctx, cudaMalloc(&d_dm, sizeof(double) * nr * nc));
-  FEASM_CUDA(ctx, cudaMalloc(&d_r, sizeof(uint32_t) * nr));
-  FEASM_CUDA(ctx, cudaMalloc(&d_c, sizeof(uint32_t) * nc));
-  cudaMemcpyAsync(d_dm, dm, sizeof(double) * nr * nc, cudaMemcpyHostToDevice, ctx->stream);
-  cudaMemcpyAsync(d_r, rows, sizeof(uint32_t) * nr, cudaMemcpyHostToDevice, ctx->stream);
-  cudaMemcpyAsync(d_c, cols, sizeof(uint32_t) * nc, cudaMemcpyHostToDevice, ctx->stream);
-  cudaMemsetAsync(ctx->d_flags, 0, 2 * sizeof(int), ctx->stream);
-  int rc = feasm_launch_add_matrix(ctx, d_dm, d_r, nr, d_c, nc);
-  if (!rc) rc = check_flags(ctx);
-  cudaFree(d_dm); cudaFree(d_r); cudaFree(d_c);
-  return rc;
+  FEASM_CUDA(ctx, cudaSetDevice(ctx->device));
+  const size_t dm_b = sizeof(double) * (size_t)nr * nc, r_b = sizeof(uint32_t) * nr, c_b = sizeof(uint32_t) * nc;
+  unsigned char *h = nullptr, *d = nullptr;
+  int rc = stage_block(ctx, dm_b + r_b + c_b, &h, &d);
+  if (rc) return rc;
+  FEASM_CUDA(ctx, cudaStreamSynchronize(ctx->stream));  // the previous call's copy has left the pinned block
+  std::memcpy(h, dm, dm_b); std::memcpy(h + dm_b, rows, r_b); std::memcpy(h + dm_b + r_b, cols, c_b);
+  FEASM_CUDA(ctx, cudaMemcpyAsync(d, h, dm_b + r_b + c_b, cudaMemcpyHostToDevice, ctx->stream));
+  rc = feasm_launch_add_matrix(ctx, reinterpret_cast<const double*>(d), reinterpret_cast<const uint32_t*>(d + dm_b), nr,
+                               reinterpret_cast<const uint32_t*>(d + dm_b + r_b), nc, mode);
+  return rc ? rc : check_flags(ctx);  // "add to an entry outside the pattern" is reported by the call that did it
+}
+
+int feasm_add_matrix(feasm_ctx* ctx, const double* dm, const uint32_t* rows, int nr, const uint32_t* cols, int nc) {
+  return put_block(ctx, dm, rows, nr, cols, nc, 0);
+}
+int feasm_set_matrix(feasm_ctx* ctx, const double* dm, const uint32_t* rows, int nr, const uint32_t* cols, int nc) {
+  return put_block(ctx, dm, rows, nr, cols, nc, 1);
 }
 
 int feasm_add_vector(feasm_ctx* ctx, const double* v, const uint32_t* rows, int n) {
   if (!ctx || !ctx->d_rhs) return feasm_fail(ctx, FEASM_ERR_STATE, "no vector");
   if (!v || !rows || n <= 0) return feasm_fail(ctx, FEASM_ERR_ARG, "bad add_vector arguments");
-  // a vector is a 1-column matrix over the RHS: reuse the exchange unpack kernel semantics on the host side
-  std::vector<double> cur(n);
-  FEASM_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
-  for (int i = 0; i < n; ++i) {
+  for (int i = 0; i < n; ++i)
     if (rows[i] >= (uint64_t)ctx->n_rows) return feasm_fail(ctx, FEASM_ERR_ARG, "row out of range");
-    FEASM_CUDA(ctx, cudaMemcpy(&cur[i], ctx->d_rhs + rows[i], sizeof(double), cudaMemcpyDeviceToHost));
-    cur[i] += v[i];
-    FEASM_CUDA(ctx, cudaMemcpy(ctx->d_rhs + rows[i], &cur[i], sizeof(double), cudaMemcpyHostToDevice));
-  }
+  FEASM_CUDA(ctx, cudaSetDevice(ctx->device));
+  const size_t v_b = sizeof(double) * (size_t)n, r_b = sizeof(uint32_t) * n;
+  unsigned char *h = nullptr, *d = nullptr;
+  int rc = stage_block(ctx, v_b + r_b, &h, &d);
+  if (rc) return rc;
+  FEASM_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
+  std::memcpy(h, v, v_b); std::memcpy(h + v_b, rows, r_b);
+  FEASM_CUDA(ctx, cudaMemcpyAsync(d, h, v_b + r_b, cudaMemcpyHostToDevice, ctx->stream));
+  // NumericVector::add_vector (numeric_vector.C:690-697): entries of one call may repeat a row; they are added in order
+  return feasm_launch_add_vector(ctx, reinterpret_cast<const double*>(d), reinterpret_cast<const uint32_t*>(d + v_b), n);
+}
+
+// A context that holds only a matrix (pattern + values) and a right-hand side: what SparseMatrix::init / clone /
+// get_transpose need when no mesh is attached; the per-element virtuals (add_matrix, set, add_vector), zero, the getters and
+// vector_mult work on it.
+int feasm_init_matrix(feasm_ctx* ctx, int64_t n_rows, int64_t n_owned, const uint64_t* row_ptr, const uint32_t* col_idx) {
+  if (!ctx) return FEASM_ERR_ARG;
+  if (n_rows <= 0 || n_owned < 0 || n_owned > n_rows || !row_ptr || !col_idx) return feasm_fail(ctx, FEASM_ERR_ARG, "bad matrix arguments");
+  if (n_rows >= 0xffffffffll) return feasm_fail(ctx, FEASM_ERR_ARG, "dof ids are 32-bit (dof_id_type)");
+  FEASM_CUDA(ctx, cudaSetDevice(ctx->device));
+  feasm_reset_mesh(ctx, 0, 0, 0);
+  release(ctx->d_xyz); release(ctx->d_conn); release(ctx->d_elem_dofs); release(ctx->d_gid);
+  int rc = feasm_reset_dofs(ctx, 1, n_rows, n_owned);
+  if (rc) return rc;
+  ctx->matrix_only = true;
+  return feasm_set_pattern(ctx, row_ptr, col_idx);
+}
+
+int feasm_set_values(feasm_ctx* ctx, const double* values, const double* rhs) {
+  if (!ctx || !ctx->d_values) return feasm_fail(ctx, FEASM_ERR_STATE, "no matrix");
+  FEASM_CUDA(ctx, cudaSetDevice(ctx->device));
+  if (values) FEASM_CUDA(ctx, cudaMemcpyAsync(ctx->d_values, values, sizeof(double) * ctx->nnz, cudaMemcpyHostToDevice, ctx->stream));
+  if (rhs) FEASM_CUDA(ctx, cudaMemcpyAsync(ctx->d_rhs, rhs, sizeof(double) * ctx->n_rows, cudaMemcpyHostToDevice, ctx->stream));
+  FEASM_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
   return FEASM_OK;
 }
 

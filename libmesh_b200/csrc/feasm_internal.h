@@ -158,6 +158,12 @@ struct feasm_ctx {
   cudaEvent_t ev_packed = nullptr, ev_exchanged = nullptr;
   bool exchange_open = false;
 
+  // per-element compat route (feasm_add_matrix / feasm_add_vector): staging blocks, kept
+  unsigned char* h_stage = nullptr;  // pinned
+  unsigned char* d_stage = nullptr;
+  size_t stage_cap = 0;
+  bool matrix_only = false;  // feasm_init_matrix: pattern + values without a mesh
+
   float last_ms[4] = {0, 0, 0, 0};
   int last_launches = 0;
   bool assemble_open = false;  // between feasm_assemble_begin and feasm_assemble_end
@@ -216,7 +222,9 @@ int feasm_launch_pack(feasm_ctx* ctx);
 int feasm_launch_unpack(feasm_ctx* ctx);
 // feasm_comm.cu: destroys an owned communicator and the communication stream
 void feasm_comm_release(feasm_ctx* ctx);
+// mode 0: add, 1: set
 int feasm_launch_add_matrix(feasm_ctx* ctx, const double* d_dm, const uint32_t* d_rows, int nr, const uint32_t* d_cols,
-                            int nc);
+                            int nc, int mode = 0);
+int feasm_launch_add_vector(feasm_ctx* ctx, const double* d_v, const uint32_t* d_rows, int n);
 
 #endif

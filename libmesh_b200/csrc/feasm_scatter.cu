@@ -232,7 +232,7 @@ __global__ void k_scatter_constraints(const uint32_t* __restrict__ rows, const d
 // call are distinct slots so there is no race).
 __global__ void k_add_matrix(const double* __restrict__ dm, const uint32_t* __restrict__ rows, int nr,
                              const uint32_t* __restrict__ cols, int nc, const uint64_t* __restrict__ row_ptr,
-                             const uint32_t* __restrict__ col_idx, double* __restrict__ values, int* flags) {
+                             const uint32_t* __restrict__ col_idx, double* __restrict__ values, int* flags, int mode) {
   const int t = blockIdx.x * blockDim.x + threadIdx.x;
   if (t >= nr * nc) return;
   const int i = t / nc, j = t % nc;
@@ -245,8 +245,14 @@ __global__ void k_add_matrix(const double* __restrict__ dm, const uint32_t* __re
     const int mid = (lo + hi) >> 1;
     if (c[mid] < col) lo = mid + 1; else hi = mid;
   }
-  if (lo < len && c[lo] == col) values[row_ptr[row] + lo] += v;
+  // add: atomic, so a block that names a dof twice (repeated ids in rows / cols) loses nothing
+  if (lo < len && c[lo] == col) { if (mode) values[row_ptr[row] + lo] = v; else atomicAdd(&values[row_ptr[row] + lo], v); }
   else if (v != 0.) atomicAdd(&flags[1], 1);  // zero may be "added" to a missing entry (sparse_matrix.h:300-303)
+}
+
+// NumericVector::add_vector for one host-supplied list: one thread walks it, so repeated rows add in order
+__global__ void k_add_vector(const double* __restrict__ v, const uint32_t* __restrict__ rows, int n, double* __restrict__ rhs) {
+  for (int i = 0; i < n; ++i) rhs[rows[i]] += v[i];
 }
 
 template <typename PosT, int ND>
@@ -391,9 +397,16 @@ int feasm_launch_scatter_constraints(feasm_ctx* ctx, int64_t n, int64_t n_prev, 
 }
 
 int feasm_launch_add_matrix(feasm_ctx* ctx, const double* d_dm, const uint32_t* d_rows, int nr, const uint32_t* d_cols,
-                            int nc) {
+                            int nc, int mode) {
   const int n = nr * nc;
-  k_add_matrix<<<(n + 127) / 128, 128, 0, ctx->stream>>>(d_dm, d_rows, nr, d_cols, nc, ctx->d_row_ptr, ctx->d_col_idx, ctx->d_values, ctx->d_flags);
+  k_add_matrix<<<(n + 127) / 128, 128, 0, ctx->stream>>>(d_dm, d_rows, nr, d_cols, nc, ctx->d_row_ptr, ctx->d_col_idx, ctx->d_values, ctx->d_flags,
+                                                         mode);
+  FEASM_CUDA(ctx, cudaGetLastError());
+  return FEASM_OK;
+}
+
+int feasm_launch_add_vector(feasm_ctx* ctx, const double* d_v, const uint32_t* d_rows, int n) {
+  k_add_vector<<<1, 1, 0, ctx->stream>>>(d_v, d_rows, n, ctx->d_rhs);
   FEASM_CUDA(ctx, cudaGetLastError());
   return FEASM_OK;
 }

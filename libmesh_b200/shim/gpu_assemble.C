@@ -3,6 +3,7 @@
 // then runs the assembly on the GPU and hands the RHS back to the system's NumericVector.
 #include "gpu_assemble.h"
 
+#include <cstring>
 #include <unordered_map>
 
 namespace feasm_libmesh {
@@ -18,11 +19,11 @@ int feasm_type(ElemType t) {
   }
 }
 
-// one flattening per (matrix, mesh size): the adaptor owns the context, this caches what was uploaded
-struct Uploaded { const MeshBase* mesh = nullptr; std::size_t n_elem = 0; };
-std::unordered_map<const void*, Uploaded>& cache() {
-  static std::unordered_map<const void*, Uploaded> c;
-  return c;
+// FNV-1a over the bit patterns of the node coordinates: a moved mesh is uploaded again, an unchanged one is not
+uint64_t checksum(const std::vector<double>& v) {
+  uint64_t h = 1469598103934665603ull;
+  for (double d : v) { uint64_t u; std::memcpy(&u, &d, 8); h = (h ^ u) * 1099511628211ull; }
+  return h;
 }
 }  // namespace
 
@@ -40,11 +41,16 @@ void assemble(EquationSystems& es, const std::string& system_name, const feasm_p
   feasm_ctx* ctx = A->ctx();
   const dof_id_type first = dof_map.first_dof(), n_local = dof_map.end_dof() - first;
 
-  // ---- flatten the mesh and the dof map (first call, or a different / refined mesh) ---------------------------
+  // ---- flatten the mesh and the dof map.  What was uploaded is remembered IN the matrix (GpuSparseMatrix::uploaded();
+  // reset by clear() and update_sparsity_pattern(), so a System::reinit or a new matrix starts over).  The node
+  // coordinates are read on every call, as the reference reads elem->point() in every assemble, and uploaded again when
+  // they moved; connectivity and dof numbering are flattened again when the mesh, its size or the dof ranges changed.
   std::size_t n_elem = 0;
   for (const Elem* e : mesh.active_local_element_ptr_range()) { (void)e; ++n_elem; }
-  Uploaded& up = cache()[A];
-  if (up.mesh != &mesh || up.n_elem != n_elem) {
+  if (!n_elem) libmesh_error_msg("no local elements");
+  auto& up = A->uploaded();
+  const bool reflatten = up.mesh != &mesh || up.n_elem != n_elem || up.n_dofs != dof_map.n_dofs() || up.n_local != n_local || up.first != first;
+  {
     std::unordered_map<dof_id_type, uint32_t> local_node;
     std::vector<double> xyz;
     std::vector<uint32_t> conn, elem_dofs;
@@ -61,8 +67,9 @@ void assemble(EquationSystems& es, const std::string& system_name, const feasm_p
           it = local_node.emplace(node->id(), (uint32_t)local_node.size()).first;
           xyz.push_back((*node)(0)); xyz.push_back((*node)(1)); xyz.push_back((*node)(2));
         }
-        conn.push_back(it->second);
+        if (reflatten) conn.push_back(it->second);
       }
+      if (!reflatten) continue;
       dof_map.dof_indices(elem, di);  // variable-major (src/base/dof_map.C:2280-2308)
       if (nd && (int)di.size() != nd) libmesh_error_msg("libfeasm needs the same number of dofs on every element");
       nd = (int)di.size();
@@ -71,11 +78,17 @@ void assemble(EquationSystems& es, const std::string& system_name, const feasm_p
         elem_dofs.push_back(d - first);
       }
     }
-    if (!n_elem) libmesh_error_msg("no local elements");
-    A->check(feasm_set_mesh(ctx, type, (int64_t)n_elem, (int64_t)local_node.size(), xyz.data(), conn.data()));
-    A->check(feasm_set_dofs(ctx, nd / type, n_local, n_local, elem_dofs.data(), nullptr));
-    A->send_pattern();
-    up.mesh = &mesh; up.n_elem = n_elem;
+    const uint64_t sum = checksum(xyz);
+    if (reflatten) {
+      A->check(feasm_set_mesh(ctx, type, (int64_t)n_elem, (int64_t)local_node.size(), xyz.data(), conn.data()));
+      A->check(feasm_set_dofs(ctx, nd / type, n_local, n_local, elem_dofs.data(), nullptr));
+      A->pattern_invalidated();
+      A->send_pattern();
+      up.mesh = &mesh; up.n_elem = n_elem; up.n_dofs = dof_map.n_dofs(); up.n_local = n_local; up.first = first;
+    } else if (sum != up.xyz_sum) {
+      A->check(feasm_update_coordinates(ctx, xyz.data()));
+    }
+    up.xyz_sum = sum;
   }
 
   // ---- loaded sides: the `if (elem->neighbor_ptr(side) == nullptr) ... has_boundary_id(elem, side, id)` test of

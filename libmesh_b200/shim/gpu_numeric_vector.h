@@ -160,7 +160,14 @@ class GpuNumericVector : public NumericVector<T> {
     feasm_vec_free(ctx(), tmp);
     if (rc) libmesh_error_msg("libfeasm error " << rc << " in add_vector: " << feasm_last_error(G->ctx()));
   }
-  void add_vector_transpose(const NumericVector<T>&, const SparseMatrix<T>&) override { libmesh_not_implemented(); }
+  // this += A^T v (numeric_vector.h): the transposed product through SparseMatrix::get_transpose on the device matrix
+  void add_vector_transpose(const NumericVector<T>& v, const SparseMatrix<T>& A) override {
+    auto* G = dynamic_cast<const GpuSparseMatrix<T>*>(&A);
+    if (!G) libmesh_error_msg("GpuNumericVector::add_vector_transpose: the matrix is not a GpuSparseMatrix");
+    GpuSparseMatrix<T> At(A.comm());
+    G->get_transpose(At);
+    this->add_vector(v, At);
+  }
 
   // ---- localize: one rank, so every flavour is a copy ------------------------------------------------------------
   void localize(std::vector<T>& v_local) const override {

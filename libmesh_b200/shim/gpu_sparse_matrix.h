@@ -47,6 +47,7 @@ class GpuSparseMatrix : public SparseMatrix<T> {
       _row_ptr.push_back(_col_idx.size());
     }
     _pattern_sent = false;
+    _uploaded = Uploaded();  // the dof set behind the Graph may have changed: the hook flattens again
   }
 
   void init(const numeric_index_type m, const numeric_index_type n, const numeric_index_type m_l, const numeric_index_type n_l,
@@ -66,6 +67,8 @@ class GpuSparseMatrix : public SparseMatrix<T> {
     _ctx = nullptr;
     _row_ptr.clear(); _col_idx.clear(); _host_values.clear();
     _pattern_sent = false; _closed = false; this->_is_initialized = false;
+    _uploaded = Uploaded();  // the context is gone: nothing is uploaded any more
+    _host_valid = false;
   }
   void zero() override { if (_ctx && _pattern_sent) check(feasm_zero(_ctx)); _host_valid = false; }
   // same communicator, dof map and sparsity pattern, all values zero (sparse_matrix.h:219); its context is created on
@@ -78,7 +81,17 @@ class GpuSparseMatrix : public SparseMatrix<T> {
     Z->_is_initialized = this->_is_initialized;
     return Z;
   }
-  std::unique_ptr<SparseMatrix<T>> clone() const override { libmesh_not_implemented(); }
+  // sparse_matrix.h:226: zero_clone plus the values, copied on the device
+  std::unique_ptr<SparseMatrix<T>> clone() const override {
+    auto Z = this->zero_clone();
+    auto* G = static_cast<GpuSparseMatrix<T>*>(Z.get());
+    if (_ctx && _pattern_sent) {
+      G->ensure_matrix();
+      check(feasm_synchronize(_ctx));
+      check(feasm_vec_copy(G->ctx(), FEASM_COPY_D2D, feasm_device_values(G->ctx()), feasm_device_values(_ctx), (int64_t)_col_idx.size()));
+    }
+    return Z;
+  }
   void close() override { if (_ctx) check(feasm_synchronize(_ctx)); _closed = true; }
   bool closed() const override { return _closed; }
 
@@ -89,9 +102,16 @@ class GpuSparseMatrix : public SparseMatrix<T> {
   numeric_index_type col_start() const override { return _row_start; }
   numeric_index_type col_stop() const override { return _row_stop; }
 
-  void set(const numeric_index_type, const numeric_index_type, const T) override { libmesh_not_implemented(); }
+  void set(const numeric_index_type i, const numeric_index_type j, const T value) override {  // sparse_matrix.h:295
+    std::lock_guard<std::mutex> lock(_mutex);
+    ensure_matrix();
+    const uint32_t r = i - _row_start, c = j;
+    check(feasm_set_matrix(ctx(), &value, &r, 1, &c, 1));
+    _host_valid = false; _closed = false;
+  }
   void add(const numeric_index_type i, const numeric_index_type j, const T value) override {
     std::lock_guard<std::mutex> lock(_mutex);
+    ensure_matrix();
     const uint32_t r = i - _row_start, c = j;
     check(feasm_add_matrix(ctx(), &value, &r, 1, &c, 1));
     _host_valid = false; _closed = false;
@@ -102,6 +122,7 @@ class GpuSparseMatrix : public SparseMatrix<T> {
                   const std::vector<numeric_index_type>& cols) override {
     std::lock_guard<std::mutex> lock(_mutex);
     if (dm.m() != rows.size() || dm.n() != cols.size()) libmesh_error_msg("add_matrix: size mismatch");
+    ensure_matrix();  // SparseMatrix::init + add_matrix works without the batched hook
     std::vector<uint32_t> lr(rows.size());
     for (std::size_t k = 0; k < rows.size(); ++k) lr[k] = rows[k] - _row_start;
     check(feasm_add_matrix(ctx(), dm.get_values().data(), lr.data(), (int)lr.size(), cols.data(), (int)cols.size()));
@@ -110,7 +131,18 @@ class GpuSparseMatrix : public SparseMatrix<T> {
   void add_matrix(const DenseMatrix<T>& dm, const std::vector<numeric_index_type>& dof_indices) override {
     this->add_matrix(dm, dof_indices, dof_indices);
   }
-  void add(const T, const SparseMatrix<T>&) override { libmesh_not_implemented(); }
+  // this += a X for a matrix with the same sparsity pattern (sparse_matrix.h:344), on the device
+  void add(const T a, const SparseMatrix<T>& X) override {
+    std::lock_guard<std::mutex> lock(_mutex);
+    auto* G = dynamic_cast<GpuSparseMatrix<T>*>(const_cast<SparseMatrix<T>*>(&X));
+    if (!G) libmesh_error_msg("GpuSparseMatrix::add(a, X): X is not a GpuSparseMatrix");
+    if (G->_row_ptr != _row_ptr || G->_col_idx != _col_idx) libmesh_error_msg("GpuSparseMatrix::add(a, X): X has a different sparsity pattern");
+    ensure_matrix();
+    G->ensure_matrix();
+    check(feasm_synchronize(G->ctx()));  // X's values are complete before this context's stream reads them
+    check(feasm_vec_axpy(ctx(), feasm_device_values(ctx()), a, feasm_device_values(G->ctx()), (int64_t)_col_idx.size()));
+    _host_valid = false; _closed = false;
+  }
 
   T operator()(const numeric_index_type i, const numeric_index_type j) const override {
     mirror();
@@ -146,7 +178,32 @@ class GpuSparseMatrix : public SparseMatrix<T> {
     for (std::size_t r = 0; r + 1 < _row_ptr.size(); ++r) dest.set(r + _row_start, (*this)(r + _row_start, r + _row_start));
     dest.close();
   }
-  void get_transpose(SparseMatrix<T>&) const override { libmesh_not_implemented(); }
+  // sparse_matrix.h:598: dest = this^T, a square matrix on one rank; the transposed CSR is built on the host (a setup-time
+  // operation in the reference too) and uploaded as a matrix-only context
+  void get_transpose(SparseMatrix<T>& dest) const override {
+    auto* D = dynamic_cast<GpuSparseMatrix<T>*>(&dest);
+    if (!D) libmesh_error_msg("GpuSparseMatrix::get_transpose: dest is not a GpuSparseMatrix");
+    if (_m != _n || _row_start != 0 || _row_stop != _m) libmesh_not_implemented();  // one rank, square
+    mirror();
+    const std::size_t n = _row_ptr.size() - 1;
+    std::vector<uint64_t> rp(n + 1, 0);
+    for (uint32_t c : _col_idx) ++rp[c + 1];
+    for (std::size_t r = 0; r < n; ++r) rp[r + 1] += rp[r];
+    std::vector<uint32_t> ci(_col_idx.size());
+    std::vector<T> val(_col_idx.size());
+    std::vector<uint64_t> cur(rp.begin(), rp.end() - 1);
+    for (std::size_t r = 0; r < n; ++r)  // rows ascending: every transposed row comes out with ascending columns
+      for (uint64_t k = _row_ptr[r]; k < _row_ptr[r + 1]; ++k) { const uint64_t q = cur[_col_idx[k]]++; ci[q] = (uint32_t)r; val[q] = _host_values[k]; }
+    if (D == this) libmesh_error_msg("GpuSparseMatrix::get_transpose: dest must be another matrix");
+    D->clear();
+    D->_dof_map = this->_dof_map;
+    D->_row_ptr = rp; D->_col_idx = ci;
+    D->_m = _m; D->_n = _n; D->_row_start = _row_start; D->_row_stop = _row_stop;
+    D->_is_initialized = true;
+    D->ensure_matrix();
+    D->check(feasm_set_values(D->ctx(), val.data(), nullptr));
+    D->_closed = true;
+  }
   void get_row(numeric_index_type i, std::vector<numeric_index_type>& indices, std::vector<T>& values) const override {
     mirror();  // ascending columns, as tests/numerics/sparse_matrix_test.h:88-149 expects
     const uint64_t lo = _row_ptr[i - _row_start], hi = _row_ptr[i - _row_start + 1];
@@ -179,6 +236,22 @@ class GpuSparseMatrix : public SparseMatrix<T> {
     }
     return _ctx;
   }
+  // The per-element virtuals without the batched hook: the stored Graph becomes a matrix-only context
+  void ensure_matrix() {
+    if (_pattern_sent) return;
+    if (_row_ptr.empty()) libmesh_error_msg("GpuSparseMatrix: update_sparsity_pattern was never called");
+    const int64_t n_local = (int64_t)_row_ptr.size() - 1;
+    check(feasm_init_matrix(ctx(), n_local, n_local, _row_ptr.data(), _col_idx.data()));
+    _pattern_sent = true;
+  }
+  // what the batched hook has uploaded into the context (reset by clear() and update_sparsity_pattern())
+  struct Uploaded {
+    const void* mesh = nullptr;
+    std::size_t n_elem = 0, n_dofs = 0, n_local = 0, first = 0;
+    uint64_t xyz_sum = 0;  // checksum of the node coordinates last uploaded
+  };
+  Uploaded& uploaded() { return _uploaded; }
+  void pattern_invalidated() { _pattern_sent = false; }  // feasm_set_dofs dropped the pattern with the old dof set
   // after feasm_set_mesh / feasm_set_dofs: hand the stored Graph to the context (host-pattern route)
   void send_pattern() {
     if (_pattern_sent) return;
@@ -209,6 +282,7 @@ class GpuSparseMatrix : public SparseMatrix<T> {
   mutable std::vector<T> _host_values;
   mutable bool _host_valid = false;
   bool _pattern_sent = false, _closed = false;
+  Uploaded _uploaded;
   std::mutex _mutex;
 };
 

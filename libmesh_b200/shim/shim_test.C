@@ -309,6 +309,95 @@ int main() {
     for (int64_t r = 0; r < n_dofs; ++r) REQUIRE(rhs._v[r] == b[r]);
   }
 
+  // ---- the rest of the SparseMatrix surface: clone, set, add(a, X), get_transpose, add_vector_transpose -------------------
+  {
+    auto Cl = A.clone();                                             // sparse_matrix.h:226: same values, its own storage
+    auto* C2 = static_cast<GpuSparseMatrix<Number>*>(Cl.get());
+    REQUIRE(C2->host_values() == A.host_values());
+    const numeric_index_type r5 = 5, c5 = graph[5][0];
+    const double a5 = A(r5, c5);
+    C2->set(r5, c5, 123.5);                                          // :295
+    C2->close();
+    REQUIRE((*C2)(r5, c5) == 123.5 && A(r5, c5) == a5);              // the clone is not a view
+    C2->set(r5, c5, a5);
+    C2->add(-1., A);                                                 // :344: C2 = C2 - A = 0
+    C2->close();
+    for (double v : C2->host_values()) REQUIRE(v == 0.);
+    C2->add(2., A);
+    C2->close();
+    for (std::size_t k = 0; k < A.host_values().size(); ++k) REQUIRE(C2->host_values()[k] == 2. * A.host_values()[k]);
+    // make A unsymmetric in one slot, then transpose
+    const numeric_index_type ri = 7, cj = graph[7][0] == 7 ? graph[7][1] : graph[7][0];
+    A.add(ri, cj, 0.375);
+    A.close();
+    GpuSparseMatrix<Number> At(comm);
+    A.get_transpose(At);                                             // :598
+    for (int64_t r = 0; r < n_dofs; ++r) {
+      std::vector<numeric_index_type> idx;
+      std::vector<Number> val;
+      At.get_row((numeric_index_type)r, idx, val);
+      for (std::size_t k = 0; k < idx.size(); ++k) REQUIRE(val[k] == A(idx[k], (numeric_index_type)r));
+      for (std::size_t k = 1; k < idx.size(); ++k) REQUIRE(idx[k - 1] < idx[k]);
+    }
+    REQUIRE(At(cj, ri) == A(ri, cj) && At(ri, cj) == A(cj, ri));
+    // y += A^T v against y += At v
+    GpuNumericVector<Number> gv2(comm, (numeric_index_type)n_dofs), y1(comm, (numeric_index_type)n_dofs), y2(comm, (numeric_index_type)n_dofs);
+    std::vector<Number> hv(n_dofs);
+    for (int64_t i = 0; i < n_dofs; ++i) hv[i] = std::sin(0.3 * i) + 0.1;
+    gv2 = hv;
+    y1.add_vector_transpose(gv2, A);
+    y2.add_vector(gv2, At);
+    std::vector<Number> h1, h2;
+    y1.localize(h1); y2.localize(h2);
+    REQUIRE(h1 == h2);
+    A.add(ri, cj, -0.375);
+    A.close();
+  }
+  // ---- SparseMatrix::init + the per-element virtuals WITHOUT the batched hook (tests/numerics/sparse_matrix_test.h:88-149) ---
+  {
+    GpuSparseMatrix<Number> B(comm);
+    B.attach_dof_map(dof_map);
+    B.update_sparsity_pattern(graph);
+    B.init();
+    DenseMatrix<Number> d3;
+    d3._m = d3._n = 3; d3._val = {1., 2., 3., 4., 5., 6., 7., 8., 9.};
+    std::vector<numeric_index_type> dofs3 = {dof_map._elem_dofs[0], dof_map._elem_dofs[1], dof_map._elem_dofs[2]};
+    B.add_matrix(d3, dofs3);
+    B.add_matrix(d3, dofs3);
+    B.close();
+    for (int a = 0; a < 3; ++a)
+      for (int c = 0; c < 3; ++c) REQUIRE(B(dofs3[a], dofs3[c]) == 2. * d3._val[3 * a + c]);
+    std::vector<numeric_index_type> idx;
+    std::vector<Number> val;
+    B.get_row(dofs3[1], idx, val);
+    REQUIRE(idx == graph[dofs3[1]]);
+    double row_sum = 0.;
+    for (double v : val) row_sum += v;
+    REQUIRE(row_sum == 2. * (4. + 5. + 6.));
+    B.zero();
+    B.close();
+    REQUIRE(B.linfty_norm() == 0.);
+  }
+  // ---- a moved mesh: the hook reads the node coordinates on every call (stale flatten cache) ---------------
+  {
+    feasm_libmesh::assemble_poisson_ex4(es, "Poisson");
+    const std::vector<Number> v_before = A.host_values();
+    std::vector<double> x0;
+    for (auto& nd : nodes) { x0.push_back(nd.c[0]); nd.c[0] *= 1.25; }  // stretch in x: every element matrix changes
+    feasm_libmesh::assemble_poisson_ex4(es, "Poisson");
+    REQUIRE(A.host_values() != v_before);
+    for (std::size_t i = 0; i < nodes.size(); ++i) nodes[i].c[0] = x0[i];
+    feasm_libmesh::assemble_poisson_ex4(es, "Poisson");
+    REQUIRE(A.host_values() == v_before);
+    // System::reinit path: clear() drops the context, the next hook call uploads everything again
+    A.clear();
+    A.attach_dof_map(dof_map);
+    A.update_sparsity_pattern(graph);
+    A.init();
+    feasm_libmesh::assemble_poisson_ex4(es, "Poisson");
+    REQUIRE(A.host_values() == v_before);
+  }
+
   auto Z = A.zero_clone();
   REQUIRE(Z->m() == A.m());
   A.clear();
