@@ -780,6 +780,7 @@ k_elem_elasticity(const double* __restrict__ xyz, const uint32_t* __restrict__ c
     product(2, 2, tile + 2 * TILE, std::true_type{});
     __syncwarp();
     if (lane < NPE) {
+#pragma unroll 3  // three rows in flight: the loop is a chain of shared-memory loads feeding stores, not issue bound
       for (int a = 0; a < NPE; ++a) {
         const double p0 = tile[a * TLD + lane], p1 = tile[TILE + a * TLD + lane], p2 = tile[2 * TILE + a * TLD + lane];
         const double tr = lam2 * ((p0 + p1) + p2);
@@ -802,6 +803,7 @@ k_elem_elasticity(const double* __restrict__ xyz, const uint32_t* __restrict__ c
       product(i, k, tile, std::false_type{});
       __syncwarp();
       if (lane < NPE) {
+#pragma unroll 3
         for (int a = 0; a < NPE; ++a) {
           const double p = tile[a * TLD + lane], pt = tile[lane * TLD + a];
           out[(i * NPE + a) * LDR + k * NPE + lane] = lam1 * p + lam2 * pt;

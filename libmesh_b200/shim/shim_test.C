@@ -8,6 +8,7 @@
 #include <set>
 #include <sstream>
 
+#include "compare_mode.h"
 #include "gpu_assemble.h"
 
 using namespace libMesh;
@@ -396,6 +397,24 @@ int main() {
     A.init();
     feasm_libmesh::assemble_poisson_ex4(es, "Poisson");
     REQUIRE(A.host_values() == v_before);
+  }
+
+  // ---- compare mode (compare_mode.h), here with the hook on both sides: exercises the comparison a libMesh box runs against
+  // the reference's own assemble function
+  {
+    GpuSparseMatrix<Number> A2(comm);
+    A2.attach_dof_map(dof_map);
+    A2.update_sparsity_pattern(graph);
+    A2.init();
+    NumericVector<Number> b1(comm), b2(comm);
+    b1.init((numeric_index_type)n_dofs); b2.init((numeric_index_type)n_dofs);
+    auto rep = feasm_libmesh::compare_assembly(es, "Poisson", feasm_libmesh::assemble_poisson_ex4, A, b1, feasm_libmesh::assemble_poisson_ex4, A2, b2);
+    REQUIRE(rep.passes() && rep.pattern_equal && rep.strict_failures == 0 && rep.entries == A.col_idx().size());
+    A2.add(5, graph[5][0], 1e-9);  // a planted difference is found
+    A2.close();
+    rep = feasm_libmesh::compare_systems(A, b1, A2, b2);
+    REQUIRE(!rep.passes() && rep.strict_failures == 1);
+    rep.print("compare mode self-check (one planted difference)");
   }
 
   auto Z = A.zero_clone();
