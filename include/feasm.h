@@ -145,6 +145,12 @@ int feasm_synchronize(feasm_ctx* ctx);
  * rank does NOT own (local rows n_owned..n_rows) and packs them into the send buffer (feasm_pack_ghost's buffer; it
  * must not be packed again); the caller starts its ncclSend/ncclRecv group, then _end reduces the owned rows while
  * the transfer is in flight; feasm_unpack_ghost after both.  Results are identical to feasm_assemble + pack. */
+/* "Assemble interface elements first, exchange while the interior assembles" (SURVEY 8e): the caller orders its local
+ * elements so that those touching a ghost row come first and names the length of that prefix; feasm_assemble_begin then
+ * assembles only the prefix before it reduces and packs the ghost rows, and feasm_assemble_end assembles the rest (under
+ * the transfer) before the owned rows.  0 (the default) = every element in _begin.  With LinearPartitioner slabs the
+ * prefix is the first element layer of the slab without any reordering.  Results do not depend on it. */
+int feasm_set_interface_prefix(feasm_ctx* ctx, int64_t n_elems);
 int feasm_assemble_begin(feasm_ctx* ctx, const feasm_params* params);
 int feasm_assemble_end(feasm_ctx* ctx);
 double* feasm_send_buffer(feasm_ctx* ctx, uint64_t* n_doubles); /* the packed buffer, without packing again */

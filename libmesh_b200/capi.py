@@ -35,7 +35,7 @@ SYMBOLS = [
     "feasm_generate_cube", "feasm_distribute_dofs_device", "feasm_generate_dirichlet", "feasm_get_mesh", "feasm_get_dofs",
     "feasm_get_constraints", "feasm_set_side_penalty", "feasm_residual", "feasm_add_matrix_noalloc",
     "feasm_set_communicator", "feasm_comm_unique_id", "feasm_comm_init", "feasm_exchange_begin", "feasm_exchange_end",
-    "feasm_exchange_ghost_rows", "feasm_comm_allgather_u64", "feasm_set_matrix", "feasm_init_matrix", "feasm_set_values",
+    "feasm_exchange_ghost_rows", "feasm_comm_allgather_u64", "feasm_set_matrix", "feasm_init_matrix", "feasm_set_values", "feasm_set_interface_prefix",
 ]
 
 
@@ -86,6 +86,7 @@ def lib():
         "feasm_add_matrix": (i32, [vp, vp, vp, i32, vp, i32]),
         "feasm_add_vector": (i32, [vp, vp, vp, i32]),
         "feasm_add_matrix_noalloc": (i32, [vp, vp, vp, i32, vp, i32]),
+        "feasm_set_interface_prefix": (i32, [vp, i64]),
         "feasm_set_matrix": (i32, [vp, vp, vp, i32, vp, i32]),
         "feasm_init_matrix": (i32, [vp, i64, i64, vp, vp]),
         "feasm_set_values": (i32, [vp, vp, vp]),
@@ -331,6 +332,9 @@ class Context:
         """introduction_ex3.C:386-455 penalty boundary term on the listed (element, side) pairs; empty lists clear."""
         e, sd = _c(elems, np.uint32), _c(sides, np.uint8)
         self._ck(self.L.feasm_set_side_penalty(self.h, len(e), _p(e), _p(sd), float(penalty), int(kind), float(value)))
+
+    def set_interface_prefix(self, n_elems):
+        self._ck(self.L.feasm_set_interface_prefix(self.h, int(n_elems)))
 
     def assemble_begin(self, params):
         self._ck(self.L.feasm_assemble_begin(self.h, C.byref(params)))

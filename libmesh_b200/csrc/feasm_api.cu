@@ -202,6 +202,8 @@ void feasm_reset_mesh(feasm_ctx* ctx, int elem_type, int64_t n_elem, int64_t n_n
   ctx->npe = elem_type;
   ctx->n_elem = n_elem;
   ctx->n_nodes = n_nodes;
+  ctx->n_iface = 0;
+  ctx->pending_e0 = -1;
   ctx->tab_qorder = -1;
   ctx->side_qorder = -1;
   release(ctx->d_side_elems); release(ctx->d_side_mask);  // element ids of the previous mesh
@@ -374,12 +376,19 @@ static int assemble_impl(feasm_ctx* ctx, const feasm_params* params, int mode) {
     if (rc) return rc;
     ++launches;
   }
-  rc = feasm_launch_element_kernel(ctx, *params, d_f, 0, ctx->n_elem, ctx->d_kf, rs, params->constrain);
+  // Interface elements first: when the caller named the prefix of elements that touch ghost rows
+  // (feasm_set_interface_prefix), feasm_assemble_begin assembles only those, reduces and packs the ghost rows, and the
+  // transfer then runs beside the element phase of all the other elements, which feasm_assemble_end launches.
+  const bool two_phase = mode == 1 && ctx->n_iface > 0 && ctx->n_iface < ctx->n_elem && ctx->n_owned < ctx->n_rows;
+  const int64_t e_first = two_phase ? ctx->n_iface : ctx->n_elem;
+  rc = feasm_launch_element_kernel(ctx, *params, d_f, 0, e_first, ctx->d_kf, rs, params->constrain);
   if (rc) return rc;
   if (ctx->n_con_elems > 0) ++launches;
   if (params->problem == FEASM_POISSON && params->affine_tensor) ++launches;  // the list kernel for non-affine elements
   FEASM_CUDA(ctx, cudaEventRecord(ctx->ev[1], ctx->stream));
   ctx->last_launches = launches;
+  ctx->pending_e0 = two_phase ? e_first : -1;
+  if (two_phase) { ctx->pending_params = *params; ctx->pending_f = d_f; }
   if (mode == 0) {
     rc = feasm_launch_row_reduce(ctx, nullptr, ctx->n_rows, ctx->stream);
     if (rc) return rc;
@@ -430,9 +439,27 @@ int feasm_assemble_end(feasm_ctx* ctx) {
   if (!ctx->assemble_open) return feasm_fail(ctx, FEASM_ERR_STATE, "feasm_assemble_end without feasm_assemble_begin");
   FEASM_CUDA(ctx, cudaSetDevice(ctx->device));
   ctx->assemble_open = false;
-  const int rc = feasm_launch_row_reduce(ctx, nullptr, ctx->n_owned, ctx->stream);
+  int rc = FEASM_OK;
+  if (ctx->pending_e0 >= 0) {  // the elements that touch no ghost row, while the ghost rows travel
+    const int rs = feasm_recb(ctx->nd, ctx->pos_bytes) / 8;
+    const int64_t e0 = ctx->pending_e0;
+    ctx->pending_e0 = -1;
+    rc = feasm_launch_element_kernel(ctx, ctx->pending_params, ctx->pending_f, e0, ctx->n_elem,
+                                     ctx->d_kf + (size_t)e0 * ctx->nd * rs, rs, ctx->pending_params.constrain);
+    if (rc) return rc;
+    ++ctx->last_launches;
+    FEASM_CUDA(ctx, cudaEventRecord(ctx->ev[1], ctx->stream));
+  }
+  rc = feasm_launch_row_reduce(ctx, nullptr, ctx->n_owned, ctx->stream);
   if (rc) return rc;
   FEASM_CUDA(ctx, cudaEventRecord(ctx->ev[2], ctx->stream));
+  return FEASM_OK;
+}
+
+int feasm_set_interface_prefix(feasm_ctx* ctx, int64_t n_elems) {
+  if (!ctx) return FEASM_ERR_ARG;
+  if (n_elems < 0 || n_elems > ctx->n_elem) return feasm_fail(ctx, FEASM_ERR_ARG, "interface prefix out of range");
+  ctx->n_iface = n_elems;
   return FEASM_OK;
 }
 

@@ -238,8 +238,7 @@ struct ElemRegs {
   double Fe;
 };
 
-// Phase A of one element by one warp, and Fe: FEMap::compute_map at quadrature point q = lane, the forcing, then
-// Fe(a) on lane a (introduction_ex4.C:536-537).  X holds the element's node coordinates, fw is a 32-double scratch.
+// Phase A of one element by one warp: FEMap::compute_map at quadrature point q = lane and the forcing (fw = JxW f).  X holds the element's node coordinates, fw is a 32-double scratch.
 // Returns has_affine_map; S = sqrt(det J) * inverse-Jacobian rows (the same on every lane when affine).
 template <int NPE, int NQ>
 __device__ __forceinline__ bool elem_geom(const double* X, double* fw, const double* s_tab, int lane, int forcing,
@@ -267,8 +266,15 @@ __device__ __forceinline__ bool elem_geom(const double* X, double* fw, const dou
     }
     fw[lane] = lane < NQ ? JxW * f : 0.;
   }
-  __syncwarp();
   Fe_out = 0.;
+  return affine;
+}
+
+// Fe(a) on lane a from fw (introduction_ex4.C:536-537); three independent chains
+template <int NPE, int NQ>
+__device__ __forceinline__ double elem_fe(const double* fw, const double* s_tab, int lane, int forcing) {
+  const double* s_phi = s_tab;
+  double Fe_out = 0.;
   if (lane < NPE && forcing != FEASM_FORCING_NONE) {
     double Fe = 0., f1 = 0., f2 = 0.;
 #pragma unroll
@@ -281,7 +287,7 @@ __device__ __forceinline__ bool elem_geom(const double* X, double* fw, const dou
     for (int q = NQ - NQ % 3; q < NQ; ++q) Fe += fw[q] * s_phi[lane * NQ + q];
     Fe_out = (Fe + f1) + f2;
   }
-  return affine;
+  return Fe_out;
 }
 
 // Phases B+C: Ke = G G^T, G[i][(d,q)] = sqrt(JxW_q) dphi_i/dx_d(q), fragments generated in registers from S and the
@@ -353,7 +359,15 @@ __device__ __forceinline__ void elem_compute(const double* X, double* fw, const 
                                              int forcing, const double* __restrict__ f_tab_e, int* flags, ElemRegs<NPE, NQ>& R) {
   double S[9];
   const bool affine = elem_geom<NPE, NQ>(X, fw, s_tab, lane, forcing, f_tab_e, flags, S, R.Fe);
+#ifdef FEASM_DEV_FE_EARLY
+  __syncwarp();
+  R.Fe = elem_fe<NPE, NQ>(fw, s_tab, lane, forcing);
   elem_contract<NPE, NQ>(S, affine, twp, lane, R);
+#else
+  elem_contract<NPE, NQ>(S, affine, twp, lane, R);  // its shuffles order the fw stores before the reads below
+  __syncwarp();
+  R.Fe = elem_fe<NPE, NQ>(fw, s_tab, lane, forcing);
+#endif
 }
 
 // Phase D: the warp's fragments into the element's block of NPE records, rs doubles apart (row a = Ke(a,:) then Fe(a)

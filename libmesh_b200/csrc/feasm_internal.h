@@ -167,6 +167,10 @@ struct feasm_ctx {
   float last_ms[4] = {0, 0, 0, 0};
   int last_launches = 0;
   bool assemble_open = false;  // between feasm_assemble_begin and feasm_assemble_end
+  int64_t n_iface = 0;         // feasm_set_interface_prefix: elements [0, n_iface) touch ghost rows
+  int64_t pending_e0 = -1;     // feasm_assemble_end still has elements [pending_e0, n_elem) to assemble
+  feasm_params pending_params{};
+  const double* pending_f = nullptr;
 };
 
 // Every cudaFree of the library goes through this: a failing free means a stale or foreign pointer — a library bug that

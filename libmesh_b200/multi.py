@@ -17,6 +17,8 @@ The host logic is plain numpy + torch.distributed and is exercised on CPU with t
 """
 from __future__ import annotations
 
+import os
+
 import numpy as np
 
 
@@ -190,6 +192,13 @@ class DistributedAssembly:
         ctx.build_pattern()
         rp, ci = ctx.get_pattern()
         self.merge_and_plan(rp, ci)
+        # interface elements first: the leading local elements that cover every element touching a ghost row (with
+        # LinearPartitioner slabs: the first element layer).  Worth it when that prefix is a small part of the rank's elements.
+        touch = np.nonzero((p.elem_dofs >= p.n_owned).any(axis=1))[0]
+        prefix = int(touch[-1]) + 1 if len(touch) else 0
+        self.iface_prefix = prefix if 0 < prefix <= len(p.elems) // 3 and os.environ.get("FEASM_IFACE", "1") != "0" else 0
+        if hasattr(ctx, "set_interface_prefix"):
+            ctx.set_interface_prefix(self.iface_prefix)
 
     def merge_and_plan(self, rp, ci):
         """Ship ghost-row column lists to their owners, merge, and derive the slot plan.  Also usable stand-alone with a
