@@ -103,20 +103,79 @@ __device__ __forceinline__ double trig_fast(double a, int add) {
   return (n & 2) ? -res : res;
 }
 
+// trig_fast in two halves, so that evaluations whose quadrants have the same parity share ONE selection of the polynomial
+// coefficients: the reduction (quadrant n, reduced argument r) ...
+struct TrigRed { double r; int n; };
+__device__ __forceinline__ TrigRed trig_reduce(double a, int add) {
+  const double MAGIC = 6755399441055744.0;
+  const double q = __fma_rn(a, 0x1.45f306dc9c883p-1, MAGIC);
+  TrigRed t;
+  t.n = __double2loint(q) + add;
+  const double j = __dadd_rn(q, -MAGIC);
+  double r = __fma_rn(-j, 0x1.921fb54442d18p+0, a);
+  r = __fma_rn(-j, 0x1.1a62633145c07p-54, r);
+  t.r = __fma_rn(-j, -0x1.f1976b7ed8fbcp-110, r);
+  return t;
+}
+// ... and the polynomial for three reduced arguments of one parity (odd = cos kernel, even = sin kernel): the same
+// operations on the same values as three trig_fast calls — bitwise the same results, a third of the coefficient selects
+// (every select is an issue slot beside the FP64 pipe, profiles/r2/issue_probe.md).
+__device__ __forceinline__ void trig_poly3(const TrigRed (&t)[3], const bool odd, double (&out)[3]) {
+  const double c6 = odd ? -1.13596475577881948265e-11 : 1.58969099521155010221e-10;
+  const double c5 = odd ? 2.08757232129817482790e-09 : -2.50507602534068634195e-08;
+  const double c4 = odd ? -2.75573143513906633035e-07 : 2.75573137070700676789e-06;
+  const double c3 = odd ? 2.48015872894767294178e-05 : -1.98412698298579493134e-04;
+  const double c2 = odd ? -1.38888888888741095749e-03 : 8.33333333332248946124e-03;
+  const double c1 = odd ? 4.16666666666666019037e-02 : -1.66666666666666324348e-01;
+  const double c0 = odd ? -0.5 : 0.0;
+#pragma unroll
+  for (int k = 0; k < 3; ++k) {
+    const double r = t[k].r, x2 = __dmul_rn(r, r);
+    double z = __fma_rn(c6, x2, c5);
+    z = __fma_rn(z, x2, c4);
+    z = __fma_rn(z, x2, c3);
+    z = __fma_rn(z, x2, c2);
+    z = __fma_rn(z, x2, c1);
+    const double w = __fma_rn(z, x2, c0);
+    const double res = __fma_rn(w, odd ? x2 : r, odd ? 1.0 : r);
+    out[k] = (t[k].n & 2) ? -res : res;
+  }
+}
+
 // introduction_ex4.C:500-537 with exact_solution of introduction_ex3/exact_solution.C:40-47.  The seven
 // exact_solution() calls share nine distinct trig values; every product below is evaluated in the example's order
 // ((cos * sin) * cos), so the result equals the literal seven-call form bit for bit up to the last bit of sin/cos.
 // Explicit _rn intrinsics: no FMA contraction.  x / eps is evaluated as the correctly rounded quotient through
 // q0 = x*(1/eps), r = fma(-q0, eps, x), q = fma(r, 1/eps, q0) (Markstein; checked exhaustively-at-random on the host).
+// FAST: the three arguments of one axis (a - h eps, a, a + h eps) lie in quadrants of one parity except within 1.6e-3 of a
+// multiple of pi/4; when that holds for all three axes on every lane of the warp, each axis takes trig_poly3, else every
+// evaluation selects its own coefficients (trig_fast) — the same values either way.
 template <bool FAST>
 __device__ __forceinline__ double ex4_forcing_t(double x, double y, double z) {
   const double hp = .5 * 3.141592653589793;  // .5 * acos(-1.)
   const double eps = 1.e-3;
-  auto cs = [](double a) { return FAST ? trig_fast(a, 1) : cos(a); };
-  auto sn = [](double a) { return FAST ? trig_fast(a, 0) : sin(a); };
-  const double cx0 = cs(__dmul_rn(hp, x)), cxm = cs(__dmul_rn(hp, __dadd_rn(x, -eps))), cxp = cs(__dmul_rn(hp, __dadd_rn(x, eps)));
-  const double sy0 = sn(__dmul_rn(hp, y)), sym = sn(__dmul_rn(hp, __dadd_rn(y, -eps))), syp = sn(__dmul_rn(hp, __dadd_rn(y, eps)));
-  const double cz0 = cs(__dmul_rn(hp, z)), czm = cs(__dmul_rn(hp, __dadd_rn(z, -eps))), czp = cs(__dmul_rn(hp, __dadd_rn(z, eps)));
+  const double ax[3] = {__dmul_rn(hp, x), __dmul_rn(hp, __dadd_rn(x, -eps)), __dmul_rn(hp, __dadd_rn(x, eps))};
+  const double ay[3] = {__dmul_rn(hp, y), __dmul_rn(hp, __dadd_rn(y, -eps)), __dmul_rn(hp, __dadd_rn(y, eps))};
+  const double az[3] = {__dmul_rn(hp, z), __dmul_rn(hp, __dadd_rn(z, -eps)), __dmul_rn(hp, __dadd_rn(z, eps))};
+  double cx[3], sy[3], cz[3];  // [0] at the point, [1] minus eps, [2] plus eps
+  if (FAST) {
+    TrigRed tx[3], ty[3], tz[3];
+#pragma unroll
+    for (int k = 0; k < 3; ++k) { tx[k] = trig_reduce(ax[k], 1); ty[k] = trig_reduce(ay[k], 0); tz[k] = trig_reduce(az[k], 1); }
+    const int mixed = ((tx[1].n ^ tx[0].n) | (tx[2].n ^ tx[0].n) | (ty[1].n ^ ty[0].n) | (ty[2].n ^ ty[0].n) | (tz[1].n ^ tz[0].n) | (tz[2].n ^ tz[0].n)) & 1;
+    if (!__any_sync(0xffffffffu, mixed)) {
+      trig_poly3(tx, tx[0].n & 1, cx);
+      trig_poly3(ty, ty[0].n & 1, sy);
+      trig_poly3(tz, tz[0].n & 1, cz);
+    } else {
+#pragma unroll
+      for (int k = 0; k < 3; ++k) { cx[k] = trig_fast(ax[k], 1); sy[k] = trig_fast(ay[k], 0); cz[k] = trig_fast(az[k], 1); }
+    }
+  } else {
+#pragma unroll
+    for (int k = 0; k < 3; ++k) { cx[k] = cos(ax[k]); sy[k] = sin(ay[k]); cz[k] = cos(az[k]); }
+  }
+  const double cx0 = cx[0], cxm = cx[1], cxp = cx[2], sy0 = sy[0], sym = sy[1], syp = sy[2], cz0 = cz[0], czm = cz[1], czp = cz[2];
   auto u = [](double a, double b, double c) { return __dmul_rn(__dmul_rn(a, b), c); };
   auto dv = [eps](double a) {
     if (!FAST) return __ddiv_rn(a, eps);

@@ -685,7 +685,7 @@ int launch_poisson_affine(feasm_ctx* ctx, const feasm_params& p, const double* d
 // contraction over 81 rows — the isotropic structure cuts the tensor work ninefold (SURVEY a7 allows either count;
 // bench/DESIGN quote the flops of THIS algorithm).  One warp per element; each P goes through a shared-memory tile
 // (odd row stride: row and column reads are both conflict free) from which the nine variable blocks are combined
-// and stored.  Fe_(i,a) = f_i sum_q JxW phi_a(q) (body force; the traction term is omitted).
+// and stored.  Fe_(i,a) = f_i sum_q JxW phi_a(q) (body force; the traction term is added by k_side_loads, feasm_side.cu).
 template <int NPE, int NQ, int WARPS>
 __global__ void __launch_bounds__(WARPS * 32, 1)
 k_elem_elasticity(const double* __restrict__ xyz, const uint32_t* __restrict__ conn, const double* __restrict__ tab, double lam1,

@@ -1,5 +1,5 @@
 """GPU: the libMesh adaptor (libmesh_b200/shim: GpuSparseMatrix + the batched assemble hook) run end to end against the
-mock libMesh classes, compared with a direct drive of the C ABI (shim/shim_test.C, built by __graft_entry__.build())."""
+mock libMesh classes, compared with a direct drive of the C ABI (tests/shim/shim_test.C, built by __graft_entry__.build())."""
 import os
 import subprocess
 
