@@ -163,7 +163,11 @@ __device__ __forceinline__ double ex4_forcing_t(double x, double y, double z) {
 #pragma unroll
     for (int k = 0; k < 3; ++k) { tx[k] = trig_reduce(ax[k], 1); ty[k] = trig_reduce(ay[k], 0); tz[k] = trig_reduce(az[k], 1); }
     const int mixed = ((tx[1].n ^ tx[0].n) | (tx[2].n ^ tx[0].n) | (ty[1].n ^ ty[0].n) | (ty[2].n ^ ty[0].n) | (tz[1].n ^ tz[0].n) | (tz[2].n ^ tz[0].n)) & 1;
+#ifdef FEASM_DEV_NO_TRIG3  // development build: every evaluation selects its own coefficients
+    if (false) {
+#else
     if (!__any_sync(0xffffffffu, mixed)) {
+#endif
       trig_poly3(tx, tx[0].n & 1, cx);
       trig_poly3(ty, ty[0].n & 1, sy);
       trig_poly3(tz, tz[0].n & 1, cz);

@@ -237,7 +237,9 @@ __global__ void k_vec_set_one(double* __restrict__ y, int64_t i, double v, int a
 int spmv(feasm_ctx* ctx, const double* d_x, double* d_y) {
   static const bool pipe = !(getenv("FEASM_SPMV_PIPE") && atoi(getenv("FEASM_SPMV_PIPE")) == 0);  // A/B knob: 0 = one row at a time
   const int64_t want = (ctx->n_rows * 32 + 255) / 256;
-  if (pipe) {
+  // long rows (several variables per node: 375 entries at 3 x HEX27) already keep enough bytes in flight per warp and lose
+  // to the pipeline's extra registers (measured: 5.6 vs 4.6 TB/s at 3 x 48^3); short rows gain 3-8 %
+  if (pipe && ctx->nnz <= (uint64_t)ctx->n_rows * 160) {
     const int64_t cap = (int64_t)ctx->sm_count * 8;  // 8 CTAs of 8 warps per SM, each warp walks many rows
     const unsigned grid = (unsigned)(want < cap ? want : cap);
     if (grid) k_spmv_pipe<<<grid, 256, 0, ctx->stream>>>(ctx->d_row_ptr, ctx->d_col_idx, ctx->d_values, d_x, ctx->n_rows, d_y);

@@ -1,0 +1,51 @@
+"""Development aid: feasm_vector_mult time and bitwise comparison of the pipelined and the one-row-at-a-time kernel.
+    python scripts/gpu_spmv_ab.py [hex27|hex8|tet10] [n] [n_vars]      (runs itself twice, FEASM_SPMV_PIPE=1 and 0)"""
+import os
+import subprocess
+import sys
+import numpy as np
+
+if "FEASM_SPMV_PIPE" not in os.environ:
+    outs = []
+    for v in ("1", "0"):
+        r = subprocess.run([sys.executable] + sys.argv, env={**os.environ, "FEASM_SPMV_PIPE": v, "SPMV_OUT": f"/tmp/spmv_{v}.npy"}, capture_output=True, text=True)
+        print(r.stdout.strip(), r.stderr.strip()[-400:])
+    a, b = np.load("/tmp/spmv_1.npy"), np.load("/tmp/spmv_0.npy")
+    print("bitwise equal:", np.array_equal(a, b), "max |y|", np.abs(a).max())
+    sys.exit(0)
+sys.path.insert(0, '.')
+import torch
+from libmesh_b200 import capi as F
+
+et = {"hex27": 27, "hex8": 8, "tet10": 10}[sys.argv[1] if len(sys.argv) > 1 else "hex27"]
+n = int(sys.argv[2]) if len(sys.argv) > 2 else 96
+nv = int(sys.argv[3]) if len(sys.argv) > 3 else 1
+ctx = F.Context(0)
+ctx.generate_cube(et, n, n, n, (-1, 1, -1, 1, -1, 1))
+ctx.distribute_dofs(nv)
+ctx.generate_dirichlet(0x3f, F.DIRICHLET_ZERO)
+ctx.build_pattern()
+ctx.prepare()
+p = F.make_params(F.ELASTICITY, 0, F.FORCING_NONE, F.CONSTRAIN_HOMOGENEOUS) if nv == 3 else F.make_params(F.POISSON, 3 if et == 8 else 0, F.FORCING_NONE)
+ctx.assemble(p)
+nd, nnz = ctx.n_rows, ctx.nnz
+g = torch.Generator(device="cuda").manual_seed(1)
+x = torch.rand(nd, dtype=torch.float64, device="cuda", generator=g)
+y = torch.zeros(nd, dtype=torch.float64, device="cuda")
+flush = torch.empty(256 << 20, dtype=torch.uint8, device="cuda")
+lib = torch.cuda.ExternalStream(ctx.stream())
+best = []
+for it in range(8):
+    flush.zero_()
+    torch.cuda.synchronize()
+    with torch.cuda.stream(lib):
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record()
+        ctx.vector_mult(x.data_ptr(), y.data_ptr())
+        e1.record()
+    ctx.synchronize(); torch.cuda.synchronize()
+    best.append(e0.elapsed_time(e1))
+ms = min(best[2:])
+by = nnz * 12 + nd * 32
+print(f"pipe={os.environ['FEASM_SPMV_PIPE']} {sys.argv[1:]} rows {nd} nnz {nnz}: {ms:.4f} ms, {by / ms / 1e6:.0f} GB/s")
+np.save(os.environ["SPMV_OUT"], y.cpu().numpy())
