@@ -273,6 +273,43 @@ int feasm_exchange_end(feasm_ctx* ctx);
 int feasm_exchange_ghost_rows(feasm_ctx* ctx);
 int feasm_comm_allgather_u64(feasm_ctx* ctx, const uint64_t* send, int n, uint64_t* recv);
 
+/* The SETUP of a multi-rank assembly (SparsityPattern::Build::parallel_sync, src/base/sparsity_pattern.C:446-575, plus the
+ * fixed routes DistributedVector::close, src/numerics/distributed_vector.C:399-470, walks every assembly).  Local numbering
+ * is the host's job (feasm_set_dofs: owned rows first = global id - first_dof[rank], then the ghost rows in ascending
+ * global id; the pattern's column ids are GLOBAL dof ids).
+ *   feasm_build_exchange : collective over the context's communicator, after feasm_build_pattern.  first_dof[n_ranks + 1] =
+ *                          the dof ranges of the ranks (DofMap::first_dof(p), end_dof(last)).  Ships the column lists of the
+ *                          ghost rows to their owners, unites them with the owned rows (feasm_set_pattern), fixes the slot
+ *                          plan (feasm_set_exchange_plan), builds the scatter maps (feasm_prepare) and picks the interface
+ *                          prefix (feasm_set_interface_prefix; environment FEASM_IFACE=0 keeps it off).
+ *   feasm_planner_*      : the same logic for hosts that carry the messages themselves (libMesh: TIMPI push_parallel_vector_data
+ *                          over MPI; no device and no communicator needed):
+ *                            create(rank, n_ranks, first_dof, n_owned, n_rows, global_ids, row_ptr, col_idx) -> NULL on bad input
+ *                            message(peer, &words) -> number of uint32 words to send to `peer` (0: none)
+ *                            receive(peer, words, n)   the message a peer made for this rank
+ *                            finish()                  merged pattern + slot plan
+ *                            sizes(out[5])             nnz, peers, send slots, receive slots, pattern grew (0 / 1)
+ *                            get(...)                  copies out whatever pointer is non-NULL
+ *                          and feasm_apply_plan(ctx, planner) = feasm_set_pattern (if it grew) + feasm_set_exchange_plan +
+ *                          feasm_prepare. */
+typedef struct feasm_planner feasm_planner;
+int feasm_build_exchange(feasm_ctx* ctx, const uint64_t* first_dof);
+feasm_planner* feasm_planner_create(int rank, int n_ranks, const uint64_t* first_dof, uint64_t n_owned, uint64_t n_rows,
+                                    const uint32_t* global_ids, const uint64_t* row_ptr, const uint32_t* col_idx);
+void feasm_planner_destroy(feasm_planner* p);
+const char* feasm_planner_error(const feasm_planner* p);
+uint64_t feasm_planner_message(feasm_planner* p, int peer, const uint32_t** words);
+int feasm_planner_receive(feasm_planner* p, int peer, const uint32_t* words, uint64_t n);
+int feasm_planner_finish(feasm_planner* p);
+int feasm_planner_sizes(const feasm_planner* p, uint64_t sizes[5]);
+int feasm_planner_get(const feasm_planner* p, uint64_t* row_ptr, uint32_t* col_idx, int32_t* peers, uint64_t* send_ptr,
+                      uint64_t* send_slots, uint64_t* recv_ptr, uint64_t* recv_slots);
+int feasm_apply_plan(feasm_ctx* ctx, const feasm_planner* p);
+/* number of peers of the plan the context holds (>= 0); peers[n], send_ptr[n + 1], send_slots, recv_ptr[n + 1], recv_slots
+ * are copied out when non-NULL */
+int feasm_get_exchange_plan(feasm_ctx* ctx, int32_t* peers, uint64_t* send_ptr, uint64_t* send_slots, uint64_t* recv_ptr,
+                            uint64_t* recv_slots);
+
 /* ---- host-side generators for stand-alone runs (no libMesh present) ---------------------------- */
 /* MeshTools::Generation::build_cube (src/mesh/mesh_generation.C:317-1937) for HEX8/HEX27/TET10: fills caller arrays.
  * Sizes: feasm_cube_sizes. */

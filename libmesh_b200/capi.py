@@ -36,6 +36,8 @@ SYMBOLS = [
     "feasm_get_constraints", "feasm_set_side_penalty", "feasm_residual", "feasm_add_matrix_noalloc",
     "feasm_set_communicator", "feasm_comm_unique_id", "feasm_comm_init", "feasm_exchange_begin", "feasm_exchange_end",
     "feasm_exchange_ghost_rows", "feasm_comm_allgather_u64", "feasm_set_matrix", "feasm_init_matrix", "feasm_set_values", "feasm_set_interface_prefix",
+    "feasm_build_exchange", "feasm_planner_create", "feasm_planner_destroy", "feasm_planner_error", "feasm_planner_message",
+    "feasm_planner_receive", "feasm_planner_finish", "feasm_planner_sizes", "feasm_planner_get", "feasm_apply_plan", "feasm_get_exchange_plan",
 ]
 
 
@@ -97,6 +99,17 @@ def lib():
         "feasm_exchange_end": (i32, [vp]),
         "feasm_exchange_ghost_rows": (i32, [vp]),
         "feasm_comm_allgather_u64": (i32, [vp, vp, i32, vp]),
+        "feasm_build_exchange": (i32, [vp, vp]),
+        "feasm_planner_create": (vp, [i32, i32, vp, C.c_uint64, C.c_uint64, vp, vp, vp]),
+        "feasm_planner_destroy": (None, [vp]),
+        "feasm_planner_error": (C.c_char_p, [vp]),
+        "feasm_planner_message": (C.c_uint64, [vp, i32, C.POINTER(vp)]),
+        "feasm_planner_receive": (i32, [vp, i32, vp, C.c_uint64]),
+        "feasm_planner_finish": (i32, [vp]),
+        "feasm_planner_sizes": (i32, [vp, vp]),
+        "feasm_planner_get": (i32, [vp, vp, vp, vp, vp, vp, vp, vp]),
+        "feasm_apply_plan": (i32, [vp, vp]),
+        "feasm_get_exchange_plan": (i32, [vp, vp, vp, vp, vp, vp]),
         "feasm_get_values": (i32, [vp, vp, vp]),
         "feasm_device_values": (vp, [vp]),
         "feasm_device_rhs": (vp, [vp]),
@@ -489,6 +502,29 @@ class Context:
         self._ck(self.L.feasm_comm_allgather_u64(self.h, _p(v), len(v), _p(out)))
         return out
 
+    def build_exchange(self, first_dof):
+        """Collective setup over the context's communicator (feasm_build_exchange): merged pattern, slot plan, scatter maps."""
+        fd = _c(first_dof, np.uint64)
+        if len(fd) != self.comm_size + 1:
+            raise FeasmError(-1, "first_dof must have n_ranks + 1 entries")
+        self._ck(self.L.feasm_build_exchange(self.h, _p(fd)))
+
+    def apply_plan(self, planner):
+        self._ck(self.L.feasm_apply_plan(self.h, planner.h))
+
+    def exchange_plan(self):
+        """(peers, send_ptr, send_slots, recv_ptr, recv_slots) of the plan the context holds."""
+        n = int(self.L.feasm_get_exchange_plan(self.h, None, None, None, None, None))
+        if n < 0:
+            self._ck(n)
+        peers, sp, rp = np.zeros(n, dtype=np.int32), np.zeros(n + 1, dtype=np.uint64), np.zeros(n + 1, dtype=np.uint64)
+        if n:
+            self.L.feasm_get_exchange_plan(self.h, _p(peers), _p(sp), None, _p(rp), None)
+        ss, rs = np.zeros(int(sp[-1]), dtype=np.uint64), np.zeros(int(rp[-1]), dtype=np.uint64)
+        if n and int(self.L.feasm_get_exchange_plan(self.h, None, None, _p(ss), None, _p(rs))) < 0:
+            self._ck(-2)
+        return peers, sp, ss, rp, rs
+
     def pack_ghost(self):
         n = C.c_uint64()
         ptr = self.L.feasm_pack_ghost(self.h, C.byref(n))
@@ -501,3 +537,59 @@ class Context:
 
     def unpack_ghost(self):
         self._ck(self.L.feasm_unpack_ghost(self.h))
+
+
+class Planner:
+    """feasm_planner_*: the host-only half of the multi-rank setup (no device, no communicator).  Messages are uint32 arrays."""
+
+    def __init__(self, rank, n_ranks, first_dof, n_owned, n_rows, global_ids, row_ptr, col_idx):
+        self.L = lib()
+        fd, gid = _c(first_dof, np.uint64), _c(global_ids, np.uint32)
+        rp, ci = _c(row_ptr, np.uint64), _c(col_idx, np.uint32)
+        self.n_rows, self.n_ranks = int(n_rows), int(n_ranks)
+        self.h = self.L.feasm_planner_create(rank, n_ranks, _p(fd), int(n_owned), int(n_rows), _p(gid), _p(rp), _p(ci))
+        if not self.h:
+            raise FeasmError(-1, self.L.feasm_planner_error(None).decode())
+
+    def _ck(self, rc):
+        if rc:
+            raise FeasmError(rc, self.L.feasm_planner_error(self.h).decode())
+
+    def messages(self):
+        """{peer: uint32 words} for every peer this rank has ghost rows of."""
+        out = {}
+        for q in range(self.n_ranks):
+            w = C.c_void_p()
+            n = int(self.L.feasm_planner_message(self.h, q, C.byref(w)))
+            if n:
+                out[q] = np.ctypeslib.as_array(C.cast(w, C.POINTER(C.c_uint32)), shape=(n,)).copy()
+        return out
+
+    def receive(self, peer, words):
+        w = _c(words, np.uint32)
+        self._ck(self.L.feasm_planner_receive(self.h, int(peer), _p(w), len(w)))
+
+    def finish(self):
+        """-> dict(row_ptr, col_idx, peers, send_ptr, send_slots, recv_ptr, recv_slots, merged)"""
+        self._ck(self.L.feasm_planner_finish(self.h))
+        sz = np.zeros(5, dtype=np.uint64)
+        self._ck(self.L.feasm_planner_sizes(self.h, _p(sz)))
+        nnz, npeer, ns, nr, merged = (int(x) for x in sz)
+        o = dict(row_ptr=np.zeros(self.n_rows + 1, dtype=np.uint64), col_idx=np.zeros(nnz, dtype=np.uint32), peers=np.zeros(npeer, dtype=np.int32),
+                 send_ptr=np.zeros(npeer + 1, dtype=np.uint64), send_slots=np.zeros(ns, dtype=np.uint64),
+                 recv_ptr=np.zeros(npeer + 1, dtype=np.uint64), recv_slots=np.zeros(nr, dtype=np.uint64))
+        self._ck(self.L.feasm_planner_get(self.h, _p(o["row_ptr"]), _p(o["col_idx"]), _p(o["peers"]), _p(o["send_ptr"]), _p(o["send_slots"]),
+                                          _p(o["recv_ptr"]), _p(o["recv_slots"])))
+        o["merged"] = bool(merged)
+        return o
+
+    def close(self):
+        if self.h:
+            self.L.feasm_planner_destroy(self.h)
+            self.h = None
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass

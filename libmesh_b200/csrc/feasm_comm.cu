@@ -11,7 +11,9 @@
 #include <dlfcn.h>
 #include <nccl.h>
 
+#include <cstdlib>
 #include <mutex>
+#include <vector>
 
 #include "feasm_internal.h"
 
@@ -198,6 +200,90 @@ int feasm_comm_allgather_u64(feasm_ctx* ctx, const uint64_t* send, int n, uint64
   rc = body();
   cudaFree(d);
   return rc;
+}
+
+// The setup of a multi-rank assembly over the context's own communicator: pattern of this rank (device) -> ghost-row
+// messages -> owners (sizes by ncclAllGather, the lists by one grouped ncclSend / ncclRecv of uint32 words) -> merged
+// pattern, slot plan, scatter maps (feasm_plan.cpp).  Collective: every rank of the communicator calls it.
+int feasm_build_exchange(feasm_ctx* ctx, const uint64_t* first_dof) {
+  if (!ctx || !first_dof) return feasm_fail(ctx, FEASM_ERR_ARG, "first_dof is NULL");
+  if (!ctx->comm) return feasm_fail(ctx, FEASM_ERR_STATE, "no communicator: feasm_comm_init / feasm_set_communicator first");
+  if (!ctx->d_row_ptr) return feasm_fail(ctx, FEASM_ERR_STATE, "pattern not set: call feasm_build_pattern first");
+  if (ctx->n_owned < ctx->n_rows && !ctx->d_gid) return feasm_fail(ctx, FEASM_ERR_STATE, "ghost rows need global ids (feasm_set_dofs)");
+  NcclApi* a = nccl_api();
+  FEASM_CUDA(ctx, cudaSetDevice(ctx->device));
+  const int world = ctx->comm_size, rank = ctx->comm_rank;
+  std::vector<uint64_t> rp((size_t)ctx->n_rows + 1);
+  std::vector<uint32_t> ci((size_t)ctx->nnz), gid((size_t)ctx->n_rows);
+  FEASM_CUDA(ctx, cudaMemcpyAsync(rp.data(), ctx->d_row_ptr, sizeof(uint64_t) * rp.size(), cudaMemcpyDeviceToHost, ctx->stream));
+  FEASM_CUDA(ctx, cudaMemcpyAsync(ci.data(), ctx->d_col_idx, sizeof(uint32_t) * ci.size(), cudaMemcpyDeviceToHost, ctx->stream));
+  if (ctx->d_gid) FEASM_CUDA(ctx, cudaMemcpyAsync(gid.data(), ctx->d_gid, sizeof(uint32_t) * gid.size(), cudaMemcpyDeviceToHost, ctx->stream));
+  FEASM_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
+  feasm_planner* pl = feasm_planner_create(rank, world, first_dof, (uint64_t)ctx->n_owned, (uint64_t)ctx->n_rows, gid.data(), rp.data(), ci.data());
+  if (!pl) return feasm_fail(ctx, FEASM_ERR_ARG, "dof ranges / global ids do not describe owned rows first, then ghost rows in ascending global id");
+  std::vector<uint32_t>().swap(ci);  // the planner holds its own copy
+  uint32_t* d_out = nullptr;
+  uint32_t* d_in = nullptr;
+  auto body = [&]() -> int {
+    // message sizes: row q of the gathered matrix = what rank q sends to every rank
+    std::vector<uint64_t> mine(world, 0), all((size_t)world * world, 0);
+    uint64_t n_out = 0, n_in = 0;
+    for (int q = 0; q < world; ++q) { mine[q] = feasm_planner_message(pl, q, nullptr); n_out += mine[q]; }
+    int rc = feasm_comm_allgather_u64(ctx, mine.data(), world, all.data());
+    if (rc) return rc;
+    for (int q = 0; q < world; ++q) n_in += all[(size_t)q * world + rank];
+    FEASM_CUDA(ctx, cudaMalloc(&d_out, sizeof(uint32_t) * (n_out + 1)));
+    FEASM_CUDA(ctx, cudaMalloc(&d_in, sizeof(uint32_t) * (n_in + 1)));
+    uint64_t o = 0;
+    for (int q = 0; q < world; ++q) {
+      const uint32_t* w = nullptr;
+      const uint64_t n = feasm_planner_message(pl, q, &w);
+      if (n) FEASM_CUDA(ctx, cudaMemcpyAsync(d_out + o, w, sizeof(uint32_t) * n, cudaMemcpyHostToDevice, ctx->stream));
+      o += n;
+    }
+    ncclComm_t comm = static_cast<ncclComm_t>(ctx->comm);
+    FEASM_NCCL(ctx, a, a->GroupStart());
+    uint64_t i = 0;
+    for (int q = 0; q < world; ++q) {
+      const uint64_t n = all[(size_t)q * world + rank];
+      if (n) FEASM_NCCL(ctx, a, a->Recv(d_in + i, n, ncclUint32, q, comm, ctx->stream));
+      i += n;
+    }
+    o = 0;
+    for (int q = 0; q < world; ++q) {
+      if (mine[q]) FEASM_NCCL(ctx, a, a->Send(d_out + o, mine[q], ncclUint32, q, comm, ctx->stream));
+      o += mine[q];
+    }
+    FEASM_NCCL(ctx, a, a->GroupEnd());
+    std::vector<uint32_t> in(n_in + 1);
+    FEASM_CUDA(ctx, cudaMemcpyAsync(in.data(), d_in, sizeof(uint32_t) * n_in, cudaMemcpyDeviceToHost, ctx->stream));
+    FEASM_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
+    i = 0;
+    for (int q = 0; q < world; ++q) {
+      const uint64_t n = all[(size_t)q * world + rank];
+      if (n && (rc = feasm_planner_receive(pl, q, in.data() + i, n)) != FEASM_OK) return feasm_fail(ctx, rc, feasm_planner_error(pl));
+      i += n;
+    }
+    if ((rc = feasm_planner_finish(pl)) != FEASM_OK) return feasm_fail(ctx, rc, feasm_planner_error(pl));
+    return feasm_apply_plan(ctx, pl);
+  };
+  int rc = body();
+  cudaFree(d_out);
+  cudaFree(d_in);
+  feasm_planner_destroy(pl);
+  if (rc) return rc;
+  // interface elements first (feasm_set_interface_prefix): the leading elements that cover every element touching a ghost
+  // row — with LinearPartitioner slabs the first element layer.  Used when that prefix is at most a third of the elements.
+  int64_t prefix = 0;
+  if (ctx->n_owned < ctx->n_rows && ctx->d_elem_dofs && !(getenv("FEASM_IFACE") && atoi(getenv("FEASM_IFACE")) == 0)) {
+    std::vector<uint32_t> ed((size_t)ctx->n_elem * ctx->nd);
+    FEASM_CUDA(ctx, cudaMemcpy(ed.data(), ctx->d_elem_dofs, sizeof(uint32_t) * ed.size(), cudaMemcpyDeviceToHost));
+    for (int64_t e = ctx->n_elem - 1; e >= 0 && !prefix; --e)
+      for (int k = 0; k < ctx->nd; ++k)
+        if (ed[(size_t)e * ctx->nd + k] >= (uint64_t)ctx->n_owned) { prefix = e + 1; break; }
+    if (prefix > ctx->n_elem / 3) prefix = 0;
+  }
+  return feasm_set_interface_prefix(ctx, prefix);
 }
 
 }  // extern "C"

@@ -13,7 +13,9 @@ owner at ``close()`` (src/numerics/distributed_vector.C:399-470, PETSc's MatAsse
             torch.distributed.batch_isend_irecv on the library's stream) -> feasm_unpack_ghost, peers added in fixed
             order, so the result is bitwise reproducible.
 
-The host logic is plain numpy + torch.distributed and is exercised on CPU with the gloo backend in tests/.
+Localisation (RankProblem) is numpy; the ghost-row messages, the pattern merge and the slot plan are libfeasm's
+(feasm_planner_* / feasm_build_exchange, csrc/feasm_plan.cpp) — this module only carries the planner's messages over
+torch.distributed when the context has no communicator of its own (the CPU tests, gloo).
 """
 from __future__ import annotations
 
@@ -83,59 +85,6 @@ class RankProblem:
         return np.unique(self.ghost_owner)
 
 
-def csr_rows(rp, ci, rows):
-    """Concatenated column lists of `rows`: (lens, cols, slots)."""
-    rows = np.asarray(rows, dtype=np.int64)
-    lo = rp[rows].astype(np.int64)
-    lens = (rp[rows + 1].astype(np.int64) - lo)
-    tot = int(lens.sum())
-    off = np.zeros(len(rows) + 1, dtype=np.int64)
-    np.cumsum(lens, out=off[1:])
-    slots = np.repeat(lo - off[:-1], lens) + np.arange(tot, dtype=np.int64)
-    return lens, ci[slots], slots
-
-
-def merge_rows(rp, ci, add_rows, add_lens, add_cols):
-    """Union the column lists (add_rows[k] gets add_cols segment k) into the CSR pattern; returns (rp, ci)."""
-    n = len(rp) - 1
-    if len(add_rows) == 0:
-        return rp, ci
-    rp = rp.astype(np.int64)
-    old_len = np.diff(rp)
-    aff = np.unique(add_rows)
-    # new column lists of the affected rows
-    seg = np.zeros(len(add_rows) + 1, dtype=np.int64)
-    np.cumsum(add_lens, out=seg[1:])
-    order = np.argsort(add_rows, kind="stable")
-    new_cols = {}
-    i = 0
-    sr = np.asarray(add_rows)[order]
-    while i < len(order):
-        j = i
-        parts = [ci[rp[sr[i]]:rp[sr[i] + 1]]]
-        while j < len(order) and sr[j] == sr[i]:
-            k = order[j]
-            parts.append(add_cols[seg[k]:seg[k + 1]])
-            j += 1
-        new_cols[int(sr[i])] = np.unique(np.concatenate(parts))
-        i = j
-    new_len = old_len.copy()
-    for r, c in new_cols.items():
-        new_len[r] = len(c)
-    nrp = np.zeros(n + 1, dtype=np.int64)
-    np.cumsum(new_len, out=nrp[1:])
-    nci = np.empty(int(nrp[-1]), dtype=ci.dtype)
-    is_aff = np.zeros(n, dtype=bool)
-    is_aff[aff] = True
-    row_of = np.repeat(np.arange(n, dtype=np.int64), old_len)
-    keep = ~is_aff[row_of]
-    within = np.arange(len(ci), dtype=np.int64) - rp[row_of]
-    nci[nrp[row_of[keep]] + within[keep]] = ci[keep]
-    for r, c in new_cols.items():
-        nci[nrp[r]:nrp[r] + len(c)] = c
-    return nrp.astype(np.uint64), nci
-
-
 # ---- setup exchange and per-step exchange (torch.distributed) -------------------------------------------------
 class DevArray:
     """A raw device pointer exposed through __cuda_array_interface__ so torch can wrap it without a copy."""
@@ -181,6 +130,7 @@ class DistributedAssembly:
         self.ctx, self.p, self.dist = ctx, prob, dist
         self.host_group, self.dev_group = host_group, dev_group
         self.rank = prob.rank
+        self._pattern = None
 
     # -- setup ---------------------------------------------------------------------------------------------
     def setup(self, constrain=True):
@@ -190,6 +140,14 @@ class DistributedAssembly:
         if constrain:
             ctx.set_constraints(p.con_rows, p.con_vals)
         ctx.build_pattern()
+        if getattr(ctx, "has_comm", False):
+            # everything below the C ABI: messages over the context's NCCL communicator, merge, plan, scatter maps and the
+            # interface prefix (feasm_build_exchange)
+            ctx.build_exchange(p.first_dof)
+            self.peers, self.send_ptr, self.send_slots, self.recv_ptr, self.recv_slots = ctx.exchange_plan()
+            self.peers = [int(q) for q in self.peers]
+            self._pattern = None
+            return
         rp, ci = ctx.get_pattern()
         self.merge_and_plan(rp, ci)
         # interface elements first: the leading local elements that cover every element touching a ghost row (with
@@ -200,73 +158,52 @@ class DistributedAssembly:
         if hasattr(ctx, "set_interface_prefix"):
             ctx.set_interface_prefix(self.iface_prefix)
 
+    @property
+    def row_ptr(self):
+        if self._pattern is None:
+            self._pattern = self.ctx.get_pattern()
+        return self._pattern[0]
+
+    @property
+    def col_idx(self):
+        if self._pattern is None:
+            self._pattern = self.ctx.get_pattern()
+        return self._pattern[1]
+
     def merge_and_plan(self, rp, ci):
-        """Ship ghost-row column lists to their owners, merge, and derive the slot plan.  Also usable stand-alone with a
-        host-built local pattern (CPU tests)."""
+        """Ship ghost-row column lists to their owners, merge, and derive the slot plan, with the messages carried by
+        torch.distributed.  Also usable stand-alone with a host-built local pattern (CPU tests)."""
         send = self.ghost_messages(rp, ci)
         got = _exchange_arrays(self.dist, self.host_group, self.rank, send)
         self.finish_plan(rp, ci, got)
 
     def ghost_messages(self, rp, ci):
-        """{owner rank: [n_rows, global row ids, row lengths, columns]} for the ghost rows of this rank."""
+        """{owner rank: uint32 words [n_rows, global row ids, row lengths, columns]} for the ghost rows of this rank
+        (feasm_planner_create / feasm_planner_message)."""
+        from . import capi as F
+
         p = self.p
-        send = {}
-        self._ghost_rows = {}
-        for q in p.peers:
-            rows = p.n_owned + np.nonzero(p.ghost_owner == q)[0]  # local ghost rows owned by q, ascending global id
-            lens, cols, _ = csr_rows(rp, ci, rows)
-            self._ghost_rows[int(q)] = rows
-            send[int(q)] = np.concatenate([[len(rows)], p.global_ids[rows].astype(np.int64), lens, cols.astype(np.int64)])
-        return send
+        self._planner = F.Planner(p.rank, p.n_parts, p.first_dof, p.n_owned, p.n_rows, p.global_ids, rp, ci)
+        return self._planner.messages()
 
     def finish_plan(self, rp, ci, got):
-        """Merge the received ghost-row patterns into the owned rows and fix the send/receive slot plan."""
-        p, ctx = self.p, self.ctx
-        add_rows, add_lens, add_cols, self._recv_desc = [], [], [], {}
+        """Hand the received messages to the planner, then the merged pattern and the slot plan to the context."""
+        ctx, pl = self.ctx, self._planner
         for q in sorted(got):
-            a = got[q]
-            n = int(a[0])
-            grow, lens, cols = a[1:1 + n], a[1 + n:1 + 2 * n], a[1 + 2 * n:]
-            lrow = grow - p.f0
-            if (lrow < 0).any() or (lrow >= p.n_owned).any():
-                raise ValueError("peer sent a row this rank does not own")
-            add_rows.append(lrow); add_lens.append(lens); add_cols.append(cols.astype(ci.dtype))
-            self._recv_desc[q] = (lrow, lens, cols)
-        if add_rows:
-            rp, ci = merge_rows(rp, ci, np.concatenate(add_rows), np.concatenate(add_lens), np.concatenate(add_cols))
-            ctx.set_pattern(rp, ci)  # SparseMatrix::update_sparsity_pattern route: the merged graph
-        self.row_ptr, self.col_idx = np.asarray(rp, dtype=np.uint64), ci
-        nnz = int(self.row_ptr[-1])
-        # slot plan: per peer, all value slots of its rows (row-major) followed by the rows' RHS slots
-        peers = sorted(set(self._ghost_rows) | set(self._recv_desc))
-        send_ptr, recv_ptr, send_slots, recv_slots = [0], [0], [], []
-        rp64 = self.row_ptr.astype(np.int64)
-        for q in peers:
-            if q in self._ghost_rows:
-                rows = self._ghost_rows[q]
-                _, _, slots = csr_rows(rp64, self.col_idx, rows)
-                send_slots += [slots, nnz + rows.astype(np.int64)]
-            send_ptr.append(send_ptr[-1] + (sum(len(x) for x in send_slots[-2:]) if q in self._ghost_rows else 0))
-            if q in self._recv_desc:
-                lrow, lens, cols = self._recv_desc[q]
-                rows_rep = np.repeat(lrow, lens)
-                # position of each received column inside its (merged, sorted) owned row: search on row*2^32 + col keys
-                _, mycols, myslots = csr_rows(rp64, self.col_idx, lrow)
-                mylens = rp64[lrow + 1] - rp64[lrow]
-                mykeys = (np.repeat(lrow, mylens).astype(np.int64) << 32) | mycols.astype(np.int64)
-                keys = (rows_rep.astype(np.int64) << 32) | cols.astype(np.int64)
-                order = np.argsort(mykeys, kind="stable")
-                k = np.searchsorted(mykeys[order], keys)
-                if (mykeys[order][k] != keys).any():
-                    raise ValueError("received column missing from the merged pattern")
-                recv_slots += [myslots[order][k], nnz + lrow.astype(np.int64)]
-            recv_ptr.append(recv_ptr[-1] + (sum(len(x) for x in recv_slots[-2:]) if q in self._recv_desc else 0))
-        self.peers = peers
-        self.send_ptr, self.recv_ptr = np.asarray(send_ptr, dtype=np.uint64), np.asarray(recv_ptr, dtype=np.uint64)
-        self.send_slots = np.concatenate(send_slots).astype(np.uint64) if send_slots else np.zeros(0, dtype=np.uint64)
-        self.recv_slots = np.concatenate(recv_slots).astype(np.uint64) if recv_slots else np.zeros(0, dtype=np.uint64)
-        ctx.set_exchange_plan(np.asarray(peers, dtype=np.int32), self.send_ptr, self.send_slots, self.recv_ptr, self.recv_slots)
-        ctx.prepare()
+            pl.receive(q, np.asarray(got[q], dtype=np.uint32))
+        o = pl.finish()
+        if hasattr(ctx, "apply_plan"):
+            ctx.apply_plan(pl)  # feasm_set_pattern (if the pattern grew) + feasm_set_exchange_plan + feasm_prepare
+        else:  # host stand-in of the CPU tests
+            if o["merged"]:
+                ctx.set_pattern(o["row_ptr"], o["col_idx"])
+            ctx.set_exchange_plan(o["peers"], o["send_ptr"], o["send_slots"], o["recv_ptr"], o["recv_slots"])
+            ctx.prepare()
+        self._pattern = (o["row_ptr"], o["col_idx"])
+        self.peers = [int(q) for q in o["peers"]]
+        self.send_ptr, self.recv_ptr = o["send_ptr"], o["recv_ptr"]
+        self.send_slots, self.recv_slots = o["send_slots"], o["recv_slots"]
+        pl.close()
 
     # -- per step --------------------------------------------------------------------------------------------
     def _exchange_ops(self):

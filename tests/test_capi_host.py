@@ -75,3 +75,39 @@ def test_no_cpu_fallback():
     with pytest.raises(F.FeasmError) as e:
         F.Context(0)
     assert e.value.code == -2 and "no CPU fallback" in str(e.value)
+
+
+def test_planner_two_ranks_by_hand():
+    """feasm_planner_* on a hand-made 1-D chain of 2-dof elements split between two ranks: 5 dofs, rank 0 owns 0-2, rank 1 owns
+    3-4; element (2,3) belongs to rank 1, so rank 1 has ghost row 2.  Columns are global ids."""
+    fd = [0, 3, 5]
+    # rank 0: elements (0,1), (1,2): rows 0..2, no ghosts
+    p0 = F.Planner(0, 2, fd, 3, 3, [0, 1, 2], [0, 2, 5, 7], [0, 1, 0, 1, 2, 1, 2])
+    # rank 1: elements (2,3), (3,4): owned rows 3, 4 (local 0, 1), ghost row 2 (local 2)
+    p1 = F.Planner(1, 2, fd, 2, 3, [3, 4, 2], [0, 3, 5, 7], [2, 3, 4, 3, 4, 2, 3])
+    assert p0.messages() == {}
+    m = p1.messages()
+    assert list(m) == [0] and m[0].tolist() == [1, 2, 2, 2, 3]  # one row, global id 2, two columns: 2 3
+    p0.receive(1, m[0])
+    o0, o1 = p0.finish(), p1.finish()
+    assert o0["merged"] and o0["row_ptr"].tolist() == [0, 2, 5, 8] and o0["col_idx"].tolist() == [0, 1, 0, 1, 2, 1, 2, 3]
+    assert not o1["merged"]
+    assert o0["peers"].tolist() == [1] and o1["peers"].tolist() == [0]
+    assert o1["send_ptr"].tolist() == [0, 3] and o1["send_slots"].tolist() == [5, 6, 7 + 2]  # two values of local row 2, then its rhs
+    assert o0["recv_ptr"].tolist() == [0, 3] and o0["recv_slots"].tolist() == [6, 7, 8 + 2]  # columns 2, 3 of merged row 2, rhs of row 2
+    assert o0["send_slots"].size == 0 and o1["recv_slots"].size == 0
+
+
+def test_planner_rejects_bad_input():
+    fd = [0, 3, 5]
+    with pytest.raises(F.FeasmError):  # ghost ids must ascend and must not be owned
+        F.Planner(1, 2, fd, 2, 3, [3, 4, 3], [0, 1, 2, 3], [3, 4, 3])
+    with pytest.raises(F.FeasmError):  # n_owned does not match the dof range
+        F.Planner(0, 2, fd, 2, 2, [0, 1], [0, 1, 2], [0, 1])
+    p0 = F.Planner(0, 2, fd, 3, 3, [0, 1, 2], [0, 1, 2, 3], [0, 1, 2])
+    with pytest.raises(F.FeasmError, match="does not own"):
+        p0.receive(1, [1, 4, 1, 4])
+    with pytest.raises(F.FeasmError, match="length"):
+        p0.receive(1, [1, 2, 2, 3])
+    with pytest.raises(F.FeasmError, match="bad peer"):
+        p0.receive(0, [1, 2, 1, 3])
