@@ -1,8 +1,19 @@
 // gpu_assemble.C — see gpu_assemble.h.  Flattens what the reference reaches through pointers (Elem -> Node ->
 // DofObject, src/fe/fe_map.C:1361-1366, src/base/dof_map.C:2201-2314) into the arrays libfeasm takes, once per mesh,
 // then runs the assembly on the GPU and hands the RHS back to the system's NumericVector.
+//
+// Several ranks (one process per GPU, mesh.comm().size() > 1): every rank flattens its active_local elements; rows are
+// numbered owned first (dof - first_dof()), then the ghost rows — dofs of local elements that another rank owns — in
+// ascending global id.  The context joins an NCCL communicator bootstrapped over the libMesh communicator
+// (GpuSparseMatrix::ensure_communicator), builds its local pattern on the device and synchronises it with the peers
+// (feasm_build_exchange: what SparsityPattern::Build::parallel_sync does, sparsity_pattern.C:446-575); the owned rows of
+// the result are checked against the Graph libMesh handed to update_sparsity_pattern.  An assembly is then
+// feasm_assemble_begin -> feasm_exchange_begin -> feasm_assemble_end -> feasm_exchange_end: the contributions to rows of
+// other ranks travel while the owned rows are reduced, the role of the stash in MatAssemblyBegin/End and of
+// DistributedVector::close (distributed_vector.C:399-470).
 #include "gpu_assemble.h"
 
+#include <algorithm>
 #include <cstring>
 #include <unordered_map>
 
@@ -33,8 +44,7 @@ void assemble(EquationSystems& es, const std::string& system_name, const feasm_p
   auto* A = dynamic_cast<GpuSparseMatrix<Number>*>(system.matrix);
   if (!A) libmesh_error_msg("feasm_libmesh::assemble: system.matrix is not a GpuSparseMatrix; add it with "
                             "system.add_matrix<GpuSparseMatrix>(\"System Matrix\") before EquationSystems::init()");
-  if (A->n_processors() > 1)
-    libmesh_not_implemented();  // the multi-rank protocol is implemented in libmesh_b200/multi.py; see INTEGRATION.md
+  const unsigned n_ranks = A->n_processors();
   std::lock_guard<std::mutex> lock(A->mutex());
   const MeshBase& mesh = system.get_mesh();
   DofMap& dof_map = system.get_dof_map();
@@ -56,6 +66,21 @@ void assemble(EquationSystems& es, const std::string& system_name, const feasm_p
     std::vector<uint32_t> conn, elem_dofs;
     std::vector<dof_id_type> di;
     int type = 0, nd = 0;
+    // ghost rows: the dofs of local elements outside [first_dof, end_dof), ascending (empty on one rank)
+    std::vector<dof_id_type> ghosts;
+    if (n_ranks > 1) {
+      if (reflatten) {
+        for (const Elem* elem : mesh.active_local_element_ptr_range()) {
+          dof_map.dof_indices(elem, di);
+          for (dof_id_type d : di) if (d < first || d >= first + n_local) ghosts.push_back(d);
+        }
+        std::sort(ghosts.begin(), ghosts.end());
+        ghosts.erase(std::unique(ghosts.begin(), ghosts.end()), ghosts.end());
+        A->set_ghosts(ghosts);
+      } else {
+        ghosts = A->ghosts();
+      }
+    }
     for (const Elem* elem : mesh.active_local_element_ptr_range()) {
       const int t = feasm_type(elem->type());
       if (type && t != type) libmesh_error_msg("libfeasm assembles one element type per context");
@@ -74,16 +99,30 @@ void assemble(EquationSystems& es, const std::string& system_name, const feasm_p
       if (nd && (int)di.size() != nd) libmesh_error_msg("libfeasm needs the same number of dofs on every element");
       nd = (int)di.size();
       for (dof_id_type d : di) {
-        if (d < first || d >= first + n_local) libmesh_error_msg("dof outside the local range on a one-rank run");
-        elem_dofs.push_back(d - first);
+        if (n_ranks == 1 && (d < first || d >= first + n_local)) libmesh_error_msg("dof outside the local range on a one-rank run");
+        elem_dofs.push_back(A->local_row(d));
       }
     }
     const uint64_t sum = checksum(xyz);
     if (reflatten) {
       A->check(feasm_set_mesh(ctx, type, (int64_t)n_elem, (int64_t)local_node.size(), xyz.data(), conn.data()));
-      A->check(feasm_set_dofs(ctx, nd / type, n_local, n_local, elem_dofs.data(), nullptr));
       A->pattern_invalidated();
-      A->send_pattern();
+      if (n_ranks == 1) {
+        A->check(feasm_set_dofs(ctx, nd / type, n_local, n_local, elem_dofs.data(), nullptr));
+        A->send_pattern();
+      } else {
+        std::vector<uint32_t> gid(n_local + ghosts.size());
+        for (dof_id_type r = 0; r < n_local; ++r) gid[r] = first + r;
+        std::copy(ghosts.begin(), ghosts.end(), gid.begin() + n_local);
+        A->check(feasm_set_dofs(ctx, nd / type, (int64_t)gid.size(), n_local, elem_dofs.data(), gid.data()));
+        std::vector<uint64_t> first_dof(n_ranks + 1);
+        for (unsigned p = 0; p < n_ranks; ++p) first_dof[p] = dof_map.first_dof(p);
+        first_dof[n_ranks] = dof_map.end_dof(n_ranks - 1);
+        A->ensure_communicator();
+        A->check(feasm_build_pattern(ctx));
+        A->check(feasm_build_exchange(ctx, first_dof.data()));  // collective
+        A->adopt_device_pattern();
+      }
       up.mesh = &mesh; up.n_elem = n_elem; up.n_dofs = dof_map.n_dofs(); up.n_local = n_local; up.first = first;
     } else if (sum != up.xyz_sum) {
       A->check(feasm_update_coordinates(ctx, xyz.data()));
@@ -136,16 +175,27 @@ void assemble(EquationSystems& es, const std::string& system_name, const feasm_p
   std::vector<uint32_t> con_rows;
   std::vector<double> con_vals;
   const DofConstraintValueMap& vals = dof_map.get_primal_constraint_values();
-  for (dof_id_type d = first; d < first + n_local; ++d)
-    if (dof_map.is_constrained_dof(d)) {
-      const auto it = vals.find(d);
-      con_rows.push_back(d - first);
-      con_vals.push_back(it == vals.end() ? 0. : it->second);
-    }
+  auto constrained = [&](dof_id_type d, uint32_t row) {
+    if (!dof_map.is_constrained_dof(d)) return;
+    const auto it = vals.find(d);
+    con_rows.push_back(row);
+    con_vals.push_back(it == vals.end() ? 0. : it->second);
+  };
+  for (dof_id_type d = first; d < first + n_local; ++d) constrained(d, d - first);
+  // the element-level constraint needs the ghost dofs of the local elements too (libMesh keeps their constraint rows on
+  // this rank as well: DofMap::scatter_constraints, dof_map_constraints.C)
+  for (std::size_t g = 0; g < A->ghosts().size(); ++g) constrained(A->ghosts()[g], (uint32_t)(n_local + g));
   A->check(feasm_set_constraints(ctx, (int64_t)con_rows.size(), con_rows.data(), con_vals.data()));
 
   // ---- the hot path -----------------------------------------------------------------------------------------------
-  A->check(feasm_assemble(ctx, &params));
+  if (n_ranks == 1) {
+    A->check(feasm_assemble(ctx, &params));
+  } else {
+    A->check(feasm_assemble_begin(ctx, &params));  // element phase (interface elements first), ghost rows reduced and packed
+    A->check(feasm_exchange_begin(ctx));           // one grouped ncclSend / ncclRecv per neighbour, on the communication stream
+    A->check(feasm_assemble_end(ctx));             // the other elements and the owned rows, under the transfer
+    A->check(feasm_exchange_end(ctx));             // the peers' contributions added in rank order
+  }
   A->invalidate_host_copy();
   if (auto* grhs = dynamic_cast<GpuNumericVector<Number>*>(system.rhs)) {
     // route (2) of SURVEY 8b: the RHS never leaves the device
@@ -153,8 +203,9 @@ void assemble(EquationSystems& es, const std::string& system_name, const feasm_p
     grhs->assign_device(feasm_device_rhs(ctx), n_local);
   } else {
     // route (1): any NumericVector, through NumericVector::operator=(const std::vector<T>&), numeric_vector.h:295
-    std::vector<Number> rhs(n_local);
+    std::vector<Number> rhs(n_local + A->ghosts().size());
     A->check(feasm_get_values(ctx, nullptr, rhs.data()));  // synchronises; throws on a degenerate map like FEMap does
+    rhs.resize(n_local);                                   // the owned rows; ghost rows were added into their owners
     *system.rhs = rhs;
   }
   system.rhs->close();

@@ -4,9 +4,12 @@
 // device, and NumericVector::add_vector(v, A) — the product SparseMatrix::vector_mult resolves to — runs on the device
 // matrix of a GpuSparseMatrix.
 //
-// One rank per vector in this round (size == local_size, SERIAL/PARALLEL alike); the Krylov operations (dot, add(a,v),
-// scale, norms, pointwise ops, add_vector) are device kernels with fixed-order reductions; entry access (operator(),
-// set/add of single entries) goes through single-entry transfers and is meant for set-up code, not loops.
+// Storage is the local part (local_size entries from first_local_index, as DistributedVector,
+// include/numerics/distributed_vector.h); on several ranks the reductions finish with the communicator's sum / max / min
+// in rank order (DistributedVector::dot, distributed_vector.C), localize gathers.  The Krylov operations (dot, add(a,v),
+// scale, norms, pointwise ops) are device kernels with fixed-order reductions; entry access (operator(), set/add of single
+// entries) goes through single-entry transfers and is meant for set-up code, not loops.  add_vector (the product with a
+// GpuSparseMatrix) is one rank only: the halo exchange of the iterate is not part of libfeasm yet.
 #ifndef FEASM_GPU_NUMERIC_VECTOR_H
 #define FEASM_GPU_NUMERIC_VECTOR_H
 
@@ -18,17 +21,18 @@
 
 namespace libMesh {
 
-// the context the vectors of this process run on (one per process: device FEASM_DEVICE or 0)
-inline feasm_ctx* feasm_vector_context() {
+// the context the vectors of this process run on (one per process: device FEASM_DEVICE, else the rank of the first vector
+// made — one process per GPU, as the matrix contexts)
+inline feasm_ctx* feasm_vector_context(int rank = 0) {
   struct Holder {
     feasm_ctx* ctx = nullptr;
-    Holder() {
+    explicit Holder(int rank) {
       const char* dev = std::getenv("FEASM_DEVICE");
-      if (feasm_create(dev ? std::atoi(dev) : 0, &ctx)) libmesh_error_msg("libfeasm: " << feasm_last_error(nullptr));
+      if (feasm_create(dev ? std::atoi(dev) : rank, &ctx)) libmesh_error_msg("libfeasm: " << feasm_last_error(nullptr));
     }
     ~Holder() { if (ctx) feasm_destroy(ctx); }
   };
-  static Holder h;
+  static Holder h(rank);
   return h.ctx;
 }
 
@@ -38,15 +42,25 @@ class GpuNumericVector : public NumericVector<T> {
   explicit GpuNumericVector(const Parallel::Communicator& comm, const ParallelType ptype = AUTOMATIC) : NumericVector<T>(comm, ptype) {}
   GpuNumericVector(const Parallel::Communicator& comm, const numeric_index_type n, const ParallelType ptype = AUTOMATIC)
       : NumericVector<T>(comm, ptype) { this->init(n, n, false, ptype); }
+  GpuNumericVector(const Parallel::Communicator& comm, const numeric_index_type n, const numeric_index_type n_local, const ParallelType ptype = AUTOMATIC)
+      : NumericVector<T>(comm, ptype) { this->init(n, n_local, false, ptype); }  // numeric_vector.h:99
   ~GpuNumericVector() override { release(); }
 
   // ---- lifetime ---------------------------------------------------------------------------------------------------
   void init(const numeric_index_type n, const numeric_index_type n_local, const bool = false, const ParallelType ptype = AUTOMATIC) override {
-    if (n != n_local) libmesh_not_implemented();  // one rank per vector in this round
     release();
-    _n = n;
-    _d = feasm_vec_alloc(ctx(), n);  // zero-initialised (fast == true would allow garbage; zero is always valid)
-    if (!_d) libmesh_error_msg("GpuNumericVector: device allocation of " << n << " entries failed");
+    _n = n_local; _n_global = n; _first = 0;
+    if (this->n_processors() > 1 && ptype != SERIAL) {  // DistributedVector::init, distributed_vector.h:457-480
+      std::vector<numeric_index_type> sizes;
+      this->comm().allgather(n_local, sizes);
+      numeric_index_type tot = 0;
+      for (processor_id_type q = 0; q < this->n_processors(); ++q) { if (q == this->processor_id()) _first = tot; tot += sizes[q]; }
+      if (tot != n) libmesh_error_msg("GpuNumericVector::init: local sizes sum to " << tot << ", not " << n);
+    } else if (n != n_local) {
+      libmesh_error_msg("GpuNumericVector::init: n != n_local on one rank");
+    }
+    _d = feasm_vec_alloc(ctx(), _n ? _n : 1);  // zero-initialised (fast == true would allow garbage; zero is always valid)
+    if (!_d) libmesh_error_msg("GpuNumericVector: device allocation of " << _n << " entries failed");
     this->_type = ptype == AUTOMATIC ? PARALLEL : ptype;
     this->_is_initialized = true;
     this->_is_closed = true;
@@ -78,15 +92,19 @@ class GpuNumericVector : public NumericVector<T> {
     return *this;
   }
   NumericVector<T>& operator=(const NumericVector<T>& v) override {
-    if (v.size() != _n) libmesh_error_msg("GpuNumericVector::operator=: size mismatch");
-    if (const auto* g = dynamic_cast<const GpuNumericVector<T>*>(&v)) check(feasm_vec_copy(ctx(), FEASM_COPY_D2D, _d, g->_d, _n));
-    else { std::vector<T> h; v.localize(h); *this = h; }
+    if (v.size() != _n_global) libmesh_error_msg("GpuNumericVector::operator=: size mismatch");
+    if (const auto* g = dynamic_cast<const GpuNumericVector<T>*>(&v)) {
+      if (g->_n != _n) libmesh_error_msg("GpuNumericVector::operator=: different local sizes");
+      check(feasm_vec_copy(ctx(), FEASM_COPY_D2D, _d, g->_d, _n));
+    } else { std::vector<T> h; v.localize(h); *this = h; }  // the whole vector on every rank; the local part is kept
     return *this;
   }
   NumericVector<T>& operator=(const T s) override { check(feasm_vec_fill(ctx(), _d, _n, s)); return *this; }
   NumericVector<T>& operator=(const std::vector<T>& v) override {
-    if (v.size() != _n) libmesh_error_msg("GpuNumericVector::operator=(std::vector): size mismatch");
-    check(feasm_vec_copy(ctx(), FEASM_COPY_H2D, _d, v.data(), _n));
+    // numeric_vector.h:295: v holds either the local part or the whole vector
+    if (v.size() == _n_global) check(feasm_vec_copy(ctx(), FEASM_COPY_H2D, _d, v.data() + _first, _n));
+    else if (v.size() == _n) check(feasm_vec_copy(ctx(), FEASM_COPY_H2D, _d, v.data(), _n));
+    else libmesh_error_msg("GpuNumericVector::operator=(std::vector): size mismatch");
     return *this;
   }
   // the batched assemble hook: take n entries that are already on the device (feasm_device_rhs of the matrix context)
@@ -98,33 +116,34 @@ class GpuNumericVector : public NumericVector<T> {
   double* device_ptr() { return _d; }
 
   // ---- reductions ---------------------------------------------------------------------------------------------------
-  Real min() const override { return reduce(FEASM_VEC_MIN); }
-  Real max() const override { return reduce(FEASM_VEC_MAX); }
-  T sum() const override { return reduce(FEASM_VEC_SUM); }
-  Real l1_norm() const override { return reduce(FEASM_VEC_L1); }
+  Real min() const override { double r = _n ? reduce(FEASM_VEC_MIN) : HUGE_VAL; if (distributed()) this->comm().min(r); return r; }
+  Real max() const override { double r = _n ? reduce(FEASM_VEC_MAX) : -HUGE_VAL; if (distributed()) this->comm().max(r); return r; }
+  T sum() const override { double r = reduce(FEASM_VEC_SUM); if (distributed()) this->comm().sum(r); return r; }
+  Real l1_norm() const override { double r = reduce(FEASM_VEC_L1); if (distributed()) this->comm().sum(r); return r; }
   Real l2_norm() const override { return std::sqrt(this->dot(*this)); }
-  Real linfty_norm() const override { return reduce(FEASM_VEC_LINF); }
+  Real linfty_norm() const override { double r = reduce(FEASM_VEC_LINF); if (distributed()) this->comm().max(r); return r; }
   T dot(const NumericVector<T>& v) const override {
     double r = 0.;
-    check(feasm_vec_reduce(ctx(), FEASM_VEC_DOT, _d, on_device(v).ptr, _n, &r));
+    if (_n) check(feasm_vec_reduce(ctx(), FEASM_VEC_DOT, _d, on_device(v).ptr, _n, &r));
+    if (distributed()) this->comm().sum(r);
     return r;
   }
 
   // ---- sizes --------------------------------------------------------------------------------------------------------
-  numeric_index_type size() const override { return _n; }
+  numeric_index_type size() const override { return _n_global; }
   numeric_index_type local_size() const override { return _n; }
-  numeric_index_type first_local_index() const override { return 0; }
-  numeric_index_type last_local_index() const override { return _n; }
+  numeric_index_type first_local_index() const override { return _first; }
+  numeric_index_type last_local_index() const override { return _first + _n; }
   std::size_t max_allowed_id() const override { return 0xffffffffu; }
 
   // ---- entries ------------------------------------------------------------------------------------------------------
   T operator()(const numeric_index_type i) const override {
     double v = 0.;
-    check(feasm_vec_copy(ctx(), FEASM_COPY_D2H, &v, _d + i, 1));
+    check(feasm_vec_copy(ctx(), FEASM_COPY_D2H, &v, _d + local(i), 1));
     return v;
   }
-  void set(const numeric_index_type i, const T value) override { check(feasm_vec_set_entry(ctx(), _d, i, value, 0)); this->_is_closed = false; }
-  void add(const numeric_index_type i, const T value) override { check(feasm_vec_set_entry(ctx(), _d, i, value, 1)); this->_is_closed = false; }
+  void set(const numeric_index_type i, const T value) override { check(feasm_vec_set_entry(ctx(), _d, local(i), value, 0)); this->_is_closed = false; }
+  void add(const numeric_index_type i, const T value) override { check(feasm_vec_set_entry(ctx(), _d, local(i), value, 1)); this->_is_closed = false; }
 
   // ---- algebra ------------------------------------------------------------------------------------------------------
   NumericVector<T>& operator+=(const NumericVector<T>& v) override { this->add(T(1), v); return *this; }
@@ -150,6 +169,7 @@ class GpuNumericVector : public NumericVector<T> {
   void add_vector(const NumericVector<T>& v, const SparseMatrix<T>& A) override {
     auto* G = dynamic_cast<GpuSparseMatrix<T>*>(const_cast<SparseMatrix<T>*>(&A));
     if (!G) libmesh_error_msg("GpuNumericVector::add_vector: the matrix is not a GpuSparseMatrix");
+    if (distributed()) libmesh_not_implemented();  // needs the halo exchange of v (see the header comment)
     if (A.n() != v.size() || A.m() != _n) libmesh_error_msg("GpuNumericVector::add_vector: size mismatch");
     const OnDevice dv = on_device(v);
     double* tmp = feasm_vec_alloc(ctx(), _n);
@@ -169,13 +189,14 @@ class GpuNumericVector : public NumericVector<T> {
     this->add_vector(v, At);
   }
 
-  // ---- localize: one rank, so every flavour is a copy ------------------------------------------------------------
+  // ---- localize: the whole vector on every rank (numeric_vector.h:637); on one rank every flavour is a copy ------------
   void localize(std::vector<T>& v_local) const override {
     v_local.resize(_n);
     if (_n) check(feasm_vec_copy(ctx(), FEASM_COPY_D2H, v_local.data(), _d, _n));
+    if (distributed()) this->comm().allgather(v_local);  // local parts in rank order = global order
   }
   void localize(NumericVector<T>& v_local) const override {
-    if (auto* g = dynamic_cast<GpuNumericVector<T>*>(&v_local)) { *g = *this; return; }
+    if (auto* g = dynamic_cast<GpuNumericVector<T>*>(&v_local)) { if (g->_n == _n) { *g = *this; return; } }
     std::vector<T> h;
     this->localize(h);
     v_local = h;
@@ -202,15 +223,19 @@ class GpuNumericVector : public NumericVector<T> {
     ~OnDevice() { if (owned) feasm_vec_free(ctx, owned); }
   };
   OnDevice on_device(const NumericVector<T>& v) const {
-    if (v.size() != _n) libmesh_error_msg("GpuNumericVector: size mismatch (" << v.size() << " vs " << _n << ")");
+    if (v.size() != _n_global) libmesh_error_msg("GpuNumericVector: size mismatch (" << v.size() << " vs " << _n_global << ")");
     OnDevice d;
-    if (const auto* g = dynamic_cast<const GpuNumericVector<T>*>(&v)) { d.ptr = g->_d; return d; }
+    if (const auto* g = dynamic_cast<const GpuNumericVector<T>*>(&v)) {
+      if (g->_n != _n) libmesh_error_msg("GpuNumericVector: different local sizes");
+      d.ptr = g->_d;
+      return d;
+    }
     std::vector<T> h;
-    v.localize(h);
+    v.localize(h);  // the whole vector; the local part is uploaded
     d.ctx = ctx();
-    d.owned = feasm_vec_alloc(d.ctx, _n);
+    d.owned = feasm_vec_alloc(d.ctx, _n ? _n : 1);
     if (!d.owned) libmesh_error_msg("GpuNumericVector: device allocation failed");
-    check(feasm_vec_copy(d.ctx, FEASM_COPY_H2D, d.owned, h.data(), _n));
+    if (_n) check(feasm_vec_copy(d.ctx, FEASM_COPY_H2D, d.owned, h.data() + (h.size() == _n_global ? _first : 0), _n));
     d.ptr = d.owned;
     return d;
   }
@@ -219,15 +244,20 @@ class GpuNumericVector : public NumericVector<T> {
     if (_n) check(feasm_vec_reduce(ctx(), op, _d, nullptr, _n, &r));
     return r;
   }
-  static feasm_ctx* ctx() { return feasm_vector_context(); }
-  static void check(int rc) { if (rc) libmesh_error_msg("libfeasm error " << rc << ": " << feasm_last_error(ctx())); }
+  feasm_ctx* ctx() const { return feasm_vector_context((int)this->processor_id()); }
+  void check(int rc) const { if (rc) libmesh_error_msg("libfeasm error " << rc << ": " << feasm_last_error(ctx())); }
+  bool distributed() const { return this->n_processors() > 1 && this->_type != SERIAL; }
+  numeric_index_type local(numeric_index_type i) const {
+    if (i < _first || i >= _first + _n) libmesh_error_msg("GpuNumericVector: index " << i << " is not local to this rank");
+    return i - _first;
+  }
   void release() {
     if (_d) feasm_vec_free(ctx(), _d);
-    _d = nullptr; _n = 0;
+    _d = nullptr; _n = 0; _n_global = 0; _first = 0;
     this->_is_initialized = false;
   }
   double* _d = nullptr;
-  numeric_index_type _n = 0;
+  numeric_index_type _n = 0, _n_global = 0, _first = 0;  // local size, global size, first local index
 };
 
 }  // namespace libMesh

@@ -22,6 +22,7 @@
 #include "libmesh/sparse_matrix.h"
 #endif
 
+#include <algorithm>
 #include <cmath>
 #include <mutex>
 
@@ -69,6 +70,7 @@ class GpuSparseMatrix : public SparseMatrix<T> {
     _pattern_sent = false; _closed = false; this->_is_initialized = false;
     _uploaded = Uploaded();  // the context is gone: nothing is uploaded any more
     _host_valid = false;
+    _ghosts.clear(); _comm_ready = false;
   }
   void zero() override { if (_ctx && _pattern_sent) check(feasm_zero(_ctx)); _host_valid = false; }
   // same communicator, dof map and sparsity pattern, all values zero (sparse_matrix.h:219); its context is created on
@@ -105,14 +107,14 @@ class GpuSparseMatrix : public SparseMatrix<T> {
   void set(const numeric_index_type i, const numeric_index_type j, const T value) override {  // sparse_matrix.h:295
     std::lock_guard<std::mutex> lock(_mutex);
     ensure_matrix();
-    const uint32_t r = i - _row_start, c = j;
+    const uint32_t r = local_row(i), c = j;
     check(feasm_set_matrix(ctx(), &value, &r, 1, &c, 1));
     _host_valid = false; _closed = false;
   }
   void add(const numeric_index_type i, const numeric_index_type j, const T value) override {
     std::lock_guard<std::mutex> lock(_mutex);
     ensure_matrix();
-    const uint32_t r = i - _row_start, c = j;
+    const uint32_t r = local_row(i), c = j;
     check(feasm_add_matrix(ctx(), &value, &r, 1, &c, 1));
     _host_valid = false; _closed = false;
   }
@@ -124,7 +126,7 @@ class GpuSparseMatrix : public SparseMatrix<T> {
     if (dm.m() != rows.size() || dm.n() != cols.size()) libmesh_error_msg("add_matrix: size mismatch");
     ensure_matrix();  // SparseMatrix::init + add_matrix works without the batched hook
     std::vector<uint32_t> lr(rows.size());
-    for (std::size_t k = 0; k < rows.size(); ++k) lr[k] = rows[k] - _row_start;
+    for (std::size_t k = 0; k < rows.size(); ++k) lr[k] = local_row(rows[k]);
     check(feasm_add_matrix(ctx(), dm.get_values().data(), lr.data(), (int)lr.size(), cols.data(), (int)cols.size()));
     _host_valid = false; _closed = false;
   }
@@ -150,7 +152,8 @@ class GpuSparseMatrix : public SparseMatrix<T> {
     for (uint64_t k = lo; k < hi; ++k) if (_col_idx[k] == j) return _host_values[k];
     return 0.;
   }
-  Real l1_norm() const override {  // max column sum (sparse_matrix.h:379), serial
+  Real l1_norm() const override {  // max column sum (sparse_matrix.h:379), one rank
+    if (this->n_processors() > 1) libmesh_not_implemented();
     mirror();
     std::vector<Real> col(_n, 0.);
     for (std::size_t k = 0; k < _col_idx.size(); ++k) col[_col_idx[k]] += std::abs(_host_values[k]);
@@ -166,6 +169,7 @@ class GpuSparseMatrix : public SparseMatrix<T> {
       for (uint64_t k = _row_ptr[r]; k < _row_ptr[r + 1]; ++k) s += std::abs(_host_values[k]);
       mx = std::max(mx, s);
     }
+    if (this->n_processors() > 1) this->comm().max(mx);  // rows are whole on their owner
     return mx;
   }
   void print_personal(std::ostream& os = libMesh::out) const override {
@@ -244,6 +248,44 @@ class GpuSparseMatrix : public SparseMatrix<T> {
     check(feasm_init_matrix(ctx(), n_local, n_local, _row_ptr.data(), _col_idx.data()));
     _pattern_sent = true;
   }
+  // ---- several ranks (one process per GPU) -----------------------------------------------------------------------
+  // Rows of the context: the owned rows [row_start, row_stop) first, then the ghost rows (dofs of local elements that
+  // another rank owns) in ascending global id — the numbering feasm_build_exchange expects.
+  void set_ghosts(std::vector<dof_id_type> g) { _ghosts = std::move(g); }
+  const std::vector<dof_id_type>& ghosts() const { return _ghosts; }
+  uint32_t local_row(numeric_index_type i) const {
+    if (i >= _row_start && i < _row_stop) return i - _row_start;
+    const auto it = std::lower_bound(_ghosts.begin(), _ghosts.end(), i);
+    if (it == _ghosts.end() || *it != i) libmesh_error_msg("GpuSparseMatrix: row " << i << " is neither owned by nor a ghost of this rank");
+    return (uint32_t)(_row_stop - _row_start + (it - _ghosts.begin()));
+  }
+  // The NCCL communicator of the context, made once per matrix: rank 0 draws the bootstrap id, the libMesh communicator
+  // (MPI) broadcasts its bytes, every rank joins (feasm_comm_init is collective).
+  void ensure_communicator() {
+    if (_comm_ready || this->n_processors() == 1) return;
+    std::vector<char> id(FEASM_COMM_ID_BYTES, 0);
+    int rc = 0;
+    if (this->processor_id() == 0) rc = feasm_comm_unique_id(id.data());
+    this->comm().broadcast(id, 0);
+    if (rc) libmesh_error_msg("libfeasm: " << feasm_last_error(nullptr));
+    check(feasm_comm_init(ctx(), (int)this->n_processors(), (int)this->processor_id(), id.data()));
+    _comm_ready = true;
+  }
+  // After feasm_build_pattern + feasm_build_exchange: the context's pattern is the local one (owned rows merged with what
+  // the peers sent, then the ghost rows).  Its owned rows must be the Graph libMesh built and synchronised itself
+  // (SparsityPattern::Build::parallel_sync) — checked here, entry by entry.
+  void adopt_device_pattern() {
+    const std::size_t n_local = _row_stop - _row_start, n_rows = n_local + _ghosts.size();
+    std::vector<uint64_t> rp(n_rows + 1);
+    std::vector<uint32_t> ci((std::size_t)feasm_nnz(ctx()));
+    check(feasm_get_pattern(ctx(), rp.data(), ci.data()));
+    if (_row_ptr.size() != n_local + 1) libmesh_error_msg("GpuSparseMatrix: the Graph has " << _row_ptr.size() - 1 << " rows, the dof map " << n_local);
+    for (std::size_t r = 0; r <= n_local; ++r)
+      if (rp[r] != _row_ptr[r]) libmesh_error_msg("GpuSparseMatrix: row " << r + _row_start << " of the merged device pattern differs in length from the Graph");
+    if (!std::equal(_col_idx.begin(), _col_idx.end(), ci.begin())) libmesh_error_msg("GpuSparseMatrix: merged device pattern differs from the Graph");
+    _pattern_sent = true;
+  }
+
   // what the batched hook has uploaded into the context (reset by clear() and update_sparsity_pattern())
   struct Uploaded {
     const void* mesh = nullptr;
@@ -271,7 +313,7 @@ class GpuSparseMatrix : public SparseMatrix<T> {
   void mirror() const {
     if (_host_valid) return;
     if (!_ctx || !_pattern_sent) libmesh_error_msg("GpuSparseMatrix: matrix has no values yet");
-    _host_values.resize(_col_idx.size());
+    _host_values.resize(std::max<std::size_t>(_col_idx.size(), (std::size_t)feasm_nnz(_ctx)));  // owned rows first; ghost rows follow on several ranks
     check(feasm_get_values(_ctx, _host_values.data(), nullptr));
     _host_valid = true;
   }
@@ -283,6 +325,8 @@ class GpuSparseMatrix : public SparseMatrix<T> {
   mutable bool _host_valid = false;
   bool _pattern_sent = false, _closed = false;
   Uploaded _uploaded;
+  std::vector<dof_id_type> _ghosts;
+  bool _comm_ready = false;
   std::mutex _mutex;
 };
 

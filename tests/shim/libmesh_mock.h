@@ -7,8 +7,13 @@
 #define FEASM_LIBMESH_MOCK_H
 
 #include <algorithm>
+#include <chrono>
 #include <cmath>
 #include <cstdint>
+#include <cstdio>
+#include <cstdlib>
+#include <cstring>
+#include <thread>
 #include <iostream>
 #include <map>
 #include <set>
@@ -37,7 +42,74 @@ enum ParallelType { AUTOMATIC = 0, SERIAL, PARALLEL, GHOSTED };     // include/e
 enum SolverPackage { PETSC_SOLVERS = 0, TRILINOS_SOLVERS, LASPACK_SOLVERS, SLEPC_SOLVERS, EIGEN_SOLVERS, NLOPT_SOLVERS, INVALID_SOLVER_PACKAGE };
 enum ElemType { HEX8 = 10, HEX27 = 12, TET10 = 9, INVALID_ELEM = 99 };  // include/enums/enum_elem_type.h
 
-namespace Parallel { struct Communicator { processor_id_type rank() const { return 0; } processor_id_type size() const { return 1; } }; }
+// include/parallel/parallel.h -> TIMPI's Communicator (timpi/communicator.h): rank / size and the few collectives the
+// adaptor uses (broadcast, allgather, sum, max, min).  One rank by default; a multi-process test sets FEASM_MOCK_RANK,
+// FEASM_MOCK_SIZE and FEASM_MOCK_DIR, and the collectives then run over files in that directory (every rank writes
+// <sequence>.<rank>, renames it into place and reads the others' — enough to stand in for MPI in a two-process test).
+namespace Parallel {
+struct Communicator {
+  Communicator() {
+    const char* r = std::getenv("FEASM_MOCK_RANK");
+    const char* n = std::getenv("FEASM_MOCK_SIZE");
+    const char* d = std::getenv("FEASM_MOCK_DIR");
+    if (r && n && d) { _rank = (processor_id_type)std::atoi(r); _size = (processor_id_type)std::atoi(n); _dir = d; }
+  }
+  processor_id_type rank() const { return _rank; }
+  processor_id_type size() const { return _size; }
+  // every rank's bytes, in rank order (all the same length)
+  std::vector<std::vector<char>> exchange(const std::vector<char>& mine) const {
+    std::vector<std::vector<char>> all(_size);
+    all[_rank] = mine;
+    if (_size == 1) return all;
+    const unsigned seq = _seq++;
+    const std::string base = _dir + "/" + std::to_string(seq) + ".";
+    {
+      const std::string tmp = base + std::to_string(_rank) + ".tmp", fin = base + std::to_string(_rank);
+      FILE* f = std::fopen(tmp.c_str(), "wb");
+      if (!f) throw std::runtime_error("mock communicator: cannot write " + tmp);
+      if (!mine.empty()) std::fwrite(mine.data(), 1, mine.size(), f);
+      std::fclose(f);
+      std::rename(tmp.c_str(), fin.c_str());
+    }
+    for (processor_id_type q = 0; q < _size; ++q) {
+      if (q == _rank) continue;
+      const std::string fin = base + std::to_string(q);
+      FILE* f = nullptr;
+      for (int tries = 0; tries < 60000 && !(f = std::fopen(fin.c_str(), "rb")); ++tries) std::this_thread::sleep_for(std::chrono::milliseconds(1));
+      if (!f) throw std::runtime_error("mock communicator: rank " + std::to_string(q) + " never wrote " + fin);
+      char buf[4096];
+      std::size_t got;
+      while ((got = std::fread(buf, 1, sizeof(buf), f)) > 0) all[q].insert(all[q].end(), buf, buf + got);
+      std::fclose(f);
+    }
+    return all;
+  }
+  template <typename T> void broadcast(std::vector<T>& data, const unsigned int root_id = 0) const {  // timpi: broadcast(T&, root)
+    std::vector<char> mine;
+    if (_rank == root_id) mine.assign((const char*)data.data(), (const char*)(data.data() + data.size()));
+    const auto all = exchange(mine);
+    data.resize(all[root_id].size() / sizeof(T));
+    std::memcpy(data.data(), all[root_id].data(), all[root_id].size());
+  }
+  template <typename T> void allgather(const T& send, std::vector<T>& recv) const {                 // timpi: allgather(const T&, vector<T>&)
+    const auto all = exchange(std::vector<char>((const char*)&send, (const char*)(&send + 1)));
+    recv.resize(_size);
+    for (processor_id_type q = 0; q < _size; ++q) std::memcpy(&recv[q], all[q].data(), sizeof(T));
+  }
+  template <typename T> void allgather(std::vector<T>& r, const bool = false) const {               // timpi: in place, variable lengths
+    const auto all = exchange(std::vector<char>((const char*)r.data(), (const char*)(r.data() + r.size())));
+    r.clear();
+    for (processor_id_type q = 0; q < _size; ++q) r.insert(r.end(), (const T*)all[q].data(), (const T*)(all[q].data() + all[q].size()));
+  }
+  template <typename T> void sum(T& x) const { std::vector<T> a; allgather(x, a); x = T(0); for (const T& v : a) x += v; }   // rank order: deterministic
+  template <typename T> void max(T& x) const { std::vector<T> a; allgather(x, a); for (const T& v : a) x = v > x ? v : x; }
+  template <typename T> void min(T& x) const { std::vector<T> a; allgather(x, a); for (const T& v : a) x = v < x ? v : x; }
+  void barrier() const { int one = 1; sum(one); }
+  processor_id_type _rank = 0, _size = 1;
+  std::string _dir;
+  mutable unsigned _seq = 0;
+};
+}  // namespace Parallel
 struct ParallelObject {                                              // include/parallel/parallel_object.h
   explicit ParallelObject(const Parallel::Communicator& c) : _communicator(c) {}
   const Parallel::Communicator& comm() const { return _communicator; }
@@ -94,8 +166,11 @@ typedef std::map<dof_id_type, Number> DofConstraintValueMap;                    
 class DofMap {                                                                     // include/base/dof_map.h
  public:
   dof_id_type n_dofs() const { return _n_dofs; }                                   // dof_map_base.h
-  dof_id_type first_dof() const { return 0; }                                      // dof_map_base.h:185
-  dof_id_type end_dof() const { return _n_dofs; }                                  // dof_map_base.h:191
+  // dof_map_base.h:185-197: first_dof(proc) / end_dof(proc), proc defaulting to this rank.  _first empty = one rank.
+  dof_id_type first_dof(processor_id_type p = (processor_id_type)-1) const { return _first.empty() ? 0 : _first[p == (processor_id_type)-1 ? _rank : p]; }
+  dof_id_type end_dof(processor_id_type p = (processor_id_type)-1) const { return _first.empty() ? _n_dofs : _first[(p == (processor_id_type)-1 ? _rank : p) + 1]; }
+  processor_id_type n_processors() const { return _first.empty() ? 1 : (processor_id_type)(_first.size() - 1); }
+  processor_id_type processor_id() const { return _rank; }
   dof_id_type n_local_dofs() const { return end_dof() - first_dof(); }
   void dof_indices(const Elem* e, std::vector<dof_id_type>& di) const {            // dof_map.h:2201 / src/base/dof_map.C:2201
     di.assign(_elem_dofs.begin() + (std::size_t)e->id() * _nd, _elem_dofs.begin() + (std::size_t)(e->id() + 1) * _nd);
@@ -107,6 +182,8 @@ class DofMap {                                                                  
   dof_id_type _n_dofs = 0;
   unsigned _nd = 0;
   std::vector<dof_id_type> _elem_dofs;  // [n_elem][_nd], element id major
+  std::vector<dof_id_type> _first;      // [n_processors + 1] dof ranges (empty: one rank owns everything)
+  processor_id_type _rank = 0;
 };
 
 template <typename T> class SparseMatrix;
