@@ -716,16 +716,35 @@ k_elem_elasticity(const double* __restrict__ xyz, const uint32_t* __restrict__ c
   __syncthreads();
 
   const int64_t stride = (int64_t)gridDim.x * WARPS;
-  for (int64_t e = e0 + (int64_t)blockIdx.x * WARPS + warp; e < e1; e += stride) {
-    if (lane < NPE) {
-      const uint64_t node = conn[e * NPE + lane];
-      X[3 * lane] = xyz[node * 3]; X[3 * lane + 1] = xyz[node * 3 + 1]; X[3 * lane + 2] = xyz[node * 3 + 2];
-    }
+  // Two-deep prefetch of the element's inputs: the node coordinates of the element after this one and the node ids of the
+  // one after that are in flight while this one is computed (connectivity -> coordinates is a dependent pair of global
+  // loads; unprefetched it was 21 % of the kernel's stall samples, profiles/r2/ncu_full_elast_64.md).
+  const int64_t e_first = e0 + (int64_t)blockIdx.x * WARPS + warp;
+  const bool nl = lane < NPE;
+  uint64_t node1 = 0;
+  double cx = 0., cy = 0., cz = 0.;
+  if (nl && e_first < e1) {
+    const uint64_t node = conn[e_first * NPE + lane];
+    cx = xyz[node * 3]; cy = xyz[node * 3 + 1]; cz = xyz[node * 3 + 2];
+  }
+  if (nl && e_first + stride < e1) node1 = conn[(e_first + stride) * NPE + lane];
+  for (int64_t e = e_first; e < e1; e += stride) {
+    if (nl) { X[3 * lane] = cx; X[3 * lane + 1] = cy; X[3 * lane + 2] = cz; }
     __syncwarp();
+    if (nl && e + stride < e1) { cx = xyz[node1 * 3]; cy = xyz[node1 * 3 + 1]; cz = xyz[node1 * 3 + 2]; }
+    if (nl && e + 2 * stride < e1) node1 = conn[(e + 2 * stride) * NPE + lane];
     double S[9], JxW, x, y, z;
     const bool affine = geom_phase<NPE, NQ>(X, s_tab, lane, false, flags, S, JxW, x, y, z);
     fw[lane] = lane < NQ ? JxW : 0.;
     double* out = kf + (uint64_t)(e - e0) * (ND * LDR);
+#ifdef FEASM_DEV_STORE_SAME  // development build: every element of a warp goes to one record (stays in L2; results are wrong)
+    out = kf + (uint64_t)(blockIdx.x * WARPS + warp) * (ND * LDR);
+#endif
+#ifdef FEASM_DEV_NOSTORE  // development build: how much of the kernel is the record stores?  (results are wrong)
+    const bool dev_store = lam1 == 12345.678;
+#else
+    constexpr bool dev_store = true;
+#endif
 
     // P_dd' for one (d, d') pair -> tile[a*TLD + b]
     // SYM (d == d'): P is symmetric, only the blocks on and above the diagonal go through DMMA and are mirrored
@@ -774,19 +793,20 @@ k_elem_elasticity(const double* __restrict__ xyz, const uint32_t* __restrict__ c
         }
     };
 
+#define OUT_IDX(i, a, k, b) (((i) * NPE + (a)) * LDR + (k) * NPE + (b))
     // diagonal variable blocks: K_dd = (l1 + l2) P_dd + l2 (P_00 + P_11 + P_22)
     product(0, 0, tile, std::true_type{});
     product(1, 1, tile + TILE, std::true_type{});
     product(2, 2, tile + 2 * TILE, std::true_type{});
     __syncwarp();
-    if (lane < NPE) {
+    if (lane < NPE && dev_store) {
 #pragma unroll 3  // three rows in flight: the loop is a chain of shared-memory loads feeding stores, not issue bound
       for (int a = 0; a < NPE; ++a) {
         const double p0 = tile[a * TLD + lane], p1 = tile[TILE + a * TLD + lane], p2 = tile[2 * TILE + a * TLD + lane];
         const double tr = lam2 * ((p0 + p1) + p2);
-        out[(0 * NPE + a) * LDR + 0 * NPE + lane] = (lam1 + lam2) * p0 + tr;
-        out[(1 * NPE + a) * LDR + 1 * NPE + lane] = (lam1 + lam2) * p1 + tr;
-        out[(2 * NPE + a) * LDR + 2 * NPE + lane] = (lam1 + lam2) * p2 + tr;
+        out[OUT_IDX(0, a, 0, lane)] = (lam1 + lam2) * p0 + tr;
+        out[OUT_IDX(1, a, 1, lane)] = (lam1 + lam2) * p1 + tr;
+        out[OUT_IDX(2, a, 2, lane)] = (lam1 + lam2) * p2 + tr;
       }
       // Fe (systems_of_equations_ex6.C:233-236): body force f_i, same for every variable up to the factor
       double m = 0.;
@@ -802,12 +822,12 @@ k_elem_elasticity(const double* __restrict__ xyz, const uint32_t* __restrict__ c
       const int i = pair == 2 ? 1 : 0, k = pair == 0 ? 1 : 2;
       product(i, k, tile, std::false_type{});
       __syncwarp();
-      if (lane < NPE) {
+      if (lane < NPE && dev_store) {
 #pragma unroll 3
         for (int a = 0; a < NPE; ++a) {
           const double p = tile[a * TLD + lane], pt = tile[lane * TLD + a];
-          out[(i * NPE + a) * LDR + k * NPE + lane] = lam1 * p + lam2 * pt;
-          out[(k * NPE + a) * LDR + i * NPE + lane] = lam2 * p + lam1 * pt;
+          out[OUT_IDX(i, a, k, lane)] = lam1 * p + lam2 * pt;
+          out[OUT_IDX(k, a, i, lane)] = lam2 * p + lam1 * pt;
         }
       }
       __syncwarp();
