@@ -186,6 +186,17 @@ inline cudaError_t feasm_checked_free(void* p, const char* what, const char* fil
 }
 #define cudaFree(p) feasm_checked_free((void*)(p), #p, __FILE__, __LINE__)
 
+// -DFEASM_DEBUG_BOUNDS: device-side asserts on every index the kernels take from a precomputed map (position rows of the
+// records, ring slots, exchange slots, pattern positions).  A failing assert ends the kernel with cudaErrorAssert and names
+// the line; the product build compiles them out.  (make DEBUG_BOUNDS=1 builds libmesh_b200/libfeasm_bounds.so; the GPU suite
+// runs against it with FEASM_LIB.)
+#ifdef FEASM_DEBUG_BOUNDS
+#include <cassert>
+#define FEASM_DEV_ASSERT(c) assert(c)
+#else
+#define FEASM_DEV_ASSERT(c) ((void)0)
+#endif
+
 // error helpers
 int feasm_fail(feasm_ctx* ctx, int code, const std::string& msg);
 inline const char* feasm_basename(const char* path) {

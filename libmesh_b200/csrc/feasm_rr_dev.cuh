@@ -199,6 +199,7 @@ __device__ __forceinline__ void rr_process_batch(const int64_t base, const int n
 #pragma unroll
       for (int bb = 0; bb < NDC; ++bb) {
         if (lane + 32 * bb <= nd) {  // positions within one record are distinct
+          FEASM_DEV_ASSERT((int)cur.p[bb] <= fe_cell);  // a position names a cell of the row image (Fe: the cell behind it)
           const uint32_t ia = img_a + (cur.p[bb] << 3);
           sts_f64(ia, lds_f64(ia) + cur.v[bb]);
         }
@@ -208,10 +209,12 @@ __device__ __forceinline__ void rr_process_batch(const int64_t base, const int n
 #pragma unroll
       for (int bb = 0; bb < NDC; ++bb) flp = bb == fl_pass ? cur.p[bb] : flp;
       if (__ballot_sync(FULL, lane == fl_lane && flp != 0)) {  // RR_LAST: write the finished row out and clear the image
+        FEASM_DEV_ASSERT(todo != 0);  // a RR_LAST flag for every row of the batch, no more
         const int jl = __ffs(todo) - 1;
         todo &= todo - 1;
         const uint64_t rp0 = __shfl_sync(FULL, my_rp0, jl);
         const int len = __shfl_sync(FULL, my_len, jl);
+        FEASM_DEV_ASSERT(len >= 0 && len <= fe_cell);
         const uint32_t r = row_list ? __shfl_sync(FULL, my_r, jl) : (uint32_t)(base + jl);
         double* dst = values + rp0 + lane;
         const uint32_t src = img_a + 8 * lane;

@@ -195,25 +195,27 @@ __global__ void k_elem_flags(const uint32_t* __restrict__ elem_dofs, const uint8
   if (any) list[atomicAdd(count, 1u)] = (uint32_t)e;  // order is irrelevant: elements are constrained independently
 }
 
-__global__ void k_pack(const uint64_t* __restrict__ slots, uint64_t n, uint64_t nnz, const double* __restrict__ values,
+__global__ void k_pack(const uint64_t* __restrict__ slots, uint64_t n, uint64_t nnz, uint64_t n_rows, const double* __restrict__ values,
                        const double* __restrict__ rhs, double* __restrict__ out) {
   const uint64_t i = blockIdx.x * (uint64_t)blockDim.x + threadIdx.x;
   if (i < n) {
     const uint64_t s = slots[i];
+    FEASM_DEV_ASSERT(s < nnz + n_rows);
     out[i] = s < nnz ? values[s] : rhs[s - nnz];
   }
 }
 
 // One thread per destination slot: the entries the peers sent for it are added in receive-buffer (= fixed peer) order.
 __global__ void k_unpack(const uint64_t* __restrict__ uslot, const uint64_t* __restrict__ seg, const uint64_t* __restrict__ perm,
-                         uint64_t n_slots, uint64_t nnz, const double* __restrict__ in, double* __restrict__ values,
-                         double* __restrict__ rhs) {
+                         uint64_t n_slots, uint64_t nnz, uint64_t n_rows, uint64_t n_recv, const double* __restrict__ in,
+                         double* __restrict__ values, double* __restrict__ rhs) {
   const uint64_t k = blockIdx.x * (uint64_t)blockDim.x + threadIdx.x;
   if (k >= n_slots) return;
   const uint64_t s = uslot[k];
+  FEASM_DEV_ASSERT(s < nnz + n_rows);
   double* dst = s < nnz ? values + s : rhs + (s - nnz);
   double acc = *dst;
-  for (uint64_t i = seg[k]; i < seg[k + 1]; ++i) acc += in[perm[i]];
+  for (uint64_t i = seg[k]; i < seg[k + 1]; ++i) { FEASM_DEV_ASSERT(perm[i] < n_recv); acc += in[perm[i]]; }
   *dst = acc;
 }
 
@@ -367,7 +369,8 @@ int feasm_launch_elem_flags(feasm_ctx* ctx) {
 
 int feasm_launch_pack(feasm_ctx* ctx) {
   const uint64_t n = ctx->send_ptr.empty() ? 0 : ctx->send_ptr.back();
-  if (n) k_pack<<<(unsigned)((n + 255) / 256), 256, 0, ctx->stream>>>(ctx->d_send_slots, n, ctx->nnz, ctx->d_values, ctx->d_rhs, ctx->d_send_buf);
+  if (n) k_pack<<<(unsigned)((n + 255) / 256), 256, 0, ctx->stream>>>(ctx->d_send_slots, n, ctx->nnz, (uint64_t)ctx->n_rows, ctx->d_values, ctx->d_rhs,
+                                                                             ctx->d_send_buf);
   FEASM_CUDA(ctx, cudaGetLastError());
   return FEASM_OK;
 }
@@ -376,6 +379,7 @@ int feasm_launch_unpack(feasm_ctx* ctx) {
   const uint64_t n = ctx->n_unpack_slots;
   if (n)
     k_unpack<<<(unsigned)((n + 255) / 256), 256, 0, ctx->stream>>>(ctx->d_unpack_slot, ctx->d_unpack_seg, ctx->d_unpack_perm, n, ctx->nnz,
+                                                                    (uint64_t)ctx->n_rows, ctx->n_peers ? ctx->recv_ptr[ctx->n_peers] : 0,
                                                                     ctx->d_recv_buf, ctx->d_values, ctx->d_rhs);
   FEASM_CUDA(ctx, cudaGetLastError());
   return FEASM_OK;
