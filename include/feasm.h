@@ -32,6 +32,7 @@ extern "C" {
 #define FEASM_HEX8 8
 #define FEASM_HEX27 27
 #define FEASM_TET10 10
+#define FEASM_HEX20 20 /* serendipity hex (cell_hex20.C, fe_lagrange_shape_3D.C:848-925); volume terms only, no side loads yet */
 
 /* problems (the Ke/Fe contraction that runs per element) */
 #define FEASM_POISSON 1    /* introduction_ex4.C:464-537: Ke = int grad phi_i . grad phi_j, Fe = int f phi_i */

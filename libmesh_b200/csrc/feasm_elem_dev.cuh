@@ -59,14 +59,18 @@ __constant__ AffineCheck c_affine_hex27[23] = {  // cell_hex27.C:125-166
     {1, 0, 25, 19, .5f, 1}, {1, 0, 26, 24, .5f, 1}, {4, 0, 7, 3, 1, 1},     {4, 0, 12, 0, .5f, 1},  {4, 0, 13, 1, .5f, 1},
     {4, 0, 14, 2, .5f, 1},  {4, 0, 15, 3, .5f, 1},  {4, 0, 22, 9, .5f, 1},  {4, 0, 24, 11, .5f, 1}, {3, 0, 11, 0, .5f, 1},
     {3, 0, 9, 1, .5f, 1},   {3, 0, 17, 5, .5f, 1},  {3, 0, 19, 4, .5f, 1}};
+__constant__ AffineCheck c_affine_hex20[16] = {  // cell_hex20.C:119-153
+    {1, 0, 2, 3, 1, 1},    {1, 0, 5, 4, 1, 1},    {1, 0, 6, 7, 1, 1},    {1, 0, 8, 0, .5f, 1},  {1, 0, 10, 3, .5f, 1}, {1, 0, 16, 4, .5f, 1},
+    {1, 0, 18, 7, .5f, 1}, {4, 0, 7, 3, 1, 1},    {4, 0, 12, 0, .5f, 1}, {4, 0, 13, 1, .5f, 1}, {4, 0, 14, 2, .5f, 1}, {4, 0, 15, 3, .5f, 1},
+    {3, 0, 11, 0, .5f, 1}, {3, 0, 9, 1, .5f, 1},  {3, 0, 17, 5, .5f, 1}, {3, 0, 19, 4, .5f, 1}};
 __constant__ AffineCheck c_affine_tet10[6] = {{1, 0, 4, 0, 1, 2}, {2, 1, 5, 1, 1, 2}, {2, 0, 6, 0, 1, 2},  // cell_tet10.C:143-170
                                               {3, 0, 7, 0, 1, 2}, {3, 1, 8, 1, 1, 2}, {3, 2, 9, 2, 1, 2}};
 
 template <int NPE>
 __device__ __forceinline__ bool affine_check_lane(const double* X, int lane) {
-  constexpr int N = NPE == 27 ? 23 : (NPE == 8 ? 4 : 6);
+  constexpr int N = NPE == 27 ? 23 : (NPE == 20 ? 16 : (NPE == 8 ? 4 : 6));
   if (lane >= N) return true;
-  const AffineCheck c = NPE == 27 ? c_affine_hex27[lane] : (NPE == 8 ? c_affine_hex8[lane] : c_affine_tet10[lane]);
+  const AffineCheck c = NPE == 27 ? c_affine_hex27[lane] : (NPE == 20 ? c_affine_hex20[lane] : (NPE == 8 ? c_affine_hex8[lane] : c_affine_tet10[lane]));
   double na = 0., nb = 0., nd = 0.;
 #pragma unroll
   for (int d = 0; d < 3; ++d) {

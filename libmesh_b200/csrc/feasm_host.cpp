@@ -104,10 +104,14 @@ int feasm_cube_sizes(int elem_type, int nx, int ny, int nz, int64_t* n_elem, int
     if (n_nodes) *n_nodes = corners + faces + cells + hex_edges + 4 * faces + 14 * cells;
     return FEASM_OK;
   }
-  if ((elem_type != FEASM_HEX8 && elem_type != FEASM_HEX27) || nx < 1 || ny < 1 || nz < 1) return FEASM_ERR_ARG;
+  if ((elem_type != FEASM_HEX8 && elem_type != FEASM_HEX27 && elem_type != FEASM_HEX20) || nx < 1 || ny < 1 || nz < 1) return FEASM_ERR_ARG;
   const int s = elem_type == FEASM_HEX8 ? 1 : 2;
   if (n_elem) *n_elem = (int64_t)nx * ny * nz;
   if (n_nodes) *n_nodes = (int64_t)(s * nx + 1) * (s * ny + 1) * (s * nz + 1);
+  if (n_nodes && elem_type == FEASM_HEX20) {  // the HEX27 lattice without its face and cell centres: corners + one node per edge
+    const int64_t X = nx, Y = ny, Z = nz;
+    *n_nodes = (X + 1) * (Y + 1) * (Z + 1) + X * (Y + 1) * (Z + 1) + (X + 1) * Y * (Z + 1) + (X + 1) * (Y + 1) * Z;
+  }
   return FEASM_OK;
 }
 
@@ -120,6 +124,37 @@ int feasm_build_cube(int elem_type, int nx, int ny, int nz, const double bounds[
   const int s = elem_type == FEASM_HEX8 ? 1 : 2;
   const int64_t gx = (int64_t)s * nx, gy = (int64_t)s * ny, gz = (int64_t)s * nz;
   const int64_t sx = gx + 1, sy = gy + 1;
+  if (elem_type == FEASM_HEX20) {
+    // build_cube(HEX20) (src/mesh/mesh_generation.C:1315-1345 nodes, :1559-1592 elements): the HEX27 lattice is laid down,
+    // every element takes the 20 lattice points of its cell with at most one odd index (corners, edge mid-points); the
+    // lattice points no element uses (two or three odd indices: face and cell centres) are deleted by prepare_for_use and
+    // the ids compacted in ascending lattice order.
+    const int64_t n_lat = sx * sy * (gz + 1);
+    std::vector<uint32_t> compact(n_lat, 0xffffffffu);
+    uint32_t next = 0;
+    for (int64_t id = 0; id < n_lat; ++id) {
+      const int64_t i = id % sx, j = (id / sx) % sy, k = id / (sx * sy);
+      if ((i & 1) + (j & 1) + (k & 1) > 1) continue;
+      const uint32_t n = compact[id] = next++;
+      if (xyz) {
+        xyz[3 * (size_t)n + 0] = (double)i / (double)gx * (bounds[1] - bounds[0]) + bounds[0];
+        xyz[3 * (size_t)n + 1] = (double)j / (double)gy * (bounds[3] - bounds[2]) + bounds[2];
+        xyz[3 * (size_t)n + 2] = (double)k / (double)gz * (bounds[5] - bounds[4]) + bounds[4];
+      }
+      if (mask) mask[n] = (uint8_t)((k == 0) << 0 | (j == 0) << 1 | (i == gx) << 2 | (j == gy) << 3 | (i == 0) << 4 | (k == gz) << 5);
+    }
+    if ((int64_t)next != nn) return FEASM_ERR_ARG;
+    if (conn) {
+      int64_t off[20];
+      for (int a = 0; a < 20; ++a) off[a] = (kRef[a][0] + 1) + sx * ((kRef[a][1] + 1) + sy * (int64_t)(kRef[a][2] + 1));
+      for (int64_t e = 0; e < ne; ++e) {
+        const int64_t ei = e % nx, ej = (e / nx) % ny, ek = e / ((int64_t)nx * ny);
+        const int64_t corner = 2 * ei + sx * (2 * ej + sy * (2 * ek));
+        for (int a = 0; a < 20; ++a) conn[e * 20 + a] = compact[corner + off[a]];
+      }
+    }
+    return FEASM_OK;
+  }
   if (xyz || mask)
     for (int64_t id = 0; id < nn; ++id) {
       const int64_t i = id % sx, j = (id / sx) % sy, k = id / (sx * sy);

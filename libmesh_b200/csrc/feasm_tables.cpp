@@ -59,7 +59,7 @@ const int kTetEdge[6][2] = {{0, 1}, {1, 2}, {0, 2}, {0, 3}, {1, 3}, {2, 3}};
 bool feasm_make_tables(int elem_type, int qorder, FeasmTables& t, std::string& err) {
   t = FeasmTables();
   t.npe = elem_type;
-  if (elem_type == FEASM_HEX8 || elem_type == FEASM_HEX27) {
+  if (elem_type == FEASM_HEX8 || elem_type == FEASM_HEX27 || elem_type == FEASM_HEX20) {
     double x[3], w[3];
     const int n1 = gauss1d(qorder, x, w);
     if (!n1) { err = "unsupported Gauss order for hex"; return false; }
@@ -74,6 +74,36 @@ bool feasm_make_tables(int elem_type, int qorder, FeasmTables& t, std::string& e
     const int deg = elem_type == FEASM_HEX8 ? 1 : 2;
     const size_t sz = (size_t)t.npe * t.nq;
     t.phi.resize(sz); t.dxi.resize(sz); t.deta.resize(sz); t.dzeta.resize(sz);
+    if (elem_type == FEASM_HEX20) {
+      // The 20-node serendipity basis (Lagrange SECOND on HEX20, fe_lagrange_shape_3D.C:848-925 / :1876-2090), in the
+      // closed form over the node's reference coordinates (x0, y0, z0) in {-1, 0, 1}:
+      //   corner:    (1 + x0 xi)(1 + y0 eta)(1 + z0 zeta)(x0 xi + y0 eta + z0 zeta - 2) / 8
+      //   mid-edge:  (1 - c_m^2)(1 + a0 a)(1 + b0 b) / 4      (m the axis with coordinate 0, a and b the other two)
+      for (int a = 0; a < 20; ++a)
+        for (int q = 0; q < t.nq; ++q) {
+          const double c[3] = {t.qp[3 * q], t.qp[3 * q + 1], t.qp[3 * q + 2]};
+          const double n0[3] = {(double)kHexNode[a][0], (double)kHexNode[a][1], (double)kHexNode[a][2]};
+          const size_t o = (size_t)a * t.nq + q;
+          double* g[3] = {&t.dxi[o], &t.deta[o], &t.dzeta[o]};
+          if (a < 8) {
+            const double f[3] = {1. + n0[0] * c[0], 1. + n0[1] * c[1], 1. + n0[2] * c[2]};
+            const double L = n0[0] * c[0] + n0[1] * c[1] + n0[2] * c[2] - 2.;
+            t.phi[o] = .125 * f[0] * f[1] * f[2] * L;
+            for (int d = 0; d < 3; ++d) {
+              const double others = f[(d + 1) % 3] * f[(d + 2) % 3];
+              *g[d] = .125 * n0[d] * others * (L + f[d]);
+            }
+          } else {
+            const int m = n0[0] == 0. ? 0 : (n0[1] == 0. ? 1 : 2), u = (m + 1) % 3, v = (m + 2) % 3;
+            const double bub = 1. - c[m] * c[m], fu = 1. + n0[u] * c[u], fv = 1. + n0[v] * c[v];
+            t.phi[o] = .25 * bub * fu * fv;
+            *g[m] = -.5 * c[m] * fu * fv;
+            *g[u] = .25 * bub * n0[u] * fv;
+            *g[v] = .25 * bub * fu * n0[v];
+          }
+        }
+      return true;
+    }
     for (int a = 0; a < t.npe; ++a)
       for (int q = 0; q < t.nq; ++q) {
         const V1 X = lagrange1d(deg, kHexNode[a][0], t.qp[3 * q]);

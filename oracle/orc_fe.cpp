@@ -46,7 +46,7 @@ static int gauss_1d(int qorder, double* x, double* w) {
 }
 
 bool gauss_rule(int elem_type, int qorder, QRule& q) {
-  if (elem_type == ORC_HEX8 || elem_type == ORC_HEX27) {
+  if (elem_type == ORC_HEX8 || elem_type == ORC_HEX27 || elem_type == ORC_HEX20) {
     double x[3], w[3];
     const int np = gauss_1d(qorder, x, w);
     if (!np) { set_error("unsupported hex quadrature order"); return false; }
@@ -160,6 +160,53 @@ void shape_table(int elem_type, int np, const double* pts, ShapeTable& t) {
         t.deta[i * np + p] = s[0][H27_I0[i]] * d[1][H27_I1[i]] * s[2][H27_I2[i]];
         t.dzeta[i * np + p] = s[0][H27_I0[i]] * s[1][H27_I1[i]] * d[2][H27_I2[i]];
       }
+    } else if (elem_type == ORC_HEX20) {
+      // Serendipity functions, fe_lagrange_shape_3D.C:848-925 (values) and :1876-2090 (derivatives), written there as 20
+      // cases in x = (xi + 1)/2 etc.  Restated by node class, with the reference's order of operations:
+      //   corner with end bits (b0,b1,b2):  f0 f1 f2 L,   f_d = b_d ? c_d : 1 - c_d,   L = sum_d (+-2 c_d) + (1 - 2 popcount),
+      //     summed starting from the first axis whose bit is set (the constant first for node 0);
+      //   mid-edge node with free axis m:   4 x the factors in axis order, the free axis giving c_m (1 - c_m).
+      const double c[3] = {.5 * (xi + 1.), .5 * (eta + 1.), .5 * (zeta + 1.)};
+      for (int i = 0; i < 20; ++i) {
+        const int b[3] = {H27_I0[i], H27_I1[i], H27_I2[i]};  // 0 / 1: the end of that axis, 2: the middle (nodes 8-19)
+        double* out[4] = {&t.phi[i * np + p], &t.dxi[i * np + p], &t.deta[i * np + p], &t.dzeta[i * np + p]};
+        if (i < 8) {
+          double f[3];
+          for (int d = 0; d < 3; ++d) f[d] = b[d] ? c[d] : (1. - c[d]);
+          const int first = b[0] ? 0 : (b[1] ? 1 : (b[2] ? 2 : -1));
+          const int pop = b[0] + b[1] + b[2];
+          double L;
+          if (first < 0) {
+            L = 1. - 2. * c[0] - 2. * c[1] - 2. * c[2];
+          } else {
+            L = 2. * c[first];
+            for (int d = 0; d < 3; ++d)
+              if (d != first) L = b[d] ? L + 2. * c[d] : L - 2. * c[d];
+            L = L - (2. * pop - 1.);
+          }
+          *out[0] = f[0] * f[1] * f[2] * L;
+          for (int d = 0; d < 3; ++d) {
+            const int o1 = d == 0 ? 1 : 0, o2 = d == 2 ? 1 : 2;
+            const double s2 = b[d] ? 2. : -2., s1 = b[d] ? 1. : -1.;
+            *out[1 + d] = .5 * f[o1] * f[o2] * (f[d] * s2 + s1 * L);
+          }
+        } else {
+          const int m = b[0] == 2 ? 0 : (b[1] == 2 ? 1 : 2);
+          double v = 4.;
+          for (int d = 0; d < 3; ++d) v = d == m ? v * c[d] * (1. - c[d]) : v * (b[d] ? c[d] : (1. - c[d]));
+          *out[0] = v;
+          for (int d = 0; d < 3; ++d) {
+            double g = 2.;
+            for (int a = 0; a < 3; ++a) {
+              if (a == d) continue;
+              g = a == m ? g * c[a] * (1. - c[a]) : g * (b[a] ? c[a] : (1. - c[a]));
+            }
+            if (d == m) g = g * (1. - 2. * c[d]);
+            else if (!b[d]) g = g * (-1.);
+            *out[1 + d] = g;
+          }
+        }
+      }
     } else {  // TET10, fe_lagrange_shape_3D.C:961-1009, :2179-2330
       const double z1 = xi, z2 = eta, z3 = zeta;
       const double z0 = 1. - z1 - z2 - z3;
@@ -247,6 +294,19 @@ bool has_affine_map(int type, const double* X) {
     if (!rfe(v, sub(P(11), P(0))) || !rfe(v, sub(P(9), P(1))) || !rfe(v, sub(P(17), P(5))) ||
         !rfe(v, sub(P(19), P(4))))
       return false;
+    return true;
+  }
+  if (type == ORC_HEX20) {  // cell_hex20.C:119-153
+    P3 v = sub(P(1), P(0));
+    if (!rfe(v, sub(P(2), P(3))) || !rfe(v, sub(P(5), P(4))) || !rfe(v, sub(P(6), P(7)))) return false;
+    v = divide(v, 2);
+    if (!rfe(v, sub(P(8), P(0))) || !rfe(v, sub(P(10), P(3))) || !rfe(v, sub(P(16), P(4))) || !rfe(v, sub(P(18), P(7)))) return false;
+    v = sub(P(4), P(0));
+    if (!rfe(v, sub(P(7), P(3)))) return false;
+    v = divide(v, 2);
+    if (!rfe(v, sub(P(12), P(0))) || !rfe(v, sub(P(13), P(1))) || !rfe(v, sub(P(14), P(2))) || !rfe(v, sub(P(15), P(3)))) return false;
+    v = divide(sub(P(3), P(0)), 2);
+    if (!rfe(v, sub(P(11), P(0))) || !rfe(v, sub(P(9), P(1))) || !rfe(v, sub(P(17), P(5))) || !rfe(v, sub(P(19), P(4)))) return false;
     return true;
   }
   // TET10, cell_tet10.C:143-170

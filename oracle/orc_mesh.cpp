@@ -75,7 +75,7 @@ static void renumber_nodes(Mesh& m, bool libmesh_order) {
 
 static bool build_cube(Mesh& m, int type, int nx, int ny, int nz, double xmin, double xmax, double ymin, double ymax,
                        double zmin, double zmax, bool libmesh_renumber) {
-  if (type != ORC_HEX8 && type != ORC_HEX27 && type != ORC_TET10) { set_error("build_cube: bad element type"); return false; }
+  if (type != ORC_HEX8 && type != ORC_HEX27 && type != ORC_TET10 && type != ORC_HEX20) { set_error("build_cube: bad element type"); return false; }
   if (nx < 1 || ny < 1 || nz < 1) { set_error("build_cube: n < 1"); return false; }
   m.type = type;
   m.npe = type;
@@ -136,7 +136,14 @@ static bool build_cube(Mesh& m, int type, int nx, int ny, int nz, double xmin, d
         }
         e++;
       }
-  if (type != ORC_TET10) {
+  if (type == ORC_HEX20) {
+    // mesh_generation.C:1559-1592: a HEX20 takes nodes 0-19 of the HEX27 lattice cell; the face and cell centres stay
+    // without an element and are deleted by prepare_for_use (below)
+    m.n_elem = nhex;
+    m.conn.resize((size_t)nhex * 20);
+    for (int64_t h = 0; h < nhex; ++h)
+      for (int a = 0; a < 20; ++a) m.conn[h * 20 + a] = hex[h * 27 + a];
+  } else if (type != ORC_TET10) {
     m.n_elem = nhex;
     m.conn.swap(hex);
   } else {
@@ -183,7 +190,7 @@ static bool build_cube(Mesh& m, int type, int nx, int ny, int nz, double xmin, d
     }
   }
   // prepare_for_use(): orphan (unused HEX27 mid-edge) nodes are deleted and, by default, nodes renumbered
-  if (libmesh_renumber || type == ORC_TET10) renumber_nodes(m, libmesh_renumber);
+  if (libmesh_renumber || type == ORC_TET10 || type == ORC_HEX20) renumber_nodes(m, libmesh_renumber);
   m.n_parts = 1;
   m.elem_pid.assign(m.n_elem, 0);
   m.node_pid.assign(m.n_nodes, 0);

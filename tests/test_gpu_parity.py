@@ -57,6 +57,9 @@ CASES = [
     ("tet10", 10, (3, 2, 2), None, 5),
     ("tet10_skew", 10, (2, 2, 2), (1, 0.02, 99), 5),
     ("hex27_single", 27, (1, 1, 1), None, 0),      # one element: every dof constrained
+    ("hex20", 20, (4, 3, 3), None, 0),             # serendipity hex: 16 rows by DMMA, 4 by DFMA
+    ("hex20_skew", 20, (3, 3, 3), (1, 0.03, 4321), 0),
+    ("hex20_single", 20, (1, 1, 1), None, 0),
 ]
 
 
@@ -82,7 +85,7 @@ def test_pattern_bit_exact_and_values_within_1e12(name, etype, dims, skew, qorde
     ctx.close()
 
 
-@pytest.mark.parametrize("etype,dims,qorder", [(27, (6, 6, 6), 0), (8, (8, 8, 8), 3), (10, (2, 2, 2), 5)])
+@pytest.mark.parametrize("etype,dims,qorder", [(27, (6, 6, 6), 0), (8, (8, 8, 8), 3), (10, (2, 2, 2), 5), (20, (5, 4, 3), 0)])
 def test_device_fd_forcing(etype, dims, qorder):
     """introduction_ex4.C:500-537 evaluated on the device.  The FD Laplacian divides an O(1e-6) difference by 1e-6,
     so one ulp of cos/sin becomes ~1e-10 in f: parity of this mode is stated against max|rhs| at 1e-11 (DESIGN.md);
@@ -110,7 +113,8 @@ def test_laplace_no_forcing_tet10():
     ctx.close()
 
 
-@pytest.mark.parametrize("etype,dims,skew,qorder", [(27, (3, 3, 3), (1, 0.03, 5), 0), (8, (4, 4, 4), None, 3), (10, (2, 2, 2), None, 5)])
+@pytest.mark.parametrize("etype,dims,skew,qorder", [(27, (3, 3, 3), (1, 0.03, 5), 0), (8, (4, 4, 4), None, 3), (10, (2, 2, 2), None, 5),
+                                                    (20, (3, 2, 2), (1, 0.03, 6), 0)])
 @pytest.mark.parametrize("constrained", [False, True])
 def test_element_matrices(etype, dims, skew, qorder, constrained):
     F, O = _mods()
@@ -202,7 +206,7 @@ def test_argument_errors():
     m, s = make_case(8, (2, 2, 2))
     xyz, conn, _ = m.arrays()
     with pytest.raises(F.FeasmError):
-        ctx.set_mesh(20, xyz, conn)  # HEX20 is not supported
+        ctx.set_mesh(18, xyz, conn)  # PRISM18 is not supported
     ctx.set_mesh(8, xyz, conn)
     ed, _, _ = s.dofs()
     with pytest.raises(F.FeasmError):
@@ -216,6 +220,8 @@ ELAST = [
     ("hex27_ex6_skew", 27, (3, 2, 2), (1, 0.004, 7)),
     ("hex8_ex6", 8, (5, 3, 2), None),
     ("tet10_ex6", 10, (3, 2, 1), None),
+    ("hex20_ex6", 20, (4, 2, 2), None),
+    ("hex20_ex6_skew", 20, (3, 2, 2), (1, 0.004, 9)),
 ]
 
 

@@ -79,7 +79,7 @@ def _hex_ref_nodes(n):
     return ref[:n]
 
 
-@pytest.mark.parametrize("etype", [O.HEX8, O.HEX27, O.TET10])
+@pytest.mark.parametrize("etype", [O.HEX8, O.HEX27, O.TET10, O.HEX20])
 def test_shapes_are_nodal_and_partition_unity(etype):
     nodes = REF_NODES[etype] if etype == O.TET10 else _hex_ref_nodes(etype)
     phi, dxi, deta, dzeta = O.shapes(etype, nodes)
@@ -114,7 +114,28 @@ def quadratic_grad(p):
     return np.stack([2 * x + 0.125 * y + 0.0625 * z, y + 0.125 * x + 0.03125 * z, 0.5 * z + 0.0625 * x + 0.03125 * y], axis=-1)
 
 
-@pytest.mark.parametrize("etype,order", [(O.HEX8, 1), (O.HEX27, 2), (O.TET10, 2)])
+def test_hex20_shapes_equal_the_textbook_serendipity_form():
+    """The oracle follows the 20-case form of fe_lagrange_shape_3D.C:848-925 in x = (xi + 1) / 2; the closed form over the
+    node's reference coordinates is the independent statement of the same basis (Zienkiewicz: corner nodes
+    (1 + xi xi_i)(1 + eta eta_i)(1 + zeta zeta_i)(xi xi_i + eta eta_i + zeta zeta_i - 2) / 8, mid-edge nodes
+    (1 - xi^2)(1 + eta eta_i)(1 + zeta zeta_i) / 4 and permutations)."""
+    nodes = _hex_ref_nodes(20)
+    pts = np.random.default_rng(3).uniform(-1, 1, size=(64, 3))
+    phi = O.shapes(O.HEX20, pts)[0]
+    xi, eta, zeta = pts.T
+    for i, (x0, y0, z0) in enumerate(nodes):
+        if i < 8:
+            want = 0.125 * (1 + xi * x0) * (1 + eta * y0) * (1 + zeta * z0) * (xi * x0 + eta * y0 + zeta * z0 - 2)
+        elif x0 == 0:
+            want = 0.25 * (1 - xi * xi) * (1 + eta * y0) * (1 + zeta * z0)
+        elif y0 == 0:
+            want = 0.25 * (1 - eta * eta) * (1 + xi * x0) * (1 + zeta * z0)
+        else:
+            want = 0.25 * (1 - zeta * zeta) * (1 + xi * x0) * (1 + eta * y0)
+        assert np.abs(phi[i] - want).max() < 5e-16
+
+
+@pytest.mark.parametrize("etype,order", [(O.HEX8, 1), (O.HEX27, 2), (O.TET10, 2), (O.HEX20, 2)])
 @pytest.mark.parametrize("skew", [False, True])
 def test_fe_reinit_reproduces_polynomials(etype, order, skew):
     """fe_test.h testU/testGradU on the build_cube unit-cube mesh (fe_lagrange_test.C:23-30), plain and SkewFunc-skewed."""
