@@ -62,6 +62,8 @@ int orc_side_reinit(int elem_type, const double* node_xyz /*n*3*/, int side, int
 /* ---- mesh (src/mesh/mesh_generation.C build_cube) ---- */
 orc_mesh* orc_mesh_build_cube(int elem_type, int nx, int ny, int nz, double xmin, double xmax, double ymin,
                               double ymax, double zmin, double zmax, int renumber_nodes);
+orc_mesh* orc_mesh_from_arrays(int elem_type, int64_t n_elem, int64_t n_nodes, const double* xyz, const uint32_t* conn,
+                               const uint8_t* boundary_mask /* may be NULL */);
 void orc_mesh_free(orc_mesh*);
 int64_t orc_mesh_n_elem(const orc_mesh*);
 int64_t orc_mesh_n_nodes(const orc_mesh*);

@@ -48,6 +48,7 @@ def _load(fast: bool):
         "orc_system_set_side_loads": (None, [vp, C.c_int64, vp, vp, vp]),
         "orc_system_set_side_penalty": (None, [vp, C.c_int64, vp, vp, C.c_double, C.c_int, C.c_double]),
         "orc_mesh_build_cube": (vp, [C.c_int] * 4 + [C.c_double] * 6 + [C.c_int]),
+        "orc_mesh_from_arrays": (vp, [C.c_int, C.c_int64, C.c_int64, vp, vp, vp]),
         "orc_mesh_free": (None, [vp]),
         "orc_mesh_n_elem": (C.c_int64, [vp]),
         "orc_mesh_n_nodes": (C.c_int64, [vp]),
@@ -160,6 +161,20 @@ class Mesh:
             raise OracleError(self.L.orc_last_error().decode())
         self.elem_type = elem_type
         self.n_parts = 1
+
+    @classmethod
+    def from_arrays(cls, elem_type, xyz, conn, mask=None, fast=False):
+        """A mesh given by its arrays (locally refined meshes with hanging nodes: what build_cube cannot make)."""
+        self = cls.__new__(cls)
+        self.L, self.fast = lib(fast), fast
+        xyz = np.ascontiguousarray(xyz, dtype=np.float64)
+        conn = np.ascontiguousarray(conn, dtype=np.uint32)
+        mask = None if mask is None else np.ascontiguousarray(mask, dtype=np.uint8)
+        self.h = self.L.orc_mesh_from_arrays(elem_type, conn.shape[0], xyz.shape[0], _ptr(xyz), _ptr(conn), None if mask is None else _ptr(mask))
+        if not self.h:
+            raise OracleError(self.L.orc_last_error().decode())
+        self.elem_type, self.n_parts = elem_type, 1
+        return self
 
     def __del__(self):
         if getattr(self, "h", None):

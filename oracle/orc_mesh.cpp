@@ -210,6 +210,25 @@ orc_mesh* orc_mesh_build_cube(int elem_type, int nx, int ny, int nz, double xmin
   }
   return h;
 }
+// A mesh given by its arrays (tests of meshes build_cube cannot make: locally refined meshes with hanging nodes)
+orc_mesh* orc_mesh_from_arrays(int elem_type, int64_t n_elem, int64_t n_nodes, const double* xyz, const uint32_t* conn, const uint8_t* mask) {
+  if ((elem_type != ORC_HEX8 && elem_type != ORC_HEX27 && elem_type != ORC_TET10 && elem_type != ORC_HEX20) || n_elem < 1 || n_nodes < 1 || !xyz || !conn) {
+    orc::set_error("mesh_from_arrays: bad arguments");
+    return nullptr;
+  }
+  orc_mesh* h = new orc_mesh;
+  orc::Mesh& m = h->m;
+  m.type = m.npe = elem_type;
+  m.n_elem = n_elem; m.n_nodes = n_nodes;
+  m.xyz.assign(xyz, xyz + 3 * n_nodes);
+  m.conn.assign(conn, conn + n_elem * elem_type);
+  if (mask) m.bmask.assign(mask, mask + n_nodes); else m.bmask.assign(n_nodes, 0);
+  for (uint32_t c : m.conn) if (c >= (uint64_t)n_nodes) { orc::set_error("mesh_from_arrays: node id out of range"); delete h; return nullptr; }
+  m.n_parts = 1;
+  m.elem_pid.assign(n_elem, 0);
+  m.node_pid.assign(n_nodes, 0);
+  return h;
+}
 void orc_mesh_free(orc_mesh* h) { delete h; }
 int64_t orc_mesh_n_elem(const orc_mesh* h) { return h->m.n_elem; }
 int64_t orc_mesh_n_nodes(const orc_mesh* h) { return h->m.n_nodes; }
