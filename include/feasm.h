@@ -101,6 +101,16 @@ int feasm_set_dofs(feasm_ctx* ctx, int n_vars, int64_t n_rows, int64_t n_owned, 
 /* DofMap::is_constrained_dof + get_primal_constraint_values for Dirichlet rows (empty constraint rows):
  * local row index and value g. */
 int feasm_set_constraints(feasm_ctx* ctx, int64_t n_constraints, const uint32_t* rows, const double* values);
+/* General constraint rows — hanging nodes, periodic dofs: u_dofs[i] = sum_k coefs[k] u_cols[k] + values[i], k in
+ * [row_ptr[i], row_ptr[i+1]) (DofConstraints, include/base/dof_map.h:97-123; an empty row is a Dirichlet value, so this call
+ * REPLACES feasm_set_constraints).  Elements that touch a dof with a non-empty row are constrained as
+ * DofMap::heterogeneously_constrain_element_matrix_and_vector does it (src/base/dof_map_constraints.C:2519-2614 with
+ * build_constraint_matrix_and_vector, :3543-3673, asymmetric_constraint_rows = true): the element's dof list grows by the
+ * constraining dofs, K <- C^T K C, F <- C^T (F - K H).  Call it BEFORE feasm_build_pattern (the device-built pattern then
+ * holds the couplings DofMap::find_connected_dofs adds, dof_map.C:2915-2975) or pass libMesh's own Graph to
+ * feasm_set_pattern.  One rank per context; feasm_assemble only (not begin / end, not feasm_residual). */
+int feasm_set_constraint_rows(feasm_ctx* ctx, int64_t n, const uint32_t* dofs, const uint64_t* row_ptr, const uint32_t* cols,
+                              const double* coefs, const double* values);
 
 /* Side (face) loads — the boundary-integral part of the assemble loop, systems_of_equations_ex6.C:240-257:
  *   for the listed (element, side) pairs:  fe_face->reinit(elem, side)  (src/fe/fe_boundary.C:109-240, QGauss(dim-1) of

@@ -38,6 +38,7 @@ SYMBOLS = [
     "feasm_exchange_ghost_rows", "feasm_comm_allgather_u64", "feasm_set_matrix", "feasm_init_matrix", "feasm_set_values", "feasm_set_interface_prefix",
     "feasm_build_exchange", "feasm_planner_create", "feasm_planner_destroy", "feasm_planner_error", "feasm_planner_message",
     "feasm_planner_receive", "feasm_planner_finish", "feasm_planner_sizes", "feasm_planner_get", "feasm_apply_plan", "feasm_get_exchange_plan",
+    "feasm_set_constraint_rows",
 ]
 
 
@@ -76,6 +77,7 @@ def lib():
         "feasm_update_coordinates": (i32, [vp, vp]),
         "feasm_set_dofs": (i32, [vp, i32, i64, i64, vp, vp]),
         "feasm_set_constraints": (i32, [vp, i64, vp, vp]),
+        "feasm_set_constraint_rows": (i32, [vp, i64, vp, vp, vp, vp, vp]),
         "feasm_set_pattern": (i32, [vp, vp, vp]),
         "feasm_build_pattern": (i32, [vp]),
         "feasm_nnz": (i64, [vp]),
@@ -306,6 +308,14 @@ class Context:
     def set_constraints(self, rows, values):
         r, v = _c(rows, np.uint32), _c(values, np.float64)
         self._ck(self.L.feasm_set_constraints(self.h, len(r), _p(r), _p(v)))
+
+    def set_constraint_rows(self, dofs, row_ptr, cols, coefs, values):
+        """General constraint rows (hanging nodes): u_dofs[i] = sum_k coefs[k] u_cols[k] + values[i]; replaces set_constraints."""
+        d, rp = _c(dofs, np.uint32), _c(row_ptr, np.uint64)
+        c, w, v = _c(cols, np.uint32), _c(coefs, np.float64), _c(values, np.float64)
+        if len(rp) != len(d) + 1 or len(v) != len(d) or len(c) != len(w):
+            raise FeasmError(-1, "inconsistent constraint row arrays")
+        self._ck(self.L.feasm_set_constraint_rows(self.h, len(d), _p(d), _p(rp), _p(c), _p(w), _p(v)))
 
     def set_pattern(self, row_ptr, col_idx):
         rp, ci = _c(row_ptr, np.uint64), _c(col_idx, np.uint32)

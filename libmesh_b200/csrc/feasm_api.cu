@@ -139,6 +139,7 @@ void feasm_destroy(feasm_ctx* ctx) {
   cudaSetDevice(ctx->device);
   cudaStreamSynchronize(ctx->stream);
   feasm_comm_release(ctx);
+  feasm_general_release(ctx);
   drop_maps(ctx);
   release(ctx->d_xyz); release(ctx->d_conn); release(ctx->d_elem_dofs); release(ctx->d_gid);
   release(ctx->d_node_mask); release(ctx->d_node_base);
@@ -216,6 +217,7 @@ void feasm_reset_mesh(feasm_ctx* ctx, int elem_type, int64_t n_elem, int64_t n_n
 
 int feasm_reset_dofs(feasm_ctx* ctx, int n_vars, int64_t n_rows, int64_t n_owned) {
   drop_maps(ctx);
+  feasm_general_release(ctx);  // constraint rows name dofs of the previous numbering
   // the pattern, the values and the exchange plan belong to the previous dof set: feasm_prepare / feasm_assemble return
   // FEASM_ERR_STATE until feasm_set_pattern / feasm_build_pattern is called again
   release(ctx->d_row_ptr); release(ctx->d_col_idx); release(ctx->d_values);
@@ -308,6 +310,7 @@ int feasm_set_pattern(feasm_ctx* ctx, const uint64_t* row_ptr, const uint32_t* c
       if (col_idx[k] <= col_idx[k - 1]) return feasm_fail(ctx, FEASM_ERR_ARG, "columns of a row must be strictly ascending");
   }
   ctx->prepared = false;
+  feasm_general_invalidate_plan(ctx);
   ctx->nnz = row_ptr[ctx->n_rows];
   int rc = upload(ctx, &ctx->d_row_ptr, row_ptr, (size_t)ctx->n_rows + 1);
   if (rc) return rc;
@@ -323,9 +326,12 @@ int feasm_build_pattern(feasm_ctx* ctx) {
   if (!ctx || !ctx->d_elem_dofs) return feasm_fail(ctx, FEASM_ERR_STATE, "set_dofs first");
   FEASM_CUDA(ctx, cudaSetDevice(ctx->device));
   ctx->prepared = false;
+  feasm_general_invalidate_plan(ctx);
   int rc = feasm_device_build_pattern(ctx);
   if (rc) return rc;
-  return alloc_values(ctx);
+  rc = alloc_values(ctx);
+  if (rc) return rc;
+  return feasm_general_extend_pattern(ctx);  // couplings of elements widened by hanging-node constraints (no-op without them)
 }
 
 int64_t feasm_nnz(const feasm_ctx* ctx) { return ctx ? (int64_t)ctx->nnz : -1; }
@@ -346,6 +352,8 @@ int feasm_prepare(feasm_ctx* ctx) {
   int rc = feasm_build_incidence(ctx);
   if (rc) return rc;
   rc = feasm_build_pos(ctx);
+  if (rc) return rc;
+  rc = feasm_general_prepare(ctx);
   if (rc) return rc;
   ctx->prepared = true;
   return FEASM_OK;
@@ -384,6 +392,14 @@ static int assemble_impl(feasm_ctx* ctx, const feasm_params* params, int mode) {
   const int64_t e_first = two_phase ? ctx->n_iface : ctx->n_elem;
   rc = feasm_launch_element_kernel(ctx, *params, d_f, 0, e_first, ctx->d_kf, rs, params->constrain);
   if (rc) return rc;
+  if (feasm_general_active(ctx)) {  // elements widened by hanging-node constraints: C^T K C into the side buffer
+    if (mode != 0) return feasm_fail(ctx, FEASM_ERR_STATE, "general constraint rows: use feasm_assemble (one rank)");
+    if (params->constrain >= 0) {
+      rc = feasm_general_transform(ctx, rs, params->constrain);
+      if (rc) return rc;
+      launches += 2;
+    }
+  }
   if (ctx->n_con_elems > 0) ++launches;
   if (params->problem == FEASM_POISSON && params->affine_tensor) ++launches;  // the list kernel for non-affine elements
   FEASM_CUDA(ctx, cudaEventRecord(ctx->ev[1], ctx->stream));
@@ -393,6 +409,10 @@ static int assemble_impl(feasm_ctx* ctx, const feasm_params* params, int mode) {
   if (mode == 0) {
     rc = feasm_launch_row_reduce(ctx, nullptr, ctx->n_rows, ctx->stream);
     if (rc) return rc;
+    if (feasm_general_active(ctx) && params->constrain >= 0) {
+      rc = feasm_general_add(ctx);
+      if (rc) return rc;
+    }
     FEASM_CUDA(ctx, cudaEventRecord(ctx->ev[2], ctx->stream));
     return FEASM_OK;
   }
@@ -412,6 +432,7 @@ static int assemble_impl(feasm_ctx* ctx, const feasm_params* params, int mode) {
 
 int feasm_residual(feasm_ctx* ctx, const feasm_params* params, const double* d_u, double* d_r) {
   if (!ctx || !params) return FEASM_ERR_ARG;
+  if (ctx && feasm_general_active(ctx)) return feasm_fail(ctx, FEASM_ERR_STATE, "feasm_residual: not with general constraint rows (feasm_set_constraint_rows) in this version");
   if (!d_u || !d_r) return feasm_fail(ctx, FEASM_ERR_ARG, "null vector");
   if (ctx->d_gid || ctx->n_owned != ctx->n_rows) return feasm_fail(ctx, FEASM_ERR_STATE, "residual: one rank per system in this version");
   FEASM_CUDA(ctx, cudaSetDevice(ctx->device));

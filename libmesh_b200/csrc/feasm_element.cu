@@ -80,7 +80,7 @@ k_elem_poisson(const double* __restrict__ xyz, const uint32_t* __restrict__ conn
   }
   while (ta < n_todo) {
     const int64_t e = e0 + ta;
-    const bool flagged = nflag != 0;
+    const bool flagged = nflag == 1;  // 2: widened by hanging-node constraints, stored unconstrained (feasm_general.cu)
     if (lane < NPE) {
       X[3 * lane] = nx; X[3 * lane + 1] = ny; X[3 * lane + 2] = nz;
       if (tb < n_todo) {

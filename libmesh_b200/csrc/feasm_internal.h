@@ -50,6 +50,8 @@ FEASM_HD constexpr int feasm_ldr(int nd) { return (nd + 1 + 3) & ~3; }
 FEASM_HD constexpr int feasm_pld(int nd, int pos_bytes) { return (((nd + 2) * pos_bytes + 31) & ~31) / pos_bytes; }
 FEASM_HD constexpr int feasm_recb(int nd, int pos_bytes) { return feasm_ldr(nd) * 8 + feasm_pld(nd, pos_bytes) * pos_bytes; }
 
+struct feasm_general;  // feasm_general.cu: general (non-Dirichlet) constraint rows
+
 struct feasm_ctx {
   int device = 0;
   cudaStream_t stream = nullptr;
@@ -164,6 +166,8 @@ struct feasm_ctx {
   size_t stage_cap = 0;
   bool matrix_only = false;  // feasm_init_matrix: pattern + values without a mesh
 
+  feasm_general* gen = nullptr;  // elements widened by hanging-node constraints (feasm_set_constraint_rows)
+
   float last_ms[4] = {0, 0, 0, 0};
   int last_launches = 0;
   bool assemble_open = false;  // between feasm_assemble_begin and feasm_assemble_end
@@ -235,6 +239,14 @@ int feasm_launch_row_reduce(feasm_ctx* ctx, const uint32_t* d_row_list, int64_t 
 int feasm_launch_row_residual(feasm_ctx* ctx, const double* d_u, double* d_r);
 int feasm_launch_pack(feasm_ctx* ctx);
 int feasm_launch_unpack(feasm_ctx* ctx);
+// feasm_general.cu: general constraint rows (hanging nodes)
+void feasm_general_release(feasm_ctx* ctx);
+bool feasm_general_active(const feasm_ctx* ctx);
+int feasm_general_extend_pattern(feasm_ctx* ctx);                           // after feasm_device_build_pattern
+void feasm_general_invalidate_plan(feasm_ctx* ctx);                       // the pattern changed
+int feasm_general_prepare(feasm_ctx* ctx);                                  // inside feasm_prepare
+int feasm_general_transform(feasm_ctx* ctx, int rs, int constrain_mode);    // after the element kernel
+int feasm_general_add(feasm_ctx* ctx);                                      // after the row reduction
 // feasm_comm.cu: destroys an owned communicator and the communication stream
 void feasm_comm_release(feasm_ctx* ctx);
 // mode 0: add, 1: set

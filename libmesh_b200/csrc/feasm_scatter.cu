@@ -191,8 +191,11 @@ __global__ void k_elem_flags(const uint32_t* __restrict__ elem_dofs, const uint8
   const uint32_t* d = elem_dofs + e * nd;
   unsigned any = 0;
   for (int b = 0; b < nd; ++b) any |= con_flag[d[b]];
-  elem_flag[e] = (uint8_t)(any ? 1 : 0);
-  if (any) list[atomicAdd(count, 1u)] = (uint32_t)e;  // order is irrelevant: elements are constrained independently
+  // 1: Dirichlet dofs only (constrained in place); 2: touches a dof with a non-empty constraint row — the element is widened
+  // by feasm_general.cu and must reach its records unconstrained
+  const unsigned f = (any & 2u) ? 2u : (any ? 1u : 0u);
+  elem_flag[e] = (uint8_t)f;
+  if (f == 1u) list[atomicAdd(count, 1u)] = (uint32_t)e;  // order is irrelevant: elements are constrained independently
 }
 
 __global__ void k_pack(const uint64_t* __restrict__ slots, uint64_t n, uint64_t nnz, uint64_t n_rows, const double* __restrict__ values,
