@@ -258,6 +258,7 @@ int feasm_set_constraints(feasm_ctx* ctx, int64_t n, const uint32_t* rows, const
   for (int64_t i = 0; i < n; ++i)
     if (rows[i] >= (uint64_t)ctx->n_rows) return feasm_fail(ctx, FEASM_ERR_ARG, "constraint row out of range");
   FEASM_CUDA(ctx, cudaSetDevice(ctx->device));
+  feasm_general_release(ctx);  // a plain (row, value) list means Dirichlet rows only; feasm_set_constraint_rows rebuilds its own
   // Only the (row, value) LIST crosses the bus (the dense flag / value arrays live on the device and are scattered
   // there).  The constrained SET decides which elements take the element-level constraint pass; when the same rows
   // come again in the same order — every assemble of a steady problem — only the values are refreshed.

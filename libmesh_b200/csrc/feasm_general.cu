@@ -216,9 +216,8 @@ extern "C" int feasm_set_constraint_rows(feasm_ctx* ctx, int64_t n, const uint32
       if (cols[k] >= (uint64_t)ctx->n_rows || cols[k] == dofs[i]) return feasm_fail(ctx, FEASM_ERR_ARG, "constraining dof out of range or equal to its own row");
   }
   FEASM_CUDA(ctx, cudaSetDevice(ctx->device));
-  int rc = feasm_set_constraints(ctx, n, dofs, values);  // flags + values of every constrained dof
+  int rc = feasm_set_constraints(ctx, n, dofs, values);  // flags + values of every constrained dof; drops the previous rows
   if (rc) return rc;
-  feasm_general_release(ctx);
   if (n_ent == 0) return FEASM_OK;  // Dirichlet rows only: nothing is widened
   if (ctx->n_owned < ctx->n_rows) return feasm_fail(ctx, FEASM_ERR_STATE, "general constraint rows: one rank per context in this version");
   feasm_general* g = new feasm_general;

@@ -185,7 +185,27 @@ void assemble(EquationSystems& es, const std::string& system_name, const feasm_p
   // the element-level constraint needs the ghost dofs of the local elements too (libMesh keeps their constraint rows on
   // this rank as well: DofMap::scatter_constraints, dof_map_constraints.C)
   for (std::size_t g = 0; g < A->ghosts().size(); ++g) constrained(A->ghosts()[g], (uint32_t)(n_local + g));
-  A->check(feasm_set_constraints(ctx, (int64_t)con_rows.size(), con_rows.data(), con_vals.data()));
+  // Hanging nodes and other non-empty constraint rows (DofMap::constraint_rows_begin, dof_map.h:1164): the same list with
+  // its rows; elements that touch such a dof are widened on the device as heterogeneously_constrain_element_matrix_and_vector
+  // widens them (feasm_set_constraint_rows).  Without any, the Dirichlet list goes the short way.
+  bool any_row = false;
+  for (auto it = dof_map.constraint_rows_begin(); it != dof_map.constraint_rows_end() && !any_row; ++it) any_row = !it->second.empty();
+  if (any_row) {
+    if (n_ranks > 1) libmesh_error_msg("feasm_libmesh::assemble: non-empty constraint rows on several ranks are not supported yet");
+    std::vector<uint64_t> row_ptr(1, 0);
+    std::vector<uint32_t> cols;
+    std::vector<double> coefs;
+    auto it = dof_map.constraint_rows_begin();
+    for (std::size_t k = 0; k < con_rows.size(); ++k) {  // con_rows ascends with the dof id, as the constraint map does
+      while (it != dof_map.constraint_rows_end() && it->first < con_rows[k] + first) ++it;
+      if (it != dof_map.constraint_rows_end() && it->first == con_rows[k] + first)
+        for (const auto& item : it->second) { cols.push_back(item.first - first); coefs.push_back(item.second); }
+      row_ptr.push_back(cols.size());
+    }
+    A->check(feasm_set_constraint_rows(ctx, (int64_t)con_rows.size(), con_rows.data(), row_ptr.data(), cols.data(), coefs.data(), con_vals.data()));
+  } else {
+    A->check(feasm_set_constraints(ctx, (int64_t)con_rows.size(), con_rows.data(), con_vals.data()));
+  }
 
   // ---- the hot path -----------------------------------------------------------------------------------------------
   if (n_ranks == 1) {

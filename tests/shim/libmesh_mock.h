@@ -162,6 +162,8 @@ typedef std::vector<dof_id_type> Row;
 typedef std::vector<Row> Graph;
 }
 typedef std::map<dof_id_type, Number> DofConstraintValueMap;                       // include/base/dof_map.h:123
+typedef std::map<dof_id_type, Real> DofConstraintRow;                              // dof_map.h:97-100
+typedef std::map<dof_id_type, DofConstraintRow> DofConstraints;                    // dof_map.h:108-112
 
 class DofMap {                                                                     // include/base/dof_map.h
  public:
@@ -175,10 +177,13 @@ class DofMap {                                                                  
   void dof_indices(const Elem* e, std::vector<dof_id_type>& di) const {            // dof_map.h:2201 / src/base/dof_map.C:2201
     di.assign(_elem_dofs.begin() + (std::size_t)e->id() * _nd, _elem_dofs.begin() + (std::size_t)(e->id() + 1) * _nd);
   }
-  bool is_constrained_dof(dof_id_type d) const { return _vals.count(d) != 0; }     // dof_map.h:2426
+  bool is_constrained_dof(dof_id_type d) const { return _vals.count(d) != 0 || _rows.count(d) != 0; }  // dof_map.h:2426
+  DofConstraints::const_iterator constraint_rows_begin() const { return _rows.begin(); }  // dof_map.h:1164
+  DofConstraints::const_iterator constraint_rows_end() const { return _rows.end(); }      // dof_map.h:1170
   DofConstraintValueMap& get_primal_constraint_values() { return _vals; }          // dof_map.h:1263
   unsigned int n_variables() const { return 1; }
   DofConstraintValueMap _vals;
+  DofConstraints _rows;                 // non-empty constraint rows (hanging nodes); Dirichlet dofs live in _vals only
   dof_id_type _n_dofs = 0;
   unsigned _nd = 0;
   std::vector<dof_id_type> _elem_dofs;  // [n_elem][_nd], element id major

@@ -379,6 +379,60 @@ int main() {
     B.close();
     REQUIRE(B.linfty_norm() == 0.);
   }
+  // ---- a non-empty constraint row through the hook (the hanging-node algebra: the element is widened by the constraining
+  // dofs, C^T K C) vs the C ABI driven directly with the same rows ---------------------------------------------------
+  {
+    std::vector<dof_id_type> inner;
+    for (int64_t i = 0; i < n_nodes && inner.size() < 3; ++i) if (!mask[i]) inner.push_back(base[i]);
+    REQUIRE(inner.size() == 3);
+    const dof_id_type slave = inner[2];
+    dof_map._rows[slave] = {{inner[0], 0.5}, {inner[1], 0.5}};
+    std::vector<uint32_t> gd;
+    std::vector<uint64_t> grp(1, 0);
+    std::vector<uint32_t> gc;
+    std::vector<double> gw, gv;
+    for (dof_id_type d = 0; d < (dof_id_type)n_dofs; ++d)
+      if (dof_map.is_constrained_dof(d)) {
+        gd.push_back(d);
+        if (d == slave) { gc.push_back(inner[0]); gc.push_back(inner[1]); gw.push_back(0.5); gw.push_back(0.5); }
+        grp.push_back(gc.size());
+        const auto v = dof_map._vals.find(d);
+        gv.push_back(v == dof_map._vals.end() ? 0. : v->second);
+      }
+    feasm_ctx* c2 = nullptr;
+    CK(feasm_create(0, &c2));
+    CK(feasm_set_mesh(c2, FEASM_HEX27, n_elem, n_nodes, xyz.data(), conn.data()));
+    CK(feasm_set_dofs(c2, 1, n_dofs, n_dofs, dof_map._elem_dofs.data(), nullptr));
+    CK(feasm_set_constraint_rows(c2, (int64_t)gd.size(), gd.data(), grp.data(), gc.data(), gw.data(), gv.data()));
+    CK(feasm_build_pattern(c2));  // with the couplings DofMap::find_connected_dofs adds: the Graph libMesh would hand over
+    std::vector<uint64_t> rp2(n_dofs + 1);
+    std::vector<uint32_t> ci2((std::size_t)feasm_nnz(c2));
+    CK(feasm_get_pattern(c2, rp2.data(), ci2.data()));
+    REQUIRE(ci2.size() > A.col_idx().size());
+    CK(feasm_assemble(c2, &p));
+    std::vector<double> v2(ci2.size()), b2(n_dofs);
+    CK(feasm_get_values(c2, v2.data(), b2.data()));
+    SparsityPattern::Graph graph2(n_dofs);
+    for (int64_t r = 0; r < n_dofs; ++r) graph2[r].assign(ci2.begin() + rp2[r], ci2.begin() + rp2[r + 1]);
+    GpuSparseMatrix<Number> Ah(comm);
+    Ah.attach_dof_map(dof_map);
+    Ah.update_sparsity_pattern(graph2);
+    Ah.init();
+    system.matrix = &Ah;
+    feasm_libmesh::assemble_poisson_ex4(es, "Poisson");
+    Ah.close();
+    REQUIRE(Ah.host_values() == v2);
+    for (int64_t r = 0; r < n_dofs; ++r) REQUIRE(rhs._v[r] == b2[r]);
+    // the constrained row: its diagonal counts the touching elements, its masters carry -coef times that count, rhs 0
+    const double t = Ah(slave, slave);
+    REQUIRE(t >= 1. && Ah(slave, inner[0]) == -0.5 * t && Ah(slave, inner[1]) == -0.5 * t && rhs._v[slave] == 0.);
+    system.matrix = &A;
+    dof_map._rows.clear();
+    feasm_libmesh::assemble_poisson_ex4(es, "Poisson");  // back to Dirichlet rows only
+    REQUIRE(A.host_values() == v);
+    feasm_destroy(c2);
+  }
+
   // ---- a moved mesh: the hook reads the node coordinates on every call (stale flatten cache) ---------------
   {
     feasm_libmesh::assemble_poisson_ex4(es, "Poisson");
