@@ -240,7 +240,9 @@ int spmv(feasm_ctx* ctx, const double* d_x, double* d_y) {
   // long rows (several variables per node: 375 entries at 3 x HEX27) already keep enough bytes in flight per warp and lose
   // to the pipeline's extra registers (measured: 5.6 vs 4.6 TB/s at 3 x 48^3); short rows gain 3-8 %
   if (pipe && ctx->nnz <= (uint64_t)ctx->n_rows * 160) {
-    const int64_t cap = (int64_t)ctx->sm_count * 8;  // 8 CTAs of 8 warps per SM, each warp walks many rows
+    static int per_sm = 0;  // resident CTAs per SM (registers decide: 4 at 54 registers): the persistent grid is one wave
+    if (!per_sm && (cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, k_spmv_pipe, 256, 0) != cudaSuccess || per_sm < 1)) per_sm = 4;
+    const int64_t cap = (int64_t)ctx->sm_count * per_sm;
     const unsigned grid = (unsigned)(want < cap ? want : cap);
     if (grid) k_spmv_pipe<<<grid, 256, 0, ctx->stream>>>(ctx->d_row_ptr, ctx->d_col_idx, ctx->d_values, d_x, ctx->n_rows, d_y);
   } else if (want) {
