@@ -686,17 +686,35 @@ int launch_poisson_affine(feasm_ctx* ctx, const feasm_params& p, const double* d
 // bench/DESIGN quote the flops of THIS algorithm).  One warp per element; each P goes through a shared-memory tile
 // (odd row stride: row and column reads are both conflict free) from which the nine variable blocks are combined
 // and stored.  Fe_(i,a) = f_i sum_q JxW phi_a(q) (body force; the traction term is added by k_side_loads, feasm_side.cu).
+// Shared memory per warp: the three symmetric products P_00, P_11, P_22 packed (upper triangle, row-major) and TWO full
+// tiles for the other products, so that every record row of the element (81 entries + Fe) is formed and written ONCE,
+// whole, rows in ascending order: the element's 70 KB of records leave the SM as one sequential stream.  Row block 0 needs
+// P_01 and P_02, block 1 P_01 and P_12, block 2 P_02 and P_12: with two tiles P_02 is computed twice (+112 of 546 DMMA) —
+// the price of 8 warps per SM instead of the 6 that three tiles allow (measured: 6 warps with all six products resident
+// ran 6.48 ms, the DRAM-side store cost gone but the DMMA chains of 1-2 warps per sub-partition exposed).  (The first form wrote each 27-wide column block of a row from a different product, microseconds apart: 216 B
+// pieces at an 864 B stride, every row touched three times with partial sectors at both ends; the stores cost 3.4 of the
+// kernel's 6.6 ms, 2.4 ms of it on the DRAM side — profiles/r2/ncu_full_elast_64.md.)
+template <int NPE>
+struct ElastTiles {
+  static constexpr int TLD = NPE | 1;                         // odd stride: row and column reads are both conflict free
+  static constexpr int TILE = ((NPE * TLD + 1) & ~1);
+  static constexpr bool PACKED = NPE > 10;                    // small elements have the room for full symmetric tiles
+  static constexpr int PK = PACKED ? ((NPE * (NPE + 1) / 2 + 1) & ~1) : TILE;  // symmetric tile: packed upper triangle, or full
+  static constexpr int PER_WARP = 3 * PK + 2 * TILE + 32 + ((NPE * 3 + 1) & ~1) + 32;  // + m[a] = sum_q JxW phi_a, + X | fw
+  __host__ __device__ static constexpr int pk(int r, int c) { return r * NPE - r * (r - 1) / 2 + (c - r); }  // r <= c
+};
+
 template <int NPE, int NQ, int WARPS>
 __global__ void __launch_bounds__(WARPS * 32, 1)
 k_elem_elasticity(const double* __restrict__ xyz, const uint32_t* __restrict__ conn, const double* __restrict__ tab, double lam1,
                   double lam2, double f0, double f1, double f2, int64_t e0, int64_t e1, double* __restrict__ kf, int rs,
                   int* flags) {
   using C = ElemCfg<NPE, NQ>;
+  using T = ElastTiles<NPE>;
   constexpr int NBP = (NPE + 7) / 8;   // 8-row blocks, padded (all go through DMMA here)
   constexpr int ND = 3 * NPE;
   const int LDR = rs;  // record stride in doubles
-  constexpr int TLD = NPE | 1;          // odd tile stride
-  constexpr int TILE = ((NPE * TLD + 1) & ~1);
+  constexpr int TLD = T::TLD;
   extern __shared__ double smem[];
   double* s_tab = smem;
   double* s_tw = smem + C::TAB_SZ;      // [c][row][TS], rows padded to NBP*8
@@ -708,17 +726,19 @@ k_elem_elasticity(const double* __restrict__ xyz, const uint32_t* __restrict__ c
     s_tw[t] = (row < NPE && q < NQ) ? sqrt(tab[4 * NPE * NQ + q]) * tab[(1 + c) * NPE * NQ + row * NQ + q] : 0.;
   }
   const double* s_phi = s_tab;
-  double* X = s_tw + TWE + (size_t)warp * (C::X_SZ + 32 + 3 * TILE);
-  double* fw = X + C::X_SZ;
-  double* tile = fw + 32;  // three tiles: P_00, P_11, P_22, then reused for the off-diagonal products
+  double* wbase = s_tw + TWE + (size_t)warp * T::PER_WARP;
+  double* diag = wbase;                  // P_00 | P_11 | P_22, packed
+  double* off = wbase + 3 * T::PK;       // two full tiles
+  double* mfe = off + 2 * T::TILE;       // m[a]
+  double* X = mfe + 32;                  // node coordinates of the element
+  double* fw = X + C::X_SZ;              // JxW per quadrature point
   const int g = lane >> 2, t4 = lane & 3;
   const double* twp = s_tw + g * C::TS + t4;
   __syncthreads();
 
   const int64_t stride = (int64_t)gridDim.x * WARPS;
   // Two-deep prefetch of the element's inputs: the node coordinates of the element after this one and the node ids of the
-  // one after that are in flight while this one is computed (connectivity -> coordinates is a dependent pair of global
-  // loads; unprefetched it was 21 % of the kernel's stall samples, profiles/r2/ncu_full_elast_64.md).
+  // one after that are in flight while this one is computed.
   const int64_t e_first = e0 + (int64_t)blockIdx.x * WARPS + warp;
   const bool nl = lane < NPE;
   uint64_t node1 = 0;
@@ -736,19 +756,18 @@ k_elem_elasticity(const double* __restrict__ xyz, const uint32_t* __restrict__ c
     double S[9], JxW, x, y, z;
     const bool affine = geom_phase<NPE, NQ>(X, s_tab, lane, false, flags, S, JxW, x, y, z);
     fw[lane] = lane < NQ ? JxW : 0.;
+    __syncwarp();
+    if (nl) {  // Fe (systems_of_equations_ex6.C:233-236): body force f_i, the same sum for every variable up to the factor
+      double m = 0.;
+      for (int q = 0; q < NQ; ++q) m += fw[q] * s_phi[lane * NQ + q];
+      mfe[lane] = m;
+    }
+    __syncwarp();
     double* out = kf + (uint64_t)(e - e0) * (ND * LDR);
-#ifdef FEASM_DEV_STORE_SAME  // development build: every element of a warp goes to one record (stays in L2; results are wrong)
-    out = kf + (uint64_t)(blockIdx.x * WARPS + warp) * (ND * LDR);
-#endif
-#ifdef FEASM_DEV_NOSTORE  // development build: how much of the kernel is the record stores?  (results are wrong)
-    const bool dev_store = lam1 == 12345.678;
-#else
-    constexpr bool dev_store = true;
-#endif
 
-    // P_dd' for one (d, d') pair -> tile[a*TLD + b]
-    // SYM (d == d'): P is symmetric, only the blocks on and above the diagonal go through DMMA and are mirrored
-    auto product = [&](int d, int dp, double* T, auto sym) {
+    // P_dd' for one (d, d') pair.  SYM (d == d'): only the blocks on and above the diagonal go through DMMA, and only
+    // the upper triangle is stored (packed); else the full tile Tl[a*TLD + b].
+    auto product = [&](int d, int dp, double* Tl, auto sym) {
       constexpr bool SYM = decltype(sym)::value;
       double acc[NBP][NBP][2];
 #pragma unroll
@@ -784,62 +803,77 @@ k_elem_elasticity(const double* __restrict__ xyz, const uint32_t* __restrict__ c
         for (int jb = 0; jb < NBP; ++jb) {
           if (SYM && ib > jb) continue;
           const int i = ib * 8 + g, j = jb * 8 + 2 * t4;
-          if (i < NPE && j < NPE) T[i * TLD + j] = acc[ib][jb][0];
-          if (i < NPE && j + 1 < NPE) T[i * TLD + j + 1] = acc[ib][jb][1];
-          if (SYM && ib < jb) {
-            if (i < NPE && j < NPE) T[j * TLD + i] = acc[ib][jb][0];
-            if (i < NPE && j + 1 < NPE) T[(j + 1) * TLD + i] = acc[ib][jb][1];
+          if (SYM && T::PACKED) {
+            if (i < NPE && j < NPE && i <= j) Tl[T::pk(i, j)] = acc[ib][jb][0];
+            if (i < NPE && j + 1 < NPE && i <= j + 1) Tl[T::pk(i, j + 1)] = acc[ib][jb][1];
+          } else if (SYM) {  // full tile: the block and its mirror image
+            if (i < NPE && j < NPE) { Tl[i * TLD + j] = acc[ib][jb][0]; Tl[j * TLD + i] = acc[ib][jb][0]; }
+            if (i < NPE && j + 1 < NPE) { Tl[i * TLD + j + 1] = acc[ib][jb][1]; Tl[(j + 1) * TLD + i] = acc[ib][jb][1]; }
+          } else {
+            if (i < NPE && j < NPE) Tl[i * TLD + j] = acc[ib][jb][0];
+            if (i < NPE && j + 1 < NPE) Tl[i * TLD + j + 1] = acc[ib][jb][1];
           }
         }
     };
-
-#define OUT_IDX(i, a, k, b) (((i) * NPE + (a)) * LDR + (k) * NPE + (b))
-    // diagonal variable blocks: K_dd = (l1 + l2) P_dd + l2 (P_00 + P_11 + P_22)
-    product(0, 0, tile, std::true_type{});
-    product(1, 1, tile + TILE, std::true_type{});
-    product(2, 2, tile + 2 * TILE, std::true_type{});
-    __syncwarp();
-    if (lane < NPE && dev_store) {
-#pragma unroll 3  // three rows in flight: the loop is a chain of shared-memory loads feeding stores, not issue bound
-      for (int a = 0; a < NPE; ++a) {
-        const double p0 = tile[a * TLD + lane], p1 = tile[TILE + a * TLD + lane], p2 = tile[2 * TILE + a * TLD + lane];
-        const double tr = lam2 * ((p0 + p1) + p2);
-        out[OUT_IDX(0, a, 0, lane)] = (lam1 + lam2) * p0 + tr;
-        out[OUT_IDX(1, a, 1, lane)] = (lam1 + lam2) * p1 + tr;
-        out[OUT_IDX(2, a, 2, lane)] = (lam1 + lam2) * p2 + tr;
-      }
-      // Fe (systems_of_equations_ex6.C:233-236): body force f_i, same for every variable up to the factor
-      double m = 0.;
-      for (int q = 0; q < NQ; ++q) m += fw[q] * s_phi[lane * NQ + q];
-      out[(0 * NPE + lane) * LDR + ND] = f0 * m;
-      out[(1 * NPE + lane) * LDR + ND] = f1 * m;
-      out[(2 * NPE + lane) * LDR + ND] = f2 * m;
-    }
-    __syncwarp();
-    // off-diagonal variable blocks: K_ik = l1 P_ik + l2 P_ik^T, K_ki = l2 P_ik + l1 P_ik^T   (i < k)
-#pragma unroll
-    for (int pair = 0; pair < 3; ++pair) {
-      const int i = pair == 2 ? 1 : 0, k = pair == 0 ? 1 : 2;
-      product(i, k, tile, std::false_type{});
-      __syncwarp();
-      if (lane < NPE && dev_store) {
+    // Emit the NPE record rows of variable block i in order.  Row (i, a), column block k, lane = b:
+    //   k == i:  (l1 + l2) P_ii[a][b] + l2 ((P_00 + P_11) + P_22)[a][b]
+    //   k >  i:  l1 P_ik[a][b] + l2 P_ik[b][a]            k < i:  l2 P_ki[a][b] + l1 P_ki[b][a]
+    // and Fe_(i,a) = f_i m_a behind the last block (lane NPE of the third store).  tk[k] = the tile that holds P_ik / P_ki.
+    auto emit = [&](auto iv, const double* t_a, const double* t_b) {
+      constexpr int i = decltype(iv)::value;
+      if (lane > NPE) return;
+      const int b = lane < NPE ? lane : 0;
+      const double fi = i == 0 ? f0 : (i == 1 ? f1 : f2);
 #pragma unroll 3
-        for (int a = 0; a < NPE; ++a) {
-          const double p = tile[a * TLD + lane], pt = tile[lane * TLD + a];
-          out[OUT_IDX(i, a, k, lane)] = lam1 * p + lam2 * pt;
-          out[OUT_IDX(k, a, i, lane)] = lam2 * p + lam1 * pt;
+      for (int a = 0; a < NPE; ++a) {
+        double* row = out + (size_t)(i * NPE + a) * LDR;
+        const int lo = a < b ? a : b, hi = a < b ? b : a;
+        const int pidx = T::PACKED ? T::pk(lo, hi) : a * TLD + b;
+        const double p0 = diag[pidx], p1 = diag[T::PK + pidx], p2 = diag[2 * T::PK + pidx];
+        const double tr = lam2 * ((p0 + p1) + p2);
+        const double pi_ = i == 0 ? p0 : (i == 1 ? p1 : p2);
+        int which = 0;
+#pragma unroll
+        for (int k = 0; k < 3; ++k) {
+          double v;
+          if (k == i) {
+            v = (lam1 + lam2) * pi_ + tr;
+          } else {
+            const double* Tl = which++ == 0 ? t_a : t_b;
+            const double p = Tl[a * TLD + b], pt = Tl[b * TLD + a];
+            v = i < k ? lam1 * p + lam2 * pt : lam2 * p + lam1 * pt;
+          }
+          if (lane < NPE) row[k * NPE + lane] = v;
+          else if (k == 2) row[ND] = fi * mfe[a];
         }
       }
-      __syncwarp();
-    }
+    };
+    double* t0 = off;
+    double* t1 = off + T::TILE;
+    product(0, 1, t0, std::false_type{});
+    product(0, 2, t1, std::false_type{});
+    product(0, 0, diag, std::true_type{});
+    product(1, 1, diag + T::PK, std::true_type{});
+    product(2, 2, diag + 2 * T::PK, std::true_type{});
+    __syncwarp();
+    emit(std::integral_constant<int, 0>{}, t0, t1);   // columns k = 1: P_01, k = 2: P_02
+    __syncwarp();
+    product(1, 2, t1, std::false_type{});
+    __syncwarp();
+    emit(std::integral_constant<int, 1>{}, t0, t1);   // k = 0: P_01 (transposed roles), k = 2: P_12
+    __syncwarp();
+    product(0, 2, t0, std::false_type{});
+    __syncwarp();
+    emit(std::integral_constant<int, 2>{}, t0, t1);   // k = 0: P_02, k = 1: P_12
+    __syncwarp();
   }
 }
 
 template <int NPE, int NQ, int WARPS>
 int launch_elasticity(feasm_ctx* ctx, const feasm_params& p, int64_t e0, int64_t e1, double* d_kf, int rs) {
   using C = ElemCfg<NPE, NQ>;
-  constexpr int NBP = (NPE + 7) / 8, TLD = NPE | 1, TILE = ((NPE * TLD + 1) & ~1);
-  const size_t smem = sizeof(double) * (size_t)(C::TAB_SZ + 3 * NBP * 8 * C::TS + WARPS * (C::X_SZ + 32 + 3 * TILE));
+  constexpr int NBP = (NPE + 7) / 8;
+  const size_t smem = sizeof(double) * (size_t)(C::TAB_SZ + 3 * NBP * 8 * C::TS + WARPS * ElastTiles<NPE>::PER_WARP);
   auto kern = k_elem_elasticity<NPE, NQ, WARPS>;
   FEASM_CUDA(ctx, cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
   // systems_of_equations_ex6.C:136-151
