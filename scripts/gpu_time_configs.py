@@ -45,6 +45,8 @@ res.append(time_case("2: Poisson HEX8 128^3, QGauss THIRD", F.HEX8, 128, F.POISS
 res.append(time_case("2b: Poisson HEX8 128^3, QGauss FIFTH (ex4-faithful)", F.HEX8, 128, F.POISSON, 5))
 res.append(time_case("3: Poisson HEX27 96^3 (one GPU)", F.HEX27, 96, F.POISSON, 0))
 res.append(time_case("4: Laplace TET10 32^3 cells x 24 tets", F.TET10, 32, F.POISSON, 5))
+res.append(time_case("f4: Poisson HEX20 96^3 (serendipity)", F.HEX20, 96, F.POISSON, 0))
+res.append(time_case("f4: elasticity HEX20 64^3", F.HEX20, 64, F.ELASTICITY, 0, n_vars=3, bounds=(0, 1, 0, 0.3, 0, 0.1), dirichlet=1 << 4))
 res.append(time_case("5: elasticity HEX27 64^3 (one GPU)", F.HEX27, 64, F.ELASTICITY, 0, n_vars=3, bounds=(0, 1, 0, 0.3, 0, 0.1), dirichlet=1 << 4))
 for r in res:
     r.pop("row_reduce_gbs")
