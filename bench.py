@@ -680,6 +680,13 @@ def run_multi(args, F, rank, world, local):
     io = torch.tensor([float(xyz_pin.nbytes + prob.con_rows.nbytes + prob.con_vals.nbytes),
                        float(nnz_owned * 8 + prob.n_owned * 8), float(len(da.send_slots) * 8), float(nnz_local)], device="cuda")
     dist.all_reduce(io)
+    # ---- the distributed matrix used on the device (feasm_halo.cu): SpMV with the halo exchange of x, and the CG solve ----
+    solve = None
+    if native:
+        try:
+            solve = multi_solve(F, ctx, da, prob, P, params, elast, torch, dist, stream)
+        except Exception as e:  # the assembly line above stays valid; the failure is reported in it
+            solve = {"error": f"{type(e).__name__}: {e}"}
     if rank == 0:
         nq = nq_of(args)
         nnz_g = int(io[3].item())  # includes ghost-row copies
@@ -705,6 +712,8 @@ def run_multi(args, F, rank, world, local):
         }
         if parity is not None:
             out["parity"] = parity
+        if solve is not None:
+            out["distributed_solve"] = solve
         fp64 = ctx.measure_fp64_peaks()
         pk = max(fp64["dmma_tflops"], fp64["dfma_tflops"])
         out["roofline"]["peak"], out["roofline"]["frac"] = pk, out["roofline"]["achieved"] / pk
@@ -713,6 +722,64 @@ def run_multi(args, F, rank, world, local):
     ctx.close()
     dist.barrier()
     dist.destroy_process_group()
+
+
+def multi_solve(F, ctx, da, prob, P, params, elast, torch, dist, stream):
+    """After the timed assembly: feasm_build_halo, then y = A x on the distributed matrix (halo exchange of x inside the
+    call; CUDA events on the library's stream, max over ranks) and, for the Poisson job, feasm_cg_solve over all ranks with
+    the nodal error against the exact ex4 solution.  Collective: every rank calls it."""
+    import ctypes as C
+
+    da.assemble(params, sync=True)  # the e2e leg left the last assembled system in place; make that explicit
+    t0 = time.perf_counter()
+    ctx.build_halo(prob.first_dof)
+    halo_s = time.perf_counter() - t0
+    peers, sp, _, rp, _ = ctx.halo_plan()
+    n = prob.n_owned
+    L = ctx.L
+    d_x, d_y = L.feasm_vec_alloc(ctx.h, n), L.feasm_vec_alloc(ctx.h, n)
+    xo = np.cos(0.37 * (prob.f0 + np.arange(n))) + 0.1
+    L.feasm_vec_copy(ctx.h, 0, C.c_void_p(d_x), xo.ctypes.data_as(C.c_void_p), n)
+    for _ in range(3):
+        ctx.vector_mult(d_x, d_y)
+    ctx.synchronize()
+    torch.cuda.synchronize()
+    dist.barrier()
+    ev0, ev1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    reps = 10
+    ev0.record(stream)
+    for _ in range(reps):
+        ctx.vector_mult(d_x, d_y)
+    ev1.record(stream)
+    ctx.synchronize()
+    torch.cuda.synchronize()
+    ms = torch.tensor([ev0.elapsed_time(ev1) / reps], device="cuda")
+    dist.all_reduce(ms, op=dist.ReduceOp.MAX)
+    y = np.empty(n)
+    L.feasm_vec_copy(ctx.h, 1, y.ctypes.data_as(C.c_void_p), C.c_void_p(d_y), n)
+    L.feasm_vec_free(ctx.h, C.c_void_p(d_x))
+    L.feasm_vec_free(ctx.h, C.c_void_p(d_y))
+    nnz_owned = int(da.row_ptr[n])
+    tot = torch.tensor([float(nnz_owned), float(int(rp[-1])), float(np.sum(y)), float(np.sum(np.abs(y)))], dtype=torch.float64, device="cuda")
+    dist.all_reduce(tot)
+    bytes_all = tot[0].item() * 12 + P["n_dofs"] * 24
+    out = {"halo_setup_s": round(halo_s, 3), "halo_entries_all_ranks": int(tot[1].item()),
+           "vector_mult": {"ms": float(ms.item()), "bytes_all_ranks": int(bytes_all), "gbs_all_ranks": bytes_all / (float(ms.item()) * 1e-3) / 1e9,
+                           "checksum_y": tot[2].item(), "checksum_abs_y": tot[3].item()}}
+    if not elast:
+        t0 = time.perf_counter()
+        u, its, rel = ctx.cg_solve(rel_tol=1e-10, max_its=4000)
+        t_s = time.perf_counter() - t0
+        node_of_dof = np.empty(P["n_dofs"], dtype=np.int64)
+        node_of_dof[P["node_base"].astype(np.int64)] = np.arange(len(P["node_base"]))
+        pts = P["xyz"][node_of_dof[prob.f0:prob.f0 + n]]
+        exact = np.cos(0.5 * np.pi * pts[:, 0]) * np.sin(0.5 * np.pi * pts[:, 1]) * np.cos(0.5 * np.pi * pts[:, 2])
+        err = torch.tensor([float(np.abs(u - exact).max()) if n else 0.0, t_s], dtype=torch.float64, device="cuda")
+        dist.all_reduce(err, op=dist.ReduceOp.MAX)
+        out["cg_solve"] = {"iterations": its, "rel_residual": rel, "seconds": float(err[1].item()),
+                           "max_nodal_error_vs_exact_solution": float(err[0].item()),
+                           "note": "Jacobi-preconditioned CG over all ranks: halo exchange of the direction per iteration, dot products finished by an all-gather added in rank order"}
+    return out
 
 
 def multi_parity(F, ctx, da, prob, P, local, params, torch, dist):

@@ -205,12 +205,16 @@ double* feasm_device_rhs(feasm_ctx* ctx);
 void* feasm_stream(feasm_ctx* ctx);                                    /* cudaStream_t */
 
 /* ---- the step after the path: SpMV and a Krylov solve on the device matrix ----- */
-/* SparseMatrix::vector_mult (sparse_matrix.h:579-587): y = A x, device pointers of n_rows doubles, on feasm_stream. */
+/* SparseMatrix::vector_mult (sparse_matrix.h:579-587): y = A x, device pointers of n_owned doubles (= n_rows on one rank),
+ * on feasm_stream.  On several ranks (feasm_build_halo below) x and y are the owned parts of distributed vectors and the
+ * call fetches the entries of x other ranks own before the product. */
 int feasm_vector_mult(feasm_ctx* ctx, const double* d_x, double* d_y);
 int feasm_vector_mult_host(feasm_ctx* ctx, const double* x, double* y); /* same with host arrays (H2D, product, D2H) */
 /* LinearSolver::solve with CG + Jacobi preconditioning on the assembled system A x = rhs.  x0 (host, may be NULL =
  * zero) is the initial guess, x (host) receives the solution; stops at ||r|| <= rel_tol ||b|| or max_its.  Returns
- * FEASM_OK (converged), FEASM_NOT_CONVERGED (max_its reached; outputs valid) or FEASM_ERR_BREAKDOWN. */
+ * FEASM_OK (converged), FEASM_NOT_CONVERGED (max_its reached; outputs valid) or FEASM_ERR_BREAKDOWN.  On several ranks
+ * (collective; communicator + feasm_build_halo) x0 / x are the owned parts, every dot product is finished by an all-gather
+ * of the ranks' partial sums added in rank order, and all ranks return the same iteration count and residual. */
 int feasm_cg_solve(feasm_ctx* ctx, double rel_tol, int max_its, const double* x0, double* x, int* iterations,
                    double* rel_residual);
 
@@ -219,7 +223,10 @@ int feasm_cg_solve(feasm_ctx* ctx, double rel_tol, int max_its, const double* x0
  * work of NonlinearImplicitSystem::ComputeResidual::residual(X, R, S) (include/systems/nonlinear_implicit_system.h:
  * 90-101) / FEMSystem::assembly(get_residual = true, get_jacobian = false) (src/systems/fem_system.C:875) for the
  * linear problems of this library: no CSR values are written or read.  d_u, d_r: device vectors of n_rows entries
- * (feasm_vec_alloc).  Runs the element phase, then one row-parallel pass over the element records.  One rank. */
+ * (feasm_vec_alloc; on several ranks the owned parts, n_owned entries).  Runs the element phase, then one row-parallel
+ * pass over the element records.  On several ranks (collective; communicator + feasm_build_halo) the ghost entries of u come
+ * from their owners first and the sums of the ghost rows go to their owners, who add them peer by peer in the fixed order
+ * of the assembly's exchange plan (DistributedVector::close, distributed_vector.C:399-470). */
 int feasm_residual(feasm_ctx* ctx, const feasm_params* params, const double* d_u, double* d_r);
 
 /* ---- device vectors: what a NumericVector back-end needs (numeric_vector.h:119-847; shim/gpu_numeric_vector.h) -- */
@@ -320,6 +327,34 @@ int feasm_apply_plan(feasm_ctx* ctx, const feasm_planner* p);
  * are copied out when non-NULL */
 int feasm_get_exchange_plan(feasm_ctx* ctx, int32_t* peers, uint64_t* send_ptr, uint64_t* send_slots, uint64_t* recv_ptr,
                             uint64_t* recv_slots);
+
+/* ---- the assembled matrix of several ranks used on the device: the halo of a distributed vector ---------------------------
+ * The owned rows hold GLOBAL column ids, so y = A x needs the entries of x that other ranks own: what
+ * NumericVector::localize(v_local, send_list) (numeric_vector.h:478-487; DistributedVector::localize,
+ * src/numerics/distributed_vector.C:474-560) fetches with the DofMap's send_list.  The library keeps a column-space copy of x
+ * of global length (n_global doubles) per context: owned part copied, ghost entries scattered in.
+ *   feasm_build_halo     : collective over the context's communicator, after the final pattern (feasm_build_exchange):
+ *                          finds the needed columns on the device (columns of the owned rows outside the owned range, plus
+ *                          the ids of the ghost rows for feasm_residual), asks their owners once.  Afterwards
+ *                          feasm_vector_mult, feasm_cg_solve and feasm_residual work on the distributed system.
+ *   feasm_halo_columns   : the needed global ids, ascending (returns the count; gids may be NULL) — for hosts that carry
+ *                          the request lists themselves (libMesh: the send_list is exactly this set) ...
+ *   feasm_set_halo_plan  : ... and hand the routes in: per peer the owned local rows it needs (send_rows) and the global
+ *                          ids this rank receives from it (recv_gids), in the order of the peer's request.
+ *   feasm_halo_pack / _recv_buffer / _unpack : the per-product exchange in pieces for such hosts: pack x's requested
+ *                          entries (returns the send buffer, peer-major), the host moves the segments into the peers'
+ *                          receive buffers, unpack scatters them into the column-space copy; feasm_vector_mult without
+ *                          a communicator then uses that copy (and refreshes the owned part itself).
+ *   feasm_get_halo_plan  : the plan the context holds (returns the number of peers). */
+int feasm_build_halo(feasm_ctx* ctx, const uint64_t* first_dof);
+int64_t feasm_halo_columns(feasm_ctx* ctx, uint64_t n_global, uint64_t first, uint32_t* gids);
+int feasm_set_halo_plan(feasm_ctx* ctx, uint64_t n_global, uint64_t first, int n_peers, const int32_t* peer_rank,
+                        const uint64_t* send_ptr, const uint32_t* send_rows, const uint64_t* recv_ptr, const uint32_t* recv_gids);
+double* feasm_halo_pack(feasm_ctx* ctx, const double* d_x, uint64_t* n_doubles);
+double* feasm_halo_recv_buffer(feasm_ctx* ctx, uint64_t* n_doubles);
+int feasm_halo_unpack(feasm_ctx* ctx);
+int feasm_get_halo_plan(feasm_ctx* ctx, int32_t* peers, uint64_t* send_ptr, uint32_t* send_rows, uint64_t* recv_ptr,
+                        uint32_t* recv_gids);
 
 /* ---- host-side generators for stand-alone runs (no libMesh present) ---------------------------- */
 /* MeshTools::Generation::build_cube (src/mesh/mesh_generation.C:317-1937) for HEX8/HEX27/TET10: fills caller arrays.

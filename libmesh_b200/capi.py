@@ -23,6 +23,8 @@ PENALTY_CONSTANT, PENALTY_EX4_EXACT = 0, 1
 
 # every symbol include/feasm.h declares (tests check the library exports each of them)
 SYMBOLS = [
+    "feasm_build_halo", "feasm_halo_columns", "feasm_set_halo_plan", "feasm_halo_pack", "feasm_halo_recv_buffer",
+    "feasm_halo_unpack", "feasm_get_halo_plan",
     "feasm_create", "feasm_destroy", "feasm_last_error", "feasm_version", "feasm_set_mesh",
     "feasm_update_coordinates", "feasm_set_dofs", "feasm_set_constraints", "feasm_set_pattern",
     "feasm_build_pattern", "feasm_nnz", "feasm_get_pattern", "feasm_prepare", "feasm_assemble",
@@ -148,6 +150,13 @@ def lib():
         "feasm_get_constraints": (i32, [vp, vp, vp]),
         "feasm_set_side_penalty": (i32, [vp, i64, vp, vp, C.c_double, i32, C.c_double]),
         "feasm_residual": (i32, [vp, C.POINTER(Params), vp, vp]),
+        "feasm_build_halo": (i32, [vp, vp]),
+        "feasm_halo_columns": (i64, [vp, C.c_uint64, C.c_uint64, vp]),
+        "feasm_set_halo_plan": (i32, [vp, C.c_uint64, C.c_uint64, i32, vp, vp, vp, vp, vp]),
+        "feasm_halo_pack": (vp, [vp, vp, C.POINTER(C.c_uint64)]),
+        "feasm_halo_recv_buffer": (vp, [vp, C.POINTER(C.c_uint64)]),
+        "feasm_halo_unpack": (i32, [vp]),
+        "feasm_get_halo_plan": (i32, [vp, vp, vp, vp, vp, vp]),
     }
     for name, (res, args) in sig.items():
         fn = getattr(L, name)
@@ -233,6 +242,7 @@ class Context:
             raise FeasmError(rc, self.L.feasm_last_error(None).decode())
         self.h = h
         self.n_rows = 0
+        self.n_owned = 0
         self.nd = 0
         self.n_elem = 0
         self.has_comm = False
@@ -263,6 +273,7 @@ class Context:
         ed = _c(elem_dofs, np.uint32)
         gid = _c(global_ids, np.uint32)
         self.n_rows, self.nd = int(n_rows), ed.shape[1]
+        self.n_owned = int(n_rows if n_owned is None else n_owned)
         self._ck(self.L.feasm_set_dofs(self.h, n_vars, n_rows, n_rows if n_owned is None else n_owned, _p(ed), _p(gid)))
 
     # ---- device-side ingest (no host arrays): build_cube, distribute_dofs + dof_indices, DirichletBoundary ----
@@ -278,6 +289,7 @@ class Context:
         if n < 0:
             self._ck(n)
         self.n_rows, self.nd, self.n_vars = n, self.elem_type * n_vars, n_vars
+        self.n_owned = n
         return n
 
     def generate_dirichlet(self, id_mask=0x3f, kind=1, var_mask=0xff):
@@ -400,6 +412,7 @@ class Context:
         n = len(rp) - 1
         self._ck(self.L.feasm_init_matrix(self.h, n, n if n_owned is None else n_owned, _p(rp), _p(ci)))
         self.n_rows = n
+        self.n_owned = int(n if n_owned is None else n_owned)
 
     def set_values(self, values=None, rhs=None):
         v, b = _c(values, np.float64), _c(rhs, np.float64)
@@ -438,12 +451,12 @@ class Context:
         return [ms[0], ms[1], ms[2], ms[3]], n.value
 
     def vector_mult(self, d_x, d_y):
-        """y = A x with device pointers (ints) of n_rows doubles."""
+        """y = A x with device pointers (ints) of n_owned doubles (= n_rows on one rank)."""
         self._ck(self.L.feasm_vector_mult(self.h, C.c_void_p(d_x), C.c_void_p(d_y)))
 
     def residual_host(self, params, u):
-        """R = K(u) u - F from the element records (feasm_residual), host arrays in and out."""
-        L, n = self.L, self.n_rows
+        """R = K(u) u - F from the element records (feasm_residual), host arrays in and out (several ranks: owned parts)."""
+        L, n = self.L, self.n_owned
         uc = _c(u, np.float64)
         out = np.empty(n, np.float64)
         d_u, d_r = L.feasm_vec_alloc(self.h, n), L.feasm_vec_alloc(self.h, n)
@@ -458,12 +471,12 @@ class Context:
 
     def vector_mult_host(self, x):
         xc = _c(x, np.float64)
-        y = np.empty(self.n_rows, np.float64)
+        y = np.empty(self.n_owned, np.float64)
         self._ck(self.L.feasm_vector_mult_host(self.h, _p(xc), _p(y)))
         return y
 
     def cg_solve(self, rel_tol=1e-12, max_its=10000, x0=None):
-        x = np.empty(self.n_rows, np.float64)
+        x = np.empty(self.n_owned, np.float64)
         x0c = _c(x0, np.float64)
         its, rel = C.c_int(), C.c_double()
         rc = self.L.feasm_cg_solve(self.h, rel_tol, max_its, _p(x0c), _p(x), C.byref(its), C.byref(rel))
@@ -518,6 +531,56 @@ class Context:
         if len(fd) != self.comm_size + 1:
             raise FeasmError(-1, "first_dof must have n_ranks + 1 entries")
         self._ck(self.L.feasm_build_exchange(self.h, _p(fd)))
+
+    # -- the halo of a distributed vector (feasm_halo.cu) ------------------------------------------------------------------
+    def build_halo(self, first_dof):
+        """Collective (feasm_build_halo): after it vector_mult / cg_solve / residual work on the distributed system."""
+        fd = _c(first_dof, np.uint64)
+        if len(fd) != self.comm_size + 1:
+            raise FeasmError(-1, "first_dof must have n_ranks + 1 entries")
+        self._ck(self.L.feasm_build_halo(self.h, _p(fd)))
+
+    def halo_columns(self, n_global, first):
+        n = int(self.L.feasm_halo_columns(self.h, int(n_global), int(first), None))
+        if n < 0:
+            self._ck(n)
+        out = np.zeros(n, dtype=np.uint32)
+        if n:
+            self.L.feasm_halo_columns(self.h, int(n_global), int(first), _p(out))
+        return out
+
+    def set_halo_plan(self, n_global, first, peers, send_ptr, send_rows, recv_ptr, recv_gids):
+        pr = _c(peers, np.int32)
+        sp, sr = _c(send_ptr, np.uint64), _c(send_rows, np.uint32)
+        rp, rg = _c(recv_ptr, np.uint64), _c(recv_gids, np.uint32)
+        self._ck(self.L.feasm_set_halo_plan(self.h, int(n_global), int(first), len(pr), _p(pr), _p(sp), _p(sr), _p(rp), _p(rg)))
+
+    def halo_pack(self, d_x):
+        n = C.c_uint64()
+        ptr = self.L.feasm_halo_pack(self.h, C.c_void_p(d_x), C.byref(n))
+        if not ptr:
+            raise FeasmError(-3, "no halo plan")
+        return ptr, n.value
+
+    def halo_recv_buffer(self):
+        n = C.c_uint64()
+        ptr = self.L.feasm_halo_recv_buffer(self.h, C.byref(n))
+        if not ptr:
+            raise FeasmError(-3, "no halo plan")
+        return ptr, n.value
+
+    def halo_unpack(self):
+        self._ck(self.L.feasm_halo_unpack(self.h))
+
+    def halo_plan(self):
+        n = int(self.L.feasm_get_halo_plan(self.h, None, None, None, None, None))
+        if n < 0:
+            self._ck(n)
+        peers, sp, rp = np.zeros(n, dtype=np.int32), np.zeros(n + 1, dtype=np.uint64), np.zeros(n + 1, dtype=np.uint64)
+        self.L.feasm_get_halo_plan(self.h, _p(peers), _p(sp), None, _p(rp), None)
+        sr, rg = np.zeros(int(sp[-1]), dtype=np.uint32), np.zeros(int(rp[-1]), dtype=np.uint32)
+        self.L.feasm_get_halo_plan(self.h, None, None, _p(sr), None, _p(rg))
+        return peers, sp, sr, rp, rg
 
     def apply_plan(self, planner):
         self._ck(self.L.feasm_apply_plan(self.h, planner.h))

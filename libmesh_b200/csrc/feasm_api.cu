@@ -140,6 +140,7 @@ void feasm_destroy(feasm_ctx* ctx) {
   cudaStreamSynchronize(ctx->stream);
   feasm_comm_release(ctx);
   feasm_general_release(ctx);
+  feasm_halo_release(ctx);
   drop_maps(ctx);
   release(ctx->d_xyz); release(ctx->d_conn); release(ctx->d_elem_dofs); release(ctx->d_gid);
   release(ctx->d_node_mask); release(ctx->d_node_base);
@@ -218,6 +219,7 @@ void feasm_reset_mesh(feasm_ctx* ctx, int elem_type, int64_t n_elem, int64_t n_n
 int feasm_reset_dofs(feasm_ctx* ctx, int n_vars, int64_t n_rows, int64_t n_owned) {
   drop_maps(ctx);
   feasm_general_release(ctx);  // constraint rows name dofs of the previous numbering
+  feasm_halo_release(ctx);     // the halo plan belongs to the previous pattern
   // the pattern, the values and the exchange plan belong to the previous dof set: feasm_prepare / feasm_assemble return
   // FEASM_ERR_STATE until feasm_set_pattern / feasm_build_pattern is called again
   release(ctx->d_row_ptr); release(ctx->d_col_idx); release(ctx->d_values);
@@ -312,6 +314,7 @@ int feasm_set_pattern(feasm_ctx* ctx, const uint64_t* row_ptr, const uint32_t* c
   }
   ctx->prepared = false;
   feasm_general_invalidate_plan(ctx);
+  feasm_halo_release(ctx);
   ctx->nnz = row_ptr[ctx->n_rows];
   int rc = upload(ctx, &ctx->d_row_ptr, row_ptr, (size_t)ctx->n_rows + 1);
   if (rc) return rc;
@@ -328,6 +331,7 @@ int feasm_build_pattern(feasm_ctx* ctx) {
   FEASM_CUDA(ctx, cudaSetDevice(ctx->device));
   ctx->prepared = false;
   feasm_general_invalidate_plan(ctx);
+  feasm_halo_release(ctx);
   int rc = feasm_device_build_pattern(ctx);
   if (rc) return rc;
   rc = alloc_values(ctx);
@@ -435,7 +439,8 @@ int feasm_residual(feasm_ctx* ctx, const feasm_params* params, const double* d_u
   if (!ctx || !params) return FEASM_ERR_ARG;
   if (ctx && feasm_general_active(ctx)) return feasm_fail(ctx, FEASM_ERR_STATE, "feasm_residual: not with general constraint rows (feasm_set_constraint_rows) in this version");
   if (!d_u || !d_r) return feasm_fail(ctx, FEASM_ERR_ARG, "null vector");
-  if (ctx->d_gid || ctx->n_owned != ctx->n_rows) return feasm_fail(ctx, FEASM_ERR_STATE, "residual: one rank per system in this version");
+  const bool several = feasm_is_distributed(ctx);
+  if (several && !feasm_halo_ready(ctx)) return feasm_fail(ctx, FEASM_ERR_STATE, "feasm_residual on several ranks: feasm_build_halo first");
   FEASM_CUDA(ctx, cudaSetDevice(ctx->device));
   int rc = feasm_prepare(ctx);
   if (rc) return rc;
@@ -451,6 +456,7 @@ int feasm_residual(feasm_ctx* ctx, const feasm_params* params, const double* d_u
   const int rs = feasm_recb(ctx->nd, ctx->pos_bytes) / 8;
   rc = feasm_launch_element_kernel(ctx, *params, d_f, 0, ctx->n_elem, ctx->d_kf, rs, params->constrain);
   if (rc) return rc;
+  if (several) return feasm_residual_distributed(ctx, d_u, d_r);  // ghost entries of u in, ghost-row sums out
   return feasm_launch_row_residual(ctx, d_u, d_r);
 }
 
@@ -642,6 +648,7 @@ int feasm_set_exchange_plan(feasm_ctx* ctx, int n_peers, const int32_t* peer_ran
                             const uint64_t* send_slots, const uint64_t* recv_ptr, const uint64_t* recv_slots) {
   if (!ctx || !ctx->d_values) return feasm_fail(ctx, FEASM_ERR_STATE, "no matrix");
   if (n_peers < 0 || (n_peers && (!peer_rank || !send_ptr || !recv_ptr))) return feasm_fail(ctx, FEASM_ERR_ARG, "bad plan");
+  feasm_halo_release(ctx);  // its vector routes are derived from this plan
   ctx->n_peers = n_peers;
   ctx->peer_rank.assign(peer_rank, peer_rank + n_peers);
   ctx->send_ptr.assign(send_ptr, send_ptr + n_peers + 1);

@@ -94,6 +94,36 @@ void feasm_comm_release(feasm_ctx* ctx) {
   }
 }
 
+// Grouped point-to-point exchange with the peers of a plan on `stream` (elem_bytes 4: uint32 words, 8: doubles): the
+// building block of the halo exchange of a distributed vector (feasm_halo.cu).
+int feasm_comm_p2p(feasm_ctx* ctx, int n_peers, const int32_t* peer, const uint64_t* send_ptr, const void* d_send,
+                   const uint64_t* recv_ptr, void* d_recv, int elem_bytes, cudaStream_t stream) {
+  if (!ctx->comm) return feasm_fail(ctx, FEASM_ERR_STATE, "no communicator: feasm_comm_init / feasm_set_communicator first");
+  NcclApi* a = nccl_api();
+  ncclComm_t comm = static_cast<ncclComm_t>(ctx->comm);
+  const ncclDataType_t dt = elem_bytes == 8 ? ncclDouble : ncclUint32;
+  FEASM_NCCL(ctx, a, a->GroupStart());
+  for (int p = 0; p < n_peers; ++p) {
+    const uint64_t r0 = recv_ptr[p], nr = recv_ptr[p + 1] - r0;
+    if (nr) FEASM_NCCL(ctx, a, a->Recv(static_cast<char*>(d_recv) + r0 * elem_bytes, nr, dt, peer[p], comm, stream));
+  }
+  for (int p = 0; p < n_peers; ++p) {
+    const uint64_t s0 = send_ptr[p], ns = send_ptr[p + 1] - s0;
+    if (ns) FEASM_NCCL(ctx, a, a->Send(static_cast<const char*>(d_send) + s0 * elem_bytes, ns, dt, peer[p], comm, stream));
+  }
+  FEASM_NCCL(ctx, a, a->GroupEnd());
+  return FEASM_OK;
+}
+
+// n doubles from every rank to every rank, in rank order, device to device on `stream`: the partial sums of a distributed
+// dot product, which every rank then adds in the same fixed order (feasm_solve.cu).
+int feasm_comm_allgather_f64(feasm_ctx* ctx, const double* d_send, double* d_recv, int n, cudaStream_t stream) {
+  if (!ctx->comm) return feasm_fail(ctx, FEASM_ERR_STATE, "no communicator");
+  NcclApi* a = nccl_api();
+  FEASM_NCCL(ctx, a, a->AllGather(d_send, d_recv, (size_t)n, ncclDouble, static_cast<ncclComm_t>(ctx->comm), stream));
+  return FEASM_OK;
+}
+
 extern "C" {
 
 int feasm_comm_unique_id(void* id_bytes) {

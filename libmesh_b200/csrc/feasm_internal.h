@@ -51,6 +51,7 @@ FEASM_HD constexpr int feasm_pld(int nd, int pos_bytes) { return (((nd + 2) * po
 FEASM_HD constexpr int feasm_recb(int nd, int pos_bytes) { return feasm_ldr(nd) * 8 + feasm_pld(nd, pos_bytes) * pos_bytes; }
 
 struct feasm_general;  // feasm_general.cu: general (non-Dirichlet) constraint rows
+struct feasm_halo;     // feasm_halo.cu: column-space copy of a distributed vector (product / solve / residual on several ranks)
 
 struct feasm_ctx {
   int device = 0;
@@ -167,6 +168,7 @@ struct feasm_ctx {
   bool matrix_only = false;  // feasm_init_matrix: pattern + values without a mesh
 
   feasm_general* gen = nullptr;  // elements widened by hanging-node constraints (feasm_set_constraint_rows)
+  feasm_halo* halo = nullptr;    // feasm_build_halo / feasm_set_halo_plan
 
   float last_ms[4] = {0, 0, 0, 0};
   int last_launches = 0;
@@ -249,6 +251,21 @@ int feasm_general_transform(feasm_ctx* ctx, int rs, int constrain_mode);    // a
 int feasm_general_add(feasm_ctx* ctx);                                      // after the row reduction
 // feasm_comm.cu: destroys an owned communicator and the communication stream
 void feasm_comm_release(feasm_ctx* ctx);
+int feasm_comm_p2p(feasm_ctx* ctx, int n_peers, const int32_t* peer, const uint64_t* send_ptr, const void* d_send,
+                   const uint64_t* recv_ptr, void* d_recv, int elem_bytes, cudaStream_t stream);
+int feasm_comm_allgather_f64(feasm_ctx* ctx, const double* d_send, double* d_recv, int n, cudaStream_t stream);
+// feasm_halo.cu: a matrix whose rows are spread over several ranks (global column ids, owned rows first)
+void feasm_halo_release(feasm_ctx* ctx);
+bool feasm_halo_ready(const feasm_ctx* ctx);  // a halo plan is set
+inline bool feasm_is_distributed(const feasm_ctx* ctx) { return ctx->d_gid || ctx->n_owned != ctx->n_rows || feasm_halo_ready(ctx); }
+// the column-space copy of the distributed vector whose owned part is d_x (n_owned doubles), current on ctx->stream when
+// the call returns: owned part copied, ghost entries fetched from their owners (NCCL) — or, without a communicator, left as
+// the caller's own feasm_halo_pack / transfer / feasm_halo_unpack made them
+int feasm_halo_exchange(feasm_ctx* ctx, const double* d_x, const double** d_xfull);
+uint32_t feasm_halo_first(const feasm_ctx* ctx);  // global id of local row 0 (0 without a halo plan)
+int feasm_residual_distributed(feasm_ctx* ctx, const double* d_u, double* d_r);
+// feasm_solve.cu: y[0..n_rows_used) = A x with x indexed by the matrix's column ids
+int feasm_spmv_rows(feasm_ctx* ctx, int64_t n_rows_used, const double* d_x, double* d_y);
 // mode 0: add, 1: set
 int feasm_launch_add_matrix(feasm_ctx* ctx, const double* d_dm, const uint32_t* d_rows, int nr, const uint32_t* d_cols,
                             int nc, int mode = 0);

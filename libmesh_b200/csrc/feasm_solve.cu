@@ -7,7 +7,10 @@
 //                        src/solvers/: the default Krylov route of the library back-ends)
 //
 // Everything is deterministic: the SpMV sums a row in column order by one warp with a fixed shuffle tree, the dot
-// products use a fixed two-level reduction (no atomics).  Single rank (column ids = local row ids).
+// products use a fixed two-level reduction (no atomics).  On several ranks (rows spread over the ranks, global column ids;
+// feasm_halo.cu) the product first fetches the ghost entries of x from their owners, and every dot product is finished by
+// an all-gather of the ranks' partial sums that every rank adds in rank order — so all ranks hold bitwise the same scalars
+// and the iterates do not depend on how NCCL would have ordered a reduction.
 #include <cmath>
 #include <cstdlib>
 #include <vector>
@@ -100,12 +103,82 @@ k_spmv_pipe(const uint64_t* __restrict__ row_ptr, const uint32_t* __restrict__ c
   }
 }
 
+// The same product as a STREAM over the non-zeros: a warp owns 32 consecutive rows = one contiguous run of the value and
+// column arrays (2000 entries on average at HEX27), which all 32 lanes read fully coalesced whatever the row lengths are
+// (one-warp-per-row leaves 3/4 of its load slots empty on a 27-entry row), multiply with the gathered x and park in shared
+// memory, CH entries at a time; then lane i adds up the entries of row r0 + i left to right.  Rows of FE matrices have odd
+// lengths (27, 45, 75, 125), so the lanes' walks through the buffer fall into different banks.  The sum of a row is the
+// plain left-to-right sum of its entries in column order (deterministic; not the order of k_spmv's strided partial sums).
+template <int WARPS, int CH>
+__global__ void __launch_bounds__(WARPS * 32)
+k_spmv_stream(const uint64_t* __restrict__ row_ptr, const uint32_t* __restrict__ col_idx, const double* __restrict__ values,
+              const double* __restrict__ x, int64_t n_rows, double* __restrict__ y) {
+  static_assert(CH % 128 == 0, "a 128-entry block never straddles two chunks");
+  __shared__ double s_prod[WARPS][CH];
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  double* prod = s_prod[warp];
+  const int64_t n_batches = (n_rows + 31) >> 5, stride = (int64_t)gridDim.x * WARPS;
+  int64_t b = (int64_t)blockIdx.x * WARPS + warp;
+  if (b >= n_batches) return;
+  auto row_bounds = [&](int64_t bb, uint64_t& rs, uint64_t& re) {
+    const int64_t r = bb * 32 + lane;
+    rs = row_ptr[r < n_rows ? r : n_rows];
+    re = row_ptr[r + 1 < n_rows ? r + 1 : n_rows];
+  };
+  uint64_t rs, re, rs_n = 0, re_n = 0;
+  row_bounds(b, rs, re);
+  for (; b < n_batches; b += stride) {
+    if (b + stride < n_batches) row_bounds(b + stride, rs_n, re_n);  // the next batch's row pointers travel under this batch
+    const uint64_t p0 = __shfl_sync(0xffffffffu, rs, 0), p1 = __shfl_sync(0xffffffffu, re, 31);
+    auto load = [&](uint64_t k0, double (&v)[4], uint32_t (&c)[4]) {
+#pragma unroll
+      for (int u = 0; u < 4; ++u) {
+        const uint64_t k = k0 + lane + 32 * u;
+        const bool ok = k < p1;
+        v[u] = ok ? __ldcs(values + k) : 0.;
+        c[u] = ok ? __ldcs(col_idx + k) : 0u;
+      }
+    };
+    // two blocks of 128 entries in flight per warp: the (value, column) loads of block j+1 and the x gather of block j;
+    // the first block of the next chunk is loaded before this chunk's rows are added up
+    double v[4];
+    uint32_t c[4];
+    load(p0, v, c);
+    double acc = 0.;
+    for (uint64_t c0 = p0; c0 < p1; c0 += CH) {
+      const uint64_t c1 = c0 + CH < p1 ? c0 + CH : p1;
+      for (uint64_t k0 = c0; k0 < c1; k0 += 128) {
+        double vn[4];
+        uint32_t cn[4];
+        load(k0 + 128, vn, cn);
+        double xv[4];
+#pragma unroll
+        for (int u = 0; u < 4; ++u) xv[u] = x[c[u]];  // (lanes past the end read x[0]; their product is not stored)
+#pragma unroll
+        for (int u = 0; u < 4; ++u) {
+          const uint64_t k = k0 + lane + 32 * u;
+          if (k < c1) prod[k - c0] = v[u] * xv[u];
+        }
+#pragma unroll
+        for (int u = 0; u < 4; ++u) { v[u] = vn[u]; c[u] = cn[u]; }
+      }
+      __syncwarp();
+      const uint64_t lo = rs > c0 ? rs : c0, hi = re < c1 ? re : c1;
+      for (uint64_t k = lo; k < hi; ++k) acc += prod[k - c0];
+      __syncwarp();
+    }
+    const int64_t r = b * 32 + lane;
+    if (r < n_rows) y[r] = acc;
+    rs = rs_n; re = re_n;
+  }
+}
+
 // 1 / A(r,r) (binary search of the diagonal in the sorted row); rows without a diagonal entry get 1.
 __global__ void k_inv_diag(const uint64_t* __restrict__ row_ptr, const uint32_t* __restrict__ col_idx, const double* __restrict__ values,
-                           const uint32_t* __restrict__ gid, int64_t n_rows, double* __restrict__ dinv) {
+                           const uint32_t* __restrict__ gid, uint32_t first, int64_t n_rows, double* __restrict__ dinv) {
   const int64_t r = blockIdx.x * (int64_t)blockDim.x + threadIdx.x;
   if (r >= n_rows) return;
-  const uint32_t col = gid ? gid[r] : (uint32_t)r;
+  const uint32_t col = gid ? gid[r] : first + (uint32_t)r;
   const uint32_t* c = col_idx + row_ptr[r];
   int lo = 0, hi = (int)(row_ptr[r + 1] - row_ptr[r]);
   const int len = hi;
@@ -148,6 +221,15 @@ __global__ void k_dot_final(const double* __restrict__ partial, int n, double* _
   for (int i = threadIdx.x; i < n; i += blockDim.x) s += partial[i];
   s = block_sum(s, sh);
   if (threadIdx.x == 0) *out = s;
+}
+
+// s[j] = sum over the ranks q = 0, 1, ... of gathered[q * cnt + j], in rank order (every rank computes the same bits)
+__global__ void k_rank_sum(const double* __restrict__ gathered, int world, int cnt, double* __restrict__ s) {
+  const int j = threadIdx.x;
+  if (j >= cnt) return;
+  double t = 0.;
+  for (int q = 0; q < world; ++q) t += gathered[q * cnt + j];
+  s[j] = t;
 }
 
 // x += alpha p; r -= alpha q; z = dinv .* r     (alpha = rz / pq read from device scalars)
@@ -234,19 +316,36 @@ __global__ void k_vec_reduce(int op, const double* __restrict__ x, int64_t n, do
 }
 __global__ void k_vec_set_one(double* __restrict__ y, int64_t i, double v, int add) { y[i] = add ? y[i] + v : v; }
 
-int spmv(feasm_ctx* ctx, const double* d_x, double* d_y) {
-  static const bool pipe = !(getenv("FEASM_SPMV_PIPE") && atoi(getenv("FEASM_SPMV_PIPE")) == 0);  // A/B knob: 0 = one row at a time
-  const int64_t want = (ctx->n_rows * 32 + 255) / 256;
+int spmv(feasm_ctx* ctx, int64_t n_rows, const double* d_x, double* d_y) {
+  const bool pipe = !(getenv("FEASM_SPMV_PIPE") && atoi(getenv("FEASM_SPMV_PIPE")) == 0);  // A/B knob: 0 = one row at a time
+  const int stream_mode = getenv("FEASM_SPMV_STREAM") ? atoi(getenv("FEASM_SPMV_STREAM")) : 0;  // A/B knob: the stream kernel
+  if (stream_mode && n_rows) {
+    constexpr int W = 8;
+    static int per_sm = 0, per_sm_b = 0;
+    if (!per_sm && (cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, k_spmv_stream<W, 512>, W * 32, 0) != cudaSuccess || per_sm < 1)) per_sm = 2;
+    if (!per_sm_b && (cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm_b, k_spmv_stream<W, 768>, W * 32, 0) != cudaSuccess || per_sm_b < 1)) per_sm_b = 2;
+    const int64_t want_b = ((n_rows + 31) / 32 + W - 1) / W;
+    if (stream_mode == 3) {  // longer chunks, fewer resident CTAs
+      const int64_t cap = (int64_t)ctx->sm_count * per_sm_b;
+      k_spmv_stream<W, 768><<<(unsigned)(want_b < cap ? want_b : cap), W * 32, 0, ctx->stream>>>(ctx->d_row_ptr, ctx->d_col_idx, ctx->d_values, d_x, n_rows, d_y);
+    } else {  // 1: persistent, one wave; 2: one batch per warp
+      const int64_t cap = (int64_t)ctx->sm_count * per_sm;
+      k_spmv_stream<W, 512><<<(unsigned)(stream_mode == 2 || want_b < cap ? want_b : cap), W * 32, 0, ctx->stream>>>(ctx->d_row_ptr, ctx->d_col_idx, ctx->d_values, d_x, n_rows, d_y);
+    }
+    FEASM_CUDA(ctx, cudaGetLastError());
+    return FEASM_OK;
+  }
+  const int64_t want = (n_rows * 32 + 255) / 256;
   // long rows (several variables per node: 375 entries at 3 x HEX27) already keep enough bytes in flight per warp and lose
   // to the pipeline's extra registers (measured: 5.6 vs 4.6 TB/s at 3 x 48^3); short rows gain 3-8 %
-  if (pipe && ctx->nnz <= (uint64_t)ctx->n_rows * 160) {
+  if (pipe && ctx->nnz <= (uint64_t)ctx->n_rows * 160) {  // (the average over owned and ghost rows: the same element type)
     static int per_sm = 0;  // resident CTAs per SM (registers decide: 4 at 54 registers): the persistent grid is one wave
     if (!per_sm && (cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, k_spmv_pipe, 256, 0) != cudaSuccess || per_sm < 1)) per_sm = 4;
     const int64_t cap = (int64_t)ctx->sm_count * per_sm;
     const unsigned grid = (unsigned)(want < cap ? want : cap);
-    if (grid) k_spmv_pipe<<<grid, 256, 0, ctx->stream>>>(ctx->d_row_ptr, ctx->d_col_idx, ctx->d_values, d_x, ctx->n_rows, d_y);
+    if (grid) k_spmv_pipe<<<grid, 256, 0, ctx->stream>>>(ctx->d_row_ptr, ctx->d_col_idx, ctx->d_values, d_x, n_rows, d_y);
   } else if (want) {
-    k_spmv<<<(unsigned)want, 256, 0, ctx->stream>>>(ctx->d_row_ptr, ctx->d_col_idx, ctx->d_values, d_x, ctx->n_rows, d_y);
+    k_spmv<<<(unsigned)want, 256, 0, ctx->stream>>>(ctx->d_row_ptr, ctx->d_col_idx, ctx->d_values, d_x, n_rows, d_y);
   }
   FEASM_CUDA(ctx, cudaGetLastError());
   return FEASM_OK;
@@ -259,27 +358,46 @@ int dot(feasm_ctx* ctx, const double* a, const double* b, int64_t n, double* d_p
   return FEASM_OK;
 }
 
+// y = A x on the owned rows; on several ranks x's ghost entries come from their owners first (feasm_halo_exchange)
+int product(feasm_ctx* ctx, const double* d_x, double* d_y) {
+  const double* xc = nullptr;
+  const int rc = feasm_halo_exchange(ctx, d_x, &xc);
+  return rc ? rc : spmv(ctx, ctx->n_owned, xc, d_y);
+}
+
+// finishes `cnt` dot products whose local sums sit in d_s[0..cnt): all-gather, then the same rank-ordered sum everywhere
+int rank_sum(feasm_ctx* ctx, double* d_s, int cnt, double* d_gather) {
+  if (ctx->comm_size <= 1 || !ctx->comm) return FEASM_OK;
+  const int rc = feasm_comm_allgather_f64(ctx, d_s, d_gather, cnt, ctx->stream);
+  if (rc) return rc;
+  k_rank_sum<<<1, 32, 0, ctx->stream>>>(d_gather, ctx->comm_size, cnt, d_s);
+  FEASM_CUDA(ctx, cudaGetLastError());
+  return FEASM_OK;
+}
+
 }  // namespace
+
+int feasm_spmv_rows(feasm_ctx* ctx, int64_t n_rows_used, const double* d_x, double* d_y) { return spmv(ctx, n_rows_used, d_x, d_y); }
 
 int feasm_vector_mult(feasm_ctx* ctx, const double* d_x, double* d_y) {
   if (!ctx || !ctx->d_values) return feasm_fail(ctx, FEASM_ERR_STATE, "no matrix");
   if (!d_x || !d_y) return feasm_fail(ctx, FEASM_ERR_ARG, "null vector");
-  if (ctx->d_gid || ctx->n_owned != ctx->n_rows) return feasm_fail(ctx, FEASM_ERR_STATE, "vector_mult: one rank per matrix in this version");
   FEASM_CUDA(ctx, cudaSetDevice(ctx->device));
-  return spmv(ctx, d_x, d_y);
+  return product(ctx, d_x, d_y);
 }
 
 int feasm_vector_mult_host(feasm_ctx* ctx, const double* x, double* y) {
   if (!ctx || !ctx->d_values) return feasm_fail(ctx, FEASM_ERR_STATE, "no matrix");
   if (!x || !y) return feasm_fail(ctx, FEASM_ERR_ARG, "null vector");
   FEASM_CUDA(ctx, cudaSetDevice(ctx->device));
-  const size_t nb = sizeof(double) * (size_t)(ctx->n_rows ? ctx->n_rows : 1);
+  const int64_t n = ctx->n_owned;  // the owned part of x and y (all rows on one rank)
+  const size_t nb = sizeof(double) * (size_t)(n ? n : 1);
   double* w = nullptr;
   FEASM_CUDA(ctx, cudaMalloc(&w, 2 * nb));
   int rc = FEASM_OK;
   if (cudaMemcpyAsync(w, x, nb, cudaMemcpyHostToDevice, ctx->stream) != cudaSuccess) rc = feasm_fail(ctx, FEASM_ERR_CUDA, "H2D x");
-  if (!rc) rc = feasm_vector_mult(ctx, w, w + ctx->n_rows);
-  if (!rc && (cudaMemcpyAsync(y, w + ctx->n_rows, nb, cudaMemcpyDeviceToHost, ctx->stream) != cudaSuccess ||
+  if (!rc) rc = feasm_vector_mult(ctx, w, w + (n ? n : 1));
+  if (!rc && (cudaMemcpyAsync(y, w + (n ? n : 1), nb, cudaMemcpyDeviceToHost, ctx->stream) != cudaSuccess ||
               cudaStreamSynchronize(ctx->stream) != cudaSuccess))
     rc = feasm_fail(ctx, FEASM_ERR_CUDA, "D2H y");
   cudaFree(w);
@@ -289,20 +407,26 @@ int feasm_vector_mult_host(feasm_ctx* ctx, const double* x, double* y) {
 int feasm_cg_solve(feasm_ctx* ctx, double rel_tol, int max_its, const double* x0, double* x, int* iterations, double* rel_residual) {
   if (!ctx || !ctx->d_values) return feasm_fail(ctx, FEASM_ERR_STATE, "no matrix");
   if (!x || max_its < 0 || !(rel_tol >= 0.)) return feasm_fail(ctx, FEASM_ERR_ARG, "bad solver arguments");
-  if (ctx->d_gid || ctx->n_owned != ctx->n_rows) return feasm_fail(ctx, FEASM_ERR_STATE, "cg_solve: one rank per matrix in this version");
+  const bool several = feasm_is_distributed(ctx);
+  if (several && !ctx->comm) return feasm_fail(ctx, FEASM_ERR_STATE, "cg_solve on several ranks needs the context's communicator (feasm_comm_init / feasm_set_communicator) and feasm_build_halo");
   FEASM_CUDA(ctx, cudaSetDevice(ctx->device));
-  const int64_t n = ctx->n_rows;
-  if (n == 0) {
+  const int64_t n = ctx->n_owned;  // every vector is the owned part; x0 / x are the owned parts on the host
+  uint32_t first = 0;
+  if (several && !feasm_halo_ready(ctx)) return feasm_fail(ctx, FEASM_ERR_STATE, "cg_solve on several ranks: feasm_build_halo first");
+  if (n == 0 && !several) {
     if (iterations) *iterations = 0;
     if (rel_residual) *rel_residual = 0.;
     return FEASM_OK;
   }
   const size_t nb = sizeof(double) * (size_t)(n ? n : 1);
   double* w = nullptr;  // x | r | z | p | q | dinv | partials | scalars(4)
-  FEASM_CUDA(ctx, cudaMalloc(&w, 6 * nb + sizeof(double) * (DOT_GRID + 4)));
-  double *d_x = w, *d_r = w + n, *d_z = w + 2 * n, *d_p = w + 3 * n, *d_q = w + 4 * n, *d_dinv = w + 5 * n;
-  double* d_part = w + 6 * (n ? n : 1);
+  const int world = several ? ctx->comm_size : 1;
+  const size_t n1 = (size_t)(n ? n : 1);
+  FEASM_CUDA(ctx, cudaMalloc(&w, 6 * nb + sizeof(double) * (DOT_GRID + 4 + 2 * world)));
+  double *d_x = w, *d_r = w + n1, *d_z = w + 2 * n1, *d_p = w + 3 * n1, *d_q = w + 4 * n1, *d_dinv = w + 5 * n1;
+  double* d_part = w + 6 * n1;
   double* d_s = d_part + DOT_GRID;  // [0] rz, [1] pq, [2] rz_new, [3] rr
+  double* d_gather = d_s + 4;       // [world][<= 2] partial sums of the ranks
   int rc = FEASM_OK, its = 0;
   double rel = 0.;
   bool breakdown = false;
@@ -310,26 +434,32 @@ int feasm_cg_solve(feasm_ctx* ctx, double rel_tol, int max_its, const double* x0
   const unsigned vg = DOT_GRID;
   if (x0) { if (cudaMemcpyAsync(d_x, x0, nb, cudaMemcpyHostToDevice, ctx->stream) != cudaSuccess) return fail(feasm_fail(ctx, FEASM_ERR_CUDA, "H2D x0")); }
   else if (cudaMemsetAsync(d_x, 0, nb, ctx->stream) != cudaSuccess) return fail(feasm_fail(ctx, FEASM_ERR_CUDA, "memset x"));
-  k_inv_diag<<<(unsigned)((n + 255) / 256), 256, 0, ctx->stream>>>(ctx->d_row_ptr, ctx->d_col_idx, ctx->d_values, ctx->d_gid, n, d_dinv);
-  if ((rc = spmv(ctx, d_x, d_q))) return fail(rc);
+  first = several ? feasm_halo_first(ctx) : 0;
+  if (n) k_inv_diag<<<(unsigned)((n + 255) / 256), 256, 0, ctx->stream>>>(ctx->d_row_ptr, ctx->d_col_idx, ctx->d_values, ctx->d_gid, first, n, d_dinv);
+  if ((rc = product(ctx, d_x, d_q))) return fail(rc);
   k_cg_start<<<vg, 256, 0, ctx->stream>>>(n, ctx->d_rhs, d_q, d_dinv, d_r, d_z, d_p);
   double h[4] = {0, 0, 0, 0};
   // ||b|| for the relative test, r.z for the first direction
   if ((rc = dot(ctx, ctx->d_rhs, ctx->d_rhs, n, d_part, d_s + 3))) return fail(rc);
+  if ((rc = rank_sum(ctx, d_s + 3, 1, d_gather))) return fail(rc);
   if ((rc = dot(ctx, d_r, d_z, n, d_part, d_s + 0))) return fail(rc);
+  if ((rc = rank_sum(ctx, d_s + 0, 1, d_gather))) return fail(rc);
   if (cudaMemcpyAsync(h, d_s, sizeof(h), cudaMemcpyDeviceToHost, ctx->stream) != cudaSuccess || cudaStreamSynchronize(ctx->stream) != cudaSuccess)
     return fail(feasm_fail(ctx, FEASM_ERR_CUDA, "cg: scalar read"));
   const double bnorm = std::sqrt(h[3]) > 0. ? std::sqrt(h[3]) : 1.;
   if ((rc = dot(ctx, d_r, d_r, n, d_part, d_s + 3))) return fail(rc);
+  if ((rc = rank_sum(ctx, d_s + 3, 1, d_gather))) return fail(rc);
   if (cudaMemcpyAsync(h, d_s, sizeof(h), cudaMemcpyDeviceToHost, ctx->stream) != cudaSuccess || cudaStreamSynchronize(ctx->stream) != cudaSuccess)
     return fail(feasm_fail(ctx, FEASM_ERR_CUDA, "cg: scalar read"));
   rel = std::sqrt(h[3]) / bnorm;
   while (its < max_its && rel > rel_tol) {
-    if ((rc = spmv(ctx, d_p, d_q))) return fail(rc);
+    if ((rc = product(ctx, d_p, d_q))) return fail(rc);
     if ((rc = dot(ctx, d_p, d_q, n, d_part, d_s + 1))) return fail(rc);
+    if ((rc = rank_sum(ctx, d_s + 1, 1, d_gather))) return fail(rc);
     k_cg_update<<<vg, 256, 0, ctx->stream>>>(n, d_s + 0, d_s + 1, d_p, d_q, d_dinv, d_x, d_r, d_z);
     if ((rc = dot(ctx, d_r, d_z, n, d_part, d_s + 2))) return fail(rc);
     if ((rc = dot(ctx, d_r, d_r, n, d_part, d_s + 3))) return fail(rc);
+    if ((rc = rank_sum(ctx, d_s + 2, 2, d_gather))) return fail(rc);  // r.z and r.r in one all-gather
     k_cg_direction<<<vg, 256, 0, ctx->stream>>>(n, d_s + 2, d_s + 0, d_z, d_p);
     if (cudaMemcpyAsync(d_s + 0, d_s + 2, sizeof(double), cudaMemcpyDeviceToDevice, ctx->stream) != cudaSuccess ||
         cudaMemcpyAsync(h, d_s, sizeof(h), cudaMemcpyDeviceToHost, ctx->stream) != cudaSuccess || cudaStreamSynchronize(ctx->stream) != cudaSuccess)

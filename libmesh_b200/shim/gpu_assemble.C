@@ -121,6 +121,7 @@ void assemble(EquationSystems& es, const std::string& system_name, const feasm_p
         A->ensure_communicator();
         A->check(feasm_build_pattern(ctx));
         A->check(feasm_build_exchange(ctx, first_dof.data()));  // collective
+        A->check(feasm_build_halo(ctx, first_dof.data()));      // collective: the products / solves after the assembly
         A->adopt_device_pattern();
       }
       up.mesh = &mesh; up.n_elem = n_elem; up.n_dofs = dof_map.n_dofs(); up.n_local = n_local; up.first = first;

@@ -9,7 +9,8 @@
 // in rank order (DistributedVector::dot, distributed_vector.C), localize gathers.  The Krylov operations (dot, add(a,v),
 // scale, norms, pointwise ops) are device kernels with fixed-order reductions; entry access (operator(), set/add of single
 // entries) goes through single-entry transfers and is meant for set-up code, not loops.  add_vector (the product with a
-// GpuSparseMatrix) is one rank only: the halo exchange of the iterate is not part of libfeasm yet.
+// GpuSparseMatrix) works on several ranks as well: libfeasm fetches the entries of v other ranks own (feasm_build_halo, set
+// up by the assemble hook) inside feasm_vector_mult.
 #ifndef FEASM_GPU_NUMERIC_VECTOR_H
 #define FEASM_GPU_NUMERIC_VECTOR_H
 
@@ -169,8 +170,8 @@ class GpuNumericVector : public NumericVector<T> {
   void add_vector(const NumericVector<T>& v, const SparseMatrix<T>& A) override {
     auto* G = dynamic_cast<GpuSparseMatrix<T>*>(const_cast<SparseMatrix<T>*>(&A));
     if (!G) libmesh_error_msg("GpuNumericVector::add_vector: the matrix is not a GpuSparseMatrix");
-    if (distributed()) libmesh_not_implemented();  // needs the halo exchange of v (see the header comment)
-    if (A.n() != v.size() || A.m() != _n) libmesh_error_msg("GpuNumericVector::add_vector: size mismatch");
+    // on several ranks v and this are the owned parts; feasm_vector_mult fetches the entries of v the other ranks own
+    if (A.n() != v.size() || A.row_stop() - A.row_start() != _n || v.local_size() != _n) libmesh_error_msg("GpuNumericVector::add_vector: size mismatch");
     const OnDevice dv = on_device(v);
     double* tmp = feasm_vec_alloc(ctx(), _n);
     if (!tmp) libmesh_error_msg("GpuNumericVector::add_vector: device allocation failed");

@@ -226,7 +226,7 @@ class GpuSparseMatrix : public SparseMatrix<T> {
   std::pair<unsigned int, Real> solve_cg(std::vector<T>& x, Real rel_tol, unsigned int max_its) {
     int its = 0;
     double rel = 0.;
-    x.resize(m());
+    x.resize(_row_stop - _row_start);  // the owned part (the whole vector on one rank); collective on several ranks
     const int rc = feasm_cg_solve(ctx(), rel_tol, (int)max_its, nullptr, x.data(), &its, &rel);
     if (rc < 0) check(rc);  // FEASM_NOT_CONVERGED (> 0) is reported through the returned residual, like LinearSolver::solve
     return {(unsigned int)its, rel};

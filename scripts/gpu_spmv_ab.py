@@ -1,18 +1,10 @@
-"""Development aid: feasm_vector_mult time and bitwise comparison of the pipelined and the one-row-at-a-time kernel.
-    python scripts/gpu_spmv_ab.py [hex27|hex8|tet10] [n] [n_vars]      (runs itself twice, FEASM_SPMV_PIPE=1 and 0)"""
+"""Development aid: feasm_vector_mult time of the SpMV kernels (A/B knobs FEASM_SPMV_PIPE / FEASM_SPMV_STREAM are read per
+call) and comparison of their results.
+    python scripts/gpu_spmv_ab.py [hex27|hex8|tet10|hex20] [n] [n_vars]"""
 import os
-import subprocess
 import sys
 import numpy as np
 
-if "FEASM_SPMV_PIPE" not in os.environ:
-    outs = []
-    for v in ("1", "0"):
-        r = subprocess.run([sys.executable] + sys.argv, env={**os.environ, "FEASM_SPMV_PIPE": v, "SPMV_OUT": f"/tmp/spmv_{v}.npy"}, capture_output=True, text=True)
-        print(r.stdout.strip(), r.stderr.strip()[-400:])
-    a, b = np.load("/tmp/spmv_1.npy"), np.load("/tmp/spmv_0.npy")
-    print("bitwise equal:", np.array_equal(a, b), "max |y|", np.abs(a).max())
-    sys.exit(0)
 sys.path.insert(0, '.')
 import torch
 from libmesh_b200 import capi as F
@@ -34,18 +26,23 @@ x = torch.rand(nd, dtype=torch.float64, device="cuda", generator=g)
 y = torch.zeros(nd, dtype=torch.float64, device="cuda")
 flush = torch.empty(256 << 20, dtype=torch.uint8, device="cuda")
 lib = torch.cuda.ExternalStream(ctx.stream())
-best = []
-for it in range(8):
-    flush.zero_()
-    torch.cuda.synchronize()
-    with torch.cuda.stream(lib):
-        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-        e0.record()
-        ctx.vector_mult(x.data_ptr(), y.data_ptr())
-        e1.record()
-    ctx.synchronize(); torch.cuda.synchronize()
-    best.append(e0.elapsed_time(e1))
-ms = min(best[2:])
-by = nnz * 12 + nd * 32
-print(f"pipe={os.environ['FEASM_SPMV_PIPE']} {sys.argv[1:]} rows {nd} nnz {nnz}: {ms:.4f} ms, {by / ms / 1e6:.0f} GB/s")
-np.save(os.environ["SPMV_OUT"], y.cpu().numpy())
+res = {}
+for name, pipe, st in (("pipe", "1", "0"), ("row", "0", "0"), ("stream512", "1", "1"), ("stream512_flat", "1", "2"), ("stream768", "1", "3")):
+    os.environ["FEASM_SPMV_PIPE"], os.environ["FEASM_SPMV_STREAM"] = pipe, st
+    best = []
+    for it in range(8):
+        flush.zero_()
+        torch.cuda.synchronize()
+        with torch.cuda.stream(lib):
+            e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            e0.record()
+            ctx.vector_mult(x.data_ptr(), y.data_ptr())
+            e1.record()
+        ctx.synchronize(); torch.cuda.synchronize()
+        best.append(e0.elapsed_time(e1))
+    ms = min(best[2:])
+    by = nnz * 12 + nd * 32
+    print(f"{name:15s} {sys.argv[1:]} rows {nd} nnz {nnz}: {ms:.4f} ms, {by / ms / 1e6:.0f} GB/s", flush=True)
+    res[name] = y.cpu().numpy().copy()
+print("pipe vs row bitwise equal:", np.array_equal(res["pipe"], res["row"]), " max |y|", np.abs(res["row"]).max(),
+      " stream vs row max abs diff", max(np.abs(res[k] - res["row"]).max() for k in res if k.startswith("stream")))

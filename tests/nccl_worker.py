@@ -4,7 +4,9 @@ process per GPU, launched by torch.distributed.run).
 What only the real run has — NCCL's own stream against the library's stream, feasm_assemble_end under the transfer, the
 next step's pack into the same send buffer, feasm_unpack_ghost — is exercised by several back-to-back asynchronous
 steps; the owned rows of every rank are then compared with the oracle's global system (1e-12 per entry), and the
-overlapped and sequential forms with each other (bitwise).
+overlapped and sequential forms with each other (bitwise).  With the communicator inside the library the distributed
+matrix is then USED: feasm_build_halo, feasm_vector_mult against scipy's product with the oracle's global matrix,
+feasm_residual against A u - b, feasm_cg_solve against a direct solve (all ranks must report the same iteration count).
 """
 import os
 import sys
@@ -71,9 +73,35 @@ def run_case(rank, world, local, host_group, etype, dims, n_vars, scramble, nati
     assert np.array_equal(da.col_idx[: hi - lo], gci[lo:hi]), "owned col_idx"
     cv_, cr_ = csr_compare(v, gv[lo:hi], da.row_ptr[: n_own + 1]), vec_compare(b, gb[f0:f0 + n_own])
     assert cv_["max_rel_err"] < TOL and cr_["max_rel_err"] < TOL, (cv_, cr_)
+    extra = ""
+    if native:  # the assembled matrix of the ranks used on the device: halo of a distributed vector (feasm_halo.cu)
+        import scipy.sparse as sp
+        import scipy.sparse.linalg as spl
+
+        A = sp.csr_matrix((gv, gci.astype(np.int64), grp.astype(np.int64)), shape=(s.n_dofs, s.n_dofs))
+        ctx.build_halo(prob.first_dof)
+        x = np.cos(0.37 * np.arange(s.n_dofs)) + 0.1
+        Ax = A @ x
+        y = ctx.vector_mult_host(x[f0:f0 + n_own])
+        e_y = np.abs(y - Ax[f0:f0 + n_own]).max() / np.abs(Ax).max()
+        assert e_y <= 1e-13, ("vector_mult", e_y)
+        r = ctx.residual_host(params, x[f0:f0 + n_own])  # K(u) u - F straight from the element records, ghost rows summed on their owners
+        e_r = np.abs(r - (Ax - gb)[f0:f0 + n_own]).max() / max(np.abs(Ax).max(), np.abs(gb).max())
+        assert e_r <= 1e-12, ("residual", e_r)
+        r2 = ctx.residual_host(params, x[f0:f0 + n_own])
+        assert np.array_equal(r, r2), "distributed residual not reproducible"
+        xs, its, rel = ctx.cg_solve(1e-10, 5000)
+        x_ref = spl.spsolve(A.tocsc(), gb)
+        e_x = np.abs(xs - x_ref[f0:f0 + n_own]).max() / np.abs(x_ref).max()
+        assert rel <= 1e-10 and e_x <= 1e-7, ("cg", its, rel, e_x)
+        meta = torch.tensor([float(its), rel], dtype=torch.float64)
+        gathered = [torch.zeros(2, dtype=torch.float64) for _ in range(world)]
+        dist.all_gather(gathered, meta, group=host_group)
+        assert all(torch.equal(g, gathered[0]) for g in gathered), "ranks disagree on the CG iteration count / residual"
+        extra = f", A x {e_y:.1e}, residual {e_r:.1e}, CG {its} its rel {rel:.1e} err {e_x:.1e}"
     ctx.close()
     print(f"rank {rank}: etype {etype} dims {dims} vars {n_vars} scramble {scramble} native {native}: {len(prob.elems)} elements, {n_own} owned + "
-          f"{len(prob.ghosts)} ghost rows, values max rel {cv_['max_rel_err']:.2e}, rhs {cr_['max_rel_err']:.2e}", flush=True)
+          f"{len(prob.ghosts)} ghost rows, values max rel {cv_['max_rel_err']:.2e}, rhs {cr_['max_rel_err']:.2e}{extra}", flush=True)
 
 
 def main():

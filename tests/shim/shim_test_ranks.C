@@ -182,6 +182,33 @@ static int run(const Parallel::Communicator& comm, int n_vars) {
     GpuNumericVector<Number> g3(comm, (numeric_index_type)n_dofs, n_local);
     g3 = whole;                                 // from the whole vector: the local part is kept
     REQUIRE(near(g3.dot(grhs), dot));
+    // the distributed matrix used on the device: y += A x with x's ghost entries fetched from their owners (feasm_build_halo
+    // was set up by the hook), against the product with the one-context matrix
+    {
+      std::vector<Number> xw(n_dofs), yref(n_dofs, 0.), yw;
+      for (int64_t i = 0; i < n_dofs; ++i) xw[i] = std::cos(0.37 * (double)i) + 0.1;
+      double ymax = 0.;
+      for (int64_t r = 0; r < n_dofs; ++r) { for (uint64_t k = rp[r]; k < rp[r + 1]; ++k) yref[r] += v[k] * xw[ci[k]]; ymax = std::max(ymax, std::fabs(yref[r])); }
+      GpuNumericVector<Number> gx(comm, (numeric_index_type)n_dofs, n_local), gy(comm, (numeric_index_type)n_dofs, n_local);
+      gx = xw;
+      gy.zero();
+      gy.add_vector(gx, A);
+      gy.localize(yw);
+      for (int64_t i = 0; i < n_dofs; ++i) REQUIRE(std::fabs(yw[i] - yref[i]) <= 1e-13 * ymax);
+      // LinearSolver::solve on the distributed system: all ranks agree on the iteration count; solution = the one-context solve
+      std::vector<Number> xs, xone(n_dofs);
+      const auto res = A.solve_cg(xs, 1e-11, 4000);
+      int its1 = 0;
+      double rel1 = 0.;
+      const int rc1 = feasm_cg_solve(ctx, 1e-11, 4000, nullptr, xone.data(), &its1, &rel1);
+      REQUIRE(rc1 == FEASM_OK && res.second <= 1e-11 && xs.size() == n_local);
+      unsigned its_max = res.first, its_min = res.first;
+      comm.max(its_max); comm.min(its_min);
+      REQUIRE(its_max == its_min);
+      double xmax = 0.;
+      for (int64_t i = 0; i < n_dofs; ++i) xmax = std::max(xmax, std::fabs(xone[i]));
+      for (dof_id_type r = f0; r < f1; ++r) REQUIRE(std::fabs(xs[r - f0] - xone[r]) <= 1e-8 * xmax);
+    }
     if (world > 1 && n_local < (dof_id_type)n_dofs) {
       bool threw = false;
       try { (void)grhs(f0 > 0 ? 0 : f1); } catch (const LogicError&) { threw = true; }

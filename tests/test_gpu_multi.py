@@ -10,11 +10,9 @@ from conftest import PARITY_TOL, csr_parity_error, vec_parity_error
 pytestmark = pytest.mark.gpu
 
 
-@pytest.mark.parametrize("split", [False, True], ids=["assemble", "begin_end"])
-@pytest.mark.parametrize("world,etype,dims,scramble", [(2, 27, (4, 4, 4), 0), (3, 27, (4, 3, 3), 1), (4, 8, (6, 5, 4), 1), (2, 10, (2, 2, 2), 0)])
-def test_emulated_ranks_match_global_oracle(world, etype, dims, scramble, split):
-    """split: feasm_assemble_begin (element phase, non-owned rows, pack) / feasm_assemble_end (owned rows) around the
-    exchange, the overlapped form bench.py --gpus N runs; otherwise feasm_assemble + feasm_pack_ghost."""
+def _assemble_emulated(world, etype, dims, scramble, split):
+    """Every rank of a `world`-rank job as one context on this GPU, assembled and exchanged; returns the rank objects and
+    the oracle's global system."""
     from libmesh_b200 import capi as F
     from libmesh_b200 import multi as M
     from oracle import oracle as O
@@ -77,6 +75,15 @@ def test_emulated_ranks_match_global_oracle(world, etype, dims, scramble, split)
         if da.peers:
             da.ctx.unpack_ghost()
         da.ctx.synchronize()
+    return das, (grp, gci, gv, gb, s.n_dofs)
+
+
+@pytest.mark.parametrize("split", [False, True], ids=["assemble", "begin_end"])
+@pytest.mark.parametrize("world,etype,dims,scramble", [(2, 27, (4, 4, 4), 0), (3, 27, (4, 3, 3), 1), (4, 8, (6, 5, 4), 1), (2, 10, (2, 2, 2), 0)])
+def test_emulated_ranks_match_global_oracle(world, etype, dims, scramble, split):
+    """split: feasm_assemble_begin (element phase, non-owned rows, pack) / feasm_assemble_end (owned rows) around the
+    exchange, the overlapped form bench.py --gpus N runs; otherwise feasm_assemble + feasm_pack_ghost."""
+    das, (grp, gci, gv, gb, _) = _assemble_emulated(world, etype, dims, scramble, split)
     for r, da in enumerate(das):
         v, b = da.owned_values()
         f0, n_own = da.p.f0, da.p.n_owned
@@ -85,4 +92,69 @@ def test_emulated_ranks_match_global_oracle(world, etype, dims, scramble, split)
         assert np.array_equal(da.col_idx[: hi - lo], gci[lo:hi])
         assert csr_parity_error(v, gv[lo:hi], da.row_ptr[: n_own + 1]) < PARITY_TOL
         assert vec_parity_error(b, gb[f0:f0 + n_own]) < PARITY_TOL
+        da.ctx.close()
+
+
+@pytest.mark.parametrize("world,etype,dims,scramble", [(2, 27, (4, 4, 4), 0), (3, 27, (4, 3, 3), 1), (4, 8, (6, 5, 4), 1)])
+def test_emulated_ranks_vector_mult_with_halo(world, etype, dims, scramble):
+    """SparseMatrix::vector_mult on the distributed matrix: feasm_halo_columns names the entries of x a rank needs from
+    others, the requests are routed by owner (here by hand, as a host with its own messaging would), feasm_halo_pack /
+    copy / feasm_halo_unpack stand in for the NCCL exchange, and the owned rows of A x equal scipy's product with the
+    oracle's global matrix."""
+    import scipy.sparse as sp
+    from libmesh_b200 import multi as M
+
+    das, (grp, gci, gv, gb, n_dofs) = _assemble_emulated(world, etype, dims, scramble, True)
+    A = sp.csr_matrix((gv, gci.astype(np.int64), grp.astype(np.int64)), shape=(n_dofs, n_dofs))
+    x = np.cos(0.37 * np.arange(n_dofs)) + 0.1
+    y_ref = A @ x
+    first = das[0].p.first_dof
+    need = [da.ctx.halo_columns(n_dofs, da.p.f0) for da in das]
+    for r, da in enumerate(das):
+        own = (need[r] >= da.p.f0) & (need[r] < da.p.f0 + da.p.n_owned)
+        assert not own.any() and np.all(np.diff(need[r].astype(np.int64)) > 0)
+        assert np.isin(da.p.ghosts, need[r]).all()  # the ghost rows are part of the halo (feasm_residual needs them)
+    owner = [np.searchsorted(first, n.astype(np.int64), side="right") - 1 for n in need]
+    for r, da in enumerate(das):
+        peers = sorted(set(int(q) for q in owner[r]) | {q for q in range(world) if q != r and (owner[q] == r).any()})
+        sp_, sr, rp_, rg = [0], [], [0], []
+        for q in peers:
+            wanted = need[q][owner[q] == r].astype(np.int64) - da.p.f0  # what q asks of r, as r's local rows
+            sr.append(wanted); sp_.append(sp_[-1] + len(wanted))
+            got = need[r][owner[r] == q]
+            rg.append(got); rp_.append(rp_[-1] + len(got))
+        cat = lambda parts, dt: np.concatenate(parts).astype(dt) if parts else np.zeros(0, dt)
+        da.ctx.set_halo_plan(n_dofs, da.p.f0, peers, sp_, cat(sr, np.uint32), rp_, cat(rg, np.uint32))
+        da.halo_peers, da.halo_sp, da.halo_rp = peers, sp_, rp_
+    L = das[0].ctx.L
+    import ctypes as C
+    dx, dy, send = [], [], []
+    for da in das:
+        n = da.p.n_owned
+        xo = np.ascontiguousarray(x[da.p.f0:da.p.f0 + n])
+        d_x, d_y = L.feasm_vec_alloc(da.ctx.h, n), L.feasm_vec_alloc(da.ctx.h, n)
+        assert L.feasm_vec_copy(da.ctx.h, 0, C.c_void_p(d_x), xo.ctypes.data_as(C.c_void_p), n) == 0
+        dx.append(d_x); dy.append(d_y)
+        ptr, ns = da.ctx.halo_pack(d_x)
+        da.ctx.synchronize()
+        send.append(torch.as_tensor(M.DevArray(ptr, max(ns, 1)), device="cuda"))
+    for r, da in enumerate(das):
+        ptr, nr = da.ctx.halo_recv_buffer()
+        rbuf = torch.as_tensor(M.DevArray(ptr, max(nr, 1)), device="cuda")
+        for i, q in enumerate(da.halo_peers):
+            r0, r1 = da.halo_rp[i], da.halo_rp[i + 1]
+            if r1 > r0:
+                dq = das[q]
+                j = dq.halo_peers.index(r)
+                rbuf[r0:r1].copy_(send[q][dq.halo_sp[j]:dq.halo_sp[j + 1]])
+        torch.cuda.synchronize()
+        da.ctx.halo_unpack()
+        da.ctx.vector_mult(dx[r], dy[r])
+        n = da.p.n_owned
+        y = np.empty(n)
+        assert L.feasm_vec_copy(da.ctx.h, 1, y.ctypes.data_as(C.c_void_p), C.c_void_p(dy[r]), n) == 0
+        ref = y_ref[da.p.f0:da.p.f0 + n]
+        assert np.abs(y - ref).max() <= 1e-13 * np.abs(y_ref).max(), (r, np.abs(y - ref).max())
+    for r, da in enumerate(das):
+        L.feasm_vec_free(da.ctx.h, C.c_void_p(dx[r])); L.feasm_vec_free(da.ctx.h, C.c_void_p(dy[r]))
         da.ctx.close()
