@@ -32,7 +32,7 @@ extern "C" {
 #define FEASM_HEX8 8
 #define FEASM_HEX27 27
 #define FEASM_TET10 10
-#define FEASM_HEX20 20 /* serendipity hex (cell_hex20.C, fe_lagrange_shape_3D.C:848-925); volume terms only, no side loads yet */
+#define FEASM_HEX20 20 /* serendipity hex (cell_hex20.C, fe_lagrange_shape_3D.C:848-925); QUAD8 sides (fe_lagrange_shape_2D.C:434-471) */
 
 /* problems (the Ke/Fe contraction that runs per element) */
 #define FEASM_POISSON 1    /* introduction_ex4.C:464-537: Ke = int grad phi_i . grad phi_j, Fe = int f phi_i */
@@ -117,8 +117,8 @@ int feasm_set_constraint_rows(feasm_ctx* ctx, int64_t n, const uint32_t* dofs, c
  *   the volume rule's order)  and  Fe_var[i](a) += JxW_face[qp] * (g[i] * phi_face[a][qp]),
  * added to Fe after the volume terms and before the element constraint in every following feasm_assemble /
  * feasm_element_matrices.  The adaptor fills the list from BoundaryInfo::has_boundary_id(elem, side, id) for sides
- * without a neighbour.  g: n_g = number of variables components (a traction; n_g = 1: a Neumann flux).  HEX8 / HEX27 (QUAD4 / QUAD9
- * sides) and TET10 (TRI6 sides, QGauss(2, FIFTH) = the 7-point rule of quadrature_gauss_2D.C:234-257).
+ * without a neighbour.  g: n_g = number of variables components (a traction; n_g = 1: a Neumann flux).  HEX8 / HEX20 / HEX27
+ * (QUAD4 / QUAD8 / QUAD9 sides) and TET10 (TRI6 sides, QGauss(2, FIFTH) = the 7-point rule of quadrature_gauss_2D.C:234-257).
  * n = 0 clears. */
 int feasm_set_side_loads(feasm_ctx* ctx, int64_t n, const uint32_t* elems, const uint8_t* sides, const double* g, int n_g);
 
@@ -127,7 +127,7 @@ int feasm_set_side_loads(feasm_ctx* ctx, int64_t n, const uint32_t* elems, const
  *   Ke(i,j) += JxW_face[qp]*penalty*phi_face[i][qp]*phi_face[j][qp];   Fe(i) += JxW_face[qp]*penalty*value*phi_face[i][qp];
  * value = the given constant or the exact solution at the side point (introduction_ex3/exact_solution.C:40-47); with
  * several variables every variable's diagonal block gets the term.  Added after the volume terms and the side loads,
- * before the element constraint.  HEX8 / HEX27 / TET10.  n = 0 clears. */
+ * before the element constraint.  HEX8 / HEX20 / HEX27 / TET10.  n = 0 clears. */
 #define FEASM_PENALTY_CONSTANT 0
 #define FEASM_PENALTY_EX4_EXACT 1
 int feasm_set_side_penalty(feasm_ctx* ctx, int64_t n, const uint32_t* elems, const uint8_t* sides, double penalty, int kind, double value);

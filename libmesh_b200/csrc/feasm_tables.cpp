@@ -168,6 +168,29 @@ bool feasm_make_tables(int elem_type, int qorder, FeasmTables& t, std::string& e
 // functions (fe_lagrange_shape_2D.C:499-530, :920-975) and the parent's shapes at the side points carried into the
 // reference tet (reference nodes fe_abstract.C:488-501).  Tables are laid out for six sides (sides 4, 5 stay zero) so
 // the kernels address them like a hex's.
+// Value of the HEX20 serendipity function of node a at a reference point (the closed form of feasm_make_tables)
+static double hex20_value(int a, const double c[3]) {
+  const double n0[3] = {(double)kHexNode[a][0], (double)kHexNode[a][1], (double)kHexNode[a][2]};
+  if (a < 8) return .125 * (1. + n0[0] * c[0]) * (1. + n0[1] * c[1]) * (1. + n0[2] * c[2]) * (n0[0] * c[0] + n0[1] * c[1] + n0[2] * c[2] - 2.);
+  const int m = n0[0] == 0. ? 0 : (n0[1] == 0. ? 1 : 2), u = (m + 1) % 3, v = (m + 2) % 3;
+  return .25 * (1. - c[m] * c[m]) * (1. + n0[u] * c[u]) * (1. + n0[v] * c[v]);
+}
+// QUAD8, the side of a HEX20 (fe_lagrange_shape_2D.C:434-471, :795-879), in the closed form over the node's coordinates:
+//   corner (x0, y0):  (1 + x0 xi)(1 + y0 eta)(x0 xi + y0 eta - 1) / 4;   mid-side: (1 - xi^2)(1 + y0 eta) / 2 or (1 + x0 xi)(1 - eta^2) / 2
+static void quad8(int a, double xi, double eta, double& v, double& dx, double& de) {
+  const double x0 = kQuadNode[a][0], y0 = kQuadNode[a][1];
+  if (a < 4) {
+    const double fx = 1. + x0 * xi, fy = 1. + y0 * eta, L = x0 * xi + y0 * eta - 1.;
+    v = .25 * fx * fy * L;
+    dx = .25 * x0 * fy * (L + fx);
+    de = .25 * y0 * fx * (L + fy);
+  } else if (x0 == 0.) {
+    v = .5 * (1. - xi * xi) * (1. + y0 * eta); dx = -xi * (1. + y0 * eta); de = .5 * (1. - xi * xi) * y0;
+  } else {
+    v = .5 * (1. + x0 * xi) * (1. - eta * eta); dx = .5 * x0 * (1. - eta * eta); de = -(1. + x0 * xi) * eta;
+  }
+}
+
 static bool make_tet10_side_tables(int qorder, FeasmSideTables& t, std::string& err) {
   if (qorder != 5) { err = "TET10 sides: only the FIFTH-order rule is built"; return false; }
   static const int kSide[4][6] = {{0, 2, 1, 6, 5, 4}, {0, 1, 3, 4, 8, 7}, {1, 2, 3, 5, 9, 8}, {2, 0, 3, 6, 7, 9}};
@@ -220,10 +243,11 @@ static bool make_tet10_side_tables(int qorder, FeasmSideTables& t, std::string& 
 bool feasm_make_side_tables(int elem_type, int qorder, FeasmSideTables& t, std::string& err) {
   t = FeasmSideTables();
   if (elem_type == FEASM_TET10) return make_tet10_side_tables(qorder, t, err);
-  if (elem_type != FEASM_HEX8 && elem_type != FEASM_HEX27) { err = "side terms: HEX8 / HEX27 / TET10 sides only"; return false; }
+  if (elem_type != FEASM_HEX8 && elem_type != FEASM_HEX27 && elem_type != FEASM_HEX20) { err = "side terms: HEX8 / HEX20 / HEX27 / TET10 sides only"; return false; }
   const int deg = elem_type == FEASM_HEX8 ? 1 : 2;
+  const bool ser = elem_type == FEASM_HEX20;  // QUAD8 sides: the first eight QUAD9 nodes (cell_hex20.C:37-45 = the first eight columns of cell_hex27.C:37-45)
   t.npe = elem_type;
-  t.ns = deg == 1 ? 4 : 9;
+  t.ns = deg == 1 ? 4 : (ser ? 8 : 9);
   double x[3], w[3];
   const int n1 = gauss1d(qorder, x, w);
   if (!n1) { err = "unsupported Gauss order for a side"; return false; }
@@ -234,6 +258,10 @@ bool feasm_make_side_tables(int elem_type, int qorder, FeasmSideTables& t, std::
     const int i = p % n1, j = p / n1;
     t.qw[p] = w[i] * w[j];
     for (int a = 0; a < t.ns; ++a) {
+      if (ser) {
+        quad8(a, x[i], x[j], t.psi[(size_t)a * t.nqf + p], t.dxi[(size_t)a * t.nqf + p], t.deta[(size_t)a * t.nqf + p]);
+        continue;
+      }
       const V1 X = lagrange1d(deg, kQuadNode[a][0], x[i]), Y = lagrange1d(deg, kQuadNode[a][1], x[j]);
       t.psi[(size_t)a * t.nqf + p] = X.v * Y.v;
       t.dxi[(size_t)a * t.nqf + p] = X.d * Y.v;
@@ -250,7 +278,8 @@ bool feasm_make_side_tables(int elem_type, int qorder, FeasmSideTables& t, std::
         for (int d = 0; d < 3; ++d) r[d] += t.psi[(size_t)a * t.nqf + p] * (double)kHexNode[kHexSide[s][a]][d];
       for (int a = 0; a < t.npe; ++a)
         t.phi[((size_t)s * t.npe + a) * t.nqf + p] =
-            lagrange1d(deg, kHexNode[a][0], r[0]).v * lagrange1d(deg, kHexNode[a][1], r[1]).v * lagrange1d(deg, kHexNode[a][2], r[2]).v;
+            ser ? hex20_value(a, r)
+                : lagrange1d(deg, kHexNode[a][0], r[0]).v * lagrange1d(deg, kHexNode[a][1], r[1]).v * lagrange1d(deg, kHexNode[a][2], r[2]).v;
     }
   }
   return true;

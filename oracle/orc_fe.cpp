@@ -435,9 +435,32 @@ static void tri6_shape(int i, double xi, double eta, double& v, double& dxi, dou
   }
 }
 
+// QUAD8 (the side of a HEX20), fe_lagrange_shape_2D.C:434-471 (values) and :795-879 (derivatives), expression for expression
+static void quad8_shape(int i, double xi, double eta, double& v, double& dxi, double& deta) {
+  switch (i) {
+    case 0: v = .25 * (1. - xi) * (1. - eta) * (-1. - xi - eta);
+      dxi = .25 * (1. - eta) * ((1. - xi) * (-1.) + (-1.) * (-1. - xi - eta));
+      deta = .25 * (1. - xi) * ((1. - eta) * (-1.) + (-1.) * (-1. - xi - eta)); break;
+    case 1: v = .25 * (1. + xi) * (1. - eta) * (-1. + xi - eta);
+      dxi = .25 * (1. - eta) * ((1. + xi) * (1.) + (1.) * (-1. + xi - eta));
+      deta = .25 * (1. + xi) * ((1. - eta) * (-1.) + (-1.) * (-1. + xi - eta)); break;
+    case 2: v = .25 * (1. + xi) * (1. + eta) * (-1. + xi + eta);
+      dxi = .25 * (1. + eta) * ((1. + xi) * (1.) + (1.) * (-1. + xi + eta));
+      deta = .25 * (1. + xi) * ((1. + eta) * (1.) + (1.) * (-1. + xi + eta)); break;
+    case 3: v = .25 * (1. - xi) * (1. + eta) * (-1. - xi + eta);
+      dxi = .25 * (1. + eta) * ((1. - xi) * (-1.) + (-1.) * (-1. - xi + eta));
+      deta = .25 * (1. - xi) * ((1. + eta) * (1.) + (1.) * (-1. - xi + eta)); break;
+    case 4: v = .5 * (1. - xi * xi) * (1. - eta); dxi = .5 * (-2. * xi) * (1. - eta); deta = .5 * (1. - xi * xi) * (-1.); break;
+    case 5: v = .5 * (1. + xi) * (1. - eta * eta); dxi = .5 * (1.) * (1. - eta * eta); deta = .5 * (1. + xi) * (-2. * eta); break;
+    case 6: v = .5 * (1. - xi * xi) * (1. + eta); dxi = .5 * (-2. * xi) * (1. + eta); deta = .5 * (1. - xi * xi) * (1.); break;
+    default: v = .5 * (1. - xi) * (1. - eta * eta); dxi = .5 * (-1.) * (1. - eta * eta); deta = .5 * (1. - xi) * (-2. * eta); break;
+  }
+}
+
 int side_nodes(int elem_type, int side, int* nodes) {
   if (side < 0 || side >= 6) return 0;
   if (elem_type == ORC_HEX27) { for (int i = 0; i < 9; ++i) nodes[i] = H27_SIDE[side][i]; return 9; }
+  if (elem_type == ORC_HEX20) { for (int i = 0; i < 8; ++i) nodes[i] = H27_SIDE[side][i]; return 8; }  // cell_hex20.C:37-45
   if (elem_type == ORC_HEX8) { for (int i = 0; i < 4; ++i) nodes[i] = H8_SIDE[side][i]; return 4; }
   if (elem_type == ORC_TET10 && side < 4) { for (int i = 0; i < 6; ++i) nodes[i] = T10_SIDE[side][i]; return 6; }
   return 0;
@@ -446,8 +469,8 @@ int side_nodes(int elem_type, int side, int* nodes) {
 int side_reinit(int elem_type, const double* X, int side, int qorder, SideData& sd) {
   int sn[9];
   const int ns = side_nodes(elem_type, side, sn);
-  if (!ns) { set_error("side_reinit: HEX8/HEX27/TET10 sides only"); return -1; }
-  const bool q2 = ns == 9, tri = ns == 6;
+  if (!ns) { set_error("side_reinit: HEX8/HEX20/HEX27/TET10 sides only"); return -1; }
+  const bool q2 = ns == 9, tri = ns == 6, q8 = ns == 8;
   double gx[3], gw[3];
   const int np = tri ? 0 : gauss_1d(qorder, gx, gw);
   if (tri && qorder != 5 && qorder != 0) { set_error("TRI6 sides: QGauss FIFTH only"); return -1; }
@@ -474,6 +497,8 @@ int side_reinit(int elem_type, const double* X, int side, int qorder, SideData& 
       const double xi = pts[2 * p], eta = pts[2 * p + 1];
       if (tri) {
         tri6_shape(i, xi, eta, psi[i * nqf + p], dxi[i * nqf + p], deta[i * nqf + p]);
+      } else if (q8) {
+        quad8_shape(i, xi, eta, psi[i * nqf + p], dxi[i * nqf + p], deta[i * nqf + p]);
       } else if (q2) {
         psi[i * nqf + p] = quad(Q9_I0[i], xi) * quad(Q9_I1[i], eta);
         dxi[i * nqf + p] = dquad(Q9_I0[i], xi) * quad(Q9_I1[i], eta);
@@ -519,7 +544,7 @@ int side_reinit(int elem_type, const double* X, int side, int qorder, SideData& 
     const int a = sn[i];
     double node[3];
     if (tri) { node[0] = T10_REF[a][0]; node[1] = T10_REF[a][1]; node[2] = T10_REF[a][2]; }
-    else { node[0] = REF[q2 ? H27_I0[a] : H8_I0[a]]; node[1] = REF[q2 ? H27_I1[a] : H8_I1[a]]; node[2] = REF[q2 ? H27_I2[a] : H8_I2[a]]; }
+    else { const bool h27 = q2 || q8; node[0] = REF[h27 ? H27_I0[a] : H8_I0[a]]; node[1] = REF[h27 ? H27_I1[a] : H8_I1[a]]; node[2] = REF[h27 ? H27_I2[a] : H8_I2[a]]; }
     for (int p = 0; p < nqf; ++p)
       for (int d = 0; d < 3; ++d) sd.ref[3 * p + d] += psi[i * nqf + p] * node[d];
   }

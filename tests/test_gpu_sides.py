@@ -14,6 +14,8 @@ EX6 = [
     ("hex27_ex6_perturbed", 27, (3, 2, 2), (1, 0.004, 7), (0.3, -0.2, -1.0)),
     ("hex8_ex6", 8, (5, 3, 2), None, (0.0, 0.0, -1.0)),
     ("hex8_ex6_perturbed", 8, (4, 3, 3), (1, 0.004, 11), (0.3, -0.2, -1.0)),
+    ("hex20_ex6", 20, (4, 3, 2), None, (0.0, 0.0, -1.0)),  # QUAD8 sides of the serendipity hex
+    ("hex20_ex6_perturbed", 20, (3, 2, 2), (1, 0.004, 5), (0.3, -0.2, -1.0)),
 ]
 
 
@@ -52,7 +54,7 @@ def test_ex6_with_the_traction_term(name, etype, dims, skew, g):
     ctx.close()
 
 
-@pytest.mark.parametrize("etype,dims,skew", [(27, (3, 3, 2), None), (27, (3, 2, 2), (1, 0.03, 5)), (8, (4, 4, 3), (1, 0.05, 9))])
+@pytest.mark.parametrize("etype,dims,skew", [(27, (3, 3, 2), None), (27, (3, 2, 2), (1, 0.03, 5)), (8, (4, 4, 3), (1, 0.05, 9)), (20, (3, 3, 2), (1, 0.03, 2))])
 def test_neumann_flux_with_two_loaded_sides_per_corner_element(etype, dims, skew):
     F, O = _mods()
     m, s = make_case(etype, dims, skew=skew, dirichlet=(4,))
@@ -95,7 +97,7 @@ def _all_boundary_sides(m):
     return np.concatenate(es), np.concatenate(ss)
 
 
-@pytest.mark.parametrize("etype,dims,skew,qorder", [(27, (4, 3, 2), None, 0), (27, (3, 3, 3), (1, 0.04, 7), 0), (8, (5, 4, 3), (1, 0.05, 3), 3)])
+@pytest.mark.parametrize("etype,dims,skew,qorder", [(27, (4, 3, 2), None, 0), (27, (3, 3, 3), (1, 0.04, 7), 0), (8, (5, 4, 3), (1, 0.05, 3), 3), (20, (3, 3, 2), (1, 0.04, 4), 0)])
 def test_penalty_sides_match_the_ex3_loop(etype, dims, skew, qorder):
     """feasm_set_side_penalty (introduction_ex3.C:386-455 on HEX sides) against the oracle: element matrices and the
     assembled system of the penalty form of ex4 (no constraint rows; penalty 1e10 on every boundary side)."""

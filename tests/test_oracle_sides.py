@@ -23,7 +23,7 @@ def _mesh(etype, dims, skew):
 
 
 @pytest.mark.parametrize("skew", [None, "skewfunc", "perturbed"])
-@pytest.mark.parametrize("etype,qorder", [(O.HEX8, 3), (O.HEX8, 5), (O.HEX27, 5)])
+@pytest.mark.parametrize("etype,qorder", [(O.HEX8, 3), (O.HEX8, 5), (O.HEX27, 5), (O.HEX20, 5), (O.HEX20, 3)])
 def test_side_shapes_reproduce_functions_of_the_side_points(etype, qorder, skew):
     m = _mesh(etype, (2, 2, 2), skew)
     xyz, conn, _ = m.arrays()
@@ -38,7 +38,7 @@ def test_side_shapes_reproduce_functions_of_the_side_points(etype, qorder, skew)
             assert np.abs(d["phi"].sum(0) - 1).max() < 1e-14                 # partition of unity on the side
             assert np.abs(d["phi"].T @ X - d["xyz"]).max() < 1e-14           # the parent map hits the side points
             assert np.abs(d["phi"].T @ lin(X) - lin(d["xyz"])).max() < 1e-13
-            if etype == O.HEX27 and skew != "perturbed":                    # quadratic reproduction needs an affine map
+            if etype in (O.HEX27, O.HEX20) and skew != "perturbed":         # quadratic reproduction needs an affine map
                 assert np.abs(d["phi"].T @ quad(X) - quad(d["xyz"])).max() < 1e-13
             # the mapped points lie on the reference face of that side
             axis, val = [(2, -1), (1, -1), (0, 1), (1, 1), (0, -1), (2, 1)][s]
@@ -46,7 +46,7 @@ def test_side_shapes_reproduce_functions_of_the_side_points(etype, qorder, skew)
 
 
 @pytest.mark.parametrize("skew", [None, "skewfunc", "perturbed"])
-@pytest.mark.parametrize("etype,qorder", [(O.HEX8, 3), (O.HEX27, 5)])
+@pytest.mark.parametrize("etype,qorder", [(O.HEX8, 3), (O.HEX27, 5), (O.HEX20, 5)])
 def test_closed_surface_identities(etype, qorder, skew):
     m = _mesh(etype, (2, 2, 2), skew)
     xyz, conn, _ = m.arrays()
@@ -74,7 +74,7 @@ def test_side_rule_is_the_tensor_rule_i_fastest():
     assert np.abs(d["JxW"] - 1.0).max() < 1e-15 and np.abs(d["normals"] - [0, 0, -1]).max() < 1e-15
 
 
-@pytest.mark.parametrize("etype,dims", [(O.HEX27, (4, 3, 2)), (O.HEX8, (5, 3, 2))])
+@pytest.mark.parametrize("etype,dims", [(O.HEX27, (4, 3, 2)), (O.HEX8, (5, 3, 2)), (O.HEX20, (3, 3, 2))])
 def test_ex6_traction_face_and_total_load(etype, dims):
     m = O.Mesh(etype, *dims, bounds=(0, 1, 0, 0.3, 0, 0.1))
     e, sd = m.boundary_sides(2)                       # BOUNDARY_ID_MAX_X, systems_of_equations_ex6.C:79
@@ -107,7 +107,7 @@ def _all_boundary_sides(m):
     return np.concatenate(es), np.concatenate(ss)
 
 
-@pytest.mark.parametrize("etype,qorder,nv", [(O.HEX27, 5, 1), (O.HEX8, 3, 1), (O.HEX8, 3, 3)])
+@pytest.mark.parametrize("etype,qorder,nv", [(O.HEX27, 5, 1), (O.HEX8, 3, 1), (O.HEX8, 3, 3), (O.HEX20, 5, 1)])
 def test_penalty_term_is_the_ex3_loop(etype, qorder, nv):
     """introduction_ex3.C:437-453 on the sides of a 3D element, against an independent numpy evaluation from side_reinit."""
     m = _mesh(etype, (3, 2, 2), "perturbed")
