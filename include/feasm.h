@@ -28,10 +28,11 @@ extern "C" {
 
 #define FEASM_VERSION 1
 
-/* element types; the value is the node count (libMesh ElemType HEX8 / HEX27 / TET10) */
+/* element types; the value is the node count (libMesh ElemType HEX8 / HEX20 / HEX27 / TET10 / PRISM18) */
 #define FEASM_HEX8 8
 #define FEASM_HEX27 27
 #define FEASM_TET10 10
+#define FEASM_PRISM18 18 /* triangular prism, TRI6 x EDGE3 (cell_prism18.C, fe_lagrange_shape_3D.C:1077-1094); volume terms only */
 #define FEASM_HEX20 20 /* serendipity hex (cell_hex20.C, fe_lagrange_shape_3D.C:848-925); QUAD8 sides (fe_lagrange_shape_2D.C:434-471) */
 
 /* problems (the Ke/Fe contraction that runs per element) */

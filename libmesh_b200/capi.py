@@ -14,7 +14,7 @@ import numpy as np
 _HERE = os.path.dirname(os.path.abspath(__file__))
 LIB_PATH = os.environ.get("FEASM_LIB") or os.path.join(_HERE, "libfeasm.so")  # FEASM_LIB: development builds
 
-HEX8, HEX27, TET10, HEX20 = 8, 27, 10, 20
+HEX8, HEX27, TET10, HEX20, PRISM18 = 8, 27, 10, 20, 18
 POISSON, ELASTICITY = 1, 2
 FORCING_NONE, FORCING_EX4_FD, FORCING_TABULATED = 0, 1, 2
 CONSTRAIN_HETEROGENEOUS, CONSTRAIN_HOMOGENEOUS = 0, 1

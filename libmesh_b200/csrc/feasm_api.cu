@@ -160,7 +160,7 @@ void feasm_destroy(feasm_ctx* ctx) {
 
 int feasm_set_mesh(feasm_ctx* ctx, int elem_type, int64_t n_elem, int64_t n_nodes, const double* xyz, const uint32_t* conn) {
   if (!ctx) return FEASM_ERR_ARG;
-  if (elem_type != FEASM_HEX8 && elem_type != FEASM_HEX27 && elem_type != FEASM_TET10 && elem_type != FEASM_HEX20)
+  if (elem_type != FEASM_HEX8 && elem_type != FEASM_HEX27 && elem_type != FEASM_TET10 && elem_type != FEASM_HEX20 && elem_type != FEASM_PRISM18)
     return feasm_fail(ctx, FEASM_ERR_ARG, "unsupported element type (HEX8, HEX20, HEX27, TET10)");
   if (n_elem < 0 || n_nodes <= 0 || !xyz || !conn) return feasm_fail(ctx, FEASM_ERR_ARG, "bad mesh arguments");
   FEASM_CUDA(ctx, cudaSetDevice(ctx->device));

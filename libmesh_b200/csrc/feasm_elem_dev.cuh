@@ -66,11 +66,16 @@ __constant__ AffineCheck c_affine_hex20[16] = {  // cell_hex20.C:119-153
 __constant__ AffineCheck c_affine_tet10[6] = {{1, 0, 4, 0, 1, 2}, {2, 1, 5, 1, 1, 2}, {2, 0, 6, 0, 1, 2},  // cell_tet10.C:143-170
                                               {3, 0, 7, 0, 1, 2}, {3, 1, 8, 1, 1, 2}, {3, 2, 9, 2, 1, 2}};
 
+__constant__ AffineCheck c_affine_prism18[14] = {  // cell_prism18.C:122-151
+    {3, 0, 4, 1, 1, 1},    {3, 0, 5, 2, 1, 1},    {3, 0, 9, 0, .5f, 1},  {3, 0, 10, 1, .5f, 1}, {3, 0, 11, 2, .5f, 1}, {3, 0, 15, 6, .5f, 1}, {3, 0, 16, 7, .5f, 1},
+    {3, 0, 17, 8, .5f, 1}, {1, 0, 6, 0, .5f, 1},  {1, 0, 12, 3, .5f, 1}, {2, 0, 8, 0, .5f, 1},  {2, 0, 14, 3, .5f, 1}, {2, 1, 7, 1, .5f, 1},  {2, 1, 13, 4, .5f, 1}};
+
 template <int NPE>
 __device__ __forceinline__ bool affine_check_lane(const double* X, int lane) {
-  constexpr int N = NPE == 27 ? 23 : (NPE == 20 ? 16 : (NPE == 8 ? 4 : 6));
+  constexpr int N = NPE == 27 ? 23 : (NPE == 20 ? 16 : (NPE == 18 ? 14 : (NPE == 8 ? 4 : 6)));
   if (lane >= N) return true;
-  const AffineCheck c = NPE == 27 ? c_affine_hex27[lane] : (NPE == 20 ? c_affine_hex20[lane] : (NPE == 8 ? c_affine_hex8[lane] : c_affine_tet10[lane]));
+  const AffineCheck c = NPE == 27 ? c_affine_hex27[lane]
+                                  : (NPE == 20 ? c_affine_hex20[lane] : (NPE == 18 ? c_affine_prism18[lane] : (NPE == 8 ? c_affine_hex8[lane] : c_affine_tet10[lane])));
   double na = 0., nb = 0., nd = 0.;
 #pragma unroll
   for (int d = 0; d < 3; ++d) {

@@ -961,6 +961,8 @@ static int launch_element_kernel(feasm_ctx* ctx, const feasm_params& p, const do
     if (ctx->elem_type == FEASM_HEX8 && ctx->tab_nq == 27) return launch_poisson<8, 27, 16>(ctx, p, d_f, e0, e1, d_kf, rs, cm, fused);
     // HEX20 (serendipity): 16 rows of Ke through DMMA, the last 4 through DFMA (ElemCfg::REM)
     if (ctx->elem_type == FEASM_HEX20 && ctx->tab_nq == 27) return launch_poisson<20, 27, 12>(ctx, p, d_f, e0, e1, d_kf, rs, cm, fused);
+    // PRISM18 with the 21-point rule: 16 rows of Ke through DMMA, 2 through DFMA
+    if (ctx->elem_type == FEASM_PRISM18 && ctx->tab_nq == 21) return launch_poisson<18, 21, 12>(ctx, p, d_f, e0, e1, d_kf, rs, cm, fused);
     if (ctx->elem_type == FEASM_TET10 && ctx->tab_nq == 14) {
       static const bool one_per_warp = getenv("FEASM_TET10_PACK") && atoi(getenv("FEASM_TET10_PACK")) == 0;  // A/B knob
       if (!one_per_warp) {
@@ -976,6 +978,7 @@ static int launch_element_kernel(feasm_ctx* ctx, const feasm_params& p, const do
     if (ctx->n_vars != 3) return feasm_fail(ctx, FEASM_ERR_ARG, "elasticity needs 3 variables per node");
     if (ctx->elem_type == FEASM_HEX27 && ctx->tab_nq == 27) return launch_elasticity<27, 27, FEASM_ELAST_WARPS>(ctx, p, e0, e1, d_kf, rs);
     if (ctx->elem_type == FEASM_HEX20 && ctx->tab_nq == 27) return launch_elasticity<20, 27, 12>(ctx, p, e0, e1, d_kf, rs);
+    if (ctx->elem_type == FEASM_PRISM18 && ctx->tab_nq == 21) return launch_elasticity<18, 21, 12>(ctx, p, e0, e1, d_kf, rs);
     if (ctx->elem_type == FEASM_HEX8 && ctx->tab_nq == 8) return launch_elasticity<8, 8, 16>(ctx, p, e0, e1, d_kf, rs);
     if (ctx->elem_type == FEASM_TET10 && ctx->tab_nq == 14) return launch_elasticity<10, 14, 16>(ctx, p, e0, e1, d_kf, rs);
     return feasm_fail(ctx, FEASM_ERR_ARG, "no elasticity kernel for this element type / quadrature order");

@@ -71,23 +71,24 @@ __global__ void k_halo_mark_rows(const uint32_t* __restrict__ gid, int64_t r0, i
   const int64_t r = r0 + blockIdx.x * (int64_t)blockDim.x + threadIdx.x;
   if (r < r1 && gid[r] < n_global) flag[gid[r]] = 1;
 }
-__global__ void k_halo_pack(const double* __restrict__ x, const uint32_t* __restrict__ rows, uint64_t n, double* __restrict__ out) {
+// `lim`: length of the indexed vector (checked by the FEASM_DEBUG_BOUNDS build only)
+__global__ void k_halo_pack(const double* __restrict__ x, const uint32_t* __restrict__ rows, uint64_t n, double* __restrict__ out, uint64_t lim) {
   const uint64_t i = blockIdx.x * (uint64_t)blockDim.x + threadIdx.x;
-  if (i < n) out[i] = x[rows[i]];
+  if (i < n) { FEASM_DEV_ASSERT(rows[i] < lim); out[i] = x[rows[i]]; }
 }
-__global__ void k_halo_unpack(const double* __restrict__ in, const uint32_t* __restrict__ gids, uint64_t n, double* __restrict__ xfull) {
+__global__ void k_halo_unpack(const double* __restrict__ in, const uint32_t* __restrict__ gids, uint64_t n, double* __restrict__ xfull, uint64_t lim) {
   const uint64_t i = blockIdx.x * (uint64_t)blockDim.x + threadIdx.x;
-  if (i < n) xfull[gids[i]] = in[i];
+  if (i < n) { FEASM_DEV_ASSERT(gids[i] < lim); xfull[gids[i]] = in[i]; }
 }
 // u_loc[r] = x_full[global id of local row r]
-__global__ void k_halo_localize(const double* __restrict__ xfull, const uint32_t* __restrict__ gid, int64_t n_rows, double* __restrict__ uloc) {
+__global__ void k_halo_localize(const double* __restrict__ xfull, const uint32_t* __restrict__ gid, int64_t n_rows, double* __restrict__ uloc, uint64_t lim) {
   const int64_t r = blockIdx.x * (int64_t)blockDim.x + threadIdx.x;
-  if (r < n_rows) uloc[r] = xfull[gid[r]];
+  if (r < n_rows) { FEASM_DEV_ASSERT(gid[r] < lim); uloc[r] = xfull[gid[r]]; }
 }
 // r[rows[i]] += in[i]; the rows of one peer's message are distinct, peers are added one launch after the other (fixed order)
-__global__ void k_halo_add_rows(const double* __restrict__ in, const uint32_t* __restrict__ rows, uint64_t n, double* __restrict__ r) {
+__global__ void k_halo_add_rows(const double* __restrict__ in, const uint32_t* __restrict__ rows, uint64_t n, double* __restrict__ r, uint64_t lim) {
   const uint64_t i = blockIdx.x * (uint64_t)blockDim.x + threadIdx.x;
-  if (i < n) r[rows[i]] += in[i];
+  if (i < n) { FEASM_DEV_ASSERT(rows[i] < lim); r[rows[i]] += in[i]; }
 }
 
 feasm_halo* halo_of(feasm_ctx* ctx) {
@@ -150,10 +151,10 @@ int feasm_halo_exchange(feasm_ctx* ctx, const double* d_x, const double** d_xful
   if (ctx->n_owned) FEASM_CUDA(ctx, cudaMemcpyAsync(h->d_xfull + h->first, d_x, sizeof(double) * ctx->n_owned, cudaMemcpyDeviceToDevice, ctx->stream));
   if (ctx->comm && h->n_peers) {
     const uint64_t ns = h->send_ptr.back(), nr = h->recv_ptr.back();
-    if (ns) k_halo_pack<<<blocks(ns), 256, 0, ctx->stream>>>(d_x, h->d_send_rows, ns, h->d_send);
+    if (ns) k_halo_pack<<<blocks(ns), 256, 0, ctx->stream>>>(d_x, h->d_send_rows, ns, h->d_send, (uint64_t)ctx->n_owned);
     int rc = feasm_comm_p2p(ctx, h->n_peers, h->peer.data(), h->send_ptr.data(), h->d_send, h->recv_ptr.data(), h->d_recv, 8, ctx->stream);
     if (rc) return rc;
-    if (nr) k_halo_unpack<<<blocks(nr), 256, 0, ctx->stream>>>(h->d_recv, h->d_recv_gids, nr, h->d_xfull);
+    if (nr) k_halo_unpack<<<blocks(nr), 256, 0, ctx->stream>>>(h->d_recv, h->d_recv_gids, nr, h->d_xfull, h->n_global);
     FEASM_CUDA(ctx, cudaGetLastError());
   }
   *d_xfull = h->d_xfull;
@@ -175,17 +176,17 @@ int feasm_residual_distributed(feasm_ctx* ctx, const double* d_u, double* d_r) {
   const double* xf = nullptr;
   rc = feasm_halo_exchange(ctx, d_u, &xf);
   if (rc) return rc;
-  if (ctx->n_rows) k_halo_localize<<<blocks(ctx->n_rows), 256, 0, ctx->stream>>>(xf, ctx->d_gid, ctx->n_rows, h->d_uloc);
+  if (ctx->n_rows) k_halo_localize<<<blocks(ctx->n_rows), 256, 0, ctx->stream>>>(xf, ctx->d_gid, ctx->n_rows, h->d_uloc, h->n_global);
   rc = feasm_launch_row_residual(ctx, h->d_uloc, h->d_rloc);
   if (rc) return rc;
   if (ctx->n_peers) {
     const uint64_t ns = h->vsend_ptr.back();
-    if (ns) k_halo_pack<<<blocks(ns), 256, 0, ctx->stream>>>(h->d_rloc, h->d_vsend_rows, ns, h->d_vsend);
+    if (ns) k_halo_pack<<<blocks(ns), 256, 0, ctx->stream>>>(h->d_rloc, h->d_vsend_rows, ns, h->d_vsend, (uint64_t)ctx->n_rows);
     rc = feasm_comm_p2p(ctx, ctx->n_peers, ctx->peer_rank.data(), h->vsend_ptr.data(), h->d_vsend, h->vrecv_ptr.data(), h->d_vrecv, 8, ctx->stream);
     if (rc) return rc;
     for (int p = 0; p < ctx->n_peers; ++p) {
       const uint64_t r0 = h->vrecv_ptr[p], n = h->vrecv_ptr[p + 1] - r0;
-      if (n) k_halo_add_rows<<<blocks(n), 256, 0, ctx->stream>>>(h->d_vrecv + r0, h->d_vrecv_rows + r0, n, h->d_rloc);
+      if (n) k_halo_add_rows<<<blocks(n), 256, 0, ctx->stream>>>(h->d_vrecv + r0, h->d_vrecv_rows + r0, n, h->d_rloc, (uint64_t)ctx->n_owned);
     }
   }
   FEASM_CUDA(ctx, cudaGetLastError());
@@ -329,7 +330,7 @@ double* feasm_halo_pack(feasm_ctx* ctx, const double* d_x, uint64_t* n_doubles) 
   feasm_halo* h = ctx->halo;
   if (cudaSetDevice(ctx->device) != cudaSuccess) return nullptr;
   const uint64_t ns = h->send_ptr.back();
-  if (ns) k_halo_pack<<<blocks(ns), 256, 0, ctx->stream>>>(d_x, h->d_send_rows, ns, h->d_send);
+  if (ns) k_halo_pack<<<blocks(ns), 256, 0, ctx->stream>>>(d_x, h->d_send_rows, ns, h->d_send, (uint64_t)ctx->n_owned);
   if (n_doubles) *n_doubles = ns;
   return h->d_send;
 }
@@ -346,7 +347,7 @@ int feasm_halo_unpack(feasm_ctx* ctx) {
   feasm_halo* h = ctx->halo;
   FEASM_CUDA(ctx, cudaSetDevice(ctx->device));
   const uint64_t nr = h->recv_ptr.back();
-  if (nr) k_halo_unpack<<<blocks(nr), 256, 0, ctx->stream>>>(h->d_recv, h->d_recv_gids, nr, h->d_xfull);
+  if (nr) k_halo_unpack<<<blocks(nr), 256, 0, ctx->stream>>>(h->d_recv, h->d_recv_gids, nr, h->d_xfull, h->n_global);
   FEASM_CUDA(ctx, cudaGetLastError());
   return FEASM_OK;
 }

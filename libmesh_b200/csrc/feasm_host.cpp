@@ -104,9 +104,9 @@ int feasm_cube_sizes(int elem_type, int nx, int ny, int nz, int64_t* n_elem, int
     if (n_nodes) *n_nodes = corners + faces + cells + hex_edges + 4 * faces + 14 * cells;
     return FEASM_OK;
   }
-  if ((elem_type != FEASM_HEX8 && elem_type != FEASM_HEX27 && elem_type != FEASM_HEX20) || nx < 1 || ny < 1 || nz < 1) return FEASM_ERR_ARG;
+  if ((elem_type != FEASM_HEX8 && elem_type != FEASM_HEX27 && elem_type != FEASM_HEX20 && elem_type != FEASM_PRISM18) || nx < 1 || ny < 1 || nz < 1) return FEASM_ERR_ARG;
   const int s = elem_type == FEASM_HEX8 ? 1 : 2;
-  if (n_elem) *n_elem = (int64_t)nx * ny * nz;
+  if (n_elem) *n_elem = (int64_t)nx * ny * nz * (elem_type == FEASM_PRISM18 ? 2 : 1);  // two prisms per lattice cell
   if (n_nodes) *n_nodes = (int64_t)(s * nx + 1) * (s * ny + 1) * (s * nz + 1);
   if (n_nodes && elem_type == FEASM_HEX20) {  // the HEX27 lattice without its face and cell centres: corners + one node per edge
     const int64_t X = nx, Y = ny, Z = nz;
@@ -167,6 +167,28 @@ int feasm_build_cube(int elem_type, int nx, int ny, int nz, const double bounds[
       if (mask)  // boundary ids: 0 z-min, 1 y-min, 2 x-max, 3 y-max, 4 x-min, 5 z-max
         mask[id] = (uint8_t)((k == 0) << 0 | (j == 0) << 1 | (i == gx) << 2 | (j == gy) << 3 | (i == 0) << 4 | (k == gz) << 5);
     }
+  if (conn && elem_type == FEASM_PRISM18) {
+    // build_cube(PRISM18) (src/mesh/mesh_generation.C:1634-1756): every cell of the HEX27 lattice is cut along the diagonal
+    // (i+2, j) - (i, j+2) into two prisms, first the one at the cell's corner (i, j), then the one at (i+2, j+2).  With the
+    // reference prism's nodes at (xi, eta, zeta) (triangle (0,0) (1,0) (0,1) times [-1, 1]), the lattice offset of a node is
+    // the affine image of 2 (xi, eta): first prism (2 xi, 2 eta), second (2 - 2 eta, 2 xi + 2 eta); zeta + 1 along k.
+    static const signed char kPrism2[18][3] = {{0, 0, -1}, {2, 0, -1}, {0, 2, -1}, {0, 0, 1}, {2, 0, 1}, {0, 2, 1}, {1, 0, -1}, {1, 1, -1}, {0, 1, -1},
+                                               {0, 0, 0},  {2, 0, 0},  {0, 2, 0},  {1, 0, 1}, {1, 1, 1}, {0, 1, 1}, {1, 0, 0},  {1, 1, 0},  {0, 1, 0}};  // (2 xi, 2 eta, zeta)
+    int64_t off[2][18];
+    for (int a = 0; a < 18; ++a) {
+      const int x2 = kPrism2[a][0], e2 = kPrism2[a][1], dk = kPrism2[a][2] + 1;
+      off[0][a] = x2 + sx * (e2 + sy * (int64_t)dk);
+      off[1][a] = (2 - e2) + sx * ((x2 + e2) + sy * (int64_t)dk);
+    }
+    const int64_t ncell = (int64_t)nx * ny * nz;
+    for (int64_t c = 0; c < ncell; ++c) {
+      const int64_t ei = c % nx, ej = (c / nx) % ny, ek = c / ((int64_t)nx * ny);
+      const int64_t corner = 2 * ei + sx * (2 * ej + sy * (2 * ek));
+      for (int h = 0; h < 2; ++h)
+        for (int a = 0; a < 18; ++a) conn[(2 * c + h) * 18 + a] = (uint32_t)(corner + off[h][a]);
+    }
+    return FEASM_OK;
+  }
   if (conn) {
     const int npe = elem_type;
     int64_t off[27];

@@ -302,17 +302,18 @@ static int generate_tet10_cube(feasm_ctx* ctx, const Lattice& L, int64_t n_elem,
 
 int feasm_generate_cube(feasm_ctx* ctx, int elem_type, int nx, int ny, int nz, const double bounds[6]) {
   if (!ctx) return FEASM_ERR_ARG;
-  if (elem_type != FEASM_HEX8 && elem_type != FEASM_HEX27 && elem_type != FEASM_TET10 && elem_type != FEASM_HEX20)
-    return feasm_fail(ctx, FEASM_ERR_ARG, "feasm_generate_cube: HEX8 / HEX20 / HEX27 / TET10");
+  if (elem_type != FEASM_HEX8 && elem_type != FEASM_HEX27 && elem_type != FEASM_TET10 && elem_type != FEASM_HEX20 && elem_type != FEASM_PRISM18)
+    return feasm_fail(ctx, FEASM_ERR_ARG, "feasm_generate_cube: HEX8 / HEX20 / HEX27 / TET10 / PRISM18");
   int64_t n_elem = 0, n_nodes = 0;
   if (!bounds || feasm_cube_sizes(elem_type, nx, ny, nz, &n_elem, &n_nodes)) return feasm_fail(ctx, FEASM_ERR_ARG, "bad build_cube arguments");
   if (n_nodes >= 0xffffffffll || n_elem * elem_type >= 0xffffffffll) return feasm_fail(ctx, FEASM_ERR_ARG, "mesh too large for 32-bit ids");
   FEASM_CUDA(ctx, cudaSetDevice(ctx->device));
-  if (elem_type == FEASM_HEX20) {
-    // the compacted HEX20 numbering (lattice points with at most one odd index, ascending) is made by the host generator
-    // and uploaded; dof numbering, Dirichlet data and the pattern are then built on the device as for the other types
+  if (elem_type == FEASM_HEX20 || elem_type == FEASM_PRISM18) {
+    // the compacted HEX20 numbering (lattice points with at most one odd index, ascending) and the two-prisms-per-cell
+    // connectivity are made by the host generator and uploaded; dof numbering, Dirichlet data and the pattern are then
+    // built on the device as for the other types
     std::vector<double> xyz((size_t)n_nodes * 3);
-    std::vector<uint32_t> conn((size_t)n_elem * 20);
+    std::vector<uint32_t> conn((size_t)n_elem * elem_type);
     std::vector<uint8_t> mask((size_t)n_nodes);
     if (feasm_build_cube(elem_type, nx, ny, nz, bounds, xyz.data(), conn.data(), mask.data())) return feasm_fail(ctx, FEASM_ERR_ARG, "bad build_cube arguments");
     int rc = feasm_set_mesh(ctx, elem_type, n_elem, n_nodes, xyz.data(), conn.data());

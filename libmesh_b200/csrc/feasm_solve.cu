@@ -158,7 +158,7 @@ k_spmv_stream(const uint64_t* __restrict__ row_ptr, const uint32_t* __restrict__
 #pragma unroll
         for (int u = 0; u < 4; ++u) {
           const uint64_t k = k0 + lane + 32 * u;
-          if (k < c1) prod[k - c0] = v[u] * xv[u];
+          if (k < c1) { FEASM_DEV_ASSERT(k - c0 < (uint64_t)CH); prod[k - c0] = v[u] * xv[u]; }
         }
 #pragma unroll
         for (int u = 0; u < 4; ++u) { v[u] = vn[u]; c[u] = cn[u]; }
@@ -170,6 +170,7 @@ k_spmv_stream(const uint64_t* __restrict__ row_ptr, const uint32_t* __restrict__
                       // 58 % of its wavefronts from shared memory).  (Four accumulators per row measured slower: 4.40 -> 3.88 TB/s.)
         uint32_t i = (uint32_t)(lo - c0);
         const uint32_t e = (uint32_t)(hi - c0);
+        FEASM_DEV_ASSERT(e <= (uint32_t)CH);
         if (i & 1) { acc += prod[i]; ++i; }
         for (; i + 2 <= e; i += 2) {
           const double2 t = *reinterpret_cast<const double2*>(prod + i);

@@ -155,6 +155,50 @@ bool feasm_make_tables(int elem_type, int qorder, FeasmTables& t, std::string& e
     }
     return true;
   }
+  if (elem_type == FEASM_PRISM18) {
+    // QGauss(3, FIFTH) on a prism (quadrature_gauss_3D.C:507-527): the 7-point degree-5 triangle rule (centroid and two
+    // orbits (a,a), (a,1-2a), (1-2a,a)) times the 3-point Gauss rule, the 1D rule outermost (quadrature.C:310-332).
+    if (qorder != 5 && qorder != 4) { err = "PRISM18: only the FIFTH-order Gauss rule is built"; return false; }
+    double gx[3], gw[3];
+    gauss1d(5, gx, gw);
+    const double r15 = std::sqrt(15.);
+    const double ta[2] = {2. / 7 + r15 / 21, 2. / 7 - r15 / 21}, tw[2] = {31. / 480 + r15 / 2400, 31. / 480 - r15 / 2400};
+    double tp[7][2], tww[7];
+    tp[0][0] = tp[0][1] = 1. / 3; tww[0] = 9. / 80;
+    for (int o = 0; o < 2; ++o) {
+      const double P[3][2] = {{ta[o], ta[o]}, {ta[o], 1 - 2 * ta[o]}, {1 - 2 * ta[o], ta[o]}};
+      for (int i = 0; i < 3; ++i) { tp[1 + 3 * o + i][0] = P[i][0]; tp[1 + 3 * o + i][1] = P[i][1]; tww[1 + 3 * o + i] = tw[o]; }
+    }
+    t.nq = 21;
+    t.qp.resize(63); t.qw.resize(21);
+    for (int j = 0; j < 3; ++j)
+      for (int i = 0; i < 7; ++i) {
+        const int q = 7 * j + i;
+        t.qp[3 * q] = tp[i][0]; t.qp[3 * q + 1] = tp[i][1]; t.qp[3 * q + 2] = gx[j];
+        t.qw[q] = tww[i] * gw[j];
+      }
+    // PRISM18 = TRI6 x EDGE3 (fe_lagrange_shape_3D.C:1077-1094, :2478-2510), written from where the node sits: in the
+    // triangle a vertex v (L_v (2 L_v - 1)) or the middle of the edge (u, v) (4 L_u L_v), along the axis at -1, +1 or 0.
+    // Node order of cell_prism18.h: bottom vertices, top vertices, bottom edges, vertical edges, top edges, mid layer.
+    static const signed char kTri[18][2] = {{0, -1}, {1, -1}, {2, -1}, {0, -1}, {1, -1}, {2, -1}, {0, 1}, {1, 2}, {0, 2}, {0, -1}, {1, -1}, {2, -1},
+                                            {0, 1}, {1, 2}, {0, 2}, {0, 1}, {1, 2}, {0, 2}};
+    static const signed char kAx[18] = {-1, -1, -1, 1, 1, 1, -1, -1, -1, 0, 0, 0, 1, 1, 1, 0, 0, 0};
+    const double dL[3][2] = {{-1, -1}, {1, 0}, {0, 1}};  // barycentric gradients wrt (xi, eta): L0 = 1 - xi - eta, L1 = xi, L2 = eta
+    const size_t sz = (size_t)18 * t.nq;
+    t.phi.resize(sz); t.dxi.resize(sz); t.deta.resize(sz); t.dzeta.resize(sz);
+    for (int a = 0; a < 18; ++a)
+      for (int q = 0; q < t.nq; ++q) {
+        const double L[3] = {1. - t.qp[3 * q] - t.qp[3 * q + 1], t.qp[3 * q], t.qp[3 * q + 1]};
+        double tv, tdx, tde;
+        const int u = kTri[a][0], v = kTri[a][1];
+        if (v < 0) { tv = L[u] * (2. * L[u] - 1.); tdx = (4. * L[u] - 1.) * dL[u][0]; tde = (4. * L[u] - 1.) * dL[u][1]; }
+        else { tv = 4. * L[u] * L[v]; tdx = 4. * (L[u] * dL[v][0] + dL[u][0] * L[v]); tde = 4. * (L[u] * dL[v][1] + dL[u][1] * L[v]); }
+        const V1 Z = lagrange1d(2, kAx[a], t.qp[3 * q + 2]);
+        const size_t o = (size_t)a * t.nq + q;
+        t.phi[o] = tv * Z.v; t.dxi[o] = tdx * Z.v; t.deta[o] = tde * Z.v; t.dzeta[o] = tv * Z.d;
+      }
+    return true;
+  }
   err = "unknown element type";
   return false;
 }

@@ -28,6 +28,7 @@ extern "C" {
 #define ORC_HEX27 27
 #define ORC_TET10 10
 #define ORC_HEX20 20
+#define ORC_PRISM18 18
 
 /* problems */
 #define ORC_POISSON_EX4 1    /* examples/introduction/introduction_ex4/introduction_ex4.C:313-563 */

@@ -13,7 +13,7 @@ import numpy as np
 
 _DIR = os.path.dirname(os.path.abspath(__file__))
 
-HEX8, HEX27, TET10, HEX20 = 8, 27, 10, 20
+HEX8, HEX27, TET10, HEX20, PRISM18 = 8, 27, 10, 20, 18
 POISSON_EX4, ELASTICITY_EX6, LAPLACE = 1, 2, 3
 FORCING_FD, FORCING_TABULATED = 0, 1
 

@@ -45,6 +45,9 @@ static int gauss_1d(int qorder, double* x, double* w) {
   }
 }
 
+static int tri_rule_fifth(double* pts /*7*2*/, double* w /*7*/);
+static void tri6_shape(int i, double xi, double eta, double& v, double& dxi, double& deta);
+
 bool gauss_rule(int elem_type, int qorder, QRule& q) {
   if (elem_type == ORC_HEX8 || elem_type == ORC_HEX27 || elem_type == ORC_HEX20) {
     double x[3], w[3];
@@ -96,6 +99,27 @@ bool gauss_rule(int elem_type, int qorder, QRule& q) {
       set(off + 5, a[2], b, b);
       for (int j = 0; j < 6; ++j) q.w[off + j] = wt[2];
     }
+    return true;
+  }
+  if (elem_type == ORC_PRISM18) {
+    // quadrature_gauss_3D.C:507-527: QGauss(1, order) x QGauss(2, order) on TRI3 through QBase::tensor_product_prism
+    // (quadrature.C:310-332: the 1D rule outermost, point = (tri.x, tri.y, x_1D), weight = w_2D * w_1D)
+    if (qorder != 5) { set_error("prism quadrature: only FIFTH restated"); return false; }
+    double x[3], w[3], tp[14], tw[7];
+    const int n1 = gauss_1d(qorder, x, w);
+    const int n2 = tri_rule_fifth(tp, tw);
+    q.nq = n1 * n2;
+    q.pts.resize(3 * q.nq);
+    q.w.resize(q.nq);
+    int p = 0;
+    for (int j = 0; j < n1; j++)
+      for (int i = 0; i < n2; i++) {
+        q.pts[3 * p + 0] = tp[2 * i];
+        q.pts[3 * p + 1] = tp[2 * i + 1];
+        q.pts[3 * p + 2] = x[j];
+        q.w[p] = tw[i] * w[j];
+        p++;
+      }
     return true;
   }
   set_error("unknown element type");
@@ -207,6 +231,19 @@ void shape_table(int elem_type, int np, const double* pts, ShapeTable& t) {
           }
         }
       }
+    } else if (elem_type == ORC_PRISM18) {
+      // fe_lagrange_shape_3D.C:1077-1094 (values), :2478-2510 (derivatives): TRI6 SECOND in (xi, eta) times the 1D quadratic
+      // Lagrange function in zeta, with the reference's index tables
+      static const int i0[18] = {0, 0, 0, 1, 1, 1, 0, 0, 0, 2, 2, 2, 1, 1, 1, 2, 2, 2};
+      static const int i1[18] = {0, 1, 2, 0, 1, 2, 3, 4, 5, 0, 1, 2, 3, 4, 5, 3, 4, 5};
+      for (int i = 0; i < 18; ++i) {
+        double tv, tdx, tde;
+        tri6_shape(i1[i], xi, eta, tv, tdx, tde);
+        t.phi[i * np + p] = tv * quad(i0[i], zeta);
+        t.dxi[i * np + p] = tdx * quad(i0[i], zeta);
+        t.deta[i * np + p] = tde * quad(i0[i], zeta);
+        t.dzeta[i * np + p] = tv * dquad(i0[i], zeta);
+      }
     } else {  // TET10, fe_lagrange_shape_3D.C:961-1009, :2179-2330
       const double z1 = xi, z2 = eta, z3 = zeta;
       const double z0 = 1. - z1 - z2 - z3;
@@ -307,6 +344,21 @@ bool has_affine_map(int type, const double* X) {
     if (!rfe(v, sub(P(12), P(0))) || !rfe(v, sub(P(13), P(1))) || !rfe(v, sub(P(14), P(2))) || !rfe(v, sub(P(15), P(3)))) return false;
     v = divide(sub(P(3), P(0)), 2);
     if (!rfe(v, sub(P(11), P(0))) || !rfe(v, sub(P(9), P(1))) || !rfe(v, sub(P(17), P(5))) || !rfe(v, sub(P(19), P(4)))) return false;
+    return true;
+  }
+  if (type == ORC_PRISM18) {  // cell_prism18.C:122-151
+    P3 v = sub(P(3), P(0));
+    if (!rfe(v, sub(P(4), P(1))) || !rfe(v, sub(P(5), P(2)))) return false;
+    v = divide(v, 2);
+    if (!rfe(v, sub(P(9), P(0))) || !rfe(v, sub(P(10), P(1))) || !rfe(v, sub(P(11), P(2))) || !rfe(v, sub(P(15), P(6))) ||
+        !rfe(v, sub(P(16), P(7))) || !rfe(v, sub(P(17), P(8))))
+      return false;
+    v = divide(sub(P(1), P(0)), 2);
+    if (!rfe(v, sub(P(6), P(0))) || !rfe(v, sub(P(12), P(3)))) return false;
+    v = divide(sub(P(2), P(0)), 2);
+    if (!rfe(v, sub(P(8), P(0))) || !rfe(v, sub(P(14), P(3)))) return false;
+    v = divide(sub(P(2), P(1)), 2);
+    if (!rfe(v, sub(P(7), P(1))) || !rfe(v, sub(P(13), P(4)))) return false;
     return true;
   }
   // TET10, cell_tet10.C:143-170

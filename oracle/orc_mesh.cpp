@@ -75,7 +75,7 @@ static void renumber_nodes(Mesh& m, bool libmesh_order) {
 
 static bool build_cube(Mesh& m, int type, int nx, int ny, int nz, double xmin, double xmax, double ymin, double ymax,
                        double zmin, double zmax, bool libmesh_renumber) {
-  if (type != ORC_HEX8 && type != ORC_HEX27 && type != ORC_TET10 && type != ORC_HEX20) { set_error("build_cube: bad element type"); return false; }
+  if (type != ORC_HEX8 && type != ORC_HEX27 && type != ORC_TET10 && type != ORC_HEX20 && type != ORC_PRISM18) { set_error("build_cube: bad element type"); return false; }
   if (nx < 1 || ny < 1 || nz < 1) { set_error("build_cube: n < 1"); return false; }
   m.type = type;
   m.npe = type;
@@ -143,6 +143,19 @@ static bool build_cube(Mesh& m, int type, int nx, int ny, int nz, double xmin, d
     m.conn.resize((size_t)nhex * 20);
     for (int64_t h = 0; h < nhex; ++h)
       for (int a = 0; a < 20; ++a) m.conn[h * 20 + a] = hex[h * 27 + a];
+  } else if (type == ORC_PRISM18) {
+    // mesh_generation.C:1634-1756: every lattice cell gives two prisms split along the diagonal (i+2, j) - (i, j+2); with
+    // c = the HEX27 connectivity of the cell, the node picks of the two set_node lists are
+    //   first : (i,j) (i+2,j) (i,j+2) | top | mid-edges (i+1,j) (i+1,j+1) (i,j+1) | verticals | top mid-edges | mid-layer
+    static const int P1[18] = {0, 1, 3, 4, 5, 7, 8, 20, 11, 12, 13, 15, 16, 25, 19, 21, 26, 24};
+    static const int P2[18] = {1, 2, 3, 5, 6, 7, 9, 10, 20, 13, 14, 15, 17, 18, 25, 22, 23, 26};
+    m.n_elem = nhex * 2;
+    m.conn.resize((size_t)m.n_elem * 18);
+    for (int64_t h = 0; h < nhex; ++h)
+      for (int a = 0; a < 18; ++a) {
+        m.conn[(2 * h) * 18 + a] = hex[h * 27 + P1[a]];
+        m.conn[(2 * h + 1) * 18 + a] = hex[h * 27 + P2[a]];
+      }
   } else if (type != ORC_TET10) {
     m.n_elem = nhex;
     m.conn.swap(hex);
@@ -212,7 +225,7 @@ orc_mesh* orc_mesh_build_cube(int elem_type, int nx, int ny, int nz, double xmin
 }
 // A mesh given by its arrays (tests of meshes build_cube cannot make: locally refined meshes with hanging nodes)
 orc_mesh* orc_mesh_from_arrays(int elem_type, int64_t n_elem, int64_t n_nodes, const double* xyz, const uint32_t* conn, const uint8_t* mask) {
-  if ((elem_type != ORC_HEX8 && elem_type != ORC_HEX27 && elem_type != ORC_TET10 && elem_type != ORC_HEX20) || n_elem < 1 || n_nodes < 1 || !xyz || !conn) {
+  if ((elem_type != ORC_HEX8 && elem_type != ORC_HEX27 && elem_type != ORC_TET10 && elem_type != ORC_HEX20 && elem_type != ORC_PRISM18) || n_elem < 1 || n_nodes < 1 || !xyz || !conn) {
     orc::set_error("mesh_from_arrays: bad arguments");
     return nullptr;
   }

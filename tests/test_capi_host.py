@@ -36,7 +36,7 @@ def test_product_never_references_the_oracle():
                 assert "fe_oracle.h" not in txt and "liboracle" not in txt and "from oracle" not in txt and "import oracle" not in txt, f
 
 
-@pytest.mark.parametrize("etype", [F.HEX8, F.HEX27, F.HEX20])
+@pytest.mark.parametrize("etype", [F.HEX8, F.HEX27, F.HEX20, F.PRISM18])
 def test_build_cube_matches_oracle(etype):
     b = (-1, 1, 0, 0.3, 0, 0.1)
     xyz, conn, mask = F.build_cube(etype, 5, 3, 4, b)

@@ -37,6 +37,7 @@ SIZE_CASES = [
     ("hex8_24_q5", 8, (24, 24, 24), 5),
     ("tet10_12", 10, (12, 12, 12), 5),           # 41 472 tets, irregular rows
     ("hex20_24", 20, (24, 24, 24), 0),           # serendipity hex at size (several waves, uint8 position rows)
+    ("prism18_20", 18, (20, 20, 20), 0),         # 16 000 prisms
 ]
 
 

@@ -18,7 +18,7 @@ def _mods():
 
 @pytest.mark.parametrize("etype,dims,bounds", [(8, (5, 3, 4), (-1, 1, 0, 0.3, 0, 0.1)), (27, (5, 3, 4), (-1, 1, 0, 0.3, 0, 0.1)),
                                                (27, (1, 1, 1), (0, 1, 0, 1, 0, 1)), (8, (1, 7, 2), (-3, -1, 2, 5, 0, 1e-3)),
-                                               (20, (4, 3, 2), (-1, 1, 0, 0.3, 0, 0.1))])
+                                               (20, (4, 3, 2), (-1, 1, 0, 0.3, 0, 0.1)), (18, (4, 3, 2), (-1, 1, 0, 0.3, 0, 0.1))])
 def test_generated_cube_is_build_cube_bit_for_bit(etype, dims, bounds):
     F, O = _mods()
     ctx = F.Context(0)
@@ -107,7 +107,7 @@ def test_device_dirichlet_set_matches_oracle(etype, nv, ids, kind):
     assert np.max(np.abs(val[rows] - vals)) <= 4e-16
 
 
-@pytest.mark.parametrize("etype,dims,qorder", [(27, (5, 4, 3), 0), (8, (6, 5, 4), 3), (20, (4, 4, 3), 0)])
+@pytest.mark.parametrize("etype,dims,qorder", [(27, (5, 4, 3), 0), (8, (6, 5, 4), 3), (20, (4, 4, 3), 0), (18, (4, 3, 3), 0)])
 def test_all_device_route_assembles_the_same_system(etype, dims, qorder):
     F, O = _mods()
     b = (-1, 1, -1, 1, -1, 1)
@@ -148,7 +148,7 @@ def test_ingest_errors_are_loud():
     F, O = _mods()
     ctx = F.Context(0)
     with pytest.raises(F.FeasmError):
-        ctx.generate_cube(18, 2, 2, 2)              # PRISM18: not an element type of this path
+        ctx.generate_cube(14, 2, 2, 2)              # PYRAMID14: not an element type of this path
     with pytest.raises(F.FeasmError):
         ctx.distribute_dofs(1)                      # no mesh yet
     xyz, conn, _ = F.build_cube(F.HEX8, 2, 2, 2)

@@ -60,6 +60,10 @@ CASES = [
     ("hex20", 20, (4, 3, 3), None, 0),             # serendipity hex: 16 rows by DMMA, 4 by DFMA
     ("hex20_skew", 20, (3, 3, 3), (1, 0.03, 4321), 0),
     ("hex20_single", 20, (1, 1, 1), None, 0),
+    ("prism18", 18, (4, 3, 3), None, 0),           # TRI6 x EDGE3 prisms, two per lattice cell, 21-point rule
+    ("prism18_skew", 18, (3, 3, 2), (1, 0.03, 2468), 0),
+    ("prism18_skewfunc", 18, (3, 2, 2), (0, 0.0, 0), 0),
+    ("prism18_single_cell", 18, (1, 1, 1), None, 0),
 ]
 
 
@@ -85,7 +89,7 @@ def test_pattern_bit_exact_and_values_within_1e12(name, etype, dims, skew, qorde
     ctx.close()
 
 
-@pytest.mark.parametrize("etype,dims,qorder", [(27, (6, 6, 6), 0), (8, (8, 8, 8), 3), (10, (2, 2, 2), 5), (20, (5, 4, 3), 0)])
+@pytest.mark.parametrize("etype,dims,qorder", [(27, (6, 6, 6), 0), (8, (8, 8, 8), 3), (10, (2, 2, 2), 5), (20, (5, 4, 3), 0), (18, (4, 4, 3), 0)])
 def test_device_fd_forcing(etype, dims, qorder):
     """introduction_ex4.C:500-537 evaluated on the device.  The FD Laplacian divides an O(1e-6) difference by 1e-6,
     so one ulp of cos/sin becomes ~1e-10 in f: parity of this mode is stated against max|rhs| at 1e-11 (DESIGN.md);
@@ -114,7 +118,7 @@ def test_laplace_no_forcing_tet10():
 
 
 @pytest.mark.parametrize("etype,dims,skew,qorder", [(27, (3, 3, 3), (1, 0.03, 5), 0), (8, (4, 4, 4), None, 3), (10, (2, 2, 2), None, 5),
-                                                    (20, (3, 2, 2), (1, 0.03, 6), 0)])
+                                                    (20, (3, 2, 2), (1, 0.03, 6), 0), (18, (3, 2, 2), (1, 0.03, 8), 0)])
 @pytest.mark.parametrize("constrained", [False, True])
 def test_element_matrices(etype, dims, skew, qorder, constrained):
     F, O = _mods()
@@ -206,7 +210,7 @@ def test_argument_errors():
     m, s = make_case(8, (2, 2, 2))
     xyz, conn, _ = m.arrays()
     with pytest.raises(F.FeasmError):
-        ctx.set_mesh(18, xyz, conn)  # PRISM18 is not supported
+        ctx.set_mesh(14, xyz, conn)  # PYRAMID14 is not supported
     ctx.set_mesh(8, xyz, conn)
     ed, _, _ = s.dofs()
     with pytest.raises(F.FeasmError):
@@ -222,6 +226,8 @@ ELAST = [
     ("tet10_ex6", 10, (3, 2, 1), None),
     ("hex20_ex6", 20, (4, 2, 2), None),
     ("hex20_ex6_skew", 20, (3, 2, 2), (1, 0.004, 9)),
+    ("prism18_ex6", 18, (3, 2, 2), None),
+    ("prism18_ex6_skew", 18, (3, 2, 1), (1, 0.004, 3)),
 ]
 
 

@@ -69,6 +69,9 @@ REF_NODES = {
     O.HEX8: None,
     O.HEX27: None,
     O.TET10: np.array([[0, 0, 0], [1, 0, 0], [0, 1, 0], [0, 0, 1], [.5, 0, 0], [.5, .5, 0], [0, .5, 0], [0, 0, .5], [.5, 0, .5], [0, .5, .5]], dtype=float),
+    # Prism18: triangle (0,0) (1,0) (0,1) x [-1, 1] (cell_prism18.h node order: bottom, top, bottom edges, verticals, top edges, mid layer)
+    O.PRISM18: np.array([[0, 0, -1], [1, 0, -1], [0, 1, -1], [0, 0, 1], [1, 0, 1], [0, 1, 1], [.5, 0, -1], [.5, .5, -1], [0, .5, -1],
+                         [0, 0, 0], [1, 0, 0], [0, 1, 0], [.5, 0, 1], [.5, .5, 1], [0, .5, 1], [.5, 0, 0], [.5, .5, 0], [0, .5, 0]], dtype=float),
 }
 
 
@@ -79,13 +82,13 @@ def _hex_ref_nodes(n):
     return ref[:n]
 
 
-@pytest.mark.parametrize("etype", [O.HEX8, O.HEX27, O.TET10, O.HEX20])
+@pytest.mark.parametrize("etype", [O.HEX8, O.HEX27, O.TET10, O.HEX20, O.PRISM18])
 def test_shapes_are_nodal_and_partition_unity(etype):
-    nodes = REF_NODES[etype] if etype == O.TET10 else _hex_ref_nodes(etype)
+    nodes = REF_NODES[etype] if etype in (O.TET10, O.PRISM18) else _hex_ref_nodes(etype)
     phi, dxi, deta, dzeta = O.shapes(etype, nodes)
     assert np.abs(phi - np.eye(etype)).max() < 1e-14  # Lagrange: phi_i(node_j) = delta_ij
     rng = np.random.default_rng(7)
-    pts = rng.uniform(0.05, 0.3, size=(20, 3)) if etype == O.TET10 else rng.uniform(-1, 1, size=(20, 3))
+    pts = rng.uniform(0.05, 0.3, size=(20, 3)) if etype in (O.TET10, O.PRISM18) else rng.uniform(-1, 1, size=(20, 3))
     phi, dxi, deta, dzeta = O.shapes(etype, pts)
     assert np.abs(phi.sum(axis=0) - 1).max() < 1e-14  # fe_test.h:671-690
     for d in (dxi, deta, dzeta):
@@ -135,7 +138,56 @@ def test_hex20_shapes_equal_the_textbook_serendipity_form():
         assert np.abs(phi[i] - want).max() < 5e-16
 
 
-@pytest.mark.parametrize("etype,order", [(O.HEX8, 1), (O.HEX27, 2), (O.TET10, 2), (O.HEX20, 2)])
+def test_prism18_shapes_equal_the_tensor_form_and_the_rule_is_exact():
+    """PRISM18 = TRI6 x EDGE3 (fe_lagrange_shape_3D.C:1077-1094): against the barycentric closed form
+    L_a (2 L_a - 1) / 4 L_a L_b in the triangle times xi (xi -+ 1) / 2, 1 - xi^2 along the axis, written from the node's
+    position; and the 21-point rule (7-point degree-5 triangle rule x 3-point Gauss, quadrature_gauss_3D.C:507-527,
+    quadrature.C:310-332) integrates the monomials x^a y^b z^c, a + b <= 5, c <= 5, exactly over the reference prism."""
+    from math import factorial as f
+
+    nodes = REF_NODES[O.PRISM18]
+    pts = np.random.default_rng(5).uniform(0.05, 0.45, size=(50, 3)) * [1, 1, 4] - [0, 0, 1]
+    phi = O.shapes(O.PRISM18, pts)[0]
+    L = np.stack([1 - pts[:, 0] - pts[:, 1], pts[:, 0], pts[:, 1]])
+    z = pts[:, 2]
+    for i, (x0, y0, z0) in enumerate(nodes):
+        lz = {-1.0: 0.5 * z * (z - 1), 1.0: 0.5 * z * (z + 1), 0.0: 1 - z * z}[z0]
+        bary = np.array([1 - x0 - y0, x0, y0])
+        if np.isclose(bary.max(), 1.0):
+            a = int(bary.argmax())
+            tri = L[a] * (2 * L[a] - 1)
+        else:
+            a, b = np.nonzero(bary > 0.25)[0]
+            tri = 4 * L[a] * L[b]
+        assert np.abs(phi[i] - tri * lz).max() < 5e-16
+    q, w = O.quadrature(O.PRISM18, 5)
+    assert q.shape == (21, 3) and abs(w.sum() - 1.0) < 1e-15
+    assert np.array_equal(q[:7, :2], q[7:14, :2]) and np.all(q[:7, 2] == q[0, 2]) and q[0, 2] < q[7, 2] < q[14, 2]  # 1D rule outermost
+    for a in range(6):
+        for b in range(6 - a):
+            for c in range(6):
+                exact = f(a) * f(b) / f(a + b + 2) * (2.0 / (c + 1) if c % 2 == 0 else 0.0)
+                assert abs((w * q[:, 0] ** a * q[:, 1] ** b * q[:, 2] ** c).sum() - exact) < 1e-15
+
+
+def test_prism18_build_cube():
+    """mesh_generation.C:1634-1756: two prisms per lattice cell on the HEX27 node lattice, all nodes in use; counts as
+    tests/mesh/mesh_generation_test.C checks them (n_elem = 2 nx ny nz, n_nodes = (2nx+1)(2ny+1)(2nz+1))."""
+    m = O.Mesh(O.PRISM18, 3, 2, 2, bounds=(-1, 1, 0, 2, 0, 3))
+    xyz, conn, _ = m.arrays()
+    assert m.n_elem == 2 * 3 * 2 * 2 and xyz.shape[0] == 7 * 5 * 5 and len(np.unique(conn)) == xyz.shape[0]
+    # the two prisms of cell 0 share the diagonal face: nodes (i+2,j) (i,j+2) and the mid-diagonal column
+    assert set(conn[0]) & set(conn[1]) == {conn[0][1], conn[0][2], conn[0][4], conn[0][5], conn[0][7], conn[0][10], conn[0][11], conn[0][13], conn[0][16]}
+    # mid-side nodes are the averages of their vertices (element-local edge table of cell_prism18.C)
+    edges = {6: (0, 1), 7: (1, 2), 8: (0, 2), 9: (0, 3), 10: (1, 4), 11: (2, 5), 12: (3, 4), 13: (4, 5), 14: (3, 5)}
+    for e in range(m.n_elem):
+        X = xyz[conn[e]]
+        for mid, (a, b) in edges.items():
+            assert np.abs(X[mid] - 0.5 * (X[a] + X[b])).max() < 1e-15
+        assert np.abs(X[15] - 0.25 * (X[0] + X[1] + X[3] + X[4])).max() < 1e-15
+
+
+@pytest.mark.parametrize("etype,order", [(O.HEX8, 1), (O.HEX27, 2), (O.TET10, 2), (O.HEX20, 2), (O.PRISM18, 2)])
 @pytest.mark.parametrize("skew", [False, True])
 def test_fe_reinit_reproduces_polynomials(etype, order, skew):
     """fe_test.h testU/testGradU on the build_cube unit-cube mesh (fe_lagrange_test.C:23-30), plain and SkewFunc-skewed."""
