@@ -318,6 +318,7 @@ int launch_row_reduce(feasm_ctx* ctx, const uint32_t* d_row_list, int64_t n_list
   switch (ctx->nd) {
     case 8: return launch_row_reduce_t<PosT, 8>(ctx, d_row_list, n_list, stream, row0);
     case 10: return launch_row_reduce_t<PosT, 10>(ctx, d_row_list, n_list, stream, row0);
+    case 18: return launch_row_reduce_t<PosT, 18>(ctx, d_row_list, n_list, stream, row0);
     case 20: return launch_row_reduce_t<PosT, 20>(ctx, d_row_list, n_list, stream, row0);
     case 27: return launch_row_reduce_t<PosT, 27>(ctx, d_row_list, n_list, stream, row0);
     case 81: return launch_row_reduce_t<PosT, 81>(ctx, d_row_list, n_list, stream, row0);

@@ -26,7 +26,9 @@ int feasm_type(ElemType t) {
     case HEX8: return FEASM_HEX8;
     case HEX27: return FEASM_HEX27;
     case TET10: return FEASM_TET10;
-    default: libmesh_error_msg("libfeasm supports HEX8, HEX27 and TET10 elements; got ElemType " << (int)t);
+    case HEX20: return FEASM_HEX20;
+    case PRISM18: return FEASM_PRISM18;
+    default: libmesh_error_msg("libfeasm supports HEX8, HEX20, HEX27, TET10 and PRISM18 elements; got ElemType " << (int)t);
   }
 }
 

@@ -9,7 +9,7 @@ sys.path.insert(0, '.')
 import torch
 from libmesh_b200 import capi as F
 
-et = {"hex27": 27, "hex8": 8, "tet10": 10, "hex20": 20}[sys.argv[1] if len(sys.argv) > 1 else "hex27"]
+et = {"hex27": 27, "hex8": 8, "tet10": 10, "hex20": 20, "prism18": 18}[sys.argv[1] if len(sys.argv) > 1 else "hex27"]
 n = int(sys.argv[2]) if len(sys.argv) > 2 else 96
 nv = int(sys.argv[3]) if len(sys.argv) > 3 else 1
 ctx = F.Context(0)

@@ -1,12 +1,12 @@
 """Development aid: kernel times of one configuration (element / constraint / row reduction / total, ms, best of 8).
-    python scripts/gpu_time_quick.py [hex27|hex8|tet10] [n] [fd|tab|none] [poisson|elasticity]
+    python scripts/gpu_time_quick.py [hex27|hex8|tet10|hex20|prism18] [n] [fd|tab|none] [poisson|elasticity]
 FEASM_LIB=<path> selects a development build of the library."""
 import sys
 import numpy as np
 sys.path.insert(0, '.')
 from libmesh_b200 import capi as F
 
-et = {"hex27": 27, "hex8": 8, "tet10": 10, "hex20": 20}[sys.argv[1] if len(sys.argv) > 1 else "hex27"]
+et = {"hex27": 27, "hex8": 8, "tet10": 10, "hex20": 20, "prism18": 18}[sys.argv[1] if len(sys.argv) > 1 else "hex27"]
 n = int(sys.argv[2]) if len(sys.argv) > 2 else 96
 forcing = {"fd": F.FORCING_EX4_FD, "tab": F.FORCING_TABULATED, "none": F.FORCING_NONE}[sys.argv[3] if len(sys.argv) > 3 else "fd"]
 elast = len(sys.argv) > 4 and sys.argv[4] == "elasticity"
@@ -21,7 +21,7 @@ qo = 3 if et == 8 else 0
 if elast:
     p = F.make_params(F.ELASTICITY, 0, F.FORCING_NONE, F.CONSTRAIN_HOMOGENEOUS)
 else:
-    ftab = np.ones((ctx.n_elem, {27: 27, 8: 8, 10: 14, 20: 27}[et])) if forcing == F.FORCING_TABULATED else None
+    ftab = np.ones((ctx.n_elem, {27: 27, 8: 8, 10: 14, 20: 27, 18: 21}[et])) if forcing == F.FORCING_TABULATED else None
     p = F.make_params(F.POISSON, qo, forcing, f_host=ftab)
 for _ in range(3):
     ctx.assemble(p)

@@ -40,7 +40,7 @@ struct NotImplemented : std::logic_error { using std::logic_error::logic_error; 
 
 enum ParallelType { AUTOMATIC = 0, SERIAL, PARALLEL, GHOSTED };     // include/enums/enum_parallel_type.h
 enum SolverPackage { PETSC_SOLVERS = 0, TRILINOS_SOLVERS, LASPACK_SOLVERS, SLEPC_SOLVERS, EIGEN_SOLVERS, NLOPT_SOLVERS, INVALID_SOLVER_PACKAGE };
-enum ElemType { HEX8 = 10, HEX27 = 12, TET10 = 9, INVALID_ELEM = 99 };  // include/enums/enum_elem_type.h
+enum ElemType { TET10 = 9, HEX8 = 10, HEX20 = 11, HEX27 = 12, PRISM18 = 15, INVALID_ELEM = 99 };  // include/enums/enum_elem_type.h
 
 // include/parallel/parallel.h -> TIMPI's Communicator (timpi/communicator.h): rank / size and the few collectives the
 // adaptor uses (broadcast, allgather, sum, max, min).  One rank by default; a multi-process test sets FEASM_MOCK_RANK,
