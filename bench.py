@@ -42,14 +42,16 @@ import numpy as np
 ROOT = os.path.dirname(os.path.abspath(__file__))
 sys.path.insert(0, ROOT)
 
-ELEM = {"hex27": 27, "hex8": 8, "tet10": 10}
+ELEM = {"hex27": 27, "hex8": 8, "tet10": 10, "hex20": 20, "prism18": 18}
 METRIC = "Q2 HEX27 assembly elements/s"
 EX4_BOUNDS = (-1.0, 1.0, -1.0, 1.0, -1.0, 1.0)
 EX6_BOUNDS = (0.0, 1.0, 0.0, 0.3, 0.0, 0.1)  # systems_of_equations_ex6.C:437-444
 
 
 def metric_name(args):
-    return METRIC if args.problem == "poisson" else "HEX27 3-variable elasticity (systems_of_equations_ex6) assembly elements/s"
+    if args.problem != "poisson":
+        return f"{args.elem.upper()} 3-variable elasticity (systems_of_equations_ex6) assembly elements/s"
+    return METRIC if args.elem == "hex27" else f"{args.elem.upper()} introduction_ex4 assembly elements/s"
 
 
 def algorithmic_counts(etype: int, nq: int, nnz: int, n_dofs: int, n_elem: int, n_nodes: int, affine: bool = True, problem: str = "poisson"):
@@ -155,7 +157,7 @@ def problem_dims(args):
 
 
 def nq_of(args):
-    return {27: 27, 8: 27 if args.qorder in (0, 5) else 8, 10: 14}[ELEM[args.elem]]
+    return {27: 27, 8: 27 if args.qorder in (0, 5) else 8, 10: 14, 20: 27, 18: 21}[ELEM[args.elem]]
 
 
 def build_problem(F, args, n_parts: int = 1, elem_pid=None):
