@@ -1,10 +1,11 @@
 """GPU: general constraint rows (hanging nodes) — feasm_set_constraint_rows against the Python restatement of
-DofMap::heterogeneously_constrain_element_matrix_and_vector (oracle/constraints.py) on locally refined HEX8 meshes."""
+DofMap::heterogeneously_constrain_element_matrix_and_vector (oracle/constraints.py) on locally refined HEX8 meshes (weights
+1/2, 1/4) and HEX27 meshes (the quadratic interpolation weights 3/8, 3/4, -1/8 and their products)."""
 import numpy as np
 import pytest
 
 from conftest import PARITY_TOL
-from hanging import refined_cube
+from hanging import refined_cube, refined_cube27
 from oracle import constraints as OC
 from oracle.parity import csr_parity_error, vec_parity_error
 
@@ -26,10 +27,11 @@ def linear(p):
     return 0.3 + p[:, 0] - 0.5 * p[:, 1] + 0.25 * p[:, 2]
 
 
-def case(n, lo, hi, bc):
+def case(n, lo, hi, bc, etype=8):
     F, O = _mods()
-    xyz, conn, mask, hang = refined_cube(n, lambda i, j, k: lo <= i < hi and lo <= j < hi and lo <= k < hi)
-    m = O.Mesh.from_arrays(O.HEX8, xyz, conn, mask)
+    make = refined_cube27 if etype == 27 else refined_cube
+    xyz, conn, mask, hang = make(n, lambda i, j, k: lo <= i < hi and lo <= j < hi and lo <= k < hi)
+    m = O.Mesh.from_arrays(etype, xyz, conn, mask)
     s = O.System(m, 1)
     ed, nb, _ = s.dofs()
     rows = {int(nb[h]): [(int(nb[v]), c) for v, c in lst] for h, lst in hang.items()}
@@ -42,10 +44,10 @@ def case(n, lo, hi, bc):
     return xyz, conn, hang, m, s, ed, nb, OC.ConstraintRows(rows, vals)
 
 
-@pytest.mark.parametrize("n,lo,hi,qorder", [(4, 1, 3, 3), (6, 2, 5, 3), (5, 1, 3, 5)])
-def test_hanging_node_assembly_matches_the_reference_algorithm(n, lo, hi, qorder):
+@pytest.mark.parametrize("n,lo,hi,qorder,etype", [(4, 1, 3, 3, 8), (6, 2, 5, 3, 8), (5, 1, 3, 5, 8), (3, 1, 2, 5, 27), (4, 1, 3, 5, 27)])
+def test_hanging_node_assembly_matches_the_reference_algorithm(n, lo, hi, qorder, etype):
     F, O = _mods()
-    xyz, conn, hang, m, s, ed, nb, con = case(n, lo, hi, exact)
+    xyz, conn, hang, m, s, ed, nb, con = case(n, lo, hi, exact, etype)
     assert len(hang) > 0
     f_tab, _ = s.forcing_at_qps(qorder)
     Ku, Fu = s.element_matrices(O.POISSON_EX4, constrained=False, qorder=qorder, forcing=O.FORCING_TABULATED, f_tab=f_tab)
@@ -53,7 +55,7 @@ def test_hanging_node_assembly_matches_the_reference_algorithm(n, lo, hi, qorder
     vo, ro = OC.assemble(con, ed, Ku, Fu, rp, ci)
 
     ctx = F.Context(0)
-    ctx.set_mesh(8, xyz, conn)
+    ctx.set_mesh(etype, xyz, conn)
     ctx.set_dofs(ed, s.n_dofs)
     ctx.set_constraint_rows(*con.arrays())
     ctx.build_pattern()   # the device-built Graph plus the couplings find_connected_dofs adds
@@ -69,7 +71,7 @@ def test_hanging_node_assembly_matches_the_reference_algorithm(n, lo, hi, qorder
     assert np.array_equal(v, v2) and np.array_equal(r, r2)
     # the host-pattern route (libMesh's own Graph) gives the same system
     ctx2 = F.Context(0)
-    ctx2.set_mesh(8, xyz, conn)
+    ctx2.set_mesh(etype, xyz, conn)
     ctx2.set_dofs(ed, s.n_dofs)
     ctx2.set_constraint_rows(*con.arrays())
     ctx2.set_pattern(rp, ci)
@@ -98,6 +100,34 @@ def test_hanging_node_patch_test_on_the_device_matrix():
     u = np.linalg.solve(A, r)
     want = np.zeros(s.n_dofs)
     want[nb] = linear(xyz)
+    assert np.abs(u - want).max() < 1e-12
+    ctx.close()
+
+
+def harmonic_quadratic(p):
+    return 0.3 + p[:, 0] - 0.5 * p[:, 1] + 0.25 * p[:, 2] + p[:, 0] ** 2 - p[:, 1] ** 2 + 0.5 * p[:, 0] * p[:, 2]
+
+
+def test_hex27_hanging_node_patch_test_with_a_quadratic_field():
+    """Q2 elements with the quadratic hanging-node weights hold every quadratic: Laplace with Dirichlet data from a harmonic
+    quadratic is solved exactly at every node by the system assembled on the GPU."""
+    F, O = _mods()
+    xyz, conn, hang, m, s, ed, nb, con = case(3, 1, 2, harmonic_quadratic, 27)
+    assert len(hang) == 72 and {round(c, 6) for lst in hang.values() for _, c in lst} >= {0.375, 0.75, -0.125, 0.140625, -0.046875}
+    ctx = F.Context(0)
+    ctx.set_mesh(27, xyz, conn)
+    ctx.set_dofs(ed, s.n_dofs)
+    ctx.set_constraint_rows(*con.arrays())
+    ctx.build_pattern()
+    ctx.assemble(F.make_params(F.POISSON, 5, F.FORCING_NONE))
+    v, r = ctx.get_values()
+    rp, ci = ctx.get_pattern()
+    A = np.zeros((s.n_dofs, s.n_dofs))
+    for row in range(s.n_dofs):
+        A[row, ci[int(rp[row]):int(rp[row + 1])]] = v[int(rp[row]):int(rp[row + 1])]
+    u = np.linalg.solve(A, r)
+    want = np.zeros(s.n_dofs)
+    want[nb] = harmonic_quadratic(xyz)
     assert np.abs(u - want).max() < 1e-12
     ctx.close()
 

@@ -4,7 +4,7 @@ field exactly (the patch test a conforming constraint must pass), and its matrix
 import numpy as np
 import pytest
 
-from hanging import refined_cube
+from hanging import refined_cube, refined_cube27
 from oracle import constraints as OC
 from oracle import oracle as O
 
@@ -72,6 +72,33 @@ def test_hanging_node_mesh_passes_the_patch_test():
     e = int(np.nonzero((conn == h).any(axis=1))[0][0])
     K, F, dofs = OC.constrain(con, Ku[e], Fu[e], ed[e])
     assert len(dofs) > 8 and K.shape == (len(dofs), len(dofs))
+
+
+def test_hex27_hanging_nodes_hold_quadratics():
+    """HEX27 with one refined cell: 72 hanging nodes with the quadratic interpolation weights (3/8, 3/4, -1/8 on an edge, their
+    products on a face); the constrained Laplace system reproduces a harmonic quadratic at every node (Q2 patch test)."""
+    quad = lambda p: 0.3 + p[:, 0] - 0.5 * p[:, 1] + 0.25 * p[:, 2] + p[:, 0] ** 2 - p[:, 1] ** 2 + 0.5 * p[:, 0] * p[:, 2]
+    xyz, conn, mask, hang = refined_cube27(3, lambda i, j, k: i == 1 and j == 1 and k == 1)
+    assert len(hang) == 72 and all(abs(sum(c for _, c in lst) - 1.0) < 1e-15 for lst in hang.values())  # weights sum to one
+    m = O.Mesh.from_arrays(O.HEX27, xyz, conn, mask)
+    s = O.System(m, 1)
+    ed, nb, _ = s.dofs()
+    rows = {int(nb[h]): [(int(nb[v]), c) for v, c in lst] for h, lst in hang.items()}
+    vals = {}
+    for node in np.nonzero(mask)[0]:
+        rows[int(nb[node])] = []
+        vals[int(nb[node])] = float(quad(xyz[node:node + 1])[0])
+    con = OC.ConstraintRows(rows, vals)
+    Ku, Fu = s.element_matrices(O.LAPLACE, constrained=False, qorder=5)
+    rp, ci = OC.sparsity(con, ed, s.n_dofs)
+    vals_, rhs = OC.assemble(con, ed, Ku, Fu, rp, ci)
+    A = np.zeros((s.n_dofs, s.n_dofs))
+    for r in range(s.n_dofs):
+        A[r, ci[int(rp[r]):int(rp[r + 1])]] = vals_[int(rp[r]):int(rp[r + 1])]
+    u = np.linalg.solve(A, rhs)
+    exact = np.zeros(s.n_dofs)
+    exact[nb] = quad(xyz)
+    assert np.abs(u - exact).max() < 1e-12
 
 
 def test_recursion_follows_new_dofs_only():
