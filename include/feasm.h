@@ -358,7 +358,7 @@ int feasm_get_halo_plan(feasm_ctx* ctx, int32_t* peers, uint64_t* send_ptr, uint
                         uint32_t* recv_gids);
 
 /* ---- host-side generators for stand-alone runs (no libMesh present) ---------------------------- */
-/* MeshTools::Generation::build_cube (src/mesh/mesh_generation.C:317-1937) for HEX8/HEX27/TET10: fills caller arrays.
+/* MeshTools::Generation::build_cube (src/mesh/mesh_generation.C:317-1937) for HEX8/HEX20/HEX27/TET10/PRISM18: fills caller arrays.
  * Sizes: feasm_cube_sizes. */
 int feasm_cube_sizes(int elem_type, int nx, int ny, int nz, int64_t* n_elem, int64_t* n_nodes);
 int feasm_build_cube(int elem_type, int nx, int ny, int nz, const double bounds[6], double* xyz, uint32_t* conn,
@@ -371,7 +371,8 @@ int64_t feasm_distribute_dofs(int npe, int64_t n_elem, int64_t n_nodes, const ui
 /* ---- device-side mesh ingest (the step before the path, without the host) --------------- */
 /* MeshTools::Generation::build_cube (src/mesh/mesh_generation.C:1285-1340 nodes, :1399-1432 elements, :1779-1785
  * rescale, :1416-1432 boundary ids; TET10: the 24-tet split + all_second_order of :1795-1907) for HEX8 / HEX27 / TET10,
- * generated in the context's device arrays; replaces
+ * generated in the context's device arrays (HEX20, :1559-1592, and PRISM18, :1634-1756: made by feasm_build_cube on the
+ * host and uploaded); replaces
  * feasm_build_cube + feasm_set_mesh.  Same node ids, element order and coordinates bit for bit. */
 int feasm_generate_cube(feasm_ctx* ctx, int elem_type, int nx, int ny, int nz, const double bounds[6]);
 /* DofMap::distribute_dofs (src/base/dof_map.C:1445-1507, one rank, one variable group of n_vars LAGRANGE variables)
