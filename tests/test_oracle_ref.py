@@ -1,0 +1,169 @@
+"""The oracle against the REFERENCE'S OWN CODE for the tables of FE::reinit: the Lagrange shape functions and their
+reference derivatives (src/fe/fe_lagrange_shape_{2,3}D.C, include/fe/fe_lagrange_shape_1D.h) and the Gauss rules
+(src/quadrature/quadrature_gauss_{1,2,3}D.C, quadrature.C, quadrature_gauss.C).  Those reference sources are compiled where
+they lie into oracle/_ref/libref_fe.so (oracle/Makefile; stub declarations in oracle/ref_stubs/), and their outputs are
+committed as tests/golden/reference_fe_tables.npz (tests/golden/make_ref_golden.py).  The bar is bit-for-bit equality: the
+restatement follows the reference's operation order, so nothing may differ."""
+import os
+
+import numpy as np
+import pytest
+
+from oracle import oracle as O
+from oracle import ref as R
+
+GOLD_MAP = np.load(os.path.join(os.path.dirname(os.path.abspath(__file__)), "golden", "reference_fe_map.npz"))
+GOLD = np.load(os.path.join(os.path.dirname(os.path.abspath(__file__)), "golden", "reference_fe_tables.npz"))
+ORC = {"HEX8": O.HEX8, "HEX27": O.HEX27, "HEX20": O.HEX20, "TET10": O.TET10, "PRISM18": O.PRISM18}
+VOLUME_CASES = [("HEX8", 3), ("HEX8", 5), ("HEX27", 3), ("HEX27", 5), ("HEX20", 5), ("TET10", 5), ("PRISM18", 5)]
+needs_ref = pytest.mark.skipif(not R.available(), reason="oracle/_ref/libref_fe.so is built only where /root/reference exists")
+
+
+@pytest.mark.parametrize("elem,order", VOLUME_CASES)
+def test_quadrature_rules_are_the_reference_bits(elem, order):
+    pts, w = O.quadrature(ORC[elem], order)
+    k = f"{elem}_q{order}"
+    assert pts.shape == GOLD[k + "_pts"].shape
+    assert np.array_equal(pts, GOLD[k + "_pts"]) and np.array_equal(w, GOLD[k + "_w"])
+
+
+@pytest.mark.parametrize("elem,order", VOLUME_CASES)
+def test_shape_tables_at_the_rule_points_are_the_reference_bits(elem, order):
+    """What FE::reinit tabulates once per element type: phi_i(q), dphi_i/dxi(q), /deta, /dzeta."""
+    k = f"{elem}_q{order}"
+    got = O.shapes(ORC[elem], GOLD[k + "_pts"])
+    for name, a in zip(("phi", "dxi", "deta", "dzeta"), got):
+        assert np.array_equal(a, GOLD[f"{k}_{name}"]), name
+
+
+@pytest.mark.parametrize("elem", sorted(ORC))
+def test_shape_functions_at_random_points_are_the_reference_bits(elem):
+    got = O.shapes(ORC[elem], GOLD[elem + "_rand_pts"])
+    for name, a in zip(("phi", "dxi", "deta", "dzeta"), got):
+        assert np.array_equal(a, GOLD[f"{elem}_rand_{name}"]), name
+
+
+HEX_REF = np.array([[-1, -1, -1], [1, -1, -1], [1, 1, -1], [-1, 1, -1], [-1, -1, 1], [1, -1, 1], [1, 1, 1], [-1, 1, 1], [0, -1, -1],
+                    [1, 0, -1], [0, 1, -1], [-1, 0, -1], [-1, -1, 0], [1, -1, 0], [1, 1, 0], [-1, 1, 0], [0, -1, 1], [1, 0, 1],
+                    [0, 1, 1], [-1, 0, 1], [0, 0, -1], [0, -1, 0], [1, 0, 0], [0, 1, 0], [-1, 0, 0], [0, 0, 1], [0, 0, 0]], dtype=float)
+TET_REF = np.array([[0, 0, 0], [1, 0, 0], [0, 1, 0], [0, 0, 1], [.5, 0, 0], [.5, .5, 0], [0, .5, 0], [0, 0, .5], [.5, 0, .5], [0, .5, .5]], dtype=float)
+
+
+@pytest.mark.parametrize("elem,side_elem,order", [("HEX8", "QUAD4", 3), ("HEX8", "QUAD4", 5), ("HEX27", "QUAD9", 5), ("HEX20", "QUAD8", 5)])
+def test_side_rule_on_the_reference_hex_is_the_reference_quad_rule(elem, side_elem, order):
+    """Side 5 (zeta = +1) of the reference hex has its side nodes at (xi, eta) = the QUAD's own reference nodes, so the side
+    points are (x_q, y_q, 1) of QGauss(2, order) on that QUAD and JxW_face = w_q (the side map is the identity)."""
+    X = HEX_REF[: ORC[elem]]
+    d = O.side_reinit(ORC[elem], X, 5, order)
+    k = f"{side_elem}_q{order}"
+    assert np.abs(d["ref"][:, :2] - GOLD[k + "_pts"][:, :2]).max() < 1e-15 and np.abs(d["ref"][:, 2] - 1).max() < 1e-15
+    assert np.abs(d["JxW"] - GOLD[k + "_w"]).max() < 1e-15
+    assert np.abs(d["xyz"] - d["ref"]).max() < 1e-15
+
+
+def test_side_rule_on_the_reference_tet_is_the_reference_triangle_rule():
+    """Side 0 of the reference tet (nodes 0, 2, 1: the face zeta = 0 walked clockwise): side point (s, t) sits at
+    (xi, eta) = (t, s); JxW_face = w_q (unit right triangle)."""
+    d = O.side_reinit(O.TET10, TET_REF, 0, 5)
+    q, w = GOLD["TRI6_q5_pts"], GOLD["TRI6_q5_w"]
+    assert np.abs(d["ref"][:, 0] - q[:, 1]).max() < 1e-15 and np.abs(d["ref"][:, 1] - q[:, 0]).max() < 1e-15
+    assert np.abs(d["ref"][:, 2]).max() < 1e-15 and np.abs(d["JxW"] - w).max() < 1e-15
+
+
+@needs_ref
+def test_golden_tables_are_what_the_compiled_reference_gives_now():
+    from golden.make_ref_golden import CASES
+
+    for elem, order in CASES:
+        pts, w = R.gauss_rule(elem, order)
+        k = f"{elem}_q{order}"
+        assert np.array_equal(pts, GOLD[k + "_pts"]) and np.array_equal(w, GOLD[k + "_w"])
+        for name, a in zip(("phi", "dxi", "deta", "dzeta"), R.shapes(elem, pts)):
+            assert np.array_equal(a, GOLD[f"{k}_{name}"])
+
+
+@needs_ref
+@pytest.mark.parametrize("elem", sorted(ORC))
+def test_oracle_equals_the_compiled_reference_on_fresh_points(elem):
+    rng = np.random.default_rng(sum(map(ord, elem)))
+    if elem == "TET10":
+        pts = rng.uniform(0.0, 0.33, size=(500, 3))
+    elif elem == "PRISM18":
+        pts = np.c_[rng.uniform(0.0, 0.5, size=(500, 2)), rng.uniform(-1, 1, size=500)]
+    else:
+        pts = rng.uniform(-1, 1, size=(500, 3))
+    for a, b in zip(O.shapes(ORC[elem], pts), R.shapes(elem, pts)):
+        assert np.array_equal(a, b)
+
+
+@needs_ref
+@pytest.mark.parametrize("elem,side", [("HEX27", 2), ("HEX20", 0), ("HEX8", 4), ("TET10", 3)])
+def test_parent_shapes_at_the_side_points_are_the_reference_bits(elem, side):
+    """FE::reinit(elem, side): the parent's shape functions evaluated at the side points carried into the parent's reference
+    space — through the reference's own shape code at the oracle's mapped points."""
+    X = TET_REF if elem == "TET10" else HEX_REF[: ORC[elem]]
+    d = O.side_reinit(ORC[elem], X, side, 5)
+    assert np.array_equal(d["phi"], R.shapes(elem, d["ref"])[0])
+
+
+@needs_ref
+def test_exact_solution_is_the_example_file():
+    """examples/introduction/introduction_ex3/exact_solution.C compiled as it is: the Dirichlet data and the FD forcing of
+    ex4 are built from this function."""
+    rng = np.random.default_rng(4)
+    for x, y, z in rng.uniform(-1.001, 1.001, size=(2000, 3)):
+        assert O.exact_solution(x, y, z) == R.exact_solution(x, y, z)
+
+
+def _map_dphi(sh, inv):
+    """H1FETransformation::map_dphi (src/fe/h1_fe_transformation.C:150-187), 3D: dphi[i][q][d] =
+    dphidxi[i][q] * dxidx_d[q] + dphideta[i][q] * detadx_d[q] + dphidzeta[i][q] * dzetadx_d[q], in that order."""
+    return sh[1][:, :, None] * inv[None, :, 0, :] + sh[2][:, :, None] * inv[None, :, 1, :] + sh[3][:, :, None] * inv[None, :, 2, :]
+
+
+@pytest.mark.parametrize("elem", sorted(ORC))
+def test_fe_reinit_is_the_reference_femap_bit_for_bit(elem):
+    """FE::reinit = FEMap::compute_map (affine and general branch) + map_dphi: the oracle's xyz, JxW and physical gradients
+    against what the reference's own fe_map.C gave for the same elements (plain, sheared, perturbed)."""
+    order = int(GOLD_MAP[elem + "_order"])
+    k = f"{elem}_q{order}"
+    pts, w = GOLD[k + "_pts"], GOLD[k + "_w"]
+    sh = [GOLD[f"{k}_{n}"] for n in ("phi", "dxi", "deta", "dzeta")]
+    n_general = 0
+    for X, aff, xyz, jxw, inv in zip(GOLD_MAP[elem + "_X"], GOLD_MAP[elem + "_affine"], GOLD_MAP[elem + "_xyz"], GOLD_MAP[elem + "_JxW"], GOLD_MAP[elem + "_inv"]):
+        r = O.fe_reinit(ORC[elem], X, pts, w)
+        assert r["affine"] == bool(aff)
+        n_general += not aff
+        assert np.array_equal(r["xyz"], xyz) and np.array_equal(r["JxW"], jxw)
+        assert np.array_equal(r["phi"], sh[0]) and np.array_equal(r["dphi"], _map_dphi(sh, inv))
+    assert 0 < n_general < len(GOLD_MAP[elem + "_affine"])  # both branches of compute_map are in the fixture
+
+
+@needs_ref
+@pytest.mark.parametrize("elem,amp", [("HEX27", 0.04), ("HEX8", 0.05), ("HEX20", 0.04), ("TET10", 0.008), ("PRISM18", 0.01)])
+def test_fe_reinit_equals_the_compiled_femap_on_fresh_meshes(elem, amp):
+    orc = ORC[elem]
+    pts, w = O.quadrature(orc, 3 if elem == "HEX8" else 5)
+    sh = R.shapes(elem, pts)
+    for skew in (None, (0, 0.0, 0), (1, amp, 31)):
+        m = O.Mesh(orc, 3, 2, 2, bounds=(-1, 1, -1, 1, 0, 1.5))
+        if skew:
+            m.skew(*skew)
+        xyz, conn, _ = m.arrays()
+        for e in range(m.n_elem):
+            X = xyz[conn[e]]
+            a = O.fe_reinit(orc, X, pts, w)
+            b = R.fe_map(elem, X, pts, w, a["affine"])
+            assert np.array_equal(a["xyz"], b["xyz"]) and np.array_equal(a["JxW"], b["JxW"])
+            assert np.array_equal(a["dphi"], _map_dphi(sh, b["inv"]))
+
+
+@needs_ref
+def test_the_reference_throws_on_the_degenerate_map_the_oracle_rejects():
+    X = HEX_REF[:8].copy()
+    X[:, 2] = 0.0  # flat element: det J = 0 (fe_map.C:467-506)
+    pts, w = O.quadrature(O.HEX8, 3)
+    with pytest.raises(O.OracleError):
+        O.fe_reinit(O.HEX8, X, pts, w)
+    with pytest.raises(RuntimeError, match="Jacobian"):
+        R.fe_map("HEX8", X, pts, w, False)
