@@ -6,11 +6,17 @@
  * libmesh_b200/ and the timed CPU baseline of bench.py.  Nothing in the product may include, link or
  * call it; only tests/, __graft_entry__.smoke() and bench.py's cpu_baseline / --impl reference legs do.
  *
- * Parity status: the reference cannot be compiled in the build container (TIMPI / MetaPhysicL
- * submodules are empty), so element-level arithmetic is pinned by the reference's own unit-test known
- * answers (tests/fe/fe_test.h, tests/quadrature/quadrature_test.C, tests/numerics/sparse_matrix_test.h,
- * tests/systems/systems_test.C, tests/base/dof_map_test.C, tests/mesh/mesh_generation_test.C) restated
- * in tests/test_oracle_*.py; GLOBAL matrix/RHS numbers against a real libMesh build are "parity unpinned".
+ * Parity status: libMesh as a whole cannot be compiled in the build container (TIMPI / MetaPhysicL submodules are
+ * empty, libmesh_config.h is generated), but the reference files that hold the arithmetic of FE::reinit can: oracle/_ref
+ * (oracle/Makefile) compiles src/fe/fe_lagrange_shape_{2,3}D.C, include/fe/fe_lagrange_shape_1D.h,
+ * src/quadrature/quadrature*.C, src/fe/fe_map.C and the examples' exact_solution.C where they lie, against stub
+ * declarations (oracle/ref_stubs/).  Against that code this oracle's Gauss rules, shape tables and FE::reinit output (xyz,
+ * JxW, dphi; affine and general branch of FEMap::compute_map) are BIT-IDENTICAL on every element type of the path
+ * (tests/test_oracle_ref.py; golden tables tests/golden/reference_fe_*.npz written from it).  What no compiled reference
+ * code checks: Elem::has_affine_map, build_cube, dof numbering, the sparsity pattern, the constraint routines and the
+ * scatter — pinned by the reference's unit-test known answers (tests/fe/fe_test.h, tests/numerics/sparse_matrix_test.h,
+ * tests/systems/systems_test.C, tests/base/dof_map_test.C, tests/mesh/mesh_generation_test.C) and its published run facts,
+ * restated in tests/test_oracle_*.py; GLOBAL matrix / RHS numbers against a real libMesh build stay "parity unpinned".
  *
  * Every function cites the reference file:line it follows (paths relative to /root/reference).
  */

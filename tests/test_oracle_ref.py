@@ -167,3 +167,94 @@ def test_the_reference_throws_on_the_degenerate_map_the_oracle_rejects():
         O.fe_reinit(O.HEX8, X, pts, w)
     with pytest.raises(RuntimeError, match="Jacobian"):
         R.fe_map("HEX8", X, pts, w, False)
+
+
+def _ex4_element_from_reference_tables(elem, X, pts, w, affine):
+    """introduction_ex4.C:464-537 written out in numpy over tables that come from the REFERENCE'S compiled code only
+    (FEMap for xyz / JxW / the inverse map, the shape files for phi / dphi, exact_solution.C for the forcing): every
+    elementwise numpy operation is one IEEE operation, applied in the example's order —
+        Ke(i,j) += JxW[qp] * (dphi[i][qp] * dphi[j][qp])      with TypeVector's a0*b0 + a1*b1 + a2*b2
+        Fe(i)   += JxW[qp] * fxy * phi[i][qp]                 fxy = -(uxx + uyy + uzz), the FD Laplacian of exact_solution."""
+    sh = R.shapes(elem, pts)
+    mp = R.fe_map(elem, X, pts, w, affine)
+    dphi = _map_dphi(sh, mp["inv"])  # [i][q][d]
+    n, nq = sh[0].shape
+    Ke, Fe = np.zeros((n, n)), np.zeros(n)
+    for q in range(nq):
+        g = dphi[:, q, :]
+        dot = (g[:, None, 0] * g[None, :, 0] + g[:, None, 1] * g[None, :, 1]) + g[:, None, 2] * g[None, :, 2]
+        Ke += mp["JxW"][q] * dot
+    eps = 1.e-3
+    ex = R.exact_solution
+    for q in range(nq):
+        x, y, z = (float(v) for v in mp["xyz"][q])
+        uxx = (ex(x - eps, y, z) + ex(x + eps, y, z) + -2. * ex(x, y, z)) / eps / eps
+        uyy = (ex(x, y - eps, z) + ex(x, y + eps, z) + -2. * ex(x, y, z)) / eps / eps
+        uzz = (ex(x, y, z - eps) + ex(x, y, z + eps) + -2. * ex(x, y, z)) / eps / eps
+        fxy = -(uxx + uyy + uzz)
+        Fe += mp["JxW"][q] * fxy * sh[0][:, q]
+    return Ke, Fe
+
+
+@needs_ref
+@pytest.mark.parametrize("elem,dims,skew", [("HEX27", (2, 2, 2), None), ("HEX27", (2, 2, 1), (1, 0.04, 11)), ("HEX8", (3, 2, 2), (1, 0.05, 5)),
+                                            ("HEX20", (2, 2, 1), (1, 0.04, 3)), ("TET10", (1, 1, 1), (1, 0.008, 2)), ("PRISM18", (2, 1, 1), (1, 0.01, 9))])
+def test_ex4_element_matrices_from_reference_tables_only(elem, dims, skew):
+    """The oracle's unconstrained Ke / Fe of introduction_ex4 against the example's loop evaluated over the reference's own
+    tables: bit for bit.  What stays between this and the global system is dof numbering, the element constraint and the
+    ordered scatter."""
+    orc = ORC[elem]
+    m = O.Mesh(orc, *dims, bounds=(-1, 1, -1, 1, -1, 1))
+    if skew:
+        m.skew(*skew)
+    s = O.System(m, 1)
+    qorder = 3 if elem == "HEX8" else 5
+    Ko, Fo = s.element_matrices(O.POISSON_EX4, constrained=False, qorder=qorder)
+    xyz, conn, _ = m.arrays()
+    pts, w = O.quadrature(orc, qorder)
+    for e in range(0, m.n_elem, max(1, m.n_elem // 6)):
+        X = xyz[conn[e]]
+        Ke, Fe = _ex4_element_from_reference_tables(elem, X, pts, w, O.has_affine_map(orc, X))
+        assert np.array_equal(Ke, Ko[e]), np.abs(Ke - Ko[e]).max()
+        assert np.array_equal(Fe, Fo[e]), np.abs(Fe - Fo[e]).max()
+
+
+@needs_ref
+@pytest.mark.parametrize("elem,skew", [("HEX27", (1, 0.004, 7)), ("HEX8", None), ("TET10", None)])
+def test_ex6_element_matrices_from_reference_tables_only(elem, skew):
+    """systems_of_equations_ex6.C:136-151 (elasticity_tensor) and :220-237 (the six-deep Ke loop, the body force) in numpy
+    over the reference's compiled tables, in the example's order ((JxW * C_ijkl) * dphi_j(l)) * dphi_i(j), j then l innermost:
+    the oracle's unconstrained 3-variable element matrix and vector, bit for bit."""
+    orc = ORC[elem]
+    m = O.Mesh(orc, 2, 1, 1, bounds=(0, 1, 0, 0.3, 0, 0.1))
+    if skew:
+        m.skew(*skew)
+    s = O.System(m, 3)
+    Ko, Fo = s.element_matrices(O.ELASTICITY_EX6, constrained=False)
+    xyz, conn, _ = m.arrays()
+    qorder = 3 if elem == "HEX8" else 5
+    pts, w = O.quadrature(orc, qorder)
+    sh = R.shapes(elem, pts)
+    n = sh[0].shape[0]
+    nu, E = 0.3, 1.
+    lam1 = (E * nu) / ((1. + nu) * (1. - 2. * nu))
+    lam2 = E / (2. * (1. + nu))
+    kd = lambda a, b: 1. if a == b else 0.
+    C = lambda i, j, k, l: lam1 * kd(i, j) * kd(k, l) + lam2 * (kd(i, k) * kd(j, l) + kd(i, l) * kd(j, k))
+    f = (0., 0., -1.)
+    for e in (0, m.n_elem - 1):
+        X = xyz[conn[e]]
+        mp = R.fe_map(elem, X, pts, w, O.has_affine_map(orc, X))
+        dphi = _map_dphi(sh, mp["inv"])
+        Ke, Fe = np.zeros((3 * n, 3 * n)), np.zeros(3 * n)
+        for q in range(len(w)):
+            g = dphi[:, q, :]
+            for i in range(3):
+                for j in range(3):
+                    for k in range(3):
+                        for l in range(3):
+                            Ke[i * n:(i + 1) * n, k * n:(k + 1) * n] += ((mp["JxW"][q] * C(i, j, k, l)) * g[None, :, l]) * g[:, None, j]
+            for i in range(3):
+                Fe[i * n:(i + 1) * n] += mp["JxW"][q] * (f[i] * sh[0][:, q])
+        assert np.array_equal(Ke, Ko[e]), np.abs(Ke - Ko[e]).max()
+        assert np.array_equal(Fe, Fo[e]), np.abs(Fe - Fo[e]).max()
