@@ -205,6 +205,39 @@ class DistributedAssembly:
         self.send_slots, self.recv_slots = o["send_slots"], o["recv_slots"]
         pl.close()
 
+    # -- the assembled matrix used on the device: halo of a distributed vector -------------------------------------------
+    def setup_halo(self):
+        """After setup(): which entries of a distributed vector this rank needs from whom (what libMesh's send_list /
+        NumericVector::localize provide).  With a communicator inside the context it is feasm_build_halo; otherwise the
+        needed global ids (feasm_halo_columns) are split by owner here, the request lists travel over torch.distributed
+        and the routes go back in through feasm_set_halo_plan — the route of hosts that carry messages themselves."""
+        p, ctx = self.p, self.ctx
+        if getattr(ctx, "has_comm", False):
+            ctx.build_halo(p.first_dof)
+            self.halo_peers, self.halo_send_ptr, self.halo_send_rows, self.halo_recv_ptr, self.halo_recv_gids = ctx.halo_plan()
+            self.halo_peers = [int(q) for q in self.halo_peers]
+            return
+        n_global = int(p.first_dof[-1])
+        need = np.asarray(ctx.halo_columns(n_global, p.f0), dtype=np.int64)  # ascending global ids, none of them owned
+        owner = np.searchsorted(p.first_dof, need, side="right") - 1
+        requests = {int(q): need[owner == q] for q in np.unique(owner)}
+        asked = _exchange_arrays(self.dist, self.host_group, self.rank, requests)  # what the peers ask of this rank
+        peers = sorted(set(requests) | set(int(q) for q in asked))
+        send_ptr, recv_ptr, send_rows, recv_gids = [0], [0], [], []
+        for q in peers:
+            rows = np.asarray(asked.get(q, np.zeros(0)), dtype=np.int64) - p.f0
+            if len(rows) and (rows.min() < 0 or rows.max() >= p.n_owned):
+                raise ValueError(f"rank {q} asked rank {self.rank} for an entry it does not own")
+            send_rows.append(rows)
+            send_ptr.append(send_ptr[-1] + len(rows))
+            got = requests.get(q, np.zeros(0, dtype=np.int64))
+            recv_gids.append(got)
+            recv_ptr.append(recv_ptr[-1] + len(got))
+        cat = lambda parts: (np.concatenate(parts) if parts else np.zeros(0)).astype(np.uint32)
+        self.halo_peers, self.halo_send_ptr, self.halo_recv_ptr = peers, np.asarray(send_ptr, dtype=np.uint64), np.asarray(recv_ptr, dtype=np.uint64)
+        self.halo_send_rows, self.halo_recv_gids = cat(send_rows), cat(recv_gids)
+        ctx.set_halo_plan(n_global, p.f0, peers, self.halo_send_ptr, self.halo_send_rows, self.halo_recv_ptr, self.halo_recv_gids)
+
     # -- per step --------------------------------------------------------------------------------------------
     def _exchange_ops(self):
         """The grouped send/recv of one step (built once: buffers and slot ranges are fixed at setup)."""

@@ -39,6 +39,12 @@ class HostCtx:
     def set_pattern(self, rp, ci): self.rp, self.ci = np.asarray(rp, dtype=np.uint64), ci
     def set_exchange_plan(self, *a): self.plan = a
     def prepare(self): pass
+    def halo_columns(self, n_global, first):  # feasm_halo_columns: columns of the owned rows outside the owned range + ghost-row ids
+        rp = self.rp.astype(np.int64)
+        cols = self.ci[: rp[self.n_owned]].astype(np.int64)
+        out = np.unique(np.concatenate([cols[(cols < first) | (cols >= first + self.n_owned)], self.gid[self.n_owned:]]))
+        return out.astype(np.uint32)
+    def set_halo_plan(self, *a): self.halo = a
 
 
 def main():
@@ -107,6 +113,32 @@ def main():
     sv = max(np.abs(ref_v).max(), 1e-300)
     assert np.abs(own_v - ref_v).max() <= 1e-13 * sv, ("values", np.abs(own_v - ref_v).max())
     assert np.abs(own_b - ref_b).max() <= 1e-13 * max(np.abs(ref_b).max(), 1e-300), "rhs"
+    # ---- the halo of a distributed vector with the requests carried by torch.distributed (DistributedAssembly.setup_halo):
+    # y = A x on the owned rows after fetching the entries of x other ranks own, against the global product
+    da.setup_halo()
+    n_global, first, hp, hsp, hsr, hrp, hrg = ctx.halo
+    assert n_global == s.n_dofs and first == f0
+    x = np.cos(0.37 * np.arange(s.n_dofs)) + 0.1
+    x_own = x[f0:f0 + n_own]
+    hs = torch.from_numpy(x_own[hsr.astype(np.int64)].copy())          # feasm_halo_pack
+    hr = torch.zeros(int(hrp[-1]), dtype=torch.float64)
+    ops = []
+    for i, q in enumerate(hp):
+        if hrp[i + 1] > hrp[i]: ops.append(dist.P2POp(dist.irecv, hr[int(hrp[i]):int(hrp[i + 1])], int(q)))
+    for i, q in enumerate(hp):
+        if hsp[i + 1] > hsp[i]: ops.append(dist.P2POp(dist.isend, hs[int(hsp[i]):int(hsp[i + 1])], int(q)))
+    if ops:
+        for w in dist.batch_isend_irecv(ops): w.wait()
+    x_full = np.full(s.n_dofs, np.nan)                                   # a column nobody sent would poison the product
+    x_full[f0:f0 + n_own] = x_own
+    x_full[hrg.astype(np.int64)] = hr.numpy()                           # feasm_halo_unpack
+    assert np.array_equal(x_full[hrg.astype(np.int64)], x[hrg.astype(np.int64)]), "halo entries are not the owners' values"
+    assert not np.isnan(x_full[prob.ghosts]).any(), "ghost rows are part of the halo (feasm_residual needs them)"
+    y = np.array([own_v[rp[r]:rp[r + 1]] @ x_full[ctx.ci[rp[r]:rp[r + 1]].astype(np.int64)] for r in range(n_own)])
+    import scipy.sparse as sps
+    A = sps.csr_matrix((gv, gci.astype(np.int64), grp.astype(np.int64)), shape=(s.n_dofs, s.n_dofs))
+    y_ref = (A @ x)[f0:f0 + n_own]
+    assert not np.isnan(y).any() and np.abs(y - y_ref).max() <= 1e-12 * np.abs(A @ x).max(), "distributed product"
     total = torch.tensor([float(n_own)])
     dist.all_reduce(total)
     assert int(total.item()) == s.n_dofs, "owned ranges do not tile the dof space"
