@@ -35,7 +35,7 @@ def lib():
         L.ref_gauss_rule.restype = C.c_int
         L.ref_gauss_rule.argtypes = [C.c_int] * 4 + [C.c_void_p] * 2 + [C.c_char_p, C.c_int]
         L.ref_fe_map.restype = C.c_int
-        L.ref_fe_map.argtypes = [C.c_int, C.c_int, C.c_void_p, C.c_int, C.c_int] + [C.c_void_p] * 6 + [C.c_char_p, C.c_int]
+        L.ref_fe_map.argtypes = [C.c_int, C.c_int, C.c_int, C.c_void_p, C.c_int, C.c_int] + [C.c_void_p] * 6 + [C.c_char_p, C.c_int]
         L.ref_exact_solution.restype = C.c_double
         L.ref_exact_solution.argtypes = [C.c_double] * 3
         _lib = L
@@ -71,15 +71,16 @@ def gauss_rule(elem: str, order: int):
 
 
 def fe_map(elem: str, node_xyz, ref_points, weights, affine: bool):
-    """FEMap::init_reference_to_physical_map<3> + FEMap::compute_map (src/fe/fe_map.C) on one element: dict(xyz [nq][3],
-    JxW [nq], jac [nq], inv [nq][3][3] with inv[q][a][d] = d(xi_a)/d(x_d)).  `affine` stands in for Elem::has_affine_map()."""
+    """FEMap::init_reference_to_physical_map + FEMap::compute_map (src/fe/fe_map.C) on one element — a 3D cell, or a 2D
+    element embedded in space (QUAD4 / QUAD8 / QUAD9 / TRI6: the surface Jacobian) — dict(xyz [nq][3], JxW [nq], jac [nq],
+    inv [nq][3][3] with inv[q][a][d] = d(xi_a)/d(x_d)).  `affine` stands in for Elem::has_affine_map()."""
     X = np.ascontiguousarray(node_xyz, dtype=np.float64).reshape(N_NODES[elem], 3)
     pts = np.ascontiguousarray(ref_points, dtype=np.float64).reshape(-1, 3)
     w = np.ascontiguousarray(weights, dtype=np.float64)
     nq = pts.shape[0]
     xyz, JxW, jac, inv = np.zeros((nq, 3)), np.zeros(nq), np.zeros(nq), np.zeros((nq, 9))
     err = C.create_string_buffer(1024)
-    rc = lib().ref_fe_map(ELEM[elem], N_NODES[elem], X.ctypes.data, int(bool(affine)), nq, pts.ctypes.data, w.ctypes.data,
+    rc = lib().ref_fe_map(DIM[elem], ELEM[elem], N_NODES[elem], X.ctypes.data, int(bool(affine)), nq, pts.ctypes.data, w.ctypes.data,
                           xyz.ctypes.data, JxW.ctypes.data, jac.ctypes.data, inv.ctypes.data, err, 1024)
     if rc:
         raise RuntimeError(err.value.decode())

@@ -83,13 +83,14 @@ int ref_gauss_rule(int dim, int elem_type, int order, int cap, double* pts, doub
   }
 }
 
-// FEMap::init_reference_to_physical_map<3> + FEMap::compute_map (src/fe/fe_map.C:109-444, :1323-1372 with
-// compute_single_point_map :448-1077 or compute_affine_map :1167-1244) for one 3D element given by its node coordinates, at
+// FEMap::init_reference_to_physical_map<dim> + FEMap::compute_map (src/fe/fe_map.C:109-444, :1323-1372 with
+// compute_single_point_map :448-1077 or compute_affine_map :1167-1244) for one element given by its node coordinates — a 3D
+// cell (dim 3) or a 2D element embedded in space (dim 2: the surface-Jacobian branch sqrt(g11 g22 - g12 g21), :810-860) — at
 // the nq reference points `pts` with weights `qw`.  `affine` plays Elem::has_affine_map() (the element classes cannot be
 // compiled stand-alone; the caller forces either branch).  Out: xyz[nq][3], JxW[nq], jac[nq] and
 // inv[nq][9] = dxidx, dxidy, dxidz, detadx, detady, detadz, dzetadx, dzetady, dzetadz.  Returns 0, or -1 when the reference
 // code throws (DegenerateMap: the message goes to err).
-int ref_fe_map(int elem_type, int n_nodes, const double* node_xyz, int affine, int nq, const double* pts, const double* qw,
+int ref_fe_map(int dim, int elem_type, int n_nodes, const double* node_xyz, int affine, int nq, const double* pts, const double* qw,
                double* xyz, double* JxW, double* jac, double* inv, char* err, int err_len) {
   try {
     Elem elem(static_cast<ElemType>(elem_type), 0);
@@ -104,13 +105,14 @@ int ref_fe_map(int elem_type, int n_nodes, const double* node_xyz, int affine, i
     const std::vector<Real>& m_jac = map.get_jacobian();
     const std::vector<Real>* m_inv[9] = {&map.get_dxidx(),  &map.get_dxidy(),  &map.get_dxidz(),  &map.get_detadx(),  &map.get_detady(),
                                          &map.get_detadz(), &map.get_dzetadx(), &map.get_dzetady(), &map.get_dzetadz()};
-    map.init_reference_to_physical_map<3>(qp, &elem);
-    map.compute_map(3, w, &elem, /*calculate_d2phi=*/false);
+    if (dim == 3) map.init_reference_to_physical_map<3>(qp, &elem);
+    else map.init_reference_to_physical_map<2>(qp, &elem);
+    map.compute_map((unsigned int)dim, w, &elem, /*calculate_d2phi=*/false);
     for (int p = 0; p < nq; ++p) {
       if (xyz) { xyz[3 * p] = m_xyz[p](0); xyz[3 * p + 1] = m_xyz[p](1); xyz[3 * p + 2] = m_xyz[p](2); }
       if (JxW) JxW[p] = m_JxW[p];
-      if (jac) jac[p] = m_jac[p];
-      if (inv) for (int k = 0; k < 9; ++k) inv[9 * p + k] = (*m_inv[k])[p];
+      if (jac) jac[p] = (std::size_t)p < m_jac.size() ? m_jac[p] : 0.;
+      if (inv) for (int k = 0; k < 9; ++k) inv[9 * p + k] = (std::size_t)p < m_inv[k]->size() ? (*m_inv[k])[p] : 0.;  // (a 2D map sizes no zeta entries)
     }
     return 0;
   } catch (const std::exception& e) {

@@ -258,3 +258,31 @@ def test_ex6_element_matrices_from_reference_tables_only(elem, skew):
                 Fe[i * n:(i + 1) * n] += mp["JxW"][q] * (f[i] * sh[0][:, q])
         assert np.array_equal(Ke, Ko[e]), np.abs(Ke - Ko[e]).max()
         assert np.array_equal(Fe, Fo[e]), np.abs(Fe - Fo[e]).max()
+
+
+H27_SIDE = [[0, 3, 2, 1, 11, 10, 9, 8, 20], [0, 1, 5, 4, 8, 13, 16, 12, 21], [1, 2, 6, 5, 9, 14, 17, 13, 22],  # cell_hex27.C:37-45
+            [2, 3, 7, 6, 10, 15, 18, 14, 23], [3, 0, 4, 7, 11, 12, 19, 15, 24], [4, 5, 6, 7, 16, 17, 18, 19, 25]]
+T10_SIDE = [[0, 2, 1, 6, 5, 4], [0, 1, 3, 4, 8, 7], [1, 2, 3, 5, 9, 8], [2, 0, 3, 6, 7, 9]]                      # cell_tet10.C:37-43
+
+
+@needs_ref
+@pytest.mark.parametrize("elem,side_elem,ns,order,amp", [("HEX27", "QUAD9", 9, 5, 0.03), ("HEX20", "QUAD8", 8, 5, 0.03), ("HEX8", "QUAD4", 4, 3, 0.04),
+                                                         ("HEX8", "QUAD4", 4, 5, 0.04), ("TET10", "TRI6", 6, 5, 0.008)])
+def test_side_maps_are_the_reference_surface_map_bit_for_bit(elem, side_elem, ns, order, amp):
+    """FE::reinit(elem, side): side points and JxW_face = sqrt(g11 g22 - g12 g21) w.  FEMap::compute_face_map itself sits in
+    fe_boundary.C (not compilable stand-alone); its arithmetic is the 2D-element-in-space branch of
+    FEMap::compute_single_point_map (fe_map.C:730-860: the same sums over the side's nodes, the same first fundamental form),
+    which IS compiled: fed with the side's nodes (Hex27 / Hex20 / Hex8 / Tet10 side_nodes_map) and the reference's 2D rule it
+    gives the oracle's side points and weights bit for bit, on perturbed (curved-side) elements."""
+    orc = ORC[elem]
+    m = O.Mesh(orc, 2, 2, 1, bounds=(-1, 1, -1, 1, 0, 1))
+    m.skew(1, amp, 5)
+    xyz, conn, _ = m.arrays()
+    pts, w = R.gauss_rule(side_elem, order)
+    for e in range(0, m.n_elem, max(1, m.n_elem // 5)):
+        X = xyz[conn[e]]
+        for side in range(4 if elem == "TET10" else 6):
+            nodes = (T10_SIDE if elem == "TET10" else H27_SIDE)[side][:ns]
+            d = O.side_reinit(orc, X, side, order)
+            r = R.fe_map(side_elem, X[nodes], pts, w, False)
+            assert np.array_equal(d["xyz"], r["xyz"]) and np.array_equal(d["JxW"], r["JxW"])
