@@ -286,3 +286,29 @@ def test_side_maps_are_the_reference_surface_map_bit_for_bit(elem, side_elem, ns
             d = O.side_reinit(orc, X, side, order)
             r = R.fe_map(side_elem, X[nodes], pts, w, False)
             assert np.array_equal(d["xyz"], r["xyz"]) and np.array_equal(d["JxW"], r["JxW"])
+
+
+@needs_ref
+def test_hanging_node_coefficients_of_the_test_meshes_are_the_reference_side_shapes():
+    """lagrange_compute_constraints (src/fe/fe_lagrange.C) sets the coefficient of a hanging node on a parent's side to the
+    parent side's shape function at the node's position there.  The refined test meshes of tests/hanging.py use 1/2 (HEX8
+    edges), 1/4 (HEX8 faces) and the products of 3/8, 3/4, -1/8 (HEX27): exactly what the reference's compiled QUAD4 / QUAD9
+    functions give at the half and quarter points."""
+    from hanging import _quad_weights
+
+    # QUAD9 nodes on the bottom edge eta = -1: corner 0 (xi = -1), corner 1 (xi = +1), mid-edge 4 (xi = 0)
+    for rel in range(5):
+        p = (rel - 2) / 2.0
+        phi = R.shapes("QUAD9", [[p, -1.0, 0.0]])[0][:, 0]
+        want = _quad_weights(rel)
+        assert phi[0] == want.get(0, 0.0) and phi[4] == want.get(2, 0.0) and phi[1] == want.get(4, 0.0)
+    # a face-hanging HEX27 node at the quarter point (-1/2, +1/2) of a coarse face: tensor products of the 1D weights
+    phi = R.shapes("QUAD9", [[-0.5, 0.5, 0.0]])[0][:, 0]
+    wx, wy = _quad_weights(1), _quad_weights(3)
+    xi_of = {0: 0, 1: 4, 2: 4, 3: 0, 4: 2, 5: 4, 6: 2, 7: 0, 8: 2}   # QUAD9 node -> coarse lattice coordinate along xi (0, 2, 4)
+    eta_of = {0: 0, 1: 0, 2: 4, 3: 4, 4: 0, 5: 2, 6: 4, 7: 2, 8: 2}
+    for a in range(9):
+        assert phi[a] == wx[xi_of[a]] * wy[eta_of[a]]
+    # HEX8: the middle of an edge / of a face of the bilinear QUAD4
+    assert np.array_equal(R.shapes("QUAD4", [[0.0, -1.0, 0.0]])[0][:, 0], [0.5, 0.5, 0.0, 0.0])
+    assert np.array_equal(R.shapes("QUAD4", [[0.0, 0.0, 0.0]])[0][:, 0], [0.25, 0.25, 0.25, 0.25])
