@@ -331,8 +331,8 @@ int feasm_get_exchange_plan(feasm_ctx* ctx, int32_t* peers, uint64_t* send_ptr, 
 
 /* ---- the assembled matrix of several ranks used on the device: the halo of a distributed vector ---------------------------
  * The owned rows hold GLOBAL column ids, so y = A x needs the entries of x that other ranks own: what
- * NumericVector::localize(v_local, send_list) (numeric_vector.h:478-487; DistributedVector::localize,
- * src/numerics/distributed_vector.C:474-560) fetches with the DofMap's send_list.  The library keeps a column-space copy of x
+ * NumericVector::localize(v_local, send_list) (numeric_vector.h:644-650; DistributedVector::localize,
+ * src/numerics/distributed_vector.C:479-521) fetches with the DofMap's send_list.  The library keeps a column-space copy of x
  * of global length (n_global doubles) per context: owned part copied, ghost entries scattered in.
  *   feasm_build_halo     : collective over the context's communicator, after the final pattern (feasm_build_exchange):
  *                          finds the needed columns on the device (columns of the owned rows outside the owned range, plus

@@ -37,7 +37,7 @@ int main(int argc, char** argv) {
   std::set<boundary_id_type> ids = {0, 1, 2, 3, 4, 5};
   std::vector<unsigned int> vars = {u_var};
   WrappedFunction<Number> g(system, exact_solution_wrapper);
-  system.get_dof_map().add_dirichlet_boundary(DirichletBoundary(ids, vars, g));  // introduction_ex4.C:217-243
+  system.get_dof_map().add_dirichlet_boundary(DirichletBoundary(ids, vars, g));  // introduction_ex4.C:242-274
   es.init();
   auto& A_gpu = static_cast<GpuSparseMatrix<Number>&>(system.get_matrix("feasm"));
   GpuNumericVector<Number> b_gpu(init.comm(), system.n_dofs());

@@ -48,7 +48,7 @@ public:
 };
 }  // namespace libMesh
 
-// include/fe/fe.h:1738-1800
+// include/fe/fe.h:1738-1788
 #define LIBMESH_DEFAULT_VECTORIZED_FE(MyDim, MyType)                                                                                           \
   template <> void FE<MyDim, MyType>::all_shapes(const Elem* elem, const Order o, const std::vector<Point>& p,                                \
                                                   std::vector<std::vector<OutputShape>>& v, const bool add_p_level) {                        \

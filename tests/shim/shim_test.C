@@ -54,7 +54,7 @@ int main() {
       load_elems.push_back((uint32_t)e); load_sides.push_back(2);
     }
   }
-  // Dirichlet dofs on the whole boundary with the exact solution of ex4 (DirichletBoundary, introduction_ex4.C:217-243)
+  // Dirichlet dofs on the whole boundary with the exact solution of ex4 (DirichletBoundary, introduction_ex4.C:242-274)
   const double hp = 1.5707963267948966;
   for (int64_t i = 0; i < n_nodes; ++i)
     if (mask[i]) dof_map._vals[base[i]] = std::cos(hp * xyz[3 * i]) * std::sin(hp * xyz[3 * i + 1]) * std::cos(hp * xyz[3 * i + 2]);
