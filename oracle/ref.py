@@ -85,3 +85,102 @@ def fe_map(elem: str, node_xyz, ref_points, weights, affine: bool):
     if rc:
         raise RuntimeError(err.value.decode())
     return dict(xyz=xyz, JxW=JxW, jac=jac, inv=inv.reshape(nq, 3, 3))
+
+
+# ---- oracle/_ref/libref_app.so: the reference's own APPLICATION source of the path (introduction_ex4.C) over the stub world of
+# oracle/ref_app/ref_world.h, plus the constraint functions of src/base/dof_map_constraints.C (see that header for what is the
+# reference's code and what is glue) -------------------------------------------------------------------------------------------------
+APP_LIB_PATH = os.path.join(os.path.dirname(os.path.abspath(__file__)), "_ref", "libref_app.so")
+_ORC_TO_LIBMESH = {8: "HEX8", 20: "HEX20", 27: "HEX27", 10: "TET10", 18: "PRISM18"}
+_app = None
+
+
+def app_available() -> bool:
+    return os.path.exists(APP_LIB_PATH)
+
+
+def app():
+    global _app
+    if _app is None:
+        L = C.CDLL(APP_LIB_PATH)
+        L.ref_world_load.restype = C.c_int
+        L.ref_world_load.argtypes = [C.c_int, C.c_int, C.c_uint, C.c_uint, C.c_uint, C.c_void_p, C.c_uint64, C.c_void_p, C.c_uint64, C.c_void_p, C.c_void_p,
+                                     C.c_void_p, C.c_int, C.c_uint64, C.c_void_p, C.c_void_p, C.c_void_p]
+        L.ref_ex4_run.restype = C.c_int
+        L.ref_ex4_run.argtypes = [C.c_int, C.POINTER(C.c_char_p), C.c_char_p, C.c_int]
+        L.ref_world_results.restype = C.c_int64
+        L.ref_world_results.argtypes = [C.c_void_p] * 4
+        L.ref_constrain_element.restype = C.c_int
+        L.ref_constrain_element.argtypes = [C.c_int, C.c_void_p, C.c_void_p, C.c_void_p, C.c_int, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p,
+                                            C.c_int, C.c_int, C.c_int, C.c_void_p, C.c_void_p, C.c_void_p, C.c_char_p, C.c_int]
+        _app = L
+    return _app
+
+
+def load_world(mesh, system, n, bounds, affine=None):
+    """Hands the stub world the integer structures of an oracle Mesh / System (oracle.py): the mesh that build_cube(n, n, n,
+    bounds) is going to be asked for, the dof of every (variable, node), and the sparsity pattern."""
+    from . import oracle as O
+
+    xyz, conn, mask = mesh.arrays()
+    ed, _, _ = system.dofs()
+    npe, nv, nn = mesh.npe, system.n_vars, mesh.n_nodes
+    node_dof = np.zeros((nv, nn), dtype=np.uint32)
+    for v in range(nv):
+        node_dof[v, conn.reshape(-1)] = ed[:, v * npe:(v + 1) * npe].reshape(-1)
+    if affine is None:
+        affine = np.array([O.has_affine_map(mesh.elem_type, xyz[conn[e]]) for e in range(mesh.n_elem)], dtype=np.uint8)
+    affine = np.ascontiguousarray(affine, dtype=np.uint8)
+    rp, ci = system.sparsity()
+    b = np.ascontiguousarray(bounds, dtype=np.float64)
+    nx, ny, nz = (n, n, n) if np.isscalar(n) else n
+    app().ref_world_load(ELEM[_ORC_TO_LIBMESH[mesh.elem_type]], npe, nx, ny, nz, b.ctypes.data, nn, xyz.ctypes.data, mesh.n_elem, conn.ctypes.data,
+                         affine.ctypes.data, mask.ctypes.data, nv, system.n_dofs, node_dof.ctypes.data, rp.ctypes.data, ci.ctypes.data)
+    return len(ci), system.n_dofs
+
+
+def run_ex4(args, nnz, n_dofs):
+    """main() of examples/introduction/introduction_ex4/introduction_ex4.C with the command line `args` ("-d 3 -n 4 ...") over the
+    loaded world: dict(values, rhs, con_dof, con_val) as the run left them (system.solve() assembles; the linear solve is not on
+    the path)."""
+    argv = [b"introduction_ex4"] + [str(a).encode() for a in args]
+    arr = (C.c_char_p * len(argv))(*argv)
+    err = C.create_string_buffer(1024)
+    rc = app().ref_ex4_run(len(argv), arr, err, 1024)
+    if rc != 0:
+        raise RuntimeError(f"introduction_ex4 returned {rc}: {err.value.decode()}")
+    values, rhs = np.zeros(nnz), np.zeros(n_dofs)
+    nc = app().ref_world_results(None, None, None, None)
+    cd, cv = np.zeros(nc, dtype=np.uint32), np.zeros(nc)
+    app().ref_world_results(values.ctypes.data, rhs.ctypes.data, cd.ctypes.data, cv.ctypes.data)
+    return dict(values=values, rhs=rhs, con_dof=cd, con_val=cv)
+
+
+def constrain_element(K, F, dofs, rows, values=None, heterogeneous=True, asymmetric=True):
+    """DofMap::(heterogeneously_)constrain_element_matrix_and_vector of the reference (src/base/dof_map_constraints.C:2439-2614,
+    with build_constraint_matrix(_and_vector) :3433-3680) on one element.  rows: {constrained dof: {dof: coefficient}} (an empty
+    dict is a Dirichlet row); values: {constrained dof: value}.  Returns (K', F', dofs') — the dof set grows by the constraining
+    dofs that are not the element's."""
+    K = np.ascontiguousarray(K, dtype=np.float64)
+    F = np.ascontiguousarray(F, dtype=np.float64)
+    d = np.ascontiguousarray(dofs, dtype=np.uint32)
+    n = len(d)
+    cd = np.array(sorted(rows), dtype=np.uint32)
+    ptr = np.zeros(len(cd) + 1, dtype=np.uint64)
+    rd, rc_ = [], []
+    for i, c in enumerate(cd):
+        for k in sorted(rows[int(c)]):
+            rd.append(k)
+            rc_.append(rows[int(c)][k])
+        ptr[i + 1] = len(rd)
+    rd = np.array(rd + [0], dtype=np.uint32)
+    rcoef = np.array(rc_ + [0.0], dtype=np.float64)
+    cv = np.array([(values or {}).get(int(c), 0.0) for c in cd] + [0.0], dtype=np.float64)
+    cap = n + len(rd) + 8
+    do, Ko, Fo = np.zeros(cap, dtype=np.uint32), np.zeros(cap * cap), np.zeros(cap)
+    err = C.create_string_buffer(1024)
+    m = app().ref_constrain_element(n, K.ctypes.data, F.ctypes.data, d.ctypes.data, len(cd), cd.ctypes.data, ptr.ctypes.data, rd.ctypes.data, rcoef.ctypes.data,
+                                    cv.ctypes.data, int(heterogeneous), int(asymmetric), cap, do.ctypes.data, Ko.ctypes.data, Fo.ctypes.data, err, 1024)
+    if m < 0:
+        raise RuntimeError(err.value.decode())
+    return Ko[: m * m].reshape(m, m).copy(), Fo[:m].copy(), do[:m].copy()

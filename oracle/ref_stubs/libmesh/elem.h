@@ -16,7 +16,8 @@ public:
   unsigned int p_level() const { return _p; }
   unsigned short dim() const { return (unsigned short)(_t <= EDGE4 ? 1 : (_t <= QUAD9 ? 2 : 3)); }  // the types this shim is asked for
   bool runtime_topology() const { return false; }
-  dof_id_type id() const { return 0; }
+  dof_id_type id() const { return _id; }
+  void set_id(dof_id_type i) { _id = i; }
   // nodes
   void set_nodes(const double* xyz, unsigned int n) { _nodes.clear(); for (unsigned int i = 0; i < n; ++i) _nodes.emplace_back(Point(xyz[3 * i], xyz[3 * i + 1], xyz[3 * i + 2]), i); }
   unsigned int n_nodes() const { return (unsigned int)_nodes.size(); }
@@ -42,6 +43,7 @@ private:
   ElemType _t;
   unsigned int _p;
   bool _affine = false;
+  dof_id_type _id = 0;
   std::vector<Node> _nodes;
 };
 }  // namespace libMesh

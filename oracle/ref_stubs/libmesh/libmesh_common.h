@@ -6,6 +6,9 @@
 #ifndef REF_STUB_LIBMESH_COMMON_H
 #define REF_STUB_LIBMESH_COMMON_H
 #include <cmath>
+#include <complex>
+#include <iomanip>
+#include <type_traits>
 #include <cstddef>
 #include <iostream>
 #include <memory>
@@ -17,10 +20,21 @@
 
 #define LIBMESH_DIM 3
 #define LIBMESH_ENABLE_SECOND_DERIVATIVES 1
+#define LIBMESH_DEFAULT_DOUBLE_PRECISION 1
+#define LIBMESH_USE_REAL_NUMBERS 1
 
 namespace libMesh {
 typedef double Real;  // include/base/libmesh_common.h:144 (default configuration)
 typedef Real Number;
+typedef std::complex<Real> Complex;
+// libmesh_common.h:189-250, :717-718
+template <typename T> inline T libmesh_real(T a) { return a; }
+template <typename T> inline T libmesh_conj(T a) { return a; }
+template <typename T> inline T libmesh_real(std::complex<T> a) { return std::real(a); }
+template <typename T> inline std::complex<T> libmesh_conj(std::complex<T> a) { return std::conj(a); }
+template <typename T> inline bool isnan(std::complex<T> a) { return std::isnan(std::real(a)) || std::isnan(std::imag(a)); }
+template <typename T> inline bool isinf(std::complex<T> a) { return std::isinf(std::real(a)) || std::isinf(std::imag(a)); }
+template <class T> constexpr std::false_type always_false{};
 typedef unsigned int dof_id_type;
 struct LogicError : std::runtime_error { using std::runtime_error::runtime_error; };
 struct NotImplemented : std::runtime_error { using std::runtime_error::runtime_error; };

@@ -9,6 +9,8 @@ public:
   Point(Real x = 0., Real y = 0., Real z = 0.) { c[0] = x; c[1] = y; c[2] = z; }
   Real operator()(unsigned int i) const { return c[i]; }
   Real& operator()(unsigned int i) { return c[i]; }
+  Real& slice(unsigned int i) { return c[i]; }                                                 // TypeVector::slice (type_vector.h)
+  Real slice(unsigned int i) const { return c[i]; }
   Point operator-() const { return Point(-c[0], -c[1], -c[2]); }
   Point operator-(const Point& o) const { return Point(c[0] - o.c[0], c[1] - o.c[1], c[2] - o.c[2]); }
   Point operator+(const Point& o) const { return Point(c[0] + o.c[0], c[1] + o.c[1], c[2] + o.c[2]); }
