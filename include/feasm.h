@@ -109,7 +109,10 @@ int feasm_set_constraints(feasm_ctx* ctx, int64_t n_constraints, const uint32_t*
  * build_constraint_matrix_and_vector, :3543-3673, asymmetric_constraint_rows = true): the element's dof list grows by the
  * constraining dofs, K <- C^T K C, F <- C^T (F - K H).  Call it BEFORE feasm_build_pattern (the device-built pattern then
  * holds the couplings DofMap::find_connected_dofs adds, dof_map.C:2915-2975) or pass libMesh's own Graph to
- * feasm_set_pattern.  One rank per context; feasm_assemble only (not begin / end, not feasm_residual). */
+ * feasm_set_pattern.  Rows are expected as DofMap::process_constraints leaves them before any assembly (no constraining
+ * dof with a NON-empty row of its own is required — those are substituted, :3595-3673 — but a constraining dof that is itself
+ * a Dirichlet dof keeps, in FEASM_CONSTRAIN_HOMOGENEOUS mode, right-hand side 0 here where :2439-2514 would leave (C^T F)_i).
+ * One rank per context; feasm_assemble only (not begin / end, not feasm_residual). */
 int feasm_set_constraint_rows(feasm_ctx* ctx, int64_t n, const uint32_t* dofs, const uint64_t* row_ptr, const uint32_t* cols,
                               const double* coefs, const double* values);
 

@@ -13,9 +13,12 @@ libMesh in plain Python for small meshes.  Nothing in the product imports this.
   assemble                             the per-element loop of introduction_ex4.C:393-563 with these pieces: Ke/Fe from the C
                                        oracle (unconstrained), constrained here, added in element order
 
-Pinned by what the construction guarantees rather than by a golden vector (the reference's own test,
-tests/systems/constraint_operator_test.C, needs a libMesh build): with empty rows only it must equal the C oracle's
-Dirichlet path entry for entry, and a hanging-node mesh must reproduce a linear solution exactly (tests/test_oracle_constraints.py).
+Pinned against the reference's own functions: the four definitions are cut out of src/base/dof_map_constraints.C at build time
+and compiled over the reference's DenseMatrix sources into oracle/_ref/libref_app.so; tests/test_oracle_ref_app.py compares
+constrain() with them on hand-made rows (recursion, Dirichlet masters, self-constrained elements, both flags) and on every
+element of locally refined HEX8 / HEX27 meshes — same widened dof sets, values to rounding (numpy's matrix products sum in
+another order).  And by construction: with empty rows only it equals the C oracle's Dirichlet path entry for entry, and a
+hanging-node mesh reproduces a linear (HEX27: quadratic) solution exactly (tests/test_oracle_constraints.py).
 """
 import numpy as np
 
@@ -94,9 +97,12 @@ def constrain(con, Ke, Fe, elem_dofs, hetero=True, asymmetric=True):
                     for k, dk in enumerate(dofs):
                         if dk == j:
                             K[i, k] = -c
-                F[i] = con.values.get(d, 0.0) if hetero else 0.0
-            else:
+                if hetero:
+                    F[i] = con.values.get(d, 0.0)
+            elif hetero:
                 F[i] = 0.0
+            # constrain_element_matrix_and_vector (:2439-2514) leaves rhs(i) = (C^T F)(i): zero for rows as
+            # DofMap::process_constraints leaves them (no constraining dof is itself constrained, so column i of C is zero)
     return K, F, dofs
 
 

@@ -108,6 +108,8 @@ def app():
                                      C.c_void_p, C.c_int, C.c_uint64, C.c_void_p, C.c_void_p, C.c_void_p]
         L.ref_ex4_run.restype = C.c_int
         L.ref_ex4_run.argtypes = [C.c_int, C.POINTER(C.c_char_p), C.c_char_p, C.c_int]
+        L.ref_ex4_assemble.restype = C.c_int
+        L.ref_ex4_assemble.argtypes = [C.c_int, C.c_uint, C.c_char_p, C.c_int]
         L.ref_world_results.restype = C.c_int64
         L.ref_world_results.argtypes = [C.c_void_p] * 4
         L.ref_constrain_element.restype = C.c_int
@@ -139,6 +141,26 @@ def load_world(mesh, system, n, bounds, affine=None):
     return len(ci), system.n_dofs
 
 
+def _results(nnz, n_dofs):
+    values, rhs = np.zeros(nnz), np.zeros(n_dofs)
+    nc = app().ref_world_results(None, None, None, None)
+    cd, cv = np.zeros(nc, dtype=np.uint32), np.zeros(nc)
+    app().ref_world_results(values.ctypes.data, rhs.ctypes.data, cd.ctypes.data, cv.ctypes.data)
+    return dict(values=values, rhs=rhs, con_dof=cd, con_val=cv)
+
+
+def assemble_ex4(order, nnz, n_dofs, boundary_ids=(0, 1, 2, 3, 4, 5)):
+    """assemble_poisson of introduction_ex4.C on the loaded mesh, set up as its main() does (a "Poisson" system, one LAGRANGE
+    variable of `order`, DirichletBoundary with the exact solution on `boundary_ids`) — for the meshes main() does not build."""
+    mask = 0
+    for b in boundary_ids:
+        mask |= 1 << b
+    err = C.create_string_buffer(1024)
+    if app().ref_ex4_assemble(int(order), mask, err, 1024) != 0:
+        raise RuntimeError(err.value.decode())
+    return _results(nnz, n_dofs)
+
+
 def run_ex4(args, nnz, n_dofs):
     """main() of examples/introduction/introduction_ex4/introduction_ex4.C with the command line `args` ("-d 3 -n 4 ...") over the
     loaded world: dict(values, rhs, con_dof, con_val) as the run left them (system.solve() assembles; the linear solve is not on
@@ -149,11 +171,7 @@ def run_ex4(args, nnz, n_dofs):
     rc = app().ref_ex4_run(len(argv), arr, err, 1024)
     if rc != 0:
         raise RuntimeError(f"introduction_ex4 returned {rc}: {err.value.decode()}")
-    values, rhs = np.zeros(nnz), np.zeros(n_dofs)
-    nc = app().ref_world_results(None, None, None, None)
-    cd, cv = np.zeros(nc, dtype=np.uint32), np.zeros(nc)
-    app().ref_world_results(values.ctypes.data, rhs.ctypes.data, cd.ctypes.data, cv.ctypes.data)
-    return dict(values=values, rhs=rhs, con_dof=cd, con_val=cv)
+    return _results(nnz, n_dofs)
 
 
 def constrain_element(K, F, dofs, rows, values=None, heterogeneous=True, asymmetric=True):

@@ -133,7 +133,10 @@ void EquationSystems::init() {
 }  // namespace libMesh
 
 using namespace libMesh;
-int ref_ex4_main(int argc, char** argv);  // examples/introduction/introduction_ex4/introduction_ex4.C, compiled with -Dmain=ref_ex4_main
+// examples/introduction/introduction_ex4/introduction_ex4.C, compiled with -Dmain=ref_ex4_main
+int ref_ex4_main(int argc, char** argv);
+void assemble_poisson(EquationSystems& es, const std::string& system_name);
+void exact_solution_wrapper(DenseVector<Number>& output, const Point& p, const Real);
 
 namespace {
 int fail(const std::exception& e, char* err, int err_len) {
@@ -174,6 +177,32 @@ int ref_ex4_run(int argc, const char* const* argv, char* err, int err_len) {
     std::vector<char*> av;
     for (auto& s : store) av.push_back(s.data());
     return ref_ex4_main(argc, av.data());
+  } catch (const std::exception& e) { return fail(e, err, err_len); }
+}
+
+// assemble_poisson of introduction_ex4.C called the way its main() sets it up (:190-274), but on whatever mesh was loaded — the
+// element types main() does not ask build_cube for (TET10, HEX20, PRISM18), skewed or locally refined meshes: a "Poisson" system
+// with one LAGRANGE variable of `order`, DirichletBoundary with exact_solution_wrapper on the boundary ids of `boundary_mask`.
+int ref_ex4_assemble(int order, unsigned int boundary_mask, char* err, int err_len) {
+  try {
+    const RefWorldData& w = ref_world();
+    const char* none[1] = {"ref_ex4_assemble"};
+    LibMeshInit init(1, none);
+    Mesh mesh(init.comm());
+    MeshTools::Generation::build_cube(mesh, w.nx, w.ny, w.nz, w.bounds[0], w.bounds[1], w.bounds[2], w.bounds[3], w.bounds[4], w.bounds[5],
+                                      static_cast<ElemType>(w.elem_type));
+    EquationSystems equation_systems(mesh);
+    LinearImplicitSystem& system = equation_systems.add_system<LinearImplicitSystem>("Poisson");
+    const unsigned int u_var = system.add_variable("u", static_cast<Order>(order), LAGRANGE);
+    system.attach_assemble_function(assemble_poisson);
+    std::set<boundary_id_type> boundary_ids;
+    for (int b = 0; b < 8; ++b) if (boundary_mask & (1u << b)) boundary_ids.insert((boundary_id_type)b);
+    AnalyticFunction<> exact_solution_object(exact_solution_wrapper);
+    DirichletBoundary dirichlet_bc(boundary_ids, {u_var}, exact_solution_object);
+    system.get_dof_map().add_dirichlet_boundary(dirichlet_bc);
+    equation_systems.init();
+    system.solve();
+    return 0;
   } catch (const std::exception& e) { return fail(e, err, err_len); }
 }
 

@@ -1,0 +1,68 @@
+"""Writes tests/golden/reference_ex4_runs.npz: the global matrix, right-hand side and Dirichlet constraints that the REFERENCE's
+own examples/introduction/introduction_ex4/introduction_ex4.C produces — its main() ("-d 3 -n N [-o FIRST]") or, for the meshes
+main() does not ask build_cube for, its assemble_poisson set up as main() does — compiled where it lies under /root/reference
+into oracle/_ref/libref_app.so (oracle/Makefile; oracle/ref_app/ref_world.h says what in that library is the reference's code
+and what is glue).  Run here, where /root/reference exists; the .npz travels to the GPU box, where tests/test_golden_ref_app.py
+and tests/test_gpu_golden_ref.py compare the oracle and the CUDA path with it.
+
+    python tests/golden/make_ref_app_golden.py
+"""
+import os
+import sys
+
+import numpy as np
+
+ROOT = os.path.dirname(os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
+sys.path.insert(0, ROOT)
+from oracle import oracle as O  # noqa: E402
+from oracle import ref as R  # noqa: E402
+
+BOUNDS = (-1.0, 1.0, -1.0, 1.0, -1.0, 1.0)
+# name, oracle element type, n (build_cube n^3), skew (kind, amplitude, seed) or None, FE order, through main()?
+CASES = [
+    ("hex27_main_n3", O.HEX27, 3, None, 2, True),
+    ("hex8_main_n4", O.HEX8, 4, None, 1, True),
+    ("hex27_skew_n2", O.HEX27, 2, (1, 0.03, 12345), 2, False),
+    ("hex8_skew_n3", O.HEX8, 3, (1, 0.05, 777), 1, False),
+    ("tet10_n2", O.TET10, 2, None, 2, False),
+    ("tet10_skew_n2", O.TET10, 2, (1, 0.02, 99), 2, False),
+    ("hex20_n2", O.HEX20, 2, None, 2, False),
+    ("hex20_skew_n2", O.HEX20, 2, (1, 0.03, 4321), 2, False),
+    ("prism18_n2", O.PRISM18, 2, None, 2, False),
+    ("prism18_skew_n2", O.PRISM18, 2, (1, 0.03, 2468), 2, False),
+]
+
+
+def oracle_case(etype, n, skew):
+    m = O.Mesh(etype, n, n, n, BOUNDS)
+    if skew is not None:
+        m.skew(*skew)
+    s = O.System(m, 1)
+    s.add_dirichlet((0, 1, 2, 3, 4, 5), 0)
+    s.build_sparsity()
+    return m, s
+
+
+def reference_run(m, s, n, order, through_main):
+    nnz, nd = R.load_world(m, s, n, BOUNDS)
+    if through_main:
+        return R.run_ex4(["-d", 3, "-n", n] + (["-o", "FIRST"] if order == 1 else []), nnz, nd)
+    return R.assemble_ex4(order, nnz, nd)
+
+
+def main():
+    out = {"names": np.array([c[0] for c in CASES])}
+    for name, etype, n, skew, order, through_main in CASES:
+        m, s = oracle_case(etype, n, skew)
+        r = reference_run(m, s, n, order, through_main)
+        out[name + "/spec"] = np.array([etype, n, order, int(through_main)] + list(skew or (-1, 0.0, 0)), dtype=np.float64)
+        for k in ("values", "rhs", "con_dof", "con_val"):
+            out[name + "/" + k] = r[k]
+        print(f"{name}: {len(r['values'])} entries, {len(r['rhs'])} dofs, {len(r['con_dof'])} constrained")
+    path = os.path.join(ROOT, "tests", "golden", "reference_ex4_runs.npz")
+    np.savez_compressed(path, **out)
+    print(path, os.path.getsize(path), "bytes")
+
+
+if __name__ == "__main__":
+    main()

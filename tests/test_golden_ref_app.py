@@ -1,0 +1,34 @@
+"""The oracle against outputs of the reference itself: tests/golden/reference_ex4_runs.npz holds the global matrix, right-hand
+side and Dirichlet constraints that the reference's own introduction_ex4.C (main() or assemble_poisson, compiled where it lies —
+tests/golden/make_ref_app_golden.py, oracle/ref_app/ref_world.h) produced on ten small meshes: every element family of the
+product, affine and skewed.  The oracle reproduces them bit for bit.  Needs neither /root/reference nor a GPU."""
+import os
+
+import numpy as np
+import pytest
+
+from oracle import oracle as O
+
+G = np.load(os.path.join(os.path.dirname(os.path.abspath(__file__)), "golden", "reference_ex4_runs.npz"))
+BOUNDS = (-1.0, 1.0, -1.0, 1.0, -1.0, 1.0)
+
+
+def golden_case(name):
+    etype, n, order, through_main, kind, amp, seed = G[name + "/spec"]
+    m = O.Mesh(int(etype), int(n), int(n), int(n), BOUNDS)
+    if kind >= 0:
+        m.skew(int(kind), float(amp), int(seed))
+    s = O.System(m, 1)
+    s.add_dirichlet((0, 1, 2, 3, 4, 5), 0)
+    s.build_sparsity()
+    return m, s
+
+
+@pytest.mark.parametrize("name", [str(n) for n in G["names"]])
+def test_oracle_reproduces_the_references_own_output(name):
+    m, s = golden_case(name)
+    v, r, _ = s.assemble(O.POISSON_EX4)
+    cd, cv = s.constraints()
+    assert np.array_equal(cd, G[name + "/con_dof"]) and np.array_equal(cv, G[name + "/con_val"])
+    assert np.array_equal(v, G[name + "/values"])
+    assert np.array_equal(r, G[name + "/rhs"])

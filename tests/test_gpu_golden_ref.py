@@ -1,0 +1,38 @@
+"""GPU parity against outputs of the reference itself: the CUDA path, through the C ABI, against the global matrix and right-hand
+side that the reference's own introduction_ex4.C produced (tests/golden/reference_ex4_runs.npz, written by
+tests/golden/make_ref_app_golden.py from the reference's sources compiled where they lie).  Same bar as test_gpu_parity.py:
+pattern bit-exact, values within 1e-12 per entry; the in-kernel finite-difference forcing at 1e-11 of max|rhs|,
+the tabulated forcing at 1e-12."""
+import numpy as np
+import pytest
+
+from conftest import PARITY_TOL, csr_parity_error, vec_parity_error
+from test_golden_ref_app import G, golden_case
+from test_gpu_parity import make_ctx
+
+pytestmark = pytest.mark.gpu
+
+
+@pytest.mark.parametrize("name", [str(n) for n in G["names"]])
+def test_cuda_path_against_the_references_own_output(name):
+    from libmesh_b200 import capi as F
+
+    m, s = golden_case(name)
+    ctx = make_ctx(m, s)
+    rp, ci = s.sparsity()
+    rp2, ci2 = ctx.get_pattern()
+    assert np.array_equal(rp, rp2) and np.array_equal(ci, ci2)
+    vg, rg = G[name + "/values"], G[name + "/rhs"]
+    assert len(vg) == ctx.nnz and len(rg) == s.n_dofs
+    # as the reference runs it: forcing by finite differences of the exact solution, inside the kernel
+    ctx.assemble(F.make_params(F.POISSON, 0, F.FORCING_EX4_FD))
+    v, r = ctx.get_values()
+    assert csr_parity_error(v, vg, rp) < PARITY_TOL
+    assert np.abs(r - rg).max() < 1e-11 * np.abs(rg).max()
+    # forcing tabulated at the quadrature points (the oracle's table): the right-hand side at the 1e-12 bar as well
+    f_tab, _ = s.forcing_at_qps(0)
+    ctx.assemble(F.make_params(F.POISSON, 0, F.FORCING_TABULATED, f_host=f_tab))
+    v, r = ctx.get_values()
+    assert csr_parity_error(v, vg, rp) < PARITY_TOL
+    assert vec_parity_error(r, rg) < PARITY_TOL
+    ctx.close()
