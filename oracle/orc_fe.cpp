@@ -604,6 +604,13 @@ int side_reinit(int elem_type, const double* X, int side, int qorder, SideData& 
   ShapeTable t;
   shape_table(elem_type, nqf, sd.ref.data(), t);
   sd.phi = t.phi;
+  // ... and its map: reinit(elem, &qp) runs FEMap::compute_map on the PARENT at the mapped points (fe.C:333-338), so what
+  // get_xyz() returns after reinit(elem, side) is sum_i phi_i(qp) x_i over the parent's nodes (fe_map.C:994-1000, :1190-1198) —
+  // the side map's own points above agree with it to rounding only
+  sd.xyz.assign(3 * nqf, 0.);
+  for (int i = 0; i < t.n; ++i)
+    for (int p = 0; p < nqf; ++p)
+      for (int d = 0; d < 3; ++d) sd.xyz[3 * p + d] += t.phi[i * nqf + p] * X[3 * i + d];
   return nqf;
 }
 

@@ -110,8 +110,14 @@ def app():
         L.ref_ex4_run.argtypes = [C.c_int, C.POINTER(C.c_char_p), C.c_char_p, C.c_int]
         L.ref_ex4_assemble.restype = C.c_int
         L.ref_ex4_assemble.argtypes = [C.c_int, C.c_uint, C.c_char_p, C.c_int]
+        L.ref_ex6_assemble.restype = C.c_int
+        L.ref_ex6_assemble.argtypes = [C.c_int, C.c_uint, C.c_char_p, C.c_int]
+        L.ref_world_set_sides.restype = C.c_int
+        L.ref_world_set_sides.argtypes = [C.c_int, C.c_void_p]
         L.ref_world_results.restype = C.c_int64
         L.ref_world_results.argtypes = [C.c_void_p] * 4
+        L.ref_side_reinit.restype = C.c_int
+        L.ref_side_reinit.argtypes = [C.c_int, C.c_int, C.c_void_p, C.c_int, C.c_int, C.c_int, C.c_int, C.c_int] + [C.c_void_p] * 5 + [C.c_char_p, C.c_int]
         L.ref_constrain_element.restype = C.c_int
         L.ref_constrain_element.argtypes = [C.c_int, C.c_void_p, C.c_void_p, C.c_void_p, C.c_int, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p,
                                             C.c_int, C.c_int, C.c_int, C.c_void_p, C.c_void_p, C.c_void_p, C.c_char_p, C.c_int]
@@ -161,6 +167,30 @@ def assemble_ex4(order, nnz, n_dofs, boundary_ids=(0, 1, 2, 3, 4, 5)):
     return _results(nnz, n_dofs)
 
 
+def load_sides(mesh):
+    """BoundaryInfo's side ids of a build_cube mesh (oracle Mesh.boundary_sides) for the loaded world: what
+    Elem::neighbor_ptr(side) == nullptr and BoundaryInfo::has_boundary_id answer from."""
+    ns = {8: 6, 20: 6, 27: 6, 10: 4, 18: 5}[mesh.elem_type]
+    bid = np.full((mesh.n_elem, ns), -1, dtype=np.int16)
+    for b in range(6):
+        e, sd = mesh.boundary_sides(b)
+        bid[e, sd] = b
+    app().ref_world_set_sides(ns, bid.ctypes.data)
+
+
+def assemble_ex6(order, nnz, n_dofs, dirichlet_ids=(4,)):
+    """LinearElasticity::assemble() of systems_of_equations_ex6.C on the loaded mesh, set up as its main() does (three LAGRANGE
+    variables of `order`, ZeroFunction DirichletBoundary on `dirichlet_ids`; traction on the sides with BOUNDARY_ID_MAX_X as the
+    example has it)."""
+    mask = 0
+    for b in dirichlet_ids:
+        mask |= 1 << b
+    err = C.create_string_buffer(1024)
+    if app().ref_ex6_assemble(int(order), mask, err, 1024) != 0:
+        raise RuntimeError(err.value.decode())
+    return _results(nnz, n_dofs)
+
+
 def run_ex4(args, nnz, n_dofs):
     """main() of examples/introduction/introduction_ex4/introduction_ex4.C with the command line `args` ("-d 3 -n 4 ...") over the
     loaded world: dict(values, rhs, con_dof, con_val) as the run left them (system.solve() assembles; the linear solve is not on
@@ -202,3 +232,19 @@ def constrain_element(K, F, dofs, rows, values=None, heterogeneous=True, asymmet
     if m < 0:
         raise RuntimeError(err.value.decode())
     return Ko[: m * m].reshape(m, m).copy(), Fo[:m].copy(), do[:m].copy()
+
+
+def side_reinit(elem: str, node_xyz, side: int, qorder: int, affine: bool):
+    """FE::reinit(elem, side) with the reference's own pieces — QGauss(2), FEMap::init_face_shape_functions / compute_face_map
+    (cut out of src/fe/fe_boundary.C), FEAbstract::get_refspace_nodes, the side_nodes_map tables of src/geom/cell_*.C, the 3D shape
+    functions and FEMap at the mapped points — in the call order of fe_boundary.C:109-238: dict(ref, xyz, JxW, normals, phi)."""
+    n = N_NODES[elem]
+    X = np.ascontiguousarray(node_xyz, dtype=np.float64).reshape(n, 3)
+    cap = 64
+    ref, xyz, JxW, nrm, phi = np.zeros((cap, 3)), np.zeros((cap, 3)), np.zeros(cap), np.zeros((cap, 3)), np.zeros(n * cap)
+    err = C.create_string_buffer(1024)
+    nqf = app().ref_side_reinit(ELEM[elem], n, X.ctypes.data, int(bool(affine)), int(side), FE_ORDER[elem], int(qorder), cap, ref.ctypes.data, xyz.ctypes.data,
+                                JxW.ctypes.data, nrm.ctypes.data, phi.ctypes.data, err, 1024)
+    if nqf < 0:
+        raise RuntimeError(err.value.decode())
+    return dict(ref=ref[:nqf], xyz=xyz[:nqf], JxW=JxW[:nqf], normals=nrm[:nqf], phi=phi[: n * nqf].reshape(n, nqf))

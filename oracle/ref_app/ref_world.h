@@ -54,6 +54,19 @@ static const Number zero = 0.;
 
 class EquationSystems;
 class MeshBase;
+// include/numerics/vector_value.h, tensor_value.h over this tree's three-component Point / RealTensor
+template <typename T> class VectorValue : public Point {
+public:
+  using Point::Point;
+  VectorValue(const Point& p) : Point(p) {}
+};
+template <typename T> class TensorValue : public RealTensor {
+public:
+  using RealTensor::RealTensor;
+};
+namespace Utility {
+template <int N, typename T> inline T pow(const T& x) { T r = 1; for (int i = 0; i < N; ++i) r *= x; return r; }  // include/utils/utility.h
+}
 
 // ---- what the test loads before the example runs (ref_app_shim.cpp: ref_world_load) -------------------------------------------------
 struct RefWorldData {
@@ -65,6 +78,8 @@ struct RefWorldData {
   std::vector<uint32_t> conn;            // [n_elem][npe]
   std::vector<uint8_t> affine;           // [n_elem]  Elem::has_affine_map() (the element classes cannot be compiled here)
   std::vector<uint8_t> node_bmask;       // [n_nodes] bit b: the node lies on a side with boundary id b
+  int n_sides = 0;
+  std::vector<int16_t> side_bid;         // [n_elem][n_sides] BoundaryInfo's id of a boundary side, -1 for an interior side (empty: none loaded)
   // dof numbering: dof of (variable, node), variable-major as DofMap::dof_indices returns them
   int n_vars = 0;
   uint64_t n_dofs = 0;
@@ -102,11 +117,23 @@ inline T command_line_next(const std::string& name, T dflt) {
 }
 
 // ---- include/mesh/*.h ------------------------------------------------------------------------------------------------------------------
+class BoundaryInfo {  // include/mesh/boundary_info.h, as far as an assembly loop asks
+public:
+  bool has_boundary_id(const Elem* const elem, const unsigned short int side, const boundary_id_type id) const { return elem->side_boundary_id(side) == id; }
+  // node and edge ids: set by main() of systems_of_equations_ex6.C, which is compiled but not run here
+  void add_node(const Node*, const boundary_id_type) { libmesh_not_implemented(); }
+  void add_edge(const Elem*, const unsigned short int, const boundary_id_type) { libmesh_not_implemented(); }
+  void regenerate_id_sets() {}
+};
 class MeshBase {
 public:
   virtual ~MeshBase() = default;
   unsigned int mesh_dimension() const { return 3; }
   const std::vector<const Elem*>& active_local_element_ptr_range() const { return _ptrs; }
+  const std::vector<const Elem*>& element_ptr_range() const { return _ptrs; }
+  const BoundaryInfo& get_boundary_info() const { return _boundary_info; }
+  BoundaryInfo& get_boundary_info() { return _boundary_info; }
+  BoundaryInfo _boundary_info;
   void print_info() const {}
   std::vector<Elem> _elems;
   std::vector<const Elem*> _ptrs;
@@ -155,6 +182,11 @@ public:
     for (std::size_t i = 0; i < dof_indices.size(); ++i) ref_world().rhs[dof_indices[i]] += v((unsigned int)i);
   }
   void zero() { std::fill(ref_world().rhs.begin(), ref_world().rhs.end(), 0.); }
+  // named by compute_stresses() of systems_of_equations_ex6.C (post-processing, not on the path): compiled, not run
+  dof_id_type first_local_index() const { return 0; }
+  dof_id_type last_local_index() const { return 0; }
+  void set(const dof_id_type, const T) { libmesh_not_implemented(); }
+  void close() {}
 };
 
 class PerfLog {  // include/utils/perf_log.h: timing only
@@ -269,15 +301,22 @@ public:
   // FE<Dim, T>::reinit(elem), src/fe/fe.C:196-368, in the order of its calls: qrule->init, init_reference_to_physical_map,
   // init_shape_functions (the tables by FE<3, LAGRANGE>::all_shapes / all_shape_derivs), compute_map, map_dphi
   void reinit(const Elem* elem);
+  // FE<Dim, T>::reinit(elem, side), src/fe/fe_boundary.C:109-238, in the order of its calls: build_side_ptr, qrule->init(side),
+  // init_face_shape_functions, compute_face_map, side_map (:347-400), reinit(elem, &qp), JxW of the side put back
+  void reinit(const Elem* elem, const unsigned int side);
+  const std::vector<Point>& get_normals() const { return _fe_map.get_normals(); }
+  const std::vector<Point>& side_reference_points() const { return _side_ref_points; }  // what side_map gave (for the tests)
 private:
+  void init_shape_functions(const std::vector<Point>& qp, const Elem* elem);
   unsigned int dim;
   FEType fe_type;
-  ElemType _elem_type = INVALID_ELEM;
+  ElemType _elem_type = INVALID_ELEM, last_side = INVALID_ELEM;
   QBase* qrule = nullptr;
   FEMap _fe_map;
   std::unique_ptr<H1FETransformation<OutputShape>> _fe_trans;  // fe_base.h: std::unique_ptr<FETransformationBase<OutputType>>
   std::vector<std::vector<OutputShape>> phi, dphidxi, dphideta, dphidzeta, dphidx, dphidy, dphidz;
   std::vector<std::vector<OutputGradient>> dphi;
+  std::vector<Point> _side_ref_points;
 };
 typedef FEGenericBase<Real> FEBase;
 
@@ -304,6 +343,9 @@ public:
   const DofMap& get_dof_map() const { return _dof_map; }
   DofMap& get_dof_map() { return _dof_map; }
   const std::string& name() const { return _name; }
+  Number current_solution(const dof_id_type) const { libmesh_not_implemented(); }  // post-processing only
+  void update() {}
+  NumericVector<Number>* solution = &_solution;
   void attach_assemble_function(void fptr(EquationSystems& es, const std::string& name)) { _assemble_fptr = fptr; }
   void attach_assemble_object(Assembly& a) { _assemble_object = &a; }
   // System::user_assembly, src/systems/system.C
@@ -316,6 +358,7 @@ protected:
   std::string _name;
   std::vector<std::string> _var_names;
   DofMap _dof_map;
+  NumericVector<Number> _solution;
   void (*_assemble_fptr)(EquationSystems&, const std::string&) = nullptr;
   Assembly* _assemble_object = nullptr;
 };

@@ -2,6 +2,7 @@
 // Test infrastructure: see ref_world.h for what in that library is the reference's own code and what is glue.  Nothing under
 // libmesh_b200/ may touch it.
 #include "ref_world.h"
+#include "libmesh/quadrature_gauss.h"
 
 namespace libMesh {
 
@@ -36,6 +37,7 @@ void build_cube(UnstructuredMesh& mesh, const unsigned int nx, const unsigned in
     mesh._elems.back().set_nodes(c.data(), (unsigned int)w.npe);
     mesh._elems.back().force_affine(w.affine[e] != 0);
     mesh._elems.back().set_id((dof_id_type)e);
+    if (!w.side_bid.empty()) mesh._elems.back().set_side_boundary_ids(&w.side_bid[e * w.n_sides], (unsigned int)w.n_sides);
   }
   for (const Elem& e : mesh._elems) mesh._ptrs.push_back(&e);
 }
@@ -84,10 +86,21 @@ template <> FEGenericBase<Real>::FEGenericBase(unsigned int d, const FEType& t) 
   _fe_map.get_xyz(); _fe_map.get_JxW(); _fe_map.get_jacobian();
   _fe_map.get_dxidx(); _fe_map.get_dxidy(); _fe_map.get_dxidz(); _fe_map.get_detadx(); _fe_map.get_detady(); _fe_map.get_detadz();
   _fe_map.get_dzetadx(); _fe_map.get_dzetady(); _fe_map.get_dzetadz();
+  _fe_map.get_normals();
 }
 template <> std::unique_ptr<FEGenericBase<Real>> FEGenericBase<Real>::build(const unsigned int dim, const FEType& type) {
   libmesh_error_msg_if(dim != 3 || type.family != LAGRANGE, "this stub builds FE<3, LAGRANGE> only");
   return std::make_unique<FEGenericBase<Real>>(dim, type);
+}
+// init_shape_functions (fe.C:372-600): phi and its reference derivatives at the given points
+template <> void FEGenericBase<Real>::init_shape_functions(const std::vector<Point>& qp, const Elem* elem) {
+  const unsigned int ns = elem->n_nodes();
+  const std::size_t nq = qp.size();
+  for (auto* t : {&phi, &dphidxi, &dphideta, &dphidzeta, &dphidx, &dphidy, &dphidz}) t->assign(ns, std::vector<Real>(nq, 0.));
+  dphi.assign(ns, std::vector<RealGradient>(nq));
+  FE<3, LAGRANGE>::all_shapes(elem, fe_type.order, qp, phi, true);
+  std::vector<std::vector<Real>>* comps[3] = {&dphidxi, &dphideta, &dphidzeta};
+  FE<3, LAGRANGE>::all_shape_derivs(elem, fe_type.order, qp, comps, true);
 }
 template <> void FEGenericBase<Real>::reinit(const Elem* elem) {
   libmesh_error_msg_if(!qrule, "no quadrature rule attached");
@@ -97,17 +110,41 @@ template <> void FEGenericBase<Real>::reinit(const Elem* elem) {
   if (_elem_type != elem->type()) {                           // fe.C:226-240: tables when the element type changes
     _elem_type = elem->type();
     _fe_map.init_reference_to_physical_map<3>(qp, elem);
-    // init_shape_functions (fe.C:372-600): phi and its reference derivatives at the rule's points
-    const unsigned int ns = elem->n_nodes();
-    const std::size_t nq = qp.size();
-    for (auto* t : {&phi, &dphidxi, &dphideta, &dphidzeta, &dphidx, &dphidy, &dphidz}) t->assign(ns, std::vector<Real>(nq, 0.));
-    dphi.assign(ns, std::vector<RealGradient>(nq));
-    FE<3, LAGRANGE>::all_shapes(elem, fe_type.order, qp, phi, true);
-    std::vector<std::vector<Real>>* comps[3] = {&dphidxi, &dphideta, &dphidzeta};
-    FE<3, LAGRANGE>::all_shape_derivs(elem, fe_type.order, qp, comps, true);
+    init_shape_functions(qp, elem);
   }
-  _fe_map.compute_map(dim, qrule->get_weights(), elem, /*calculate_d2phi=*/false);  // fe.C:330
-  _fe_trans->map_dphi(dim, elem, qp, *this, dphi, dphidx, dphidy, dphidz);           // compute_shape_functions, fe_base.C
+  _fe_map.compute_map(dim, qrule->get_weights(), elem, /*calculate_d2phi=*/false);  // fe.C:340
+  _fe_trans->map_dphi(dim, elem, qp, *this, dphi, dphidx, dphidy, dphidz);          // compute_shape_functions, fe_base.C
+}
+template <> void FEGenericBase<Real>::reinit(const Elem* elem, const unsigned int s) {
+  libmesh_error_msg_if(!qrule, "no quadrature rule attached");
+  const std::unique_ptr<const Elem> side(elem->build_side_ptr(s));                  // fe_boundary.C:137
+  qrule->init(*side, elem->p_level());                                              // :172
+  if (_elem_type != elem->type() || side->type() != last_side) {                    // :176-190
+    _elem_type = elem->type();
+    last_side = side->type();
+    _fe_map.init_face_shape_functions<3>(qrule->get_points(), side.get());
+  }
+  _fe_map.compute_face_map(3, qrule->get_weights(), side.get());                    // :204
+  const std::vector<Real> JxW_int(_fe_map.get_JxW());                               // :211
+  // side_map, :347-400: the side's points in the parent's reference space
+  const std::vector<Point>& reference_side_points = qrule->get_points();
+  std::vector<Point> qp(reference_side_points.size());
+  for (Point& p : qp) p.zero();
+  std::vector<Point> refspace_nodes;
+  FEAbstract::get_refspace_nodes(elem->type(), refspace_nodes);
+  const std::vector<std::vector<Real>>& psi_map = _fe_map.get_psi();
+  for (std::size_t i = 0; i < psi_map.size(); ++i) {
+    const Point& side_node = refspace_nodes[elem->local_side_node(s, (unsigned int)i)];
+    for (std::size_t p = 0; p < qp.size(); ++p) qp[p].add_scaled(side_node, psi_map[i][p]);
+  }
+  _side_ref_points = qp;
+  // reinit(elem, &qp), fe.C:206-216 and :333-338 (no weights: 1)
+  _fe_map.init_reference_to_physical_map<3>(qp, elem);
+  init_shape_functions(qp, elem);
+  std::vector<Real> dummy_weights(qp.size(), 1.);
+  _fe_map.compute_map(dim, dummy_weights, elem, /*calculate_d2phi=*/false);
+  _fe_trans->map_dphi(dim, elem, qp, *this, dphi, dphidx, dphidy, dphidz);
+  _fe_map.get_JxW() = JxW_int;                                                      // :237
 }
 
 // ---- EquationSystems ------------------------------------------------------------------------------------------------------------------
@@ -170,6 +207,15 @@ int ref_world_load(int elem_type, int npe, unsigned int nx, unsigned int ny, uns
   return 0;
 }
 
+// BoundaryInfo's ids of the boundary sides: bid[n_elem][n_sides], -1 on interior sides (what Elem::neighbor_ptr(side) == nullptr and
+// BoundaryInfo::has_boundary_id(elem, side, id) answer from)
+int ref_world_set_sides(int n_sides, const int16_t* bid) {
+  RefWorldData& w = ref_world();
+  w.n_sides = n_sides;
+  w.side_bid.assign(bid, bid + w.n_elem() * (uint64_t)n_sides);
+  return 0;
+}
+
 // main() of introduction_ex4.C with the given command line ("-d 3 -n 4 ..."); returns its return value, or -1 with the message
 int ref_ex4_run(int argc, const char* const* argv, char* err, int err_len) {
   try {
@@ -214,6 +260,33 @@ int64_t ref_world_results(double* values, double* rhs, uint32_t* con_dof, double
   if (con_dof) std::memcpy(con_dof, w.con_dof.data(), sizeof(uint32_t) * w.con_dof.size());
   if (con_val) std::memcpy(con_val, w.con_val.data(), sizeof(double) * w.con_val.size());
   return (int64_t)w.con_dof.size();
+}
+
+// FE::reinit(elem, side) on one element given by its node coordinates, with QGauss(2, qorder) on the side: the number of side points
+// nqf (<= cap), ref[nqf][3] (the points in the parent's reference space), xyz[nqf][3], JxW[nqf], normals[nqf][3], phi[n][nqf].
+int ref_side_reinit(int elem_type, int n_nodes, const double* node_xyz, int affine, int side, int fe_order, int qorder, int cap, double* ref, double* xyz,
+                    double* JxW, double* normals, double* phi, char* err, int err_len) {
+  try {
+    Elem elem(static_cast<ElemType>(elem_type), 0);
+    elem.set_nodes(node_xyz, (unsigned int)n_nodes);
+    elem.force_affine(affine != 0);
+    std::unique_ptr<FEBase> fe_face(FEBase::build(3, FEType(fe_order, LAGRANGE)));
+    QGauss qface(2, static_cast<Order>(qorder));
+    fe_face->attach_quadrature_rule(&qface);
+    fe_face->reinit(&elem, (unsigned int)side);
+    const int nqf = (int)qface.n_points();
+    libmesh_error_msg_if(nqf > cap, nqf << " side points, room for " << cap);
+    for (int p = 0; p < nqf; ++p) {
+      JxW[p] = fe_face->get_JxW()[p];
+      for (int d = 0; d < 3; ++d) {
+        ref[3 * p + d] = fe_face->side_reference_points()[p](d);
+        xyz[3 * p + d] = fe_face->get_xyz()[p](d);
+        normals[3 * p + d] = fe_face->get_normals()[p](d);
+      }
+      for (int i = 0; i < n_nodes; ++i) phi[(std::size_t)i * nqf + p] = fe_face->get_phi()[i][p];
+    }
+    return nqf;
+  } catch (const std::exception& e) { return fail(e, err, err_len); }
 }
 
 // DofMap::constrain_element_matrix_and_vector (hetero = 0) / heterogeneously_constrain_element_matrix_and_vector (hetero = 1) of the

@@ -1,26 +1,43 @@
-"""Build step of oracle/_ref/libref_app.so (oracle/Makefile): writes, into a build intermediate that the Makefile deletes after
-the compile, the DEFINITIONS of a few member functions of the reference, each cut from the file where it lies — from the first
-line of the definition to its closing brace at column 0 — so that they can be compiled against the stub class declarations of
-oracle/ref_app/ref_world.h.  (The files as a whole — src/base/dof_map_constraints.C, 5 000 lines over the whole DofMap, and
-src/fe/h1_fe_transformation.C with its vector-valued instantiations — cannot be compiled stand-alone.)  Nothing is committed:
-the output goes under oracle/_ref/, which is git-ignored."""
+"""Build step of oracle/_ref/*.so (oracle/Makefile): writes, into a build intermediate that the Makefile deletes after the
+compile, the DEFINITIONS of a few functions and tables of the reference, each cut from the file where it lies — from the first
+line of the definition to its closing line — so that they can be compiled against the stub class declarations of
+oracle/ref_stubs/ and oracle/ref_app/.  (The files as a whole — src/base/dof_map_constraints.C, 5 000 lines over the whole
+DofMap; src/fe/fe_boundary.C and h1_fe_transformation.C with their instantiations for every family; the element classes of
+src/geom/ — cannot be compiled stand-alone.)  Nothing is committed: the output goes under oracle/_ref/, which is git-ignored.
+
+    python3 ref_excerpt.py <reference root> <set: fe | app> <output file>
+"""
 import re
 import sys
 
-ref, out = sys.argv[1], sys.argv[2]
-WANT = [
-    ("src/base/dof_map_constraints.C", r"^void DofMap::build_constraint_matrix \(", ""),
-    ("src/base/dof_map_constraints.C", r"^void DofMap::build_constraint_matrix_and_vector \(", ""),
-    ("src/base/dof_map_constraints.C", r"^void DofMap::constrain_element_matrix_and_vector \(", ""),
-    ("src/base/dof_map_constraints.C", r"^void DofMap::heterogeneously_constrain_element_matrix_and_vector \(", ""),
-    ("src/fe/h1_fe_transformation.C", r"^void H1FETransformation<OutputShape>::map_dphi\(", "template<typename OutputShape>\n"),
-]
+ref, which, out = sys.argv[1], sys.argv[2], sys.argv[3]
+FUNC_END, TABLE_END = r"^}$", r"^  };$"
+SETS = {
+    # (file, first line of the definition, last line, text put in front)
+    "fe": [
+        ("src/fe/fe_boundary.C", r"^void FEMap::init_face_shape_functions\(", FUNC_END, "template<unsigned int Dim>\n"),
+        ("src/fe/fe_boundary.C", r"^void FEMap::compute_face_map\(", FUNC_END, ""),
+        ("src/fe/fe_abstract.C", r"^void FEAbstract::get_refspace_nodes\(", FUNC_END, ""),
+        ("src/geom/cell_hex8.C", r"^const unsigned int Hex8::side_nodes_map\[", TABLE_END, ""),
+        ("src/geom/cell_hex20.C", r"^const unsigned int Hex20::side_nodes_map\[", TABLE_END, ""),
+        ("src/geom/cell_hex27.C", r"^const unsigned int Hex27::side_nodes_map\[", TABLE_END, ""),
+        ("src/geom/cell_tet10.C", r"^const unsigned int Tet10::side_nodes_map\[", TABLE_END, ""),
+        ("src/geom/cell_prism18.C", r"^const unsigned int Prism18::side_nodes_map\[", TABLE_END, ""),
+    ],
+    "app": [
+        ("src/base/dof_map_constraints.C", r"^void DofMap::build_constraint_matrix \(", FUNC_END, ""),
+        ("src/base/dof_map_constraints.C", r"^void DofMap::build_constraint_matrix_and_vector \(", FUNC_END, ""),
+        ("src/base/dof_map_constraints.C", r"^void DofMap::constrain_element_matrix_and_vector \(", FUNC_END, ""),
+        ("src/base/dof_map_constraints.C", r"^void DofMap::heterogeneously_constrain_element_matrix_and_vector \(", FUNC_END, ""),
+        ("src/fe/h1_fe_transformation.C", r"^void H1FETransformation<OutputShape>::map_dphi\(", FUNC_END, "template<typename OutputShape>\n"),
+    ],
+}
 with open(out, "w") as o:
-    for path, start, prefix in WANT:
+    for path, start, stop, prefix in SETS[which]:
         lines = open(f"{ref}/{path}").read().split("\n")
         hits = [i for i, l in enumerate(lines) if re.match(start, l)]
         if len(hits) != 1:
             sys.exit(f"ref_excerpt: {len(hits)} definitions match {start!r} in {path}")
-        end = next(i for i in range(hits[0], len(lines)) if lines[i] == "}")
+        end = next(i for i in range(hits[0], len(lines)) if re.match(stop, lines[i]))
         o.write(f"// ---- {path}:{hits[0] + 1}-{end + 1}\n{prefix}")
         o.write("\n".join(lines[hits[0]:end + 1]) + "\n\n")

@@ -5,6 +5,8 @@
 // enum_order.h).
 #include "libmesh/fe.h"
 #include "libmesh/fe_map.h"
+#include "libmesh/fe_interface.h"
+#include "libmesh/enum_to_string.h"
 #include "libmesh/quadrature_gauss.h"
 
 using namespace libMesh;
@@ -12,11 +14,15 @@ using namespace libMesh;
 // QBase::clone() names the rule factory (src/quadrature/quadrature_build.C, which would pull in every rule class of the
 // library); nothing here clones a rule.
 std::unique_ptr<QBase> QBase::build(const QuadratureType, const unsigned int, const Order) { libmesh_not_implemented(); }
-// FEMap's side / edge maps live in src/fe/fe_boundary.C together with explicit instantiations of FE<Dim, T>::reinit(elem, side)
-// for every family of the library — not compilable stand-alone.  FEMap's vtable names them; nothing here calls them (the
-// oracle's side code stays pinned by the known answers of tests/test_oracle_sides.py and by the reference's 2D rules and
-// shape functions, which ARE compiled here).
-void FEMap::compute_face_map(int, const std::vector<Real>&, const Elem*) { libmesh_not_implemented(); }
+// FEMap's side maps live in src/fe/fe_boundary.C together with explicit instantiations of FE<Dim, T>::reinit(elem, side) for
+// every family of the library — not compilable as a whole.  The DEFINITIONS of FEMap::init_face_shape_functions<Dim> and
+// FEMap::compute_face_map are cut out of it at build time (oracle/ref_excerpt.py, set "fe"), together with
+// FEAbstract::get_refspace_nodes (src/fe/fe_abstract.C) and the side_nodes_map tables of the element classes (src/geom/cell_*.C),
+// and compiled here against the stub declarations of ref_stubs/.  Edge maps are not on the path.
+namespace libMesh {
+#include "ref_fe_excerpts.inc"
+template void FEMap::init_face_shape_functions<3>(const std::vector<Point>&, const Elem*);
+}  // namespace libMesh
 void FEMap::compute_edge_map(int, const std::vector<Real>&, const Elem*) { libmesh_not_implemented(); }
 
 // examples/introduction/introduction_ex3/exact_solution.C (the manufactured solution of ex3 / ex4), compiled where it lies

@@ -8,8 +8,28 @@
 #include "libmesh/enum_order.h"
 #include "libmesh/point.h"
 namespace libMesh {
+// DECLARATIONS of the side-node tables of the element classes (include/geom/cell_hex8.h ...: num_sides, nodes_per_side,
+// side_nodes_map).  The table DEFINITIONS are the reference's own, cut out of src/geom/cell_*.C at build time
+// (oracle/ref_excerpt.py, set "fe") and compiled in ref_shim.cpp.
+struct Hex8 { static const int num_sides = 6, nodes_per_side = 4; static const unsigned int side_nodes_map[num_sides][nodes_per_side]; };
+struct Hex20 { static const int num_sides = 6, nodes_per_side = 8; static const unsigned int side_nodes_map[num_sides][nodes_per_side]; };
+struct Hex27 { static const int num_sides = 6, nodes_per_side = 9; static const unsigned int side_nodes_map[num_sides][nodes_per_side]; };
+struct Tet10 { static const int num_sides = 4, nodes_per_side = 6; static const unsigned int side_nodes_map[num_sides][nodes_per_side]; };
+struct Prism18 { static const int num_sides = 5, nodes_per_side = 9; static const unsigned int side_nodes_map[num_sides][nodes_per_side]; };
+
 class Elem {
 public:
+  // Elem::type_to_n_nodes_map (src/geom/elem.C), for the types this shim is asked for
+  struct NNodesMap {
+    unsigned int operator[](ElemType t) const {
+      switch (t) {
+        case EDGE2: return 2; case EDGE3: return 3; case TRI3: return 3; case TRI6: return 6; case QUAD4: return 4; case QUAD8: return 8; case QUAD9: return 9;
+        case TET4: return 4; case TET10: return 10; case HEX8: return 8; case HEX20: return 20; case HEX27: return 27; case PRISM6: return 6; case PRISM18: return 18;
+        default: return invalid_uint;
+      }
+    }
+  };
+  static constexpr NNodesMap type_to_n_nodes_map{};
   explicit Elem(ElemType t = INVALID_ELEM, unsigned int p = 0) : _t(t), _p(p) {}
   virtual ~Elem() = default;
   ElemType type() const { return _t; }
@@ -37,6 +57,46 @@ public:
   bool on_reference_element(const Point&, Real = 0.) const { return true; }
   Real hmax() const { return 1.; }
   Point master_point(unsigned int) const { return Point(); }  // only inverse_map (never called here) asks
+  // sides: Elem::n_sides / local_side_node / side_type / build_side_ptr over the side_nodes_map tables above
+  unsigned int n_sides() const { return (_t == HEX8 || _t == HEX20 || _t == HEX27) ? 6u : (_t == TET10 ? 4u : (_t == PRISM18 ? 5u : 0u)); }
+  IntRange<unsigned short> side_index_range() const { return IntRange<unsigned short>(0, (unsigned short)n_sides()); }
+  ElemType side_type(unsigned int s) const {
+    switch (_t) {
+      case HEX8: return QUAD4; case HEX20: return QUAD8; case HEX27: return QUAD9; case TET10: return TRI6;
+      case PRISM18: return (s == 0 || s == 4) ? TRI6 : QUAD9;
+      default: return INVALID_ELEM;
+    }
+  }
+  unsigned int local_side_node(unsigned int s, unsigned int i) const {
+    switch (_t) {
+      case HEX8: return Hex8::side_nodes_map[s][i]; case HEX20: return Hex20::side_nodes_map[s][i]; case HEX27: return Hex27::side_nodes_map[s][i];
+      case TET10: return Tet10::side_nodes_map[s][i]; case PRISM18: return Prism18::side_nodes_map[s][i];
+      default: return invalid_uint;
+    }
+  }
+  std::unique_ptr<Elem> build_side_ptr(unsigned int s) const {
+    const ElemType st = side_type(s);
+    auto side = std::make_unique<Elem>(st, _p);
+    const unsigned int n = type_to_n_nodes_map[st];
+    std::vector<double> c(3 * (std::size_t)n);
+    for (unsigned int i = 0; i < n; ++i) for (int d = 0; d < 3; ++d) c[3 * i + d] = _nodes[local_side_node(s, i)](d);
+    side->set_nodes(c.data(), n);
+    return side;
+  }
+  bool is_node_on_side(unsigned int n, unsigned int s) const {
+    const unsigned int ns = type_to_n_nodes_map[side_type(s)];
+    for (unsigned int i = 0; i < ns; ++i) if (local_side_node(s, i) == n) return true;
+    return false;
+  }
+  // edges: named by main() of systems_of_equations_ex6.C only (node / edge boundary ids), which is compiled but not run
+  IntRange<unsigned short> edge_index_range() const { return IntRange<unsigned short>(0, 0); }
+  bool is_edge_on_side(unsigned int, unsigned int) const { libmesh_not_implemented(); }
+  // neighbours and boundary ids, as far as an assembly loop asks: is the side on the boundary, and with which id
+  void set_side_boundary_ids(const short* ids, unsigned int n) { _side_bid.assign(ids, ids + n); }
+  short side_boundary_id(unsigned int s) const { return s < _side_bid.size() ? _side_bid[s] : (short)-1; }
+  const Elem* interior_parent() const { return nullptr; }                  // the 1D / 2D branches of compute_face_map ask (never run here)
+  dof_id_type node_id(unsigned int i) const { return _nodes[i].id(); }
+  const Elem* neighbor_ptr(unsigned int s) const { return side_boundary_id(s) >= 0 ? nullptr : this; }  // non-null = "has a neighbour"
   void print_info(std::ostream& os) const { os << get_info(); }
   std::string get_info() const { return "Elem (stub) type " + std::to_string((int)_t); }
 private:
@@ -44,6 +104,7 @@ private:
   unsigned int _p;
   bool _affine = false;
   dof_id_type _id = 0;
+  std::vector<short> _side_bid;
   std::vector<Node> _nodes;
 };
 }  // namespace libMesh

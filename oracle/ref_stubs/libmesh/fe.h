@@ -13,6 +13,13 @@ namespace libMesh {
 template <typename F> inline Real fe_fdm_deriv(const ElemType, const Order, const Elem*, const unsigned int, const unsigned int, const Point&, F) { libmesh_not_implemented(); }
 template <typename F> inline Real fe_fdm_second_deriv(const ElemType, const Order, const Elem*, const unsigned int, const unsigned int, const Point&, F) { libmesh_not_implemented(); }
 
+// include/fe/fe_abstract.h: DECLARATION only; the definition (the reference-element node coordinates of every element type) is
+// the reference's own, cut out of src/fe/fe_abstract.C at build time
+class FEAbstract {
+public:
+  static void get_refspace_nodes(const ElemType t, std::vector<Point>& nodes);
+};
+
 template <unsigned int Dim, FEFamily T>
 class FE {
 public:

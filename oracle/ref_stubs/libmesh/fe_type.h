@@ -18,6 +18,8 @@ public:
   FEType(int o = 1, FEFamily f = LAGRANGE) : order(o), family(f) {}
   OrderWrapper order;
   FEFamily family;
+  // include/fe/fe_type.h:414-418
+  Order default_quadrature_order() const { return static_cast<Order>(2 * static_cast<unsigned int>(order.get_order()) + 1); }
 };
 }  // namespace libMesh
 #endif

@@ -22,6 +22,7 @@ public:
   Real norm_sq() const { return c[0] * c[0] + c[1] * c[1] + c[2] * c[2]; }
   bool operator==(const Point& o) const { return c[0] == o.c[0] && c[1] == o.c[1] && c[2] == o.c[2]; }
   Point cross(const Point& o) const { return Point(c[1] * o.c[2] - c[2] * o.c[1], c[2] * o.c[0] - c[0] * o.c[2], c[0] * o.c[1] - c[1] * o.c[0]); }
+  Point unit() const { const Real l = norm(); return Point(c[0] / l, c[1] / l, c[2] / l); }       // TypeVector::unit (type_vector.h)
   Real norm() const { return std::sqrt(c[0] * c[0] + c[1] * c[1] + c[2] * c[2]); }
   Point& operator+=(const Point& o) { c[0] += o.c[0]; c[1] += o.c[1]; c[2] += o.c[2]; return *this; }
   Point& operator*=(Real s) { c[0] *= s; c[1] *= s; c[2] *= s; return *this; }

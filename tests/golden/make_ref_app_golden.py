@@ -1,8 +1,10 @@
-"""Writes tests/golden/reference_ex4_runs.npz: the global matrix, right-hand side and Dirichlet constraints that the REFERENCE's
+"""Writes tests/golden/reference_ex4_runs.npz and reference_ex6_runs.npz: the global matrix, right-hand side and Dirichlet constraints that the REFERENCE's
 own examples/introduction/introduction_ex4/introduction_ex4.C produces — its main() ("-d 3 -n N [-o FIRST]") or, for the meshes
 main() does not ask build_cube for, its assemble_poisson set up as main() does — compiled where it lies under /root/reference
 into oracle/_ref/libref_app.so (oracle/Makefile; oracle/ref_app/ref_world.h says what in that library is the reference's code
-and what is glue).  Run here, where /root/reference exists; the .npz travels to the GPU box, where tests/test_golden_ref_app.py
+and what is glue); for reference_ex6_runs.npz the same of LinearElasticity::assemble() of
+examples/systems_of_equations/systems_of_equations_ex6/systems_of_equations_ex6.C (three variables, traction on the max-x sides,
+homogeneous Dirichlet on the min-x side: BASELINE's config 5 in small).  Run here, where /root/reference exists; the .npz travels to the GPU box, where tests/test_golden_ref_app.py
 and tests/test_gpu_golden_ref.py compare the oracle and the CUDA path with it.
 
     python tests/golden/make_ref_app_golden.py
@@ -50,6 +52,48 @@ def reference_run(m, s, n, order, through_main):
     return R.assemble_ex4(order, nnz, nd)
 
 
+EX6_BOUNDS = (0.0, 1.0, 0.0, 0.3, 0.0, 0.1)
+# name, oracle element type, (nx, ny, nz), skew or None, FE order
+CASES6 = [
+    ("hex27_ex6", O.HEX27, (2, 2, 2), None, 2),
+    ("hex27_ex6_perturbed", O.HEX27, (2, 2, 2), (1, 0.004, 7), 2),
+    ("hex8_ex6", O.HEX8, (5, 3, 2), None, 1),
+    ("hex8_ex6_perturbed", O.HEX8, (4, 3, 3), (1, 0.004, 11), 1),
+]
+
+
+def oracle_case6(etype, dims, skew):
+    m = O.Mesh(etype, *dims, EX6_BOUNDS)
+    if skew is not None:
+        m.skew(*skew)
+    s = O.System(m, 3)
+    s.add_dirichlet((4,), 1)                      # BOUNDARY_ID_MIN_X, ZeroFunction
+    e, sd = m.boundary_sides(2)                   # BOUNDARY_ID_MAX_X
+    s.set_side_loads(e, sd, (0.0, 0.0, -1.0))     # g_vec of systems_of_equations_ex6.C:240
+    s.build_sparsity()
+    return m, s
+
+
+def reference_run6(m, s, dims, order):
+    nnz, nd = R.load_world(m, s, dims, EX6_BOUNDS)
+    R.load_sides(m)
+    return R.assemble_ex6(order, nnz, nd, (4,))
+
+
+def main6():
+    out = {"names": np.array([c[0] for c in CASES6])}
+    for name, etype, dims, skew, order in CASES6:
+        m, s = oracle_case6(etype, dims, skew)
+        r = reference_run6(m, s, dims, order)
+        out[name + "/spec"] = np.array([etype, *dims, order] + list(skew or (-1, 0.0, 0)), dtype=np.float64)
+        for k in ("values", "rhs", "con_dof", "con_val"):
+            out[name + "/" + k] = r[k]
+        print(f"{name}: {len(r['values'])} entries, {len(r['rhs'])} dofs, {len(r['con_dof'])} constrained")
+    path = os.path.join(ROOT, "tests", "golden", "reference_ex6_runs.npz")
+    np.savez_compressed(path, **out)
+    print(path, os.path.getsize(path), "bytes")
+
+
 def main():
     out = {"names": np.array([c[0] for c in CASES])}
     for name, etype, n, skew, order, through_main in CASES:
@@ -66,3 +110,4 @@ def main():
 
 if __name__ == "__main__":
     main()
+    main6()

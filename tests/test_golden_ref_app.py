@@ -1,7 +1,9 @@
 """The oracle against outputs of the reference itself: tests/golden/reference_ex4_runs.npz holds the global matrix, right-hand
 side and Dirichlet constraints that the reference's own introduction_ex4.C (main() or assemble_poisson, compiled where it lies —
 tests/golden/make_ref_app_golden.py, oracle/ref_app/ref_world.h) produced on ten small meshes: every element family of the
-product, affine and skewed.  The oracle reproduces them bit for bit.  Needs neither /root/reference nor a GPU."""
+product, affine and skewed; tests/golden/reference_ex6_runs.npz the same of LinearElasticity::assemble() of its
+systems_of_equations_ex6.C (three variables, traction on the max-x sides) on four.  The oracle reproduces them bit for bit.
+Needs neither /root/reference nor a GPU."""
 import os
 
 import numpy as np
@@ -32,3 +34,30 @@ def test_oracle_reproduces_the_references_own_output(name):
     assert np.array_equal(cd, G[name + "/con_dof"]) and np.array_equal(cv, G[name + "/con_val"])
     assert np.array_equal(v, G[name + "/values"])
     assert np.array_equal(r, G[name + "/rhs"])
+
+
+G6 = np.load(os.path.join(os.path.dirname(os.path.abspath(__file__)), "golden", "reference_ex6_runs.npz"))
+EX6_BOUNDS = (0.0, 1.0, 0.0, 0.3, 0.0, 0.1)
+
+
+def golden_case6(name):
+    etype, nx, ny, nz, order, kind, amp, seed = G6[name + "/spec"]
+    m = O.Mesh(int(etype), int(nx), int(ny), int(nz), EX6_BOUNDS)
+    if kind >= 0:
+        m.skew(int(kind), float(amp), int(seed))
+    s = O.System(m, 3)
+    s.add_dirichlet((4,), 1)
+    e, sd = m.boundary_sides(2)
+    s.set_side_loads(e, sd, (0.0, 0.0, -1.0))
+    s.build_sparsity()
+    return m, s, e, sd
+
+
+@pytest.mark.parametrize("name", [str(n) for n in G6["names"]])
+def test_oracle_reproduces_the_references_own_elasticity_output(name):
+    m, s, _, _ = golden_case6(name)
+    v, r, _ = s.assemble(O.ELASTICITY_EX6)
+    cd, cv = s.constraints()
+    assert np.array_equal(cd, G6[name + "/con_dof"]) and np.array_equal(cv, G6[name + "/con_val"])
+    assert np.array_equal(v, G6[name + "/values"])
+    assert np.array_equal(r, G6[name + "/rhs"])

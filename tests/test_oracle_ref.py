@@ -268,24 +268,31 @@ T10_SIDE = [[0, 2, 1, 6, 5, 4], [0, 1, 3, 4, 8, 7], [1, 2, 3, 5, 9, 8], [2, 0, 3
 @needs_ref
 @pytest.mark.parametrize("elem,side_elem,ns,order,amp", [("HEX27", "QUAD9", 9, 5, 0.03), ("HEX20", "QUAD8", 8, 5, 0.03), ("HEX8", "QUAD4", 4, 3, 0.04),
                                                          ("HEX8", "QUAD4", 4, 5, 0.04), ("TET10", "TRI6", 6, 5, 0.008)])
-def test_side_maps_are_the_reference_surface_map_bit_for_bit(elem, side_elem, ns, order, amp):
-    """FE::reinit(elem, side): side points and JxW_face = sqrt(g11 g22 - g12 g21) w.  FEMap::compute_face_map itself sits in
-    fe_boundary.C (not compilable stand-alone); its arithmetic is the 2D-element-in-space branch of
-    FEMap::compute_single_point_map (fe_map.C:730-860: the same sums over the side's nodes, the same first fundamental form),
-    which IS compiled: fed with the side's nodes (Hex27 / Hex20 / Hex8 / Tet10 side_nodes_map) and the reference's 2D rule it
-    gives the oracle's side points and weights bit for bit, on perturbed (curved-side) elements."""
+def test_side_reinit_is_the_references_own_face_machinery_bit_for_bit(elem, side_elem, ns, order, amp):
+    """FE::reinit(elem, side).  FEMap::init_face_shape_functions and FEMap::compute_face_map (cut out of src/fe/fe_boundary.C),
+    FEAbstract::get_refspace_nodes (fe_abstract.C), the side_nodes_map tables of src/geom/cell_*.C, the reference's 2D rule, its
+    QUAD4 / QUAD8 / QUAD9 / TRI6 and 3D shape functions and FEMap::compute_map at the mapped points, called in the order of
+    fe_boundary.C:109-238: the oracle's side points in the parent's reference space, physical points, JxW_face, normals and
+    phi_face are those bits — on straight and on perturbed (curved-side) elements.  (The surface Jacobian of the
+    2D-element-in-space branch of compute_single_point_map, fe_map.C:730-860, is the same number as well.)"""
+    if not R.app_available():
+        pytest.skip("oracle/_ref/libref_app.so not built")
     orc = ORC[elem]
-    m = O.Mesh(orc, 2, 2, 1, bounds=(-1, 1, -1, 1, 0, 1))
-    m.skew(1, amp, 5)
-    xyz, conn, _ = m.arrays()
     pts, w = R.gauss_rule(side_elem, order)
-    for e in range(0, m.n_elem, max(1, m.n_elem // 5)):
-        X = xyz[conn[e]]
-        for side in range(4 if elem == "TET10" else 6):
-            nodes = (T10_SIDE if elem == "TET10" else H27_SIDE)[side][:ns]
-            d = O.side_reinit(orc, X, side, order)
-            r = R.fe_map(side_elem, X[nodes], pts, w, False)
-            assert np.array_equal(d["xyz"], r["xyz"]) and np.array_equal(d["JxW"], r["JxW"])
+    for amplitude in (0.0, amp):
+        m = O.Mesh(orc, 2, 2, 1, bounds=(-1, 1, -1, 1, 0, 1))
+        if amplitude:
+            m.skew(1, amplitude, 5)
+        xyz, conn, _ = m.arrays()
+        for e in range(0, m.n_elem, max(1, m.n_elem // 5)):
+            X = xyz[conn[e]]
+            for side in range(4 if elem == "TET10" else 6):
+                d = O.side_reinit(orc, X, side, order)
+                r = R.side_reinit(elem, X, side, order, O.has_affine_map(orc, X))
+                for k in ("ref", "xyz", "JxW", "normals", "phi"):
+                    assert np.array_equal(d[k], r[k]), (k, e, side, np.abs(d[k] - r[k]).max())
+                nodes = (T10_SIDE if elem == "TET10" else H27_SIDE)[side][:ns]
+                assert np.array_equal(d["JxW"], R.fe_map(side_elem, X[nodes], pts, w, False)["JxW"])
 
 
 @needs_ref

@@ -1,5 +1,6 @@
-"""The oracle against the REFERENCE's own application source of the path: examples/introduction/introduction_ex4/
-introduction_ex4.C (assemble_poisson and main) and the constraint functions of src/base/dof_map_constraints.C, compiled where
+"""The oracle against the REFERENCE's own application sources of the path: examples/introduction/introduction_ex4/
+introduction_ex4.C (assemble_poisson and main), examples/systems_of_equations/systems_of_equations_ex6/systems_of_equations_ex6.C
+(LinearElasticity::assemble, traction side term included) and the constraint functions of src/base/dof_map_constraints.C, compiled where
 they lie under /root/reference into oracle/_ref/libref_app.so (oracle/Makefile) and run over the stub world of
 oracle/ref_app/ref_world.h — which says what in that library is the reference's code and what is glue.  The integer structures
 (mesh, dof numbering, pattern) are the oracle's; every floating-point number of the global matrix and right-hand side comes out
@@ -80,6 +81,36 @@ def test_config_1_at_full_size():
     _same(s, R.run_ex4(["-d", 3, "-n", 20], nnz, nd))
 
 
+# ---- systems_of_equations_ex6.C: LinearElasticity::assemble() -----------------------------------------------------------------------
+EX6_BOUNDS = (0.0, 1.0, 0.0, 0.3, 0.0, 0.1)
+EX6 = [("hex8_as_the_example_runs_it", O.HEX8, (8, 4, 2), None, 1), ("hex8_perturbed", O.HEX8, (4, 3, 3), (1, 0.004, 11), 1),
+       ("hex27_config5_small", O.HEX27, (4, 3, 2), None, 2), ("hex27_perturbed", O.HEX27, (3, 2, 2), (1, 0.004, 7), 2)]
+
+
+@pytest.mark.parametrize("name,etype,dims,skew,order", EX6, ids=[c[0] for c in EX6])
+def test_linear_elasticity_assemble_of_ex6_gives_the_oracles_bits(name, etype, dims, skew, order):
+    """The 6-deep tensor loop over DenseSubMatrix blocks (:220-237), the body force, the traction on the max-x sides through
+    fe_face->reinit(elem, side) (:240-257) and constrain_element_matrix_and_vector (:259) — matrix and right-hand side bitwise."""
+    m = O.Mesh(etype, *dims, EX6_BOUNDS)
+    if skew is not None:
+        m.skew(*skew)
+    s = O.System(m, 3)
+    s.add_dirichlet((4,), 1)
+    e, sd = m.boundary_sides(2)
+    s.set_side_loads(e, sd, (0.0, 0.0, -1.0))
+    s.build_sparsity()
+    nnz, nd = R.load_world(m, s, dims, EX6_BOUNDS)
+    R.load_sides(m)
+    out = R.assemble_ex6(order, nnz, nd, (4,))
+    v, r, _ = s.assemble(O.ELASTICITY_EX6)
+    cd, cv = s.constraints()
+    assert np.array_equal(cd, out["con_dof"]) and np.array_equal(cv, out["con_val"])
+    assert np.array_equal(v, out["values"]) and np.array_equal(r, out["rhs"])
+    # the traction really is in there: without the side list the oracle's right-hand side differs
+    s.set_side_loads([], [], (0.0, 0.0, -1.0))
+    assert np.abs(s.assemble(O.ELASTICITY_EX6)[1] - out["rhs"]).max() > 1e-4
+
+
 # ---- DofMap::constrain_element_matrix_and_vector / heterogeneously_... / build_constraint_matrix(_and_vector) ----------------------
 def _both(rows, vals, K, F, dofs, hetero=True, asym=True):
     K1, F1, d1 = OC.constrain(OC.ConstraintRows(rows, vals), K.copy(), F.copy(), [int(d) for d in dofs], hetero, asym)
@@ -155,5 +186,12 @@ def test_committed_golden_outputs_are_what_the_reference_gives_today():
     for name, etype, n, skew, order, through_main in G.CASES:
         m, s = G.oracle_case(etype, n, skew)
         r = G.reference_run(m, s, n, order, through_main)
+        for k in ("values", "rhs", "con_dof", "con_val"):
+            assert np.array_equal(r[k], g[name + "/" + k]), (name, k)
+    g = np.load(os.path.join(os.path.dirname(os.path.abspath(__file__)), "golden", "reference_ex6_runs.npz"))
+    assert list(g["names"]) == [c[0] for c in G.CASES6]
+    for name, etype, dims, skew, order in G.CASES6:
+        m, s = G.oracle_case6(etype, dims, skew)
+        r = G.reference_run6(m, s, dims, order)
         for k in ("values", "rhs", "con_dof", "con_val"):
             assert np.array_equal(r[k], g[name + "/" + k]), (name, k)
