@@ -6,17 +6,23 @@
  * libmesh_b200/ and the timed CPU baseline of bench.py.  Nothing in the product may include, link or
  * call it; only tests/, __graft_entry__.smoke() and bench.py's cpu_baseline / --impl reference legs do.
  *
- * Parity status: libMesh as a whole cannot be compiled in the build container (TIMPI / MetaPhysicL submodules are
- * empty, libmesh_config.h is generated), but the reference files that hold the arithmetic of FE::reinit can: oracle/_ref
- * (oracle/Makefile) compiles src/fe/fe_lagrange_shape_{2,3}D.C, include/fe/fe_lagrange_shape_1D.h,
- * src/quadrature/quadrature*.C, src/fe/fe_map.C and the examples' exact_solution.C where they lie, against stub
- * declarations (oracle/ref_stubs/).  Against that code this oracle's Gauss rules, shape tables and FE::reinit output (xyz,
- * JxW, dphi; affine and general branch of FEMap::compute_map) are BIT-IDENTICAL on every element type of the path
- * (tests/test_oracle_ref.py; golden tables tests/golden/reference_fe_*.npz written from it).  What no compiled reference
- * code checks: Elem::has_affine_map, build_cube, dof numbering, the sparsity pattern, the constraint routines and the
- * scatter — pinned by the reference's unit-test known answers (tests/fe/fe_test.h, tests/numerics/sparse_matrix_test.h,
- * tests/systems/systems_test.C, tests/base/dof_map_test.C, tests/mesh/mesh_generation_test.C) and its published run facts,
- * restated in tests/test_oracle_*.py; GLOBAL matrix / RHS numbers against a real libMesh build stay "parity unpinned".
+ * Parity status: PINNED AGAINST OUTPUTS OF THE REFERENCE ITSELF, RUN HERE, for every floating-point number of the path.
+ * libMesh as a whole cannot be compiled in the build container (TIMPI / MetaPhysicL submodules are empty, libmesh_config.h
+ * is generated), but the reference files that hold the arithmetic of the path can, where they lie, against stub declarations
+ * (oracle/Makefile -> oracle/_ref/; oracle/ref_stubs/, oracle/ref_app/):
+ *   libref_fe.so   src/fe/fe_lagrange_shape_{2,3}D.C, include/fe/fe_lagrange_shape_1D.h, src/quadrature/quadrature*.C,
+ *                  src/fe/fe_map.C, the face maps of src/fe/fe_boundary.C, the examples' exact_solution.C: this oracle's Gauss
+ *                  rules, shape tables, FE::reinit and FE::reinit(elem, side) output are BIT-IDENTICAL on every element type
+ *                  of the path, affine and general branch (tests/test_oracle_ref.py, golden tables reference_fe_*.npz);
+ *   libref_app.so  the examples themselves — introduction_ex4.C (main and assemble_poisson), systems_of_equations_ex6.C
+ *                  (LinearElasticity::assemble) — over the reference's DenseMatrix sources and its DofMap constraint
+ *                  functions: the GLOBAL matrix and right-hand side they produce are BIT-IDENTICAL to orc_assemble's, config 1
+ *                  (20^3 HEX27) at full size included (tests/test_oracle_ref_app.py; golden outputs reference_ex{4,6}_runs.npz,
+ *                  which tests/test_golden_ref_app.py and the GPU suite compare with on machines without /root/reference).
+ * What no compiled reference code checks is the integer side: build_cube's numbering, Elem::has_affine_map, the dof numbering,
+ * the sparsity pattern, the partitioner — pinned by the reference's unit-test known answers (tests/fe/fe_test.h,
+ * tests/numerics/sparse_matrix_test.h, tests/systems/systems_test.C, tests/base/dof_map_test.C,
+ * tests/mesh/mesh_generation_test.C) and its published run facts, restated in tests/test_oracle_*.py.
  *
  * Every function cites the reference file:line it follows (paths relative to /root/reference).
  */
