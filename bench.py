@@ -293,14 +293,56 @@ def cpu_baseline(args, budget_s: float = 12.0):
     t1 = time.perf_counter() - t1
     tot = float(ph.sum()) or 1.0
     names = ["elem_init", "Ke", "Fe", "matrix_insertion"]
+    ref_code = reference_code_sample(args, O)
     return {"value": rate, "unit": "elements/s", "cores": threads, "kind": "port", "sample": sample,
             "single_thread": {"value": m1.n_elem / t1, "unit": "elements/s", "sample": f"one pass of build_cube {n1}^3 ({m1.n_elem} elements), 1 thread",
                               "phase_seconds": {k: round(float(v), 4) for k, v in zip(names, ph)},
                               "phase_percent": {k: round(100 * float(v) / tot, 2) for k, v in zip(names, ph)},
                               "reference_published_percent": {"elem_init": 33.54, "Ke": 40.71, "Fe": 10.14, "matrix_insertion": 15.61,
                                                               "source": "doc/html/examples/introduction_ex4.html:490-493 (-d 3 -n 6, 1 rank)"}},
-            "note": "oracle = CPU restatement of the reference loop (g++ -O3 -march=x86-64-v3, OpenMP over elements); the "
-                    "reference itself cannot be compiled here (empty TIMPI/MetaPhysicL submodules)"}
+            "reference_code": ref_code,
+            "note": "oracle = CPU restatement of the reference loop (g++ -O3 -march=x86-64-v3, OpenMP over elements); libMesh as a "
+                    "library cannot be compiled here (empty TIMPI/MetaPhysicL submodules); reference_code = the example's own "
+                    "assembly function compiled where it lies (oracle/_ref), one thread, reported beside the port"}
+
+
+def reference_code_sample(args, O, n: int = 24):
+    """assemble_poisson of the reference's own introduction_ex4.C — compiled where it lies into oracle/_ref/libref_app*.so over the
+    reference's quadrature, shape, FEMap, DenseMatrix and constraint code and a stub mesh / matrix world (oracle/ref_app/
+    ref_world.h) — timed on one thread on a bounded sample, at the port's optimisation level (the _fast build; the -O2
+    no-contraction build is the bitwise checker of the oracle, tests/test_oracle_ref_app.py).  A data point beside the port,
+    not the reference arm: the stub world's matrix insertion is a search into a CSR array, not a solver package's."""
+    try:
+        from oracle import ref as R
+
+        if args.problem != "poisson" or not R.app_available(fast=True):
+            return None
+        etype = ELEM[args.elem]
+        b = problem_dims(args)[1]
+        m = O.Mesh(etype, n, n, n, bounds=b, fast=True)
+        s = O.System(m, 1)
+        s.add_dirichlet()
+        s.build_sparsity()
+        R.use_fast(True)
+        try:
+            nnz, nd = R.load_world(m, s, n, b, affine=np.ones(m.n_elem, dtype=np.uint8))
+            order = 1 if args.elem == "hex8" else 2
+            R.assemble_ex4(order, nnz, nd)  # warm-up
+            out = R.assemble_ex4(order, nnz, nd)
+            dt = R.last_solve_seconds()
+        finally:
+            R.use_fast(False)
+        t1 = time.perf_counter()
+        vo, ro, _ = s.assemble(O.POISSON_EX4, n_threads=1)
+        t1 = time.perf_counter() - t1
+        return {"value": m.n_elem / dt, "unit": "elements/s", "cores": 1, "kind": "reference",
+                "sample": f"assemble_poisson of introduction_ex4.C on build_cube {n}^3 {args.elem.upper()} ({m.n_elem} elements), 1 thread, {dt:.2f} s",
+                "port_on_the_same_sample": {"value": m.n_elem / t1, "unit": "elements/s"},
+                "max_abs_diff_to_the_port": {"values": float(np.abs(vo - out["values"]).max()), "rhs": float(np.abs(ro - out["rhs"]).max()),
+                                             "note": "both at -O3 with FMA contraction; the -O2 builds agree bit for bit"}}
+    except Exception as e:  # a data point only: never takes the bench line down
+        return {"unavailable": f"{type(e).__name__}: {e}"[:200]}
+
 
 # ---- our arm, one GPU ---------------------------------------------------------------------------------------------------
 def run_ours(args):

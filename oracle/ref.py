@@ -92,17 +92,25 @@ def fe_map(elem: str, node_xyz, ref_points, weights, affine: bool):
 # reference's code and what is glue) -------------------------------------------------------------------------------------------------
 APP_LIB_PATH = os.path.join(os.path.dirname(os.path.abspath(__file__)), "_ref", "libref_app.so")
 _ORC_TO_LIBMESH = {8: "HEX8", 20: "HEX20", 27: "HEX27", 10: "TET10", 18: "PRISM18"}
-_app = None
+APP_FAST_LIB_PATH = os.path.join(os.path.dirname(os.path.abspath(__file__)), "_ref", "libref_app_fast.so")
+_apps = {}
+_fast = False
 
 
-def app_available() -> bool:
-    return os.path.exists(APP_LIB_PATH)
+def app_available(fast: bool = False) -> bool:
+    return os.path.exists(APP_FAST_LIB_PATH if fast else APP_LIB_PATH)
+
+
+def use_fast(on: bool) -> None:
+    """Route the calls below to libref_app_fast.so — the same sources at -O3 -march=x86-64-v3, for timing (bench.py) — instead of
+    the -O2 -ffp-contract=off build that is the bitwise checker."""
+    global _fast
+    _fast = bool(on)
 
 
 def app():
-    global _app
-    if _app is None:
-        L = C.CDLL(APP_LIB_PATH)
+    if _fast not in _apps:
+        L = C.CDLL(APP_FAST_LIB_PATH if _fast else APP_LIB_PATH)
         L.ref_world_load.restype = C.c_int
         L.ref_world_load.argtypes = [C.c_int, C.c_int, C.c_uint, C.c_uint, C.c_uint, C.c_void_p, C.c_uint64, C.c_void_p, C.c_uint64, C.c_void_p, C.c_void_p,
                                      C.c_void_p, C.c_int, C.c_uint64, C.c_void_p, C.c_void_p, C.c_void_p]
@@ -114,6 +122,8 @@ def app():
         L.ref_ex6_assemble.argtypes = [C.c_int, C.c_uint, C.c_char_p, C.c_int]
         L.ref_world_set_sides.restype = C.c_int
         L.ref_world_set_sides.argtypes = [C.c_int, C.c_void_p]
+        L.ref_world_solve_seconds.restype = C.c_double
+        L.ref_world_solve_seconds.argtypes = []
         L.ref_world_results.restype = C.c_int64
         L.ref_world_results.argtypes = [C.c_void_p] * 4
         L.ref_side_reinit.restype = C.c_int
@@ -121,8 +131,8 @@ def app():
         L.ref_constrain_element.restype = C.c_int
         L.ref_constrain_element.argtypes = [C.c_int, C.c_void_p, C.c_void_p, C.c_void_p, C.c_int, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p,
                                             C.c_int, C.c_int, C.c_int, C.c_void_p, C.c_void_p, C.c_void_p, C.c_char_p, C.c_int]
-        _app = L
-    return _app
+        _apps[_fast] = L
+    return _apps[_fast]
 
 
 def load_world(mesh, system, n, bounds, affine=None):
@@ -189,6 +199,11 @@ def assemble_ex6(order, nnz, n_dofs, dirichlet_ids=(4,)):
     if app().ref_ex6_assemble(int(order), mask, err, 1024) != 0:
         raise RuntimeError(err.value.decode())
     return _results(nnz, n_dofs)
+
+
+def last_solve_seconds() -> float:
+    """Wall-clock seconds of the system.solve() (zero + the example's assembly function) of the last assemble_ex4."""
+    return float(app().ref_world_solve_seconds())
 
 
 def run_ex4(args, nnz, n_dofs):

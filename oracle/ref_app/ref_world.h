@@ -92,6 +92,7 @@ struct RefWorldData {
   std::vector<uint32_t> con_dof;         // the constrained dofs and their values, as EquationSystems::init left them
   std::vector<double> con_val;
   std::vector<std::string> args;         // the command line LibMeshInit saw
+  double solve_seconds = 0.;
   uint64_t n_nodes() const { return xyz.size() / 3; }
   uint64_t n_elem() const { return npe ? conn.size() / npe : 0; }
 };

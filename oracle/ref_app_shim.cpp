@@ -1,6 +1,8 @@
 // ref_app_shim.cpp — the stub world of ref_app/ref_world.h (definitions) and the C entry points of oracle/_ref/libref_app.so.
 // Test infrastructure: see ref_world.h for what in that library is the reference's own code and what is glue.  Nothing under
 // libmesh_b200/ may touch it.
+#include <chrono>
+
 #include "ref_world.h"
 #include "libmesh/quadrature_gauss.h"
 
@@ -247,10 +249,15 @@ int ref_ex4_assemble(int order, unsigned int boundary_mask, char* err, int err_l
     DirichletBoundary dirichlet_bc(boundary_ids, {u_var}, exact_solution_object);
     system.get_dof_map().add_dirichlet_boundary(dirichlet_bc);
     equation_systems.init();
+    const auto t0 = std::chrono::steady_clock::now();
     system.solve();
+    ref_world().solve_seconds = std::chrono::duration<double>(std::chrono::steady_clock::now() - t0).count();
     return 0;
   } catch (const std::exception& e) { return fail(e, err, err_len); }
 }
+
+// wall-clock seconds of the last system.solve() (= zero + the example's assembly function) of ref_ex4_assemble
+double ref_world_solve_seconds(void) { return ref_world().solve_seconds; }
 
 // what the run left behind: matrix values in the loaded pattern's order, the right-hand side, the Dirichlet constraints
 int64_t ref_world_results(double* values, double* rhs, uint32_t* con_dof, double* con_val) {
