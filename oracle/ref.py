@@ -124,6 +124,8 @@ def app():
         L.ref_world_set_sides.argtypes = [C.c_int, C.c_void_p]
         L.ref_world_solve_seconds.restype = C.c_double
         L.ref_world_solve_seconds.argtypes = []
+        L.ref_world_untouched_entries.restype = C.c_int64
+        L.ref_world_untouched_entries.argtypes = []
         L.ref_world_results.restype = C.c_int64
         L.ref_world_results.argtypes = [C.c_void_p] * 4
         L.ref_side_reinit.restype = C.c_int
@@ -162,7 +164,7 @@ def _results(nnz, n_dofs):
     nc = app().ref_world_results(None, None, None, None)
     cd, cv = np.zeros(nc, dtype=np.uint32), np.zeros(nc)
     app().ref_world_results(values.ctypes.data, rhs.ctypes.data, cd.ctypes.data, cv.ctypes.data)
-    return dict(values=values, rhs=rhs, con_dof=cd, con_val=cv)
+    return dict(values=values, rhs=rhs, con_dof=cd, con_val=cv, untouched_entries=int(app().ref_world_untouched_entries()))
 
 
 def assemble_ex4(order, nnz, n_dofs, boundary_ids=(0, 1, 2, 3, 4, 5)):

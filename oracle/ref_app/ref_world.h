@@ -89,6 +89,7 @@ struct RefWorldData {
   std::vector<uint32_t> col_idx;
   // results
   std::vector<double> values, rhs;
+  std::vector<uint8_t> touched;          // [nnz] 1 once SparseMatrix::add_matrix has added into the entry (zeros count: sparse_matrix.h:300-303)
   std::vector<uint32_t> con_dof;         // the constrained dofs and their values, as EquationSystems::init left them
   std::vector<double> con_val;
   std::vector<std::string> args;         // the command line LibMeshInit saw
@@ -171,6 +172,7 @@ public:
         const uint32_t* p = std::lower_bound(w.col_idx.data() + b, w.col_idx.data() + e, (uint32_t)dof_indices[j]);
         libmesh_error_msg_if(p == w.col_idx.data() + e || *p != dof_indices[j], "entry (" << r << ", " << dof_indices[j] << ") is not in the sparsity pattern");
         w.values[p - w.col_idx.data()] += dm(i, j);
+        w.touched[p - w.col_idx.data()] = 1;
       }
   }
   void zero() { std::fill(ref_world().values.begin(), ref_world().values.end(), 0.); }

@@ -166,6 +166,7 @@ void EquationSystems::init() {
     }
   }
   w.values.assign(w.col_idx.size(), 0.);
+  w.touched.assign(w.col_idx.size(), 0);
   w.rhs.assign(w.n_dofs, 0.);
 }
 
@@ -258,6 +259,14 @@ int ref_ex4_assemble(int order, unsigned int boundary_mask, char* err, int err_l
 
 // wall-clock seconds of the last system.solve() (= zero + the example's assembly function) of ref_ex4_assemble
 double ref_world_solve_seconds(void) { return ref_world().solve_seconds; }
+
+// entries of the loaded sparsity pattern that no add_matrix call of the run added into (an entry outside the pattern throws): 0 means
+// the pattern is exactly the set of (row, column) pairs the example's element loop touches
+int64_t ref_world_untouched_entries(void) {
+  int64_t n = 0;
+  for (uint8_t t : ref_world().touched) n += !t;
+  return n;
+}
 
 // what the run left behind: matrix values in the loaded pattern's order, the right-hand side, the Dirichlet constraints
 int64_t ref_world_results(double* values, double* rhs, uint32_t* con_dof, double* con_val) {

@@ -38,6 +38,9 @@ def _same(s, out):
     assert np.array_equal(cd, out["con_dof"]) and np.array_equal(cv, out["con_val"]), "Dirichlet constraints differ"
     assert np.array_equal(v, out["values"]), f"matrix values differ by {np.abs(v - out['values']).max()}"
     assert np.array_equal(r, out["rhs"]), f"right-hand side differs by {np.abs(r - out['rhs']).max()}"
+    # the sparsity pattern is EXACTLY what the example's element loop adds into: an entry outside it throws in the stub matrix
+    # ("not in the sparsity pattern"), and no entry of it stays untouched — what SparsityPattern::Build computes for this system
+    assert out["untouched_entries"] == 0
 
 
 @pytest.mark.parametrize("etype,n,extra", [(O.HEX27, 3, []), (O.HEX27, 6, []), (O.HEX8, 5, ["-o", "FIRST"])], ids=["hex27_n3", "hex27_n6_published_shape", "hex8_n5"])
@@ -105,7 +108,7 @@ def test_linear_elasticity_assemble_of_ex6_gives_the_oracles_bits(name, etype, d
     v, r, _ = s.assemble(O.ELASTICITY_EX6)
     cd, cv = s.constraints()
     assert np.array_equal(cd, out["con_dof"]) and np.array_equal(cv, out["con_val"])
-    assert np.array_equal(v, out["values"]) and np.array_equal(r, out["rhs"])
+    assert np.array_equal(v, out["values"]) and np.array_equal(r, out["rhs"]) and out["untouched_entries"] == 0
     # the traction really is in there: without the side list the oracle's right-hand side differs
     s.set_side_loads([], [], (0.0, 0.0, -1.0))
     assert np.abs(s.assemble(O.ELASTICITY_EX6)[1] - out["rhs"]).max() > 1e-4
