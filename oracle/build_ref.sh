@@ -52,3 +52,11 @@ $APP -I"$REF/examples/systems_of_equations/systems_of_equations_ex6" -o $OBJ/ex6
 OBJS="$OBJ/app_shim.o $OBJ/ex4.o $OBJ/ex6.o"
 for s in $APP_REF_SRC; do $APP -o $OBJ/$s.o "$REF/src/numerics/$s.C"; OBJS="$OBJS $OBJ/$s.o"; done
 $CXX -shared -o _ref/libref_app$SFX.so $OBJS -L_ref -lref_fe$SFX -Wl,-rpath,'$ORIGIN'
+
+# ---- libref_mesh (checker build only): the reference's own MeshTools::Generation::build_cube over the recording mesh of
+# ref_mesh/ref_mesh_world.h
+if [ -z "$SFX" ]; then
+  python3 ref_excerpt.py "$REF" mesh_idx _ref/gen/ref_mesh_idx.inc
+  python3 ref_excerpt.py "$REF" mesh _ref/gen/ref_mesh_excerpts.inc
+  $CXX -std=c++17 $OPT -fPIC -shared -I_ref/inc -Iref_stubs -Iref_mesh -I_ref/gen -o _ref/libref_mesh.so ref_mesh_shim.cpp
+fi

@@ -15,6 +15,7 @@ LIB_PATH = os.path.join(os.path.dirname(os.path.abspath(__file__)), "_ref", "lib
 
 # libMesh's enum values (include/enums/enum_elem_type.h, enum_order.h)
 ELEM = {"TRI6": 4, "QUAD4": 5, "QUAD8": 6, "QUAD9": 7, "TET10": 9, "HEX8": 10, "HEX20": 11, "HEX27": 12, "PRISM18": 15}
+ELEM_ALL = dict(ELEM, TET4=8)
 N_NODES = {"TRI6": 6, "QUAD4": 4, "QUAD8": 8, "QUAD9": 9, "TET10": 10, "HEX8": 8, "HEX20": 20, "HEX27": 27, "PRISM18": 18}
 DIM = {"TRI6": 2, "QUAD4": 2, "QUAD8": 2, "QUAD9": 2, "TET10": 3, "HEX8": 3, "HEX20": 3, "HEX27": 3, "PRISM18": 3}
 FE_ORDER = {"TRI6": 2, "QUAD4": 1, "QUAD8": 2, "QUAD9": 2, "TET10": 2, "HEX8": 1, "HEX20": 2, "HEX27": 2, "PRISM18": 2}
@@ -265,3 +266,39 @@ def side_reinit(elem: str, node_xyz, side: int, qorder: int, affine: bool):
     if nqf < 0:
         raise RuntimeError(err.value.decode())
     return dict(ref=ref[:nqf], xyz=xyz[:nqf], JxW=JxW[:nqf], normals=nrm[:nqf], phi=phi[: n * nqf].reshape(n, nqf))
+
+
+# ---- oracle/_ref/libref_mesh.so: the reference's own MeshTools::Generation::build_cube over a recording mesh
+# (oracle/ref_mesh/ref_mesh_world.h) -------------------------------------------------------------------------------------------------------
+MESH_LIB_PATH = os.path.join(os.path.dirname(os.path.abspath(__file__)), "_ref", "libref_mesh.so")
+_mesh_lib = None
+
+
+def mesh_available() -> bool:
+    return os.path.exists(MESH_LIB_PATH)
+
+
+def build_cube(elem: str, nx: int, ny: int, nz: int, bounds):
+    """MeshTools::Generation::build_cube(mesh, nx, ny, nz, bounds, type) of the reference (src/mesh/mesh_generation.C:317-1938), as
+    far as it goes before all_second_order / prepare_for_use: dict(xyz [n_nodes][3], conn [n_elem][npe] (node ids, in the order the
+    elements were added), elem_id, sides = (element position, side, boundary id) in the order they were added,
+    second_order_requests, prepared).  TET10 comes back as the 24 TET4 per cell that all_second_order is then asked to raise."""
+    global _mesh_lib
+    if _mesh_lib is None:
+        L = C.CDLL(MESH_LIB_PATH)
+        L.ref_build_cube.restype = C.c_int
+        L.ref_build_cube.argtypes = [C.c_uint, C.c_uint, C.c_uint, C.c_void_p, C.c_int, C.c_char_p, C.c_int]
+        L.ref_mesh_sizes.argtypes = [C.c_void_p]
+        L.ref_mesh_get.argtypes = [C.c_void_p] * 6
+        _mesh_lib = L
+    b = np.ascontiguousarray(bounds, dtype=np.float64)
+    err = C.create_string_buffer(1024)
+    if _mesh_lib.ref_build_cube(nx, ny, nz, b.ctypes.data, ELEM_ALL[elem], err, 1024) != 0:
+        raise RuntimeError(err.value.decode())
+    sz = np.zeros(6, dtype=np.int64)
+    _mesh_lib.ref_mesh_sizes(sz.ctypes.data)
+    nn, ne, npe, ns = (int(x) for x in sz[:4])
+    xyz, conn, eid = np.zeros((nn, 3)), np.zeros((ne, npe), dtype=np.uint32), np.zeros(ne, dtype=np.uint32)
+    se, sn, sb = np.zeros(ns, dtype=np.uint32), np.zeros(ns, dtype=np.uint8), np.zeros(ns, dtype=np.int16)
+    _mesh_lib.ref_mesh_get(xyz.ctypes.data, conn.ctypes.data, eid.ctypes.data, se.ctypes.data, sn.ctypes.data, sb.ctypes.data)
+    return dict(xyz=xyz, conn=conn, elem_id=eid, sides=(se, sn, sb), second_order_requests=int(sz[4]), prepared=bool(sz[5]))

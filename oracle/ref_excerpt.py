@@ -5,7 +5,7 @@ oracle/ref_stubs/ and oracle/ref_app/.  (The files as a whole — src/base/dof_m
 DofMap; src/fe/fe_boundary.C and h1_fe_transformation.C with their instantiations for every family; the element classes of
 src/geom/ — cannot be compiled stand-alone.)  Nothing is committed: the output goes under oracle/_ref/, which is git-ignored.
 
-    python3 ref_excerpt.py <reference root> <set: fe | app> <output file>
+    python3 ref_excerpt.py <reference root> <set: fe | app | mesh_idx | mesh> <output file>
 """
 import re
 import sys
@@ -24,6 +24,13 @@ SETS = {
         ("src/geom/cell_tet10.C", r"^const unsigned int Tet10::side_nodes_map\[", TABLE_END, ""),
         ("src/geom/cell_prism18.C", r"^const unsigned int Prism18::side_nodes_map\[", TABLE_END, ""),
     ],
+    "mesh_idx": [
+        ("src/mesh/mesh_generation.C", r"^unsigned int idx\(const ElemType type,", FUNC_END, "inline\n"),
+    ],
+    "mesh": [
+        ("src/mesh/mesh_generation.C", r"^void MeshTools::Generation::build_cube\(", FUNC_END, ""),
+        ("src/geom/cell_hex27.C", r"^const unsigned int Hex27::side_nodes_map\[", TABLE_END, ""),
+    ],
     "app": [
         ("src/base/dof_map_constraints.C", r"^void DofMap::build_constraint_matrix \(", FUNC_END, ""),
         ("src/base/dof_map_constraints.C", r"^void DofMap::build_constraint_matrix_and_vector \(", FUNC_END, ""),
@@ -36,8 +43,9 @@ with open(out, "w") as o:
     for path, start, stop, prefix in SETS[which]:
         lines = open(f"{ref}/{path}").read().split("\n")
         hits = [i for i, l in enumerate(lines) if re.match(start, l)]
-        if len(hits) != 1:
+        if len(hits) != (2 if which == "mesh_idx" else 1):  # idx() has a 2D and a 3D overload
             sys.exit(f"ref_excerpt: {len(hits)} definitions match {start!r} in {path}")
-        end = next(i for i in range(hits[0], len(lines)) if re.match(stop, lines[i]))
-        o.write(f"// ---- {path}:{hits[0] + 1}-{end + 1}\n{prefix}")
-        o.write("\n".join(lines[hits[0]:end + 1]) + "\n\n")
+        for h in hits:
+            end = next(i for i in range(h, len(lines)) if re.match(stop, lines[i]))
+            o.write(f"// ---- {path}:{h + 1}-{end + 1}\n{prefix}")
+            o.write("\n".join(lines[h:end + 1]) + "\n\n")

@@ -1,0 +1,146 @@
+// ref_mesh/ref_mesh_world.h — STUB mesh world (test infrastructure, written for this repository; not reference code).
+//
+// Purpose: run the reference's own MeshTools::Generation::build_cube (src/mesh/mesh_generation.C:317-1938, with its idx() helpers
+// :81-157) — the DEFINITIONS are cut out of the file where it lies at build time (oracle/ref_excerpt.py, sets "mesh_idx" /
+// "mesh"; the file as a whole pulls in every element class, the sphere / extrusion / Delaunay generators and MeshRefinement) —
+// against a mesh that only RECORDS what the generator does: points with their ids, elements with their node pointers, side and
+// node boundary ids.  tests/test_oracle_ref_mesh.py compares the record with the oracle's build_cube restatement (orc_mesh.cpp)
+// before renumbering: lattice indexing, node coordinates (the reference's own scaling arithmetic), connectivity, boundary sides,
+// and the 24-tet split that precedes all_second_order for TET10.  What this world does NOT do: UnstructuredMesh::all_second_order
+// and MeshBase::prepare_for_use (node renumbering, neighbours, partitioning) — recorded as requests and left to the oracle's
+// restatement, which stays pinned by the reference's published run facts.
+#ifndef REF_MESH_WORLD_H
+#define REF_MESH_WORLD_H
+#include <array>
+#include <map>
+
+#include "libmesh/libmesh_common.h"
+#include "libmesh/enum_elem_type.h"  // the reference's own enum
+#include "libmesh/enum_to_string.h"
+#include "libmesh/point.h"
+
+#define LIBMESH_ENABLE_UNIQUE_ID 1
+
+namespace libMesh {
+typedef short boundary_id_type;
+
+// the side-node table build_side_ptr of the HEX27 base elements needs (include/geom/cell_hex27.h); DEFINITION excerpted from
+// src/geom/cell_hex27.C
+struct Hex27 { static const int num_sides = 6, nodes_per_side = 9; static const unsigned int side_nodes_map[num_sides][nodes_per_side]; };
+
+class MNode : public Point {  // include/geom/node.h: a point with an id
+public:
+  MNode(const Point& p, dof_id_type id) : Point(p), _id(id) {}
+  dof_id_type id() const { return _id; }
+private:
+  dof_id_type _id;
+};
+#define Node MNode  /* ref_stubs' point.h already names a value-type Node for the FE library; this world's nodes are shared by pointer */
+
+class Elem {
+public:
+  explicit Elem(ElemType t = INVALID_ELEM) : _t(t) {}
+  virtual ~Elem() = default;
+  static std::unique_ptr<Elem> build(const ElemType t) { return std::make_unique<Elem>(t); }
+  static std::unique_ptr<Elem> build_with_id(const ElemType t, dof_id_type id) { auto e = std::make_unique<Elem>(t); e->_id = id; return e; }
+  ElemType type() const { return _t; }
+  dof_id_type id() const { return _id; }
+  void set_id(dof_id_type i) { _id = i; }
+  dof_id_type& set_id() { return _id; }
+  void set_node(unsigned int i, Node* n) { if (_nodes.size() <= i) _nodes.resize(i + 1, nullptr); _nodes[i] = n; }
+  Node* node_ptr(unsigned int i) const { return _nodes.at(i); }
+  unsigned int n_nodes() const { return (unsigned int)_nodes.size(); }
+  IntRange<unsigned short> side_index_range() const { return IntRange<unsigned short>(0, (unsigned short)(_t == HEX27 ? 6 : 0)); }
+  // Hex27::build_side_ptr: a QUAD9 over the nodes of Hex27::side_nodes_map[s]
+  void build_side_ptr(std::unique_ptr<Elem>& side, const unsigned int s) {
+    libmesh_error_msg_if(_t != HEX27, "build_side_ptr: HEX27 only in this stub");
+    side = std::make_unique<Elem>(QUAD9);
+    for (unsigned int i = 0; i < 9; ++i) side->set_node(i, _nodes[Hex27::side_nodes_map[s][i]]);
+  }
+  bool deleted = false;
+private:
+  ElemType _t;
+  dof_id_type _id = 0;
+  std::vector<Node*> _nodes;
+};
+class Polygon : public Elem { public: using Elem::Elem; };
+class C0Polygon : public Polygon { public: explicit C0Polygon(unsigned int) : Polygon(C0POLYGON) {} };
+class C0Polyhedron : public Elem {
+public:
+  C0Polyhedron(const std::vector<std::shared_ptr<Polygon>>&, std::unique_ptr<Node>&) : Elem(C0POLYHEDRON) { libmesh_not_implemented(); }
+};
+
+class BoundaryInfo {
+public:
+  static const boundary_id_type invalid_id = -123;  // include/mesh/boundary_info.h
+  void add_side(const Elem* e, const unsigned short int side, const boundary_id_type id) { sides.push_back({e, side, id}); }
+  void add_node(const Node* n, const boundary_id_type id) { nodes.push_back({n, id}); }
+  void boundary_ids(const Elem* const e, const unsigned short int side, std::vector<boundary_id_type>& out) const {
+    out.clear();
+    for (const auto& s : sides) if (s.e == e && s.side == side) out.push_back(s.id);
+  }
+  void remove(const Elem* e) { for (auto& s : sides) if (s.e == e) s.e = nullptr; }
+  std::string& sideset_name(boundary_id_type id) { return _ss[id]; }
+  std::string& nodeset_name(boundary_id_type id) { return _ns[id]; }
+  struct Side { const Elem* e; unsigned short side; boundary_id_type id; };
+  struct NodeId { const Node* n; boundary_id_type id; };
+  std::vector<Side> sides;
+  std::vector<NodeId> nodes;
+private:
+  std::map<boundary_id_type, std::string> _ss, _ns;
+};
+
+class UnstructuredMesh {
+public:
+  void clear() { _nodes.clear(); _elems.clear(); _bi = BoundaryInfo(); second_order_requests = 0; prepared = false; }
+  BoundaryInfo& get_boundary_info() { return _bi; }
+  void set_mesh_dimension(unsigned char d) { _dim = d; }
+  void set_spatial_dimension(unsigned char) {}
+  unsigned int mesh_dimension() const { return _dim; }
+  void reserve_elem(dof_id_type n) { reserved_elem = n; }
+  void reserve_nodes(dof_id_type n) { reserved_nodes = n; }
+  Node* add_point(const Point& p, const dof_id_type id = (dof_id_type)-1) {
+    _nodes.push_back(std::make_unique<Node>(p, id == (dof_id_type)-1 ? (dof_id_type)_nodes.size() : id));
+    libmesh_error_msg_if(_nodes.back()->id() != _nodes.size() - 1, "nodes are expected in id order");
+    return _nodes.back().get();
+  }
+  Node* add_node(std::unique_ptr<Node> n) { _nodes.push_back(std::move(n)); return _nodes.back().get(); }
+  Node* node_ptr(const dof_id_type i) { return _nodes.at(i).get(); }
+  Elem* add_elem(std::unique_ptr<Elem> e) { _elems.push_back(std::move(e)); return _elems.back().get(); }
+  dof_id_type n_elem() const { dof_id_type n = 0; for (const auto& e : _elems) n += !e->deleted; return n; }
+  std::vector<Node*> node_ptr_range() { std::vector<Node*> v; for (auto& n : _nodes) v.push_back(n.get()); return v; }
+  std::vector<Elem*> element_ptr_range() { std::vector<Elem*> v; for (auto& e : _elems) if (!e->deleted) v.push_back(e.get()); return v; }
+  void delete_elem(Elem* e) { e->deleted = true; }
+  // not done here (see the header comment): recorded as requests
+  void all_second_order(const bool = true) { ++second_order_requests; }
+  void all_complete_order() { libmesh_not_implemented(); }
+  void prepare_for_use() { prepared = true; }
+  int second_order_requests = 0;
+  bool prepared = false;
+  dof_id_type reserved_elem = 0, reserved_nodes = 0;
+  std::vector<std::unique_ptr<Node>> _nodes;
+  std::vector<std::unique_ptr<Elem>> _elems;
+private:
+  BoundaryInfo _bi;
+  unsigned char _dim = 0;
+};
+
+template <typename Output> class FunctionBase { public: virtual ~FunctionBase() = default; };
+namespace MeshTools {
+namespace Modification { inline void redistribute(UnstructuredMesh&, const FunctionBase<Real>&) { libmesh_not_implemented(); } }
+namespace Generation {
+// DECLARATION (include/mesh/mesh_generation.h:70-86); the definition is the reference's
+void build_cube(UnstructuredMesh& mesh, const unsigned int nx = 0, const unsigned int ny = 0, const unsigned int nz = 0, const Real xmin = 0., const Real xmax = 1.,
+                const Real ymin = 0., const Real ymax = 1., const Real zmin = 0., const Real zmax = 1., const ElemType type = INVALID_ELEM,
+                const bool gauss_lobatto_grid = false);
+namespace Private {
+// the Gauss-Lobatto grid option of build_cube (mesh_generation.C:165-308) is not on the path: named, never constructed with true
+class GaussLobattoRedistributionFunction : public FunctionBase<Real> {
+public:
+  GaussLobattoRedistributionFunction(unsigned int, Real, Real, unsigned int = 0, Real = 0, Real = 0, unsigned int = 0, Real = 0, Real = 0) { libmesh_not_implemented(); }
+};
+}  // namespace Private
+}  // namespace Generation
+}  // namespace MeshTools
+}  // namespace libMesh
+#endif

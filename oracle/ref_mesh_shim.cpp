@@ -1,0 +1,68 @@
+// ref_mesh_shim.cpp — the reference's own MeshTools::Generation::build_cube over the recording mesh of ref_mesh/ref_mesh_world.h:
+// oracle/_ref/libref_mesh.so.  Test infrastructure (see that header); nothing under libmesh_b200/ may touch it.
+#include "ref_mesh_world.h"
+
+namespace libMesh {
+namespace MeshTools { namespace Generation { namespace Private {
+#include "ref_mesh_idx.inc"  // unsigned int idx(type, nx, i, j) and idx(type, nx, ny, i, j, k), mesh_generation.C:81-157
+} } }
+#include "ref_mesh_excerpts.inc"  // void MeshTools::Generation::build_cube(...), mesh_generation.C:317-1938; Hex27::side_nodes_map
+}  // namespace libMesh
+
+using namespace libMesh;
+
+namespace {
+UnstructuredMesh g_mesh;
+std::vector<Elem*> g_active;
+}
+
+extern "C" {
+
+// build_cube(nx, ny, nz, bounds, type): returns 0 and leaves the record to the getters below, or -1 with the message
+int ref_build_cube(unsigned int nx, unsigned int ny, unsigned int nz, const double* b, int elem_type, char* err, int err_len) {
+  try {
+    MeshTools::Generation::build_cube(g_mesh, nx, ny, nz, b[0], b[1], b[2], b[3], b[4], b[5], static_cast<ElemType>(elem_type));
+    g_active = g_mesh.element_ptr_range();
+    return 0;
+  } catch (const std::exception& e) {
+    if (err && err_len > 0) {
+      int n = 0;
+      for (const char* c = e.what(); *c && n < err_len - 1; ++c) err[n++] = *c;
+      err[n] = 0;
+    }
+    return -1;
+  }
+}
+// sizes: n_nodes, n_elem (active), nodes per element, number of boundary sides, all_second_order requests, prepare_for_use called
+void ref_mesh_sizes(int64_t* out) {
+  out[0] = (int64_t)g_mesh._nodes.size();
+  out[1] = (int64_t)g_active.size();
+  out[2] = g_active.empty() ? 0 : (int64_t)g_active[0]->n_nodes();
+  int64_t ns = 0;
+  for (const auto& s : g_mesh.get_boundary_info().sides) ns += s.e != nullptr;
+  out[3] = ns;
+  out[4] = g_mesh.second_order_requests;
+  out[5] = g_mesh.prepared ? 1 : 0;
+}
+// xyz[n_nodes][3]; conn[n_elem][npe] (node ids) in the order the elements were added; elem ids; boundary sides (position of the
+// element in that order, side, id) in the order they were added
+void ref_mesh_get(double* xyz, uint32_t* conn, uint32_t* elem_id, uint32_t* side_elem, uint8_t* side_no, int16_t* side_bid) {
+  for (std::size_t n = 0; n < g_mesh._nodes.size(); ++n) for (int d = 0; d < 3; ++d) xyz[3 * n + d] = (*g_mesh._nodes[n])(d);
+  std::map<const Elem*, uint32_t> pos;
+  const std::size_t npe = g_active.empty() ? 0 : g_active[0]->n_nodes();
+  for (std::size_t e = 0; e < g_active.size(); ++e) {
+    pos[g_active[e]] = (uint32_t)e;
+    elem_id[e] = g_active[e]->id();
+    for (std::size_t a = 0; a < npe; ++a) conn[e * npe + a] = g_active[e]->node_ptr((unsigned int)a)->id();
+  }
+  std::size_t k = 0;
+  for (const auto& s : g_mesh.get_boundary_info().sides) {
+    if (!s.e) continue;
+    side_elem[k] = pos.at(s.e);
+    side_no[k] = (uint8_t)s.side;
+    side_bid[k] = s.id;
+    ++k;
+  }
+}
+
+}  // extern "C"

@@ -1,0 +1,64 @@
+"""The oracle's build_cube restatement (oracle/orc_mesh.cpp) against the REFERENCE's own MeshTools::Generation::build_cube
+(src/mesh/mesh_generation.C:317-1938 with its idx() helpers :81-157): the definitions are cut out of the file where it lies and
+run over a mesh that records what the generator does (oracle/ref_mesh/ref_mesh_world.h -> oracle/_ref/libref_mesh.so).  Compared
+BEFORE MeshBase::prepare_for_use (node renumbering) and UnstructuredMesh::all_second_order, which that recording mesh does not
+do: lattice indexing, node coordinates (the reference's own scaling arithmetic — bitwise), connectivity in element order, the
+boundary id of every boundary side, and for TET10 the 24-tet split of every cell.  Runs where /root/reference exists."""
+import numpy as np
+import pytest
+
+from oracle import oracle as O
+from oracle import ref as R
+
+pytestmark = pytest.mark.skipif(not R.mesh_available(), reason="oracle/_ref/libref_mesh.so exists only where /root/reference does")
+NAME = {O.HEX8: "HEX8", O.HEX20: "HEX20", O.HEX27: "HEX27", O.TET10: "TET10", O.PRISM18: "PRISM18"}
+BOUNDS = [(-1.0, 1.0, -1.0, 1.0, -1.0, 1.0), (0.0, 1.0, 0.0, 0.3, 0.0, 0.1), (-1.0, 1.0, -0.5, 0.25, 0.0, 3.0)]
+
+
+def _compacted(r):
+    """prepare_for_use removes the lattice nodes no element uses (HEX20: face and cell centres; the tet split: mid-edge lattice
+    nodes) and closes the gaps in ascending id order."""
+    used = np.unique(r["conn"])
+    rank = np.full(r["xyz"].shape[0], -1, dtype=np.int64)
+    rank[used] = np.arange(len(used))
+    return rank[r["conn"]], r["xyz"][used]
+
+
+@pytest.mark.parametrize("etype", [O.HEX8, O.HEX20, O.HEX27, O.PRISM18, O.TET10], ids=lambda e: NAME[e])
+@pytest.mark.parametrize("dims", [(3, 2, 4), (1, 1, 1), (5, 5, 5)], ids=lambda d: "x".join(map(str, d)))
+@pytest.mark.parametrize("bounds", BOUNDS, ids=["ex4_cube", "ex6_bar", "ragged_box"])
+def test_build_cube_before_renumbering_is_the_references(etype, dims, bounds):
+    r = R.build_cube(NAME[etype], *dims, bounds)
+    assert r["prepared"] and r["second_order_requests"] == (1 if etype == O.TET10 else 0)
+    m = O.Mesh(etype, *dims, bounds=bounds, renumber_nodes=False)
+    xyz, conn, _ = m.arrays()
+    rc, rx = _compacted(r)
+    nv = rc.shape[1]  # TET10: the four vertices of the TET4 the reference builds before all_second_order
+    assert rc.shape[0] == conn.shape[0] and np.array_equal(r["elem_id"], np.arange(conn.shape[0]))
+    assert np.array_equal(rc, conn[:, :nv]), "connectivity differs"
+    assert np.array_equal(rx, xyz[: len(rx)]), f"node coordinates differ by {np.abs(rx - xyz[:len(rx)]).max()}"
+    if etype != O.TET10:
+        assert len(rx) == len(xyz)
+
+
+@pytest.mark.parametrize("etype", [O.HEX8, O.HEX27], ids=lambda e: NAME[e])
+def test_boundary_sides_are_the_references(etype):
+    """BoundaryInfo::add_side calls of build_cube: 0 back (min z), 1 bottom (min y), 2 right (max x), 3 top (max y), 4 left (min x),
+    5 front (max z)."""
+    dims = (3, 2, 4)
+    r = R.build_cube(NAME[etype], *dims, BOUNDS[1])
+    se, sn, sb = r["sides"]
+    m = O.Mesh(etype, *dims, bounds=BOUNDS[1], renumber_nodes=False)
+    total = 0
+    for bid in range(6):
+        e, s = m.boundary_sides(bid)
+        want = sorted(zip(e.tolist(), s.tolist()))
+        got = sorted((int(a), int(b)) for a, b, c in zip(se, sn, sb) if c == bid)
+        assert got == want, f"boundary id {bid}"
+        total += len(want)
+    assert total == len(se) == 2 * (3 * 2 + 3 * 4 + 2 * 4)
+
+
+def test_reference_rejects_what_it_rejects():
+    with pytest.raises(RuntimeError, match="Unrecognized 3D element type"):
+        R.build_cube("QUAD9", 2, 2, 2, BOUNDS[0])
