@@ -279,10 +279,14 @@ def mesh_available() -> bool:
 
 
 def build_cube(elem: str, nx: int, ny: int, nz: int, bounds):
-    """MeshTools::Generation::build_cube(mesh, nx, ny, nz, bounds, type) of the reference (src/mesh/mesh_generation.C:317-1938), as
-    far as it goes before all_second_order / prepare_for_use: dict(xyz [n_nodes][3], conn [n_elem][npe] (node ids, in the order the
-    elements were added), elem_id, sides = (element position, side, boundary id) in the order they were added,
-    second_order_requests, prepared).  TET10 comes back as the 24 TET4 per cell that all_second_order is then asked to raise."""
+    """MeshTools::Generation::build_cube(mesh, nx, ny, nz, bounds, type) of the reference (src/mesh/mesh_generation.C:317-1938)
+    followed by its ReplicatedMesh::renumber_nodes_and_elements (src/mesh/replicated_mesh.C:700-857; the numbering step of
+    prepare_for_use).  dict with
+      before = (xyz [lattice nodes][3], conn [n_elem][npe]) as the generator left them when it called prepare_for_use,
+      xyz, conn, elem_id                                     after the renumbering (orphaned lattice nodes removed),
+      sides = (element position, side, boundary id)          in the order the generator added them,
+      second_order_requests, prepared.
+    TET10 comes back as the 24 TET4 per cell that all_second_order is then asked to raise, NOT renumbered (see ref_mesh_world.h)."""
     global _mesh_lib
     if _mesh_lib is None:
         L = C.CDLL(MESH_LIB_PATH)
@@ -290,6 +294,8 @@ def build_cube(elem: str, nx: int, ny: int, nz: int, bounds):
         L.ref_build_cube.argtypes = [C.c_uint, C.c_uint, C.c_uint, C.c_void_p, C.c_int, C.c_char_p, C.c_int]
         L.ref_mesh_sizes.argtypes = [C.c_void_p]
         L.ref_mesh_get.argtypes = [C.c_void_p] * 6
+        L.ref_mesh_before_sizes.argtypes = [C.c_void_p]
+        L.ref_mesh_before.argtypes = [C.c_void_p] * 2
         _mesh_lib = L
     b = np.ascontiguousarray(bounds, dtype=np.float64)
     err = C.create_string_buffer(1024)
@@ -301,4 +307,9 @@ def build_cube(elem: str, nx: int, ny: int, nz: int, bounds):
     xyz, conn, eid = np.zeros((nn, 3)), np.zeros((ne, npe), dtype=np.uint32), np.zeros(ne, dtype=np.uint32)
     se, sn, sb = np.zeros(ns, dtype=np.uint32), np.zeros(ns, dtype=np.uint8), np.zeros(ns, dtype=np.int16)
     _mesh_lib.ref_mesh_get(xyz.ctypes.data, conn.ctypes.data, eid.ctypes.data, se.ctypes.data, sn.ctypes.data, sb.ctypes.data)
-    return dict(xyz=xyz, conn=conn, elem_id=eid, sides=(se, sn, sb), second_order_requests=int(sz[4]), prepared=bool(sz[5]))
+    bs = np.zeros(2, dtype=np.int64)
+    _mesh_lib.ref_mesh_before_sizes(bs.ctypes.data)
+    xb, cb = np.zeros((int(bs[0]), 3)), np.zeros(int(bs[1]), dtype=np.uint32)
+    _mesh_lib.ref_mesh_before(xb.ctypes.data, cb.ctypes.data)
+    return dict(xyz=xyz, conn=conn, elem_id=eid, sides=(se, sn, sb), second_order_requests=int(sz[4]), prepared=bool(sz[5]),
+                before=(xb, cb.reshape(ne, npe)))

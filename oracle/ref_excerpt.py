@@ -30,6 +30,7 @@ SETS = {
     "mesh": [
         ("src/mesh/mesh_generation.C", r"^void MeshTools::Generation::build_cube\(", FUNC_END, ""),
         ("src/geom/cell_hex27.C", r"^const unsigned int Hex27::side_nodes_map\[", TABLE_END, ""),
+        ("src/mesh/replicated_mesh.C", r"^void ReplicatedMesh::renumber_nodes_and_elements \(\)", FUNC_END, ""),
     ],
     "app": [
         ("src/base/dof_map_constraints.C", r"^void DofMap::build_constraint_matrix \(", FUNC_END, ""),

@@ -6,13 +6,16 @@
 // against a mesh that only RECORDS what the generator does: points with their ids, elements with their node pointers, side and
 // node boundary ids.  tests/test_oracle_ref_mesh.py compares the record with the oracle's build_cube restatement (orc_mesh.cpp)
 // before renumbering: lattice indexing, node coordinates (the reference's own scaling arithmetic), connectivity, boundary sides,
-// and the 24-tet split that precedes all_second_order for TET10.  What this world does NOT do: UnstructuredMesh::all_second_order
-// and MeshBase::prepare_for_use (node renumbering, neighbours, partitioning) — recorded as requests and left to the oracle's
-// restatement, which stays pinned by the reference's published run facts.
+// and the 24-tet split that precedes all_second_order for TET10.  prepare_for_use() here is ONE step of the reference's: its own
+// ReplicatedMesh::renumber_nodes_and_elements (src/mesh/replicated_mesh.C:700-857, excerpted likewise) — the node renumbering in
+// order of first touch and the removal of orphaned lattice nodes that give a build_cube mesh its final numbering; the record can
+// be read before and after it.  What this world does NOT do: UnstructuredMesh::all_second_order (recorded as a request; a TET10
+// mesh is left as the TET4 split, unrenumbered), neighbours, partitioning.
 #ifndef REF_MESH_WORLD_H
 #define REF_MESH_WORLD_H
 #include <array>
 #include <map>
+#include <unordered_set>
 
 #include "libmesh/libmesh_common.h"
 #include "libmesh/enum_elem_type.h"  // the reference's own enum
@@ -32,6 +35,7 @@ class MNode : public Point {  // include/geom/node.h: a point with an id
 public:
   MNode(const Point& p, dof_id_type id) : Point(p), _id(id) {}
   dof_id_type id() const { return _id; }
+  void set_id(dof_id_type i) { _id = i; }
 private:
   dof_id_type _id;
 };
@@ -50,6 +54,19 @@ public:
   void set_node(unsigned int i, Node* n) { if (_nodes.size() <= i) _nodes.resize(i + 1, nullptr); _nodes[i] = n; }
   Node* node_ptr(unsigned int i) const { return _nodes.at(i); }
   unsigned int n_nodes() const { return (unsigned int)_nodes.size(); }
+  // Elem::node_ref_range: the element's nodes by reference
+  struct NodeRefRange {
+    struct iterator {
+      Node* const* p;
+      Node& operator*() const { return **p; }
+      iterator& operator++() { ++p; return *this; }
+      bool operator!=(const iterator& o) const { return p != o.p; }
+    };
+    Node* const* b; Node* const* e;
+    iterator begin() const { return {b}; }
+    iterator end() const { return {e}; }
+  };
+  NodeRefRange node_ref_range() const { return {_nodes.data(), _nodes.data() + _nodes.size()}; }
   IntRange<unsigned short> side_index_range() const { return IntRange<unsigned short>(0, (unsigned short)(_t == HEX27 ? 6 : 0)); }
   // Hex27::build_side_ptr: a QUAD9 over the nodes of Hex27::side_nodes_map[s]
   void build_side_ptr(std::unique_ptr<Elem>& side, const unsigned int s) {
@@ -57,7 +74,6 @@ public:
     side = std::make_unique<Elem>(QUAD9);
     for (unsigned int i = 0; i < 9; ++i) side->set_node(i, _nodes[Hex27::side_nodes_map[s][i]]);
   }
-  bool deleted = false;
 private:
   ElemType _t;
   dof_id_type _id = 0;
@@ -80,6 +96,7 @@ public:
     for (const auto& s : sides) if (s.e == e && s.side == side) out.push_back(s.id);
   }
   void remove(const Elem* e) { for (auto& s : sides) if (s.e == e) s.e = nullptr; }
+  void remove(const Node* n) { for (auto& s : nodes) if (s.n == n) s.n = nullptr; }
   std::string& sideset_name(boundary_id_type id) { return _ss[id]; }
   std::string& nodeset_name(boundary_id_type id) { return _ns[id]; }
   struct Side { const Elem* e; unsigned short side; boundary_id_type id; };
@@ -90,39 +107,78 @@ private:
   std::map<boundary_id_type, std::string> _ss, _ns;
 };
 
+// include/utils/simple_range.h as_range
+template <typename It> struct SimpleRange { It b, e; It begin() const { return b; } It end() const { return e; } };
+template <typename It> SimpleRange<It> as_range(It b, It e) { return {b, e}; }
+
+// storage as in ReplicatedMesh (include/mesh/replicated_mesh.h): _nodes[id], _elements[id], null where deleted
 class UnstructuredMesh {
 public:
-  void clear() { _nodes.clear(); _elems.clear(); _bi = BoundaryInfo(); second_order_requests = 0; prepared = false; }
+  virtual ~UnstructuredMesh() { clear(); }
+  void clear() {
+    for (Node* n : _nodes) delete n;
+    for (Elem* e : _elements) delete e;
+    _nodes.clear(); _elements.clear(); _bi = BoundaryInfo(); _n_nodes = 0;
+    second_order_requests = 0; prepared = false;
+  }
   BoundaryInfo& get_boundary_info() { return _bi; }
   void set_mesh_dimension(unsigned char d) { _dim = d; }
   void set_spatial_dimension(unsigned char) {}
   unsigned int mesh_dimension() const { return _dim; }
   void reserve_elem(dof_id_type n) { reserved_elem = n; }
   void reserve_nodes(dof_id_type n) { reserved_nodes = n; }
-  Node* add_point(const Point& p, const dof_id_type id = (dof_id_type)-1) {
-    _nodes.push_back(std::make_unique<Node>(p, id == (dof_id_type)-1 ? (dof_id_type)_nodes.size() : id));
-    libmesh_error_msg_if(_nodes.back()->id() != _nodes.size() - 1, "nodes are expected in id order");
-    return _nodes.back().get();
+  Node* add_point(const Point& p, const dof_id_type id = (dof_id_type)-1) {  // ReplicatedMesh::add_point: at _nodes[id], or appended
+    const dof_id_type i = id == (dof_id_type)-1 ? (dof_id_type)_nodes.size() : id;
+    if (_nodes.size() <= i) _nodes.resize(i + 1, nullptr);
+    libmesh_error_msg_if(_nodes[i], "node id " << i << " is taken");
+    _nodes[i] = new Node(p, i);
+    ++_n_nodes;
+    return _nodes[i];
   }
-  Node* add_node(std::unique_ptr<Node> n) { _nodes.push_back(std::move(n)); return _nodes.back().get(); }
-  Node* node_ptr(const dof_id_type i) { return _nodes.at(i).get(); }
-  Elem* add_elem(std::unique_ptr<Elem> e) { _elems.push_back(std::move(e)); return _elems.back().get(); }
-  dof_id_type n_elem() const { dof_id_type n = 0; for (const auto& e : _elems) n += !e->deleted; return n; }
-  std::vector<Node*> node_ptr_range() { std::vector<Node*> v; for (auto& n : _nodes) v.push_back(n.get()); return v; }
-  std::vector<Elem*> element_ptr_range() { std::vector<Elem*> v; for (auto& e : _elems) if (!e->deleted) v.push_back(e.get()); return v; }
-  void delete_elem(Elem* e) { e->deleted = true; }
-  // not done here (see the header comment): recorded as requests
-  void all_second_order(const bool = true) { ++second_order_requests; }
+  Node* add_node(std::unique_ptr<Node> n) { _nodes.push_back(n.release()); ++_n_nodes; return _nodes.back(); }
+  Node* node_ptr(const dof_id_type i) { return _nodes.at(i); }
+  Elem* add_elem(std::unique_ptr<Elem> e) {  // ReplicatedMesh::add_elem: at _elements[id]
+    const dof_id_type i = e->id();
+    if (_elements.size() <= i) _elements.resize(i + 1, nullptr);
+    libmesh_error_msg_if(_elements[i], "element id " << i << " is taken");
+    _elements[i] = e.release();
+    return _elements[i];
+  }
+  dof_id_type n_elem() const { dof_id_type n = 0; for (const Elem* e : _elements) n += e != nullptr; return n; }
+  std::vector<Node*> node_ptr_range() { std::vector<Node*> v; for (Node* n : _nodes) if (n) v.push_back(n); return v; }
+  std::vector<Elem*> element_ptr_range() { std::vector<Elem*> v; for (Elem* e : _elements) if (e) v.push_back(e); return v; }
+  void delete_elem(Elem* e) { _elements.at(e->id()) = nullptr; delete e; }  // ReplicatedMesh::delete_elem
+  void all_second_order(const bool = true) { ++second_order_requests; }     // not done here (see the header comment)
   void all_complete_order() { libmesh_not_implemented(); }
-  void prepare_for_use() { prepared = true; }
+  virtual void prepare_for_use() { prepared = true; }
   int second_order_requests = 0;
   bool prepared = false;
   dof_id_type reserved_elem = 0, reserved_nodes = 0;
-  std::vector<std::unique_ptr<Node>> _nodes;
-  std::vector<std::unique_ptr<Elem>> _elems;
-private:
+  std::vector<Node*> _nodes;
+  std::vector<Elem*> _elements;
+  dof_id_type _n_nodes = 0;
+protected:
   BoundaryInfo _bi;
   unsigned char _dim = 0;
+};
+class ReplicatedMesh : public UnstructuredMesh {
+public:
+  // DECLARATION (include/mesh/replicated_mesh.h); the definition is the reference's, src/mesh/replicated_mesh.C:700-857
+  void renumber_nodes_and_elements();
+  // MeshBase::prepare_for_use, as far as this world goes: the numbering step, once the generator is done.  The record before it
+  // is kept for the tests.  (A mesh that still waits for all_second_order is left alone.)
+  void prepare_for_use() override {
+    prepared = true;
+    snapshot_before();
+    if (!second_order_requests) this->renumber_nodes_and_elements();
+  }
+  void snapshot_before();
+  std::vector<double> xyz_before;
+  std::vector<uint32_t> conn_before;
+  void update_parallel_id_counts() {}
+  bool _skip_renumber_nodes_and_elements = false;
+  std::map<const Node*, int> _constraint_rows;
+  struct { bool has_removed_orphaned_nodes = false; } _preparation;
 };
 
 template <typename Output> class FunctionBase { public: virtual ~FunctionBase() = default; };

@@ -6,13 +6,20 @@ namespace libMesh {
 namespace MeshTools { namespace Generation { namespace Private {
 #include "ref_mesh_idx.inc"  // unsigned int idx(type, nx, i, j) and idx(type, nx, ny, i, j, k), mesh_generation.C:81-157
 } } }
-#include "ref_mesh_excerpts.inc"  // void MeshTools::Generation::build_cube(...), mesh_generation.C:317-1938; Hex27::side_nodes_map
+#include "ref_mesh_excerpts.inc"  // void MeshTools::Generation::build_cube(...), mesh_generation.C:317-1938; Hex27::side_nodes_map;
+                                  // void ReplicatedMesh::renumber_nodes_and_elements(), replicated_mesh.C:700-857
+void ReplicatedMesh::snapshot_before() {
+  xyz_before.clear();
+  conn_before.clear();
+  for (const Node* n : _nodes) for (int d = 0; d < 3; ++d) xyz_before.push_back(n ? (*n)(d) : 0.);
+  for (const Elem* e : _elements) if (e) for (unsigned int a = 0; a < e->n_nodes(); ++a) conn_before.push_back(e->node_ptr(a)->id());
+}
 }  // namespace libMesh
 
 using namespace libMesh;
 
 namespace {
-UnstructuredMesh g_mesh;
+ReplicatedMesh g_mesh;
 std::vector<Elem*> g_active;
 }
 
@@ -44,10 +51,16 @@ void ref_mesh_sizes(int64_t* out) {
   out[4] = g_mesh.second_order_requests;
   out[5] = g_mesh.prepared ? 1 : 0;
 }
+// the record as it was when prepare_for_use was called (before the renumbering): sizes (lattice nodes, connectivity entries), arrays
+void ref_mesh_before_sizes(int64_t* out) { out[0] = (int64_t)g_mesh.xyz_before.size() / 3; out[1] = (int64_t)g_mesh.conn_before.size(); }
+void ref_mesh_before(double* xyz, uint32_t* conn) {
+  std::copy(g_mesh.xyz_before.begin(), g_mesh.xyz_before.end(), xyz);
+  std::copy(g_mesh.conn_before.begin(), g_mesh.conn_before.end(), conn);
+}
 // xyz[n_nodes][3]; conn[n_elem][npe] (node ids) in the order the elements were added; elem ids; boundary sides (position of the
 // element in that order, side, id) in the order they were added
 void ref_mesh_get(double* xyz, uint32_t* conn, uint32_t* elem_id, uint32_t* side_elem, uint8_t* side_no, int16_t* side_bid) {
-  for (std::size_t n = 0; n < g_mesh._nodes.size(); ++n) for (int d = 0; d < 3; ++d) xyz[3 * n + d] = (*g_mesh._nodes[n])(d);
+  for (std::size_t n = 0; n < g_mesh._nodes.size(); ++n) for (int d = 0; d < 3; ++d) xyz[3 * n + d] = g_mesh._nodes[n] ? (*g_mesh._nodes[n])(d) : 0.;
   std::map<const Elem*, uint32_t> pos;
   const std::size_t npe = g_active.empty() ? 0 : g_active[0]->n_nodes();
   for (std::size_t e = 0; e < g_active.size(); ++e) {

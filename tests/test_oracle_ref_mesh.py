@@ -1,9 +1,11 @@
 """The oracle's build_cube restatement (oracle/orc_mesh.cpp) against the REFERENCE's own MeshTools::Generation::build_cube
 (src/mesh/mesh_generation.C:317-1938 with its idx() helpers :81-157): the definitions are cut out of the file where it lies and
-run over a mesh that records what the generator does (oracle/ref_mesh/ref_mesh_world.h -> oracle/_ref/libref_mesh.so).  Compared
-BEFORE MeshBase::prepare_for_use (node renumbering) and UnstructuredMesh::all_second_order, which that recording mesh does not
-do: lattice indexing, node coordinates (the reference's own scaling arithmetic — bitwise), connectivity in element order, the
-boundary id of every boundary side, and for TET10 the 24-tet split of every cell.  Runs where /root/reference exists."""
+run over a mesh that records what the generator does (oracle/ref_mesh/ref_mesh_world.h -> oracle/_ref/libref_mesh.so), followed
+by the reference's own ReplicatedMesh::renumber_nodes_and_elements (src/mesh/replicated_mesh.C:700-857), the numbering step of
+prepare_for_use.  Compared BEFORE that step — lattice indexing, node coordinates (the reference's own scaling arithmetic —
+bitwise), connectivity in element order, the boundary id of every boundary side, for TET10 the 24-tet split of every cell — and
+AFTER it: the final node numbering and coordinates of HEX8 / HEX20 / HEX27 / PRISM18 meshes are the reference's.  (TET10's last
+step, UnstructuredMesh::all_second_order, is not run by that world and stays a restatement.)  Runs where /root/reference exists."""
 import numpy as np
 import pytest
 
@@ -16,12 +18,13 @@ BOUNDS = [(-1.0, 1.0, -1.0, 1.0, -1.0, 1.0), (0.0, 1.0, 0.0, 0.3, 0.0, 0.1), (-1
 
 
 def _compacted(r):
-    """prepare_for_use removes the lattice nodes no element uses (HEX20: face and cell centres; the tet split: mid-edge lattice
-    nodes) and closes the gaps in ascending id order."""
-    used = np.unique(r["conn"])
-    rank = np.full(r["xyz"].shape[0], -1, dtype=np.int64)
+    """The generator's record with the lattice nodes no element uses taken out (HEX20: face and cell centres; the tet split:
+    mid-edge lattice nodes) and the gaps closed in ascending id order — the oracle's renumber_nodes=False form."""
+    xb, cb = r["before"]
+    used = np.unique(cb)
+    rank = np.full(xb.shape[0], -1, dtype=np.int64)
     rank[used] = np.arange(len(used))
-    return rank[r["conn"]], r["xyz"][used]
+    return rank[cb], xb[used]
 
 
 @pytest.mark.parametrize("etype", [O.HEX8, O.HEX20, O.HEX27, O.PRISM18, O.TET10], ids=lambda e: NAME[e])
@@ -39,6 +42,17 @@ def test_build_cube_before_renumbering_is_the_references(etype, dims, bounds):
     assert np.array_equal(rx, xyz[: len(rx)]), f"node coordinates differ by {np.abs(rx - xyz[:len(rx)]).max()}"
     if etype != O.TET10:
         assert len(rx) == len(xyz)
+
+
+@pytest.mark.parametrize("etype", [O.HEX8, O.HEX20, O.HEX27, O.PRISM18], ids=lambda e: NAME[e])
+@pytest.mark.parametrize("dims", [(3, 2, 4), (1, 1, 1), (6, 6, 6)], ids=lambda d: "x".join(map(str, d)))
+def test_final_numbering_is_the_references_renumber_nodes_and_elements(etype, dims):
+    """The mesh as an assembly sees it: nodes renumbered in order of first touch by the elements, orphans removed."""
+    for bounds in BOUNDS[:2]:
+        r = R.build_cube(NAME[etype], *dims, bounds)
+        xyz, conn, _ = O.Mesh(etype, *dims, bounds=bounds).arrays()
+        assert np.array_equal(r["conn"], conn) and np.array_equal(r["xyz"], xyz)
+        assert np.array_equal(r["elem_id"], np.arange(len(conn)))
 
 
 @pytest.mark.parametrize("etype", [O.HEX8, O.HEX27], ids=lambda e: NAME[e])
