@@ -71,6 +71,18 @@ def gauss_rule(elem: str, order: int):
     return pts[:n].copy(), w[:n].copy()
 
 
+def has_affine_map(elem: str, node_xyz) -> bool:
+    """Hex8 / Hex20 / Hex27 / Tet10 / Prism18::has_affine_map of the reference (src/geom/cell_*.C)."""
+    L = lib()
+    L.ref_has_affine_map.restype = C.c_int
+    L.ref_has_affine_map.argtypes = [C.c_int, C.c_int, C.c_void_p]
+    X = np.ascontiguousarray(node_xyz, dtype=np.float64).reshape(N_NODES[elem], 3)
+    rc = L.ref_has_affine_map(ELEM[elem], N_NODES[elem], X.ctypes.data)
+    if rc < 0:
+        raise RuntimeError(f"no has_affine_map for {elem}")
+    return bool(rc)
+
+
 def fe_map(elem: str, node_xyz, ref_points, weights, affine: bool):
     """FEMap::init_reference_to_physical_map + FEMap::compute_map (src/fe/fe_map.C) on one element — a 3D cell, or a 2D
     element embedded in space (QUAD4 / QUAD8 / QUAD9 / TRI6: the surface Jacobian) — dict(xyz [nq][3], JxW [nq], jac [nq],
@@ -149,8 +161,8 @@ def load_world(mesh, system, n, bounds, affine=None):
     node_dof = np.zeros((nv, nn), dtype=np.uint32)
     for v in range(nv):
         node_dof[v, conn.reshape(-1)] = ed[:, v * npe:(v + 1) * npe].reshape(-1)
-    if affine is None:
-        affine = np.array([O.has_affine_map(mesh.elem_type, xyz[conn[e]]) for e in range(mesh.n_elem)], dtype=np.uint8)
+    if affine is None:  # the reference's own Hex27::has_affine_map ... decides, element by element
+        affine = np.full(mesh.n_elem, 255, dtype=np.uint8)
     affine = np.ascontiguousarray(affine, dtype=np.uint8)
     rp, ci = system.sparsity()
     b = np.ascontiguousarray(bounds, dtype=np.float64)
@@ -313,3 +325,17 @@ def build_cube(elem: str, nx: int, ny: int, nz: int, bounds):
     _mesh_lib.ref_mesh_before(xb.ctypes.data, cb.ctypes.data)
     return dict(xyz=xyz, conn=conn, elem_id=eid, sides=(se, sn, sb), second_order_requests=int(sz[4]), prepared=bool(sz[5]),
                 before=(xb, cb.reshape(ne, npe)))
+
+
+def distribute_dofs(n_vars: int, n_nodes: int):
+    """DofMap::distribute_local_dofs_var_major of the reference (src/base/dof_map.C:1417-1535) on the mesh of the last build_cube,
+    for one group of n_vars LAGRANGE variables of the element's order: (n_dofs, dof_base [n_nodes]); the dof of variable v at a
+    node is dof_base + v."""
+    _mesh_lib.ref_distribute_dofs.restype = C.c_int64
+    _mesh_lib.ref_distribute_dofs.argtypes = [C.c_uint, C.c_void_p, C.c_char_p, C.c_int]
+    base = np.zeros(n_nodes, dtype=np.uint32)
+    err = C.create_string_buffer(1024)
+    n = _mesh_lib.ref_distribute_dofs(n_vars, base.ctypes.data, err, 1024)
+    if n < 0:
+        raise RuntimeError(err.value.decode())
+    return int(n), base

@@ -76,7 +76,7 @@ struct RefWorldData {
   double bounds[6] = {0, 0, 0, 0, 0, 0};
   std::vector<double> xyz;               // [n_nodes][3]
   std::vector<uint32_t> conn;            // [n_elem][npe]
-  std::vector<uint8_t> affine;           // [n_elem]  Elem::has_affine_map() (the element classes cannot be compiled here)
+  std::vector<uint8_t> affine;           // [n_elem]  255: Elem::has_affine_map() is the element class's own test (the default); 0 / 1 force a branch
   std::vector<uint8_t> node_bmask;       // [n_nodes] bit b: the node lies on a side with boundary id b
   int n_sides = 0;
   std::vector<int16_t> side_bid;         // [n_elem][n_sides] BoundaryInfo's id of a boundary side, -1 for an interior side (empty: none loaded)

@@ -37,7 +37,7 @@ void build_cube(UnstructuredMesh& mesh, const unsigned int nx, const unsigned in
     for (int a = 0; a < w.npe; ++a) std::memcpy(&c[3 * a], &w.xyz[3 * (std::size_t)w.conn[e * w.npe + a]], 3 * sizeof(double));
     mesh._elems.emplace_back(type, 0);
     mesh._elems.back().set_nodes(c.data(), (unsigned int)w.npe);
-    mesh._elems.back().force_affine(w.affine[e] != 0);
+    if (w.affine[e] != 255) mesh._elems.back().force_affine(w.affine[e] != 0);  // 255: the element class's own has_affine_map decides
     mesh._elems.back().set_id((dof_id_type)e);
     if (!w.side_bid.empty()) mesh._elems.back().set_side_boundary_ids(&w.side_bid[e * w.n_sides], (unsigned int)w.n_sides);
   }
@@ -285,7 +285,7 @@ int ref_side_reinit(int elem_type, int n_nodes, const double* node_xyz, int affi
   try {
     Elem elem(static_cast<ElemType>(elem_type), 0);
     elem.set_nodes(node_xyz, (unsigned int)n_nodes);
-    elem.force_affine(affine != 0);
+    if (affine >= 0) elem.force_affine(affine != 0);
     std::unique_ptr<FEBase> fe_face(FEBase::build(3, FEType(fe_order, LAGRANGE)));
     QGauss qface(2, static_cast<Order>(qorder));
     fe_face->attach_quadrature_rule(&qface);

@@ -23,6 +23,11 @@ SETS = {
         ("src/geom/cell_hex27.C", r"^const unsigned int Hex27::side_nodes_map\[", TABLE_END, ""),
         ("src/geom/cell_tet10.C", r"^const unsigned int Tet10::side_nodes_map\[", TABLE_END, ""),
         ("src/geom/cell_prism18.C", r"^const unsigned int Prism18::side_nodes_map\[", TABLE_END, ""),
+        ("src/geom/cell_hex8.C", r"^bool Hex8::has_affine_map\(\) const", FUNC_END, ""),
+        ("src/geom/cell_hex20.C", r"^bool Hex20::has_affine_map\(\) const", FUNC_END, ""),
+        ("src/geom/cell_hex27.C", r"^bool Hex27::has_affine_map\(\) const", FUNC_END, ""),
+        ("src/geom/cell_tet10.C", r"^bool Tet10::has_affine_map\(\) const", FUNC_END, ""),
+        ("src/geom/cell_prism18.C", r"^bool Prism18::has_affine_map\(\) const", FUNC_END, ""),
     ],
     "mesh_idx": [
         ("src/mesh/mesh_generation.C", r"^unsigned int idx\(const ElemType type,", FUNC_END, "inline\n"),
@@ -31,6 +36,7 @@ SETS = {
         ("src/mesh/mesh_generation.C", r"^void MeshTools::Generation::build_cube\(", FUNC_END, ""),
         ("src/geom/cell_hex27.C", r"^const unsigned int Hex27::side_nodes_map\[", TABLE_END, ""),
         ("src/mesh/replicated_mesh.C", r"^void ReplicatedMesh::renumber_nodes_and_elements \(\)", FUNC_END, ""),
+        ("src/base/dof_map.C", r"^void DofMap::distribute_local_dofs_var_major$", FUNC_END, ""),
     ],
     "app": [
         ("src/base/dof_map_constraints.C", r"^void DofMap::build_constraint_matrix \(", FUNC_END, ""),

@@ -9,7 +9,8 @@
 // and the 24-tet split that precedes all_second_order for TET10.  prepare_for_use() here is ONE step of the reference's: its own
 // ReplicatedMesh::renumber_nodes_and_elements (src/mesh/replicated_mesh.C:700-857, excerpted likewise) — the node renumbering in
 // order of first touch and the removal of orphaned lattice nodes that give a build_cube mesh its final numbering; the record can
-// be read before and after it.  What this world does NOT do: UnstructuredMesh::all_second_order (recorded as a request; a TET10
+// be read before and after it.  On the finished mesh the reference's own DofMap::distribute_local_dofs_var_major
+// (src/base/dof_map.C:1417-1535) numbers the dofs of one group of LAGRANGE variables.  What this world does NOT do: UnstructuredMesh::all_second_order (recorded as a request; a TET10
 // mesh is left as the TET4 split, unrenumbered), neighbours, partitioning.
 #ifndef REF_MESH_WORLD_H
 #define REF_MESH_WORLD_H
@@ -36,9 +37,19 @@ public:
   MNode(const Point& p, dof_id_type id) : Point(p), _id(id) {}
   dof_id_type id() const { return _id; }
   void set_id(dof_id_type i) { _id = i; }
+  // DofObject (include/base/dof_object.h), as far as DofMap::distribute_local_dofs_var_major asks: one system, one variable group
+  // of LAGRANGE variables whose order is the element's (one component per node), one processor
+  static const dof_id_type invalid_id = static_cast<dof_id_type>(-1);
+  unsigned int n_comp_group(const unsigned int, const unsigned int) const { return 1; }
+  unsigned int processor_id() const { return 0; }
+  dof_id_type vg_dof_base(const unsigned int, const unsigned int) const { return _dof_base; }
+  void set_vg_dof_base(const unsigned int, const unsigned int, const dof_id_type db) { _dof_base = db; }
 private:
   dof_id_type _id;
+  dof_id_type _dof_base = invalid_id;
 };
+typedef MNode DofObject;
+typedef unsigned short subdomain_id_type;
 #define Node MNode  /* ref_stubs' point.h already names a value-type Node for the FE library; this world's nodes are shared by pointer */
 
 class Elem {
@@ -54,6 +65,11 @@ public:
   void set_node(unsigned int i, Node* n) { if (_nodes.size() <= i) _nodes.resize(i + 1, nullptr); _nodes[i] = n; }
   Node* node_ptr(unsigned int i) const { return _nodes.at(i); }
   unsigned int n_nodes() const { return (unsigned int)_nodes.size(); }
+  Node& node_ref(unsigned int i) const { return *_nodes.at(i); }
+  subdomain_id_type subdomain_id() const { return 0; }
+  unsigned int n_comp_group(const unsigned int, const unsigned int) const { return 0; }  // LAGRANGE: no element dofs
+  dof_id_type vg_dof_base(const unsigned int, const unsigned int) const { return (dof_id_type)-1; }
+  void set_vg_dof_base(const unsigned int, const unsigned int, const dof_id_type) { libmesh_not_implemented(); }
   // Elem::node_ref_range: the element's nodes by reference
   struct NodeRefRange {
     struct iterator {
@@ -147,6 +163,8 @@ public:
   dof_id_type n_elem() const { dof_id_type n = 0; for (const Elem* e : _elements) n += e != nullptr; return n; }
   std::vector<Node*> node_ptr_range() { std::vector<Node*> v; for (Node* n : _nodes) if (n) v.push_back(n); return v; }
   std::vector<Elem*> element_ptr_range() { std::vector<Elem*> v; for (Elem* e : _elements) if (e) v.push_back(e); return v; }
+  std::vector<Elem*> active_local_element_ptr_range() { return element_ptr_range(); }  // one level, one processor
+  std::vector<Node*> local_node_ptr_range() { return node_ptr_range(); }
   void delete_elem(Elem* e) { _elements.at(e->id()) = nullptr; delete e; }  // ReplicatedMesh::delete_elem
   void all_second_order(const bool = true) { ++second_order_requests; }     // not done here (see the header comment)
   void all_complete_order() { libmesh_not_implemented(); }
@@ -179,6 +197,37 @@ public:
   bool _skip_renumber_nodes_and_elements = false;
   std::map<const Node*, int> _constraint_rows;
   struct { bool has_removed_orphaned_nodes = false; } _preparation;
+};
+
+typedef UnstructuredMesh MeshBase;
+
+// include/base/dof_map.h, variable.h: one system with one group of `n` LAGRANGE variables of the same type (what
+// System::add_variable makes of consecutive variables of one FEType, identify_variable_groups = true)
+enum FEFamilyStub { LAGRANGE_FAMILY = 0, SCALAR = 31 };
+struct FETypeStub { FEFamilyStub family = LAGRANGE_FAMILY; };
+class VariableGroup {
+public:
+  explicit VariableGroup(unsigned int n) : _n(n) {}
+  unsigned int n_variables() const { return _n; }
+  const FETypeStub& type() const { return _type; }
+  bool active_on_subdomain(subdomain_id_type) const { return true; }
+private:
+  unsigned int _n;
+  FETypeStub _type;
+};
+class DofMap {
+public:
+  explicit DofMap(unsigned int n_vars) : _group(n_vars) {}
+  unsigned int sys_number() const { return 0; }
+  unsigned int n_variable_groups() const { return 1; }
+  const VariableGroup& variable_group(unsigned int) const { return _group; }
+  unsigned int processor_id() const { return 0; }
+  void distribute_scalar_dofs(dof_id_type&) {}
+  // DECLARATION (include/base/dof_map.h); the definition is the reference's, src/base/dof_map.C:1417-1535
+  void distribute_local_dofs_var_major(dof_id_type& next_free_dof, MeshBase& mesh,
+                                       const std::map<const Node*, std::set<subdomain_id_type>>& constraining_subdomains);
+private:
+  VariableGroup _group;
 };
 
 template <typename Output> class FunctionBase { public: virtual ~FunctionBase() = default; };

@@ -7,7 +7,8 @@ namespace MeshTools { namespace Generation { namespace Private {
 #include "ref_mesh_idx.inc"  // unsigned int idx(type, nx, i, j) and idx(type, nx, ny, i, j, k), mesh_generation.C:81-157
 } } }
 #include "ref_mesh_excerpts.inc"  // void MeshTools::Generation::build_cube(...), mesh_generation.C:317-1938; Hex27::side_nodes_map;
-                                  // void ReplicatedMesh::renumber_nodes_and_elements(), replicated_mesh.C:700-857
+                                  // void ReplicatedMesh::renumber_nodes_and_elements(), replicated_mesh.C:700-857;
+                                  // void DofMap::distribute_local_dofs_var_major(...), dof_map.C:1417-1535
 void ReplicatedMesh::snapshot_before() {
   xyz_before.clear();
   conn_before.clear();
@@ -51,6 +52,27 @@ void ref_mesh_sizes(int64_t* out) {
   out[4] = g_mesh.second_order_requests;
   out[5] = g_mesh.prepared ? 1 : 0;
 }
+// DofMap::distribute_local_dofs_var_major on the mesh of the last ref_build_cube, for one group of n_vars LAGRANGE variables whose
+// order is the element's: dof_base[n_nodes] (the dof of variable v at a node is dof_base + v, DofObject::dof_number with one
+// component per variable); returns n_dofs, or -1
+int64_t ref_distribute_dofs(unsigned int n_vars, uint32_t* dof_base, char* err, int err_len) {
+  try {
+    for (Node* n : g_mesh._nodes) if (n) n->set_vg_dof_base(0, 0, DofObject::invalid_id);
+    DofMap dof_map(n_vars);
+    dof_id_type next_free_dof = 0;
+    dof_map.distribute_local_dofs_var_major(next_free_dof, g_mesh, {});
+    for (std::size_t i = 0; i < g_mesh._nodes.size(); ++i) dof_base[i] = g_mesh._nodes[i] ? g_mesh._nodes[i]->vg_dof_base(0, 0) : (uint32_t)-1;
+    return (int64_t)next_free_dof;
+  } catch (const std::exception& e) {
+    if (err && err_len > 0) {
+      int n = 0;
+      for (const char* c = e.what(); *c && n < err_len - 1; ++c) err[n++] = *c;
+      err[n] = 0;
+    }
+    return -1;
+  }
+}
+
 // the record as it was when prepare_for_use was called (before the renumbering): sizes (lattice nodes, connectivity entries), arrays
 void ref_mesh_before_sizes(int64_t* out) { out[0] = (int64_t)g_mesh.xyz_before.size() / 3; out[1] = (int64_t)g_mesh.conn_before.size(); }
 void ref_mesh_before(double* xyz, uint32_t* conn) {

@@ -89,6 +89,16 @@ int ref_gauss_rule(int dim, int elem_type, int order, int cap, double* pts, doub
   }
 }
 
+// Elem::has_affine_map() of the element class (Hex8 / Hex20 / Hex27 / Tet10 / Prism18::has_affine_map, src/geom/cell_*.C, the
+// reference's own definitions): 1 / 0, or -1 for a type without one here
+int ref_has_affine_map(int elem_type, int n_nodes, const double* node_xyz) {
+  const ElemType t = static_cast<ElemType>(elem_type);
+  if (t != HEX8 && t != HEX20 && t != HEX27 && t != TET10 && t != PRISM18) return -1;
+  Elem elem(t, 0);
+  elem.set_nodes(node_xyz, (unsigned int)n_nodes);
+  return elem.has_affine_map() ? 1 : 0;
+}
+
 // FEMap::init_reference_to_physical_map<dim> + FEMap::compute_map (src/fe/fe_map.C:109-444, :1323-1372 with
 // compute_single_point_map :448-1077 or compute_affine_map :1167-1244) for one element given by its node coordinates — a 3D
 // cell (dim 3) or a 2D element embedded in space (dim 2: the surface-Jacobian branch sqrt(g11 g22 - g12 g21), :810-860) — at
@@ -101,7 +111,7 @@ int ref_fe_map(int dim, int elem_type, int n_nodes, const double* node_xyz, int 
   try {
     Elem elem(static_cast<ElemType>(elem_type), 0);
     elem.set_nodes(node_xyz, (unsigned int)n_nodes);
-    elem.force_affine(affine != 0);
+    if (affine >= 0) elem.force_affine(affine != 0);  // < 0: the element class's own has_affine_map decides
     std::vector<Point> qp;
     std::vector<Real> w(qw, qw + nq);
     for (int p = 0; p < nq; ++p) qp.emplace_back(pts[3 * p], pts[3 * p + 1], pts[3 * p + 2]);

@@ -8,14 +8,24 @@
 #include "libmesh/enum_order.h"
 #include "libmesh/point.h"
 namespace libMesh {
-// DECLARATIONS of the side-node tables of the element classes (include/geom/cell_hex8.h ...: num_sides, nodes_per_side,
-// side_nodes_map).  The table DEFINITIONS are the reference's own, cut out of src/geom/cell_*.C at build time
-// (oracle/ref_excerpt.py, set "fe") and compiled in ref_shim.cpp.
-struct Hex8 { static const int num_sides = 6, nodes_per_side = 4; static const unsigned int side_nodes_map[num_sides][nodes_per_side]; };
-struct Hex20 { static const int num_sides = 6, nodes_per_side = 8; static const unsigned int side_nodes_map[num_sides][nodes_per_side]; };
-struct Hex27 { static const int num_sides = 6, nodes_per_side = 9; static const unsigned int side_nodes_map[num_sides][nodes_per_side]; };
-struct Tet10 { static const int num_sides = 4, nodes_per_side = 6; static const unsigned int side_nodes_map[num_sides][nodes_per_side]; };
-struct Prism18 { static const int num_sides = 5, nodes_per_side = 9; static const unsigned int side_nodes_map[num_sides][nodes_per_side]; };
+// DECLARATIONS of what is taken from the element classes (include/geom/cell_hex8.h ...): the side-node tables (num_sides,
+// nodes_per_side, side_nodes_map) and has_affine_map().  The DEFINITIONS — tables and function bodies — are the reference's own,
+// cut out of src/geom/cell_*.C at build time (oracle/ref_excerpt.py, set "fe") and compiled in ref_shim.cpp.
+class Elem;
+#define REF_CELL_STUB(Name, NS, NPS)                                                                                      \
+  struct Name {                                                                                                            \
+    static const int num_sides = NS, nodes_per_side = NPS;                                                                 \
+    static const unsigned int side_nodes_map[num_sides][nodes_per_side];                                                   \
+    static constexpr Real affine_tol = TOLERANCE * TOLERANCE; /* Elem::affine_tol, include/geom/elem.h:2070 */             \
+    const Elem* _e = nullptr;                                                                                              \
+    const Point& point(const unsigned int i) const;                                                                        \
+    bool has_affine_map() const; /* DECLARATION; the definition is the reference's, cut out of src/geom/cell_*.C */        \
+  };
+REF_CELL_STUB(Hex8, 6, 4)
+REF_CELL_STUB(Hex20, 6, 8)
+REF_CELL_STUB(Hex27, 6, 9)
+REF_CELL_STUB(Tet10, 4, 6)
+REF_CELL_STUB(Prism18, 5, 9)
 
 class Elem {
 public:
@@ -51,8 +61,10 @@ public:
   Order default_order() const { return (_t == HEX8 || _t == QUAD4 || _t == TET4 || _t == PRISM6 || _t == TRI3 || _t == EDGE2) ? FIRST : SECOND; }  // cell_*.h
   bool is_linear() const { return _t == TET4 || _t == TRI3 || _t == EDGE2; }  // elem.h: constant Jacobian by type
   bool infinite() const { return false; }
-  bool has_affine_map() const { return _affine; }
-  void force_affine(bool a) { _affine = a; }
+  // Elem::has_affine_map: the element class's own test (Hex27::has_affine_map ...), unless a caller forces a branch of compute_map
+  bool has_affine_map() const;
+  void force_affine(bool a) { _affine = a ? 1 : 0; }
+  void auto_affine() { _affine = -1; }
   unsigned int local_singular_node(const Point&, Real = 0.) const { return invalid_uint; }
   bool on_reference_element(const Point&, Real = 0.) const { return true; }
   Real hmax() const { return 1.; }
@@ -102,10 +114,23 @@ public:
 private:
   ElemType _t;
   unsigned int _p;
-  bool _affine = false;
+  int _affine = -1;
   dof_id_type _id = 0;
   std::vector<short> _side_bid;
   std::vector<Node> _nodes;
 };
+#define REF_CELL_POINT(Name) inline const Point& Name::point(const unsigned int i) const { return _e->point(i); }
+REF_CELL_POINT(Hex8) REF_CELL_POINT(Hex20) REF_CELL_POINT(Hex27) REF_CELL_POINT(Tet10) REF_CELL_POINT(Prism18)
+inline bool Elem::has_affine_map() const {
+  if (_affine >= 0) return _affine != 0;
+  switch (_t) {
+    case HEX8: { Hex8 c; c._e = this; return c.has_affine_map(); }
+    case HEX20: { Hex20 c; c._e = this; return c.has_affine_map(); }
+    case HEX27: { Hex27 c; c._e = this; return c.has_affine_map(); }
+    case TET10: { Tet10 c; c._e = this; return c.has_affine_map(); }
+    case PRISM18: { Prism18 c; c._e = this; return c.has_affine_map(); }
+    default: return false;  // sides and the like: the general branch is always right
+  }
+}
 }  // namespace libMesh
 #endif

@@ -47,7 +47,7 @@ template <typename... Args> inline void libmesh_ignore(const Args&...) {}
 template <typename Tnew, typename Told> inline Tnew cast_ptr(Told* p) { return static_cast<Tnew>(p); }
 template <typename Tnew, typename Told> inline Tnew cast_int(Told v) { return static_cast<Tnew>(v); }
 inline constexpr Real operator""_R(long double x) { return static_cast<Real>(x); }  // libmesh_common.h: Real literals
-static const Real TOLERANCE = 1.e-6;
+static constexpr Real TOLERANCE = 1.e-6;  // libmesh_common.h
 static std::ostream& out = std::cout;  // libMesh::out / libMesh::err (include/base/libmesh_base.h)
 static std::ostream& err = std::cerr;
 static const unsigned int invalid_uint = static_cast<unsigned int>(-1);

@@ -22,6 +22,10 @@ public:
   Real norm_sq() const { return c[0] * c[0] + c[1] * c[1] + c[2] * c[2]; }
   bool operator==(const Point& o) const { return c[0] == o.c[0] && c[1] == o.c[1] && c[2] == o.c[2]; }
   Point cross(const Point& o) const { return Point(c[1] * o.c[2] - c[2] * o.c[1], c[2] * o.c[0] - c[0] * o.c[2], c[0] * o.c[1] - c[1] * o.c[0]); }
+  // TypeVector::l1_norm (type_vector.h:961-971) and relative_fuzzy_equals (include/utils/fuzzy_equals.h:95-112): |a - b|_1 <= tol (|a|_1 + |b|_1)
+  Real l1_norm() const { Real ret{}; for (int i = 0; i < 3; ++i) ret += std::abs(c[i]); return ret; }
+  bool absolute_fuzzy_equals(const Point& rhs, Real tol = TOLERANCE) const { return (*this - rhs).l1_norm() <= tol; }
+  bool relative_fuzzy_equals(const Point& rhs, Real tol = TOLERANCE) const { return absolute_fuzzy_equals(rhs, tol * (l1_norm() + rhs.l1_norm())); }
   Point unit() const { const Real l = norm(); return Point(c[0] / l, c[1] / l, c[2] / l); }       // TypeVector::unit (type_vector.h)
   Real norm() const { return std::sqrt(c[0] * c[0] + c[1] * c[1] + c[2] * c[2]); }
   Point& operator+=(const Point& o) { c[0] += o.c[0]; c[1] += o.c[1]; c[2] += o.c[2]; return *this; }

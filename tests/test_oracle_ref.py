@@ -319,3 +319,24 @@ def test_hanging_node_coefficients_of_the_test_meshes_are_the_reference_side_sha
     # HEX8: the middle of an edge / of a face of the bilinear QUAD4
     assert np.array_equal(R.shapes("QUAD4", [[0.0, -1.0, 0.0]])[0][:, 0], [0.5, 0.5, 0.0, 0.0])
     assert np.array_equal(R.shapes("QUAD4", [[0.0, 0.0, 0.0]])[0][:, 0], [0.25, 0.25, 0.25, 0.25])
+
+
+@needs_ref
+@pytest.mark.parametrize("elem", sorted(ORC))
+def test_has_affine_map_is_the_element_classes_own_test(elem):
+    """Hex8 / Hex20 / Hex27 / Tet10 / Prism18::has_affine_map (src/geom/cell_*.C; the reference's own definitions, cut out of the
+    element classes and compiled over relative_fuzzy_equals as include/utils/fuzzy_equals.h states it) decide which branch of
+    FEMap::compute_map an element takes.  Plain, sheared (SkewFunc: still affine) and perturbed elements, with perturbations on
+    either side of the tolerance affine_tol = TOLERANCE^2 = 1e-12."""
+    n_affine = n_general = 0
+    for skew in (None, (0, 0.0, 0), (1, 0.03, 3), (1, 1e-9, 3), (1, 1e-11, 4), (1, 1e-12, 5), (1, 1e-13, 3), (1, 1e-15, 6)):
+        m = O.Mesh(ORC[elem], 2, 2, 2, (-1, 1, -1, 1, -1, 1))
+        if skew:
+            m.skew(*skew)
+        xyz, conn, _ = m.arrays()
+        for e in range(m.n_elem):
+            a, b = O.has_affine_map(ORC[elem], xyz[conn[e]]), R.has_affine_map(elem, xyz[conn[e]])
+            assert a == b, (skew, e)
+            n_affine += b
+            n_general += not b
+    assert n_affine > 0 and n_general > 0

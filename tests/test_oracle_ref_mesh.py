@@ -76,3 +76,21 @@ def test_boundary_sides_are_the_references(etype):
 def test_reference_rejects_what_it_rejects():
     with pytest.raises(RuntimeError, match="Unrecognized 3D element type"):
         R.build_cube("QUAD9", 2, 2, 2, BOUNDS[0])
+
+
+@pytest.mark.parametrize("etype", [O.HEX8, O.HEX20, O.HEX27, O.PRISM18], ids=lambda e: NAME[e])
+@pytest.mark.parametrize("n_vars", [1, 3])
+def test_dof_numbering_is_the_references_distribute_local_dofs_var_major(etype, n_vars):
+    """DofMap::distribute_local_dofs_var_major (src/base/dof_map.C:1417-1535, the reference's own definition) on the reference's
+    own mesh: nodes get their dof base in order of first touch by the elements; one variable group of n_vars LAGRANGE variables
+    (what add_variable makes of u, v, w in ex6), so variable v of a node sits at base + v.  The oracle's node bases, n_dofs and
+    the element dof lists DofMap::dof_indices returns (variable-major) are those."""
+    for dims in [(3, 2, 4), (1, 1, 1), (5, 4, 3)]:
+        r = R.build_cube(NAME[etype], *dims, BOUNDS[1])
+        n_dofs, base = R.distribute_dofs(n_vars, len(r["xyz"]))
+        m = O.Mesh(etype, *dims, bounds=BOUNDS[1])
+        s = O.System(m, n_vars)
+        ed, nb, fd = s.dofs()
+        assert n_dofs == s.n_dofs == n_vars * m.n_nodes and fd.tolist() == [0, n_dofs]
+        assert np.array_equal(nb, base)
+        assert np.array_equal(ed, np.concatenate([base[r["conn"]] + v for v in range(n_vars)], axis=1))
