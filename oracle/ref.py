@@ -339,3 +339,15 @@ def distribute_dofs(n_vars: int, n_nodes: int):
     if n < 0:
         raise RuntimeError(err.value.decode())
     return int(n), base
+
+
+def partition_linear(n_parts: int, n_elem: int):
+    """LinearPartitioner::partition_range of the reference (src/partitioning/linear_partitioner.C:36-117) over all elements of the
+    mesh of the last build_cube: elem_pid [n_elem]."""
+    _mesh_lib.ref_partition_linear.restype = C.c_int
+    _mesh_lib.ref_partition_linear.argtypes = [C.c_uint, C.c_void_p, C.c_char_p, C.c_int]
+    pid = np.zeros(n_elem, dtype=np.int32)
+    err = C.create_string_buffer(1024)
+    if _mesh_lib.ref_partition_linear(n_parts, pid.ctypes.data, err, 1024) != 0:
+        raise RuntimeError(err.value.decode())
+    return pid

@@ -37,6 +37,7 @@ SETS = {
         ("src/geom/cell_hex27.C", r"^const unsigned int Hex27::side_nodes_map\[", TABLE_END, ""),
         ("src/mesh/replicated_mesh.C", r"^void ReplicatedMesh::renumber_nodes_and_elements \(\)", FUNC_END, ""),
         ("src/base/dof_map.C", r"^void DofMap::distribute_local_dofs_var_major$", FUNC_END, ""),
+        ("src/partitioning/linear_partitioner.C", r"^void LinearPartitioner::partition_range\(", FUNC_END, ""),
     ],
     "app": [
         ("src/base/dof_map_constraints.C", r"^void DofMap::build_constraint_matrix \(", FUNC_END, ""),

@@ -10,7 +10,8 @@
 // ReplicatedMesh::renumber_nodes_and_elements (src/mesh/replicated_mesh.C:700-857, excerpted likewise) — the node renumbering in
 // order of first touch and the removal of orphaned lattice nodes that give a build_cube mesh its final numbering; the record can
 // be read before and after it.  On the finished mesh the reference's own DofMap::distribute_local_dofs_var_major
-// (src/base/dof_map.C:1417-1535) numbers the dofs of one group of LAGRANGE variables.  What this world does NOT do: UnstructuredMesh::all_second_order (recorded as a request; a TET10
+// (src/base/dof_map.C:1417-1535) numbers the dofs of one group of LAGRANGE variables, and its own LinearPartitioner::partition_range
+// (src/partitioning/linear_partitioner.C:36-117) assigns the elements to ranks.  What this world does NOT do: UnstructuredMesh::all_second_order (recorded as a request; a TET10
 // mesh is left as the TET4 split, unrenumbered), neighbours, partitioning.
 #ifndef REF_MESH_WORLD_H
 #define REF_MESH_WORLD_H
@@ -67,6 +68,8 @@ public:
   unsigned int n_nodes() const { return (unsigned int)_nodes.size(); }
   Node& node_ref(unsigned int i) const { return *_nodes.at(i); }
   subdomain_id_type subdomain_id() const { return 0; }
+  unsigned int& processor_id() { return _pid; }  // DofObject::processor_id
+  unsigned int processor_id() const { return _pid; }
   unsigned int n_comp_group(const unsigned int, const unsigned int) const { return 0; }  // LAGRANGE: no element dofs
   dof_id_type vg_dof_base(const unsigned int, const unsigned int) const { return (dof_id_type)-1; }
   void set_vg_dof_base(const unsigned int, const unsigned int, const dof_id_type) { libmesh_not_implemented(); }
@@ -93,6 +96,7 @@ public:
 private:
   ElemType _t;
   dof_id_type _id = 0;
+  unsigned int _pid = 0;
   std::vector<Node*> _nodes;
 };
 class Polygon : public Elem { public: using Elem::Elem; };
@@ -131,6 +135,12 @@ template <typename It> SimpleRange<It> as_range(It b, It e) { return {b, e}; }
 class UnstructuredMesh {
 public:
   virtual ~UnstructuredMesh() { clear(); }
+  // as far as LinearPartitioner::partition_range asks: a serial (replicated, one process) mesh
+  typedef std::vector<Elem*>::iterator element_iterator;
+  bool is_serial() const { return true; }
+  struct Comm { template <typename S> void set_union(S&) const {} };
+  Comm comm() const { return Comm(); }
+  Elem* query_elem_ptr(const dof_id_type i) { return i < _elements.size() ? _elements[i] : nullptr; }
   void clear() {
     for (Node* n : _nodes) delete n;
     for (Elem* e : _elements) delete e;
@@ -228,6 +238,15 @@ public:
                                        const std::map<const Node*, std::set<subdomain_id_type>>& constraining_subdomains);
 private:
   VariableGroup _group;
+};
+
+typedef unsigned int processor_id_type;
+// include/partitioning/linear_partitioner.h: DECLARATION; the definition of partition_range is the reference's,
+// src/partitioning/linear_partitioner.C:36-117
+class LinearPartitioner {
+public:
+  void partition_range(MeshBase& mesh, MeshBase::element_iterator it, MeshBase::element_iterator end, const unsigned int n);
+  void single_partition_range(MeshBase::element_iterator it, MeshBase::element_iterator end) { for (; it != end; ++it) (*it)->processor_id() = 0; }  // partitioner.C
 };
 
 template <typename Output> class FunctionBase { public: virtual ~FunctionBase() = default; };

@@ -8,7 +8,8 @@ namespace MeshTools { namespace Generation { namespace Private {
 } } }
 #include "ref_mesh_excerpts.inc"  // void MeshTools::Generation::build_cube(...), mesh_generation.C:317-1938; Hex27::side_nodes_map;
                                   // void ReplicatedMesh::renumber_nodes_and_elements(), replicated_mesh.C:700-857;
-                                  // void DofMap::distribute_local_dofs_var_major(...), dof_map.C:1417-1535
+                                  // void DofMap::distribute_local_dofs_var_major(...), dof_map.C:1417-1535;
+                                  // void LinearPartitioner::partition_range(...), linear_partitioner.C:36-117
 void ReplicatedMesh::snapshot_before() {
   xyz_before.clear();
   conn_before.clear();
@@ -63,6 +64,23 @@ int64_t ref_distribute_dofs(unsigned int n_vars, uint32_t* dof_base, char* err, 
     dof_map.distribute_local_dofs_var_major(next_free_dof, g_mesh, {});
     for (std::size_t i = 0; i < g_mesh._nodes.size(); ++i) dof_base[i] = g_mesh._nodes[i] ? g_mesh._nodes[i]->vg_dof_base(0, 0) : (uint32_t)-1;
     return (int64_t)next_free_dof;
+  } catch (const std::exception& e) {
+    if (err && err_len > 0) {
+      int n = 0;
+      for (const char* c = e.what(); *c && n < err_len - 1; ++c) err[n++] = *c;
+      err[n] = 0;
+    }
+    return -1;
+  }
+}
+
+// LinearPartitioner::partition_range over all elements of the mesh of the last ref_build_cube: elem_pid[n_elem]
+int ref_partition_linear(unsigned int n_parts, int32_t* elem_pid, char* err, int err_len) {
+  try {
+    LinearPartitioner lp;
+    lp.partition_range(g_mesh, g_mesh._elements.begin(), g_mesh._elements.end(), n_parts);
+    for (std::size_t e = 0; e < g_mesh._elements.size(); ++e) elem_pid[e] = (int32_t)g_mesh._elements[e]->processor_id();
+    return 0;
   } catch (const std::exception& e) {
     if (err && err_len > 0) {
       int n = 0;
