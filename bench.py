@@ -889,13 +889,95 @@ def multi_parity(F, ctx, da, prob, P, local, params, torch, dist):
 
 
 # ---- the reference arm ------------------------------------------------------------------------------------------------
+def _ref_rank(w, n_ranks, etype, n, bounds, order, warmup, steps, barrier, out):
+    """One emulated MPI rank of the reference (a fresh process): the replicated mesh, its slab of elements (LinearPartitioner
+    blocks), the nodes they touch, local dofs and pattern from the oracle, and the reference's own assemble_poisson
+    (oracle/_ref/libref_app_fast.so) over them."""
+    try:
+        from oracle import oracle as O
+        from oracle import ref as R
+
+        gm = O.Mesh(etype, n, n, n, bounds=bounds, fast=True)
+        xyz, conn, mask = gm.arrays()
+        del gm
+        ne = conn.shape[0]
+        blk = ne // n_ranks
+        e0, e1 = (0 if w == 0 else blk * w + ne % n_ranks), blk * (w + 1) + ne % n_ranks
+        nodes = np.unique(conn[e0:e1])
+        lconn = np.searchsorted(nodes, conn[e0:e1]).astype(np.uint32)
+        m = O.Mesh.from_arrays(etype, xyz[nodes], lconn, mask[nodes], fast=True)
+        s = O.System(m, 1)
+        s.add_dirichlet()
+        s.build_sparsity()
+        R.use_fast(True)
+        nnz, nd = R.load_world(m, s, (0, 0, 0), (0.0,) * 6)  # has_affine_map: the element class's own test, per element
+        times = []
+        barrier.wait()
+        for i in range(warmup + steps):
+            R.assemble_ex4(order, nnz, nd)
+            if i >= warmup:
+                times.append(R.last_solve_seconds())
+        out.put((w, e1 - e0, times, None))
+    except Exception as e:  # reported by the parent
+        try:
+            barrier.abort()
+        except Exception:
+            pass
+        out.put((w, 0, [], f"{type(e).__name__}: {e}"[:300]))
+
+
+def reference_code_ranks(args, warmup: int = 1, steps: int = 2):
+    """The reference's OWN assembly function on all host cores, the way libMesh uses them: one process per core, each assembling its
+    contiguous block of the mesh's elements (LinearPartitioner) with assemble_poisson of introduction_ex4.C compiled where it lies
+    (oracle/_ref, -O3 build) — local matrix and right-hand side per process; the exchange of ghost rows that follows in an MPI run
+    is NOT counted.  Rate = elements of the whole job / the slowest process's mean step time."""
+    import multiprocessing as mp
+
+    from oracle import oracle as O
+    from oracle import ref as R
+
+    if args.problem != "poisson" or not R.app_available(fast=True):
+        return None
+    n_ranks = os.cpu_count() or 1
+    n, b, _ = problem_dims(args)
+    etype = ELEM[args.elem]
+    n_elem = {10: 24, 18: 2}.get(etype, 1) * n ** 3
+    ctx = mp.get_context("spawn")  # fresh processes: nothing of this one's OpenMP or CUDA state is inherited
+    barrier, out = ctx.Barrier(n_ranks), ctx.Queue()
+    order = 1 if args.elem == "hex8" else 2
+    procs = [ctx.Process(target=_ref_rank, args=(w, n_ranks, etype, n, b, order, warmup, steps, barrier, out)) for w in range(n_ranks)]
+    t0 = time.perf_counter()
+    for p in procs:
+        p.start()
+    res = [out.get(timeout=900) for _ in procs]
+    for p in procs:
+        p.join(timeout=60)
+    errs = [r[3] for r in res if r[3]]
+    if errs:
+        return {"unavailable": errs[0]}
+    slowest = max(float(np.mean(r[2])) for r in res)
+    if sum(r[1] for r in res) != n_elem:
+        return {"unavailable": f"the ranks assembled {sum(r[1] for r in res)} of {n_elem} elements"}
+    return {"value": n_elem / slowest, "unit": "elements/s", "cores": n_ranks, "kind": "reference",
+            "sample": f"{steps} steps after {warmup} warm-up: assemble_poisson of introduction_ex4.C in {n_ranks} processes, each on its block of "
+                      f"{n_elem // n_ranks} of the {n_elem} elements (build_cube {n}^3), slowest process {slowest:.2f} s per step",
+            "wall_s_with_setup": round(time.perf_counter() - t0, 1),
+            "note": "ghost-row exchange of an MPI run not counted; stub mesh / matrix world of oracle/ref_app/ref_world.h"}
+
+
 def run_reference(args):
-    """The reference's CPU path (oracle port: the reference itself cannot be compiled here) on all host threads, on the
-    SAME configuration as our arm: every step is one assembly of the whole mesh."""
+    """The reference's CPU path on all host cores, on the SAME configuration as our arm.  Two implementations are run and the
+    FASTER one is the arm's value: the oracle port (CPU restatement, OpenMP over elements; every step one assembly of the whole
+    mesh) and the reference's own code (oracle/_ref: assemble_poisson of introduction_ex4.C compiled where it lies, one process per
+    core over element blocks, a bounded number of steps), reported beside it in cpu_baseline."""
     rank = int(os.environ.get("RANK", "0"))
     if rank != 0:
         return
     threads = os.cpu_count() or 1
+    try:
+        ref_code = reference_code_ranks(args)
+    except Exception as e:
+        ref_code = {"unavailable": f"{type(e).__name__}: {e}"[:300]}
     O, m, s = oracle_system(args, fast=True)
     for _ in range(max(args.warmup, 1)):
         oracle_assemble(O, s, args, threads)
@@ -905,13 +987,19 @@ def run_reference(args):
     dt = (time.perf_counter() - t0) / args.steps
     value = m.n_elem / dt
     sample = f"each step = one assembly of the full job ({m.n_elem} elements), {threads} OpenMP threads"
+    kind, cores = "port", threads
+    port = {"value": value, "unit": "elements/s", "cores": threads, "sample": sample}
+    if ref_code and ref_code.get("value", 0.0) > value:  # the arm's value is the faster CPU implementation
+        value, dt, kind, cores, sample = ref_code["value"], m.n_elem / ref_code["value"], "reference", ref_code["cores"], ref_code["sample"]
     print(json.dumps({
         "impl": "reference", "metric": metric_name(args), "value": value, "unit": "elements/s", "n_gpus": args.gpus, "steps": args.steps,
         "warmup": args.warmup, "ms_per_step": dt * 1e3, "higher_is_better": True, "scaling": "strong", "vs_baseline": None,
         "dtype": "f64", "data": "synthetic",
         "config": {"workload": workload_name(args), "n_elem": int(m.n_elem), "n_dofs": int(s.n_dofs), "nnz": int(s.nnz),
-                   "note": "CPU assembly loop of the reference (oracle port, g++ -O3 -march=x86-64-v3, OpenMP over elements)"},
-        "cpu_baseline": {"value": value, "unit": "elements/s", "cores": threads, "kind": "port", "sample": sample},
+                   "note": "CPU assembly loop of the reference: the faster of the oracle port (g++ -O3 -march=x86-64-v3, OpenMP over elements) "
+                           "and the reference's own code from oracle/_ref (one process per core over element blocks)"},
+        "cpu_baseline": {"value": value, "unit": "elements/s", "cores": cores, "kind": kind, "sample": sample, "port": port,
+                         "reference_code": ref_code},
         "e2e": {"value": value, "unit": "elements/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
         "gpu_launches": 0,
     }))
