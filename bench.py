@@ -912,7 +912,7 @@ def _ref_rank(w, n_ranks, etype, n, bounds, order, warmup, steps, barrier, out):
         R.use_fast(True)
         nnz, nd = R.load_world(m, s, (0, 0, 0), (0.0,) * 6)  # has_affine_map: the element class's own test, per element
         times = []
-        barrier.wait()
+        barrier.wait(timeout=180)
         for i in range(warmup + steps):
             R.assemble_ex4(order, nnz, nd)
             if i >= warmup:
@@ -949,9 +949,16 @@ def reference_code_ranks(args, warmup: int = 1, steps: int = 2):
     t0 = time.perf_counter()
     for p in procs:
         p.start()
-    res = [out.get(timeout=900) for _ in procs]
+    res, deadline = [], t0 + 300.0  # a data point beside the port: bounded, and never allowed to stall the arm
+    try:
+        for _ in procs:
+            res.append(out.get(timeout=max(deadline - time.perf_counter(), 1.0)))
+    except Exception:
+        res.append((-1, 0, [], "a rank process did not answer within 300 s"))
     for p in procs:
-        p.join(timeout=60)
+        p.join(timeout=5)
+        if p.is_alive():
+            p.terminate()
     errs = [r[3] for r in res if r[3]]
     if errs:
         return {"unavailable": errs[0]}
