@@ -3,7 +3,7 @@
 # (called by oracle/Makefile; TEST INFRASTRUCTURE).  The reference's sources are compiled WHERE THEY LIE under <reference root>:
 #   _ref/inc/libmesh/<name>.h, _ref/inc_app/libmesh/<name>.h   one-line forwarders to the reference's own self-contained headers
 #                                                              (or to the stub world); no reference source is copied
-#   _ref/gen/                                                  a few function / table DEFINITIONS cut by ref_excerpt.py out of files
+#   $GEN/                                                  a few function / table DEFINITIONS cut by ref_excerpt.py out of files
 #                                                              that cannot be compiled whole: a build intermediate, removed below
 # suffix ""      -O2 -ffp-contract=off   the bitwise checker of the oracle (operation order as written, no FMA contraction)
 # suffix "_fast" -O3 -march=x86-64-v3    the same code as a timed data point beside the CPU baseline (bench.py)
@@ -12,8 +12,9 @@ REF="$1"; SFX="$2"; OPT="$3"
 CXX="${CXX_REF:-/usr/bin/g++}"
 cd "$(dirname "$0")"
 OBJ="_ref/obj$SFX"
-mkdir -p _ref/inc/libmesh _ref/inc_app/libmesh _ref/gen "$OBJ"
-trap 'rm -rf _ref/gen "$OBJ"' EXIT
+GEN="_ref/gen$SFX"
+mkdir -p _ref/inc/libmesh _ref/inc_app/libmesh "$GEN" "$OBJ"
+trap 'rm -rf "$GEN" "$OBJ"' EXIT
 
 REF_HDR="enums/enum_elem_type.h enums/enum_order.h enums/enum_fe_family.h enums/enum_quadrature_type.h fe/fe_lagrange_shape_1D.h
  quadrature/quadrature.h quadrature/quadrature_gauss.h quadrature/quadrature_conical.h quadrature/quadrature_gm.h
@@ -36,16 +37,16 @@ for h in $APP_WORLD_HDR; do echo '#include "ref_world.h"' > _ref/inc_app/libmesh
 echo '#include "../../../ref_app/libmesh_config.h"' > _ref/inc_app/libmesh/libmesh_config.h
 
 # ---- libref_fe: shape functions, quadrature, FEMap (volume and face maps), exact_solution
-python3 ref_excerpt.py "$REF" fe _ref/gen/ref_fe_excerpts.inc
+python3 ref_excerpt.py "$REF" fe $GEN/ref_fe_excerpts.inc
 SRCS=""
 for s in $REF_SRC; do SRCS="$SRCS $REF/src/$s"; done
-$CXX -std=c++17 $OPT -fPIC -shared -I_ref/inc -Iref_stubs -I_ref/gen -o _ref/libref_fe$SFX.so ref_shim.cpp $SRCS \
+$CXX -std=c++17 $OPT -fPIC -shared -I_ref/inc -Iref_stubs -I$GEN -o _ref/libref_fe$SFX.so ref_shim.cpp $SRCS \
     "$REF/examples/introduction/introduction_ex3/exact_solution.C"
 
 # ---- libref_app: the examples (introduction_ex4.C: assemble_poisson and main; systems_of_equations_ex6.C: LinearElasticity::assemble),
 # the reference's DenseMatrix sources and its DofMap constraint functions over the stub world of ref_app/ref_world.h
-APP="$CXX -std=c++17 $OPT -fPIC -c -I_ref/inc_app -Iref_app -I_ref/gen -I_ref/inc -Iref_stubs"
-python3 ref_excerpt.py "$REF" app _ref/gen/ref_excerpts.inc
+APP="$CXX -std=c++17 $OPT -fPIC -c -I_ref/inc_app -Iref_app -I$GEN -I_ref/inc -Iref_stubs"
+python3 ref_excerpt.py "$REF" app $GEN/ref_excerpts.inc
 $APP -o $OBJ/app_shim.o ref_app_shim.cpp
 $APP -Dmain=ref_ex4_main -o $OBJ/ex4.o "$REF/examples/introduction/introduction_ex4/introduction_ex4.C"
 $APP -I"$REF/examples/systems_of_equations/systems_of_equations_ex6" -o $OBJ/ex6.o ref_ex6_glue.cpp
@@ -56,7 +57,7 @@ $CXX -shared -o _ref/libref_app$SFX.so $OBJS -L_ref -lref_fe$SFX -Wl,-rpath,'$OR
 # ---- libref_mesh (checker build only): the reference's own MeshTools::Generation::build_cube over the recording mesh of
 # ref_mesh/ref_mesh_world.h
 if [ -z "$SFX" ]; then
-  python3 ref_excerpt.py "$REF" mesh_idx _ref/gen/ref_mesh_idx.inc
-  python3 ref_excerpt.py "$REF" mesh _ref/gen/ref_mesh_excerpts.inc
-  $CXX -std=c++17 $OPT -fPIC -shared -I_ref/inc -Iref_stubs -Iref_mesh -I_ref/gen -o _ref/libref_mesh.so ref_mesh_shim.cpp
+  python3 ref_excerpt.py "$REF" mesh_idx $GEN/ref_mesh_idx.inc
+  python3 ref_excerpt.py "$REF" mesh $GEN/ref_mesh_excerpts.inc
+  $CXX -std=c++17 $OPT -fPIC -shared -I_ref/inc -Iref_stubs -Iref_mesh -I$GEN -o _ref/libref_mesh.so ref_mesh_shim.cpp
 fi
