@@ -139,6 +139,8 @@ def app():
         L.ref_world_solve_seconds.argtypes = []
         L.ref_world_untouched_entries.restype = C.c_int64
         L.ref_world_untouched_entries.argtypes = []
+        L.ref_world_set_constraint_rows.restype = C.c_int
+        L.ref_world_set_constraint_rows.argtypes = [C.c_int64] + [C.c_void_p] * 5
         L.ref_world_results.restype = C.c_int64
         L.ref_world_results.argtypes = [C.c_void_p] * 4
         L.ref_side_reinit.restype = C.c_int
@@ -150,9 +152,19 @@ def app():
     return _apps[_fast]
 
 
-def load_world(mesh, system, n, bounds, affine=None):
+def load_constraint_rows(dofs, row_ptr, cols, coefs, values):
+    """Constraint rows for the loaded world, given as such (the argument list of feasm_set_constraint_rows /
+    oracle.constraints.ConstraintRows.arrays()): hanging nodes, and Dirichlet rows as empty rows with a value."""
+    a = [np.ascontiguousarray(dofs, dtype=np.uint32), np.ascontiguousarray(row_ptr, dtype=np.uint64), np.ascontiguousarray(cols, dtype=np.uint32),
+         np.ascontiguousarray(coefs, dtype=np.float64), np.ascontiguousarray(values, dtype=np.float64)]
+    pad = [np.zeros(1, dtype=x.dtype) if x.size == 0 else x for x in a]
+    app().ref_world_set_constraint_rows(len(a[0]), *[x.ctypes.data for x in pad])
+
+
+def load_world(mesh, system, n, bounds, affine=None, pattern=None):
     """Hands the stub world the integer structures of an oracle Mesh / System (oracle.py): the mesh that build_cube(n, n, n,
-    bounds) is going to be asked for, the dof of every (variable, node), and the sparsity pattern."""
+    bounds) is going to be asked for, the dof of every (variable, node), and the sparsity pattern (the system's own, or the
+    one given: with constraint rows the Graph holds the couplings DofMap::find_connected_dofs adds)."""
     from . import oracle as O
 
     xyz, conn, mask = mesh.arrays()
@@ -164,7 +176,8 @@ def load_world(mesh, system, n, bounds, affine=None):
     if affine is None:  # the reference's own Hex27::has_affine_map ... decides, element by element
         affine = np.full(mesh.n_elem, 255, dtype=np.uint8)
     affine = np.ascontiguousarray(affine, dtype=np.uint8)
-    rp, ci = system.sparsity()
+    rp, ci = system.sparsity() if pattern is None else pattern
+    rp, ci = np.ascontiguousarray(rp, dtype=np.uint64), np.ascontiguousarray(ci, dtype=np.uint32)
     b = np.ascontiguousarray(bounds, dtype=np.float64)
     nx, ny, nz = (n, n, n) if np.isscalar(n) else n
     app().ref_world_load(ELEM[_ORC_TO_LIBMESH[mesh.elem_type]], npe, nx, ny, nz, b.ctypes.data, nn, xyz.ctypes.data, mesh.n_elem, conn.ctypes.data,

@@ -87,6 +87,11 @@ struct RefWorldData {
   // sparsity pattern
   std::vector<uint64_t> row_ptr;
   std::vector<uint32_t> col_idx;
+  // constraint rows given as such (hanging nodes, and Dirichlet rows as empty rows with a value): u_dof = sum coef u_col + val;
+  // what DofMap::create_dof_constraints would have computed from the mesh's refinement tree, which this world does not hold
+  std::vector<uint32_t> crow_dof, crow_col;
+  std::vector<uint64_t> crow_ptr;
+  std::vector<double> crow_coef, crow_val;
   // results
   std::vector<double> values, rhs;
   std::vector<uint8_t> touched;          // [nnz] 1 once SparseMatrix::add_matrix has added into the entry (zeros count: sparse_matrix.h:300-303)

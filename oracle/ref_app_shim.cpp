@@ -80,6 +80,14 @@ void DofMap::create_dof_constraints() {
       }
     }
   }
+  // rows loaded as such (ref_world_set_constraint_rows)
+  for (std::size_t c = 0; c < w.crow_dof.size(); ++c) {
+    DofConstraintRow row;
+    for (uint64_t k = w.crow_ptr[c]; k < w.crow_ptr[c + 1]; ++k) row[w.crow_col[k]] = w.crow_coef[k];
+    _dof_constraints[w.crow_dof[c]] = row;
+    if (w.crow_val[c] != 0.) _primal_constraint_values[w.crow_dof[c]] = w.crow_val[c];
+    else _primal_constraint_values.erase(w.crow_dof[c]);
+  }
 }
 
 // ---- FEBase ---------------------------------------------------------------------------------------------------------------------------
@@ -153,7 +161,7 @@ template <> void FEGenericBase<Real>::reinit(const Elem* elem, const unsigned in
 void EquationSystems::init() {
   RefWorldData& w = ref_world();
   for (auto& s : _systems) {
-    if (s->get_dof_map()._dirichlet.empty() && s->n_vars() != (unsigned int)w.n_vars) continue;  // an auxiliary system: not loaded
+    if (s->n_vars() != (unsigned int)w.n_vars && s->get_dof_map()._dirichlet.empty()) continue;  // an auxiliary system: not loaded
     libmesh_error_msg_if(s->n_vars() != (unsigned int)w.n_vars, "system " << s->name() << " has " << s->n_vars() << " variables, " << w.n_vars << " were loaded");
     s->get_dof_map().create_dof_constraints();
     w.con_dof.clear();
@@ -216,6 +224,17 @@ int ref_world_set_sides(int n_sides, const int16_t* bid) {
   RefWorldData& w = ref_world();
   w.n_sides = n_sides;
   w.side_bid.assign(bid, bid + w.n_elem() * (uint64_t)n_sides);
+  return 0;
+}
+
+// constraint rows given as such: hanging nodes (and Dirichlet rows as empty rows with a value), CSR over the constrained dofs
+int ref_world_set_constraint_rows(int64_t n, const uint32_t* dofs, const uint64_t* row_ptr, const uint32_t* cols, const double* coefs, const double* values) {
+  RefWorldData& w = ref_world();
+  w.crow_dof.assign(dofs, dofs + n);
+  w.crow_ptr.assign(row_ptr, row_ptr + n + 1);
+  w.crow_col.assign(cols, cols + row_ptr[n]);
+  w.crow_coef.assign(coefs, coefs + row_ptr[n]);
+  w.crow_val.assign(values, values + n);
   return 0;
 }
 

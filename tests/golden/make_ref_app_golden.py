@@ -1,10 +1,12 @@
-"""Writes tests/golden/reference_ex4_runs.npz and reference_ex6_runs.npz: the global matrix, right-hand side and Dirichlet constraints that the REFERENCE's
+"""Writes tests/golden/reference_ex4_runs.npz, reference_ex6_runs.npz and reference_hanging_runs.npz: the global matrix, right-hand side and Dirichlet constraints that the REFERENCE's
 own examples/introduction/introduction_ex4/introduction_ex4.C produces — its main() ("-d 3 -n N [-o FIRST]") or, for the meshes
 main() does not ask build_cube for, its assemble_poisson set up as main() does — compiled where it lies under /root/reference
 into oracle/_ref/libref_app.so (oracle/Makefile; oracle/ref_app/ref_world.h says what in that library is the reference's code
 and what is glue); for reference_ex6_runs.npz the same of LinearElasticity::assemble() of
 examples/systems_of_equations/systems_of_equations_ex6/systems_of_equations_ex6.C (three variables, traction on the max-x sides,
-homogeneous Dirichlet on the min-x side: BASELINE's config 5 in small).  Run here, where /root/reference exists; the .npz travels to the GPU box, where tests/test_golden_ref_app.py
+homogeneous Dirichlet on the min-x side: BASELINE's config 5 in small); for reference_hanging_runs.npz assemble_poisson on
+locally refined HEX8 / HEX27 meshes whose hanging-node rows go through the reference's own
+DofMap::heterogeneously_constrain_element_matrix_and_vector / build_constraint_matrix_and_vector.  Run here, where /root/reference exists; the .npz travels to the GPU box, where tests/test_golden_ref_app.py
 and tests/test_gpu_golden_ref.py compare the oracle and the CUDA path with it.
 
     python tests/golden/make_ref_app_golden.py
@@ -94,6 +96,57 @@ def main6():
     print(path, os.path.getsize(path), "bytes")
 
 
+# name, element type, n (coarse cells per side), refined block [lo, hi)^3
+CASES_H = [("hex8_hanging", O.HEX8, 4, 1, 3), ("hex27_hanging", O.HEX27, 3, 1, 2)]
+
+
+def exact(p):
+    return np.cos(.5 * np.pi * p[:, 0]) * np.sin(.5 * np.pi * p[:, 1]) * np.cos(.5 * np.pi * p[:, 2])
+
+
+def hanging_case(etype, n, lo, hi):
+    """(xyz, conn, mesh, system, elem dofs, ConstraintRows, pattern): the case of tests/test_gpu_constraints.py — hanging rows of
+    the refined block plus Dirichlet rows (the exact solution of ex4) on the boundary."""
+    sys.path.insert(0, os.path.join(ROOT, "tests"))
+    from hanging import refined_cube, refined_cube27
+    from oracle import constraints as OC
+
+    make = refined_cube27 if etype == O.HEX27 else refined_cube
+    xyz, conn, mask, hang = make(n, lambda i, j, k: lo <= i < hi and lo <= j < hi and lo <= k < hi)
+    m = O.Mesh.from_arrays(etype, xyz, conn, mask)
+    s = O.System(m, 1)
+    ed, nb, _ = s.dofs()
+    rows = {int(nb[h]): [(int(nb[v]), c) for v, c in lst] for h, lst in hang.items()}
+    vals = {}
+    bn = np.nonzero(mask)[0]
+    for node, v in zip(bn, exact(xyz[bn])):
+        rows[int(nb[node])] = []
+        vals[int(nb[node])] = float(v)
+    con = OC.ConstraintRows(rows, vals)
+    return xyz, conn, m, s, ed, con, OC.sparsity(con, ed, s.n_dofs)
+
+
+def reference_run_h(m, s, con, pattern, etype):
+    nnz, nd = R.load_world(m, s, (0, 0, 0), (0.0,) * 6, pattern=pattern)
+    R.load_constraint_rows(*con.arrays())
+    return R.assemble_ex4(1 if etype == O.HEX8 else 2, nnz, nd, boundary_ids=())
+
+
+def main_h():
+    out = {"names": np.array([c[0] for c in CASES_H])}
+    for name, etype, n, lo, hi in CASES_H:
+        xyz, conn, m, s, ed, con, pattern = hanging_case(etype, n, lo, hi)
+        r = reference_run_h(m, s, con, pattern, etype)
+        assert r["untouched_entries"] == 0
+        out[name + "/spec"] = np.array([etype, n, lo, hi], dtype=np.int64)
+        for k in ("values", "rhs"):
+            out[name + "/" + k] = r[k]
+        print(f"{name}: {len(r['values'])} entries, {len(r['rhs'])} dofs, {len(con.rows)} constraint rows")
+    path = os.path.join(ROOT, "tests", "golden", "reference_hanging_runs.npz")
+    np.savez_compressed(path, **out)
+    print(path, os.path.getsize(path), "bytes")
+
+
 def main():
     out = {"names": np.array([c[0] for c in CASES])}
     for name, etype, n, skew, order, through_main in CASES:
@@ -111,3 +164,4 @@ def main():
 if __name__ == "__main__":
     main()
     main6()
+    main_h()

@@ -61,3 +61,45 @@ def test_oracle_reproduces_the_references_own_elasticity_output(name):
     assert np.array_equal(cd, G6[name + "/con_dof"]) and np.array_equal(cv, G6[name + "/con_val"])
     assert np.array_equal(v, G6[name + "/values"])
     assert np.array_equal(r, G6[name + "/rhs"])
+
+
+GH = np.load(os.path.join(os.path.dirname(os.path.abspath(__file__)), "golden", "reference_hanging_runs.npz"))
+
+
+def golden_case_h(name):
+    """The locally refined mesh of a hanging-node golden case: (xyz, conn, mesh, system, elem dofs, ConstraintRows, (rp, ci))."""
+    import sys
+
+    sys.path.insert(0, os.path.dirname(os.path.abspath(__file__)))
+    from hanging import refined_cube, refined_cube27
+    from oracle import constraints as OC
+
+    etype, n, lo, hi = (int(x) for x in GH[name + "/spec"])
+    make = refined_cube27 if etype == O.HEX27 else refined_cube
+    xyz, conn, mask, hang = make(n, lambda i, j, k: lo <= i < hi and lo <= j < hi and lo <= k < hi)
+    m = O.Mesh.from_arrays(etype, xyz, conn, mask)
+    s = O.System(m, 1)
+    ed, nb, _ = s.dofs()
+    rows = {int(nb[h]): [(int(nb[v]), c) for v, c in lst] for h, lst in hang.items()}
+    vals = {}
+    bn = np.nonzero(mask)[0]
+    g = np.cos(.5 * np.pi * xyz[bn, 0]) * np.sin(.5 * np.pi * xyz[bn, 1]) * np.cos(.5 * np.pi * xyz[bn, 2])
+    for node, v in zip(bn, g):
+        rows[int(nb[node])] = []
+        vals[int(nb[node])] = float(v)
+    con = OC.ConstraintRows(rows, vals)
+    return xyz, conn, m, s, ed, con, OC.sparsity(con, ed, s.n_dofs)
+
+
+@pytest.mark.parametrize("name", [str(n) for n in GH["names"]])
+def test_constraint_restatement_reproduces_the_references_hanging_node_system(name):
+    """oracle/constraints.py (what the product's general-constraint kernels are tested against) against the global system the
+    reference's own element loop and constraint functions produced on a locally refined mesh."""
+    from oracle import constraints as OC
+
+    xyz, conn, m, s, ed, con, (rp, ci) = golden_case_h(name)
+    Ku, Fu = s.element_matrices(O.POISSON_EX4, constrained=False)
+    vo, ro = OC.assemble(con, ed, Ku, Fu, rp, ci)
+    assert len(vo) == len(GH[name + "/values"])
+    assert np.abs(vo - GH[name + "/values"]).max() <= 4e-16 * np.abs(vo).max()
+    assert np.abs(ro - GH[name + "/rhs"]).max() <= 4e-16 * max(np.abs(ro).max(), 1.0)

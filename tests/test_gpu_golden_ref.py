@@ -7,7 +7,7 @@ import numpy as np
 import pytest
 
 from conftest import PARITY_TOL, csr_parity_error, vec_parity_error
-from test_golden_ref_app import G, G6, golden_case, golden_case6
+from test_golden_ref_app import G, G6, GH, golden_case, golden_case6, golden_case_h
 from test_gpu_parity import make_ctx
 
 pytestmark = pytest.mark.gpu
@@ -53,4 +53,26 @@ def test_cuda_elasticity_against_the_references_own_output(name):
     v, r = ctx.get_values()
     assert csr_parity_error(v, G6[name + "/values"], rp) < PARITY_TOL
     assert vec_parity_error(r, G6[name + "/rhs"]) < PARITY_TOL
+    ctx.close()
+
+
+@pytest.mark.parametrize("name", [str(n) for n in GH["names"]])
+def test_cuda_hanging_node_assembly_against_the_references_own_output(name):
+    """feasm_set_constraint_rows: locally refined HEX8 / HEX27 meshes against the system the reference's own element loop and
+    DofMap::heterogeneously_constrain_element_matrix_and_vector produced (tests/golden/reference_hanging_runs.npz)."""
+    from libmesh_b200 import capi as F
+
+    xyz, conn, m, s, ed, con, (rp, ci) = golden_case_h(name)
+    ctx = F.Context(0)
+    ctx.set_mesh(m.elem_type, xyz, conn)
+    ctx.set_dofs(ed, s.n_dofs)
+    ctx.set_constraint_rows(*con.arrays())
+    ctx.build_pattern()
+    rp2, ci2 = ctx.get_pattern()
+    assert np.array_equal(rp, rp2) and np.array_equal(ci, ci2)
+    f_tab, _ = s.forcing_at_qps(0)
+    ctx.assemble(F.make_params(F.POISSON, 0, F.FORCING_TABULATED, f_host=f_tab))
+    v, r = ctx.get_values()
+    assert csr_parity_error(v, GH[name + "/values"], rp) < PARITY_TOL
+    assert vec_parity_error(r, GH[name + "/rhs"]) < PARITY_TOL
     ctx.close()

@@ -179,6 +179,30 @@ def test_hanging_node_rows_the_restatement_against_the_reference(which):
     assert widened > 0
 
 
+@pytest.mark.parametrize("which", ["hex8", "hex27"])
+def test_hanging_node_mesh_assembled_by_the_references_own_loop_and_constraint_code(which):
+    """assemble_poisson of introduction_ex4.C on a locally refined mesh, with the hanging-node and Dirichlet rows loaded into the
+    stub DofMap: every element goes through the reference's own heterogeneously_constrain_element_matrix_and_vector (widened dof
+    sets, C^T K C, C^T (F - K H)) and add_matrix.  The global system is oracle/constraints.py's (bitwise for HEX8's weights 1/2,
+    1/4; to rounding for HEX27, where numpy's matrix products sum in another order), and the pattern with the couplings
+    DofMap::find_connected_dofs adds is exactly the set of entries the loop adds into."""
+    sys.path.insert(0, os.path.join(os.path.dirname(os.path.abspath(__file__)), "golden"))
+    import make_ref_app_golden as G
+
+    name, etype, n, lo, hi = G.CASES_H[0 if which == "hex8" else 1]
+    xyz, conn, m, s, ed, con, (rp, ci) = G.hanging_case(etype, n, lo, hi)
+    out = G.reference_run_h(m, s, con, (rp, ci), etype)
+    assert out["untouched_entries"] == 0 and len(out["con_dof"]) == len(con.rows)
+    Ku, Fu = s.element_matrices(O.POISSON_EX4, constrained=False)
+    vo, ro = OC.assemble(con, ed, Ku, Fu, rp, ci)
+    assert np.abs(vo - out["values"]).max() <= 4e-16 * np.abs(vo).max()
+    assert np.abs(ro - out["rhs"]).max() <= 4e-16 * max(np.abs(ro).max(), 1.0)
+    if which == "hex8":
+        assert np.array_equal(vo, out["values"])
+    g = np.load(os.path.join(os.path.dirname(os.path.abspath(__file__)), "golden", "reference_hanging_runs.npz"))
+    assert np.array_equal(out["values"], g[name + "/values"]) and np.array_equal(out["rhs"], g[name + "/rhs"])
+
+
 def test_committed_golden_outputs_are_what_the_reference_gives_today():
     """tests/golden/reference_ex4_runs.npz (written by make_ref_app_golden.py) regenerated and compared."""
     sys.path.insert(0, os.path.join(os.path.dirname(os.path.abspath(__file__)), "golden"))
