@@ -58,6 +58,7 @@ $CXX -shared -o _ref/libref_app$SFX.so $OBJS -L_ref -lref_fe$SFX -Wl,-rpath,'$OR
 # ref_mesh/ref_mesh_world.h
 if [ -z "$SFX" ]; then
   python3 ref_excerpt.py "$REF" mesh_idx $GEN/ref_mesh_idx.inc
+  python3 ref_excerpt.py "$REF" mesh_so $GEN/ref_mesh_so_excerpts.inc
   python3 ref_excerpt.py "$REF" mesh $GEN/ref_mesh_excerpts.inc
   $CXX -std=c++17 $OPT -fPIC -shared -I_ref/inc -Iref_stubs -Iref_mesh -I$GEN -o _ref/libref_mesh.so ref_mesh_shim.cpp
 fi

@@ -19,13 +19,14 @@
  *                  functions: the GLOBAL matrix and right-hand side they produce are BIT-IDENTICAL to orc_assemble's, config 1
  *                  (20^3 HEX27) at full size included (tests/test_oracle_ref_app.py; golden outputs reference_ex{4,6}_runs.npz,
  *                  which tests/test_golden_ref_app.py and the GPU suite compare with on machines without /root/reference).
- *   libref_mesh.so the integer side — MeshTools::Generation::build_cube, ReplicatedMesh::renumber_nodes_and_elements,
+ *   libref_mesh.so the integer side — MeshTools::Generation::build_cube, UnstructuredMesh::all_second_order_range (TET10),
+ *                  ReplicatedMesh::renumber_nodes_and_elements,
  *                  DofMap::distribute_local_dofs_var_major, LinearPartitioner::partition_range — over a recording mesh: this
  *                  oracle's mesh (coordinates bitwise), node numbering, dof numbering and element shards ARE the reference's
  *                  (tests/test_oracle_ref_mesh.py); Hex8 ... Prism18::has_affine_map likewise (libref_fe.so), and the sparsity
  *                  pattern is exactly the set of entries the reference's element loop adds into (libref_app.so).
- * Still only restated: UnstructuredMesh::all_second_order (the last step of a TET10 mesh), the call order inside FE::reinit,
- * DirichletBoundary on LAGRANGE variables as nodal evaluation — held by the reference's unit-test known answers
+ * Still only restated (glue): the call order inside FE::reinit, dof_indices as a lookup, DirichletBoundary on LAGRANGE
+ * variables as nodal evaluation — held by the reference's unit-test known answers
  * (tests/fe/fe_test.h, tests/numerics/sparse_matrix_test.h, tests/systems/systems_test.C, tests/base/dof_map_test.C,
  * tests/mesh/mesh_generation_test.C) and its published run facts, restated in tests/test_oracle_*.py.
  *

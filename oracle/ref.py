@@ -311,7 +311,7 @@ def build_cube(elem: str, nx: int, ny: int, nz: int, bounds):
       xyz, conn, elem_id                                     after the renumbering (orphaned lattice nodes removed),
       sides = (element position, side, boundary id)          in the order the generator added them,
       second_order_requests, prepared.
-    TET10 comes back as the 24 TET4 per cell that all_second_order is then asked to raise, NOT renumbered (see ref_mesh_world.h)."""
+    For TET10 `before` holds the 24 TET4 per cell that the reference's own all_second_order then raises."""
     global _mesh_lib
     if _mesh_lib is None:
         L = C.CDLL(MESH_LIB_PATH)
@@ -337,7 +337,7 @@ def build_cube(elem: str, nx: int, ny: int, nz: int, bounds):
     xb, cb = np.zeros((int(bs[0]), 3)), np.zeros(int(bs[1]), dtype=np.uint32)
     _mesh_lib.ref_mesh_before(xb.ctypes.data, cb.ctypes.data)
     return dict(xyz=xyz, conn=conn, elem_id=eid, sides=(se, sn, sb), second_order_requests=int(sz[4]), prepared=bool(sz[5]),
-                before=(xb, cb.reshape(ne, npe)))
+                before=(xb, cb.reshape(ne, len(cb) // ne if ne else 0)))
 
 
 def distribute_dofs(n_vars: int, n_nodes: int):

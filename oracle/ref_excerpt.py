@@ -5,7 +5,7 @@ oracle/ref_stubs/ and oracle/ref_app/.  (The files as a whole — src/base/dof_m
 DofMap; src/fe/fe_boundary.C and h1_fe_transformation.C with their instantiations for every family; the element classes of
 src/geom/ — cannot be compiled stand-alone.)  Nothing is committed: the output goes under oracle/_ref/, which is git-ignored.
 
-    python3 ref_excerpt.py <reference root> <set: fe | app | mesh_idx | mesh> <output file>
+    python3 ref_excerpt.py <reference root> <set: fe | app | mesh_idx | mesh_so | mesh> <output file>
 """
 import re
 import sys
@@ -32,12 +32,20 @@ SETS = {
     "mesh_idx": [
         ("src/mesh/mesh_generation.C", r"^unsigned int idx\(const ElemType type,", FUNC_END, "inline\n"),
     ],
+    "mesh_so": [
+        ("src/mesh/unstructured_mesh.C", r"^map_hi_order_node\(unsigned int hon,", FUNC_END, "std::map<std::vector<dof_id_type>, Node *>::iterator\n"),
+        ("src/mesh/unstructured_mesh.C", r"^void transfer_elem\(Elem & lo_elem,", FUNC_END, ""),
+        ("src/mesh/unstructured_mesh.C", r"^all_increased_order_range \(UnstructuredMesh & mesh,", FUNC_END, "template <typename ElemTypeConverter>\nvoid\n"),
+    ],
     "mesh": [
         ("src/mesh/mesh_generation.C", r"^void MeshTools::Generation::build_cube\(", FUNC_END, ""),
         ("src/geom/cell_hex27.C", r"^const unsigned int Hex27::side_nodes_map\[", TABLE_END, ""),
         ("src/mesh/replicated_mesh.C", r"^void ReplicatedMesh::renumber_nodes_and_elements \(\)", FUNC_END, ""),
         ("src/base/dof_map.C", r"^void DofMap::distribute_local_dofs_var_major$", FUNC_END, ""),
         ("src/partitioning/linear_partitioner.C", r"^void LinearPartitioner::partition_range\(", FUNC_END, ""),
+        ("src/mesh/unstructured_mesh.C", r"^UnstructuredMesh::all_second_order_range \(", FUNC_END, "void\n"),
+        ("src/geom/elem.C", r"^ElemType Elem::second_order_equivalent_type \(const ElemType et,", FUNC_END, ""),
+        ("src/geom/cell_tet10.C", r"^const unsigned short int Tet10::_second_order_adjacent_vertices\[6\]\[2\] =", TABLE_END, ""),
     ],
     "app": [
         ("src/base/dof_map_constraints.C", r"^void DofMap::build_constraint_matrix \(", FUNC_END, ""),

@@ -6,11 +6,16 @@ namespace libMesh {
 namespace MeshTools { namespace Generation { namespace Private {
 #include "ref_mesh_idx.inc"  // unsigned int idx(type, nx, i, j) and idx(type, nx, ny, i, j, k), mesh_generation.C:81-157
 } } }
+namespace {
+#include "ref_mesh_so_excerpts.inc"  // map_hi_order_node, transfer_elem, all_increased_order_range: unstructured_mesh.C:60-587
+}
 #include "ref_mesh_excerpts.inc"  // void MeshTools::Generation::build_cube(...), mesh_generation.C:317-1938; Hex27::side_nodes_map;
                                   // void ReplicatedMesh::renumber_nodes_and_elements(), replicated_mesh.C:700-857;
                                   // void DofMap::distribute_local_dofs_var_major(...), dof_map.C:1417-1535;
                                   // void LinearPartitioner::partition_range(...), linear_partitioner.C:36-117
-void ReplicatedMesh::snapshot_before() {
+void UnstructuredMesh::snapshot_before() {
+  if (have_snapshot) return;
+  have_snapshot = true;
   xyz_before.clear();
   conn_before.clear();
   for (const Node* n : _nodes) for (int d = 0; d < 3; ++d) xyz_before.push_back(n ? (*n)(d) : 0.);

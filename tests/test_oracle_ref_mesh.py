@@ -4,8 +4,10 @@ run over a mesh that records what the generator does (oracle/ref_mesh/ref_mesh_w
 by the reference's own ReplicatedMesh::renumber_nodes_and_elements (src/mesh/replicated_mesh.C:700-857), the numbering step of
 prepare_for_use.  Compared BEFORE that step — lattice indexing, node coordinates (the reference's own scaling arithmetic —
 bitwise), connectivity in element order, the boundary id of every boundary side, for TET10 the 24-tet split of every cell — and
-AFTER it: the final node numbering and coordinates of HEX8 / HEX20 / HEX27 / PRISM18 meshes are the reference's.  (TET10's last
-step, UnstructuredMesh::all_second_order, is not run by that world and stays a restatement.)  Runs where /root/reference exists."""
+AFTER it: the final node numbering and coordinates of HEX8 / HEX20 / HEX27 / PRISM18 / TET10 meshes are the reference's — for
+TET10 through the reference's own UnstructuredMesh::all_second_order_range with all_increased_order_range / transfer_elem /
+map_hi_order_node (src/mesh/unstructured_mesh.C), Elem::second_order_equivalent_type and Tet10's mid-edge table, which raise the
+TET4 split and renumber.  Runs where /root/reference exists."""
 import numpy as np
 import pytest
 
@@ -44,10 +46,11 @@ def test_build_cube_before_renumbering_is_the_references(etype, dims, bounds):
         assert len(rx) == len(xyz)
 
 
-@pytest.mark.parametrize("etype", [O.HEX8, O.HEX20, O.HEX27, O.PRISM18], ids=lambda e: NAME[e])
+@pytest.mark.parametrize("etype", [O.HEX8, O.HEX20, O.HEX27, O.PRISM18, O.TET10], ids=lambda e: NAME[e])
 @pytest.mark.parametrize("dims", [(3, 2, 4), (1, 1, 1), (6, 6, 6)], ids=lambda d: "x".join(map(str, d)))
 def test_final_numbering_is_the_references_renumber_nodes_and_elements(etype, dims):
-    """The mesh as an assembly sees it: nodes renumbered in order of first touch by the elements, orphans removed."""
+    """The mesh as an assembly sees it: nodes renumbered in order of first touch by the elements, orphans removed; for TET10 after
+    the reference's all_second_order created the mid-edge nodes (coordinates: the mean of the two vertices, bitwise)."""
     for bounds in BOUNDS[:2]:
         r = R.build_cube(NAME[etype], *dims, bounds)
         xyz, conn, _ = O.Mesh(etype, *dims, bounds=bounds).arrays()
@@ -78,7 +81,7 @@ def test_reference_rejects_what_it_rejects():
         R.build_cube("QUAD9", 2, 2, 2, BOUNDS[0])
 
 
-@pytest.mark.parametrize("etype", [O.HEX8, O.HEX20, O.HEX27, O.PRISM18], ids=lambda e: NAME[e])
+@pytest.mark.parametrize("etype", [O.HEX8, O.HEX20, O.HEX27, O.PRISM18, O.TET10], ids=lambda e: NAME[e])
 @pytest.mark.parametrize("n_vars", [1, 3])
 def test_dof_numbering_is_the_references_distribute_local_dofs_var_major(etype, n_vars):
     """DofMap::distribute_local_dofs_var_major (src/base/dof_map.C:1417-1535, the reference's own definition) on the reference's
