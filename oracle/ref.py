@@ -185,6 +185,22 @@ def load_world(mesh, system, n, bounds, affine=None, pattern=None):
     return len(ci), system.n_dofs
 
 
+def load_world_arrays(elem: str, dims, bounds, xyz, conn, node_bmask, node_dof, row_ptr, col_idx, affine=None):
+    """The same from plain arrays — e.g. the mesh of build_cube() and the numbering of distribute_dofs() below, so that nothing the
+    world is loaded with comes from the oracle: node_dof [n_vars][n_nodes], node_bmask [n_nodes] (bit b: on boundary id b)."""
+    xyz = np.ascontiguousarray(xyz, dtype=np.float64)
+    conn = np.ascontiguousarray(conn, dtype=np.uint32)
+    mask = np.ascontiguousarray(node_bmask, dtype=np.uint8)
+    node_dof = np.ascontiguousarray(node_dof, dtype=np.uint32).reshape(-1, xyz.shape[0])
+    affine = np.full(conn.shape[0], 255, dtype=np.uint8) if affine is None else np.ascontiguousarray(affine, dtype=np.uint8)
+    rp, ci = np.ascontiguousarray(row_ptr, dtype=np.uint64), np.ascontiguousarray(col_idx, dtype=np.uint32)
+    b = np.ascontiguousarray(bounds, dtype=np.float64)
+    n_dofs = len(rp) - 1
+    app().ref_world_load(ELEM[elem], conn.shape[1], dims[0], dims[1], dims[2], b.ctypes.data, xyz.shape[0], xyz.ctypes.data, conn.shape[0], conn.ctypes.data,
+                         affine.ctypes.data, mask.ctypes.data, node_dof.shape[0], n_dofs, node_dof.ctypes.data, rp.ctypes.data, ci.ctypes.data)
+    return len(ci), n_dofs
+
+
 def _results(nnz, n_dofs):
     values, rhs = np.zeros(nnz), np.zeros(n_dofs)
     nc = app().ref_world_results(None, None, None, None)

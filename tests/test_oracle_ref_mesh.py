@@ -109,3 +109,39 @@ def test_linear_partitioner_is_the_references(dims, n_parts):
     m = O.Mesh(O.HEX27, *dims, bounds=BOUNDS[0])
     m.partition_linear(n_parts)
     assert np.array_equal(pid, m.partition()[0])
+
+
+@pytest.mark.skipif(not R.app_available(), reason="oracle/_ref/libref_app.so not built")
+@pytest.mark.parametrize("etype,n,order,through_main", [(O.HEX27, 4, 2, True), (O.HEX8, 5, 1, True), (O.TET10, 2, 2, False), (O.HEX20, 3, 2, False),
+                                                        (O.PRISM18, 3, 2, False)], ids=lambda v: NAME.get(v, str(v)) if isinstance(v, int) and v in NAME else str(v))
+def test_the_whole_chain_by_the_references_own_code(etype, n, order, through_main):
+    """Nothing of the oracle goes IN: the mesh is the reference's build_cube (+ all_second_order for TET10) after its own
+    renumbering, the dof numbering its distribute_local_dofs_var_major, the sparsity graph the element-couples-its-dofs definition
+    written out in numpy, the boundary nodes a coordinate test; then main() / assemble_poisson of introduction_ex4.C assemble over
+    them.  What comes OUT — the global matrix, the right-hand side, the Dirichlet set — is the oracle's, bit for bit."""
+    bounds = BOUNDS[0]
+    r = R.build_cube(NAME[etype], n, n, n, bounds)
+    xyz, conn = r["xyz"], r["conn"]
+    n_dofs, base = R.distribute_dofs(1, len(xyz))
+    ed = base[conn]
+    # SparsityPattern::Build for one variable without constraints: every element couples all of its dofs
+    pairs = np.unique((ed[:, :, None].astype(np.int64) * n_dofs + ed[:, None, :]).reshape(-1))
+    rows, cols = pairs // n_dofs, pairs % n_dofs
+    rp = np.zeros(n_dofs + 1, dtype=np.uint64)
+    rp[1:] = np.cumsum(np.bincount(rows, minlength=n_dofs))
+    mask = np.zeros(len(xyz), dtype=np.uint8)  # build_cube's ids: 0 min z, 1 min y, 2 max x, 3 max y, 4 min x, 5 max z
+    for b, (axis, value) in enumerate([(2, bounds[4]), (1, bounds[2]), (0, bounds[1]), (1, bounds[3]), (0, bounds[0]), (2, bounds[5])]):
+        mask[xyz[:, axis] == value] |= 1 << b
+    node_dof = base[None, :]
+    nnz, nd = R.load_world_arrays(NAME[etype], (n, n, n), bounds, xyz, conn, mask, node_dof, rp, cols.astype(np.uint32))
+    out = R.run_ex4(["-d", 3, "-n", n] + (["-o", "FIRST"] if order == 1 else []), nnz, nd) if through_main else R.assemble_ex4(order, nnz, nd)
+    assert out["untouched_entries"] == 0
+    m = O.Mesh(etype, n, n, n, bounds=bounds)
+    s = O.System(m, 1)
+    s.add_dirichlet((0, 1, 2, 3, 4, 5), 0)
+    rp0, ci0 = s.sparsity()
+    assert np.array_equal(rp0, rp) and np.array_equal(ci0, cols)
+    v, rhs, _ = s.assemble(O.POISSON_EX4)
+    cd, cv = s.constraints()
+    assert np.array_equal(cd, out["con_dof"]) and np.array_equal(cv, out["con_val"])
+    assert np.array_equal(v, out["values"]) and np.array_equal(rhs, out["rhs"])
