@@ -87,7 +87,8 @@ def test_config_1_at_full_size():
 # ---- systems_of_equations_ex6.C: LinearElasticity::assemble() -----------------------------------------------------------------------
 EX6_BOUNDS = (0.0, 1.0, 0.0, 0.3, 0.0, 0.1)
 EX6 = [("hex8_as_the_example_runs_it", O.HEX8, (8, 4, 2), None, 1), ("hex8_perturbed", O.HEX8, (4, 3, 3), (1, 0.004, 11), 1),
-       ("hex27_config5_small", O.HEX27, (4, 3, 2), None, 2), ("hex27_perturbed", O.HEX27, (3, 2, 2), (1, 0.004, 7), 2)]
+       ("hex27_config5_small", O.HEX27, (4, 3, 2), None, 2), ("hex27_perturbed", O.HEX27, (3, 2, 2), (1, 0.004, 7), 2),
+       ("hex27_config5_cube_8", O.HEX27, (8, 8, 8), None, 2)]  # BASELINE config 5's mesh shape (n^3 HEX27 on the ex6 bar) at n = 8: 14 739 dofs
 
 
 @pytest.mark.parametrize("name,etype,dims,skew,order", EX6, ids=[c[0] for c in EX6])
