@@ -938,10 +938,10 @@ def reference_code_ranks(args, warmup: int = 1, steps: int = 2):
 
     if args.problem != "poisson" or not R.app_available(fast=True):
         return None
-    n_ranks = os.cpu_count() or 1
     n, b, _ = problem_dims(args)
     etype = ELEM[args.elem]
     n_elem = {10: 24, 18: 2}.get(etype, 1) * n ** 3
+    n_ranks = max(1, min(os.cpu_count() or 1, n_elem // 32))  # a rank without elements is not a rank
     ctx = mp.get_context("spawn")  # fresh processes: nothing of this one's OpenMP or CUDA state is inherited
     barrier, out = ctx.Barrier(n_ranks), ctx.Queue()
     order = 1 if args.elem == "hex8" else 2
