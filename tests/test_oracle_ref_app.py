@@ -76,12 +76,14 @@ def test_assemble_poisson_on_every_family_and_both_map_branches(name, etype, n, 
     _same(s, R.assemble_ex4(order, nnz, nd))
 
 
-def test_config_1_at_full_size():
-    """BASELINE.json configs[0]: 20^3 HEX27, 8 000 elements, 68 921 dofs — every one of the 4.1 M entries bitwise."""
-    m, s = _case(O.HEX27, 20)
-    nnz, nd = R.load_world(m, s, 20, BOUNDS)
-    assert nd == 41 ** 3
-    _same(s, R.run_ex4(["-d", 3, "-n", 20], nnz, nd))
+@pytest.mark.parametrize("n", [20, 32])
+def test_config_1_at_full_size(n):
+    """BASELINE.json configs[0]: 20^3 HEX27, 8 000 elements, 68 921 dofs — every one of the 4.1 M entries bitwise; and 32^3
+    (32 768 elements, 17 M entries), the size of the GPU suite's largest HEX27 parity case."""
+    m, s = _case(O.HEX27, n)
+    nnz, nd = R.load_world(m, s, n, BOUNDS)
+    assert nd == (2 * n + 1) ** 3
+    _same(s, R.run_ex4(["-d", 3, "-n", n], nnz, nd))
 
 
 # ---- systems_of_equations_ex6.C: LinearElasticity::assemble() -----------------------------------------------------------------------
