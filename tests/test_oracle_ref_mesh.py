@@ -145,3 +145,33 @@ def test_the_whole_chain_by_the_references_own_code(etype, n, order, through_mai
     cd, cv = s.constraints()
     assert np.array_equal(cd, out["con_dof"]) and np.array_equal(cv, out["con_val"])
     assert np.array_equal(v, out["values"]) and np.array_equal(rhs, out["rhs"])
+
+
+# ---- PRODUCT host code against the reference's own generator and numbering, directly (no GPU: host entry points of libfeasm.so) -----
+@pytest.mark.parametrize("etype", [O.HEX8, O.HEX20, O.HEX27, O.PRISM18, O.TET10], ids=lambda e: NAME[e])
+def test_product_build_cube_is_the_references_generator(etype):
+    """feasm_build_cube (libmesh_b200/csrc/feasm_host.cpp, written independently of the oracle) against the record of the
+    reference's own build_cube: the lattice nodes an element uses in ascending id order (the product does not renumber nodes by
+    first touch — its dof numbering, below, does not depend on that), coordinates bitwise, connectivity; TET10: the four vertices
+    of every tet of the reference's 24-split."""
+    from libmesh_b200 import capi as F
+
+    for dims, bounds in [((3, 2, 4), BOUNDS[1]), ((2, 2, 2), BOUNDS[0])]:
+        xyz, conn, _ = F.build_cube(etype, *dims, bounds)
+        rc, rx = _compacted(R.build_cube(NAME[etype], *dims, bounds))
+        nv = rc.shape[1]
+        assert np.array_equal(conn[:, :nv], rc) and np.array_equal(xyz[: len(rx)], rx)
+
+
+@pytest.mark.parametrize("etype", [O.HEX8, O.HEX27, O.TET10], ids=lambda e: NAME[e])
+@pytest.mark.parametrize("n_vars", [1, 3])
+def test_product_dof_numbering_is_the_references(etype, n_vars):
+    """feasm_distribute_dofs (host) on the reference's own finished mesh against the reference's own
+    DofMap::distribute_local_dofs_var_major."""
+    from libmesh_b200 import capi as F
+
+    r = R.build_cube(NAME[etype], 3, 2, 2, BOUNDS[0])
+    n_dofs, base = R.distribute_dofs(n_vars, len(r["xyz"]))
+    n, pbase, first, _ = F.distribute_dofs(r["conn"], len(r["xyz"]), n_vars, 1, np.zeros(len(r["conn"]), dtype=np.int32))
+    assert n == n_dofs and np.array_equal(pbase, base) and first.tolist() == [0, n_dofs]
+    assert np.array_equal(F.elem_dofs_from_nodes(r["conn"], pbase, n_vars), np.concatenate([base[r["conn"]] + v for v in range(n_vars)], axis=1))
