@@ -165,8 +165,6 @@ def load_world(mesh, system, n, bounds, affine=None, pattern=None):
     """Hands the stub world the integer structures of an oracle Mesh / System (oracle.py): the mesh that build_cube(n, n, n,
     bounds) is going to be asked for, the dof of every (variable, node), and the sparsity pattern (the system's own, or the
     one given: with constraint rows the Graph holds the couplings DofMap::find_connected_dofs adds)."""
-    from . import oracle as O
-
     xyz, conn, mask = mesh.arrays()
     ed, _, _ = system.dofs()
     npe, nv, nn = mesh.npe, system.n_vars, mesh.n_nodes
